@@ -1,0 +1,191 @@
+"""ctypes binding of the UNMODIFIED reference built by oracle/Makefile.ref into oracle/_ref/<variant>/.
+
+TEST INFRASTRUCTURE ONLY (checker for the oracle, golden-vector generator, timed CPU baseline).
+Nothing here reads /root/reference at run time; it only loads the prebuilt libraries.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K, Q8_K = 0, 2, 8, 9, 12, 14, 15
+_NAMES = {Q4_0: "q4_0", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q6_K: "q6_K", Q8_K: "q8_K"}
+
+
+def cpu_flags():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    return set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def best_variant():
+    fl = cpu_flags()
+    need512 = {"avx512f", "avx512bw", "avx512vl", "avx512dq", "avx512cd", "avx512_vnni", "avx512vbmi"}
+    order = []
+    if need512 <= fl:
+        order.append("avx512")
+    if {"avx2", "fma", "f16c", "bmi2"} <= fl:
+        order.append("avx2")
+    order.append("scalar")
+    for v in order:
+        if os.path.exists(os.path.join(HERE, "_ref", v, "libggml-cpu.so")):
+            return v
+    return None
+
+
+def ref_dir(variant=None):
+    v = variant or best_variant()
+    return None if v is None else os.path.join(HERE, "_ref", v)
+
+
+class Ref:
+    def __init__(self, variant=None):
+        d = ref_dir(variant)
+        if d is None or not os.path.exists(os.path.join(d, "libggml-cpu.so")):
+            raise FileNotFoundError("oracle/_ref not built (run: make -f oracle/Makefile.ref VARIANT=...)")
+        self.dir = d
+        self.variant = os.path.basename(d)
+        self.base = C.CDLL(os.path.join(d, "libggml-base.so"), mode=C.RTLD_GLOBAL)
+        self.cpu = C.CDLL(os.path.join(d, "libggml-cpu.so"), mode=C.RTLD_GLOBAL)
+        self.base.ggml_quantize_chunk.restype = C.c_size_t
+        self.base.ggml_quantize_chunk.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+        self.base.ggml_row_size.restype = C.c_size_t
+        self.base.ggml_row_size.argtypes = [C.c_int, C.c_int64]
+        self.cpu.ggml_cpu_init()
+
+    @staticmethod
+    def _p(a):
+        return a.ctypes.data_as(C.c_void_p)
+
+    def row_size(self, t, k):
+        return self.base.ggml_row_size(t, k)
+
+    def quantize_chunk(self, t, x):
+        """ggml_quantize_chunk (ggml.c) — how test-backend-ops makes quantised tensors."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.shape
+        out = np.zeros((rows, self.row_size(t, k)), dtype=np.uint8)
+        self.base.ggml_quantize_chunk(t, self._p(x), self._p(out), 0, rows, k, None)
+        return out
+
+    def quantize_row_ref(self, t, x):
+        """quantize_row_<t>_ref (ggml-quants.c)"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.shape
+        out = np.zeros((rows, self.row_size(t, k)), dtype=np.uint8)
+        f = getattr(self.base, "quantize_row_%s_ref" % _NAMES[t])
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        for r in range(rows):
+            f(self._p(x[r]), self._p(out[r]), k)
+        return out
+
+    def quantize_row_cpu(self, t, x):
+        """quantize_row_<t> (ggml-cpu-quants.c; SIMD from_float used by ggml-cpu MUL_MAT)"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.shape
+        out = np.zeros((rows, self.row_size(t, k)), dtype=np.uint8)
+        f = getattr(self.cpu, "quantize_row_%s" % _NAMES[t])
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        for r in range(rows):
+            f(self._p(x[r]), self._p(out[r]), k)
+        return out
+
+    def dequantize(self, t, w, k):
+        w = np.ascontiguousarray(w, dtype=np.uint8)
+        out = np.empty((w.shape[0], k), dtype=np.float32)
+        f = getattr(self.base, "dequantize_row_%s" % _NAMES[t])
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        for r in range(w.shape[0]):
+            f(self._p(w[r]), self._p(out[r]), k)
+        return out
+
+    def vec_dot(self, t, k, wrow, arow):
+        """ggml_vec_dot_<t>_<q8_0|q8_K> (ggml-cpu-quants.c)"""
+        at = "q8_K" if t in (Q4_K, Q6_K) else "q8_0"
+        f = getattr(self.cpu, "ggml_vec_dot_%s_%s" % (_NAMES[t], at))
+        f.restype = None
+        f.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_int]
+        s = C.c_float(0)
+        f(k, C.byref(s), 0, self._p(np.ascontiguousarray(wrow)), 0, self._p(np.ascontiguousarray(arow)), 0, 1)
+        return s.value
+
+    # ---- full graph through ggml-cpu (ggml_compute_forward_mul_mat / add), the parity oracle of north_star
+    class _InitParams(C.Structure):
+        _fields_ = [("mem_size", C.c_size_t), ("mem_buffer", C.c_void_p), ("no_alloc", C.c_bool)]
+
+    def _ctx(self, nbytes):
+        b = self.base
+        b.ggml_init.restype = C.c_void_p
+        b.ggml_init.argtypes = [Ref._InitParams]
+        for n in ("ggml_new_tensor_2d",):
+            getattr(b, n).restype = C.c_void_p
+        b.ggml_new_tensor_2d.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64]
+        b.ggml_new_tensor_4d.restype = C.c_void_p
+        b.ggml_new_tensor_4d.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64]
+        b.ggml_mul_mat.restype = C.c_void_p
+        b.ggml_mul_mat.argtypes = [C.c_void_p] * 3
+        b.ggml_add.restype = C.c_void_p
+        b.ggml_add.argtypes = [C.c_void_p] * 3
+        b.ggml_new_graph.restype = C.c_void_p
+        b.ggml_new_graph.argtypes = [C.c_void_p]
+        b.ggml_build_forward_expand.restype = None
+        b.ggml_build_forward_expand.argtypes = [C.c_void_p, C.c_void_p]
+        b.ggml_get_data.restype = C.c_void_p
+        b.ggml_get_data.argtypes = [C.c_void_p]
+        b.ggml_nbytes.restype = C.c_size_t
+        b.ggml_nbytes.argtypes = [C.c_void_p]
+        b.ggml_free.argtypes = [C.c_void_p]
+        self.cpu.ggml_graph_compute_with_ctx.restype = C.c_int
+        self.cpu.ggml_graph_compute_with_ctx.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        return b.ggml_init(Ref._InitParams(nbytes, None, False))
+
+    def mul_mat(self, t, w, x, n_threads=1):
+        """dst[N, M] = ggml_mul_mat(W[type t, M rows of K], X[f32, N rows of K]) on ggml-cpu."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        w = np.ascontiguousarray(w)
+        N, K = x.shape
+        M = w.shape[0]
+        ctx = self._ctx(w.nbytes + x.nbytes + 4 * N * M + 2 * (x.nbytes + 4096) * max(1, n_threads) + (64 << 20))
+        b = self.base
+        tw = b.ggml_new_tensor_2d(ctx, t, K, M)
+        tx = b.ggml_new_tensor_2d(ctx, F32, K, N)
+        assert b.ggml_nbytes(tw) == w.nbytes, (b.ggml_nbytes(tw), w.nbytes)
+        C.memmove(b.ggml_get_data(tw), self._p(w), w.nbytes)
+        C.memmove(b.ggml_get_data(tx), self._p(x), x.nbytes)
+        td = b.ggml_mul_mat(ctx, tw, tx)
+        g = b.ggml_new_graph(ctx)
+        b.ggml_build_forward_expand(g, td)
+        rc = self.cpu.ggml_graph_compute_with_ctx(ctx, g, n_threads)
+        assert rc == 0
+        out = np.empty((N, M), dtype=np.float32)
+        C.memmove(self._p(out), b.ggml_get_data(td), out.nbytes)
+        b.ggml_free(ctx)
+        return out
+
+    def add(self, a, bb, n_threads=1):
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        bb = np.ascontiguousarray(bb, dtype=np.float32)
+        a4 = a.reshape((1,) * (4 - a.ndim) + a.shape)
+        b4 = bb.reshape((1,) * (4 - bb.ndim) + bb.shape)
+        ctx = self._ctx(2 * a.nbytes + bb.nbytes + (16 << 20))
+        b = self.base
+        ta = b.ggml_new_tensor_4d(ctx, F32, *a4.shape[::-1])
+        tb = b.ggml_new_tensor_4d(ctx, F32, *b4.shape[::-1])
+        C.memmove(b.ggml_get_data(ta), self._p(a4), a4.nbytes)
+        C.memmove(b.ggml_get_data(tb), self._p(b4), b4.nbytes)
+        td = b.ggml_add(ctx, ta, tb)
+        g = b.ggml_new_graph(ctx)
+        b.ggml_build_forward_expand(g, td)
+        assert self.cpu.ggml_graph_compute_with_ctx(ctx, g, n_threads) == 0
+        out = np.empty_like(a4)
+        C.memmove(self._p(out), b.ggml_get_data(td), out.nbytes)
+        b.ggml_free(ctx)
+        return out.reshape(a.shape)
