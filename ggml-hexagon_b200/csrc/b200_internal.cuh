@@ -1,0 +1,98 @@
+// b200_internal.cuh — shared declarations of the B200 op layer (device layouts + launchers).
+// Not part of the public C-ABI (include/ggml_b200_ops.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace b200 {
+
+enum : int { T_F32 = 0, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q6_K = 14 };
+
+// ---------------------------------------------------------------- HBM layout of quantised weights
+// A weight allocation of T blocks keeps the native byte count (T * block_bytes) but stores the
+// fields of all blocks as separate arrays ("SoA"), so that every hot load is a naturally aligned
+// 128-bit load and consecutive lanes read consecutive 16 B:
+//   q4_0 : [qs  T x 16 B][d  T x f16]
+//   q8_0 : [qs  T x 32 B][d  T x f16]
+//   q4_K : [qs  T x 128 B][hdr T x 16 B = f16 d, f16 dmin, 12 B packed scales/mins]
+//   q6_K : [ql  T x 128 B][qh T x 64 B][sc T x 16 x i8][d T x f16]
+// Native layouts: ggml/src/ggml-common.h:167-172 (q4_0), :211-215 (q8_0), :285-296 (q4_K), :320-326 (q6_K).
+struct WFields {            // field table used by the repack kernels (native offset, size), SoA order
+    int n;
+    int native_off[4];
+    int size[4];
+    int block_bytes;
+};
+
+__host__ __device__ inline WFields wfields(int type) {
+    WFields f{};
+    switch (type) {
+        case T_Q4_0: f.n = 2; f.native_off[0] = 2;  f.size[0] = 16;  f.native_off[1] = 0;  f.size[1] = 2;  f.block_bytes = 18;  break;
+        case T_Q8_0: f.n = 2; f.native_off[0] = 2;  f.size[0] = 32;  f.native_off[1] = 0;  f.size[1] = 2;  f.block_bytes = 34;  break;
+        case T_Q4_K: f.n = 2; f.native_off[0] = 16; f.size[0] = 128; f.native_off[1] = 0;  f.size[1] = 16; f.block_bytes = 144; break;
+        case T_Q6_K: f.n = 4; f.native_off[0] = 0;  f.size[0] = 128; f.native_off[1] = 128; f.size[1] = 64;
+                              f.native_off[2] = 192; f.size[2] = 16; f.native_off[3] = 208; f.size[3] = 2; f.block_bytes = 210; break;
+        default: f.n = 0; f.block_bytes = 0;
+    }
+    return f;
+}
+
+inline int block_elems(int type) { return type == T_F32 ? 1 : (type == T_Q4_K || type == T_Q6_K) ? 256 : 32; }
+inline int block_bytes(int type) { return type == T_F32 ? 4 : type == T_Q8_1 ? 36 : wfields(type).block_bytes; }
+
+// pointers to the field arrays, already offset to the first block of the tensor at hand
+struct WPtrs { const uint8_t * p[4]; };
+
+inline WPtrs wptrs(int type, const void * base, int64_t T, int64_t first) {
+    WFields f = wfields(type);
+    WPtrs w{};
+    const uint8_t * b = (const uint8_t *) base;
+    int64_t off = 0;
+    for (int i = 0; i < f.n; i++) { w.p[i] = b + off + first * f.size[i]; off += T * f.size[i]; }
+    return w;
+}
+
+// ---------------------------------------------------------------- activation scratch (q8_1, SoA, two planes)
+// For a column of K f32 activations (NB = K/32 blocks):
+//   qs : int8 [2][NB][16]  plane 0 = elements 0..15 of each block, plane 1 = elements 16..31
+//   ds : {float d (the fp16-rounded scale of quantize_row_q8_1_ref), int16 isum0, int16 isum1} [NB]
+//        isum_p = exact integer sum of the 16 quants of plane p
+struct ActDS { float d; short isum0; short isum1; };
+static_assert(sizeof(ActDS) == 8, "ActDS");
+
+struct ActView {            // N columns
+    const int8_t * qs; const ActDS * ds;
+    int64_t NB;             // blocks per column
+};
+
+// ---------------------------------------------------------------- launchers (each returns cudaGetLastError())
+// x: f32, row r at (const char*)x + r*row_stride_bytes.
+cudaError_t launch_quantize_q8_1_soa(const float * x, int64_t row_stride_bytes, int64_t K, int64_t nrows,
+                                     int8_t * qs, ActDS * ds, cudaStream_t st);
+cudaError_t launch_quantize_q8_1_aos(const float * x, int64_t K, int64_t nrows, void * y, cudaStream_t st);
+
+// dst[c*dst_col_stride + m] for m < M, c < ncols (<= 8). `pdl`: launch with programmatic stream serialization.
+cudaError_t launch_gemv_q(int type, WPtrs w, int64_t M, int64_t K, ActView act, int ncols,
+                          float * dst, int64_t dst_col_stride, cudaStream_t st, bool pdl);
+// f32 weights (row stride in bytes), f32 activations (col stride bytes)
+cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, int64_t K,
+                            const float * x, int64_t x_col_stride, int ncols,
+                            float * dst, int64_t dst_col_stride, cudaStream_t st);
+// scratch: sq = int8[K], sd = ActDS[K/32] (two-plane copy of a_qs built inside the kernel)
+cudaError_t launch_block_dots_impl(int type, WPtrs w, int64_t K, const int8_t * a_qs, int32_t * out,
+                                   int8_t * sq, ActDS * sd, cudaStream_t st);
+
+struct AddArgs {
+    const char * a; const char * b; char * d;
+    int64_t ne[4];      // dst / src0 shape
+    int64_t neb[4];     // src1 shape
+    int64_t nba[4], nbb[4], nbd[4];   // byte strides
+};
+cudaError_t launch_add_f32(const AddArgs & a, cudaStream_t st);
+
+cudaError_t launch_repack(int type, bool to_soa, uint8_t * soa_base, int64_t T, int64_t first, int64_t n,
+                          uint8_t * native, cudaStream_t st);
+cudaError_t launch_fill(void * p, size_t n_bytes, uint32_t v, cudaStream_t st);
+
+}  // namespace b200

@@ -1,0 +1,523 @@
+// ops_api.cu — implementation of the C-ABI declared in include/ggml_b200_ops.h.
+// Host-side runtime of the op layer: context (device, stream, scratch), argument validation, dispatch to the
+// kernels, CUDA-graph cache for node lists, staging for host-pointer tensors, NCCL row-split.
+// No CPU compute path exists here: every op is a kernel launch or an error.
+#include "../../include/ggml_b200_ops.h"
+#include "b200_internal.cuh"
+
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+static int fail(int code, const char * fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+    return code;
+}
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return fail(e_ == cudaErrorMemoryAllocation ? B200_ENOMEM : B200_ECUDA, "%s -> %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+extern "C" const char * b200_last_error(void) { return g_err; }
+
+// ------------------------------------------------------------------------------------------------ NCCL (dlopen'ed)
+typedef struct { char internal[128]; } nccl_uid;
+typedef void * nccl_comm;
+struct NcclApi {
+    void * lib = nullptr;
+    int (*GetUniqueId)(nccl_uid *) = nullptr;
+    int (*CommInitRank)(nccl_comm *, int, nccl_uid, int) = nullptr;
+    int (*CommDestroy)(nccl_comm) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, nccl_comm, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char * (*GetErrorString)(int) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+static int nccl_load() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.lib) return 0;
+    const char * names[] = { "libnccl.so.2", "libnccl.so" };
+    void * l = nullptr;
+    for (const char * n : names) { l = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (l) break; }
+    if (!l) return fail(B200_ENCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define SYM(f) *(void **) &g_nccl.f = dlsym(l, "nccl" #f); if (!g_nccl.f) return fail(B200_ENCCL, "nccl" #f " missing")
+    SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(AllGather); SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
+#undef SYM
+    g_nccl.lib = l;
+    return 0;
+}
+#define NC(call) do { int r_ = (call); if (r_ != 0) return fail(B200_ENCCL, "%s -> %s", #call, g_nccl.GetErrorString(r_)); } while (0)
+
+// ------------------------------------------------------------------------------------------------ context
+struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; };
+
+struct Ctx {
+    uint64_t magic = 0xB200B200B200B200ull;
+    int dev = 0;
+    cudaStream_t st = nullptr;
+    // q8_1 activation scratch (two-plane SoA), capacity in 32-element blocks
+    int8_t * act_qs = nullptr; ActDS * act_ds = nullptr; int64_t act_cap = 0;
+    // device staging (host tensors, repack)
+    uint8_t * stage = nullptr; size_t stage_cap = 0;
+    uint8_t * flush = nullptr; size_t flush_bytes = 0;
+    int64_t launches = 0;
+    bool in_graph = false;        // inside b200_graph_compute: src1 quantisation may be reused between nodes
+    const void * q_ptr = nullptr; int64_t q_K = 0, q_N = 0, q_stride = 0;
+    std::unordered_map<uint64_t, GraphEntry> graphs;
+    // row split
+    nccl_comm comm = nullptr; int rank = 0, world = 1;
+};
+
+static Ctx * ctx_of(b200_handle h) {
+    Ctx * c = (Ctx *) (uintptr_t) h;
+    if (!c || c->magic != 0xB200B200B200B200ull) return nullptr;
+    return c;
+}
+#define CTX(h) Ctx * c = ctx_of(h); if (!c) return fail(B200_EINVAL, "bad handle"); \
+    { cudaError_t e_ = cudaSetDevice(c->dev); if (e_ != cudaSuccess) return fail(B200_ECUDA, "cudaSetDevice: %s", cudaGetErrorString(e_)); }
+
+static int ensure_act(Ctx * c, int64_t blocks) {
+    if (blocks <= c->act_cap) return 0;
+    if (c->act_qs) { CU(cudaStreamSynchronize(c->st)); cudaFree(c->act_qs); cudaFree(c->act_ds); c->act_qs = nullptr; c->act_ds = nullptr; c->act_cap = 0; }
+    int64_t cap = blocks < 4096 ? 4096 : blocks;
+    CU(cudaMalloc((void **) &c->act_qs, (size_t) cap * 32));
+    CU(cudaMalloc((void **) &c->act_ds, (size_t) cap * sizeof(ActDS)));
+    c->act_cap = cap;
+    c->q_ptr = nullptr;
+    return 0;
+}
+static int ensure_stage(Ctx * c, size_t bytes) {
+    if (bytes <= c->stage_cap) return 0;
+    if (c->stage) { CU(cudaStreamSynchronize(c->st)); cudaFree(c->stage); c->stage = nullptr; c->stage_cap = 0; }
+    size_t cap = bytes < (size_t) (1 << 20) ? (size_t) (1 << 20) : bytes;
+    CU(cudaMalloc((void **) &c->stage, cap));
+    c->stage_cap = cap;
+    return 0;
+}
+
+extern "C" int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int b200_device_info(int device, char * name, int len, int64_t * total, int64_t * free_b, int32_t * sms) {
+    cudaDeviceProp p;
+    CU(cudaGetDeviceProperties(&p, device));
+    if (name && len > 0) { strncpy(name, p.name, len - 1); name[len - 1] = 0; }
+    if (sms) *sms = p.multiProcessorCount;
+    if (total || free_b) {
+        int cur = 0; cudaGetDevice(&cur);
+        CU(cudaSetDevice(device));
+        size_t f = 0, t = 0;
+        CU(cudaMemGetInfo(&f, &t));
+        if (total) *total = (int64_t) t;
+        if (free_b) *free_b = (int64_t) f;
+        cudaSetDevice(cur);
+    }
+    return 0;
+}
+
+extern "C" int b200_open(const char * uri, b200_handle * h) {
+    if (!h) return fail(B200_EINVAL, "h is NULL");
+    int dev = 0;
+    if (uri && *uri) {
+        if (strncmp(uri, "cuda:", 5) != 0) return fail(B200_EINVAL, "uri must be cuda:<ordinal>, got '%s'", uri);
+        dev = atoi(uri + 5);
+    }
+    int n = b200_device_count();
+    if (n <= 0) return fail(B200_ENODEV, "no CUDA device visible (the B200 op layer has no CPU fallback)");
+    if (dev < 0 || dev >= n) return fail(B200_ENODEV, "device %d out of range (%d visible)", dev, n);
+    CU(cudaSetDevice(dev));
+    Ctx * c = new Ctx();
+    c->dev = dev;
+    CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    int rc = ensure_act(c, 4096);
+    if (rc) { delete c; return rc; }
+    *h = (b200_handle) (uintptr_t) c;
+    return 0;
+}
+
+extern "C" int b200_close(b200_handle h) {
+    CTX(h);
+    cudaStreamSynchronize(c->st);
+    for (auto & kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
+    cudaStreamDestroy(c->st);
+    c->magic = 0;
+    delete c;
+    return 0;
+}
+
+extern "C" int b200_setclocks(b200_handle h, int32_t, int32_t, int32_t) { CTX(h); return 0; }
+extern "C" int b200_synchronize(b200_handle h) { CTX(h); CU(cudaStreamSynchronize(c->st)); return 0; }
+extern "C" int64_t b200_launch_count(b200_handle h) { Ctx * c = ctx_of(h); return c ? c->launches : -1; }
+
+extern "C" int64_t b200_block_elems(int32_t type) {
+    switch (type) { case T_F32: case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_K: case T_Q6_K: return block_elems(type); }
+    return 0;
+}
+extern "C" int64_t b200_block_bytes(int32_t type) {
+    switch (type) { case T_F32: case T_Q4_0: case T_Q8_0: case T_Q8_1: case T_Q4_K: case T_Q6_K: return block_bytes(type); }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ memory
+extern "C" int b200_malloc(b200_handle h, size_t size, void ** ptr) {
+    CTX(h); if (!ptr) return fail(B200_EINVAL, "ptr is NULL");
+    *ptr = nullptr;
+    cudaError_t e = cudaMalloc(ptr, size ? size : 1);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(B200_ENOMEM, "cudaMalloc(%zu): %s", size, cudaGetErrorString(e)); }
+    return 0;
+}
+extern "C" int b200_free(b200_handle h, void * ptr) { CTX(h); CU(cudaStreamSynchronize(c->st)); CU(cudaFree(ptr)); return 0; }
+extern "C" int b200_memcpy_h2d(b200_handle h, void * d, const void * s, size_t n) {
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+}
+extern "C" int b200_memcpy_d2h(b200_handle h, void * d, const void * s, size_t n) {
+    CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+}
+extern "C" int b200_memcpy_d2d(b200_handle h, void * d, const void * s, size_t n) {
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, c->st)); return 0;
+}
+extern "C" int b200_memset(b200_handle h, void * d, int v, size_t n) {
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemsetAsync(d, v, n, c->st)); return 0;
+}
+extern "C" int b200_host_alloc(b200_handle h, size_t size, void ** ptr) { CTX(h); CU(cudaMallocHost(ptr, size ? size : 1)); return 0; }
+extern "C" int b200_host_free(b200_handle h, void * ptr) { CTX(h); CU(cudaFreeHost(ptr)); return 0; }
+
+extern "C" int b200_flush_l2(b200_handle h) {
+    CTX(h);
+    if (!c->flush) { c->flush_bytes = (size_t) 256 << 20; CU(cudaMalloc((void **) &c->flush, c->flush_bytes)); }
+    CU(launch_fill(c->flush, c->flush_bytes, 0x01010101u, c->st));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ weights
+static bool is_qweight(int t) { return t == T_Q4_0 || t == T_Q8_0 || t == T_Q4_K || t == T_Q6_K; }
+
+extern "C" int b200_weights_upload(b200_handle h, int32_t type, void * base, int64_t T, int64_t first, int64_t n, const void * host) {
+    CTX(h);
+    if (!is_qweight(type)) return fail(B200_EINVAL, "weights_upload: type %d is not a quantised weight type", type);
+    if (first < 0 || n < 0 || first + n > T) return fail(B200_EINVAL, "weights_upload: block range [%lld,+%lld) outside %lld", (long long) first, (long long) n, (long long) T);
+    const size_t bytes = (size_t) n * block_bytes(type);
+    int rc = ensure_stage(c, bytes); if (rc) return rc;
+    CU(cudaMemcpyAsync(c->stage, host, bytes, cudaMemcpyHostToDevice, c->st));
+    CU(launch_repack(type, true, (uint8_t *) base, T, first, n, c->stage, c->st)); c->launches++;
+    CU(cudaStreamSynchronize(c->st));
+    return 0;
+}
+extern "C" int b200_weights_download(b200_handle h, int32_t type, const void * base, int64_t T, int64_t first, int64_t n, void * host) {
+    CTX(h);
+    if (!is_qweight(type)) return fail(B200_EINVAL, "weights_download: type %d is not a quantised weight type", type);
+    if (first < 0 || n < 0 || first + n > T) return fail(B200_EINVAL, "weights_download: bad block range");
+    const size_t bytes = (size_t) n * block_bytes(type);
+    int rc = ensure_stage(c, bytes); if (rc) return rc;
+    CU(launch_repack(type, false, (uint8_t *) base, T, first, n, c->stage, c->st)); c->launches++;
+    CU(cudaMemcpyAsync(host, c->stage, bytes, cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ quantize / block dots
+extern "C" int b200_quantize_q8_1(b200_handle h, const float * x, void * y, int64_t k, int64_t nrows) {
+    CTX(h);
+    if (k <= 0 || k % 32 || nrows < 0) return fail(B200_EINVAL, "quantize_q8_1: k=%lld must be a positive multiple of 32", (long long) k);
+    if (((uintptr_t) x & 15) || ((uintptr_t) y & 3)) return fail(B200_EINVAL, "quantize_q8_1: x must be 16-byte and y 4-byte aligned");
+    if (nrows == 0) return 0;
+    CU(launch_quantize_q8_1_aos(x, k, nrows, y, c->st)); c->launches++;
+    return 0;
+}
+
+static int wptrs_of(const b200_tensor * t, WPtrs * out) {
+    if (!(t->flags & B200_TENSOR_REPACKED)) return fail(B200_EINVAL, "quantised src0 must be REPACKED device weights (b200_weights_upload)");
+    if (!t->w_base || t->w_blocks <= 0 || t->w_first < 0) return fail(B200_EINVAL, "REPACKED tensor without w_base/w_blocks");
+    *out = wptrs(t->type, t->w_base, t->w_blocks, t->w_first);
+    return 0;
+}
+
+extern "C" int b200_block_dots(b200_handle h, const b200_tensor * w, const int8_t * a_qs, int32_t * out) {
+    CTX(h);
+    if (!w || !is_qweight(w->type)) return fail(B200_EINVAL, "block_dots: quantised weight row expected");
+    const int64_t K = w->ne[0];
+    if (K <= 0 || K % block_elems(w->type)) return fail(B200_EINVAL, "block_dots: K=%lld not a multiple of the block size", (long long) K);
+    WPtrs wp; int rc = wptrs_of(w, &wp); if (rc) return rc;
+    rc = ensure_stage(c, (size_t) K + (size_t) (K / 32) * sizeof(ActDS) + 64); if (rc) return rc;
+    int8_t * sq = (int8_t *) c->stage;
+    ActDS * sd = (ActDS *) (c->stage + ((K + 15) / 16) * 16);
+    CU(launch_block_dots_impl(w->type, wp, K, a_qs, out, sq, sd, c->st)); c->launches++;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ ADD
+static int add_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    if (s0->type != T_F32 || s1->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "add: f32 only (ggml-hexagon.cpp:5079-5085)");
+    AddArgs a{};
+    a.a = (const char *) s0->data; a.b = (const char *) s1->data; a.d = (char *) d->data;
+    for (int i = 0; i < 4; i++) {
+        if (s0->ne[i] != d->ne[i]) return fail(B200_EINVAL, "add: src0 and dst shapes differ in dim %d", i);
+        if (s1->ne[i] <= 0 || d->ne[i] % s1->ne[i]) return fail(B200_EINVAL, "add: src1 dim %d (%lld) does not repeat into %lld", i, (long long) s1->ne[i], (long long) d->ne[i]);
+        a.ne[i] = d->ne[i]; a.neb[i] = s1->ne[i];
+        a.nba[i] = s0->nb[i]; a.nbb[i] = s1->nb[i]; a.nbd[i] = d->nb[i];
+    }
+    CU(launch_add_f32(a, c->st)); c->launches++;
+    // dst may alias a cached quantised activation
+    c->q_ptr = nullptr;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT
+static int mulmat_check(const b200_tensor * s0, const b200_tensor * s1, const b200_tensor * d) {
+    if (s1->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "mulmat: src1 and dst must be f32");
+    if (!(is_qweight(s0->type) || s0->type == T_F32)) return fail(B200_ENOTSUP, "mulmat: src0 type %d not supported", s0->type);
+    const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
+    if (s1->ne[0] != K) return fail(B200_EINVAL, "mulmat: K mismatch %lld vs %lld", (long long) K, (long long) s1->ne[0]);
+    if (d->ne[0] != M || d->ne[1] != N || d->ne[2] != s1->ne[2] || d->ne[3] != s1->ne[3]) return fail(B200_EINVAL, "mulmat: dst shape mismatch");
+    if (s0->ne[2] <= 0 || s0->ne[3] <= 0 || s1->ne[2] % s0->ne[2] || s1->ne[3] % s0->ne[3]) return fail(B200_EINVAL, "mulmat: batch dims do not broadcast");
+    if (K % block_elems(s0->type)) return fail(B200_EINVAL, "mulmat: K=%lld not a multiple of the block size", (long long) K);
+    if (s1->nb[0] != 4 || d->nb[0] != 4) return fail(B200_ENOTSUP, "mulmat: src1/dst must be contiguous in dim 0");
+    if (is_qweight(s0->type)) {
+        if (K % 32) return fail(B200_EINVAL, "mulmat: K must be a multiple of 32");
+        const int64_t bb = block_bytes(s0->type);
+        if (s0->nb[0] != bb || s0->nb[1] != K / block_elems(s0->type) * bb) return fail(B200_ENOTSUP, "mulmat: quantised src0 must have contiguous rows");
+        if (s0->nb[2] % bb || s0->nb[3] % bb) return fail(B200_ENOTSUP, "mulmat: src0 batch strides not block aligned");
+        if (((uintptr_t) s1->data & 15) || (s1->nb[1] & 15) || (s1->nb[2] & 15) || (s1->nb[3] & 15)) return fail(B200_ENOTSUP, "mulmat: src1 rows must be 16-byte aligned");
+    } else {
+        if (s0->nb[0] != 4) return fail(B200_ENOTSUP, "mulmat: f32 src0 must be contiguous in dim 0");
+    }
+    return 0;
+}
+
+static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst /*rowsplit*/) {
+    int rc = mulmat_check(s0, s1, d); if (rc) return rc;
+    const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
+    if (M == 0 || N == 0 || K == 0) return 0;
+    const int64_t r2 = s1->ne[2] / s0->ne[2], r3 = s1->ne[3] / s0->ne[3];
+    const bool q = is_qweight(s0->type);
+    WPtrs wp0{};
+    if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
+    const int64_t NB = K / 32;
+    if (q) { rc = ensure_act(c, NB * N); if (rc) return rc; }
+    const int64_t dcs = d->nb[1] / 4;
+    for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
+    for (int64_t i12 = 0; i12 < s1->ne[2]; i12++) {
+        const char * x = (const char *) s1->data + i12 * s1->nb[2] + i13 * s1->nb[3];
+        float * y = (float *) ((char *) d->data + i12 * d->nb[2] + i13 * d->nb[3]) + row_off_dst;
+        const int64_t i02 = i12 / r2, i03 = i13 / r3;
+        if (q) {
+            const bool reuse = c->in_graph && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
+            if (!reuse) {
+                CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
+                c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
+            }
+            const int64_t bb = block_bytes(s0->type);
+            const int64_t blk_off = (i02 * s0->nb[2] + i03 * s0->nb[3]) / bb;     // blocks from the tensor's first block
+            WFields f = wfields(s0->type);
+            WPtrs wp = wp0;
+            for (int i = 0; i < f.n; i++) wp.p[i] += blk_off * f.size[i];
+            for (int64_t c0 = 0; c0 < N; c0 += 8) {
+                const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
+                ActView av{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
+                CU(launch_gemv_q(s0->type, wp, M, K, av, nc, y + c0 * dcs, dcs, c->st, /*pdl=*/true)); c->launches++;
+            }
+        } else {
+            const char * w = (const char *) s0->data + i02 * s0->nb[2] + i03 * s0->nb[3];
+            for (int64_t c0 = 0; c0 < N; c0 += 8) {
+                const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
+                CU(launch_gemv_f32((const float *) w, s0->nb[1], M, K, (const float *) (x + c0 * s1->nb[1]), s1->nb[1], nc, y + c0 * dcs, dcs, c->st)); c->launches++;
+            }
+        }
+    }
+    // dst may overwrite the memory the cached quantisation was taken from
+    {
+        const char * lo = (const char *) d->data; const char * hi = lo + d->data_len;
+        const char * qp = (const char *) c->q_ptr;
+        if (qp && (d->data_len <= 0 || (qp >= lo && qp < hi))) c->q_ptr = nullptr;
+    }
+    return 0;
+}
+
+// ---- host-pointer tensors: stage in, run, stage out, synchronise (FastRPC semantics: dsptensor.data is host memory)
+static size_t tensor_span(const b200_tensor * t) {
+    if (t->data_len > 0) return (size_t) t->data_len;
+    size_t s = 0;
+    if (t->type == T_F32) { s = 4; for (int i = 0; i < 4; i++) s += (size_t) (t->ne[i] - 1) * t->nb[i]; }
+    else { s = (size_t) t->nb[1] * t->ne[1]; if (t->ne[2] > 1) s = (size_t) t->nb[2] * t->ne[2]; if (t->ne[3] > 1) s = (size_t) t->nb[3] * t->ne[3]; }
+    return s;
+}
+
+static int run_with_staging(Ctx * c, int op, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    const bool h0 = s0->flags & B200_TENSOR_HOST, h1 = s1->flags & B200_TENSOR_HOST, hd = d->flags & B200_TENSOR_HOST;
+    if (!(h0 || h1 || hd)) return op == B200_OP_ADD ? add_dev(c, s0, s1, d) : mulmat_dev(c, s0, s1, d, 0);
+    b200_tensor t0 = *s0, t1 = *s1, td = *d;
+    const size_t n0 = h0 ? tensor_span(s0) : 0, n1 = h1 ? tensor_span(s1) : 0, nd = hd ? tensor_span(d) : 0;
+    auto al = [](size_t v) { return (v + 255) & ~(size_t) 255; };
+    const bool q0 = h0 && is_qweight(s0->type);
+    // layout of the staging buffer: [src1][dst][src0 SoA][src0 native]
+    const size_t o1 = 0, od = o1 + al(n1), o0 = od + al(nd), o0n = o0 + al(n0);
+    int rc = ensure_stage(c, o0n + (q0 ? al(n0) : 0) + 256); if (rc) return rc;
+    if (h1) { CU(cudaMemcpyAsync(c->stage + o1, s1->data, n1, cudaMemcpyHostToDevice, c->st)); t1.data = c->stage + o1; t1.flags &= ~B200_TENSOR_HOST; }
+    if (h0) {
+        if (q0) {
+            const int64_t bb = block_bytes(s0->type);
+            if (n0 % bb) return fail(B200_EINVAL, "host src0 span is not a whole number of blocks");
+            const int64_t T = (int64_t) n0 / bb;
+            CU(cudaMemcpyAsync(c->stage + o0n, s0->data, n0, cudaMemcpyHostToDevice, c->st));
+            CU(launch_repack(s0->type, true, c->stage + o0, T, 0, T, c->stage + o0n, c->st)); c->launches++;
+            t0.data = c->stage + o0; t0.w_base = c->stage + o0; t0.w_blocks = T; t0.w_first = 0;
+            t0.flags = (t0.flags & ~B200_TENSOR_HOST) | B200_TENSOR_REPACKED;
+        } else {
+            CU(cudaMemcpyAsync(c->stage + o0, s0->data, n0, cudaMemcpyHostToDevice, c->st));
+            t0.data = c->stage + o0; t0.flags &= ~B200_TENSOR_HOST;
+        }
+    }
+    if (hd) { td.data = c->stage + od; td.flags &= ~B200_TENSOR_HOST; td.data_len = (int64_t) nd; }
+    c->q_ptr = nullptr;
+    rc = op == B200_OP_ADD ? add_dev(c, &t0, &t1, &td) : mulmat_dev(c, &t0, &t1, &td, 0);
+    c->q_ptr = nullptr;
+    if (rc) return rc;
+    if (hd) CU(cudaMemcpyAsync(d->data, c->stage + od, nd, cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+extern "C" int b200_add(b200_handle h, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    CTX(h); if (!s0 || !s1 || !d) return fail(B200_EINVAL, "NULL tensor");
+    return run_with_staging(c, B200_OP_ADD, s0, s1, d);
+}
+extern "C" int b200_mulmat(b200_handle h, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    CTX(h); if (!s0 || !s1 || !d) return fail(B200_EINVAL, "NULL tensor");
+    return run_with_staging(c, B200_OP_MUL_MAT, s0, s1, d);
+}
+
+// ------------------------------------------------------------------------------------------------ graph compute
+static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
+    c->in_graph = true; c->q_ptr = nullptr;
+    int rc = 0;
+    for (int i = 0; i < n && !rc; i++) {
+        b200_tensor d = nodes[i].dst;
+        switch (d.op) {
+            case B200_OP_NONE: break;
+            case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_MUL_MAT: rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0); break;
+            default: rc = fail(B200_ENOTSUP, "graph node %d: op %d not offloaded", i, d.op);
+        }
+    }
+    c->in_graph = false; c->q_ptr = nullptr;
+    return rc;
+}
+
+static uint64_t fnv1a(const void * p, size_t n, uint64_t hsh = 1469598103934665603ull) {
+    const uint8_t * b = (const uint8_t *) p;
+    for (size_t i = 0; i < n; i++) { hsh ^= b[i]; hsh *= 1099511628211ull; }
+    return hsh;
+}
+
+extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n, int32_t use_cuda_graph) {
+    CTX(h);
+    if (n < 0 || (n > 0 && !nodes)) return fail(B200_EINVAL, "bad node list");
+    if (n == 0) return 0;
+    bool any_host = false; int64_t need_act = 0;
+    for (int i = 0; i < n; i++) {
+        const b200_node & nd = nodes[i];
+        any_host |= (nd.src0.flags | nd.src1.flags | nd.dst.flags) & B200_TENSOR_HOST;
+        if (nd.dst.op == B200_OP_MUL_MAT && is_qweight(nd.src0.type)) {
+            int rc = mulmat_check(&nd.src0, &nd.src1, &nd.dst); if (rc) return rc;
+            const int64_t b = nd.src0.ne[0] / 32 * nd.src1.ne[1];
+            if (b > need_act) need_act = b;
+        }
+    }
+    if (any_host) return fail(B200_ENOTSUP, "graph_compute takes device tensors only");
+    int rc = ensure_act(c, need_act); if (rc) return rc;
+    if (!use_cuda_graph) return run_nodes(c, nodes, n);
+
+    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *)));
+    auto it = c->graphs.find(key);
+    if (it == c->graphs.end()) {
+        const int64_t before = c->launches;
+        CU(cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal));
+        rc = run_nodes(c, nodes, n);
+        cudaGraph_t g = nullptr;
+        cudaError_t e = cudaStreamEndCapture(c->st, &g);
+        const int64_t captured = c->launches - before;
+        c->launches = before;
+        if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+        if (e != cudaSuccess) return fail(B200_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+        GraphEntry ge; ge.n_kernels = captured;
+        e = cudaGraphInstantiate(&ge.exec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) return fail(B200_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+        if (c->graphs.size() > 64) { for (auto & kv : c->graphs) cudaGraphExecDestroy(kv.second.exec); c->graphs.clear(); }
+        it = c->graphs.emplace(key, ge).first;
+    }
+    CU(cudaGraphLaunch(it->second.exec, c->st));
+    c->launches += it->second.n_kernels;      // a replay runs exactly the kernels captured
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ events
+extern "C" int b200_event_create(b200_handle h, void ** ev) { CTX(h); cudaEvent_t e; CU(cudaEventCreate(&e)); *ev = e; return 0; }
+extern "C" int b200_event_record(b200_handle h, void * ev) { CTX(h); CU(cudaEventRecord((cudaEvent_t) ev, c->st)); return 0; }
+extern "C" int b200_event_elapsed_ms(b200_handle h, void * a, void * b, float * ms) {
+    CTX(h); CU(cudaEventSynchronize((cudaEvent_t) b)); CU(cudaEventElapsedTime(ms, (cudaEvent_t) a, (cudaEvent_t) b)); return 0;
+}
+extern "C" int b200_event_destroy(b200_handle h, void * ev) { CTX(h); CU(cudaEventDestroy((cudaEvent_t) ev)); return 0; }
+
+// ------------------------------------------------------------------------------------------------ row split (NCCL)
+extern "C" int b200_rowsplit_unique_id(void * id128) {
+    int rc = nccl_load(); if (rc) return rc;
+    nccl_uid id; NC(g_nccl.GetUniqueId(&id));
+    memcpy(id128, &id, 128);
+    return 0;
+}
+extern "C" int b200_rowsplit_init(b200_handle h, const void * id128, int32_t rank, int32_t world) {
+    CTX(h);
+    if (world < 1 || rank < 0 || rank >= world) return fail(B200_EINVAL, "rowsplit_init: rank %d of %d", rank, world);
+    int rc = nccl_load(); if (rc) return rc;
+    nccl_uid id; memcpy(&id, id128, 128);
+    NC(g_nccl.CommInitRank(&c->comm, world, id, rank));
+    c->rank = rank; c->world = world;
+    return 0;
+}
+extern "C" int b200_rowsplit_finalize(b200_handle h) {
+    CTX(h);
+    if (c->comm) { CU(cudaStreamSynchronize(c->st)); NC(g_nccl.CommDestroy(c->comm)); c->comm = nullptr; }
+    c->world = 1; c->rank = 0;
+    return 0;
+}
+extern "C" int b200_mulmat_rowsplit(b200_handle h, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    CTX(h); if (!s0 || !s1 || !d) return fail(B200_EINVAL, "NULL tensor");
+    if (!c->comm && c->world != 1) return fail(B200_EINVAL, "rowsplit not initialised");
+    const int64_t rows = s0->ne[1], Mtot = d->ne[0], N = s1->ne[1];
+    if (rows * c->world != Mtot) return fail(B200_EINVAL, "rowsplit: %lld rows x %d ranks != M %lld", (long long) rows, c->world, (long long) Mtot);
+    if (s1->ne[2] != 1 || s1->ne[3] != 1) return fail(B200_ENOTSUP, "rowsplit: 2-D only");
+    if (d->nb[0] != 4 || d->nb[1] != Mtot * 4) return fail(B200_ENOTSUP, "rowsplit: dst must be contiguous");
+    // local rows straight into this rank's slice of the full dst
+    b200_tensor dl = *d; dl.ne[0] = rows;
+    int rc = mulmat_check(s0, s1, &dl); if (rc) return rc;
+    c->q_ptr = nullptr;
+    rc = mulmat_dev(c, s0, s1, &dl, c->rank * rows); if (rc) return rc;
+    c->q_ptr = nullptr;
+    if (c->world == 1) return 0;
+    float * base = (float *) d->data;
+    NC(g_nccl.GroupStart());
+    for (int64_t n = 0; n < N; n++) {
+        float * col = base + n * Mtot;
+        int r = g_nccl.AllGather(col + c->rank * rows, col, (size_t) rows, /*ncclFloat32*/ 7, c->comm, c->st);
+        if (r) { g_nccl.GroupEnd(); return fail(B200_ENCCL, "ncclAllGather: %s", g_nccl.GetErrorString(r)); }
+    }
+    NC(g_nccl.GroupEnd());
+    return 0;
+}

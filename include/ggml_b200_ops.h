@@ -1,0 +1,164 @@
+/*
+ * ggml_b200_ops.h — C-ABI of the B200 op layer (libb200ops.so).
+ *
+ * This is the seat of the reference's FastRPC interface between the host backend and the
+ * Hexagon cDSP kernels: `ggmlop_dsp_open/close/setclocks/add/mulmat` taking `struct dsptensor`
+ * (ggml/src/ggml-hexagon/kernels/ggmlop_ap_skel.h:235-244 and :266-280), called from
+ * ggmlhexagon_compute (ggml/src/ggml-hexagon/ggml-hexagon.cpp:4975-5060).
+ * Plain C: pointers, sizes, ints.  No ggml, torch or CUDA types in any signature.
+ *
+ * Every function returns 0 on success or a negative B200_E* code (the FastRPC functions return 0 or
+ * an AEE error the same way); b200_last_error() gives the text.  There is no CPU fallback: on a
+ * machine without a CUDA device b200_open fails with B200_ENODEV and nothing else is usable.
+ */
+#ifndef GGML_B200_OPS_H
+#define GGML_B200_OPS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+/* tensor element types: numeric values of enum ggml_type (ggml/include/ggml.h:349-390) */
+enum b200_type {
+    B200_TYPE_F32  = 0,
+    B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q8_0 = 8,
+    B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q4_K = 12,
+    B200_TYPE_Q6_K = 14,
+};
+
+/* ops: numeric values of enum ggml_op for the two ops the cDSP path offloads
+ * (ggml-hexagon.cpp:5079-5098; ggml/include/ggml.h:426-, GGML_OP_ADD = 2, GGML_OP_MUL_MAT = 27) */
+enum b200_op {
+    B200_OP_NONE    = 0,
+    B200_OP_ADD     = 2,
+    B200_OP_MUL_MAT = 27,
+};
+
+enum b200_err {
+    B200_OK       = 0,
+    B200_ENODEV   = -1,  /* no CUDA device / driver */
+    B200_EINVAL   = -2,  /* bad handle / argument / unsupported shape or type */
+    B200_ENOMEM   = -3,  /* device allocation failed */
+    B200_ECUDA    = -4,  /* CUDA runtime error (text in b200_last_error) */
+    B200_ENCCL    = -5,  /* NCCL error */
+    B200_ENOTSUP  = -6,  /* valid request the kernels do not implement (caller must not route it here) */
+};
+
+/* flags of b200_tensor */
+#define B200_TENSOR_HOST      0x1  /* data is a HOST pointer: the call copies it in/out (as FastRPC does with dsptensor.data) */
+#define B200_TENSOR_REPACKED  0x2  /* quantised weight already in the device SoA layout written by b200_weights_upload */
+
+/*
+ * Replaces `struct dsptensor` (ggmlop_ap_skel.h:235-244).  Same fields, but ne/nb are 64-bit
+ * (the reference narrows ggml's int64/size_t to int32 at ggml-hexagon.cpp:5006-5049, which cannot
+ * describe a 128256x8192 matrix in bytes).  ne/nb have ggml_tensor meaning (ggml.h:578-610):
+ * ne[0] is the contiguous dimension in ELEMENTS, nb[i] the stride in BYTES of the native ggml block
+ * layout (nb[0] = block size; nb[1] = row size ...), also for REPACKED weights.
+ */
+typedef struct b200_tensor {
+    int32_t type;          /* enum b200_type */
+    int32_t op;            /* enum b200_op (dst only) */
+    int32_t flags;
+    int32_t reserved;
+    int64_t ne[4];
+    int64_t nb[4];
+    int32_t op_params[16];
+    void *  data;          /* device pointer (or host pointer with B200_TENSOR_HOST) */
+    int64_t data_len;      /* bytes addressable from data */
+    /* REPACKED weights only: the SoA region is laid out over the whole allocation it was uploaded into */
+    void *  w_base;        /* base of that allocation (device) */
+    int64_t w_blocks;      /* total blocks (32- or 256-element units) in that allocation */
+    int64_t w_first;       /* index of this tensor's first block inside it */
+} b200_tensor;
+
+/* one node of a compute graph: dst = op(src0, src1)   (ggml_cgraph node, ggml-hexagon.cpp:5555-5574) */
+typedef struct b200_node {
+    b200_tensor src0, src1, dst;
+} b200_node;
+
+typedef uint64_t b200_handle;   /* replaces remote_handle64 */
+
+/* ---- session (ggmlop_dsp_open / _close / _setclocks, ggmlop_ap_skel.h:266-275; ggml-hexagon.cpp:4945-4951) */
+/* uri: "cuda:<ordinal>" (NULL or "" = "cuda:0").  Creates the context: device, stream, q8_1 scratch. */
+B200_API int b200_open(const char * uri, b200_handle * h);
+B200_API int b200_close(b200_handle h);
+/* kept for interface symmetry; GPU clocks are never touched, returns 0 */
+B200_API int b200_setclocks(b200_handle h, int32_t power_level, int32_t latency, int32_t dcvs_enable);
+B200_API const char * b200_last_error(void);
+B200_API int b200_device_count(void);
+/* name[<=len], total/free HBM bytes, SM count */
+B200_API int b200_device_info(int device, char * name, int len, int64_t * total, int64_t * free_b, int32_t * sms);
+
+/* ---- the two ops (ggmlop_dsp_add / ggmlop_dsp_mulmat, ggmlop_ap_skel.h:276-277; ggml-dsp.c:1069,1192) */
+/* dst = src0 + src1, f32; src1 broadcast by repetition in every dim (ggml-dsp.c:991-1066, binary-ops.cpp:50-117) */
+B200_API int b200_add(b200_handle h, const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst);
+/* dst[M,N,ne12,ne13] = src0[K,M,ne02,ne03] x src1[K,N,ne12,ne13] (ggml-dsp.c:1192-1351, ggml-cpu.c:6745-6937).
+ * src0: q4_0/q8_0/q4_K/q6_K REPACKED device weights, or f32; src1, dst: f32. Asynchronous on the handle's stream
+ * unless a tensor carries B200_TENSOR_HOST (then the call returns after dst is back in host memory). */
+B200_API int b200_mulmat(b200_handle h, const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst);
+/* a whole node list in one call (graph_compute, ggml-hexagon.cpp:5555-5574); asynchronous.
+ * With use_cuda_graph != 0 the launch sequence is captured once per distinct node list and replayed. */
+B200_API int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph);
+B200_API int b200_synchronize(b200_handle h);
+
+/* ---- activation quantiser, exposed for parity tests (= quantize_row_q8_1_ref, ggml-quants.c:220-253)
+ * x: device f32 [nrows][k] contiguous, y: device block_q8_1 AoS [nrows][k/32] (36 B blocks). */
+B200_API int b200_quantize_q8_1(b200_handle h, const float * x, void * y, int64_t k, int64_t nrows);
+/* per-32-group (q6_K: per-16-group) exact integer dot products of one weight row with int8 activations
+ * (the bit-exact contract, oracle_block_dots).  a_qs: device int8[k]; out: device int32[k/32 or k/16]. */
+B200_API int b200_block_dots(b200_handle h, const b200_tensor * w_row, const int8_t * a_qs, int32_t * out);
+
+/* ---- device memory (buffer_type.alloc_buffer / buffer.set_tensor / get_tensor / memset / clear,
+ *      ggml-backend-impl.h:17-58; ggml-hexagon.cpp:5361-5478) */
+B200_API int b200_malloc(b200_handle h, size_t size, void ** ptr);
+B200_API int b200_free(b200_handle h, void * ptr);
+B200_API int b200_memcpy_h2d(b200_handle h, void * dst_dev, const void * src_host, size_t n);
+B200_API int b200_memcpy_d2h(b200_handle h, void * dst_host, const void * src_dev, size_t n);
+B200_API int b200_memcpy_d2d(b200_handle h, void * dst_dev, const void * src_dev, size_t n);
+B200_API int b200_memset(b200_handle h, void * dst_dev, int value, size_t n);
+/* pinned host staging memory for the host-buffer (e2e) path */
+B200_API int b200_host_alloc(b200_handle h, size_t size, void ** ptr);
+B200_API int b200_host_free(b200_handle h, void * ptr);
+
+/* ---- quantised weights: native ggml blocks (host) <-> device SoA layout (DESIGN.md "HBM layout").
+ * The region [base, base + total_blocks*block_bytes) holds total_blocks blocks of `type`;
+ * upload/download blocks [first, first+n).  Byte count is identical to the native layout. */
+B200_API int b200_weights_upload(b200_handle h, int32_t type, void * base, int64_t total_blocks,
+                                 int64_t first, int64_t n, const void * host_blocks);
+B200_API int b200_weights_download(b200_handle h, int32_t type, const void * base, int64_t total_blocks,
+                                   int64_t first, int64_t n, void * host_blocks);
+B200_API int64_t b200_block_elems(int32_t type);   /* 32 / 256 / 1 */
+B200_API int64_t b200_block_bytes(int32_t type);   /* 18 / 34 / 144 / 210 / 4 */
+
+/* ---- device-side timing on the handle's stream (CUDA events) */
+B200_API int b200_event_create(b200_handle h, void ** ev);
+B200_API int b200_event_record(b200_handle h, void * ev);
+B200_API int b200_event_elapsed_ms(b200_handle h, void * start, void * stop, float * ms); /* syncs on stop */
+B200_API int b200_event_destroy(b200_handle h, void * ev);
+/* kernels launched through this handle since open (the `gpu_launches` evidence of bench.py) */
+B200_API int64_t b200_launch_count(b200_handle h);
+/* overwrite a >L2-sized scratch buffer so the next kernel starts from a cold L2 */
+B200_API int b200_flush_l2(b200_handle h);
+
+/* ---- row-split MUL_MAT across the GPUs of one box: one process per GPU, NCCL over NVLink
+ *      (takes the seat of ggml-cuda's split buffers, ggml-cuda.cu:727-753,1365-1673) */
+B200_API int b200_rowsplit_unique_id(void * id128);                       /* 128 bytes, rank 0 creates, all ranks get */
+B200_API int b200_rowsplit_init(b200_handle h, const void * id128, int32_t rank, int32_t world);
+B200_API int b200_rowsplit_finalize(b200_handle h);
+/* src0 = THIS rank's row slice [rows_local x K] (REPACKED); src1 replicated; dst_full [M_total x N] on every rank.
+ * rows_local must be equal on all ranks (M_total = world * rows_local).  GEMV/GEMM into the local slice of
+ * dst_full, then all-gather of the slices. */
+B200_API int b200_mulmat_rowsplit(b200_handle h, const b200_tensor * src0_slice, const b200_tensor * src1,
+                                  b200_tensor * dst_full);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GGML_B200_OPS_H */
