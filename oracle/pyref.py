@@ -189,3 +189,103 @@ class Ref:
         C.memmove(self._p(out), b.ggml_get_data(td), out.nbytes)
         b.ggml_free(ctx)
         return out.reshape(a.shape)
+
+
+def bench_decode(ref, layer_shapes, out_shape, n_layers_total, n_layers_sample, wtype, n_threads, budget_s=15.0, seed=7):
+    """Timed CPU baseline: the reference's ggml-cpu runs the decode MUL_MAT/ADD node list (batch 1) of
+    `n_layers_sample` layers (+ the output matrix), all `n_threads` host threads, repeated until `budget_s`.
+    Returns (seconds per FULL token extrapolated to n_layers_total, sample description)."""
+    import time
+    rng = np.random.default_rng(seed)
+    b, cpu = ref.base, ref.cpu
+    tot = 0
+    for _, M, K in layer_shapes:
+        tot += ref.row_size(wtype, K) * M
+    tot = tot * n_layers_sample + ref.row_size(wtype, out_shape[2]) * out_shape[1]
+    ctx = ref._ctx(tot + (512 << 20))
+    b.ggml_new_tensor_1d.restype = C.c_void_p
+    b.ggml_new_tensor_1d.argtypes = [C.c_void_p, C.c_int, C.c_int64]
+
+    def fill_w(t, M, K):
+        n = ref.row_size(wtype, K) * M
+        raw = rng.integers(0, 256, size=n, dtype=np.uint8)
+        # keep scales finite: overwrite with a small quantised random matrix pattern on the first rows only is overkill;
+        # force the fp16 scale bytes of q4_0/q8_0 blocks to ~0.002
+        if wtype in (Q4_0, Q8_0):
+            bs = 18 if wtype == Q4_0 else 34
+            v = raw.reshape(-1, bs)
+            v[:, 0] = 0x19
+            v[:, 1] = 0x18          # 0x1819 = 0.00199 in fp16
+        C.memmove(b.ggml_get_data(t), raw.ctypes.data, n)
+
+    def vec(n):
+        t = b.ggml_new_tensor_1d(ctx, F32, n)
+        x = rng.uniform(-1, 1, n).astype(np.float32)
+        C.memmove(b.ggml_get_data(t), x.ctypes.data, 4 * n)
+        return t
+
+    dims = dict((n, (M, K)) for n, M, K in layer_shapes)
+    h, f = dims["wq"][1], dims["down"][1]
+    x = vec(h)
+    g = b.ggml_new_graph(ctx)
+    last = None
+    for _ in range(n_layers_sample):
+        ws = {}
+        for n, M, K in layer_shapes:
+            ws[n] = b.ggml_new_tensor_2d(ctx, wtype, K, M)
+            fill_w(ws[n], M, K)
+        q = b.ggml_mul_mat(ctx, ws["wq"], x)
+        k = b.ggml_mul_mat(ctx, ws["wk"], x)
+        v = b.ggml_mul_mat(ctx, ws["wv"], x)
+        o = b.ggml_mul_mat(ctx, ws["wo"], q)
+        hres = b.ggml_add(ctx, x, o)
+        gt = b.ggml_mul_mat(ctx, ws["gate"], hres)
+        up = b.ggml_mul_mat(ctx, ws["up"], hres)
+        dn = b.ggml_mul_mat(ctx, ws["down"], gt)
+        x = b.ggml_add(ctx, hres, dn)
+        for t in (k, v, up, x):
+            b.ggml_build_forward_expand(g, t)
+        last = x
+    g_out = b.ggml_new_graph(ctx)
+    wo = b.ggml_new_tensor_2d(ctx, wtype, out_shape[2], out_shape[1])
+    fill_w(wo, out_shape[1], out_shape[2])
+    logits = b.ggml_mul_mat(ctx, wo, vec(h))
+    b.ggml_build_forward_expand(g_out, logits)
+    # ggml_graph_compute_with_ctx allocates its work buffer inside ctx at every call -> plan once instead
+    class CPlan(C.Structure):
+        _fields_ = [("work_size", C.c_size_t), ("work_data", C.c_void_p), ("n_threads", C.c_int),
+                    ("threadpool", C.c_void_p), ("abort_callback", C.c_void_p), ("abort_callback_data", C.c_void_p)]
+    cpu.ggml_graph_plan.restype = CPlan
+    cpu.ggml_graph_plan.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    cpu.ggml_graph_compute.restype = C.c_int
+    cpu.ggml_graph_compute.argtypes = [C.c_void_p, C.POINTER(CPlan)]
+    plans = []
+    for gr in (g, g_out):
+        p = cpu.ggml_graph_plan(gr, n_threads, None)
+        buf = np.empty(max(p.work_size, 16), dtype=np.uint8)
+        p.work_data = buf.ctypes.data
+        plans.append((gr, p, buf))
+
+    def run():
+        for gr, p, _ in plans:
+            assert cpu.ggml_graph_compute(gr, C.byref(p)) == 0
+    run()  # warm-up
+    t_layers = t_out = 0.0
+    reps = 0
+    t_start = time.perf_counter()
+    while True:
+        t0 = time.perf_counter()
+        assert cpu.ggml_graph_compute(plans[0][0], C.byref(plans[0][1])) == 0
+        t1 = time.perf_counter()
+        assert cpu.ggml_graph_compute(plans[1][0], C.byref(plans[1][1])) == 0
+        t2 = time.perf_counter()
+        t_layers += t1 - t0
+        t_out += t2 - t1
+        reps += 1
+        if time.perf_counter() - t_start > budget_s or reps >= 200:
+            break
+    b.ggml_free(ctx)
+    per_token = t_layers / reps * (n_layers_total / n_layers_sample) + t_out / reps
+    desc = ("%d of %d layers (7 MUL_MAT + 2 ADD each) + output matrix, %d reps, extrapolated x%.1f on the layer part"
+            % (n_layers_sample, n_layers_total, reps, n_layers_total / n_layers_sample))
+    return per_token, desc
