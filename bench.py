@@ -228,3 +228,179 @@ def time_shapes(B, s, wl, iters=3):
         out.append({"shape": "%s %dx%d" % (name, rows, K), "us": round(per * 1e6, 3), "GB/s": round(by / per / 1e9, 1)})
         dst.free()
     return out
+
+
+def cpu_baseline(model, budget_s):
+    """reference ggml-cpu (oracle/_ref) on the host cores; falls back to the single-threaded C port only if _ref is absent"""
+    import pyref
+    layer, L, out, h, f = llama_shapes(model)
+    cores = os.cpu_count() or 1
+    try:
+        R = pyref.Ref()
+        per_tok, desc = pyref.bench_decode(R, layer, out, L, 2, Q4_0, cores, budget_s=budget_s)
+        return {"value": round(1.0 / per_tok, 4), "unit": "tokens/s", "cores": cores, "kind": "reference",
+                "sample": desc + "; oracle/_ref/%s ggml-cpu, llamafile on, OpenMP off" % R.variant}
+    except (FileNotFoundError, OSError):
+        import pyoracle as O
+        rng = np.random.default_rng(0)
+        M, K = 512, 4096
+        w = random_q4_0(M, K, rng)
+        x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+        t0 = time.perf_counter(); n = 0
+        while time.perf_counter() - t0 < budget_s:
+            O.mul_mat(O.Q4_0, w, x, 0); n += 1
+        per_row = (time.perf_counter() - t0) / n / M / K
+        tot = sum(m * k for _, m, k in layer) * L + out[1] * out[2]
+        return {"value": round(1.0 / (per_row * tot), 5), "unit": "tokens/s", "cores": 1, "kind": "port",
+                "sample": "oracle C port, %dx%d q4_0 GEMV x%d, extrapolated by weight elements" % (M, K, n)}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    model = "llama2-7b" if args.gpus == 1 else "llama3-70b"
+    vals = []
+    cb = None
+    for i in range(args.warmup + args.steps):
+        cb = cpu_baseline(model, budget_s=max(2.0, 40.0 / (args.warmup + args.steps)))
+        if i >= args.warmup:
+            vals.append(cb["value"])
+    v = float(np.mean(vals))
+    cb["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+            "vs_baseline": None, "dtype": "q4_0 x q8_0 int8 dot, f32 accumulate", "data": "synthetic",
+            "config": {"workload": model + "-q4_0-decode", "batch": 1}, "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_b200(args, rank, world):
+    import ctypes as C
+    import b200ops as B
+    dist = None
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    s = B.Session(local)
+    model = "llama2-7b" if world == 1 else "llama3-70b"
+    if world > 1:
+        import torch
+        idb = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C.c_uint8 * 128)()
+            B._ck(B.lib().b200_rowsplit_unique_id(buf))
+            idb = torch.tensor(list(buf), dtype=torch.uint8)
+        idb = idb.cuda()
+        dist.broadcast(idb, 0)
+        idh = (C.c_uint8 * 128)(*idb.cpu().tolist())
+        B._ck(B.lib().b200_rowsplit_init(s.h, idh, rank, world))
+    wl = DecodeWorkload(B, s, model, rank, world)
+
+    def barrier():
+        s.sync()
+        if dist is not None:
+            dist.barrier()
+            import torch
+            torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        wl.step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = s.launch_count()
+    e0, e1 = s.event(), s.event()
+    s.record(e0)
+    for _ in range(args.steps):
+        wl.step()
+    s.record(e1)
+    ms = s.elapsed_ms(e0, e1)
+    launches = s.launch_count() - l0
+    barrier()
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    step_s = ms * 1e-3 / args.steps
+    # e2e: host buffers in, host buffers out, through the C-ABI, every step (pinned x -> HBM, graph, logits -> pinned)
+    hx, hy = C.c_void_p(), C.c_void_p()
+    B._ck(B.lib().b200_host_alloc(s.h, 4 * wl.h, C.byref(hx)))
+    B._ck(B.lib().b200_host_alloc(s.h, 4 * wl.out[1], C.byref(hy)))
+    C.memmove(hx, wl.x_host.ctypes.data, 4 * wl.h)
+    def e2e_step():
+        B._ck(B.lib().b200_memcpy_h2d(s.h, wl.x.ptr, hx, 4 * wl.h))
+        wl.step()
+        B._ck(B.lib().b200_memcpy_d2h(s.h, hy, wl.logits.ptr, 4 * wl.out[1]))
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    if dist is not None:
+        import torch
+        t = torch.tensor([e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    clocks = sampler.stop()
+    logits = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(wl.out[1],)).copy()
+    shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
+    if rank != 0:
+        s.close()
+        return
+    peak, peak_src = measured_peak_hbm()
+    # roofline of the dominant kernel (gemv_q_kernel<q4_0>): algorithmic bytes of all MUL_MATs of one rank's step over the
+    # device time of the WHOLE step (quantise + add kernels included -> conservative); per launch = / n_mulmat
+    alg = wl.alg_bytes if world == 1 else sum(gemv_bytes(M // world, K) for _, M, K in wl.layer) * wl.L + gemv_bytes(wl.out[1] // world, wl.out[2])
+    achieved = alg / step_s / 1e9
+    line = {"metric": METRIC, "value": round(1.0 / step_s, 3), "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(step_s * 1e3, 5), "higher_is_better": True,
+            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+            "dtype": "q4_0 x q8_1 int8 dp4a, f32 accumulate", "data": "synthetic (random-init q4_0 blocks, seeded)",
+            "config": {"workload": model + "-q4_0-decode" + ("-rowsplit%d" % world if world > 1 else ""), "batch": 1,
+                       "layers": wl.L, "mul_mat_per_step": wl.n_mulmat, "add_per_step": 2 * wl.L,
+                       "weight_bytes_per_gpu": wl.weight_bytes_local, "l2": "inputs larger than L2 (weights streamed once per step)",
+                       "submit": "one b200_graph_compute (CUDA graph + PDL)" if world == 1 else "per-node b200_mulmat_rowsplit + ncclAllGather"},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                         "traffic": None, "peak_source": peak_src, "kernel": "gemv_q_kernel<q4_0,1,2>",
+                         "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
+            "e2e": {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
+                    "timer": "host perf_counter around K calls of h2d + graph_compute + d2h (each step ends synchronised)"},
+            "gpu_launches": int(launches), "clocks": clocks, "logits_finite": bool(np.isfinite(logits).all())}
+    if shapes:
+        line["shapes"] = shapes
+    if not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
+    print(json.dumps(line))
+    s.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-shapes", action="store_true", help="skip the per-shape GEMV table")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus and not (world == 1 and args.gpus == 1):
+        if world == 1 and args.gpus > 1:
+            sys.exit("launch with torchrun --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    run_b200(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()
