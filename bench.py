@@ -140,7 +140,7 @@ class DecodeWorkload:
         kv = dict((n, m) for n, m, _ in layer)["wk"]
         mk = lambda n: sess.malloc(4 * n)
         self.x = mk(h); self.q = mk(h); self.k = mk(kv); self.v = mk(kv); self.o = mk(h); self.hres = mk(h)
-        self.g = mk(f); self.u = mk(f); self.dn = mk(h); self.x2 = mk(h); self.logits = mk(out[1])
+        self.g = mk(f); self.u = mk(f); self.dn = mk(h); self.x2 = mk(h); self.x3 = mk(h); self.logits = mk(out[1])
         self.x_host = np.random.default_rng(seed + 1).uniform(-1, 1, h).astype(np.float32)
         sess.h2d(self.x, self.x_host)
         self._nodes = None
@@ -177,7 +177,8 @@ class DecodeWorkload:
             nodes.append(self._mm(lw["up"], self.hres, h, self.u, f))
             nodes.append(self._mm(lw["down"], self.g, f, self.dn, h))
             nodes.append(self._add(self.hres, self.dn, xout, h))
-            xin, xout = xout, (self.x if xout is self.x2 else self.x2)
+            # self.x (the step's input) is never written: every step computes the same token from the same input
+            xin, xout = xout, (self.x3 if xout is self.x2 else self.x2)
         nodes.append(self._mm(self.w_out, xin, h, self.logits, self.out[1]))
         self.final_x = xin
         self.node_list = nodes

@@ -72,9 +72,22 @@ cudaError_t launch_quantize_q8_1_soa(const float * x, int64_t row_stride_bytes, 
                                      int8_t * qs, ActDS * ds, cudaStream_t st);
 cudaError_t launch_quantize_q8_1_aos(const float * x, int64_t K, int64_t nrows, void * y, cudaStream_t st);
 
-// dst[c*dst_col_stride + m] for m < M, c < ncols (<= 8). `pdl`: launch with programmatic stream serialization.
-cudaError_t launch_gemv_q(int type, WPtrs w, int64_t M, int64_t K, ActView act, int ncols,
-                          float * dst, int64_t dst_col_stride, cudaStream_t st, bool pdl);
+// ---- GEMV (gemv.cu).  Up to 3 matrices sharing one activation vector run as one launch.
+struct GemvMat {
+    WPtrs w; int64_t M;
+    float * dst;                 // dst[c*dcs + row]
+    const float * add_src;       // optional fused GGML_OP_ADD: add_dst[c*dcs + row] = add_src[c*dcs + row] + dst[...]
+    float * add_dst;             // (nullptr = none)
+};
+struct GemvArgs {
+    GemvMat mat[3]; int nmat; int cta_end[3];
+    int steps; int64_t K; int64_t dcs;
+    const float * x; int64_t x_col_stride;     // FUSEQ: f32 activations, column stride in bytes
+    ActView act;                                // !FUSEQ: pre-quantised scratch
+};
+// fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
+cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
+bool gemv_pdl_enabled();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)
 cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, int64_t K,
                             const float * x, int64_t x_col_stride, int ncols,

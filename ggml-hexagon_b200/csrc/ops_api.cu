@@ -300,7 +300,17 @@ static int mulmat_check(const b200_tensor * s0, const b200_tensor * s1, const b2
     return 0;
 }
 
-static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst /*rowsplit*/) {
+struct FusedAdd { const float * src = nullptr; float * dst = nullptr; };
+
+static WPtrs wptrs_offset(const b200_tensor * s0, WPtrs wp, int64_t byte_off) {
+    const int64_t blk_off = byte_off / block_bytes(s0->type);
+    WFields f = wfields(s0->type);
+    for (int i = 0; i < f.n; i++) wp.p[i] += blk_off * f.size[i];
+    return wp;
+}
+
+static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst /*rowsplit*/,
+                      const FusedAdd * fa = nullptr) {
     int rc = mulmat_check(s0, s1, d); if (rc) return rc;
     const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
     if (M == 0 || N == 0 || K == 0) return 0;
@@ -309,7 +319,8 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     WPtrs wp0{};
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
-    if (q) { rc = ensure_act(c, NB * N); if (rc) return rc; }
+    const bool fuseq = q && N <= 2;
+    if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
     for (int64_t i12 = 0; i12 < s1->ne[2]; i12++) {
@@ -317,20 +328,27 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
         float * y = (float *) ((char *) d->data + i12 * d->nb[2] + i13 * d->nb[3]) + row_off_dst;
         const int64_t i02 = i12 / r2, i03 = i13 / r3;
         if (q) {
-            const bool reuse = c->in_graph && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
-            if (!reuse) {
-                CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
-                c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
-            }
-            const int64_t bb = block_bytes(s0->type);
-            const int64_t blk_off = (i02 * s0->nb[2] + i03 * s0->nb[3]) / bb;     // blocks from the tensor's first block
-            WFields f = wfields(s0->type);
-            WPtrs wp = wp0;
-            for (int i = 0; i < f.n; i++) wp.p[i] += blk_off * f.size[i];
-            for (int64_t c0 = 0; c0 < N; c0 += 8) {
-                const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
-                ActView av{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
-                CU(launch_gemv_q(s0->type, wp, M, K, av, nc, y + c0 * dcs, dcs, c->st, /*pdl=*/true)); c->launches++;
+            GemvArgs a{};
+            a.nmat = 1; a.K = K; a.dcs = dcs;
+            a.mat[0].w = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
+            a.mat[0].M = M;
+            if (fuseq) {
+                a.mat[0].dst = y;
+                if (fa) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
+                a.x = (const float *) x; a.x_col_stride = s1->nb[1];
+                CU(launch_gemv2(s0->type, a, (int) N, true, c->st)); c->launches++;
+            } else {
+                const bool reuse = c->in_graph && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
+                if (!reuse) {
+                    CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
+                    c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
+                }
+                for (int64_t c0 = 0; c0 < N; c0 += 8) {
+                    const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
+                    a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
+                    a.mat[0].dst = y + c0 * dcs;
+                    CU(launch_gemv2(s0->type, a, nc, false, c->st)); c->launches++;
+                }
             }
         } else {
             const char * w = (const char *) s0->data + i02 * s0->nb[2] + i03 * s0->nb[3];
@@ -346,6 +364,64 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
         const char * qp = (const char *) c->q_ptr;
         if (qp && (d->data_len <= 0 || (qp >= lo && qp < hi))) c->q_ptr = nullptr;
     }
+    return 0;
+}
+
+// ---- graph-level fusion helpers (b200_graph_compute only)
+static bool is_vec_mulmat(const b200_node & n) {       // quantised W x one f32 column, plain 2-D, device tensors
+    return n.dst.op == B200_OP_MUL_MAT && is_qweight(n.src0.type) && (n.src0.flags & B200_TENSOR_REPACKED) &&
+           n.src1.ne[1] == 1 && n.src1.ne[2] == 1 && n.src1.ne[3] == 1 && n.src0.ne[2] == 1 && n.src0.ne[3] == 1;
+}
+static bool overlap(const void * a, int64_t na, const void * b, int64_t nb) {
+    const char * x = (const char *) a; const char * y = (const char *) b;
+    return x < y + nb && y < x + na;
+}
+static bool is_vec_f32(const b200_tensor & t, int64_t n) {
+    return t.type == T_F32 && t.ne[0] == n && t.ne[1] == 1 && t.ne[2] == 1 && t.ne[3] == 1 && t.nb[0] == 4;
+}
+// MUL_MAT node i followed by ADD node i+1 that consumes its dst: one launch writes both results
+static bool can_fuse_add(const b200_node & mm, const b200_node & ad, FusedAdd * fa) {
+    if (!is_vec_mulmat(mm) || ad.dst.op != B200_OP_ADD) return false;
+    const int64_t M = mm.src0.ne[1];
+    if (!is_vec_f32(ad.src0, M) || !is_vec_f32(ad.src1, M) || !is_vec_f32(ad.dst, M) || !is_vec_f32(mm.dst, M)) return false;
+    const void * other;
+    if (ad.src0.data == mm.dst.data) other = ad.src1.data; else if (ad.src1.data == mm.dst.data) other = ad.src0.data; else return false;
+    const int64_t bytes = M * 4, K4 = mm.src0.ne[0] * 4;
+    // the add result must not land on anything other CTAs of the same launch still read or write
+    if (overlap(ad.dst.data, bytes, mm.src1.data, K4) || overlap(ad.dst.data, bytes, mm.dst.data, bytes)) return false;
+    if (other != ad.dst.data && overlap(ad.dst.data, bytes, other, bytes)) return false;
+    if (overlap(mm.dst.data, bytes, other, bytes) || overlap(mm.dst.data, bytes, mm.src1.data, K4)) return false;
+    fa->src = (const float *) other; fa->dst = (float *) ad.dst.data;
+    return true;
+}
+// consecutive vector MUL_MATs over the same activation vector and weight type: one grouped launch (q/k/v, gate/up)
+static int group_len(const b200_node * nodes, int i, int n) {
+    if (!is_vec_mulmat(nodes[i])) return 1;
+    int len = 1;
+    while (len < 3 && i + len < n) {
+        const b200_node & a = nodes[i]; const b200_node & b = nodes[i + len];
+        if (!is_vec_mulmat(b) || b.src0.type != a.src0.type || b.src1.data != a.src1.data || b.src0.ne[0] != a.src0.ne[0] ||
+            b.src1.nb[0] != 4 || !is_vec_f32(b.dst, b.src0.ne[1])) break;
+        // no member may write what another member (or the shared activation) occupies
+        bool clash = overlap(b.dst.data, b.src0.ne[1] * 4, a.src1.data, a.src0.ne[0] * 4);
+        for (int j = 0; j < len && !clash; j++) clash = overlap(b.dst.data, b.src0.ne[1] * 4, nodes[i + j].dst.data, nodes[i + j].src0.ne[1] * 4);
+        if (clash) break;
+        len++;
+    }
+    if (len > 1 && (!is_vec_f32(nodes[i].dst, nodes[i].src0.ne[1]) ||
+                    overlap(nodes[i].dst.data, nodes[i].src0.ne[1] * 4, nodes[i].src1.data, nodes[i].src0.ne[0] * 4))) return 1;
+    return len;
+}
+static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
+    GemvArgs a{};
+    a.nmat = len; a.K = nodes[0].src0.ne[0]; a.dcs = 0;
+    a.x = (const float *) nodes[0].src1.data; a.x_col_stride = nodes[0].src1.nb[1];
+    for (int j = 0; j < len; j++) {
+        int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &nodes[j].dst); if (rc) return rc;
+        WPtrs wp; rc = wptrs_of(&nodes[j].src0, &wp); if (rc) return rc;
+        a.mat[j].w = wp; a.mat[j].M = nodes[j].src0.ne[1]; a.mat[j].dst = (float *) nodes[j].dst.data;
+    }
+    CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
     return 0;
 }
 
@@ -404,16 +480,26 @@ extern "C" int b200_mulmat(b200_handle h, const b200_tensor * s0, const b200_ten
 
 // ------------------------------------------------------------------------------------------------ graph compute
 static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
+    static const bool fuse = !(getenv("B200_FUSE") && atoi(getenv("B200_FUSE")) == 0);
     c->in_graph = true; c->q_ptr = nullptr;
     int rc = 0;
-    for (int i = 0; i < n && !rc; i++) {
+    for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
+        int used = 1;
         switch (d.op) {
             case B200_OP_NONE: break;
             case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
-            case B200_OP_MUL_MAT: rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0); break;
+            case B200_OP_MUL_MAT: {
+                FusedAdd fa;
+                const int gl = fuse ? group_len(nodes, i, n) : 1;
+                if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
+                else if (fuse && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
+                else rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0);
+                break;
+            }
             default: rc = fail(B200_ENOTSUP, "graph node %d: op %d not offloaded", i, d.op);
         }
+        i += used;
     }
     c->in_graph = false; c->q_ptr = nullptr;
     return rc;
