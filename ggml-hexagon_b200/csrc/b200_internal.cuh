@@ -84,10 +84,12 @@ struct GemvArgs {
     int steps; int64_t K; int64_t dcs;
     const float * x; int64_t x_col_stride;     // FUSEQ: f32 activations, column stride in bytes
     ActView act;                                // !FUSEQ: pre-quantised scratch
+    int l2_prefetch;                            // each CTA bulk-prefetches its row slice into L2 first
 };
 // fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
 cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
 bool gemv_pdl_enabled();
+bool gemv_fuseq_enabled();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)
 cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, int64_t K,
                             const float * x, int64_t x_col_stride, int ncols,

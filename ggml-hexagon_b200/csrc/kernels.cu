@@ -103,8 +103,8 @@ quantize_q8_1_kernel(const char * __restrict__ x, const int64_t row_stride, cons
     const int64_t gid = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;      // one per 4 elements
     const int64_t blk = gid >> 3;                                              // global block index
 #if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();   // dependents only prefetch weights until their own sync returns
     cudaGridDependencySynchronize();
-    cudaTriggerProgrammaticLaunchCompletion();
 #endif
     if (blk >= NB * nrows) return;             // whole 8-lane groups exit together
     const int64_t row = blk / NB, b = blk - row * NB;
@@ -169,15 +169,13 @@ __global__ void __launch_bounds__(256)
 add_f32_vec_kernel(const float4 * __restrict__ a, const float4 * __restrict__ b, float4 * __restrict__ d,
                    const int64_t n4, const int64_t nb4 /* period of b in float4, or n4 */) {
 #if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();
     cudaGridDependencySynchronize();
 #endif
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
         const float4 x = a[i], y = b[nb4 == n4 ? i : i % nb4];
         d[i] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
     }
-#if __CUDA_ARCH__ >= 900
-    cudaTriggerProgrammaticLaunchCompletion();
-#endif
 }
 // General path: any byte strides, src1 repeated in every dim (i % ne1x), one thread per element.
 __global__ void __launch_bounds__(256) add_f32_gen_kernel(const AddArgs p, const int64_t n) {

@@ -319,7 +319,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     WPtrs wp0{};
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
-    const bool fuseq = q && N <= 2;
+    const bool fuseq = q && N <= 2 && gemv_fuseq_enabled();
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
@@ -343,6 +343,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
                     c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
                 }
+                if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
                     a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
@@ -414,14 +415,29 @@ static int group_len(const b200_node * nodes, int i, int n) {
 }
 static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     GemvArgs a{};
-    a.nmat = len; a.K = nodes[0].src0.ne[0]; a.dcs = 0;
-    a.x = (const float *) nodes[0].src1.data; a.x_col_stride = nodes[0].src1.nb[1];
+    const int64_t K = nodes[0].src0.ne[0], NB = K / 32;
+    a.nmat = len; a.K = K; a.dcs = 0;
+    const float * x = (const float *) nodes[0].src1.data;
     for (int j = 0; j < len; j++) {
         int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &nodes[j].dst); if (rc) return rc;
         WPtrs wp; rc = wptrs_of(&nodes[j].src0, &wp); if (rc) return rc;
         a.mat[j].w = wp; a.mat[j].M = nodes[j].src0.ne[1]; a.mat[j].dst = (float *) nodes[j].dst.data;
     }
-    CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
+    if (gemv_fuseq_enabled()) {
+        a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
+        CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
+        return 0;
+    }
+    int rc = ensure_act(c, NB); if (rc) return rc;
+    const bool reuse = c->q_ptr == (const void *) x && c->q_K == K && c->q_N == 1;
+    if (!reuse) {
+        CU(launch_quantize_q8_1_soa(x, K * 4, K, 1, c->act_qs, c->act_ds, c->st)); c->launches++;
+        c->q_ptr = x; c->q_K = K; c->q_N = 1; c->q_stride = nodes[0].src1.nb[1];
+    }
+    a.act = ActView{c->act_qs, c->act_ds, NB};
+    CU(launch_gemv2(nodes[0].src0.type, a, 1, false, c->st)); c->launches++;
+    for (int j = 0; j < len; j++)
+        if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4, c->q_ptr, K * 4)) c->q_ptr = nullptr;
     return 0;
 }
 

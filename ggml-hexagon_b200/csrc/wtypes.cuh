@@ -200,4 +200,105 @@ template <> struct WT<T_Q6_K> {
     }
 };
 
+// ------------------------------------------------------------------------------------------------ register-resident activations
+// GEMV v4 (gemv.cu): a lane owns ONE step of the row for the whole CTA tile, so it loads that step's activations into
+// registers once (WR<T>::Act) and then only streams weights.  dp4a.u32.s32 lets the high nibbles stay in place:
+// dot(q & 0xF0F0F0F0, a) = 16 * dot(q >> 4, a), exact, so no shift per word is needed.
+__device__ __forceinline__ int dp4a_u8s8(uint32_t a, uint32_t b, int c) {
+    int d; asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ int dot16_lo(const uint4 & q, const uint4 & a) {     // low nibbles
+    int s = dp4a_u8s8(q.x & 0x0F0F0F0Fu, a.x, 0); s = dp4a_u8s8(q.y & 0x0F0F0F0Fu, a.y, s);
+    s = dp4a_u8s8(q.z & 0x0F0F0F0Fu, a.z, s); return dp4a_u8s8(q.w & 0x0F0F0F0Fu, a.w, s);
+}
+__device__ __forceinline__ int dot16_hi16(const uint4 & q, const uint4 & a) {   // 16 x (high nibbles . a)
+    int s = dp4a_u8s8(q.x & 0xF0F0F0F0u, a.x, 0); s = dp4a_u8s8(q.y & 0xF0F0F0F0u, a.y, s);
+    s = dp4a_u8s8(q.z & 0xF0F0F0F0u, a.z, s); return dp4a_u8s8(q.w & 0xF0F0F0F0u, a.w, s);
+}
+
+template <int TYPE> struct WR;
+
+template <> struct WR<T_Q4_0> {
+    struct Act { uint4 a0, a1; float d; int isum8; };
+    static __device__ __forceinline__ Act load_act(const ActCol & a, int s) {
+        Act r; r.a0 = a.p0[s]; r.a1 = a.p1[s];
+        const ADesc ad = load_adesc(a.ds + s); r.d = ad.d; r.isum8 = 8 * (ad.isum0 + ad.isum1);
+        return r;
+    }
+    static __device__ __forceinline__ float dot(const WT<T_Q4_0>::Frag & f, const Act & a) {
+        const int sumi = dot16_lo(f.q, a.a0) + (dot16_hi16(f.q, a.a1) >> 4) - a.isum8;
+        return (f.d * a.d) * (float) sumi;
+    }
+};
+
+template <> struct WR<T_Q8_0> {
+    struct Act { uint4 a0, a1; float d; };
+    static __device__ __forceinline__ Act load_act(const ActCol & a, int s) {
+        Act r; r.a0 = a.p0[s]; r.a1 = a.p1[s]; r.d = load_adesc(a.ds + s).d; return r;
+    }
+    static __device__ __forceinline__ float dot(const WT<T_Q8_0>::Frag & f, const Act & a) {
+        const int sumi = dot16_ss(f.q0, a.a0) + dot16_ss(f.q1, a.a1);
+        return (f.d * a.d) * (float) sumi;
+    }
+};
+
+template <> struct WR<T_Q4_K> {
+    struct Act { uint4 a00, a01, a10, a11; float d0, d1; int isum0, isum1; };
+    static __device__ __forceinline__ Act load_act(const ActCol & a, int s) {
+        Act r; const int b0 = 2 * s, b1 = 2 * s + 1;
+        r.a00 = a.p0[b0]; r.a01 = a.p1[b0]; r.a10 = a.p0[b1]; r.a11 = a.p1[b1];
+        const ADesc x = load_adesc(a.ds + b0), y = load_adesc(a.ds + b1);
+        r.d0 = x.d; r.d1 = y.d; r.isum0 = x.isum0 + x.isum1; r.isum1 = y.isum0 + y.isum1;
+        return r;
+    }
+    // s = step index within the row (only s & 3 matters: which 64-element chunk of the super-block)
+    static __device__ __forceinline__ float dot(const WT<T_Q4_K>::Frag & f, const Act & a, int s) {
+        const int dlo = dot16_lo(f.q0, a.a00) + dot16_lo(f.q1, a.a01);
+        const int dhi = (dot16_hi16(f.q0, a.a10) + dot16_hi16(f.q1, a.a11)) >> 4;
+        const int c = s & 3;
+        int sc0, m0, sc1, m1;
+        k4_scale_min(f.hdr.y, f.hdr.z, f.hdr.w, 2 * c,     sc0, m0);
+        k4_scale_min(f.hdr.y, f.hdr.z, f.hdr.w, 2 * c + 1, sc1, m1);
+        const float2 dm = __half22float2(*reinterpret_cast<const __half2 *>(&f.hdr.x));
+        const float sd = a.d0 * (float) (dlo * sc0) + a.d1 * (float) (dhi * sc1);
+        const float sm = a.d0 * (float) (a.isum0 * m0) + a.d1 * (float) (a.isum1 * m1);
+        return dm.x * sd - dm.y * sm;
+    }
+};
+
+template <> struct WR<T_Q6_K> {
+    struct Act { uint4 a[4]; float d[4]; int isum32[4]; };
+    static __device__ __forceinline__ Act load_act(const ActCol & a, int s) {
+        Act r; const int sbh = (s >> 1) * 4, j = s & 1;
+        const uint4 * pl = j ? a.p1 : a.p0;
+        #pragma unroll
+        for (int q = 0; q < 4; q++) {
+            r.a[q] = pl[sbh + q];
+            const ADesc ad = load_adesc(a.ds + sbh + q);
+            r.d[q] = ad.d; r.isum32[q] = 32 * (j ? ad.isum1 : ad.isum0);
+        }
+        return r;
+    }
+    static __device__ __forceinline__ float dot(const WT<T_Q6_K>::Frag & f, const Act & a, int s) {
+        const int j = s & 1;
+        const uint32_t M3 = 0x30303030u, ML = 0x0F0F0F0Fu;
+        uint4 v0, v1, v2, v3;
+        v0 = make_uint4((f.l0.x & ML) | ((f.hq.x << 4) & M3), (f.l0.y & ML) | ((f.hq.y << 4) & M3), (f.l0.z & ML) | ((f.hq.z << 4) & M3), (f.l0.w & ML) | ((f.hq.w << 4) & M3));
+        v1 = make_uint4((f.l1.x & ML) | ((f.hq.x << 2) & M3), (f.l1.y & ML) | ((f.hq.y << 2) & M3), (f.l1.z & ML) | ((f.hq.z << 2) & M3), (f.l1.w & ML) | ((f.hq.w << 2) & M3));
+        v2 = make_uint4(((f.l0.x >> 4) & ML) | (f.hq.x & M3), ((f.l0.y >> 4) & ML) | (f.hq.y & M3), ((f.l0.z >> 4) & ML) | (f.hq.z & M3), ((f.l0.w >> 4) & ML) | (f.hq.w & M3));
+        v3 = make_uint4(((f.l1.x >> 4) & ML) | ((f.hq.x >> 2) & M3), ((f.l1.y >> 4) & ML) | ((f.hq.y >> 2) & M3), ((f.l1.z >> 4) & ML) | ((f.hq.z >> 2) & M3), ((f.l1.w >> 4) & ML) | ((f.hq.w >> 2) & M3));
+        const int d0 = dot16_ss(v0, a.a[0]) - a.isum32[0], d1 = dot16_ss(v1, a.a[1]) - a.isum32[1];
+        const int d2 = dot16_ss(v2, a.a[2]) - a.isum32[2], d3 = dot16_ss(v3, a.a[3]) - a.isum32[3];
+        const uint32_t lo = f.sc.x >> (8 * j), hi = f.sc.y >> (8 * j);
+        const int sc0 = (int8_t) (lo & 0xFF), sc1 = (int8_t) ((lo >> 16) & 0xFF);
+        const int sc2 = (int8_t) (hi & 0xFF), sc3 = (int8_t) ((hi >> 16) & 0xFF);
+        const float sd = a.d[0] * (float) (d0 * sc0) + a.d[1] * (float) (d1 * sc1) + a.d[2] * (float) (d2 * sc2) + a.d[3] * (float) (d3 * sc3);
+        return f.d * sd;
+    }
+};
+// uniform call shape for the kernel
+template <int TYPE> __device__ __forceinline__ float wr_dot(const typename WT<TYPE>::Frag & f, const typename WR<TYPE>::Act & a, int s) {
+    if constexpr (TYPE == T_Q4_0 || TYPE == T_Q8_0) return WR<TYPE>::dot(f, a); else return WR<TYPE>::dot(f, a, s);
+}
+
 }  // namespace b200
