@@ -1,0 +1,411 @@
+// ggml-b200.cpp — the ggml backend plugin (libggml-b200.so): drop-in for libggml-hexagon.so in cDSP mode.
+//
+// Mirrors section 8 of the reference backend (ggml/src/ggml-hexagon/ggml-hexagon.cpp:5065-6110): registry entry,
+// device, buffer type, buffer, backend, supports_op, graph_compute.  Everything below the ggml structs goes
+// through the C-ABI op layer (include/ggml_b200_ops.h), which takes the seat of the FastRPC calls
+// ggmlop_dsp_open/close/add/mulmat (ggml-hexagon.cpp:4975-5060).  No CPU compute path: an op we do not
+// accelerate is declined in supports_op, never emulated.
+//
+// Compiled against the reference's own headers (ggml.h, ggml-backend.h, ggml-backend-impl.h); nothing of the
+// reference is copied into this repository.
+#include "ggml-b200.h"
+#include "ggml-backend-impl.h"
+#include "ggml-impl.h"
+#include "ggml_b200_ops.h"
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#define B200_LOG(...) do { if (getenv("GGML_B200_VERBOSE")) { fprintf(stderr, "[ggml-b200] " __VA_ARGS__); fputc('\n', stderr); } } while (0)
+
+// ------------------------------------------------------------------------------------------------ contexts
+struct b200_device_ctx {
+    int         ordinal = 0;
+    std::string name;            // "B200_<ordinal>"   (ggml_backend_hexagon_get_devname)
+    std::string desc;            // CUDA device name
+    b200_handle mem = 0;         // session used by the buffers of this device (set/get/memset/clear)
+    std::mutex  mu;
+    ggml_backend_buffer_type buft;
+};
+struct b200_backend_ctx {
+    b200_device_ctx * dev = nullptr;
+    b200_handle       h   = 0;   // own stream, scratch and CUDA-graph cache
+    std::string       name;
+    std::vector<b200_node> nodes;
+};
+struct b200_buffer_ctx {
+    b200_device_ctx * dev = nullptr;
+    void *            base = nullptr;
+    size_t            size = 0;
+};
+
+static b200_handle dev_session(b200_device_ctx * d) {
+    std::lock_guard<std::mutex> lk(d->mu);
+    if (!d->mem) {
+        char uri[32]; snprintf(uri, sizeof(uri), "cuda:%d", d->ordinal);
+        if (b200_open(uri, &d->mem) != 0) { fprintf(stderr, "[ggml-b200] %s\n", b200_last_error()); d->mem = 0; }
+    }
+    return d->mem;
+}
+
+static bool is_qweight(enum ggml_type t) {
+    return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K;
+}
+static const ggml_tensor * root_of(const ggml_tensor * t) { return t->view_src ? t->view_src : t; }
+
+// ------------------------------------------------------------------------------------------------ tensor -> C-ABI descriptor
+// (what ggmlhexagon_compute does when it fills struct dsptensor, ggml-hexagon.cpp:5003-5049; 64-bit ne/nb here)
+static bool to_b200(const ggml_tensor * t, b200_tensor * o, int op) {
+    memset(o, 0, sizeof(*o));
+    o->type = (int32_t) t->type; o->op = op;
+    for (int i = 0; i < 4; i++) { o->ne[i] = t->ne[i]; o->nb[i] = (int64_t) t->nb[i]; }
+    memcpy(o->op_params, t->op_params, sizeof(o->op_params));
+    o->data = t->data;
+    o->data_len = (int64_t) ggml_nbytes(t);
+    if (is_qweight(t->type)) {
+        // quantised tensors live in HBM in the SoA layout over their ROOT tensor's region (see buffer set_tensor)
+        const ggml_tensor * r = root_of(t);
+        const int64_t bb = (int64_t) ggml_type_size(t->type);
+        const int64_t off = (const char *) t->data - (const char *) r->data;
+        if (off < 0 || off % bb) return false;
+        o->flags = B200_TENSOR_REPACKED;
+        o->w_base = r->data; o->w_blocks = (int64_t) ggml_nbytes(r) / bb; o->w_first = off / bb;
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ supports_op
+// Reference predicate: ggmlhexagon_can_handle_op_through_cdsp (ggml-hexagon.cpp:5065-5115): NONE -> true;
+// ADD f32; MUL_MAT with f32 src1/dst and f32 or quantised src0.  We widen ADD to ggml's repeat-broadcast
+// (binary-ops.cpp:50-117) and the quantised set to q4_0/q8_0/q4_K/q6_K, and decline layouts the kernels
+// do not take (the caller then keeps the node on another backend; test-backend-ops prints "not supported").
+static bool b200_supports_mul_mat(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0]; const ggml_tensor * b = op->src[1];
+    if (!a || !b) return false;
+    if (b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (!(a->type == GGML_TYPE_F32 || is_qweight(a->type))) return false;
+    if (b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
+    if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
+    if (is_qweight(a->type)) {
+        const size_t bb = ggml_type_size(a->type);
+        if (a->ne[0] % 32) return false;
+        if (a->nb[0] != bb || a->nb[1] != ggml_row_size(a->type, a->ne[0])) return false;      // contiguous rows
+        if (a->nb[2] % bb || a->nb[3] % bb) return false;
+        if ((b->nb[1] | b->nb[2] | b->nb[3]) & 15) return false;                                // 128-bit activation loads
+        const ggml_tensor * r = root_of(a);
+        if (a->data && r->data && (((const char *) a->data - (const char *) r->data) % (ptrdiff_t) bb)) return false;
+    } else {
+        if (a->nb[0] != sizeof(float)) return false;
+    }
+    return true;
+}
+static bool b200_supports_add(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0]; const ggml_tensor * b = op->src[1];
+    if (!a || !b) return false;
+    if (a->type != GGML_TYPE_F32 || b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (!ggml_are_same_shape(a, op) || !ggml_can_repeat(b, a)) return false;
+    return true;
+}
+static bool b200_device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    switch (op->op) {
+        case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_ADD:     return b200_supports_add(op);
+        case GGML_OP_MUL_MAT: return b200_supports_mul_mat(op);
+        default:              return false;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ buffer
+// (ggml_backend_hexagon_buffer_interface, ggml-hexagon.cpp:5361-5427.)  Device-private memory (is_host = false):
+// callers reach the data only through set/get, which lets quantised tensors be kept in the SoA layout.
+static void b200_buffer_free(ggml_backend_buffer_t buffer) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    if (c->base) b200_free(dev_session(c->dev), c->base);
+    delete c;
+}
+static void * b200_buffer_get_base(ggml_backend_buffer_t buffer) { return ((b200_buffer_ctx *) buffer->context)->base; }
+
+static void qrange(const ggml_tensor * t, size_t offset, size_t size, void ** base, int64_t * T, int64_t * first, int64_t * n) {
+    const ggml_tensor * r = root_of(t);
+    const int64_t bb = (int64_t) ggml_type_size(t->type);
+    const int64_t pos = ((const char *) t->data - (const char *) r->data) + (int64_t) offset;
+    GGML_ASSERT(pos % bb == 0 && (int64_t) size % bb == 0 && "b200: quantised tensors are read/written in whole blocks");
+    *base = r->data; *T = (int64_t) ggml_nbytes(r) / bb; *first = pos / bb; *n = (int64_t) size / bb;
+}
+static void b200_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    b200_handle h = dev_session(c->dev);
+    int rc;
+    if (is_qweight(t->type)) {
+        void * base; int64_t T, first, n; qrange(t, offset, size, &base, &T, &first, &n);
+        rc = b200_weights_upload(h, (int32_t) t->type, base, T, first, n, data);
+    } else {
+        rc = b200_memcpy_h2d(h, (char *) t->data + offset, data, size);
+    }
+    if (rc) GGML_ABORT("b200 set_tensor: %s", b200_last_error());
+}
+static void b200_buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * t, void * data, size_t offset, size_t size) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    b200_handle h = dev_session(c->dev);
+    int rc;
+    if (is_qweight(t->type)) {
+        void * base; int64_t T, first, n; qrange(t, offset, size, &base, &T, &first, &n);
+        rc = b200_weights_download(h, (int32_t) t->type, base, T, first, n, data);
+    } else {
+        rc = b200_memcpy_d2h(h, data, (const char *) t->data + offset, size);
+    }
+    if (rc) GGML_ABORT("b200 get_tensor: %s", b200_last_error());
+}
+static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, uint8_t value, size_t offset, size_t size) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    b200_handle h = dev_session(c->dev);
+    // a constant byte pattern is the same in the native and in the SoA layout only over whole tensors; partial
+    // fills of a quantised tensor are not a thing callers do (ggml-backend.cpp uses memset for f32/kv zeroing)
+    GGML_ASSERT(!is_qweight(t->type) || (offset == 0 && size == ggml_nbytes(t)));
+    if (b200_memset(h, (char *) t->data + offset, value, size) || b200_synchronize(h)) GGML_ABORT("b200 memset_tensor: %s", b200_last_error());
+}
+static void b200_buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    b200_handle h = dev_session(c->dev);
+    if (b200_memset(h, c->base, value, c->size) || b200_synchronize(h)) GGML_ABORT("b200 clear: %s", b200_last_error());
+}
+static const ggml_backend_buffer_i b200_buffer_iface = {
+    /* free_buffer   */ b200_buffer_free,
+    /* get_base      */ b200_buffer_get_base,
+    /* init_tensor   */ nullptr,
+    /* memset_tensor */ b200_buffer_memset_tensor,
+    /* set_tensor    */ b200_buffer_set_tensor,
+    /* get_tensor    */ b200_buffer_get_tensor,
+    /* cpy_tensor    */ nullptr,          // copies go through get/set (layout-aware)
+    /* clear         */ b200_buffer_clear,
+    /* reset         */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------------ buffer type
+// (ggml_backend_hexagon_buffer_type_*, ggml-hexagon.cpp:5429-5510.)
+static const char * b200_buft_name(ggml_backend_buffer_type_t buft) { return ((b200_device_ctx *) buft->context)->name.c_str(); }
+static ggml_backend_buffer_t b200_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    b200_device_ctx * d = (b200_device_ctx *) buft->context;
+    b200_handle h = dev_session(d);
+    if (!h) return nullptr;
+    void * p = nullptr;
+    if (b200_malloc(h, size + 256, &p) != 0) {       // NULL on OOM, as ggml-hexagon.cpp:5470-5472
+        B200_LOG("alloc_buffer(%zu) failed: %s", size, b200_last_error());
+        return nullptr;
+    }
+    b200_buffer_ctx * c = new b200_buffer_ctx{d, p, size};
+    return ggml_backend_buffer_init(buft, b200_buffer_iface, c, size);
+}
+static size_t b200_buft_alignment(ggml_backend_buffer_type_t) { return 256; }
+static size_t b200_buft_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * t) {
+    // room for the 16-byte-granular bulk copies of the 2-byte scale arrays to over-read
+    return ggml_nbytes(t) + (is_qweight(t->type) ? 64 : 0);
+}
+static bool b200_buft_is_host(ggml_backend_buffer_type_t) { return false; }
+static const ggml_backend_buffer_type_i b200_buft_iface = {
+    /* get_name       */ b200_buft_name,
+    /* alloc_buffer   */ b200_buft_alloc,
+    /* get_alignment  */ b200_buft_alignment,
+    /* get_max_size   */ nullptr,
+    /* get_alloc_size */ b200_buft_alloc_size,
+    /* is_host        */ b200_buft_is_host,
+};
+
+// ------------------------------------------------------------------------------------------------ backend
+// (ggml_backend_hexagon_* backend interface, ggml-hexagon.cpp:5517-5574, table :5836-5850.)
+static ggml_guid_t b200_guid(void) {
+    static ggml_guid guid = {0xb2, 0x00, 0x5a, 0x10, 0x0a, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x01};
+    return &guid;
+}
+static const char * b200_backend_name(ggml_backend_t backend) { return ((b200_backend_ctx *) backend->context)->name.c_str(); }
+static void b200_backend_free(ggml_backend_t backend) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    if (c->h) b200_close(c->h);
+    delete c;
+    delete backend;
+}
+static void b200_backend_synchronize(ggml_backend_t backend) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    if (b200_synchronize(c->h)) GGML_ABORT("b200 synchronize: %s", b200_last_error());
+}
+static bool is_view_op(enum ggml_op op) {
+    return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE;
+}
+// node loop of ggmlhexagon_backend_graph_compute_general (ggml-hexagon.cpp:5555-5574): view ops are no-ops, every other
+// node is dst = op(src0, src1).  The whole list goes down in ONE call; asynchronous (ggml_backend_graph_compute adds
+// the synchronize, ggml-backend.cpp:327-335).
+static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    c->nodes.clear();
+    for (int i = 0; i < cgraph->n_nodes; i++) {
+        ggml_tensor * node = cgraph->nodes[i];
+        if (is_view_op(node->op) || ggml_is_empty(node)) continue;
+        int op;
+        switch (node->op) {
+            case GGML_OP_ADD:     op = B200_OP_ADD; break;
+            case GGML_OP_MUL_MAT: op = B200_OP_MUL_MAT; break;
+            default:
+                fprintf(stderr, "[ggml-b200] graph_compute: op %s was never admitted by supports_op\n", ggml_op_name(node->op));
+                return GGML_STATUS_FAILED;
+        }
+        b200_node n;
+        if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || !to_b200(node->src[1], &n.src1, B200_OP_NONE) || !to_b200(node, &n.dst, op)) {
+            fprintf(stderr, "[ggml-b200] graph_compute: node %s has a layout supports_op declines\n", node->name);
+            return GGML_STATUS_FAILED;
+        }
+        c->nodes.push_back(n);
+    }
+    if (c->nodes.empty()) return GGML_STATUS_SUCCESS;
+    // long node lists (a decode step) are captured once as a CUDA graph and replayed; short ones are launched directly
+    static const int graph_min = getenv("GGML_B200_GRAPH_MIN") ? atoi(getenv("GGML_B200_GRAPH_MIN")) : 8;
+    const int rc = b200_graph_compute(c->h, c->nodes.data(), (int32_t) c->nodes.size(), (int) c->nodes.size() >= graph_min);
+    if (rc == B200_ENOMEM) return GGML_STATUS_ALLOC_FAILED;
+    if (rc) { fprintf(stderr, "[ggml-b200] graph_compute: %s\n", b200_last_error()); return GGML_STATUS_FAILED; }
+    return GGML_STATUS_SUCCESS;
+}
+static const ggml_backend_i b200_backend_iface = {
+    /* get_name           */ b200_backend_name,
+    /* free               */ b200_backend_free,
+    /* set_tensor_async   */ nullptr,
+    /* get_tensor_async   */ nullptr,
+    /* cpy_tensor_async   */ nullptr,
+    /* synchronize        */ b200_backend_synchronize,
+    /* graph_plan_create  */ nullptr,
+    /* graph_plan_free    */ nullptr,
+    /* graph_plan_update  */ nullptr,
+    /* graph_plan_compute */ nullptr,
+    /* graph_compute      */ b200_backend_graph_compute,
+    /* event_record       */ nullptr,
+    /* event_wait         */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------------ device
+// (ggml_backend_hexagon_device_*, ggml-hexagon.cpp:5630-5834.)
+static const char * b200_device_name(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->name.c_str(); }
+static const char * b200_device_desc(ggml_backend_dev_t dev) { return ((b200_device_ctx *) dev->context)->desc.c_str(); }
+static void b200_device_memory(ggml_backend_dev_t dev, size_t * free, size_t * total) {
+    int64_t t = 0, f = 0;
+    b200_device_info(((b200_device_ctx *) dev->context)->ordinal, nullptr, 0, &t, &f, nullptr);
+    *free = (size_t) f; *total = (size_t) t;
+}
+static enum ggml_backend_dev_type b200_device_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }   // as cDSP mode, :5640-5644
+static void b200_device_props(ggml_backend_dev_t dev, ggml_backend_dev_props * props) {
+    props->name = b200_device_name(dev);
+    props->description = b200_device_desc(dev);
+    props->type = b200_device_type(dev);
+    b200_device_memory(dev, &props->memory_free, &props->memory_total);
+    props->caps = { /* async */ false, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ false };
+}
+static ggml_backend_t b200_device_init_backend(ggml_backend_dev_t dev, const char *) {
+    b200_device_ctx * d = (b200_device_ctx *) dev->context;
+    b200_backend_ctx * c = new b200_backend_ctx();
+    c->dev = d; c->name = d->name;
+    char uri[32]; snprintf(uri, sizeof(uri), "cuda:%d", d->ordinal);
+    if (b200_open(uri, &c->h) != 0) {
+        fprintf(stderr, "[ggml-b200] init_backend: %s\n", b200_last_error());
+        delete c;
+        return nullptr;
+    }
+    return new ggml_backend{ /* guid */ b200_guid(), /* iface */ b200_backend_iface, /* device */ dev, /* context */ c };
+}
+static ggml_backend_buffer_type_t b200_device_buffer_type(ggml_backend_dev_t dev) { return &((b200_device_ctx *) dev->context)->buft; }
+static bool b200_device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return buft->iface.get_name == b200_buft_name && buft->context == dev->context;           // own buffers only, :5806-5816
+}
+static bool b200_device_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    // worth pulling a weight over for: batched MUL_MAT (same threshold idea as ggml-cuda's min batch size)
+    return op->op == GGML_OP_MUL_MAT && op->ne[1] >= 32;
+}
+static const ggml_backend_device_i b200_device_iface = {
+    /* get_name             */ b200_device_name,
+    /* get_description      */ b200_device_desc,
+    /* get_memory           */ b200_device_memory,
+    /* get_type             */ b200_device_type,
+    /* get_props            */ b200_device_props,
+    /* init_backend         */ b200_device_init_backend,
+    /* get_buffer_type      */ b200_device_buffer_type,
+    /* get_host_buffer_type */ nullptr,
+    /* buffer_from_host_ptr */ nullptr,
+    /* supports_op          */ b200_device_supports_op,
+    /* supports_buft        */ b200_device_supports_buft,
+    /* offload_op           */ b200_device_offload_op,
+    /* event_new            */ nullptr,
+    /* event_free           */ nullptr,
+    /* event_synchronize    */ nullptr,
+};
+
+// ------------------------------------------------------------------------------------------------ registry
+// (ggml_backend_hexagon_reg_*, ggml-hexagon.cpp:5885-5994.)
+struct b200_reg_ctx {
+    std::vector<ggml_backend_device *> devices;
+    std::vector<b200_device_ctx *>     ctxs;
+};
+static const char * b200_reg_name(ggml_backend_reg_t) { return GGML_B200_BACKEND_NAME; }
+static size_t b200_reg_device_count(ggml_backend_reg_t reg) { return ((b200_reg_ctx *) reg->context)->devices.size(); }
+static ggml_backend_dev_t b200_reg_device(ggml_backend_reg_t reg, size_t i) {
+    b200_reg_ctx * r = (b200_reg_ctx *) reg->context;
+    GGML_ASSERT(i < r->devices.size());
+    return r->devices[i];
+}
+static void b200_set_n_threads(ggml_backend_t, int) {}     // accepted and ignored, as ggml-hexagon.cpp:5921-5932
+static void * b200_reg_proc_address(ggml_backend_reg_t, const char * name) {
+    if (strcmp(name, "ggml_backend_set_n_threads") == 0) return (void *) b200_set_n_threads;
+    // "ggml_backend_split_buffer_type": row split runs one process per GPU over NCCL (b200_mulmat_rowsplit), not as
+    // a single-process split buffer, so the name is not exported
+    return nullptr;
+}
+static const ggml_backend_reg_i b200_reg_iface = {
+    /* get_name         */ b200_reg_name,
+    /* get_device_count */ b200_reg_device_count,
+    /* get_device       */ b200_reg_device,
+    /* get_proc_address */ b200_reg_proc_address,
+};
+
+ggml_backend_reg_t ggml_backend_b200_reg(void) {
+    static std::mutex mu;
+    static ggml_backend_reg reg;
+    static bool done = false;
+    std::lock_guard<std::mutex> lk(mu);                      // init guarded by a mutex, as ggml-hexagon.cpp:5953-5954
+    if (!done) {
+        b200_reg_ctx * r = new b200_reg_ctx();               // static lifetime: the registry never frees a reg
+        int n = b200_device_count();
+        if (n > GGML_B200_MAX_DEVICES) n = GGML_B200_MAX_DEVICES;
+        reg = ggml_backend_reg{ /* api_version */ GGML_BACKEND_API_VERSION, /* iface */ b200_reg_iface, /* context */ r };
+        for (int i = 0; i < n; i++) {
+            b200_device_ctx * d = new b200_device_ctx();
+            char nm[128] = "";
+            b200_device_info(i, nm, sizeof(nm), nullptr, nullptr, nullptr);
+            d->ordinal = i; d->name = std::string("B200_") + std::to_string(i); d->desc = nm;
+            d->buft = ggml_backend_buffer_type{ /* iface */ b200_buft_iface, /* device */ nullptr, /* context */ d };
+            ggml_backend_device * dev = new ggml_backend_device{ /* iface */ b200_device_iface, /* reg */ &reg, /* context */ d };
+            d->buft.device = dev;
+            r->devices.push_back(dev); r->ctxs.push_back(d);
+        }
+        done = true;
+    }
+    return &reg;
+}
+
+int ggml_backend_b200_get_device_count(void) { return (int) b200_reg_device_count(ggml_backend_b200_reg()); }
+const char * ggml_backend_b200_get_devname(size_t dev_num) {
+    ggml_backend_reg_t reg = ggml_backend_b200_reg();
+    if (dev_num >= b200_reg_device_count(reg)) return "unknown";
+    return b200_device_name(b200_reg_device(reg, dev_num));
+}
+ggml_backend_t ggml_backend_b200_init(size_t dev_num, const char * params) {
+    ggml_backend_reg_t reg = ggml_backend_b200_reg();
+    if (dev_num >= b200_reg_device_count(reg)) return nullptr;
+    return b200_device_init_backend(b200_reg_device(reg, dev_num), params);
+}
+bool ggml_backend_is_b200(ggml_backend_t backend) { return backend != nullptr && ggml_guid_matches(backend->guid, b200_guid()); }
+
+// dynamic-loading entry points (ggml-backend-impl.h:215-246): no CUDA device -> score 0, the loader skips us
+static int b200_score(void) { return b200_device_count() > 0 ? 100 : 0; }
+GGML_BACKEND_DL_IMPL(ggml_backend_b200_reg)
+GGML_BACKEND_DL_SCORE_IMPL(b200_score)
