@@ -301,7 +301,7 @@ class Session:
 
     def graph_compute(self, nodes, use_cuda_graph=True):
         arr = (Node * len(nodes))(*nodes) if not isinstance(nodes, C.Array) else nodes
-        _ck(lib().b200_graph_compute(self.h, arr, len(arr), 1 if use_cuda_graph else 0))
+        _ck(lib().b200_graph_compute(self.h, arr, len(arr), int(use_cuda_graph)))
         return arr
 
     # timing

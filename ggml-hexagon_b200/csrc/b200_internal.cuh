@@ -98,6 +98,42 @@ cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, in
 cudaError_t launch_block_dots_impl(int type, WPtrs w, int64_t K, const int8_t * a_qs, int32_t * out,
                                    int8_t * sq, ActDS * sd, cudaStream_t st);
 
+// ---- decode stream kernel (decode_stream.cu): a whole decode node list as ONE persistent cooperative launch.
+// The host compiles the node list into stages; a stage is up to 3 vector MUL_MATs that share one activation vector
+// (optionally each with a fused residual ADD), or one plain vector ADD.
+enum : int { DS_GEMV = 0, DS_ADD = 1 };
+constexpr int DS_SLOT_BYTES = 18432 + 128;   // one ring slot: R weight rows of one matrix (all SoA fields)
+constexpr int DS_NSLOTS     = 10;
+constexpr int DS_ACT_BYTES  = 35840;         // q8_1 activations of one stage: K*1.25 bytes -> K <= 28672
+constexpr int DS_KMAX       = 28672;
+struct DsOp {
+    const uint8_t * f[4];        // SoA field pointers at the first block of the matrix
+    float * dst;                 // [M]
+    const float * add_src;       // fused GGML_OP_ADD (nullptr = none): add_dst[r] = add_src[r] + dst[r]
+    float * add_dst;
+    int M; int pad;
+};
+struct DsStage {
+    int kind, type, nops, K;
+    int steps;                   // lane-steps per row (K/32, K-quants K/64)
+    int R;                       // rows per ring slot (1, 2, 4 or 8)
+    int wait_prev;               // all CTAs must have finished every earlier stage before this one reads its inputs
+    int nfields;
+    int rw, pad0;                // rows of a slot one consumer warp handles (1 or 2)
+    int rowbytes[4];             // bytes of one row in each field array
+    int foff[4];                 // offset of each field inside a slot
+    int flead[4];                // 1: 2-byte field whose row start may be only 2-byte aligned (copy starts 16-B aligned, lead kept)
+    const float * x;             // GEMV: activations [K];  ADD: src0
+    DsOp op[3];                  // ADD: op[0].add_src = src1, op[0].dst = dst, op[0].M = n
+};
+int  ds_smem_bytes();
+int  ds_block_threads();
+int  ds_grid(int device);
+// cooperative launch, grid = number of SMs; counters: one uint32 per stage, zeroed once; epoch: 1, 2, 3 ... per launch
+int  ds_type_bit(int type);
+cudaError_t launch_decode_stream(const DsStage * prog_dev, int nstages, uint32_t * counters, uint32_t epoch, int grid, int type_mask,
+                                 long long * trace /* development: 4 clocks per (CTA, stage), or nullptr */, cudaStream_t st);
+
 struct AddArgs {
     const char * a; const char * b; char * d;
     int64_t ne[4];      // dst / src0 shape

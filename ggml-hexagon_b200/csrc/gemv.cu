@@ -24,26 +24,6 @@
 
 namespace b200 {
 
-// v[0..R) per lane -> total over the 32 lanes of v[row], returned in every lane with row == (lane >> (5-log2 R)) & (R-1)
-template <int R>
-__device__ __forceinline__ float reduce_rows(float (&v)[R], const int lane) {
-    int m = 16;
-    #pragma unroll
-    for (int n = R; n > 1; n >>= 1, m >>= 1) {
-        const bool up = lane & m;
-        #pragma unroll
-        for (int i = 0; i < n / 2; i++) {
-            const float keep = up ? v[i + n / 2] : v[i];
-            const float send = up ? v[i] : v[i + n / 2];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
-        }
-    }
-    for (; m > 0; m >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], m);
-    return v[0];
-}
-template <int R> struct Log2 { static constexpr int v = 1 + Log2<R / 2>::v; };
-template <> struct Log2<1> { static constexpr int v = 0; };
-
 // ITERS > 1: the row has more than 32*nwarps steps; warp w then owns slices w, w+nwarps, ... and the fragments of the
 // next slice are requested before the current one is consumed (DB = register double buffer).
 template <int TYPE, int NCOLS, int R, bool DB>

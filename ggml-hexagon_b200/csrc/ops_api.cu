@@ -61,6 +61,8 @@ static int nccl_load() {
 
 // ------------------------------------------------------------------------------------------------ context
 struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; };
+// a node list compiled for the decode stream kernel (decode_stream.cu); dev == nullptr: not compilable, use the graph path
+struct StreamProgram { DsStage * dev = nullptr; uint32_t * counters = nullptr; int nstages = 0; uint32_t epoch = 0; int type_mask = 0; };
 
 struct Ctx {
     uint64_t magic = 0xB200B200B200B200ull;
@@ -75,6 +77,8 @@ struct Ctx {
     bool in_graph = false;        // inside b200_graph_compute: src1 quantisation may be reused between nodes
     const void * q_ptr = nullptr; int64_t q_K = 0, q_N = 0, q_stride = 0;
     std::unordered_map<uint64_t, GraphEntry> graphs;
+    std::unordered_map<uint64_t, StreamProgram> programs;
+    int ds_grid = -1;             // CTAs of the decode stream kernel (-1: not probed yet, 0: unavailable)
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
 };
@@ -153,6 +157,7 @@ extern "C" int b200_close(b200_handle h) {
     CTX(h);
     cudaStreamSynchronize(c->st);
     for (auto & kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); }
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
     cudaStreamDestroy(c->st);
@@ -178,7 +183,7 @@ extern "C" int64_t b200_block_bytes(int32_t type) {
 extern "C" int b200_malloc(b200_handle h, size_t size, void ** ptr) {
     CTX(h); if (!ptr) return fail(B200_EINVAL, "ptr is NULL");
     *ptr = nullptr;
-    cudaError_t e = cudaMalloc(ptr, size ? size : 1);
+    cudaError_t e = cudaMalloc(ptr, size + 256);      // slack: 16-B granular bulk copies of 2-byte scale arrays may over-read
     if (e != cudaSuccess) { cudaGetLastError(); return fail(B200_ENOMEM, "cudaMalloc(%zu): %s", size, cudaGetErrorString(e)); }
     return 0;
 }
@@ -441,6 +446,112 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ decode stream program
+// Compile a node list into stages for decode_stream.cu.  Returns false when any node falls outside what the stream
+// kernel takes (then the per-node kernels run, as a CUDA graph): it takes vector MUL_MATs (one f32 column) over
+// REPACKED q4_0/q8_0/q4_K/q6_K weights with K <= DS_KMAX, and contiguous same-shape f32 vector ADDs.
+struct Span { const char * p; int64_t n; };
+static bool spans_clash(const std::vector<Span> & a, const std::vector<Span> & b) {
+    for (const Span & x : a) for (const Span & y : b) if (x.n > 0 && y.n > 0 && overlap(x.p, x.n, y.p, y.n)) return true;
+    return false;
+}
+static bool ds_fill_gemv(DsStage & st, const b200_node * nodes, int len, const FusedAdd * fa) {
+    const b200_tensor & w0 = nodes[0].src0;
+    const int type = w0.type;
+    const int64_t K = w0.ne[0];
+    const int be = block_elems(type);
+    if (K <= 0 || K > DS_KMAX || K % 32 || K % be) return false;
+    if ((uintptr_t) nodes[0].src1.data & 15) return false;
+    const WFields wf = wfields(type);
+    st = DsStage{};
+    st.kind = DS_GEMV; st.type = type; st.nops = len; st.K = (int) K;
+    st.steps = (int) (K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
+    st.nfields = wf.n;
+    st.x = (const float *) nodes[0].src1.data;
+    const int64_t bpr = K / be;                                    // blocks per row
+    for (int f = 0; f < wf.n; f++) {
+        st.rowbytes[f] = (int) (bpr * wf.size[f]);
+        st.flead[f] = (st.rowbytes[f] % 16) != 0;
+        if (st.flead[f] && wf.size[f] != 2) return false;
+    }
+    int R = 8;
+    for (; R >= 1; R >>= 1) {
+        int off = 0;
+        for (int f = 0; f < wf.n; f++) { st.foff[f] = off; off += ((R * st.rowbytes[f] + (st.flead[f] ? 16 : 0) + 15) & ~15); off = (off + 127) & ~127; }
+        if (off <= DS_SLOT_BYTES) break;
+    }
+    if (R < 1) return false;
+    // consumer mapping (decode_stream.cu): nsl K-slices of 32 lanes; up to 16 warps = nsl slices x rg row groups
+    {
+        const int nsl = (st.steps + 31) / 32;
+        if (nsl > 32) return false;
+        if (nsl > 16) { while (R > 1) R >>= 1; st.rw = 1; }             // two slices per warp, one row per slot
+        else {
+            int rgc = 16 / nsl, p2 = 1; while (p2 * 2 <= rgc) p2 *= 2;
+            while (R / (R < p2 ? R : p2) > 2) R >>= 1;                 // at most 2 rows of a slot per warp
+            st.rw = R / (R < p2 ? R : p2);
+            if (st.rw == 2 && type != T_Q4_0) { R >>= 1; st.rw = 1; }   // only the q4_0 kernels carry the 2-row variant
+        }
+        int off = 0;
+        for (int f = 0; f < wf.n; f++) { st.foff[f] = off; off += ((R * st.rowbytes[f] + (st.flead[f] ? 16 : 0) + 15) & ~15); off = (off + 127) & ~127; }
+    }
+    st.R = R;
+    for (int j = 0; j < len; j++) {
+        const b200_tensor & w = nodes[j].src0;
+        if (w.ne[1] <= 0 || w.ne[1] > 0x7fffffff) return false;
+        WPtrs wp; if (wptrs_of(&w, &wp)) return false;
+        for (int f = 0; f < wf.n; f++) {
+            if (!st.flead[f] && ((uintptr_t) wp.p[f] & 15)) return false;
+            st.op[j].f[f] = wp.p[f];
+        }
+        st.op[j].M = (int) w.ne[1];
+        st.op[j].dst = (float *) nodes[j].dst.data;
+    }
+    if (fa) { st.op[0].add_src = fa->src; st.op[0].add_dst = fa->dst; }
+    return true;
+}
+static bool ds_compile(const b200_node * nodes, int n, std::vector<DsStage> & out) {
+    out.clear();
+    std::vector<Span> reads_since, writes_since;                   // of the stages since the last grid-wide wait
+    for (int i = 0; i < n; ) {
+        const b200_node & nd = nodes[i];
+        DsStage st{};
+        std::vector<Span> rd, wr;
+        int used = 1;
+        if (nd.dst.op == B200_OP_NONE) { i++; continue; }
+        if (nd.dst.op == B200_OP_MUL_MAT) {
+            if (!is_vec_mulmat(nd) || mulmat_check(&nd.src0, &nd.src1, &nd.dst)) return false;
+            if (!is_vec_f32(nd.dst, nd.src0.ne[1]) || nd.src1.nb[0] != 4) return false;
+            FusedAdd fa; bool fused = false;
+            int gl = group_len(nodes, i, n);
+            if (gl == 1 && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) fused = true;
+            for (int j = 1; j < gl; j++) if (mulmat_check(&nodes[i + j].src0, &nodes[i + j].src1, &nodes[i + j].dst)) return false;
+            if (!ds_fill_gemv(st, nodes + i, gl, fused ? &fa : nullptr)) return false;
+            used = fused ? 2 : gl;
+            rd.push_back({(const char *) st.x, (int64_t) st.K * 4});
+            for (int j = 0; j < gl; j++) wr.push_back({(const char *) st.op[j].dst, (int64_t) st.op[j].M * 4});
+            if (fused) { rd.push_back({(const char *) fa.src, (int64_t) st.op[0].M * 4}); wr.push_back({(const char *) fa.dst, (int64_t) st.op[0].M * 4}); }
+        } else if (nd.dst.op == B200_OP_ADD) {
+            const int64_t ne = nd.dst.ne[0];
+            if (!is_vec_f32(nd.dst, ne) || !is_vec_f32(nd.src0, ne) || !is_vec_f32(nd.src1, ne) || ne % 4 || ne > 0x7fffffff) return false;
+            if (nd.src0.type != T_F32 || (((uintptr_t) nd.src0.data | (uintptr_t) nd.src1.data | (uintptr_t) nd.dst.data) & 15)) return false;
+            st.kind = DS_ADD; st.x = (const float *) nd.src0.data;
+            st.op[0].add_src = (const float *) nd.src1.data; st.op[0].dst = (float *) nd.dst.data; st.op[0].M = (int) ne;
+            rd.push_back({(const char *) nd.src0.data, ne * 4}); rd.push_back({(const char *) nd.src1.data, ne * 4});
+            wr.push_back({(const char *) nd.dst.data, ne * 4});
+        } else return false;
+        // RAW, WAR and WAW against every stage that may still be running somewhere on the grid
+        const bool hazard = spans_clash(rd, writes_since) || spans_clash(wr, reads_since) || spans_clash(wr, writes_since);
+        st.wait_prev = !out.empty() && hazard;
+        if (st.wait_prev) { reads_since.clear(); writes_since.clear(); }
+        reads_since.insert(reads_since.end(), rd.begin(), rd.end());
+        writes_since.insert(writes_since.end(), wr.begin(), wr.end());
+        out.push_back(st);
+        i += used;
+    }
+    return !out.empty();
+}
+
 // ---- host-pointer tensors: stage in, run, stage out, synchronise (FastRPC semantics: dsptensor.data is host memory)
 static size_t tensor_span(const b200_tensor * t) {
     if (t->data_len > 0) return (size_t) t->data_len;
@@ -546,6 +657,50 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
 
     const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *)));
+    // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
+    static const bool stream_on = !(getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) == 0);
+    if (stream_on && use_cuda_graph != 2 && c->ds_grid != 0) {
+        if (c->ds_grid < 0) c->ds_grid = ds_grid(c->dev);
+        auto ps = c->programs.find(key);
+        if (ps == c->programs.end() && c->ds_grid > 0) {
+            StreamProgram sp;
+            std::vector<DsStage> stages;
+            if (ds_compile(nodes, n, stages)) {
+                sp.nstages = (int) stages.size();
+                for (const DsStage & g : stages) if (g.kind == DS_GEMV) sp.type_mask |= ds_type_bit(g.type) | (g.steps > 512 ? 16 : 0);
+                CU(cudaMalloc((void **) &sp.dev, stages.size() * sizeof(DsStage)));
+                CU(cudaMalloc((void **) &sp.counters, stages.size() * sizeof(uint32_t)));
+                CU(cudaMemcpyAsync(sp.dev, stages.data(), stages.size() * sizeof(DsStage), cudaMemcpyHostToDevice, c->st));
+                CU(cudaMemsetAsync(sp.counters, 0, stages.size() * sizeof(uint32_t), c->st));
+                CU(cudaStreamSynchronize(c->st));            // `stages` is pageable host memory
+            }
+            if (c->programs.size() > 64) { CU(cudaStreamSynchronize(c->st)); for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); } c->programs.clear(); }
+            ps = c->programs.emplace(key, sp).first;
+        }
+        if (ps != c->programs.end() && ps->second.dev) {
+            StreamProgram & sp = ps->second;
+            sp.epoch++;
+            // development aid: B200_STREAM_TRACE=<file> dumps the per-(CTA, stage) clocks of every launch (synchronous!)
+            static const char * trace_path = getenv("B200_STREAM_TRACE");
+            long long * trace = nullptr;
+            const size_t trace_n = (size_t) c->ds_grid * sp.nstages * 4;
+            if (trace_path) { CU(cudaMalloc((void **) &trace, trace_n * sizeof(long long))); CU(cudaMemsetAsync(trace, 0, trace_n * sizeof(long long), c->st)); }
+            CU(launch_decode_stream(sp.dev, sp.nstages, sp.counters, sp.epoch, c->ds_grid, sp.type_mask, trace, c->st));
+            if (trace_path) {
+                std::vector<long long> hbuf(trace_n);
+                CU(cudaMemcpyAsync(hbuf.data(), trace, trace_n * sizeof(long long), cudaMemcpyDeviceToHost, c->st));
+                CU(cudaStreamSynchronize(c->st));
+                cudaFree(trace);
+                if (FILE * fp = fopen(trace_path, "wb")) {
+                    int hdr[2] = { c->ds_grid, sp.nstages };
+                    fwrite(hdr, sizeof(int), 2, fp); fwrite(hbuf.data(), sizeof(long long), trace_n, fp); fclose(fp);
+                }
+            }
+            c->launches++;
+            c->q_ptr = nullptr;
+            return 0;
+        }
+    }
     auto it = c->graphs.find(key);
     if (it == c->graphs.end()) {
         const int64_t before = c->launches;

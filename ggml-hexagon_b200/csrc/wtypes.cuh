@@ -72,6 +72,10 @@ template <> struct WT<T_Q4_0> {
     static __device__ __forceinline__ Frag load(const WPtrs & w, int64_t blk) {
         Frag f; f.q = ldg_stream(w.p[0] + blk * 16); f.d = ldg_stream_h(w.p[1] + blk * 2); return f;
     }
+    // same fragment from a shared-memory copy of the SoA fields (decode_stream.cu); plain loads -> LDS
+    static __device__ __forceinline__ Frag loads(const WPtrs & w, int blk) {
+        Frag f; f.q = *(const uint4 *) (w.p[0] + blk * 16); f.d = __half2float(*(const __half *) (w.p[1] + blk * 2)); return f;
+    }
     static __device__ __forceinline__ void idots(const Frag & f, const ActCol & a, int s, int * out) {
         const uint4 a0 = ldg_cached(a.p0 + s), a1 = ldg_cached(a.p1 + s);
         const ADesc  ad = load_adesc(a.ds + s);
@@ -93,6 +97,10 @@ template <> struct WT<T_Q8_0> {
     static __device__ __forceinline__ Frag load(const WPtrs & w, int64_t blk) {
         Frag f; f.q0 = ldg_stream(w.p[0] + blk * 32); f.q1 = ldg_stream(w.p[0] + blk * 32 + 16);
         f.d = ldg_stream_h(w.p[1] + blk * 2); return f;
+    }
+    static __device__ __forceinline__ Frag loads(const WPtrs & w, int blk) {
+        Frag f; f.q0 = *(const uint4 *) (w.p[0] + blk * 32); f.q1 = *(const uint4 *) (w.p[0] + blk * 32 + 16);
+        f.d = __half2float(*(const __half *) (w.p[1] + blk * 2)); return f;
     }
     static __device__ __forceinline__ void idots(const Frag & f, const ActCol & a, int s, int * out) {
         out[0] = dot16_ss(f.q0, ldg_cached(a.p0 + s)) + dot16_ss(f.q1, ldg_cached(a.p1 + s));
@@ -130,6 +138,12 @@ template <> struct WT<T_Q4_K> {
         f.hdr = __ldg((const uint4 *) (w.p[1] + (step >> 2) * 16));     // shared by the 4 lanes of a super-block
         return f;
     }
+    static __device__ __forceinline__ Frag loads(const WPtrs & w, int step) {
+        Frag f;
+        f.q0 = *(const uint4 *) (w.p[0] + step * 32); f.q1 = *(const uint4 *) (w.p[0] + step * 32 + 16);
+        f.hdr = *(const uint4 *) (w.p[1] + (step >> 2) * 16);
+        return f;
+    }
     static __device__ __forceinline__ void idots(const Frag & f, const ActCol & a, int s, int * out) {
         const int b0 = 2 * s, b1 = 2 * s + 1;
         out[0] = dot16_us(lo_nib(f.q0), ldg_cached(a.p0 + b0)) + dot16_us(lo_nib(f.q1), ldg_cached(a.p1 + b0));
@@ -164,6 +178,16 @@ template <> struct WT<T_Q6_K> {
         f.hq = ldg_stream(w.p[1] + sb * 64 + 32 * h + 16 * j);
         f.sc = ldg_stream8(w.p[2] + sb * 16 + 8 * h);
         f.d  = ldg_stream_h(w.p[3] + sb * 2);
+        return f;
+    }
+    static __device__ __forceinline__ Frag loads(const WPtrs & w, int step) {
+        const int sb = step >> 2; const int h = (step & 3) >> 1, j = step & 1;
+        Frag f;
+        f.l0 = *(const uint4 *) (w.p[0] + sb * 128 + 64 * h + 16 * j);
+        f.l1 = *(const uint4 *) (w.p[0] + sb * 128 + 64 * h + 32 + 16 * j);
+        f.hq = *(const uint4 *) (w.p[1] + sb * 64 + 32 * h + 16 * j);
+        f.sc = *(const uint2 *) (w.p[2] + sb * 16 + 8 * h);
+        f.d  = __half2float(*(const __half *) (w.p[3] + sb * 2));
         return f;
     }
     static __device__ __forceinline__ void idots(const Frag & f, const ActCol & a, int s, int * out) {
@@ -300,5 +324,26 @@ template <> struct WR<T_Q6_K> {
 template <int TYPE> __device__ __forceinline__ float wr_dot(const typename WT<TYPE>::Frag & f, const typename WR<TYPE>::Act & a, int s) {
     if constexpr (TYPE == T_Q4_0 || TYPE == T_Q8_0) return WR<TYPE>::dot(f, a); else return WR<TYPE>::dot(f, a, s);
 }
+
+// ------------------------------------------------------------------------------------------------ lane reductions
+// v[0..R) per lane -> total over the 32 lanes of v[row], returned in every lane with row == (lane >> (5-log2 R)) & (R-1)
+template <int R>
+__device__ __forceinline__ float reduce_rows(float (&v)[R], const int lane) {
+    int m = 16;
+    #pragma unroll
+    for (int n = R; n > 1; n >>= 1, m >>= 1) {
+        const bool up = lane & m;
+        #pragma unroll
+        for (int i = 0; i < n / 2; i++) {
+            const float keep = up ? v[i + n / 2] : v[i];
+            const float send = up ? v[i] : v[i + n / 2];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, m);
+        }
+    }
+    for (; m > 0; m >>= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], m);
+    return v[0];
+}
+template <int R> struct Log2 { static constexpr int v = 1 + Log2<R / 2>::v; };
+template <> struct Log2<1> { static constexpr int v = 0; };
 
 }  // namespace b200

@@ -123,7 +123,7 @@ def add_f32(a, b):
     return out.reshape(a.shape)
 
 
-def random_blocks(t, rows, k, rng):
+def random_blocks(t, rows, k, rng, scale=1.0):
     """Random-init quantised weights made directly in the wire format (valid for every type):
     random quant bytes, fp16 scales log-uniform-ish in a range that keeps |w| ~ O(0.1)."""
     bl, by = BLOCK[t]
@@ -131,7 +131,7 @@ def random_blocks(t, rows, k, rng):
     raw = rng.integers(0, 256, size=(rows, nb, by), dtype=np.uint8)
 
     def put_f16(off, lo, hi, signed=True):
-        v = rng.uniform(lo, hi, size=(rows, nb)).astype(np.float32)
+        v = (rng.uniform(lo, hi, size=(rows, nb)) * scale).astype(np.float32)
         if signed:
             v *= rng.choice(np.array([-1.0, 1.0], dtype=np.float32), size=(rows, nb))
         h = v.astype(np.float16).view(np.uint16)

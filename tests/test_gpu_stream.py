@@ -1,0 +1,142 @@
+"""GPU parity tests of the decode stream kernel (decode_stream.cu): a whole node list as one persistent launch,
+called through b200_graph_compute(use_cuda_graph=1) and checked against the oracle (q8_1 algebra, mode 1) and
+against ggml-cpu semantics (mode 0, NMSE <= 5e-4, tests/test-backend-ops.cpp:1982-1984)."""
+import numpy as np
+import pytest
+
+import pyoracle as O
+import b200ops as B
+
+pytestmark = pytest.mark.gpu
+WTYPES = [(O.Q4_0, "q4_0"), (O.Q8_0, "q8_0"), (O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")]
+
+
+def nmse(a, b):
+    return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
+
+
+@pytest.fixture(scope="module")
+def sess():
+    s = B.Session(0)
+    yield s
+    s.close()
+
+
+def mm_node(w, xbuf, K, dbuf, M):
+    n = B.Node()
+    n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xbuf.ptr, [K, 1]), B.f32_tensor(dbuf.ptr, [M, 1], op=B.OP_MUL_MAT)
+    return n
+
+
+def add_node(a, b, d, n_el):
+    n = B.Node()
+    n.src0, n.src1, n.dst = B.f32_tensor(a.ptr, [n_el]), B.f32_tensor(b.ptr, [n_el]), B.f32_tensor(d.ptr, [n_el], op=B.OP_ADD)
+    return n
+
+
+def weights_for(sess, t, M, K, rng, scale=1.0):
+    raw = O.random_blocks(t, M, K, rng, scale)
+    return sess.weights(t, raw, K), raw
+
+
+@pytest.mark.parametrize("t,name", WTYPES)
+@pytest.mark.parametrize("M,K", [(16, 256), (1000, 1024), (4099, 4096), (300, 11008), (148, 2048), (1, 512)])
+def test_stream_single_mulmat(sess, t, name, M, K):
+    rng = np.random.default_rng(M * 7 + K + t)
+    w, raw = weights_for(sess, t, M, K, rng)
+    x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    xb, db = sess.to_device(x), sess.malloc(4 * M)
+    nodes = [mm_node(w, xb, K, db, M)]
+    for rep in range(2):                              # second launch: epoch 2 on the same counters
+        sess.h2d(db, np.full(M, 7.0, np.float32))
+        sess.graph_compute(nodes, use_cuda_graph=1)
+        got = sess.to_host(db, (M,), np.float32)
+        assert nmse(got, O.mul_mat(t, raw, x, 1).reshape(-1)) <= 1e-9, (name, M, K, rep)
+        assert nmse(got, O.mul_mat(t, raw, x, 0).reshape(-1)) <= 5e-4
+    sess.graph_compute(nodes, use_cuda_graph=0)
+    assert nmse(got, sess.to_host(db, (M,), np.float32)) <= 1e-10
+    for b in (xb, db):
+        b.free()
+    w.free()
+
+
+def test_stream_two_slices_per_warp(sess):
+    """K = 28672 (Llama-3-70B ffn down): 28 K-slices of 32 blocks > 16 consumer warps"""
+    rng = np.random.default_rng(5)
+    M, K = 96, 28672
+    w, raw = weights_for(sess, O.Q4_0, M, K, rng)
+    x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    xb, db = sess.to_device(x), sess.malloc(4 * M)
+    sess.graph_compute([mm_node(w, xb, K, db, M)], use_cuda_graph=1)
+    assert nmse(sess.to_host(db, (M,), np.float32), O.mul_mat(O.Q4_0, raw, x, 1).reshape(-1)) <= 1e-9
+
+
+@pytest.mark.parametrize("t,name", WTYPES)
+def test_stream_layer_chain(sess, t, name):
+    """two 'layers' of q/k/v (grouped) -> wo + residual (fused) -> gate/up (grouped) -> down + residual (fused),
+    then a plain ADD and an output matrix: every stage kind, grid-wide dependencies between all of them"""
+    rng = np.random.default_rng(100 + t)
+    h, kv, f = 1024, 256, 2816 if t in (O.Q4_0, O.Q8_0) else 2816 - 2816 % 256
+    V = 3001
+    mk = lambda n: sess.malloc(4 * n)
+    x_host = rng.uniform(-1, 1, (1, h)).astype(np.float32)
+    x = sess.to_device(x_host)
+    q, k, v, o, hres, g, u, dn, x2, x3, ysum, logits = mk(h), mk(kv), mk(kv), mk(h), mk(h), mk(f), mk(f), mk(h), mk(h), mk(h), mk(h), mk(V)
+    layers, nodes = [], []
+    xin, xout = x, x2
+    for _ in range(2):
+        W = {n: weights_for(sess, t, M, K, rng, 0.03) for n, M, K in
+             [("wq", h, h), ("wk", kv, h), ("wv", kv, h), ("wo", h, h), ("gate", f, h), ("up", f, h), ("down", h, f)]}
+        layers.append(W)
+        nodes += [mm_node(W["wq"][0], xin, h, q, h), mm_node(W["wk"][0], xin, h, k, kv), mm_node(W["wv"][0], xin, h, v, kv),
+                  mm_node(W["wo"][0], q, h, o, h), add_node(xin, o, hres, h),
+                  mm_node(W["gate"][0], hres, h, g, f), mm_node(W["up"][0], hres, h, u, f),
+                  mm_node(W["down"][0], g, f, dn, h), add_node(hres, dn, xout, h)]
+        xin, xout = xout, x3
+    nodes.append(add_node(xin, x, ysum, h))           # not preceded by a MUL_MAT writing one of its inputs: plain ADD stage
+    wout, wout_raw = weights_for(sess, t, V, h, rng)
+    nodes.append(mm_node(wout, ysum, h, logits, V))
+
+    mm = lambda raw, vec: O.mul_mat(t, raw, vec.reshape(1, -1), 1).reshape(-1)      # mode 1 = the same q8_1 algebra
+    rd = lambda buf, n: sess.to_host(buf, (n,), np.float32)
+    for rep in range(3):
+        sess.h2d(logits, np.zeros(V, np.float32))
+        sess.graph_compute(nodes, use_cuda_graph=1)
+        got = rd(logits, V)
+        assert np.isfinite(got).all()
+        # every stage of the LAST layer against the oracle fed with the GPU's own stage inputs (a chain amplifies the
+        # rounding flips a different float summation order causes in the next quantisation, so end-to-end is loose)
+        W = layers[-1]
+        x_in = rd(x2, h)                              # output of layer 1 = input of layer 2
+        qv, kv_, vv, ov, hv = rd(q, h), rd(k, kv), rd(v, kv), rd(o, h), rd(hres, h)
+        gv, uv, dv, xo, ys = rd(g, f), rd(u, f), rd(dn, h), rd(x3, h), rd(ysum, h)
+        tight = 1e-9
+        assert nmse(qv, mm(W["wq"][1], x_in)) <= tight and nmse(kv_, mm(W["wk"][1], x_in)) <= tight and nmse(vv, mm(W["wv"][1], x_in)) <= tight
+        assert nmse(ov, mm(W["wo"][1], qv)) <= tight
+        assert np.array_equal(hv, x_in + ov)          # fused residual: plain IEEE add of the stored MUL_MAT result
+        assert nmse(gv, mm(W["gate"][1], hv)) <= tight and nmse(uv, mm(W["up"][1], hv)) <= tight
+        assert nmse(dv, mm(W["down"][1], gv)) <= tight
+        assert np.array_equal(xo, hv + dv)
+        assert np.array_equal(ys, xo + x_host.reshape(-1))
+        assert nmse(got, mm(wout_raw, ys)) <= tight
+    # end to end against the oracle chain, and against the per-node path
+    xv = x_host.reshape(-1)
+    for W in layers:
+        hv_ = xv + mm(W["wo"][1], mm(W["wq"][1], xv))
+        xv = hv_ + mm(W["down"][1], mm(W["gate"][1], hv_))
+    assert nmse(got, mm(wout_raw, xv + x_host.reshape(-1))) <= 5e-3
+    sess.graph_compute(nodes, use_cuda_graph=0)
+    assert nmse(got, rd(logits, V)) <= 5e-3
+
+
+def test_stream_falls_back_for_matrices(sess):
+    """a node list with a 4-column MUL_MAT is not a decode list: the call must still succeed (CUDA-graph path)"""
+    rng = np.random.default_rng(9)
+    M, K, N = 64, 512, 4
+    w, raw = weights_for(sess, O.Q4_0, M, K, rng)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    xb, db = sess.to_device(x), sess.malloc(4 * M * N)
+    n = B.Node()
+    n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(db.ptr, [M, N], op=B.OP_MUL_MAT)
+    sess.graph_compute([n], use_cuda_graph=1)
+    assert nmse(sess.to_host(db, (N, M), np.float32), O.mul_mat(O.Q4_0, raw, x, 1)) <= 1e-9
