@@ -105,7 +105,7 @@ gemv4_kernel(const GemvArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------ launch
-struct Tune { int rows = 8; bool pdl = true; };
+struct Tune { int rows = 0; bool pdl = true; };    // rows 0 = per-shape heuristic
 static const Tune & tune() {
     static Tune t = [] {
         Tune x;
@@ -144,7 +144,9 @@ template <int TYPE, int NCOLS>
 static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
     constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
     if constexpr (NCOLS == 1) {
-        const int r = tune().rows;
+        // rows per CTA, from the B200 sweep (profiles/r01_b_gemv_rows_sweep.txt): tall matrices want 8, long rows 2, else 4
+        int64_t mtot = 0; for (int i = 0; i < a.nmat; i++) mtot += a.mat[i].M;
+        const int r = tune().rows > 0 ? tune().rows : (mtot >= 8192 ? 8 : (a.K >= 8192 ? 2 : 4));
         if constexpr (TYPE == T_Q4_0) {
             if (r == 2) return launch_cfg<TYPE, 1, 2>(a, st, pdl);
             if (r == 4) return launch_cfg<TYPE, 1, 4>(a, st, pdl);

@@ -472,7 +472,7 @@ static bool ds_fill_gemv(DsStage & st, const b200_node * nodes, int len, const F
     for (int f = 0; f < wf.n; f++) {
         st.rowbytes[f] = (int) (bpr * wf.size[f]);
         st.flead[f] = (st.rowbytes[f] % 16) != 0;
-        if (st.flead[f] && wf.size[f] != 2) return false;
+        if (st.flead[f]) return false;      // rows of a 2-byte scale array that are not 16-B multiples: per-node kernels
     }
     int R = 8;
     for (; R >= 1; R >>= 1) {
@@ -658,8 +658,9 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
 
     const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *)));
     // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
-    static const bool stream_on = !(getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) == 0);
-    if (stream_on && use_cuda_graph != 2 && c->ds_grid != 0) {
+    // opt-in while it is slower than the CUDA-graph replay of the per-node kernels (DESIGN.md has the trace numbers)
+    static const bool stream_on = getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) != 0;
+    if ((stream_on || use_cuda_graph == 3) && use_cuda_graph != 2 && c->ds_grid != 0) {
         if (c->ds_grid < 0) c->ds_grid = ds_grid(c->dev);
         auto ps = c->programs.find(key);
         if (ps == c->programs.end() && c->ds_grid > 0) {
@@ -701,6 +702,7 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
             return 0;
         }
     }
+    if (use_cuda_graph == 3) return fail(B200_ENOTSUP, "graph_compute: this node list does not compile to the decode stream kernel");
     auto it = c->graphs.find(key);
     if (it == c->graphs.end()) {
         const int64_t before = c->launches;

@@ -105,11 +105,12 @@ B200_API int b200_add(b200_handle h, const b200_tensor * src0, const b200_tensor
 B200_API int b200_mulmat(b200_handle h, const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst);
 /* a whole node list in one call (graph_compute, ggml-hexagon.cpp:5555-5574); asynchronous.
  * use_cuda_graph = 0: one launch per node (fused where adjacent nodes allow).
- * use_cuda_graph = 1: replayable fast path, chosen per distinct node list and cached: if every node is a vector
- *                     MUL_MAT (one f32 column, REPACKED weights) or a contiguous vector ADD, the list is compiled into
- *                     ONE persistent cooperative launch that streams all weights through shared memory
- *                     (decode_stream.cu); otherwise the per-node launches are captured as a CUDA graph and replayed.
- * use_cuda_graph = 2: CUDA-graph replay only. */
+ * use_cuda_graph = 1: replayable fast path, cached per distinct node list: the per-node launches are captured once as a
+ *                     CUDA graph and replayed.  With B200_STREAM=1 in the environment a list made only of vector MUL_MATs
+ *                     (one f32 column, REPACKED weights) and contiguous vector ADDs is instead compiled into ONE persistent
+ *                     cooperative launch that streams all weights through shared memory (decode_stream.cu).
+ * use_cuda_graph = 2: CUDA-graph replay only.
+ * use_cuda_graph = 3: decode stream kernel only; B200_ENOTSUP if the list does not compile to it. */
 B200_API int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph);
 B200_API int b200_synchronize(b200_handle h);
 

@@ -196,7 +196,7 @@ def test_add_special_values(sess):
 def test_graph_compute_matches_direct(sess):
     import ctypes as C
     rng = np.random.default_rng(21)
-    K, M = 1024, 1024
+    K, M = 2048, 2048
     ws = [sess.weights(t, O.random_blocks(t, M, K, rng) if t in (O.Q4_K, O.Q6_K) else
                        O.quantize(t, rng.uniform(-1, 1, (M, K)).astype(np.float32)), K) for t, _ in WTYPES]
     x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
@@ -220,7 +220,7 @@ def test_graph_compute_matches_direct(sess):
         assert np.array_equal(sess.to_host(bufs[4], (M,), np.float32), direct)
     for _ in range(3):                              # decode stream kernel: same integers, other float summation order
         sess.h2d(bufs[4], np.zeros(M, np.float32))
-        sess.graph_compute(nodes, use_cuda_graph=1)
+        sess.graph_compute(nodes, use_cuda_graph=3)
         assert nmse(sess.to_host(bufs[4], (M,), np.float32), direct) <= 1e-10
     # oracle chain (mode 1) for the value itself
     y = x

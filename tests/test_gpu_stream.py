@@ -1,5 +1,5 @@
 """GPU parity tests of the decode stream kernel (decode_stream.cu): a whole node list as one persistent launch,
-called through b200_graph_compute(use_cuda_graph=1) and checked against the oracle (q8_1 algebra, mode 1) and
+called through b200_graph_compute(use_cuda_graph=3) and checked against the oracle (q8_1 algebra, mode 1) and
 against ggml-cpu semantics (mode 0, NMSE <= 5e-4, tests/test-backend-ops.cpp:1982-1984)."""
 import numpy as np
 import pytest
@@ -47,9 +47,14 @@ def test_stream_single_mulmat(sess, t, name, M, K):
     x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
     xb, db = sess.to_device(x), sess.malloc(4 * M)
     nodes = [mm_node(w, xb, K, db, M)]
+    if t == O.Q6_K and K % 2048:
+        # rows of the fp16 super-block scale array are not 16-byte multiples: declined (the per-node kernels take it)
+        with pytest.raises(B.B200Error):
+            sess.graph_compute(nodes, use_cuda_graph=3)
+        return
     for rep in range(2):                              # second launch: epoch 2 on the same counters
         sess.h2d(db, np.full(M, 7.0, np.float32))
-        sess.graph_compute(nodes, use_cuda_graph=1)
+        sess.graph_compute(nodes, use_cuda_graph=3)
         got = sess.to_host(db, (M,), np.float32)
         assert nmse(got, O.mul_mat(t, raw, x, 1).reshape(-1)) <= 1e-9, (name, M, K, rep)
         assert nmse(got, O.mul_mat(t, raw, x, 0).reshape(-1)) <= 5e-4
@@ -67,7 +72,7 @@ def test_stream_two_slices_per_warp(sess):
     w, raw = weights_for(sess, O.Q4_0, M, K, rng)
     x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
     xb, db = sess.to_device(x), sess.malloc(4 * M)
-    sess.graph_compute([mm_node(w, xb, K, db, M)], use_cuda_graph=1)
+    sess.graph_compute([mm_node(w, xb, K, db, M)], use_cuda_graph=3)
     assert nmse(sess.to_host(db, (M,), np.float32), O.mul_mat(O.Q4_0, raw, x, 1).reshape(-1)) <= 1e-9
 
 
@@ -76,7 +81,7 @@ def test_stream_layer_chain(sess, t, name):
     """two 'layers' of q/k/v (grouped) -> wo + residual (fused) -> gate/up (grouped) -> down + residual (fused),
     then a plain ADD and an output matrix: every stage kind, grid-wide dependencies between all of them"""
     rng = np.random.default_rng(100 + t)
-    h, kv, f = 1024, 256, 2816 if t in (O.Q4_0, O.Q8_0) else 2816 - 2816 % 256
+    h, kv, f = 2048, 256, 2816 if t in (O.Q4_0, O.Q8_0) else 4096      # q6_K: K % 2048 == 0 for the stream kernel
     V = 3001
     mk = lambda n: sess.malloc(4 * n)
     x_host = rng.uniform(-1, 1, (1, h)).astype(np.float32)
@@ -101,7 +106,7 @@ def test_stream_layer_chain(sess, t, name):
     rd = lambda buf, n: sess.to_host(buf, (n,), np.float32)
     for rep in range(3):
         sess.h2d(logits, np.zeros(V, np.float32))
-        sess.graph_compute(nodes, use_cuda_graph=1)
+        sess.graph_compute(nodes, use_cuda_graph=3)
         got = rd(logits, V)
         assert np.isfinite(got).all()
         # every stage of the LAST layer against the oracle fed with the GPU's own stage inputs (a chain amplifies the
