@@ -134,6 +134,13 @@ int  ds_type_bit(int type);
 cudaError_t launch_decode_stream(const DsStage * prog_dev, int nstages, uint32_t * counters, uint32_t epoch, int grid, int type_mask,
                                  long long * trace /* development: 4 clocks per (CTA, stage), or nullptr */, cudaStream_t st);
 
+// ---- prefill GEMM on the tensor cores (gemm_i8.cu): int8 tcgen05.mma per 32-element block, fp32 scale-accumulate
+cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, cudaStream_t st);
+cudaError_t launch_unpack_q4_0_i8(const void * qs, long long nblocks, int8_t * out, cudaStream_t st);
+int gemm_i8_ldb(int N);
+cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA, const int8_t * B, const float * dB, long long ldb,
+                           float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st);
+
 struct AddArgs {
     const char * a; const char * b; char * d;
     int64_t ne[4];      // dst / src0 shape

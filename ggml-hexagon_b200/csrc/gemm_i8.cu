@@ -1,0 +1,321 @@
+// gemm_i8.cu — prefill MUL_MAT (many activation columns) on the 5th-generation tensor cores: int8 x int8 -> int32
+// tcgen05.mma with TMEM accumulators, operands staged by TMA, exact per-32-block integer sums scaled in fp32.
+//
+// Takes the seat of the reference's blocked mul_mat loop for src1 with many columns
+// (ggml_compute_forward_mul_mat_one_chunk, ggml-dsp.c:1091-1189 / ggml-cpu.c:6655-6743; vec_dot kernels
+// ggml-cpu-quants.c:4004-4012 (q8_0), :2591-2604 (q4_0)).
+//
+// Math (identical to the CPU reference block by block):
+//     dst[m, n] = sum_b  (d_w[m, b] * d_a[n, b]) * sumi_b[m, n],      sumi_b = sum_{k in block b} w_q[m, k] * a_q[n, k]   (int32, exact)
+// Block scales change every 32 k, so an int32 accumulator cannot run over the whole K: ONE tcgen05.mma (M128 x N128 x K32)
+// produces the 128 x 128 exact sums of one block into one of four TMEM accumulator buffers, and the epilogue warps
+// fold it into fp32 registers while the tensor core already works on the next blocks.
+//
+// CTA (1 per SM, persistent over 128 x 128 output tiles), 10 warps:
+//   warp 0      TMA producer: A = weights int8 [M][K] (the SoA quant array of q8_0 as it lies in HBM, or the unpacked
+//               scratch of q4_0), B = activations int8 [N][K]; 128 x 128-byte boxes, 128-B swizzle, 6-stage ring
+//   warp 1      TMEM allocation + MMA issue (one elected lane): 4 MMAs per stage, one per block, each into its own buffer
+//   warps 2..9  epilogue: tcgen05.ld (32 lanes x 64 columns per warp), acc += float(sumi) * (d_w * d_a), final store
+#include "b200_internal.cuh"
+
+#include <cuda.h>
+#include <stdio.h>
+
+namespace b200 {
+
+constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 128;        // tile; BK in int8 elements = bytes = one 128-B swizzle row
+constexpr int GM_STAGES = 6;
+constexpr int GM_NBUF = 4;                                  // TMEM accumulator buffers of GM_BN columns
+constexpr int GM_THREADS = 320;
+constexpr int GM_STAGE_A = GM_BM * GM_BK, GM_STAGE_B = GM_BN * GM_BK;
+constexpr int GM_OFF_A = 0, GM_OFF_B = GM_STAGES * GM_STAGE_A, GM_OFF_BAR = GM_OFF_B + GM_STAGES * GM_STAGE_B;
+constexpr int GM_SMEM = GM_OFF_BAR + 256 + 1024;            // + barriers + slack to align the base to 1024 B
+constexpr long long GM_TIMEOUT_CYCLES = 8000000000ll;
+
+struct GemmI8Args {
+    const __half * dA; long long dA_stride;     // weight block scales [M][dA_stride] (fp16)
+    const float *  dB; long long dB_stride;     // activation block scales [K/32][dB_stride] (f32), dB_stride >= ntiles * 128
+    float * out; long long out_cs;              // dst[n * out_cs + m]
+    int M, N, K;
+    int mtiles, ntiles;
+};
+
+// ------------------------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t gm_smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void gm_mbar_init(uint32_t bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count)); }
+__device__ __forceinline__ void gm_mbar_arrive(uint32_t bar) { asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" :: "r"(bar) : "memory"); }
+__device__ __forceinline__ void gm_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool gm_mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void gm_mbar_wait(uint32_t bar, uint32_t parity) {
+    if (gm_mbar_try(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!gm_mbar_try(bar, parity)) { if (clock64() - t0 > GM_TIMEOUT_CYCLES) __trap(); }
+}
+__device__ __forceinline__ void gm_tma_2d(uint32_t dst, const CUtensorMap * map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO), LBO unused, descriptor version 1
+__device__ __forceinline__ uint64_t gm_smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t) ((saddr & 0x3FFFF) >> 4);             // start address, bits [0,14)
+    d |= (uint64_t) (1024 >> 4) << 32;                    // stride byte offset, bits [32,46)
+    d |= (uint64_t) 1 << 46;                              // version = 1 (sm_100)
+    d |= (uint64_t) 2 << 61;                              // SWIZZLE_128B
+    return d;
+}
+__device__ __forceinline__ void gm_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void gm_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void gm_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void gm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, int (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void gm_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------ kernel
+__global__ void __launch_bounds__(GM_THREADS, 1)
+gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmI8Args p) {
+    extern __shared__ uint8_t gm_smem_raw[];
+    const uint32_t base = (gm_smem_u32(gm_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
+    uint8_t * smem = gm_smem_raw + (base - gm_smem_u32(gm_smem_raw));
+    const uint32_t sA = base + GM_OFF_A, sB = base + GM_OFF_B, bars = base + GM_OFF_BAR;
+    const uint32_t full0 = bars, empty0 = bars + GM_STAGES * 8, tfull0 = bars + 2 * GM_STAGES * 8, tempty0 = tfull0 + GM_NBUF * 8;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + GM_OFF_BAR + 2 * GM_STAGES * 8 + 2 * GM_NBUF * 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nks = (p.K + GM_BK - 1) / GM_BK, KB = p.K / 32, ntiles_total = p.mtiles * p.ntiles;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
+        for (int i = 0; i < GM_NBUF; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {            // all 512 TMEM columns: four 128-column int32 accumulator buffers
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(gm_smem_u32((const void *) tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    gm_fence_before();
+    __syncthreads();
+    gm_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
+                const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+                for (int ks = 0; ks < nks; ks++, it++) {
+                    const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
+                    gm_mbar_wait(empty0 + s * 8, ph ^ 1);
+                    gm_mbar_expect_tx(full0 + s * 8, GM_STAGE_A + GM_STAGE_B);
+                    gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * GM_BK, mt * GM_BM);
+                    gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * GM_BK, nt * GM_BN);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one lane, one tcgen05.mma per 32-element block, each into its own accumulator buffer
+        if (lane == 0) {
+            // instruction descriptor: D = s32, A = B = signed int8, both K-major, N = 128, M = 128
+            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (GM_BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
+            uint32_t it = 0, bc = 0;
+            for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
+                for (int ks = 0; ks < nks; ks++, it++) {
+                    const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
+                    gm_mbar_wait(full0 + s * 8, ph);
+                    gm_fence_after();
+                    const int nb = min(4, KB - ks * 4);
+                    for (int j = 0; j < nb; j++, bc++) {
+                        const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
+                        gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
+                        gm_fence_after();
+                        const uint64_t ad = gm_smem_desc(sA + s * GM_STAGE_A + j * 32), bd = gm_smem_desc(sB + s * GM_STAGE_B + j * 32);
+                        gm_mma_i8(tmem + buf * GM_BN, ad, bd, idesc, 0u);
+                        gm_commit(tfull0 + buf * 8);          // arrives when this block's sums are in TMEM
+                    }
+                    gm_commit(empty0 + s * 8);                // arrives when the stage's MMAs have read shared memory
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), column half (w - 2) / 4
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int m_local = q * 32 + lane;
+        uint32_t bc = 0;
+        for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
+            const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+            const int m = mt * GM_BM + m_local;
+            const __half * dw_row = p.dA + (long long) min(m, p.M - 1) * p.dA_stride;
+            const float * db_col = p.dB + nt * GM_BN + half * 64;
+            float acc[64];
+            #pragma unroll
+            for (int i = 0; i < 64; i++) acc[i] = 0.f;
+            for (int b = 0; b < KB; b++, bc++) {
+                const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
+                const float dw = __half2float(dw_row[b]);
+                const float4 * db4 = (const float4 *) (db_col + (long long) b * p.dB_stride);
+                gm_mbar_wait(tfull0 + buf * 8, bph);
+                gm_fence_after();
+                const uint32_t taddr = tmem + ((uint32_t) (q * 32) << 16) + buf * GM_BN + half * 64;
+                int v0[32], v1[32];
+                gm_tmem_ld32(taddr, v0);
+                gm_tmem_ld32(taddr + 32, v1);
+                gm_tmem_ld_wait();
+                gm_fence_before();
+                __syncwarp();
+                if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);     // buffer free for the MMA issuer
+                #pragma unroll
+                for (int i4 = 0; i4 < 8; i4++) {
+                    const float4 d = __ldg(db4 + i4);
+                    acc[i4 * 4 + 0] = fmaf((float) v0[i4 * 4 + 0], dw * d.x, acc[i4 * 4 + 0]);
+                    acc[i4 * 4 + 1] = fmaf((float) v0[i4 * 4 + 1], dw * d.y, acc[i4 * 4 + 1]);
+                    acc[i4 * 4 + 2] = fmaf((float) v0[i4 * 4 + 2], dw * d.z, acc[i4 * 4 + 2]);
+                    acc[i4 * 4 + 3] = fmaf((float) v0[i4 * 4 + 3], dw * d.w, acc[i4 * 4 + 3]);
+                }
+                #pragma unroll
+                for (int i4 = 0; i4 < 8; i4++) {
+                    const float4 d = __ldg(db4 + 8 + i4);
+                    acc[32 + i4 * 4 + 0] = fmaf((float) v1[i4 * 4 + 0], dw * d.x, acc[32 + i4 * 4 + 0]);
+                    acc[32 + i4 * 4 + 1] = fmaf((float) v1[i4 * 4 + 1], dw * d.y, acc[32 + i4 * 4 + 1]);
+                    acc[32 + i4 * 4 + 2] = fmaf((float) v1[i4 * 4 + 2], dw * d.z, acc[32 + i4 * 4 + 2]);
+                    acc[32 + i4 * 4 + 3] = fmaf((float) v1[i4 * 4 + 3], dw * d.w, acc[32 + i4 * 4 + 3]);
+                }
+            }
+            if (m < p.M) {
+                const int n0 = nt * GM_BN + half * 64;
+                #pragma unroll
+                for (int i = 0; i < 64; i++)
+                    if (n0 + i < p.N) p.out[(long long) (n0 + i) * p.out_cs + m] = acc[i];      // 32 lanes = 32 consecutive m: coalesced
+            }
+        }
+    }
+    gm_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ operand preparation
+// Activations for the GEMM: q8_1 quantisation (= quantize_row_q8_1_ref, ggml-quants.c:220-253) into a plain row-major
+// int8 matrix [N][K] (TMA operand B) and block-major scales dB[K/32][ldb] (f32 value of the fp16-rounded d).
+// 8 lanes per 32-element block, one float4 each.
+__global__ void __launch_bounds__(256)
+quantize_rows_i8_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N,
+                        int8_t * __restrict__ q, float * __restrict__ dB, const long long ldb) {
+    const int NB = K / 32;
+    const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    const long long blk = gid >> 3;
+    if (blk >= (long long) NB * N) return;
+    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 7);
+    const float4 v = *(const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 4) * 4);
+    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
+    const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
+    const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
+    *(uint32_t *) (q + (long long) row * K + b * 32 + sub * 4) = packed;
+    if (sub == 0) dB[(long long) b * ldb + row] = __half2float(__float2half_rn(d));
+}
+
+// q4_0 nibbles (SoA quant array, 16 B per block: low nibbles = elements 0..15, high = 16..31, ggml-common.h:167-172)
+// -> signed int8 (q - 8) row-major [M][K], the TMA operand A.  One thread per block.
+__global__ void __launch_bounds__(256)
+unpack_q4_0_i8_kernel(const uint4 * __restrict__ qs, const long long nblocks, int8_t * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nblocks; i += (long long) gridDim.x * blockDim.x) {
+        const uint4 v = qs[i];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t lo[4], hi[4];
+        #pragma unroll
+        for (int j = 0; j < 4; j++) {
+            // per-byte (nibble - 8): nibbles are 0..15, so the subtraction never borrows across bytes after the +0x80 bias trick
+            lo[j] = __vsub4(w[j] & 0x0F0F0F0Fu, 0x08080808u);
+            hi[j] = __vsub4((w[j] >> 4) & 0x0F0F0F0Fu, 0x08080808u);
+        }
+        uint4 * o = (uint4 *) (out + i * 32);
+        o[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        o[1] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    }
+}
+
+cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, cudaStream_t st) {
+    const long long threads = (long long) (K / 4) * N;
+    quantize_rows_i8_kernel<<<(unsigned) ((threads + 255) / 256), 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    return cudaGetLastError();
+}
+cudaError_t launch_unpack_q4_0_i8(const void * qs, long long nblocks, int8_t * out, cudaStream_t st) {
+    long long blocks = (nblocks + 255) / 256; if (blocks > 148 * 32) blocks = 148 * 32;
+    unpack_q4_0_i8_kernel<<<(unsigned) blocks, 256, 0, st>>>((const uint4 *) qs, nblocks, out);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ host: tensor maps + launch
+typedef CUresult (*encode_tiled_t)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_t encode_tiled() {
+    static encode_tiled_t fn = [] {
+        void * p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || qres != cudaDriverEntryPointSuccess) p = nullptr;
+        return (encode_tiled_t) p;
+    }();
+    return fn;
+}
+// int8 matrix [rows][K], K contiguous; box = 128 bytes of K x 128 rows, 128-B swizzle, out-of-range rows / k read as zero
+static bool make_map_i8(CUtensorMap * m, const void * base, long long rows, long long K) {
+    encode_tiled_t enc = encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t) K, (cuuint64_t) rows};
+    const cuuint64_t strides[1] = {(cuuint64_t) K};
+    const cuuint32_t box[2] = {(cuuint32_t) GM_BK, (cuuint32_t) GM_BM};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+int gemm_i8_ldb(int N) { return (N + GM_BN - 1) / GM_BN * GM_BN; }      // leading dimension the caller must give dB
+
+// A: int8 [M][K] (16-B aligned, K % 16 == 0), dA: fp16 [M][K/32]; B: int8 [N][K], dB: f32 [K/32][ldb]; out[n * out_cs + m]
+cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA, const int8_t * B, const float * dB, long long ldb,
+                           float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    CUtensorMap tmA, tmB;
+    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K)) return cudaErrorInvalidValue;
+    GemmI8Args p{};
+    p.dA = dA; p.dA_stride = K / 32; p.dB = dB; p.dB_stride = ldb; p.out = out; p.out_cs = out_cs;
+    p.M = M; p.N = N; p.K = K;
+    p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + GM_BN - 1) / GM_BN;
+    const int tiles = p.mtiles * p.ntiles;
+    gemm_i8_kernel<<<(unsigned) (tiles < sms ? tiles : sms), GM_THREADS, GM_SMEM, st>>>(tmA, tmB, p);
+    return cudaGetLastError();
+}
+
+}  // namespace b200

@@ -79,6 +79,11 @@ struct Ctx {
     std::unordered_map<uint64_t, GraphEntry> graphs;
     std::unordered_map<uint64_t, StreamProgram> programs;
     int ds_grid = -1;             // CTAs of the decode stream kernel (-1: not probed yet, 0: unavailable)
+    // tensor-core GEMM scratch (gemm_i8.cu): int8 activations [N][K], their block scales, unpacked q4_0 weights [M][K]
+    int8_t * gm_qb = nullptr; size_t gm_qb_cap = 0;
+    float *  gm_db = nullptr; size_t gm_db_cap = 0;
+    int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;
+    int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
 };
@@ -99,6 +104,14 @@ static int ensure_act(Ctx * c, int64_t blocks) {
     CU(cudaMalloc((void **) &c->act_ds, (size_t) cap * sizeof(ActDS)));
     c->act_cap = cap;
     c->q_ptr = nullptr;
+    return 0;
+}
+template <typename T>
+static int ensure_buf(Ctx * c, T ** p, size_t * cap, size_t bytes) {
+    if (bytes <= *cap) return 0;
+    if (*p) { CU(cudaStreamSynchronize(c->st)); cudaFree(*p); *p = nullptr; *cap = 0; }
+    CU(cudaMalloc((void **) p, bytes + 256));
+    *cap = bytes;
     return 0;
 }
 static int ensure_stage(Ctx * c, size_t bytes) {
@@ -147,6 +160,7 @@ extern "C" int b200_open(const char * uri, b200_handle * h) {
     Ctx * c = new Ctx();
     c->dev = dev;
     CU(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    CU(cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, dev));
     int rc = ensure_act(c, 4096);
     if (rc) { delete c; return rc; }
     *h = (b200_handle) (uintptr_t) c;
@@ -160,6 +174,7 @@ extern "C" int b200_close(b200_handle h) {
     for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); }
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
+    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a);
     cudaStreamDestroy(c->st);
     c->magic = 0;
     delete c;
@@ -325,6 +340,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
     const bool fuseq = q && N <= 2 && gemv_fuseq_enabled();
+    // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N, development knob)
+    static const int gemm_min_n = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : 32;
+    const bool use_gemm = q && (s0->type == T_Q8_0 || s0->type == T_Q4_0) && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
+                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0;
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
@@ -332,7 +351,22 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
         const char * x = (const char *) s1->data + i12 * s1->nb[2] + i13 * s1->nb[3];
         float * y = (float *) ((char *) d->data + i12 * d->nb[2] + i13 * d->nb[3]) + row_off_dst;
         const int64_t i02 = i12 / r2, i03 = i13 / r3;
-        if (q) {
+        if (q && use_gemm) {
+            // ---- many columns: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
+            const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
+            const long long ldb = gemm_i8_ldb((int) N);
+            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K); if (rc) return rc;
+            rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) NB * ldb * sizeof(float)); if (rc) return rc;
+            CU(launch_quantize_rows_i8((const float *) x, s1->nb[1], (int) K, (int) N, c->gm_qb, c->gm_db, ldb, c->st)); c->launches++;
+            const int8_t * A = (const int8_t *) wp.p[0];
+            if (s0->type == T_Q4_0) {
+                rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K); if (rc) return rc;
+                CU(launch_unpack_q4_0_i8(wp.p[0], M * NB, c->gm_a, c->st)); c->launches++;
+                A = c->gm_a;
+            }
+            CU(launch_gemm_i8(A, (const __half *) wp.p[1], c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) K, c->sms, c->st)); c->launches++;
+            c->q_ptr = nullptr;
+        } else if (q) {
             GemvArgs a{};
             a.nmat = 1; a.K = K; a.dcs = dcs;
             a.mat[0].w = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
