@@ -11,11 +11,12 @@
 // produces the 128 x 128 exact sums of one block into one of four TMEM accumulator buffers, and the epilogue warps
 // fold it into fp32 registers while the tensor core already works on the next blocks.
 //
-// CTA (1 per SM, persistent over 128 x 128 output tiles), 10 warps:
+// CTA (1 per SM, persistent over 128 x 128 output tiles), 18 warps:
 //   warp 0      TMA producer: A = weights int8 [M][K] (the SoA quant array of q8_0 as it lies in HBM, or the unpacked
 //               scratch of q4_0), B = activations int8 [N][K]; 128 x 128-byte boxes, 128-B swizzle, 6-stage ring
 //   warp 1      TMEM allocation + MMA issue (one elected lane): 4 MMAs per stage, one per block, each into its own buffer
-//   warps 2..9  epilogue: tcgen05.ld (32 lanes x 64 columns per warp), acc += float(sumi) * (d_w * d_a), final store
+//   warps 2..17 epilogue: tcgen05.ld (32 lanes x 32 columns per warp), acc += float(sumi) * (d_w * d_a) in packed
+//               fp32x2 math, final store
 #include "b200_internal.cuh"
 
 #include <cuda.h>
@@ -26,10 +27,14 @@ namespace b200 {
 constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 128;        // tile; BK in int8 elements = bytes = one 128-B swizzle row
 constexpr int GM_STAGES = 6;
 constexpr int GM_NBUF = 4;                                  // TMEM accumulator buffers of GM_BN columns
-constexpr int GM_THREADS = 320;
+constexpr int GM_EPI_WARPS = 16;                           // 4 TMEM lane quarters x 4 column groups of 32
+constexpr int GM_THREADS = 64 + GM_EPI_WARPS * 32;
 constexpr int GM_STAGE_A = GM_BM * GM_BK, GM_STAGE_B = GM_BN * GM_BK;
-constexpr int GM_OFF_A = 0, GM_OFF_B = GM_STAGES * GM_STAGE_A, GM_OFF_BAR = GM_OFF_B + GM_STAGES * GM_STAGE_B;
+constexpr int GM_STAGE_S = 4 * GM_BN * 4;                   // activation block scales of a stage: 4 blocks x 128 columns f32
+constexpr int GM_OFF_A = 0, GM_OFF_B = GM_STAGES * GM_STAGE_A, GM_OFF_S = GM_OFF_B + GM_STAGES * GM_STAGE_B;
+constexpr int GM_OFF_BAR = GM_OFF_S + GM_STAGES * GM_STAGE_S;
 constexpr int GM_SMEM = GM_OFF_BAR + 256 + 1024;            // + barriers + slack to align the base to 1024 B
+static_assert(GM_SMEM <= 232448, "shared memory");
 constexpr long long GM_TIMEOUT_CYCLES = 8000000000ll;
 
 struct GemmI8Args {
@@ -92,19 +97,22 @@ __device__ __forceinline__ void gm_tmem_ld_wait() { asm volatile("tcgen05.wait::
 
 // ------------------------------------------------------------------------------------------------ kernel
 __global__ void __launch_bounds__(GM_THREADS, 1)
-gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmI8Args p) {
+gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
+               const GemmI8Args p) {
     extern __shared__ uint8_t gm_smem_raw[];
     const uint32_t base = (gm_smem_u32(gm_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
     uint8_t * smem = gm_smem_raw + (base - gm_smem_u32(gm_smem_raw));
-    const uint32_t sA = base + GM_OFF_A, sB = base + GM_OFF_B, bars = base + GM_OFF_BAR;
-    const uint32_t full0 = bars, empty0 = bars + GM_STAGES * 8, tfull0 = bars + 2 * GM_STAGES * 8, tempty0 = tfull0 + GM_NBUF * 8;
-    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + GM_OFF_BAR + 2 * GM_STAGES * 8 + 2 * GM_NBUF * 8);
+    const uint32_t sA = base + GM_OFF_A, sB = base + GM_OFF_B, sS = base + GM_OFF_S, bars = base + GM_OFF_BAR;
+    // full: TMA landed (A, B, scales); empty: the stage's MMAs are done with A/B; sempty: the epilogue is done with the scales
+    const uint32_t full0 = bars, empty0 = bars + GM_STAGES * 8, sempty0 = bars + 2 * GM_STAGES * 8;
+    const uint32_t tfull0 = bars + 3 * GM_STAGES * 8, tempty0 = tfull0 + GM_NBUF * 8;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + GM_OFF_BAR + 3 * GM_STAGES * 8 + 2 * GM_NBUF * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nks = (p.K + GM_BK - 1) / GM_BK, KB = p.K / 32, ntiles_total = p.mtiles * p.ntiles;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
-        for (int i = 0; i < GM_NBUF; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, 8); }
+        for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(sempty0 + i * 8, GM_EPI_WARPS); }
+        for (int i = 0; i < GM_NBUF; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, GM_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {            // all 512 TMEM columns: four 128-column int32 accumulator buffers
@@ -121,15 +129,18 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmS) : "memory");
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
                 const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
                 for (int ks = 0; ks < nks; ks++, it++) {
                     const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
-                    gm_mbar_expect_tx(full0 + s * 8, GM_STAGE_A + GM_STAGE_B);
+                    gm_mbar_wait(sempty0 + s * 8, ph ^ 1);
+                    gm_mbar_expect_tx(full0 + s * 8, GM_STAGE_A + GM_STAGE_B + GM_STAGE_S);
                     gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * GM_BK, mt * GM_BM);
                     gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * GM_BK, nt * GM_BN);
+                    gm_tma_2d(sS + s * GM_STAGE_S, &tmS, full0 + s * 8, nt * GM_BN, ks * 4);
                 }
             }
         }
@@ -158,54 +169,72 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
     } else {
-        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), column half (w - 2) / 4
-        const int q = warp & 3, half = (warp - 2) >> 2;
+        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), columns 32 * ((w - 2) / 4) .. +31
+        const int q = warp & 3, cg = (warp - 2) >> 2;
         const int m_local = q * 32 + lane;
-        uint32_t bc = 0;
+        uint32_t bc = 0, it = 0;
         for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
             const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
             const int m = mt * GM_BM + m_local;
             const __half * dw_row = p.dA + (long long) min(m, p.M - 1) * p.dA_stride;
-            const float * db_col = p.dB + nt * GM_BN + half * 64;
-            float acc[64];
+            float2 acc[16];
             #pragma unroll
-            for (int i = 0; i < 64; i++) acc[i] = 0.f;
-            for (int b = 0; b < KB; b++, bc++) {
-                const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
-                const float dw = __half2float(dw_row[b]);
-                const float4 * db4 = (const float4 *) (db_col + (long long) b * p.dB_stride);
-                gm_mbar_wait(tfull0 + buf * 8, bph);
-                gm_fence_after();
-                const uint32_t taddr = tmem + ((uint32_t) (q * 32) << 16) + buf * GM_BN + half * 64;
-                int v0[32], v1[32];
-                gm_tmem_ld32(taddr, v0);
-                gm_tmem_ld32(taddr + 32, v1);
-                gm_tmem_ld_wait();
-                gm_fence_before();
+            for (int i = 0; i < 16; i++) acc[i] = make_float2(0.f, 0.f);
+            // weight scales of this row: 4 fp16 (one stage) per 8-byte load, fetched one stage ahead
+            const bool dw_vec = (p.dA_stride & 3) == 0 && ((uintptr_t) p.dA & 7) == 0;     // else (K % 128 != 0): 2-byte loads
+            auto load_dw = [&](int ks) -> uint2 {
+                if (dw_vec) return *(const uint2 *) (dw_row + ks * 4);
+                unsigned short h[4] = {0, 0, 0, 0};
+                for (int j = 0; j < 4 && ks * 4 + j < KB; j++) h[j] = *(const unsigned short *) (dw_row + ks * 4 + j);
+                return make_uint2((uint32_t) h[0] | ((uint32_t) h[1] << 16), (uint32_t) h[2] | ((uint32_t) h[3] << 16));
+            };
+            uint2 dwn = load_dw(0);
+            for (int ks = 0; ks < nks; ks++, it++) {
+                const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
+                const uint2 dwc = dwn;
+                if (ks + 1 < nks) dwn = load_dw(ks + 1);
+                const __half2 h01 = *(const __half2 *) &dwc.x, h23 = *(const __half2 *) &dwc.y;
+                const float dws[4] = {__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23)};
+                gm_mbar_wait(full0 + s * 8, ph);                            // scales of this stage are in shared memory
+                const float4 * sc = (const float4 *) (smem + GM_OFF_S + s * GM_STAGE_S) + cg * 8;
+                const int nb = min(4, KB - ks * 4);
+                #pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (j < nb) {
+                        const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
+                        gm_mbar_wait(tfull0 + buf * 8, bph);
+                        gm_fence_after();
+                        int v[32];
+                        gm_tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * GM_BN + cg * 32, v);
+                        gm_tmem_ld_wait();
+                        gm_fence_before();
+                        __syncwarp();
+                        if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);  // buffer free for the MMA issuer
+                        bc++;
+                        // acc += float(sumi) * (d_w * d_a), as ggml_vec_dot_q8_0_q8_0 does per block (ggml-cpu-quants.c:4004-4012).
+                        // int -> float without the quarter-rate I2F: |sumi| <= 32 * 127 * 127 < 2^22, so
+                        // as_float(0x4B400000 + sumi) == 12582912 + sumi exactly, and subtracting 12582912 is exact too.
+                        const float2 dw2 = make_float2(dws[j], dws[j]), mg = make_float2(-12582912.f, -12582912.f);
+                        #pragma unroll
+                        for (int i = 0; i < 8; i++) {
+                            const float4 d = sc[j * (GM_BN / 4) + i];     // activation scales of block j, columns 4i..4i+3 of this group
+                            const float2 f0 = __fadd2_rn(make_float2(__int_as_float(v[4 * i + 0] + 0x4B400000), __int_as_float(v[4 * i + 1] + 0x4B400000)), mg);
+                            const float2 f1 = __fadd2_rn(make_float2(__int_as_float(v[4 * i + 2] + 0x4B400000), __int_as_float(v[4 * i + 3] + 0x4B400000)), mg);
+                            acc[2 * i + 0] = __ffma2_rn(f0, __fmul2_rn(dw2, make_float2(d.x, d.y)), acc[2 * i + 0]);
+                            acc[2 * i + 1] = __ffma2_rn(f1, __fmul2_rn(dw2, make_float2(d.z, d.w)), acc[2 * i + 1]);
+                        }
+                    }
+                }
                 __syncwarp();
-                if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);     // buffer free for the MMA issuer
-                #pragma unroll
-                for (int i4 = 0; i4 < 8; i4++) {
-                    const float4 d = __ldg(db4 + i4);
-                    acc[i4 * 4 + 0] = fmaf((float) v0[i4 * 4 + 0], dw * d.x, acc[i4 * 4 + 0]);
-                    acc[i4 * 4 + 1] = fmaf((float) v0[i4 * 4 + 1], dw * d.y, acc[i4 * 4 + 1]);
-                    acc[i4 * 4 + 2] = fmaf((float) v0[i4 * 4 + 2], dw * d.z, acc[i4 * 4 + 2]);
-                    acc[i4 * 4 + 3] = fmaf((float) v0[i4 * 4 + 3], dw * d.w, acc[i4 * 4 + 3]);
-                }
-                #pragma unroll
-                for (int i4 = 0; i4 < 8; i4++) {
-                    const float4 d = __ldg(db4 + 8 + i4);
-                    acc[32 + i4 * 4 + 0] = fmaf((float) v1[i4 * 4 + 0], dw * d.x, acc[32 + i4 * 4 + 0]);
-                    acc[32 + i4 * 4 + 1] = fmaf((float) v1[i4 * 4 + 1], dw * d.y, acc[32 + i4 * 4 + 1]);
-                    acc[32 + i4 * 4 + 2] = fmaf((float) v1[i4 * 4 + 2], dw * d.z, acc[32 + i4 * 4 + 2]);
-                    acc[32 + i4 * 4 + 3] = fmaf((float) v1[i4 * 4 + 3], dw * d.w, acc[32 + i4 * 4 + 3]);
-                }
+                if (lane == 0) gm_mbar_arrive(sempty0 + s * 8);            // scale tile of this stage may be overwritten
             }
             if (m < p.M) {
-                const int n0 = nt * GM_BN + half * 64;
+                const int n0 = nt * GM_BN + cg * 32;
                 #pragma unroll
-                for (int i = 0; i < 64; i++)
-                    if (n0 + i < p.N) p.out[(long long) (n0 + i) * p.out_cs + m] = acc[i];      // 32 lanes = 32 consecutive m: coalesced
+                for (int i = 0; i < 16; i++) {                              // 32 lanes = 32 consecutive m: coalesced
+                    if (n0 + 2 * i     < p.N) p.out[(long long) (n0 + 2 * i)     * p.out_cs + m] = acc[i].x;
+                    if (n0 + 2 * i + 1 < p.N) p.out[(long long) (n0 + 2 * i + 1) * p.out_cs + m] = acc[i].y;
+                }
             }
         }
     }
@@ -296,6 +325,18 @@ static bool make_map_i8(CUtensorMap * m, const void * base, long long rows, long
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// activation block scales f32 [KB][ldb]: box = 128 columns x 4 blocks, no swizzle
+static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, long long ldb) {
+    encode_tiled_t enc = encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t) ldb, (cuuint64_t) KB};
+    const cuuint64_t strides[1] = {(cuuint64_t) ldb * 4};
+    const cuuint32_t box[2] = {(cuuint32_t) GM_BN, 4};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 int gemm_i8_ldb(int N) { return (N + GM_BN - 1) / GM_BN * GM_BN; }      // leading dimension the caller must give dB
 
 // A: int8 [M][K] (16-B aligned, K % 16 == 0), dA: fp16 [M][K/32]; B: int8 [N][K], dB: f32 [K/32][ldb]; out[n * out_cs + m]
@@ -307,14 +348,14 @@ cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA, const int8_t * B
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    CUtensorMap tmA, tmB;
-    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K)) return cudaErrorInvalidValue;
+    CUtensorMap tmA, tmB, tmS;
+    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K) || !make_map_scales(&tmS, dB, K / 32, ldb)) return cudaErrorInvalidValue;
     GemmI8Args p{};
     p.dA = dA; p.dA_stride = K / 32; p.dB = dB; p.dB_stride = ldb; p.out = out; p.out_cs = out_cs;
     p.M = M; p.N = N; p.K = K;
     p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + GM_BN - 1) / GM_BN;
     const int tiles = p.mtiles * p.ntiles;
-    gemm_i8_kernel<<<(unsigned) (tiles < sms ? tiles : sms), GM_THREADS, GM_SMEM, st>>>(tmA, tmB, p);
+    gemm_i8_kernel<<<(unsigned) (tiles < sms ? tiles : sms), GM_THREADS, GM_SMEM, st>>>(tmA, tmB, tmS, p);
     return cudaGetLastError();
 }
 
