@@ -28,6 +28,9 @@ for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "ggml-hexagon_b200"))
 
 Q4_0 = 2
 METRIC = "tokens/s Llama Q4_0 decode (tg, MUL_MAT+ADD path, batch 1)"
+# dram__bytes_read + dram__bytes_write of one step / 225 MUL_MAT launches, from the ncu --set full capture of the step
+# (profiles/r01_b_ncu_decode_stream_q4_0_llama2_7b.txt: 3 716 608 000 + 16 083 456 B); the per-node kernels read the same bytes
+TRAFFIC_PER_LAUNCH = int((3716608000 + 16083456) / 225)
 
 
 # ------------------------------------------------------------------------------------------------ workloads
@@ -110,8 +113,9 @@ def measured_peak_hbm():
 class DecodeWorkload:
     """All MUL_MAT/ADD nodes of one decoded token, device resident.  Row r-th slice of every weight when world > 1."""
 
-    def __init__(self, B, sess, model, rank=0, world=1, seed=1234):
+    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p"):
         import ctypes as C
+        self.mode = mode
         self.B, self.s, self.C = B, sess, C
         self.rank, self.world = rank, world
         layer, L, out, h, f = llama_shapes(model)
@@ -138,7 +142,10 @@ class DecodeWorkload:
         self.weight_bytes_local = sum(w.nbytes for lw in self.weights for w in lw.values()) + self.w_out.nbytes
         # activations (f32, device)
         kv = dict((n, m) for n, m, _ in layer)["wk"]
-        mk = lambda n: sess.malloc(4 * n)
+        # row split: activations live in the symmetric heap (same offsets on every rank) so that the GEMVs can store
+        # their slices straight into every peer's copy over NVLink
+        self.heap = B.SymHeap(sess, 4 * (8 * h + 2 * kv + 2 * f + out[1]) + 64 * 256) if world > 1 else None
+        mk = (lambda n: self.heap.malloc(4 * n)) if world > 1 else (lambda n: sess.malloc(4 * n))
         self.x = mk(h); self.q = mk(h); self.k = mk(kv); self.v = mk(kv); self.o = mk(h); self.hres = mk(h)
         self.g = mk(f); self.u = mk(f); self.dn = mk(h); self.x2 = mk(h); self.x3 = mk(h); self.logits = mk(out[1])
         self.x_host = np.random.default_rng(seed + 1).uniform(-1, 1, h).astype(np.float32)
@@ -189,6 +196,9 @@ class DecodeWorkload:
         if self.world == 1:
             self.s.graph_compute(self._nodes, use_cuda_graph=True)
             return
+        if self.mode == "p2p":
+            self.s.graph_compute_rowsplit(self._nodes, use_cuda_graph=True)
+            return
         L = B.lib()
         for n in self.node_list:
             if n.dst.op == B.OP_MUL_MAT:
@@ -229,6 +239,49 @@ def time_shapes(B, s, wl, iters=3):
         out.append({"shape": "%s %dx%d" % (name, rows, K), "us": round(per * 1e6, 3), "GB/s": round(by / per / 1e9, 1)})
         dst.free()
     return out
+
+
+def time_prefill(B, s, model, N=512, types=((8, "q8_0"), (2, "q4_0")), iters=5):
+    """BASELINE.json configs[2]: the layer MUL_MATs with N = 512 activation columns through the tensor-core GEMM
+    (b200_mulmat, device resident).  One HBM copy per shape, timed back to back with CUDA events; pp tokens/s =
+    N / (layers * sum of the layer's MUL_MAT times + output matrix) -- MUL_MAT only, as for decode."""
+    import ctypes as C
+    import pyoracle as O
+    layer, L, out, h, f = llama_shapes(model)
+    rng = np.random.default_rng(7)
+    res = {}
+    for t, name in types:
+        per_shape, tot_s, flops = [], 0.0, 0.0
+        seen = {}
+        for nm, M, K in layer + [out]:
+            if (M, K) not in seen:
+                raw = np.tile(O.random_blocks(t, 128, K, rng), ((M + 127) // 128, 1))[:M]
+                w = s.weights(t, raw, K)
+                x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+                xb, db = s.to_device(x), s.malloc(4 * N * M)
+                s0, s1, d = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(db.ptr, [M, N], op=B.OP_MUL_MAT)
+                for _ in range(2):
+                    B._ck(B.lib().b200_mulmat(s.h, C.byref(s0), C.byref(s1), C.byref(d)))
+                s.sync()
+                e0, e1 = s.event(), s.event()
+                s.record(e0)
+                for _ in range(iters):
+                    B._ck(B.lib().b200_mulmat(s.h, C.byref(s0), C.byref(s1), C.byref(d)))
+                s.record(e1)
+                sec = s.elapsed_ms(e0, e1) * 1e-3 / iters
+                seen[(M, K)] = sec
+                per_shape.append({"shape": "%dx%d" % (M, K), "us": round(sec * 1e6, 1), "TOPS": round(2.0 * M * N * K / sec / 1e12, 1)})
+                for b in (xb, db):
+                    b.free()
+                w.free()
+            reps = 1 if nm == out[0] else L
+            tot_s += reps * seen[(M, K)]
+            flops += reps * 2.0 * M * N * K
+        res[name] = {"tokens_per_s": round(N / tot_s, 1), "ms": round(tot_s * 1e3, 3), "TOPS": round(flops / tot_s / 1e12, 1),
+                     "frac_of_int8_nominal_4500": round(flops / tot_s / 4.5e15, 4), "shapes": per_shape}
+    res["note"] = ("N=%d columns, MUL_MAT only; exact per-32-block int8 tcgen05.mma + fp32 scale-accumulate: bound by the FMA pipe, "
+                   "not the tensor pipe (DESIGN.md section 6)" % N)
+    return res
 
 
 def cpu_baseline(model, budget_s):
@@ -288,7 +341,7 @@ def run_b200(args, rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     s = B.Session(local)
     model = "llama2-7b" if world == 1 else "llama3-70b"
-    if world > 1:
+    if world > 1 and args.rowsplit == "nccl":
         import torch
         idb = torch.zeros(128, dtype=torch.uint8)
         if rank == 0:
@@ -299,7 +352,14 @@ def run_b200(args, rank, world):
         dist.broadcast(idb, 0)
         idh = (C.c_uint8 * 128)(*idb.cpu().tolist())
         B._ck(B.lib().b200_rowsplit_init(s.h, idh, rank, world))
-    wl = DecodeWorkload(B, s, model, rank, world)
+    wl = DecodeWorkload(B, s, model, rank, world, mode=args.rowsplit)
+    if world > 1:
+        import torch
+        mine = torch.tensor(list(wl.heap.handle), dtype=torch.uint8, device="cuda")
+        allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(allh, mine)
+        wl.heap.attach(b"".join(bytes(t.cpu().tolist()) for t in allh), rank, world)
+        dist.barrier()
 
     def barrier():
         s.sync()
@@ -353,6 +413,7 @@ def run_b200(args, rank, world):
     clocks = sampler.stop()
     logits = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(wl.out[1],)).copy()
     shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
+    prefill = time_prefill(B, s, model) if world == 1 and not args.no_shapes and rank == 0 else None
     if rank != 0:
         s.close()
         return
@@ -368,15 +429,19 @@ def run_b200(args, rank, world):
             "config": {"workload": model + "-q4_0-decode" + ("-rowsplit%d" % world if world > 1 else ""), "batch": 1,
                        "layers": wl.L, "mul_mat_per_step": wl.n_mulmat, "add_per_step": 2 * wl.L,
                        "weight_bytes_per_gpu": wl.weight_bytes_local, "l2": "inputs larger than L2 (weights streamed once per step)",
-                       "submit": "one b200_graph_compute (CUDA graph + PDL)" if world == 1 else "per-node b200_mulmat_rowsplit + ncclAllGather"},
+                       "submit": "one b200_graph_compute (CUDA graph + PDL)" if world == 1 else
+                       ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores slices into peer HBM over NVLink, flag exchange per op)"
+                        if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": None, "peak_source": peak_src, "kernel": "gemv_q_kernel<q4_0,1,2>",
+                         "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv4_kernel<q4_0,1,R>",
                          "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
             "e2e": {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
                     "timer": "host perf_counter around K calls of h2d + graph_compute + d2h (each step ends synchronised)"},
             "gpu_launches": int(launches), "clocks": clocks, "logits_finite": bool(np.isfinite(logits).all())}
     if shapes:
         line["shapes"] = shapes
+    if prefill:
+        line["pp512"] = prefill
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
     print(json.dumps(line))
@@ -389,6 +454,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rowsplit", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: p2p = GEMV stores into peer memory + flag exchange (default); nccl = ncclAllGather per MUL_MAT")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-shapes", action="store_true", help="skip the per-shape GEMV table")
     args = ap.parse_args()

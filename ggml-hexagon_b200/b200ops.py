@@ -24,7 +24,8 @@ SYMBOLS = [
     "b200_host_alloc", "b200_host_free", "b200_weights_upload", "b200_weights_download", "b200_block_elems",
     "b200_block_bytes", "b200_event_create", "b200_event_record", "b200_event_elapsed_ms", "b200_event_destroy",
     "b200_launch_count", "b200_flush_l2", "b200_rowsplit_unique_id", "b200_rowsplit_init", "b200_rowsplit_finalize",
-    "b200_mulmat_rowsplit",
+    "b200_mulmat_rowsplit", "b200_rowsplit_heap_create", "b200_rowsplit_heap_attach", "b200_rowsplit_heap_attach_ptrs",
+    "b200_rowsplit_heap_destroy", "b200_graph_compute_rowsplit",
 ]
 
 
@@ -88,6 +89,11 @@ def lib():
         L.b200_rowsplit_unique_id.argtypes = [VP]
         L.b200_rowsplit_init.argtypes = [H, VP, I32, I32]
         L.b200_rowsplit_finalize.argtypes = [H]
+        L.b200_rowsplit_heap_create.argtypes = [H, C.c_size_t, C.POINTER(VP), VP]
+        L.b200_rowsplit_heap_attach.argtypes = [H, VP, I32, I32]
+        L.b200_rowsplit_heap_attach_ptrs.argtypes = [H, C.POINTER(VP), C.POINTER(I32), I32, I32]
+        L.b200_rowsplit_heap_destroy.argtypes = [H]
+        L.b200_graph_compute_rowsplit.argtypes = [H, C.POINTER(Node), I32, I32]
         _lib = L
     return _lib
 
@@ -120,6 +126,43 @@ class DevBuf:
         if self.ptr:
             _ck(lib().b200_free(self.sess.h, self.ptr))
             self.ptr = None
+
+
+class HeapBuf:
+    """A slice of the symmetric row-split heap (same offset on every rank)."""
+
+    def __init__(self, ptr, nbytes):
+        self.ptr, self.nbytes = ptr, nbytes
+
+    def free(self):
+        pass
+
+
+class SymHeap:
+    """b200_rowsplit_heap_create + a bump allocator: every rank must allocate the same sizes in the same order."""
+
+    def __init__(self, sess, nbytes):
+        self.sess = sess
+        base = C.c_void_p()
+        self.handle = (C.c_uint8 * 64)()
+        _ck(lib().b200_rowsplit_heap_create(sess.h, nbytes, C.byref(base), self.handle))
+        self.base, self.size, self.off = base.value, nbytes, 0
+
+    def malloc(self, nbytes):
+        nbytes = (int(nbytes) + 255) & ~255
+        assert self.off + nbytes <= self.size, "symmetric heap exhausted"
+        b = HeapBuf(self.base + self.off, nbytes)
+        self.off += nbytes
+        return b
+
+    def attach(self, all_handles_bytes, rank, world):
+        buf = (C.c_uint8 * (64 * world)).from_buffer_copy(bytes(all_handles_bytes))
+        _ck(lib().b200_rowsplit_heap_attach(self.sess.h, buf, rank, world))
+
+    def attach_ptrs(self, bases, devices, rank, world):
+        pb = (C.c_void_p * world)(*bases)
+        pd = (C.c_int32 * world)(*devices)
+        _ck(lib().b200_rowsplit_heap_attach_ptrs(self.sess.h, pb, pd, rank, world))
 
 
 class Weights:
@@ -219,7 +262,7 @@ class Session:
 
     def to_host(self, buf, shape, dtype):
         out = np.empty(shape, dtype=dtype)
-        _ck(lib().b200_memcpy_d2h(self.h, _p(out), buf.ptr if isinstance(buf, DevBuf) else buf, out.nbytes))
+        _ck(lib().b200_memcpy_d2h(self.h, _p(out), buf.ptr if hasattr(buf, "ptr") else buf, out.nbytes))
         return out
 
     def weights(self, t, raw, K):
@@ -298,6 +341,11 @@ class Session:
         ab.free()
         ob.free()
         return out
+
+    def graph_compute_rowsplit(self, nodes, use_cuda_graph=True):
+        arr = (Node * len(nodes))(*nodes) if not isinstance(nodes, C.Array) else nodes
+        _ck(lib().b200_graph_compute_rowsplit(self.h, arr, len(arr), int(use_cuda_graph)))
+        return arr
 
     def graph_compute(self, nodes, use_cuda_graph=True):
         arr = (Node * len(nodes))(*nodes) if not isinstance(nodes, C.Array) else nodes

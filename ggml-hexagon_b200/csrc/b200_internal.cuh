@@ -85,7 +85,13 @@ struct GemvArgs {
     const float * x; int64_t x_col_stride;     // FUSEQ: f32 activations, column stride in bytes
     ActView act;                                // !FUSEQ: pre-quantised scratch
     int l2_prefetch;                            // each CTA bulk-prefetches its row slice into L2 first
+    // row split over the GPUs of one box: every result is also stored into the peers' copies of dst over NVLink
+    // (peer address = local address + peer_delta[p]; dst lies in the symmetric heap every rank allocated alike)
+    int npeers; long long peer_delta[7];
 };
+// one warp: tell every peer "my slice of the op is in your memory" (release, system scope), then wait for theirs
+cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr /* [npeers] */,
+                                     const int * peer_rank /* [npeers] */, cudaStream_t st);
 // fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
 cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
 bool gemv_pdl_enabled();

@@ -99,7 +99,12 @@ gemv4_kernel(const GemvArgs a) {
         if (row0 + r < M) {
             const int64_t o = (int64_t) c * a.dcs + row0 + r;
             mt.dst[o] = v;
-            if (mt.add_dst) mt.add_dst[o] = mt.add_src[o] + v;
+            float s = 0.f;
+            if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
+            for (int pi = 0; pi < a.npeers; pi++) {           // row split: the same values into every peer's dst (NVLink stores)
+                *(float *) ((char *) (mt.dst + o) + a.peer_delta[pi]) = v;
+                if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
+            }
         }
     }
 }

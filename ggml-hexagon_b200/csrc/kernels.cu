@@ -252,6 +252,37 @@ cudaError_t launch_repack(int type, bool to_soa, uint8_t * soa, int64_t T, int64
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ row-split exchange
+// Runs after a row-split GEMV (stream order: its NVLink stores are complete).  Lane p: publish "op number n of this
+// rank is in your memory" into peer p's flag slot, then wait until peer p has published the same op number here.
+// Counters only grow, so CUDA-graph replays need no reset.  The waits are bounded (trap instead of hanging the GPU).
+struct ExchangeArgs { long long peer_flag_addr[7]; int peer_rank[7]; int npeers; };
+__global__ void rowsplit_exchange_kernel(uint32_t * local_flags, uint32_t * counter, const ExchangeArgs a) {
+    const int p = threadIdx.x;
+    const uint32_t n = *counter + 1;
+    __syncwarp();
+    if (p < a.npeers) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag_addr[p]), "r"(n) : "memory");
+        const long long t0 = clock64();
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local_flags + a.peer_rank[p]) : "memory");
+            if (clock64() - t0 > 8000000000ll) __trap();
+        } while ((int) (v - n) < 0);
+    }
+    __syncwarp();
+    if (p == 0) *counter = n;
+}
+cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr,
+                                     const int * peer_rank, cudaStream_t st) {
+    ExchangeArgs a{};
+    a.npeers = npeers;
+    for (int i = 0; i < npeers; i++) { a.peer_flag_addr[i] = peer_flag_addr[i]; a.peer_rank[i] = peer_rank[i]; }
+    rowsplit_exchange_kernel<<<1, 32, 0, st>>>(local_flags, counter, a);
+    return cudaGetLastError();
+}
+
 __global__ void fill_kernel(uint4 * p, size_t n16, uint32_t v) {
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t) gridDim.x * blockDim.x)
         p[i] = make_uint4(v, v, v, v);

@@ -86,6 +86,10 @@ struct Ctx {
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
+    // fused row split over peer memory: symmetric heap [flags 4 KB | user area], peers' mappings of theirs
+    char * rs_heap = nullptr; size_t rs_heap_bytes = 0;
+    char * rs_peer[8] = {nullptr}; bool rs_ipc[8] = {false};
+    bool rs_attached = false, rs_on = false;
 };
 
 static Ctx * ctx_of(b200_handle h) {
@@ -172,6 +176,8 @@ extern "C" int b200_close(b200_handle h) {
     cudaStreamSynchronize(c->st);
     for (auto & kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); }
+    for (int r = 0; r < 8; r++) if (c->rs_ipc[r] && c->rs_peer[r]) cudaIpcCloseMemHandle(c->rs_peer[r]);
+    cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
     cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a);
@@ -322,6 +328,25 @@ static int mulmat_check(const b200_tensor * s0, const b200_tensor * s1, const b2
 
 struct FusedAdd { const float * src = nullptr; float * dst = nullptr; };
 
+// ---- fused row split: peer deltas for the GEMV stores, and the exchange that follows each row-split op
+static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64_t * bytes, int n) {
+    a.npeers = 0;
+    if (!c->rs_on || c->world == 1) return 0;
+    for (int i = 0; i < n; i++) {
+        const char * p = (const char *) dsts[i];
+        if (p < c->rs_heap + 4096 || p + bytes[i] > c->rs_heap + c->rs_heap_bytes) return fail(B200_EINVAL, "rowsplit: dst is outside the symmetric heap (b200_rowsplit_heap_create)");
+    }
+    for (int r = 0; r < c->world; r++) if (r != c->rank) a.peer_delta[a.npeers++] = (long long) (c->rs_peer[r] - c->rs_heap);
+    return 0;
+}
+static int rs_exchange(Ctx * c) {
+    if (!c->rs_on || c->world == 1) return 0;
+    long long addr[7]; int ranks[7]; int np = 0;
+    for (int r = 0; r < c->world; r++) if (r != c->rank) { addr[np] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank); ranks[np] = r; np++; }
+    CU(launch_rowsplit_exchange((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, addr, ranks, c->st)); c->launches++;
+    return 0;
+}
+
 static WPtrs wptrs_offset(const b200_tensor * s0, WPtrs wp, int64_t byte_off) {
     const int64_t blk_off = byte_off / block_bytes(s0->type);
     WFields f = wfields(s0->type);
@@ -343,7 +368,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N, development knob)
     static const int gemm_min_n = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : 32;
     const bool use_gemm = q && (s0->type == T_Q8_0 || s0->type == T_Q4_0) && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
-                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0;
+                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 && !c->rs_on;
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
@@ -383,6 +408,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
                 }
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
+                { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; rc = rs_fill(c, a, dp, db_, 1); if (rc) return rc; }
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
                     a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
@@ -398,6 +424,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             }
         }
     }
+    if (q) { rc = rs_exchange(c); if (rc) return rc; }
     // dst may overwrite the memory the cached quantisation was taken from
     {
         const char * lo = (const char *) d->data; const char * hi = lo + d->data_len;
@@ -408,6 +435,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
 }
 
 // ---- graph-level fusion helpers (b200_graph_compute only)
+static thread_local int g_rs_world = 1;     // > 1 inside b200_graph_compute_rowsplit: MUL_MAT dst has world x the rows of src0
 static bool is_vec_mulmat(const b200_node & n) {       // quantised W x one f32 column, plain 2-D, device tensors
     return n.dst.op == B200_OP_MUL_MAT && is_qweight(n.src0.type) && (n.src0.flags & B200_TENSOR_REPACKED) &&
            n.src1.ne[1] == 1 && n.src1.ne[2] == 1 && n.src1.ne[3] == 1 && n.src0.ne[2] == 1 && n.src0.ne[3] == 1;
@@ -421,7 +449,7 @@ static bool is_vec_f32(const b200_tensor & t, int64_t n) {
 }
 // MUL_MAT node i followed by ADD node i+1 that consumes its dst: one launch writes both results
 static bool can_fuse_add(const b200_node & mm, const b200_node & ad, FusedAdd * fa) {
-    if (!is_vec_mulmat(mm) || ad.dst.op != B200_OP_ADD) return false;
+    if (g_rs_world > 1 || !is_vec_mulmat(mm) || ad.dst.op != B200_OP_ADD) return false;
     const int64_t M = mm.src0.ne[1];
     if (!is_vec_f32(ad.src0, M) || !is_vec_f32(ad.src1, M) || !is_vec_f32(ad.dst, M) || !is_vec_f32(mm.dst, M)) return false;
     const void * other;
@@ -441,15 +469,16 @@ static int group_len(const b200_node * nodes, int i, int n) {
     while (len < 3 && i + len < n) {
         const b200_node & a = nodes[i]; const b200_node & b = nodes[i + len];
         if (!is_vec_mulmat(b) || b.src0.type != a.src0.type || b.src1.data != a.src1.data || b.src0.ne[0] != a.src0.ne[0] ||
-            b.src1.nb[0] != 4 || !is_vec_f32(b.dst, b.src0.ne[1])) break;
+            b.src1.nb[0] != 4 || !is_vec_f32(b.dst, b.src0.ne[1] * g_rs_world)) break;
         // no member may write what another member (or the shared activation) occupies
-        bool clash = overlap(b.dst.data, b.src0.ne[1] * 4, a.src1.data, a.src0.ne[0] * 4);
-        for (int j = 0; j < len && !clash; j++) clash = overlap(b.dst.data, b.src0.ne[1] * 4, nodes[i + j].dst.data, nodes[i + j].src0.ne[1] * 4);
+        const int64_t W4 = 4 * g_rs_world;
+        bool clash = overlap(b.dst.data, b.src0.ne[1] * W4, a.src1.data, a.src0.ne[0] * 4);
+        for (int j = 0; j < len && !clash; j++) clash = overlap(b.dst.data, b.src0.ne[1] * W4, nodes[i + j].dst.data, nodes[i + j].src0.ne[1] * W4);
         if (clash) break;
         len++;
     }
-    if (len > 1 && (!is_vec_f32(nodes[i].dst, nodes[i].src0.ne[1]) ||
-                    overlap(nodes[i].dst.data, nodes[i].src0.ne[1] * 4, nodes[i].src1.data, nodes[i].src0.ne[0] * 4))) return 1;
+    if (len > 1 && (!is_vec_f32(nodes[i].dst, nodes[i].src0.ne[1] * g_rs_world) ||
+                    overlap(nodes[i].dst.data, nodes[i].src0.ne[1] * 4 * g_rs_world, nodes[i].src1.data, nodes[i].src0.ne[0] * 4))) return 1;
     return len;
 }
 static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
@@ -457,11 +486,16 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     const int64_t K = nodes[0].src0.ne[0], NB = K / 32;
     a.nmat = len; a.K = K; a.dcs = 0;
     const float * x = (const float *) nodes[0].src1.data;
+    const void * dsts[3]; int64_t dbytes[3];
     for (int j = 0; j < len; j++) {
-        int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &nodes[j].dst); if (rc) return rc;
+        b200_tensor dl = nodes[j].dst; dl.ne[0] = nodes[j].src0.ne[1];            // row split: this rank's slice of dst
+        int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &dl); if (rc) return rc;
         WPtrs wp; rc = wptrs_of(&nodes[j].src0, &wp); if (rc) return rc;
-        a.mat[j].w = wp; a.mat[j].M = nodes[j].src0.ne[1]; a.mat[j].dst = (float *) nodes[j].dst.data;
+        a.mat[j].w = wp; a.mat[j].M = nodes[j].src0.ne[1];
+        a.mat[j].dst = (float *) nodes[j].dst.data + (c->rs_on ? c->rank * nodes[j].src0.ne[1] : 0);
+        dsts[j] = a.mat[j].dst; dbytes[j] = a.mat[j].M * 4;
     }
+    { int rc = rs_fill(c, a, dsts, dbytes, len); if (rc) return rc; }
     if (gemv_fuseq_enabled()) {
         a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
         CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
@@ -475,6 +509,7 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     }
     a.act = ActView{c->act_qs, c->act_ds, NB};
     CU(launch_gemv2(nodes[0].src0.type, a, 1, false, c->st)); c->launches++;
+    { int rc2 = rs_exchange(c); if (rc2) return rc2; }
     for (int j = 0; j < len; j++)
         if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4, c->q_ptr, K * 4)) c->q_ptr = nullptr;
     return 0;
@@ -655,6 +690,12 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                 const int gl = fuse ? group_len(nodes, i, n) : 1;
                 if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
                 else if (fuse && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
+                else if (c->rs_on) {
+                    const int64_t rows = nodes[i].src0.ne[1];
+                    if (d.ne[0] != rows * c->world) { rc = fail(B200_EINVAL, "rowsplit: dst has %lld rows, expected %lld x %d", (long long) d.ne[0], (long long) rows, c->world); break; }
+                    b200_tensor dl = d; dl.ne[0] = rows;
+                    rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &dl, c->rank * rows);
+                }
                 else rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0);
                 break;
             }
@@ -681,7 +722,8 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         const b200_node & nd = nodes[i];
         any_host |= (nd.src0.flags | nd.src1.flags | nd.dst.flags) & B200_TENSOR_HOST;
         if (nd.dst.op == B200_OP_MUL_MAT && is_qweight(nd.src0.type)) {
-            int rc = mulmat_check(&nd.src0, &nd.src1, &nd.dst); if (rc) return rc;
+            b200_tensor dl = nd.dst; if (c->rs_on) dl.ne[0] = nd.src0.ne[1];
+            int rc = mulmat_check(&nd.src0, &nd.src1, &dl); if (rc) return rc;
             const int64_t b = nd.src0.ne[0] / 32 * nd.src1.ne[1];
             if (b > need_act) need_act = b;
         }
@@ -690,11 +732,11 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     int rc = ensure_act(c, need_act); if (rc) return rc;
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
 
-    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *)));
+    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *))) ^ (c->rs_on ? 0x9e3779b97f4a7c15ull : 0);
     // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
     // opt-in while it is slower than the CUDA-graph replay of the per-node kernels (DESIGN.md has the trace numbers)
     static const bool stream_on = getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) != 0;
-    if ((stream_on || use_cuda_graph == 3) && use_cuda_graph != 2 && c->ds_grid != 0) {
+    if ((stream_on || use_cuda_graph == 3) && use_cuda_graph != 2 && c->ds_grid != 0 && !c->rs_on) {
         if (c->ds_grid < 0) c->ds_grid = ds_grid(c->dev);
         auto ps = c->programs.find(key);
         if (ps == c->programs.end() && c->ds_grid > 0) {
@@ -813,4 +855,80 @@ extern "C" int b200_mulmat_rowsplit(b200_handle h, const b200_tensor * s0, const
     }
     NC(g_nccl.GroupEnd());
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ fused row split over peer memory
+// One process per GPU.  Every rank allocates the same symmetric heap, publishes its IPC handle, maps the peers' heaps
+// (NVLink P2P), and puts every activation vector of the decode step at the same offset.  A row-split MUL_MAT then stores
+// its slice straight into every rank's copy of dst from inside the GEMV (gemv.cu), and one 32-thread exchange kernel per
+// op replaces the ncclAllGather: release-store of the op counter into each peer, acquire-spin on theirs.
+extern "C" int b200_rowsplit_heap_create(b200_handle h, size_t bytes, void ** user_base, void * ipc_handle64) {
+    CTX(h);
+    if (c->rs_heap) return fail(B200_EINVAL, "rowsplit heap already created");
+    if (!user_base) return fail(B200_EINVAL, "user_base is NULL");
+    const size_t total = ((bytes + 255) & ~(size_t) 255) + 4096;
+    CU(cudaMalloc((void **) &c->rs_heap, total));
+    CU(cudaMemsetAsync(c->rs_heap, 0, total, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    c->rs_heap_bytes = total;
+    if (ipc_handle64) {
+        cudaIpcMemHandle_t hd;
+        static_assert(sizeof(hd) == 64, "ipc handle size");
+        CU(cudaIpcGetMemHandle(&hd, c->rs_heap));
+        memcpy(ipc_handle64, &hd, 64);
+    }
+    *user_base = c->rs_heap + 4096;
+    return 0;
+}
+static int rs_check_attach(Ctx * c, int rank, int world) {
+    if (!c->rs_heap) return fail(B200_EINVAL, "rowsplit: create the heap first");
+    if (world < 1 || world > 8 || rank < 0 || rank >= world) return fail(B200_EINVAL, "rowsplit: rank %d of %d (at most 8)", rank, world);
+    return 0;
+}
+extern "C" int b200_rowsplit_heap_attach(b200_handle h, const void * handles, int32_t rank, int32_t world) {
+    CTX(h);
+    int rc = rs_check_attach(c, rank, world); if (rc) return rc;
+    for (int r = 0; r < world; r++) {
+        if (r == rank) { c->rs_peer[r] = c->rs_heap; continue; }
+        cudaIpcMemHandle_t hd; memcpy(&hd, (const char *) handles + 64 * r, 64);
+        void * p = nullptr;
+        CU(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+        c->rs_peer[r] = (char *) p; c->rs_ipc[r] = true;
+    }
+    c->rank = rank; c->world = world; c->rs_attached = true;
+    return 0;
+}
+// same-process variant (tests: two sessions on two devices of one process): peers' heap bases are plain device pointers
+extern "C" int b200_rowsplit_heap_attach_ptrs(b200_handle h, void * const * peer_user_bases, const int32_t * peer_devices, int32_t rank, int32_t world) {
+    CTX(h);
+    int rc = rs_check_attach(c, rank, world); if (rc) return rc;
+    for (int r = 0; r < world; r++) {
+        if (r == rank) { c->rs_peer[r] = c->rs_heap; continue; }
+        if (peer_devices[r] != c->dev) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(peer_devices[r], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(B200_ECUDA, "cudaDeviceEnablePeerAccess(%d): %s", peer_devices[r], cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+        c->rs_peer[r] = (char *) peer_user_bases[r] - 4096;
+    }
+    c->rank = rank; c->world = world; c->rs_attached = true;
+    return 0;
+}
+extern "C" int b200_rowsplit_heap_destroy(b200_handle h) {
+    CTX(h);
+    CU(cudaStreamSynchronize(c->st));
+    for (int r = 0; r < 8; r++) { if (c->rs_ipc[r] && c->rs_peer[r]) cudaIpcCloseMemHandle(c->rs_peer[r]); c->rs_peer[r] = nullptr; c->rs_ipc[r] = false; }
+    if (c->rs_heap) cudaFree(c->rs_heap);
+    c->rs_heap = nullptr; c->rs_heap_bytes = 0; c->rs_attached = false;
+    return 0;
+}
+// node list of a row-split decode step: MUL_MAT src0 = THIS rank's row slice [rows x K] (REPACKED), dst = the full vector
+// [rows * world] inside the symmetric heap (complete on every rank when the op's exchange has run); ADD nodes are replicated.
+extern "C" int b200_graph_compute_rowsplit(b200_handle h, const b200_node * nodes, int32_t n, int32_t use_cuda_graph) {
+    CTX(h);
+    if (c->world > 1 && !c->rs_attached) return fail(B200_EINVAL, "rowsplit: attach the peers' heaps first");
+    c->rs_on = true; g_rs_world = c->world;
+    const int rc = b200_graph_compute(h, nodes, n, use_cuda_graph ? 2 : 0);
+    c->rs_on = false; g_rs_world = 1;
+    return rc;
 }

@@ -164,6 +164,18 @@ B200_API int b200_rowsplit_finalize(b200_handle h);
 B200_API int b200_mulmat_rowsplit(b200_handle h, const b200_tensor * src0_slice, const b200_tensor * src1,
                                   b200_tensor * dst_full);
 
+
+/* ---- fused row split over peer memory (NVLink P2P stores from inside the GEMV + a flag exchange per op instead of the
+ *      ncclAllGather).  Every rank: heap_create (same size everywhere), exchange the 64-byte IPC handles by any means,
+ *      heap_attach, carve its activation vectors out of the heap at the same offsets on every rank. */
+B200_API int b200_rowsplit_heap_create(b200_handle h, size_t bytes, void ** user_base, void * ipc_handle64);
+B200_API int b200_rowsplit_heap_attach(b200_handle h, const void * all_handles /* world x 64 bytes, by rank */, int32_t rank, int32_t world);
+/* same-process variant: the peers' user_base pointers and CUDA ordinals */
+B200_API int b200_rowsplit_heap_attach_ptrs(b200_handle h, void * const * peer_user_bases, const int32_t * peer_devices, int32_t rank, int32_t world);
+B200_API int b200_rowsplit_heap_destroy(b200_handle h);
+/* MUL_MAT nodes: src0 = this rank's row slice, dst = full vector in the heap; ADD nodes replicated; N = 1..8 columns */
+B200_API int b200_graph_compute_rowsplit(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph);
+
 #ifdef __cplusplus
 }
 #endif
