@@ -332,6 +332,9 @@ def run_reference(args, rank):
 def run_b200(args, rank, world):
     import ctypes as C
     import b200ops as B
+    # libraries (NCCL's version banner) write to fd 1: keep stdout clean for the ONE JSON line
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
@@ -444,7 +447,9 @@ def run_b200(args, rank, world):
         line["pp512"] = prefill
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
     s.close()
 
 

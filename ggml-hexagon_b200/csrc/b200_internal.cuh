@@ -88,10 +88,16 @@ struct GemvArgs {
     // row split over the GPUs of one box: every result is also stored into the peers' copies of dst over NVLink
     // (peer address = local address + peer_delta[p]; dst lies in the symmetric heap every rank allocated alike)
     int npeers; long long peer_delta[7];
+    // the LAST CTA of the launch publishes "op n of this rank is in your memory" to every peer (release, system scope):
+    // rs_ctrl[0] = CTA arrival counter, rs_ctrl[1] = ops signalled so far; peer_flag[p] = this rank's slot in peer p's flags
+    int rs_signal; uint32_t * rs_ctrl; long long peer_flag[7];
 };
 // one warp: tell every peer "my slice of the op is in your memory" (release, system scope), then wait for theirs
 cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr /* [npeers] */,
                                      const int * peer_rank /* [npeers] */, cudaStream_t st);
+// wait half only (the GEMV signalled): one warp, programmatic dependent launch, spins on the peers' flags while the GEMV
+// before it still runs, then waits for that GEMV's completion
+cudaError_t launch_rowsplit_wait(uint32_t * local_flags, uint32_t * counter, int npeers, const int * peer_rank, cudaStream_t st);
 // fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
 cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
 bool gemv_pdl_enabled();

@@ -106,6 +106,24 @@ gemv4_kernel(const GemvArgs a) {
                 if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
             }
         }
+        // gpu-scope fence + the gpu-scope arrive below order this thread's peer stores before the last CTA's system-scope
+        // release (PTX causality order is transitive over scopes); a system fence here costs an NVLink round trip per CTA
+        if (a.rs_signal) __threadfence();
+    }
+    if (a.rs_signal) {
+        // last-CTA pattern: when every CTA of the launch has arrived, one thread tells the peers the op is complete
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned prev = atomicAdd(a.rs_ctrl, 1u);
+            if (prev == gridDim.x - 1) {
+                a.rs_ctrl[0] = 0;
+                __threadfence_system();
+                const uint32_t n = a.rs_ctrl[1] + 1;
+                a.rs_ctrl[1] = n;
+                for (int pi = 0; pi < a.npeers; pi++)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag[pi]), "r"(n) : "memory");
+            }
+        }
     }
 }
 

@@ -336,14 +336,25 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
         const char * p = (const char *) dsts[i];
         if (p < c->rs_heap + 4096 || p + bytes[i] > c->rs_heap + c->rs_heap_bytes) return fail(B200_EINVAL, "rowsplit: dst is outside the symmetric heap (b200_rowsplit_heap_create)");
     }
-    for (int r = 0; r < c->world; r++) if (r != c->rank) a.peer_delta[a.npeers++] = (long long) (c->rs_peer[r] - c->rs_heap);
+    for (int r = 0; r < c->world; r++) if (r != c->rank) {
+        a.peer_flag[a.npeers] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank);
+        a.peer_delta[a.npeers++] = (long long) (c->rs_peer[r] - c->rs_heap);
+    }
+    // default: a separate 32-thread exchange kernel after the GEMV (signal + wait).  B200_RS_INLINE=1: the GEMV's last CTA
+    // signals (heap + 260: CTA arrivals, + 264: ops signalled) and a PDL wait kernel follows -- measured SLOWER on 2 GPUs
+    // (9.2 vs 7.6 ms per Llama-3-70B token: the per-CTA fences wait for NVLink store acknowledgements), kept for study
+    static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
+    a.rs_signal = sep ? 0 : 1; a.rs_ctrl = (uint32_t *) (c->rs_heap + 260);
     return 0;
 }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
     long long addr[7]; int ranks[7]; int np = 0;
     for (int r = 0; r < c->world; r++) if (r != c->rank) { addr[np] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank); ranks[np] = r; np++; }
-    CU(launch_rowsplit_exchange((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, addr, ranks, c->st)); c->launches++;
+    static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
+    if (sep) { CU(launch_rowsplit_exchange((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, addr, ranks, c->st)); }
+    else     { CU(launch_rowsplit_wait((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, ranks, c->st)); }
+    c->launches++;
     return 0;
 }
 
@@ -409,8 +420,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 }
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
                 { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; rc = rs_fill(c, a, dp, db_, 1); if (rc) return rc; }
+                const int rs_signal = a.rs_signal;
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
+                    a.rs_signal = (c0 + 8 >= N && i12 == s1->ne[2] - 1 && i13 == s1->ne[3] - 1) ? rs_signal : 0;   // once per op
                     a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
                     a.mat[0].dst = y + c0 * dcs;
                     CU(launch_gemv2(s0->type, a, nc, false, c->st)); c->launches++;
