@@ -26,7 +26,9 @@ namespace b200 {
 
 // ITERS > 1: the row has more than 32*nwarps steps; warp w then owns slices w, w+nwarps, ... and the fragments of the
 // next slice are requested before the current one is consumed (DB = register double buffer).
-template <int TYPE, int NCOLS, int R, bool DB>
+// FQ: the activations are the f32 vector itself; every lane quantises the q8_1 block(s) of its own step (wtypes.cuh),
+// which removes the separate quantise launch (and its dependency latency) in front of every decode GEMV.
+template <int TYPE, int NCOLS, int R, bool DB, bool FQ>
 __global__ void __launch_bounds__(512)
 gemv4_kernel(const GemvArgs a) {
     using W = WT<TYPE>;
@@ -74,8 +76,9 @@ gemv4_kernel(const GemvArgs a) {
         }
         #pragma unroll
         for (int c = 0; c < NCOLS; c++) {
-            const ActCol ac(a.act, c);
-            const typename A::Act av = A::load_act(ac, s);
+            typename A::Act av;
+            if constexpr (FQ) av = A::quant_act((const float *) ((const char *) a.x + (int64_t) c * a.x_col_stride), s, 0);
+            else { const ActCol ac(a.act, c); av = A::load_act(ac, s); }
             #pragma unroll
             for (int r = 0; r < R; r++) acc[c][r] += wr_dot<TYPE>(f[r], av, s);
         }
@@ -139,9 +142,9 @@ static const Tune & tune() {
     return t;
 }
 bool gemv_pdl_enabled() { return tune().pdl; }
-bool gemv_fuseq_enabled() { return false; }
+bool gemv_fuseq_enabled() { static const bool on = getenv("B200_FUSEQ") && atoi(getenv("B200_FUSEQ")) != 0; return on; }   // opt-in: measured 2-3x slower (every CTA re-quantises its lanes' blocks)
 
-template <int TYPE, int NCOLS, int R>
+template <int TYPE, int NCOLS, int R, bool FQ = false>
 static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     const int nslices = (a.steps + 31) / 32;
     const int iters = (nslices + 15) / 16;                  // at most 16 warps (512 threads) per CTA
@@ -158,12 +161,12 @@ static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
     // the register double buffer only where it fits without spills (ptxas -v): q4_0 / q8_0, one column
     if constexpr ((TYPE == T_Q4_0 || TYPE == T_Q8_0) && NCOLS == 1) {
-        if (iters > 1) return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, true>, a);
+        if (iters > 1) return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, true, FQ>, a);
     }
-    return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false>, a);
+    return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false, FQ>, a);
 }
 
-template <int TYPE, int NCOLS>
+template <int TYPE, int NCOLS, bool FQ = false>
 static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
     constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
     if constexpr (NCOLS == 1) {
@@ -171,12 +174,12 @@ static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
         int64_t mtot = 0; for (int i = 0; i < a.nmat; i++) mtot += a.mat[i].M;
         const int r = tune().rows > 0 ? tune().rows : (mtot >= 8192 ? 8 : (a.K >= 8192 ? 2 : 4));
         if constexpr (TYPE == T_Q4_0) {
-            if (r == 2) return launch_cfg<TYPE, 1, 2>(a, st, pdl);
-            if (r == 4) return launch_cfg<TYPE, 1, 4>(a, st, pdl);
-            return launch_cfg<TYPE, 1, 8>(a, st, pdl);
+            if (r == 2) return launch_cfg<TYPE, 1, 2, FQ>(a, st, pdl);
+            if (r == 4) return launch_cfg<TYPE, 1, 4, FQ>(a, st, pdl);
+            return launch_cfg<TYPE, 1, 8, FQ>(a, st, pdl);
         } else {
-            if (r == 2) return launch_cfg<TYPE, 1, 2>(a, st, pdl);
-            return launch_cfg<TYPE, 1, 4>(a, st, pdl);
+            if (r == 2) return launch_cfg<TYPE, 1, 2, FQ>(a, st, pdl);
+            return launch_cfg<TYPE, 1, 4, FQ>(a, st, pdl);
         }
     } else if constexpr (NCOLS == 2) {
         return launch_cfg<TYPE, NCOLS, (KQ ? 2 : 4)>(a, st, pdl);
@@ -188,7 +191,8 @@ static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
 }
 
 template <int TYPE>
-static cudaError_t launch_type(GemvArgs & a, int ncols, cudaStream_t st, bool pdl) {
+static cudaError_t launch_type(GemvArgs & a, int ncols, bool fuseq, cudaStream_t st, bool pdl) {
+    if (fuseq) return ncols == 1 ? launch_ncols<TYPE, 1, true>(a, st, pdl) : cudaErrorInvalidValue;
     switch (ncols) {
         case 1: return launch_ncols<TYPE, 1>(a, st, pdl);
         case 2: return launch_ncols<TYPE, 2>(a, st, pdl);
@@ -203,14 +207,13 @@ static cudaError_t launch_type(GemvArgs & a, int ncols, cudaStream_t st, bool pd
 }
 
 cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st) {
-    if (fuseq) return cudaErrorInvalidValue;
     a.steps = (int) (a.K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
     const bool pdl = tune().pdl;
     switch (type) {
-        case T_Q4_0: return launch_type<T_Q4_0>(a, ncols, st, pdl);
-        case T_Q8_0: return launch_type<T_Q8_0>(a, ncols, st, pdl);
-        case T_Q4_K: return launch_type<T_Q4_K>(a, ncols, st, pdl);
-        case T_Q6_K: return launch_type<T_Q6_K>(a, ncols, st, pdl);
+        case T_Q4_0: return launch_type<T_Q4_0>(a, ncols, fuseq, st, pdl);
+        case T_Q8_0: return launch_type<T_Q8_0>(a, ncols, fuseq, st, pdl);
+        case T_Q4_K: return launch_type<T_Q4_K>(a, ncols, fuseq, st, pdl);
+        case T_Q6_K: return launch_type<T_Q6_K>(a, ncols, fuseq, st, pdl);
     }
     return cudaErrorInvalidValue;
 }

@@ -375,7 +375,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     WPtrs wp0{};
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
-    const bool fuseq = q && N <= 2 && gemv_fuseq_enabled();
+    const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
     // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N, development knob)
     static const int gemm_min_n = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : 32;
     const bool use_gemm = q && (s0->type == T_Q8_0 || s0->type == T_Q4_0) && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
