@@ -28,9 +28,10 @@ for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "ggml-hexagon_b200"))
 
 Q4_0 = 2
 METRIC = "tokens/s Llama Q4_0 decode (tg, MUL_MAT+ADD path, batch 1)"
-# dram__bytes_read + dram__bytes_write of one step / 225 MUL_MAT launches, from the ncu --set full capture of the step
-# (profiles/r01_b_ncu_decode_stream_q4_0_llama2_7b.txt: 3 716 608 000 + 16 083 456 B); the per-node kernels read the same bytes
-TRAFFIC_PER_LAUNCH = int((3716608000 + 16083456) / 225)
+# dram__bytes_read + dram__bytes_write of the step's gemv4_kernel launches / 225 MUL_MAT ops (129 grouped launches), from the
+# ncu --set full capture of this bench command (profiles/r01_e_ncu_gemv4_full_llama2_7b.txt: 113.966 MB per layer + the
+# 73.73 MB output matrix) -- equal to the algorithmic bytes within 0.2 %
+TRAFFIC_PER_LAUNCH = int((32 * 113.966e6 + 73.73e6) / 225)
 
 
 # ------------------------------------------------------------------------------------------------ workloads
