@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libb200ops.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "lib", "libb200ops.so")     # B200_LIB: development builds
 
 F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K = 0, 2, 8, 9, 12, 14
 OP_NONE, OP_ADD, OP_MUL_MAT = 0, 2, 27

@@ -147,11 +147,15 @@ cudaError_t launch_decode_stream(const DsStage * prog_dev, int nstages, uint32_t
                                  long long * trace /* development: 4 clocks per (CTA, stage), or nullptr */, cudaStream_t st);
 
 // ---- prefill GEMM on the tensor cores (gemm_i8.cu): int8 tcgen05.mma per 32-element block, fp32 scale-accumulate
-cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, cudaStream_t st);
+// mode 0: q [N][K], dB [K/32][ldb];  1: + d * isum in [K/32][ldb] behind dB (q4_K);  2: 16-element groups spread to 32-byte
+// blocks, q [N][2K], dB [K/16][ldb] (q6_K)
+cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, int mode, cudaStream_t st);
 cudaError_t launch_unpack_q4_0_i8(const void * qs, long long nblocks, int8_t * out, cudaStream_t st);
+cudaError_t launch_unpack_q4_K_i8(const WPtrs & w, long long nsuper, int8_t * out, float * wS, float * wM, cudaStream_t st);
+cudaError_t launch_unpack_q6_K_i8(const WPtrs & w, long long nsuper, int8_t * out, float * wS, cudaStream_t st);
 int gemm_i8_ldb(int N);
-cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA, const int8_t * B, const float * dB, long long ldb,
-                           float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st);
+cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA_h, const float * dA_f, const float * mA, const int8_t * B, const float * dB,
+                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st);
 
 struct AddArgs {
     const char * a; const char * b; char * d;

@@ -30,16 +30,18 @@ constexpr int GM_NBUF = 4;                                  // TMEM accumulator 
 constexpr int GM_EPI_WARPS = 16;                           // 4 TMEM lane quarters x 4 column groups of 32
 constexpr int GM_THREADS = 64 + GM_EPI_WARPS * 32;
 constexpr int GM_STAGE_A = GM_BM * GM_BK, GM_STAGE_B = GM_BN * GM_BK;
-constexpr int GM_STAGE_S = 4 * GM_BN * 4;                   // activation block scales of a stage: 4 blocks x 128 columns f32
+constexpr int GM_STAGE_S1 = 4 * GM_BN * 4;                  // activation block scales of a stage: 4 blocks x 128 columns f32
 constexpr int GM_OFF_A = 0, GM_OFF_B = GM_STAGES * GM_STAGE_A, GM_OFF_S = GM_OFF_B + GM_STAGES * GM_STAGE_B;
-constexpr int GM_OFF_BAR = GM_OFF_S + GM_STAGES * GM_STAGE_S;
-constexpr int GM_SMEM = GM_OFF_BAR + 256 + 1024;            // + barriers + slack to align the base to 1024 B
-static_assert(GM_SMEM <= 232448, "shared memory");
+// HASMIN (q4_K): a second scale tile per stage, d_a * isum_a, for the block-minimum term
+__host__ __device__ constexpr int gm_stage_s(bool hasmin) { return (hasmin ? 2 : 1) * GM_STAGE_S1; }
+__host__ __device__ constexpr int gm_off_bar(bool hasmin) { return GM_OFF_S + GM_STAGES * gm_stage_s(hasmin); }
+__host__ __device__ constexpr int gm_smem(bool hasmin)    { return gm_off_bar(hasmin) + 256 + 1024; }   // + barriers + slack to align the base to 1024 B
+static_assert(gm_smem(true) <= 232448, "shared memory");
 constexpr long long GM_TIMEOUT_CYCLES = 8000000000ll;
 
 struct GemmI8Args {
-    const __half * dA; long long dA_stride;     // weight block scales [M][dA_stride] (fp16)
-    const float *  dB; long long dB_stride;     // activation block scales [K/32][dB_stride] (f32), dB_stride >= ntiles * 128
+    const void *  dA; long long dA_stride;      // weight block scales [M][dA_stride]: fp16 (WS = 0) or f32 (WS = 1)
+    const float * mA;                           // HASMIN: -(dmin * m_b) per weight block, f32 [M][dA_stride]
     float * out; long long out_cs;              // dst[n * out_cs + m]
     int M, N, K;
     int mtiles, ntiles;
@@ -96,9 +98,13 @@ __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, int (&v)[32]) {
 __device__ __forceinline__ void gm_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------------ kernel
+// WS: weight block scales are fp16 (0: q8_0 / q4_0, read where they lie in HBM) or f32 (1: products d * sc of the K-quants)
+// HASMIN: dst also gets sum_b mA[m, b] * sB[b, n] (q4_K: -(dmin * m_b) * (d_a * isum_a), ggml-cpu-quants.c:7535-7590)
+template <int WS, bool HASMIN>
 __global__ void __launch_bounds__(GM_THREADS, 1)
 gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
-               const GemmI8Args p) {
+               const __grid_constant__ CUtensorMap tmS2, const GemmI8Args p) {
+    constexpr int GM_STAGE_S = gm_stage_s(HASMIN), GM_OFF_BAR = gm_off_bar(HASMIN);
     extern __shared__ uint8_t gm_smem_raw[];
     const uint32_t base = (gm_smem_u32(gm_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
     uint8_t * smem = gm_smem_raw + (base - gm_smem_u32(gm_smem_raw));
@@ -130,6 +136,7 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmS) : "memory");
+            if (HASMIN) asm volatile("prefetch.tensormap [%0];" :: "l"(&tmS2) : "memory");
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
                 const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
@@ -141,6 +148,7 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * GM_BK, mt * GM_BM);
                     gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * GM_BK, nt * GM_BN);
                     gm_tma_2d(sS + s * GM_STAGE_S, &tmS, full0 + s * 8, nt * GM_BN, ks * 4);
+                    if (HASMIN) gm_tma_2d(sS + s * GM_STAGE_S + GM_STAGE_S1, &tmS2, full0 + s * 8, nt * GM_BN, ks * 4);
                 }
             }
         }
@@ -172,32 +180,59 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), columns 32 * ((w - 2) / 4) .. +31
         const int q = warp & 3, cg = (warp - 2) >> 2;
         const int m_local = q * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + cg * 32;
         uint32_t bc = 0, it = 0;
         for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
             const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
             const int m = mt * GM_BM + m_local;
-            const __half * dw_row = p.dA + (long long) min(m, p.M - 1) * p.dA_stride;
+            const long long row_off = (long long) min(m, p.M - 1) * p.dA_stride;
             float2 acc[16];
             #pragma unroll
             for (int i = 0; i < 16; i++) acc[i] = make_float2(0.f, 0.f);
-            // weight scales of this row: 4 fp16 (one stage) per 8-byte load, fetched one stage ahead
-            const bool dw_vec = (p.dA_stride & 3) == 0 && ((uintptr_t) p.dA & 7) == 0;     // else (K % 128 != 0): 2-byte loads
-            auto load_dw = [&](int ks) -> uint2 {
-                if (dw_vec) return *(const uint2 *) (dw_row + ks * 4);
-                unsigned short h[4] = {0, 0, 0, 0};
-                for (int j = 0; j < 4 && ks * 4 + j < KB; j++) h[j] = *(const unsigned short *) (dw_row + ks * 4 + j);
-                return make_uint2((uint32_t) h[0] | ((uint32_t) h[1] << 16), (uint32_t) h[2] | ((uint32_t) h[3] << 16));
+            // weight scales of this row: the 4 blocks of one stage per load, fetched one stage ahead
+            const bool dw_vec = (p.dA_stride & 3) == 0 && ((uintptr_t) p.dA & (WS == 0 ? 7 : 15)) == 0;     // else (K % 128 != 0): scalar loads
+            // WS == 0 keeps the prefetched scales as the two packed fp16 pairs they are in HBM (registers are tight)
+            auto load_dw = [&](int ks) -> float4 {
+                if (WS == 0) {
+                    const __half * dw_row = (const __half *) p.dA + row_off;
+                    uint2 u = make_uint2(0u, 0u);
+                    if (dw_vec) u = *(const uint2 *) (dw_row + ks * 4);
+                    else {
+                        unsigned short h[4] = {0, 0, 0, 0};
+                        for (int j = 0; j < 4 && ks * 4 + j < KB; j++) h[j] = *(const unsigned short *) (dw_row + ks * 4 + j);
+                        u = make_uint2((uint32_t) h[0] | ((uint32_t) h[1] << 16), (uint32_t) h[2] | ((uint32_t) h[3] << 16));
+                    }
+                    return make_float4(__uint_as_float(u.x), __uint_as_float(u.y), 0.f, 0.f);
+                } else {
+                    const float * dw_row = (const float *) p.dA + row_off;
+                    if (dw_vec) return *(const float4 *) (dw_row + ks * 4);
+                    float f[4] = {0.f, 0.f, 0.f, 0.f};
+                    for (int j = 0; j < 4 && ks * 4 + j < KB; j++) f[j] = dw_row[ks * 4 + j];
+                    return make_float4(f[0], f[1], f[2], f[3]);
+                }
             };
-            uint2 dwn = load_dw(0);
+            auto cvt_dw = [&](float4 r) -> float4 {
+                if (WS != 0) return r;
+                const uint32_t a = __float_as_uint(r.x), b = __float_as_uint(r.y);
+                const __half2 h01 = *(const __half2 *) &a, h23 = *(const __half2 *) &b;
+                return make_float4(__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23));
+            };
+            auto load_mw = [&](int ks) -> float4 {          // HASMIN only: K-quant rows are always 16-B aligned (K % 256 == 0)
+                return *(const float4 *) (p.mA + row_off + ks * 4);
+            };
+            float4 dwn = load_dw(0), mwn = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (HASMIN) mwn = load_mw(0);
             for (int ks = 0; ks < nks; ks++, it++) {
                 const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
-                const uint2 dwc = dwn;
-                if (ks + 1 < nks) dwn = load_dw(ks + 1);
-                const __half2 h01 = *(const __half2 *) &dwc.x, h23 = *(const __half2 *) &dwc.y;
-                const float dws[4] = {__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23)};
+                const float4 dwc = cvt_dw(dwn), mwc = mwn;
+                if (ks + 1 < nks) { dwn = load_dw(ks + 1); if (HASMIN) mwn = load_mw(ks + 1); }
+                const float dws[4] = {dwc.x, dwc.y, dwc.z, dwc.w};
+                const float mws[4] = {mwc.x, mwc.y, mwc.z, mwc.w};
                 gm_mbar_wait(full0 + s * 8, ph);                            // scales of this stage are in shared memory
                 const float4 * sc = (const float4 *) (smem + GM_OFF_S + s * GM_STAGE_S) + cg * 8;
                 const int nb = min(4, KB - ks * 4);
+                // acc += float(sumi) * (d_w * d_a), as ggml_vec_dot_q8_0_q8_0 does per block (ggml-cpu-quants.c:4004-4012);
+                // |sumi| <= 32 * 127 * 127 < 2^24: the conversion is exact.
                 #pragma unroll
                 for (int j = 0; j < 4; j++) {
                     if (j < nb) {
@@ -205,23 +240,28 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         gm_mbar_wait(tfull0 + buf * 8, bph);
                         gm_fence_after();
                         int v[32];
-                        gm_tmem_ld32(tmem + ((uint32_t) (q * 32) << 16) + buf * GM_BN + cg * 32, v);
+                        gm_tmem_ld32(tbase + buf * GM_BN, v);
                         gm_tmem_ld_wait();
                         gm_fence_before();
                         __syncwarp();
                         if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);  // buffer free for the MMA issuer
                         bc++;
-                        // acc += float(sumi) * (d_w * d_a), as ggml_vec_dot_q8_0_q8_0 does per block (ggml-cpu-quants.c:4004-4012).
-                        // int -> float without the quarter-rate I2F: |sumi| <= 32 * 127 * 127 < 2^22, so
-                        // as_float(0x4B400000 + sumi) == 12582912 + sumi exactly, and subtracting 12582912 is exact too.
-                        const float2 dw2 = make_float2(dws[j], dws[j]), mg = make_float2(-12582912.f, -12582912.f);
+                        const float2 dw2 = make_float2(dws[j], dws[j]);
                         #pragma unroll
                         for (int i = 0; i < 8; i++) {
                             const float4 d = sc[j * (GM_BN / 4) + i];     // activation scales of block j, columns 4i..4i+3 of this group
-                            const float2 f0 = __fadd2_rn(make_float2(__int_as_float(v[4 * i + 0] + 0x4B400000), __int_as_float(v[4 * i + 1] + 0x4B400000)), mg);
-                            const float2 f1 = __fadd2_rn(make_float2(__int_as_float(v[4 * i + 2] + 0x4B400000), __int_as_float(v[4 * i + 3] + 0x4B400000)), mg);
+                            // int -> float on the conversion unit: one issue slot per element.  (The magic-number route, as_float(
+                            // 0x4B400000 + sumi) - 12582912.f, costs 1.5 slots and measured 15 % slower: the loop is issue-bound.)
+                            const float2 f0 = make_float2(__int2float_rn(v[4 * i + 0]), __int2float_rn(v[4 * i + 1]));
+                            const float2 f1 = make_float2(__int2float_rn(v[4 * i + 2]), __int2float_rn(v[4 * i + 3]));
                             acc[2 * i + 0] = __ffma2_rn(f0, __fmul2_rn(dw2, make_float2(d.x, d.y)), acc[2 * i + 0]);
                             acc[2 * i + 1] = __ffma2_rn(f1, __fmul2_rn(dw2, make_float2(d.z, d.w)), acc[2 * i + 1]);
+                            if (HASMIN) {
+                                const float4 sb = sc[GM_STAGE_S1 / 16 + j * (GM_BN / 4) + i];      // d_a * isum_a, same columns
+                                const float2 mw2 = make_float2(mws[j], mws[j]);
+                                acc[2 * i + 0] = __ffma2_rn(mw2, make_float2(sb.x, sb.y), acc[2 * i + 0]);
+                                acc[2 * i + 1] = __ffma2_rn(mw2, make_float2(sb.z, sb.w), acc[2 * i + 1]);
+                            }
                         }
                     }
                 }
@@ -247,6 +287,10 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // Activations for the GEMM: q8_1 quantisation (= quantize_row_q8_1_ref, ggml-quants.c:220-253) into a plain row-major
 // int8 matrix [N][K] (TMA operand B) and block-major scales dB[K/32][ldb] (f32 value of the fp16-rounded d).
 // 8 lanes per 32-element block, one float4 each.
+// MODE 0: as above.  MODE 1 (q4_K weights): also sB[b][row] = d * isum (isum = exact sum of the block's quants), stored
+// KB * ldb floats after dB.  MODE 2 (q6_K weights, scales per 16 elements): every 16-element half block becomes its own
+// 32-byte MMA block [16 quants, 16 zeros] in q [N][2K], dB [K/16][ldb] -- the weights are laid out alike (unpack_q6_K).
+template <int MODE>
 __global__ void __launch_bounds__(256)
 quantize_rows_i8_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N,
                         int8_t * __restrict__ q, float * __restrict__ dB, const long long ldb) {
@@ -265,8 +309,23 @@ quantize_rows_i8_kernel(const char * __restrict__ x, const long long row_stride,
     const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
     const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
     const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
-    *(uint32_t *) (q + (long long) row * K + b * 32 + sub * 4) = packed;
-    if (sub == 0) dB[(long long) b * ldb + row] = __half2float(__float2half_rn(d));
+    const float dh = __half2float(__float2half_rn(d));
+    if (MODE == 2) {
+        const int g = 2 * b + (sub >> 2);
+        uint32_t * o = (uint32_t *) (q + (long long) row * 2 * K + (long long) g * 32 + (sub & 3) * 4);
+        o[0] = packed; o[4] = 0u;
+        if ((sub & 3) == 0) dB[(long long) g * ldb + row] = dh;
+    } else {
+        *(uint32_t *) (q + (long long) row * K + b * 32 + sub * 4) = packed;
+        if (MODE == 1) {
+            int isum = q0 + q1 + q2 + q3;
+            isum += __shfl_xor_sync(0xffffffffu, isum, 1);
+            isum += __shfl_xor_sync(0xffffffffu, isum, 2);
+            isum += __shfl_xor_sync(0xffffffffu, isum, 4);
+            if (sub == 0) dB[((long long) NB + b) * ldb + row] = __fmul_rn(dh, (float) isum);
+        }
+        if (sub == 0) dB[(long long) b * ldb + row] = dh;
+    }
 }
 
 // q4_0 nibbles (SoA quant array, 16 B per block: low nibbles = elements 0..15, high = 16..31, ggml-common.h:167-172)
@@ -289,14 +348,87 @@ unpack_q4_0_i8_kernel(const uint4 * __restrict__ qs, const long long nblocks, in
     }
 }
 
-cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, cudaStream_t st) {
+// q4_K (SoA: qs 128 B + header {f16 d, f16 dmin, 12 B packed 6-bit scales/mins} per 256-element super-block,
+// ggml-common.h:285-296; nibble order and get_scale_min_k4 as dequantize_row_q4_K, ggml-quants.c:1352-1374)
+// -> A int8 [M][K] = the raw 4-bit quants 0..15, wS f32 = d * sc_g, wM f32 = -(dmin * m_g) per 32-element sub-block g.
+// One thread per 64 elements (one 32-byte run: low nibbles = sub-block 2j, high nibbles = sub-block 2j + 1).
+__global__ void __launch_bounds__(256)
+unpack_q4_K_kernel(const uint4 * __restrict__ qs, const uint4 * __restrict__ hdr, const long long nsuper,
+                   int8_t * __restrict__ out, float * __restrict__ wS, float * __restrict__ wM) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 4; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 2; const int j = (int) (i & 3);
+        const uint4 v0 = qs[sb * 8 + 2 * j], v1 = qs[sb * 8 + 2 * j + 1];
+        uint4 * o = (uint4 *) (out + sb * 256 + j * 64);
+        o[0] = make_uint4(v0.x & 0x0F0F0F0Fu, v0.y & 0x0F0F0F0Fu, v0.z & 0x0F0F0F0Fu, v0.w & 0x0F0F0F0Fu);
+        o[1] = make_uint4(v1.x & 0x0F0F0F0Fu, v1.y & 0x0F0F0F0Fu, v1.z & 0x0F0F0F0Fu, v1.w & 0x0F0F0F0Fu);
+        o[2] = make_uint4((v0.x >> 4) & 0x0F0F0F0Fu, (v0.y >> 4) & 0x0F0F0F0Fu, (v0.z >> 4) & 0x0F0F0F0Fu, (v0.w >> 4) & 0x0F0F0F0Fu);
+        o[3] = make_uint4((v1.x >> 4) & 0x0F0F0F0Fu, (v1.y >> 4) & 0x0F0F0F0Fu, (v1.z >> 4) & 0x0F0F0F0Fu, (v1.w >> 4) & 0x0F0F0F0Fu);
+        const uint4 h = hdr[sb];
+        const __half2 dd = *(const __half2 *) &h.x;
+        const float d = __low2float(dd), dmin = __high2float(dd);
+        const uint32_t w[3] = {h.y, h.z, h.w};
+        auto byte = [&](int k) -> uint32_t { return (w[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
+        #pragma unroll
+        for (int e = 0; e < 2; e++) {
+            const int g = 2 * j + e;
+            uint32_t sc, mn;
+            if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
+            else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
+            wS[sb * 8 + g] = __fmul_rn(d, (float) sc);
+            wM[sb * 8 + g] = -__fmul_rn(dmin, (float) mn);
+        }
+    }
+}
+
+// q6_K (SoA: ql 128 B, qh 64 B, 16 int8 scales, f16 d per super-block, ggml-common.h:320-326; bit layout as
+// dequantize_row_q6_K, ggml-quants.c:1681-1710) -> A int8 [M][2K]: each 16-element scale group g becomes one 32-byte MMA block
+// [16 x (q - 32), 16 x 0]; wS f32 [M][K/16] = d * sc_g.  16 threads per super-block: thread t handles l = 4 (t & 7) .. +3
+// of half (t >> 3) (4 quants for each of the 4 rows of the bit layout) and writes scale t.
+__global__ void __launch_bounds__(256)
+unpack_q6_K_kernel(const uint32_t * __restrict__ ql, const uint32_t * __restrict__ qh, const int8_t * __restrict__ sc,
+                   const __half * __restrict__ dd, const long long nsuper, int8_t * __restrict__ out, float * __restrict__ wS) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 16; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 4; const int t = (int) (i & 15), half = t >> 3, l4 = t & 7;
+        const uint32_t a = ql[sb * 32 + half * 16 + l4], b = ql[sb * 32 + half * 16 + 8 + l4], h = qh[sb * 16 + half * 8 + l4];
+        const uint32_t v[4] = {
+            (a & 0x0F0F0F0Fu)        | ((h << 4) & 0x30303030u),
+            (b & 0x0F0F0F0Fu)        | ((h << 2) & 0x30303030u),
+            ((a >> 4) & 0x0F0F0F0Fu) | ( h       & 0x30303030u),
+            ((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)};
+        #pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int e = half * 128 + r * 32 + l4 * 4;          // element index inside the super-block
+            const int g = e >> 4;
+            uint32_t * o = (uint32_t *) (out + (sb * 16 + g) * 32 + (e & 15));
+            o[0] = __vsub4(v[r], 0x20202020u);
+            o[4] = 0u;
+        }
+        wS[sb * 16 + t] = __fmul_rn(__half2float(dd[sb]), (float) sc[sb * 16 + t]);
+    }
+}
+
+cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, int mode, cudaStream_t st) {
     const long long threads = (long long) (K / 4) * N;
-    quantize_rows_i8_kernel<<<(unsigned) ((threads + 255) / 256), 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    const unsigned grid = (unsigned) ((threads + 255) / 256);
+    if (mode == 0)      quantize_rows_i8_kernel<0><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    else if (mode == 1) quantize_rows_i8_kernel<1><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    else                quantize_rows_i8_kernel<2><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
     return cudaGetLastError();
 }
 cudaError_t launch_unpack_q4_0_i8(const void * qs, long long nblocks, int8_t * out, cudaStream_t st) {
     long long blocks = (nblocks + 255) / 256; if (blocks > 148 * 32) blocks = 148 * 32;
     unpack_q4_0_i8_kernel<<<(unsigned) blocks, 256, 0, st>>>((const uint4 *) qs, nblocks, out);
+    return cudaGetLastError();
+}
+cudaError_t launch_unpack_q4_K_i8(const WPtrs & w, long long nsuper, int8_t * out, float * wS, float * wM, cudaStream_t st) {
+    long long blocks = (nsuper * 4 + 255) / 256; if (blocks > 148 * 32) blocks = 148 * 32;
+    unpack_q4_K_kernel<<<(unsigned) blocks, 256, 0, st>>>((const uint4 *) w.p[0], (const uint4 *) w.p[1], nsuper, out, wS, wM);
+    return cudaGetLastError();
+}
+cudaError_t launch_unpack_q6_K_i8(const WPtrs & w, long long nsuper, int8_t * out, float * wS, cudaStream_t st) {
+    long long blocks = (nsuper * 16 + 255) / 256; if (blocks > 148 * 32) blocks = 148 * 32;
+    unpack_q6_K_kernel<<<(unsigned) blocks, 256, 0, st>>>((const uint32_t *) w.p[0], (const uint32_t *) w.p[1], (const int8_t *) w.p[2],
+                                                           (const __half *) w.p[3], nsuper, out, wS);
     return cudaGetLastError();
 }
 
@@ -339,24 +471,37 @@ static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, lo
 
 int gemm_i8_ldb(int N) { return (N + GM_BN - 1) / GM_BN * GM_BN; }      // leading dimension the caller must give dB
 
-// A: int8 [M][K] (16-B aligned, K % 16 == 0), dA: fp16 [M][K/32]; B: int8 [N][K], dB: f32 [K/32][ldb]; out[n * out_cs + m]
-cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA, const int8_t * B, const float * dB, long long ldb,
-                           float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st) {
+// A: int8 [M][K] (16-B aligned, K % 16 == 0); dA_h: fp16 [M][K/32] or dA_f: f32 [M][K/32] (exactly one); mA: f32 [M][K/32] or
+// nullptr; B: int8 [N][K], dB: f32 [K/32][ldb] (+ [K/32][ldb] of d * isum behind it when mA is given); out[n * out_cs + m].
+// K is the MMA-side contraction length (2 x the tensor's for q6_K).
+template <int WS, bool HASMIN>
+static cudaError_t gemm_i8_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const CUtensorMap & tmS, const CUtensorMap & tmS2,
+                                    const GemmI8Args & p, int grid, cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, HASMIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gm_smem(HASMIN));
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    CUtensorMap tmA, tmB, tmS;
-    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K) || !make_map_scales(&tmS, dB, K / 32, ldb)) return cudaErrorInvalidValue;
+    gemm_i8_kernel<WS, HASMIN><<<(unsigned) grid, GM_THREADS, gm_smem(HASMIN), st>>>(tmA, tmB, tmS, tmS2, p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA_h, const float * dA_f, const float * mA, const int8_t * B, const float * dB,
+                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st) {
+    CUtensorMap tmA, tmB, tmS, tmS2;
+    const long long KB = K / 32;
+    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K) || !make_map_scales(&tmS, dB, KB, ldb)) return cudaErrorInvalidValue;
+    if (!make_map_scales(&tmS2, mA ? dB + KB * ldb : dB, KB, ldb)) return cudaErrorInvalidValue;
     GemmI8Args p{};
-    p.dA = dA; p.dA_stride = K / 32; p.dB = dB; p.dB_stride = ldb; p.out = out; p.out_cs = out_cs;
+    p.dA = dA_h ? (const void *) dA_h : (const void *) dA_f; p.dA_stride = KB; p.mA = mA; p.out = out; p.out_cs = out_cs;
     p.M = M; p.N = N; p.K = K;
     p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + GM_BN - 1) / GM_BN;
     const int tiles = p.mtiles * p.ntiles;
-    gemm_i8_kernel<<<(unsigned) (tiles < sms ? tiles : sms), GM_THREADS, GM_SMEM, st>>>(tmA, tmB, tmS, p);
-    return cudaGetLastError();
+    const int grid = tiles < sms ? tiles : sms;
+    if (dA_h)    return gemm_i8_launch_t<0, false>(tmA, tmB, tmS, tmS2, p, grid, st);
+    if (mA)      return gemm_i8_launch_t<1, true >(tmA, tmB, tmS, tmS2, p, grid, st);
+    return gemm_i8_launch_t<1, false>(tmA, tmB, tmS, tmS2, p, grid, st);
 }
 
 }  // namespace b200

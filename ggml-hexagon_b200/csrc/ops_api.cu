@@ -83,6 +83,7 @@ struct Ctx {
     int8_t * gm_qb = nullptr; size_t gm_qb_cap = 0;
     float *  gm_db = nullptr; size_t gm_db_cap = 0;
     int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;
+    float *  gm_ws = nullptr; size_t gm_ws_cap = 0;      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
@@ -180,7 +181,7 @@ extern "C" int b200_close(b200_handle h) {
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
-    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a);
+    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws);
     cudaStreamDestroy(c->st);
     c->magic = 0;
     delete c;
@@ -378,7 +379,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
     // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N, development knob)
     static const int gemm_min_n = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : 32;
-    const bool use_gemm = q && (s0->type == T_Q8_0 || s0->type == T_Q4_0) && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
+    const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
                           M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 && !c->rs_on;
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
@@ -391,16 +392,29 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             // ---- many columns: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
             const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
             const long long ldb = gemm_i8_ldb((int) N);
-            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K); if (rc) return rc;
-            rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) NB * ldb * sizeof(float)); if (rc) return rc;
-            CU(launch_quantize_rows_i8((const float *) x, s1->nb[1], (int) K, (int) N, c->gm_qb, c->gm_db, ldb, c->st)); c->launches++;
+            // MMA-side shape: q6_K scales change every 16 elements, so each 16-group is padded to its own 32-byte block (K doubles)
+            const int t = s0->type;
+            const long long Kg = t == T_Q6_K ? 2 * K : K, KBg = Kg / 32;
+            const int qmode = t == T_Q4_K ? 1 : t == T_Q6_K ? 2 : 0;
+            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * Kg); if (rc) return rc;
+            rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) (qmode == 1 ? 2 : 1) * KBg * ldb * sizeof(float)); if (rc) return rc;
+            CU(launch_quantize_rows_i8((const float *) x, s1->nb[1], (int) K, (int) N, c->gm_qb, c->gm_db, ldb, qmode, c->st)); c->launches++;
             const int8_t * A = (const int8_t *) wp.p[0];
-            if (s0->type == T_Q4_0) {
-                rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K); if (rc) return rc;
+            const __half * dA_h = t == T_Q8_0 || t == T_Q4_0 ? (const __half *) wp.p[1] : nullptr;
+            const float * dA_f = nullptr, * mA = nullptr;
+            if (t != T_Q8_0) { rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * Kg); if (rc) return rc; A = c->gm_a; }
+            if (t == T_Q4_0) {
                 CU(launch_unpack_q4_0_i8(wp.p[0], M * NB, c->gm_a, c->st)); c->launches++;
-                A = c->gm_a;
+            } else if (t == T_Q4_K) {
+                rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) 2 * M * KBg * sizeof(float)); if (rc) return rc;
+                dA_f = c->gm_ws; mA = c->gm_ws + M * KBg;
+                CU(launch_unpack_q4_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->gm_ws + M * KBg, c->st)); c->launches++;
+            } else if (t == T_Q6_K) {
+                rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) M * KBg * sizeof(float)); if (rc) return rc;
+                dA_f = c->gm_ws;
+                CU(launch_unpack_q6_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->st)); c->launches++;
             }
-            CU(launch_gemm_i8(A, (const __half *) wp.p[1], c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) K, c->sms, c->st)); c->launches++;
+            CU(launch_gemm_i8(A, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) Kg, c->sms, c->st)); c->launches++;
             c->q_ptr = nullptr;
         } else if (q) {
             GemvArgs a{};

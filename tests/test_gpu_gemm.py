@@ -37,6 +37,36 @@ def test_gemm_vs_oracle(sess, t, name, M, K, N):
     w.free()
 
 
+@pytest.mark.parametrize("t,name", [(O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")])
+@pytest.mark.parametrize("M,K,N", [(128, 256, 128), (16, 256, 32), (200, 1024, 77), (384, 4096, 512), (130, 512, 33), (257, 11008, 129)])
+def test_gemm_kquants_vs_oracle(sess, t, name, M, K, N):
+    """K-quants through the same tensor-core kernel: q4_K as 32-element sub-blocks with f32 scales d*sc and the block-minimum
+    term folded into the epilogue, q6_K with every 16-element scale group padded to its own 32-byte MMA block"""
+    rng = np.random.default_rng(M + 3 * K + 7 * N + t)
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = sess.mulmat(w, x)
+    assert got.shape == (N, M)
+    ref1 = O.mul_mat(t, raw, x, 1)
+    assert nmse(got, ref1) <= 1e-10, (name, M, K, N, nmse(got, ref1))
+    assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
+    w.free()
+
+
+@pytest.mark.parametrize("t", [O.Q4_K, O.Q6_K])
+def test_gemm_kquants_match_gemv_columns(sess, t):
+    rng = np.random.default_rng(5 + t)
+    M, K, N = 256, 2048, 40
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    big = sess.mulmat(w, x)
+    small = np.concatenate([sess.mulmat(w, x[i:i + 8]) for i in range(0, N, 8)])
+    assert nmse(big, small) <= 1e-10
+    w.free()
+
+
 def test_gemm_matches_gemv_columns(sess):
     """the same matrix through the GEMV (8 columns at a time) and through the GEMM: same integers, same scales"""
     rng = np.random.default_rng(3)

@@ -10,13 +10,19 @@ import pyoracle as O
 
 def main():
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 512
-    types = [(O.Q8_0, "q8_0"), (O.Q4_0, "q4_0")]
-    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (4096, 14336)]
+    types = [(O.Q8_0, "q8_0"), (O.Q4_0, "q4_0"), (O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")]
+    if len(sys.argv) > 2:
+        types = [x for x in types if x[1] in sys.argv[2].split(",")]
+    shapes = [(4096, 4096), (11008, 4096), (4096, 11008), (14336, 4096), (4096, 14336)]
+    if len(sys.argv) > 3:
+        shapes = shapes[:int(sys.argv[3])]
     rng = np.random.default_rng(0)
     out = []
     with B.Session(0) as s:
         for t, name in types:
             for M, K in shapes:
+                if K % 256 and t in (O.Q4_K, O.Q6_K):
+                    continue
                 raw = O.random_blocks(t, 128, K, rng)
                 raw = np.tile(raw, (M // 128, 1))
                 w = s.weights(t, raw, K)
