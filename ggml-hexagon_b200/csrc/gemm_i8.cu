@@ -24,7 +24,19 @@
 
 namespace b200 {
 
-constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 128;        // tile; BK in int8 elements = bytes = one 128-B swizzle row
+// KIND selects the tensor-core data path of one exact block sum:
+//   0  kind::i8  : int8 operands, s32 sums; one M128 x N128 x K32 MMA per 32-element block; the epilogue converts s32 -> f32
+//   1  kind::f16 : the SAME integers stored as fp16 (|q| <= 127 is exact), f32 sums (every partial sum is an integer below 2^24,
+//                  so the f32 accumulation is exact too); two K16 MMAs per 32-element block; no conversion in the epilogue
+//   2  kind::f16 with 16-element blocks (q6_K: one scale per 16 weights): one K16 MMA per block, no zero padding
+// Measured on B200 (4096 x 4096 x 512, q8_0): kind 0 is bound by the epilogue's issue slots (60.8 us; 32 us
+// with the math removed = the TMA/L2 feed of 128 MB at 4 TB/s); kind 1 drops the 32 conversions per block and warp but doubles
+// the operand bytes and lands on the TMA/L2 feed instead (60.9 us + 12 us more preparation).  So kind 0 is the default for the
+// 32-element-block types and kind 2 for q6_K, where it saves the zero padding of kind 0 (119 vs 140 us).
+constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 128;        // tile; BK = bytes of K per stage and row = one 128-B swizzle row
+__host__ __device__ constexpr int gm_bps(int kind) { return kind == 1 ? 2 : 4; }      // blocks per stage
+__host__ __device__ constexpr int gm_kpb(int kind) { return kind == 2 ? 16 : 32; }    // K elements per block
+__host__ __device__ constexpr int gm_mpb(int kind) { return kind == 1 ? 2 : 1; }      // MMA instructions per block
 constexpr int GM_STAGES = 6;
 constexpr int GM_NBUF = 4;                                  // TMEM accumulator buffers of GM_BN columns
 constexpr int GM_EPI_WARPS = 16;                           // 4 TMEM lane quarters x 4 column groups of 32
@@ -81,6 +93,10 @@ __device__ __forceinline__ void gm_mma_i8(uint32_t tmem_d, uint64_t adesc, uint6
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
                  :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void gm_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void gm_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
@@ -100,11 +116,13 @@ __device__ __forceinline__ void gm_tmem_ld_wait() { asm volatile("tcgen05.wait::
 // ------------------------------------------------------------------------------------------------ kernel
 // WS: weight block scales are fp16 (0: q8_0 / q4_0, read where they lie in HBM) or f32 (1: products d * sc of the K-quants)
 // HASMIN: dst also gets sum_b mA[m, b] * sB[b, n] (q4_K: -(dmin * m_b) * (d_a * isum_a), ggml-cpu-quants.c:7535-7590)
-template <int WS, bool HASMIN>
+template <int WS, bool HASMIN, int KIND>
 __global__ void __launch_bounds__(GM_THREADS, 1)
 gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
                const __grid_constant__ CUtensorMap tmS2, const GemmI8Args p) {
     constexpr int GM_STAGE_S = gm_stage_s(HASMIN), GM_OFF_BAR = gm_off_bar(HASMIN);
+    constexpr int BPS = gm_bps(KIND), KPB = gm_kpb(KIND), MPB = gm_mpb(KIND), KSTAGE = BPS * KPB;      // KSTAGE: K elements per stage
+    constexpr uint32_t TX_S = (HASMIN ? 2u : 1u) * BPS * GM_BN * 4u;                                   // scale bytes per stage
     extern __shared__ uint8_t gm_smem_raw[];
     const uint32_t base = (gm_smem_u32(gm_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
     uint8_t * smem = gm_smem_raw + (base - gm_smem_u32(gm_smem_raw));
@@ -114,7 +132,7 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t tfull0 = bars + 3 * GM_STAGES * 8, tempty0 = tfull0 + GM_NBUF * 8;
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + GM_OFF_BAR + 3 * GM_STAGES * 8 + 2 * GM_NBUF * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nks = (p.K + GM_BK - 1) / GM_BK, KB = p.K / 32, ntiles_total = p.mtiles * p.ntiles;
+    const int nks = (p.K + KSTAGE - 1) / KSTAGE, KB = p.K / KPB, ntiles_total = p.mtiles * p.ntiles;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(sempty0 + i * 8, GM_EPI_WARPS); }
@@ -144,32 +162,39 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
                     gm_mbar_wait(sempty0 + s * 8, ph ^ 1);
-                    gm_mbar_expect_tx(full0 + s * 8, GM_STAGE_A + GM_STAGE_B + GM_STAGE_S);
-                    gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * GM_BK, mt * GM_BM);
-                    gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * GM_BK, nt * GM_BN);
-                    gm_tma_2d(sS + s * GM_STAGE_S, &tmS, full0 + s * 8, nt * GM_BN, ks * 4);
-                    if (HASMIN) gm_tma_2d(sS + s * GM_STAGE_S + GM_STAGE_S1, &tmS2, full0 + s * 8, nt * GM_BN, ks * 4);
+                    gm_mbar_expect_tx(full0 + s * 8, GM_STAGE_A + GM_STAGE_B + TX_S);
+                    gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * KSTAGE, mt * GM_BM);
+                    gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * KSTAGE, nt * GM_BN);
+                    gm_tma_2d(sS + s * GM_STAGE_S, &tmS, full0 + s * 8, nt * GM_BN, ks * BPS);
+                    if (HASMIN) gm_tma_2d(sS + s * GM_STAGE_S + GM_STAGE_S1, &tmS2, full0 + s * 8, nt * GM_BN, ks * BPS);
                 }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer: one lane, one tcgen05.mma per 32-element block, each into its own accumulator buffer
         if (lane == 0) {
-            // instruction descriptor: D = s32, A = B = signed int8, both K-major, N = 128, M = 128
-            const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t) (GM_BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
+            // instruction descriptor: D format (bits 4-5: 1 = f32, 2 = s32), A / B format (bits 7-9 / 10-12: kind::i8 1 = s8,
+            // kind::f16 0 = fp16), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+            const uint32_t idesc = (KIND == 0 ? (2u << 4) | (1u << 7) | (1u << 10) : (1u << 4)) |
+                                   ((uint32_t) (GM_BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
             uint32_t it = 0, bc = 0;
             for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
                 for (int ks = 0; ks < nks; ks++, it++) {
                     const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
                     gm_mbar_wait(full0 + s * 8, ph);
                     gm_fence_after();
-                    const int nb = min(4, KB - ks * 4);
+                    const int nb = min(BPS, KB - ks * BPS);
                     for (int j = 0; j < nb; j++, bc++) {
                         const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
                         gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
                         gm_fence_after();
-                        const uint64_t ad = gm_smem_desc(sA + s * GM_STAGE_A + j * 32), bd = gm_smem_desc(sB + s * GM_STAGE_B + j * 32);
-                        gm_mma_i8(tmem + buf * GM_BN, ad, bd, idesc, 0u);
+                        #pragma unroll
+                        for (int mm = 0; mm < MPB; mm++) {        // every MMA consumes 32 bytes of K per row (32 int8 or 16 fp16)
+                            const uint32_t off = (uint32_t) (j * MPB + mm) * 32u;
+                            const uint64_t ad = gm_smem_desc(sA + s * GM_STAGE_A + off), bd = gm_smem_desc(sB + s * GM_STAGE_B + off);
+                            if (KIND == 0) gm_mma_i8(tmem + buf * GM_BN, ad, bd, idesc, 0u);
+                            else           gm_mma_f16(tmem + buf * GM_BN, ad, bd, idesc, mm == 0 ? 0u : 1u);
+                        }
                         gm_commit(tfull0 + buf * 8);          // arrives when this block's sums are in TMEM
                     }
                     gm_commit(empty0 + s * 8);                // arrives when the stage's MMAs have read shared memory
@@ -189,27 +214,36 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             float2 acc[16];
             #pragma unroll
             for (int i = 0; i < 16; i++) acc[i] = make_float2(0.f, 0.f);
-            // weight scales of this row: the 4 blocks of one stage per load, fetched one stage ahead
-            const bool dw_vec = (p.dA_stride & 3) == 0 && ((uintptr_t) p.dA & (WS == 0 ? 7 : 15)) == 0;     // else (K % 128 != 0): scalar loads
-            // WS == 0 keeps the prefetched scales as the two packed fp16 pairs they are in HBM (registers are tight)
+            // weight scales of this row: the BPS blocks of one stage per load, fetched one stage ahead.  WS == 0 keeps them as
+            // the packed fp16 they are in HBM until use (registers are tight).
+            constexpr int DWB = BPS * (WS == 0 ? 2 : 4);                                  // bytes of weight scales per stage and row
+            const bool dw_vec = (p.dA_stride % BPS) == 0 && ((uintptr_t) p.dA % DWB) == 0;     // else (ragged K): scalar loads
             auto load_dw = [&](int ks) -> float4 {
+                float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (WS == 0) {
-                    const __half * dw_row = (const __half *) p.dA + row_off;
-                    uint2 u = make_uint2(0u, 0u);
-                    if (dw_vec) u = *(const uint2 *) (dw_row + ks * 4);
-                    else {
+                    const __half * dw_row = (const __half *) p.dA + row_off + ks * BPS;
+                    uint32_t u[2] = {0u, 0u};
+                    if (dw_vec) {
+                        if (BPS == 4) { const uint2 t = *(const uint2 *) dw_row; u[0] = t.x; u[1] = t.y; }
+                        else          u[0] = *(const uint32_t *) dw_row;
+                    } else {
                         unsigned short h[4] = {0, 0, 0, 0};
-                        for (int j = 0; j < 4 && ks * 4 + j < KB; j++) h[j] = *(const unsigned short *) (dw_row + ks * 4 + j);
-                        u = make_uint2((uint32_t) h[0] | ((uint32_t) h[1] << 16), (uint32_t) h[2] | ((uint32_t) h[3] << 16));
+                        for (int j = 0; j < BPS && ks * BPS + j < KB; j++) h[j] = *(const unsigned short *) (dw_row + j);
+                        u[0] = (uint32_t) h[0] | ((uint32_t) h[1] << 16); u[1] = (uint32_t) h[2] | ((uint32_t) h[3] << 16);
                     }
-                    return make_float4(__uint_as_float(u.x), __uint_as_float(u.y), 0.f, 0.f);
+                    r.x = __uint_as_float(u[0]); r.y = __uint_as_float(u[1]);
                 } else {
-                    const float * dw_row = (const float *) p.dA + row_off;
-                    if (dw_vec) return *(const float4 *) (dw_row + ks * 4);
-                    float f[4] = {0.f, 0.f, 0.f, 0.f};
-                    for (int j = 0; j < 4 && ks * 4 + j < KB; j++) f[j] = dw_row[ks * 4 + j];
-                    return make_float4(f[0], f[1], f[2], f[3]);
+                    const float * dw_row = (const float *) p.dA + row_off + ks * BPS;
+                    if (dw_vec) {
+                        if (BPS == 4) r = *(const float4 *) dw_row;
+                        else { const float2 t = *(const float2 *) dw_row; r.x = t.x; r.y = t.y; }
+                    } else {
+                        float f[4] = {0.f, 0.f, 0.f, 0.f};
+                        for (int j = 0; j < BPS && ks * BPS + j < KB; j++) f[j] = dw_row[j];
+                        r = make_float4(f[0], f[1], f[2], f[3]);
+                    }
                 }
+                return r;
             };
             auto cvt_dw = [&](float4 r) -> float4 {
                 if (WS != 0) return r;
@@ -218,7 +252,10 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 return make_float4(__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23));
             };
             auto load_mw = [&](int ks) -> float4 {          // HASMIN only: K-quant rows are always 16-B aligned (K % 256 == 0)
-                return *(const float4 *) (p.mA + row_off + ks * 4);
+                const float * mw_row = p.mA + row_off + ks * BPS;
+                if (BPS == 4) return *(const float4 *) mw_row;
+                const float2 t = *(const float2 *) mw_row;
+                return make_float4(t.x, t.y, 0.f, 0.f);
             };
             float4 dwn = load_dw(0), mwn = make_float4(0.f, 0.f, 0.f, 0.f);
             if (HASMIN) mwn = load_mw(0);
@@ -230,11 +267,11 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const float mws[4] = {mwc.x, mwc.y, mwc.z, mwc.w};
                 gm_mbar_wait(full0 + s * 8, ph);                            // scales of this stage are in shared memory
                 const float4 * sc = (const float4 *) (smem + GM_OFF_S + s * GM_STAGE_S) + cg * 8;
-                const int nb = min(4, KB - ks * 4);
+                const int nb = min(BPS, KB - ks * BPS);
                 // acc += float(sumi) * (d_w * d_a), as ggml_vec_dot_q8_0_q8_0 does per block (ggml-cpu-quants.c:4004-4012);
-                // |sumi| <= 32 * 127 * 127 < 2^24: the conversion is exact.
+                // |sumi| <= 32 * 127 * 127 < 2^24: exact as f32 either way.
                 #pragma unroll
-                for (int j = 0; j < 4; j++) {
+                for (int j = 0; j < BPS; j++) {
                     if (j < nb) {
                         const uint32_t buf = bc % GM_NBUF, bph = (bc / GM_NBUF) & 1;
                         gm_mbar_wait(tfull0 + buf * 8, bph);
@@ -252,8 +289,11 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             const float4 d = sc[j * (GM_BN / 4) + i];     // activation scales of block j, columns 4i..4i+3 of this group
                             // int -> float on the conversion unit: one issue slot per element.  (The magic-number route, as_float(
                             // 0x4B400000 + sumi) - 12582912.f, costs 1.5 slots and measured 15 % slower: the loop is issue-bound.)
-                            const float2 f0 = make_float2(__int2float_rn(v[4 * i + 0]), __int2float_rn(v[4 * i + 1]));
-                            const float2 f1 = make_float2(__int2float_rn(v[4 * i + 2]), __int2float_rn(v[4 * i + 3]));
+                            // kind::f16 delivers the sums as f32 already
+                            const float2 f0 = KIND == 0 ? make_float2(__int2float_rn(v[4 * i + 0]), __int2float_rn(v[4 * i + 1]))
+                                                        : make_float2(__int_as_float(v[4 * i + 0]), __int_as_float(v[4 * i + 1]));
+                            const float2 f1 = KIND == 0 ? make_float2(__int2float_rn(v[4 * i + 2]), __int2float_rn(v[4 * i + 3]))
+                                                        : make_float2(__int_as_float(v[4 * i + 2]), __int_as_float(v[4 * i + 3]));
                             acc[2 * i + 0] = __ffma2_rn(f0, __fmul2_rn(dw2, make_float2(d.x, d.y)), acc[2 * i + 0]);
                             acc[2 * i + 1] = __ffma2_rn(f1, __fmul2_rn(dw2, make_float2(d.z, d.w)), acc[2 * i + 1]);
                             if (HASMIN) {
@@ -407,6 +447,141 @@ unpack_q6_K_kernel(const uint32_t * __restrict__ ql, const uint32_t * __restrict
     }
 }
 
+// ---- fp16 operand preparation (KIND 1 / 2): the same integers, stored as fp16
+// 4 unsigned bytes -> 4 halfs (value - bias): 0x6400 | b is the half 1024 + b (ulp 1 in [1024, 2048)), then one packed subtract
+__device__ __forceinline__ uint2 gm_h4(uint32_t w, float bias) {
+    const uint32_t lo = __byte_perm(w, 0x64646464u, 0x4140), hi = __byte_perm(w, 0x64646464u, 0x4342);
+    const __half2 off = __float2half2_rn(1024.f + bias);
+    const __half2 a = __hsub2(*(const __half2 *) &lo, off), b = __hsub2(*(const __half2 *) &hi, off);
+    return make_uint2(*(const uint32_t *) &a, *(const uint32_t *) &b);
+}
+__device__ __forceinline__ void gm_store_h16(__half * out, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, float bias) {
+    const uint2 a = gm_h4(w0, bias), b = gm_h4(w1, bias), c = gm_h4(w2, bias), d = gm_h4(w3, bias);
+    ((uint4 *) out)[0] = make_uint4(a.x, a.y, b.x, b.y);
+    ((uint4 *) out)[1] = make_uint4(c.x, c.y, d.x, d.y);
+}
+// q8_0 quants (signed bytes; b ^ 0x80 = b + 128 as unsigned): one thread per 16 elements
+__global__ void __launch_bounds__(256)
+unpack_q8_0_f16_kernel(const uint4 * __restrict__ qs, const long long n16, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long) gridDim.x * blockDim.x) {
+        const uint4 v = qs[i];
+        gm_store_h16(out + i * 16, v.x ^ 0x80808080u, v.y ^ 0x80808080u, v.z ^ 0x80808080u, v.w ^ 0x80808080u, 128.f);
+    }
+}
+__global__ void __launch_bounds__(256)
+unpack_q4_0_f16_kernel(const uint4 * __restrict__ qs, const long long nblocks, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nblocks; i += (long long) gridDim.x * blockDim.x) {
+        const uint4 v = qs[i];
+        const uint32_t m = 0x0F0F0F0Fu;
+        gm_store_h16(out + i * 32,      v.x & m, v.y & m, v.z & m, v.w & m, 8.f);
+        gm_store_h16(out + i * 32 + 16, (v.x >> 4) & m, (v.y >> 4) & m, (v.z >> 4) & m, (v.w >> 4) & m, 8.f);
+    }
+}
+__global__ void __launch_bounds__(256)
+unpack_q4_K_f16_kernel(const uint4 * __restrict__ qs, const uint4 * __restrict__ hdr, const long long nsuper,
+                       __half * __restrict__ out, float * __restrict__ wS, float * __restrict__ wM) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 4; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 2; const int j = (int) (i & 3);
+        const uint4 v0 = qs[sb * 8 + 2 * j], v1 = qs[sb * 8 + 2 * j + 1];
+        const uint32_t m = 0x0F0F0F0Fu;
+        __half * o = out + sb * 256 + j * 64;
+        gm_store_h16(o,      v0.x & m, v0.y & m, v0.z & m, v0.w & m, 0.f);
+        gm_store_h16(o + 16, v1.x & m, v1.y & m, v1.z & m, v1.w & m, 0.f);
+        gm_store_h16(o + 32, (v0.x >> 4) & m, (v0.y >> 4) & m, (v0.z >> 4) & m, (v0.w >> 4) & m, 0.f);
+        gm_store_h16(o + 48, (v1.x >> 4) & m, (v1.y >> 4) & m, (v1.z >> 4) & m, (v1.w >> 4) & m, 0.f);
+        const uint4 h = hdr[sb];
+        const __half2 dd = *(const __half2 *) &h.x;
+        const float d = __low2float(dd), dmin = __high2float(dd);
+        const uint32_t w[3] = {h.y, h.z, h.w};
+        auto byte = [&](int k) -> uint32_t { return (w[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
+        #pragma unroll
+        for (int e = 0; e < 2; e++) {
+            const int g = 2 * j + e;
+            uint32_t sc, mn;
+            if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
+            else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
+            wS[sb * 8 + g] = __fmul_rn(d, (float) sc);
+            wM[sb * 8 + g] = -__fmul_rn(dmin, (float) mn);
+        }
+    }
+}
+// q6_K without padding: the 16-element scale groups are the MMA blocks of KIND 2
+__global__ void __launch_bounds__(256)
+unpack_q6_K_f16_kernel(const uint32_t * __restrict__ ql, const uint32_t * __restrict__ qh, const int8_t * __restrict__ sc,
+                       const __half * __restrict__ dd, const long long nsuper, __half * __restrict__ out, float * __restrict__ wS) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 16; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 4; const int t = (int) (i & 15), half = t >> 3, l4 = t & 7;
+        const uint32_t a = ql[sb * 32 + half * 16 + l4], b = ql[sb * 32 + half * 16 + 8 + l4], h = qh[sb * 16 + half * 8 + l4];
+        const uint32_t v[4] = {
+            (a & 0x0F0F0F0Fu)        | ((h << 4) & 0x30303030u),
+            (b & 0x0F0F0F0Fu)        | ((h << 2) & 0x30303030u),
+            ((a >> 4) & 0x0F0F0F0Fu) | ( h       & 0x30303030u),
+            ((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)};
+        #pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int e = half * 128 + r * 32 + l4 * 4;
+            *(uint2 *) (out + sb * 256 + e) = gm_h4(v[r], 32.f);
+        }
+        wS[sb * 16 + t] = __fmul_rn(__half2float(dd[sb]), (float) sc[sb * 16 + t]);
+    }
+}
+// activations: q8_1 quants as fp16 [N][K]; MODE 1: + d * isum behind dB; MODE 2: dB per 16-element group ([K/16][ldb])
+template <int MODE>
+__global__ void __launch_bounds__(256)
+quantize_rows_f16_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N,
+                         __half * __restrict__ q, float * __restrict__ dB, const long long ldb) {
+    const int NB = K / 32;
+    const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    const long long blk = gid >> 3;
+    if (blk >= (long long) NB * N) return;
+    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 7);
+    const float4 v = *(const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 4) * 4);
+    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const float r0 = roundf(__fmul_rn(v.x, id)), r1 = roundf(__fmul_rn(v.y, id)), r2 = roundf(__fmul_rn(v.z, id)), r3 = roundf(__fmul_rn(v.w, id));
+    const __half2 h01 = __floats2half2_rn(r0, r1), h23 = __floats2half2_rn(r2, r3);
+    *(uint2 *) (q + (long long) row * K + b * 32 + sub * 4) = make_uint2(*(const uint32_t *) &h01, *(const uint32_t *) &h23);
+    const float dh = __half2float(__float2half_rn(d));
+    if (MODE == 2) {
+        if ((sub & 3) == 0) dB[(long long) (2 * b + (sub >> 2)) * ldb + row] = dh;
+    } else {
+        if (MODE == 1) {
+            int isum = (int) r0 + (int) r1 + (int) r2 + (int) r3;
+            isum += __shfl_xor_sync(0xffffffffu, isum, 1);
+            isum += __shfl_xor_sync(0xffffffffu, isum, 2);
+            isum += __shfl_xor_sync(0xffffffffu, isum, 4);
+            if (sub == 0) dB[((long long) NB + b) * ldb + row] = __fmul_rn(dh, (float) isum);
+        }
+        if (sub == 0) dB[(long long) b * ldb + row] = dh;
+    }
+}
+
+cudaError_t launch_quantize_rows_f16(const float * x, long long row_stride_bytes, int K, int N, __half * q, float * dB, long long ldb, int mode, cudaStream_t st) {
+    const long long threads = (long long) (K / 4) * N;
+    const unsigned grid = (unsigned) ((threads + 255) / 256);
+    if (mode == 0)      quantize_rows_f16_kernel<0><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    else if (mode == 1) quantize_rows_f16_kernel<1><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    else                quantize_rows_f16_kernel<2><<<grid, 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, q, dB, ldb);
+    return cudaGetLastError();
+}
+// weights of `type` (SoA field pointers w, nblocks native blocks) -> fp16 integers [M][K]; K-quants also get wS (and q4_K wM)
+cudaError_t launch_unpack_f16(int type, const WPtrs & w, long long nblocks, __half * out, float * wS, float * wM, cudaStream_t st) {
+    auto grid_for = [](long long threads) { long long b = (threads + 255) / 256; return (unsigned) (b > 148 * 32 ? 148 * 32 : (b < 1 ? 1 : b)); };
+    switch (type) {
+        case T_Q8_0: unpack_q8_0_f16_kernel<<<grid_for(nblocks * 2), 256, 0, st>>>((const uint4 *) w.p[0], nblocks * 2, out); break;
+        case T_Q4_0: unpack_q4_0_f16_kernel<<<grid_for(nblocks), 256, 0, st>>>((const uint4 *) w.p[0], nblocks, out); break;
+        case T_Q4_K: unpack_q4_K_f16_kernel<<<grid_for(nblocks * 4), 256, 0, st>>>((const uint4 *) w.p[0], (const uint4 *) w.p[1], nblocks, out, wS, wM); break;
+        case T_Q6_K: unpack_q6_K_f16_kernel<<<grid_for(nblocks * 16), 256, 0, st>>>((const uint32_t *) w.p[0], (const uint32_t *) w.p[1], (const int8_t *) w.p[2],
+                                                                                   (const __half *) w.p[3], nblocks, out, wS); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t launch_quantize_rows_i8(const float * x, long long row_stride_bytes, int K, int N, int8_t * q, float * dB, long long ldb, int mode, cudaStream_t st) {
     const long long threads = (long long) (K / 4) * N;
     const unsigned grid = (unsigned) ((threads + 255) / 256);
@@ -445,25 +620,26 @@ static encode_tiled_t encode_tiled() {
     }();
     return fn;
 }
-// int8 matrix [rows][K], K contiguous; box = 128 bytes of K x 128 rows, 128-B swizzle, out-of-range rows / k read as zero
-static bool make_map_i8(CUtensorMap * m, const void * base, long long rows, long long K) {
+// operand matrix [rows][K], K contiguous, 1-byte (int8) or 2-byte (fp16) elements; box = 128 bytes of K x 128 rows, 128-B swizzle,
+// out-of-range rows / k read as zero
+static bool make_map_operand(CUtensorMap * m, const void * base, long long rows, long long K, int esize) {
     encode_tiled_t enc = encode_tiled();
     if (!enc) return false;
     const cuuint64_t dims[2] = {(cuuint64_t) K, (cuuint64_t) rows};
-    const cuuint64_t strides[1] = {(cuuint64_t) K};
-    const cuuint32_t box[2] = {(cuuint32_t) GM_BK, (cuuint32_t) GM_BM};
+    const cuuint64_t strides[1] = {(cuuint64_t) K * esize};
+    const cuuint32_t box[2] = {(cuuint32_t) (GM_BK / esize), (cuuint32_t) GM_BM};
     const cuuint32_t estr[2] = {1, 1};
-    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return enc(m, esize == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-// activation block scales f32 [KB][ldb]: box = 128 columns x 4 blocks, no swizzle
-static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, long long ldb) {
+// activation block scales f32 [KB][ldb]: box = 128 columns x (blocks per stage), no swizzle
+static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, long long ldb, int bps) {
     encode_tiled_t enc = encode_tiled();
     if (!enc) return false;
     const cuuint64_t dims[2] = {(cuuint64_t) ldb, (cuuint64_t) KB};
     const cuuint64_t strides[1] = {(cuuint64_t) ldb * 4};
-    const cuuint32_t box[2] = {(cuuint32_t) GM_BN, 4};
+    const cuuint32_t box[2] = {(cuuint32_t) GM_BN, (cuuint32_t) bps};
     const cuuint32_t estr[2] = {1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -471,37 +647,47 @@ static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, lo
 
 int gemm_i8_ldb(int N) { return (N + GM_BN - 1) / GM_BN * GM_BN; }      // leading dimension the caller must give dB
 
-// A: int8 [M][K] (16-B aligned, K % 16 == 0); dA_h: fp16 [M][K/32] or dA_f: f32 [M][K/32] (exactly one); mA: f32 [M][K/32] or
-// nullptr; B: int8 [N][K], dB: f32 [K/32][ldb] (+ [K/32][ldb] of d * isum behind it when mA is given); out[n * out_cs + m].
-// K is the MMA-side contraction length (2 x the tensor's for q6_K).
-template <int WS, bool HASMIN>
+// A: [M][K] int8 (kind 0) or fp16 (kind 1, 2), 16-B aligned rows; dA_h: fp16 [M][KB] or dA_f: f32 [M][KB] (exactly one), KB = K / 32
+// (kind 2: K / 16); mA: f32 [M][KB] or nullptr; B: [N][K] like A; dB: f32 [KB][ldb] (+ [KB][ldb] of d * isum behind it when mA is
+// given); out[n * out_cs + m].  K is the MMA-side contraction length (kind 0 with q6_K: 2 x the tensor's, zero padded).
+template <int WS, bool HASMIN, int KIND>
 static cudaError_t gemm_i8_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const CUtensorMap & tmS, const CUtensorMap & tmS2,
                                     const GemmI8Args & p, int grid, cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, HASMIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gm_smem(HASMIN));
+        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, HASMIN, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, gm_smem(HASMIN));
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    gemm_i8_kernel<WS, HASMIN><<<(unsigned) grid, GM_THREADS, gm_smem(HASMIN), st>>>(tmA, tmB, tmS, tmS2, p);
+    gemm_i8_kernel<WS, HASMIN, KIND><<<(unsigned) grid, GM_THREADS, gm_smem(HASMIN), st>>>(tmA, tmB, tmS, tmS2, p);
     return cudaGetLastError();
 }
 
-cudaError_t launch_gemm_i8(const int8_t * A, const __half * dA_h, const float * dA_f, const float * mA, const int8_t * B, const float * dB,
+cudaError_t launch_gemm_i8(int kind, const void * A, const __half * dA_h, const float * dA_f, const float * mA, const void * B, const float * dB,
                            long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st) {
     CUtensorMap tmA, tmB, tmS, tmS2;
-    const long long KB = K / 32;
-    if (!make_map_i8(&tmA, A, M, K) || !make_map_i8(&tmB, B, N, K) || !make_map_scales(&tmS, dB, KB, ldb)) return cudaErrorInvalidValue;
-    if (!make_map_scales(&tmS2, mA ? dB + KB * ldb : dB, KB, ldb)) return cudaErrorInvalidValue;
+    const long long KB = K / gm_kpb(kind);
+    const int esize = kind == 0 ? 1 : 2, bps = gm_bps(kind);
+    if (!make_map_operand(&tmA, A, M, K, esize) || !make_map_operand(&tmB, B, N, K, esize) || !make_map_scales(&tmS, dB, KB, ldb, bps)) return cudaErrorInvalidValue;
+    if (!make_map_scales(&tmS2, mA ? dB + KB * ldb : dB, KB, ldb, bps)) return cudaErrorInvalidValue;
     GemmI8Args p{};
     p.dA = dA_h ? (const void *) dA_h : (const void *) dA_f; p.dA_stride = KB; p.mA = mA; p.out = out; p.out_cs = out_cs;
     p.M = M; p.N = N; p.K = K;
     p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + GM_BN - 1) / GM_BN;
     const int tiles = p.mtiles * p.ntiles;
     const int grid = tiles < sms ? tiles : sms;
-    if (dA_h)    return gemm_i8_launch_t<0, false>(tmA, tmB, tmS, tmS2, p, grid, st);
-    if (mA)      return gemm_i8_launch_t<1, true >(tmA, tmB, tmS, tmS2, p, grid, st);
-    return gemm_i8_launch_t<1, false>(tmA, tmB, tmS, tmS2, p, grid, st);
+    if (kind == 0) {
+        if (dA_h) return gemm_i8_launch_t<0, false, 0>(tmA, tmB, tmS, tmS2, p, grid, st);
+        if (mA)   return gemm_i8_launch_t<1, true,  0>(tmA, tmB, tmS, tmS2, p, grid, st);
+        return gemm_i8_launch_t<1, false, 0>(tmA, tmB, tmS, tmS2, p, grid, st);
+    }
+    if (kind == 1) {
+        if (dA_h) return gemm_i8_launch_t<0, false, 1>(tmA, tmB, tmS, tmS2, p, grid, st);
+        if (mA)   return gemm_i8_launch_t<1, true,  1>(tmA, tmB, tmS, tmS2, p, grid, st);
+        return cudaErrorInvalidValue;
+    }
+    if (dA_f && !mA) return gemm_i8_launch_t<1, false, 2>(tmA, tmB, tmS, tmS2, p, grid, st);
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace b200

@@ -392,29 +392,50 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             // ---- many columns: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
             const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
             const long long ldb = gemm_i8_ldb((int) N);
-            // MMA-side shape: q6_K scales change every 16 elements, so each 16-group is padded to its own 32-byte block (K doubles)
             const int t = s0->type;
-            const long long Kg = t == T_Q6_K ? 2 * K : K, KBg = Kg / 32;
-            const int qmode = t == T_Q4_K ? 1 : t == T_Q6_K ? 2 : 0;
-            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * Kg); if (rc) return rc;
-            rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) (qmode == 1 ? 2 : 1) * KBg * ldb * sizeof(float)); if (rc) return rc;
-            CU(launch_quantize_rows_i8((const float *) x, s1->nb[1], (int) K, (int) N, c->gm_qb, c->gm_db, ldb, qmode, c->st)); c->launches++;
-            const int8_t * A = (const int8_t *) wp.p[0];
-            const __half * dA_h = t == T_Q8_0 || t == T_Q4_0 ? (const __half *) wp.p[1] : nullptr;
+            // int8 operands with s32 block sums (kind::i8), or the same integers as fp16 operands with exact f32 block sums
+            // (kind::f16: twice the operand bytes, no int -> float conversion).  Measured default: i8, except q6_K whose 16-element
+            // scale groups are native K16 fp16 MMAs but need zero padding as int8.  B200_GEMM_KIND=i8|f16 forces one (development).
+            const int kind_env = !getenv("B200_GEMM_KIND") ? -1 : strcmp(getenv("B200_GEMM_KIND"), "i8") == 0 ? 0 : 1;
+            const bool kind_i8 = kind_env < 0 ? t != T_Q6_K : kind_env == 0;
             const float * dA_f = nullptr, * mA = nullptr;
-            if (t != T_Q8_0) { rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * Kg); if (rc) return rc; A = c->gm_a; }
-            if (t == T_Q4_0) {
-                CU(launch_unpack_q4_0_i8(wp.p[0], M * NB, c->gm_a, c->st)); c->launches++;
-            } else if (t == T_Q4_K) {
-                rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) 2 * M * KBg * sizeof(float)); if (rc) return rc;
-                dA_f = c->gm_ws; mA = c->gm_ws + M * KBg;
-                CU(launch_unpack_q4_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->gm_ws + M * KBg, c->st)); c->launches++;
-            } else if (t == T_Q6_K) {
-                rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) M * KBg * sizeof(float)); if (rc) return rc;
-                dA_f = c->gm_ws;
-                CU(launch_unpack_q6_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->st)); c->launches++;
+            const __half * dA_h = t == T_Q8_0 || t == T_Q4_0 ? (const __half *) wp.p[1] : nullptr;
+            if (kind_i8) {
+                // MMA-side shape: q6_K scales change every 16 elements, so each 16-group is padded to its own 32-byte block (K doubles)
+                const long long Kg = t == T_Q6_K ? 2 * K : K, KBg = Kg / 32;
+                const int qmode = t == T_Q4_K ? 1 : t == T_Q6_K ? 2 : 0;
+                rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * Kg); if (rc) return rc;
+                rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) (qmode == 1 ? 2 : 1) * KBg * ldb * sizeof(float)); if (rc) return rc;
+                CU(launch_quantize_rows_i8((const float *) x, s1->nb[1], (int) K, (int) N, c->gm_qb, c->gm_db, ldb, qmode, c->st)); c->launches++;
+                const int8_t * A = (const int8_t *) wp.p[0];
+                if (t != T_Q8_0) { rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * Kg); if (rc) return rc; A = c->gm_a; }
+                if (t == T_Q4_0) {
+                    CU(launch_unpack_q4_0_i8(wp.p[0], M * NB, c->gm_a, c->st)); c->launches++;
+                } else if (t == T_Q4_K) {
+                    rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) 2 * M * KBg * sizeof(float)); if (rc) return rc;
+                    dA_f = c->gm_ws; mA = c->gm_ws + M * KBg;
+                    CU(launch_unpack_q4_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->gm_ws + M * KBg, c->st)); c->launches++;
+                } else if (t == T_Q6_K) {
+                    rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) M * KBg * sizeof(float)); if (rc) return rc;
+                    dA_f = c->gm_ws;
+                    CU(launch_unpack_q6_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->st)); c->launches++;
+                }
+                CU(launch_gemm_i8(0, A, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) Kg, c->sms, c->st)); c->launches++;
+            } else {
+                const int kind = t == T_Q6_K ? 2 : 1;
+                const long long KBg = K / (kind == 2 ? 16 : 32);
+                const int qmode = t == T_Q4_K ? 1 : t == T_Q6_K ? 2 : 0;
+                rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+                rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) (qmode == 1 ? 2 : 1) * KBg * ldb * sizeof(float)); if (rc) return rc;
+                CU(launch_quantize_rows_f16((const float *) x, s1->nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->gm_db, ldb, qmode, c->st)); c->launches++;
+                rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc;
+                if (t == T_Q4_K || t == T_Q6_K) {
+                    rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) 2 * M * KBg * sizeof(float)); if (rc) return rc;
+                    dA_f = c->gm_ws; if (t == T_Q4_K) mA = c->gm_ws + M * KBg;
+                }
+                CU(launch_unpack_f16(t, wp, M * (K / block_elems(t)), (__half *) c->gm_a, c->gm_ws, c->gm_ws + M * KBg, c->st)); c->launches++;
+                CU(launch_gemm_i8(kind, c->gm_a, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) K, c->sms, c->st)); c->launches++;
             }
-            CU(launch_gemm_i8(A, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) Kg, c->sms, c->st)); c->launches++;
             c->q_ptr = nullptr;
         } else if (q) {
             GemvArgs a{};

@@ -78,3 +78,41 @@ def test_gemm_matches_gemv_columns(sess):
     small = np.concatenate([sess.mulmat(w, x[i:i + 8]) for i in range(0, N, 8)])
     assert nmse(big, small) <= 1e-10
     w.free()
+
+
+def test_gemm_block_sums_are_exact_integers(sess):
+    """q8_0 weights with d = 1 and integer activations whose blocks all contain +-127 (so d_a = 1 and the quants are the
+    activations themselves): every block sum and the whole result are integers below 2^24, and the tensor-core path must
+    reproduce the int64 matrix product bit for bit -- whichever MMA kind computes the block sums."""
+    rng = np.random.default_rng(11)
+    M, K, N = 256, 2048, 96
+    wq = rng.integers(-15, 16, size=(M, K // 32, 32), dtype=np.int8)
+    raw = np.zeros((M, K // 32, 34), dtype=np.uint8)
+    raw[:, :, 0:2] = np.frombuffer(np.float16(1.0).tobytes(), dtype=np.uint8)
+    raw[:, :, 2:] = wq.view(np.uint8)
+    raw = raw.reshape(M, -1)
+    x = rng.integers(-127, 128, size=(N, K // 32, 32)).astype(np.float32)
+    x[:, :, 5] = 127.0 * rng.choice([-1.0, 1.0], size=(N, K // 32))
+    x = x.reshape(N, K)
+    w = sess.weights(O.Q8_0, raw, K)
+    got = sess.mulmat(w, x)
+    want = x.astype(np.int64) @ wq.reshape(M, K).astype(np.int64).T
+    assert np.abs(want).max() < 2 ** 24
+    assert np.array_equal(got.astype(np.int64), want) and np.array_equal(got, want.astype(np.float32))
+    w.free()
+
+
+@pytest.mark.parametrize("kind", ["i8", "f16"])
+@pytest.mark.parametrize("t", [O.Q8_0, O.Q4_0, O.Q4_K, O.Q6_K])
+def test_gemm_both_mma_kinds(sess, monkeypatch, kind, t):
+    """kind::i8 (int8 operands, s32 sums) and kind::f16 (the same integers as fp16, f32 sums) give the same block sums:
+    the two results may differ only in float rounding of the scale-accumulate, and both match the oracle"""
+    monkeypatch.setenv("B200_GEMM_KIND", kind)
+    rng = np.random.default_rng(17 + t)
+    M, K, N = 200, 1280, 70
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = sess.mulmat(w, x)
+    assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-10
+    w.free()
