@@ -54,6 +54,49 @@ def gemv_bytes(M, K, N=1, blk=(32, 18)):
     return M * (K // blk[0]) * blk[1] + N * K * 4 + N * M * 4
 
 
+BLK = {2: (32, 18), 8: (32, 34), 12: (256, 144), 14: (256, 210)}      # ggml type -> (elements, bytes) per block
+Q8_0, Q4_K, Q6_K = 8, 12, 14
+
+
+def random_weights(t, rows, K, rng):
+    """random-init weights of ggml type t in the wire format: random quant bytes, small fp16 scales (|w| << 1 so that chains
+    of layers stay finite).  q4_K: 6-bit scales/mins are whatever the random bytes say; d, dmin positive."""
+    if t == Q4_0:
+        return random_q4_0(rows, K, rng)
+    bl, by = BLK[t]
+    nb = K // bl
+    raw = rng.integers(0, 256, size=(rows, nb, by), dtype=np.uint8)
+
+    def put(off, lo, hi, signed):
+        v = rng.uniform(lo, hi, size=(rows, nb))
+        if signed:
+            v = v * rng.choice([-1.0, 1.0], size=(rows, nb))
+        d = v.astype(np.float16).view(np.uint16)
+        raw[:, :, off] = (d & 0xFF).astype(np.uint8)
+        raw[:, :, off + 1] = (d >> 8).astype(np.uint8)
+
+    if t == Q8_0:
+        put(0, 0.00002, 0.00004, True)
+    elif t == Q4_K:
+        put(0, 0.000004, 0.000008, False)
+        put(2, 0.000004, 0.000008, False)
+    elif t == Q6_K:
+        put(208, 0.0000005, 0.000001, True)
+    else:
+        raise ValueError(t)
+    return raw.reshape(rows, nb * by)
+
+
+def quant_mix(quant):
+    """weight type per matrix name.  q4_K_M-like: llama.cpp's Q4_K_M recipe in outline (q6_K for attn_v, ffn_down and the output
+    matrix, q4_K elsewhere)"""
+    if quant == "q4_0":
+        return lambda name: Q4_0
+    if quant == "q4_K_M":
+        return lambda name: Q6_K if name in ("wv", "down", "output") else Q4_K
+    raise ValueError(quant)
+
+
 def random_q4_0(rows, K, rng):
     """random-init q4_0 weights in the wire format: random nibbles, fp16 scale ~U(0.0002,0.0004) with random sign
     (|w| ~ 0.0014: the per-layer map stays a contraction, so an 80-layer chain of identical matrices stays finite)"""
@@ -114,9 +157,11 @@ def measured_peak_hbm():
 class DecodeWorkload:
     """All MUL_MAT/ADD nodes of one decoded token, device resident.  Row r-th slice of every weight when world > 1."""
 
-    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p"):
+    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0"):
         import ctypes as C
         self.mode = mode
+        wt = quant_mix(quant)
+        self.quant = quant
         self.B, self.s, self.C = B, sess, C
         self.rank, self.world = rank, world
         layer, L, out, h, f = llama_shapes(model)
@@ -130,15 +175,15 @@ class DecodeWorkload:
             assert M % world == 0, (name, M, world)
             full_rows = M // world
             # one random host matrix per shape; every layer gets its own HBM copy (distinct addresses, no L2 reuse)
-            host[name] = random_q4_0(full_rows, K, rng)
+            host[name] = random_weights(wt(name), full_rows, K, rng)
         for _ in range(L):
-            self.weights.append({name: sess.weights(Q4_0, host[name], K) for name, M, K in layer})
-        self.w_out = sess.weights(Q4_0, host[out[0]], out[2])
+            self.weights.append({name: sess.weights(wt(name), host[name], K) for name, M, K in layer})
+        self.w_out = sess.weights(wt(out[0]), host[out[0]], out[2])
         self.layer, self.out = layer, out
         for name, M, K in layer:
-            self.alg_bytes += L * gemv_bytes(M, K)
+            self.alg_bytes += L * gemv_bytes(M, K, blk=BLK[wt(name)])
             self.n_mulmat += L
-        self.alg_bytes += gemv_bytes(out[1], out[2])
+        self.alg_bytes += gemv_bytes(out[1], out[2], blk=BLK[wt(out[0])])
         self.n_mulmat += 1
         self.weight_bytes_local = sum(w.nbytes for lw in self.weights for w in lw.values()) + self.w_out.nbytes
         # activations (f32, device)
@@ -153,6 +198,15 @@ class DecodeWorkload:
         sess.h2d(self.x, self.x_host)
         self._nodes = None
         self._build()
+
+    def free(self):
+        for lw in self.weights:
+            for w in lw.values():
+                w.free()
+        self.w_out.free()
+        if self.heap is None:
+            for b in (self.x, self.q, self.k, self.v, self.o, self.hres, self.g, self.u, self.dn, self.x2, self.x3, self.logits):
+                b.free()
 
     def _mm(self, w, src, K, dst, M):
         B = self.B
@@ -242,21 +296,21 @@ def time_shapes(B, s, wl, iters=3):
     return out
 
 
-def time_prefill(B, s, model, N=512, types=((8, "q8_0"), (2, "q4_0")), iters=5):
-    """BASELINE.json configs[2]: the layer MUL_MATs with N = 512 activation columns through the tensor-core GEMM
-    (b200_mulmat, device resident).  One HBM copy per shape, timed back to back with CUDA events; pp tokens/s =
-    N / (layers * sum of the layer's MUL_MAT times + output matrix) -- MUL_MAT only, as for decode."""
+def time_prefill(B, s, model, N=512, mixes=(("q8_0", lambda name: Q8_0), ("q4_0", lambda name: Q4_0)), iters=5):
+    """BASELINE.json configs[2] (and [3] with a K-quant mix): the layer MUL_MATs with N = 512 activation columns through the
+    tensor-core GEMM (b200_mulmat, device resident).  One HBM copy per (shape, type), timed back to back with CUDA events;
+    pp tokens/s = N / (layers * sum of the layer's MUL_MAT times + output matrix) -- MUL_MAT only, as for decode."""
     import ctypes as C
-    import pyoracle as O
     layer, L, out, h, f = llama_shapes(model)
     rng = np.random.default_rng(7)
     res = {}
-    for t, name in types:
+    for name, wt in mixes:
         per_shape, tot_s, flops = [], 0.0, 0.0
         seen = {}
         for nm, M, K in layer + [out]:
-            if (M, K) not in seen:
-                raw = np.tile(O.random_blocks(t, 128, K, rng), ((M + 127) // 128, 1))[:M]
+            t = wt(nm)
+            if (M, K, t) not in seen:
+                raw = np.tile(random_weights(t, 128, K, rng), ((M + 127) // 128, 1))[:M]
                 w = s.weights(t, raw, K)
                 x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
                 xb, db = s.to_device(x), s.malloc(4 * N * M)
@@ -270,19 +324,43 @@ def time_prefill(B, s, model, N=512, types=((8, "q8_0"), (2, "q4_0")), iters=5):
                     B._ck(B.lib().b200_mulmat(s.h, C.byref(s0), C.byref(s1), C.byref(d)))
                 s.record(e1)
                 sec = s.elapsed_ms(e0, e1) * 1e-3 / iters
-                seen[(M, K)] = sec
-                per_shape.append({"shape": "%dx%d" % (M, K), "us": round(sec * 1e6, 1), "TOPS": round(2.0 * M * N * K / sec / 1e12, 1)})
+                seen[(M, K, t)] = sec
+                per_shape.append({"shape": "%dx%d" % (M, K), "type": {2: "q4_0", 8: "q8_0", 12: "q4_K", 14: "q6_K"}[t],
+                                  "us": round(sec * 1e6, 1), "TOPS": round(2.0 * M * N * K / sec / 1e12, 1)})
                 for b in (xb, db):
                     b.free()
                 w.free()
             reps = 1 if nm == out[0] else L
-            tot_s += reps * seen[(M, K)]
+            tot_s += reps * seen[(M, K, t)]
             flops += reps * 2.0 * M * N * K
         res[name] = {"tokens_per_s": round(N / tot_s, 1), "ms": round(tot_s * 1e3, 3), "TOPS": round(flops / tot_s / 1e12, 1),
                      "frac_of_int8_nominal_4500": round(flops / tot_s / 4.5e15, 4), "shapes": per_shape}
-    res["note"] = ("N=%d columns, MUL_MAT only; exact per-32-block int8 tcgen05.mma + fp32 scale-accumulate: bound by the FMA pipe, "
-                   "not the tensor pipe (DESIGN.md section 6)" % N)
+    res["note"] = ("N=%d columns, MUL_MAT only, operand preparation (activation quantise, weight unpack) inside the timed region; exact "
+                   "per-block tcgen05.mma sums + fp32 scale-accumulate: bound by the epilogue's issue slots, not the tensor pipe "
+                   "(DESIGN.md section 6)" % N)
     return res
+
+
+def time_kquant(B, s, steps):
+    """BASELINE.json configs[3]: Llama-3-8B shapes with a Q4_K_M-like q4_K / q6_K mix: decode step (same node list shape as the
+    headline workload) and pp512"""
+    wl = DecodeWorkload(B, s, "llama3-8b", quant="q4_K_M", seed=4321)
+    for _ in range(3):
+        wl.step()
+    s.sync()
+    e0, e1 = s.event(), s.event()
+    s.record(e0)
+    for _ in range(steps):
+        wl.step()
+    s.record(e1)
+    step_s = s.elapsed_ms(e0, e1) * 1e-3 / steps
+    peak, _ = measured_peak_hbm()
+    out = {"workload": "llama3-8b-q4_K_M-like-decode (q6_K: wv, down, output; q4_K: the rest)", "tokens_per_s": round(1.0 / step_s, 2),
+           "ms_per_step": round(step_s * 1e3, 4), "GB/s": round(wl.alg_bytes / step_s / 1e9, 1),
+           "hbm_frac": round(wl.alg_bytes / step_s / 1e9 / peak, 4), "weight_bytes": wl.weight_bytes_local}
+    wl.free()
+    out["pp512"] = time_prefill(B, s, "llama3-8b", mixes=(("q4_K_M", quant_mix("q4_K_M")),))["q4_K_M"]
+    return out
 
 
 def cpu_baseline(model, budget_s):
@@ -418,6 +496,10 @@ def run_b200(args, rank, world):
     logits = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(wl.out[1],)).copy()
     shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
     prefill = time_prefill(B, s, model) if world == 1 and not args.no_shapes and rank == 0 else None
+    kquant = None
+    if world == 1 and not args.no_shapes and rank == 0:
+        wl.free()
+        kquant = time_kquant(B, s, args.steps)
     if rank != 0:
         s.close()
         return
@@ -446,6 +528,8 @@ def run_b200(args, rank, world):
         line["shapes"] = shapes
     if prefill:
         line["pp512"] = prefill
+    if kquant:
+        line["kquant"] = kquant
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
     sys.stdout.flush()

@@ -156,7 +156,8 @@ cudaError_t launch_unpack_q6_K_i8(const WPtrs & w, long long nsuper, int8_t * ou
 int gemm_i8_ldb(int N);
 // kind 0: int8 operands (kind::i8 MMA); 1: the same integers as fp16 (kind::f16, f32 sums); 2: fp16 with 16-element blocks (q6_K)
 cudaError_t launch_gemm_i8(int kind, const void * A, const __half * dA_h, const float * dA_f, const float * mA, const void * B, const float * dB,
-                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st);
+                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st);
+int gemm_i8_ksplit(int M, int N, int K, int kind, int sms);     // > 1: launch_gemm_i8 wants a workspace of that many x N x M floats
 // fp16 operand preparation for kind 1 / 2 (modes as launch_quantize_rows_i8, without the q6_K padding)
 cudaError_t launch_quantize_rows_f16(const float * x, long long row_stride_bytes, int K, int N, __half * q, float * dB, long long ldb, int mode, cudaStream_t st);
 cudaError_t launch_unpack_f16(int type, const WPtrs & w, long long nblocks, __half * out, float * wS, float * wM, cudaStream_t st);

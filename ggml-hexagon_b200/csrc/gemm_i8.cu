@@ -44,19 +44,19 @@ constexpr int GM_THREADS = 64 + GM_EPI_WARPS * 32;
 constexpr int GM_STAGE_A = GM_BM * GM_BK, GM_STAGE_B = GM_BN * GM_BK;
 constexpr int GM_STAGE_S1 = 4 * GM_BN * 4;                  // activation block scales of a stage: 4 blocks x 128 columns f32
 constexpr int GM_OFF_A = 0, GM_OFF_B = GM_STAGES * GM_STAGE_A, GM_OFF_S = GM_OFF_B + GM_STAGES * GM_STAGE_B;
-// HASMIN (q4_K): a second scale tile per stage, d_a * isum_a, for the block-minimum term
-__host__ __device__ constexpr int gm_stage_s(bool hasmin) { return (hasmin ? 2 : 1) * GM_STAGE_S1; }
-__host__ __device__ constexpr int gm_off_bar(bool hasmin) { return GM_OFF_S + GM_STAGES * gm_stage_s(hasmin); }
-__host__ __device__ constexpr int gm_smem(bool hasmin)    { return gm_off_bar(hasmin) + 256 + 1024; }   // + barriers + slack to align the base to 1024 B
-static_assert(gm_smem(true) <= 232448, "shared memory");
+constexpr int GM_STAGE_S = GM_STAGE_S1;
+constexpr int GM_OFF_BAR = GM_OFF_S + GM_STAGES * GM_STAGE_S;
+constexpr int GM_SMEM = GM_OFF_BAR + 256 + 1024;            // + barriers + slack to align the base to 1024 B
+static_assert(GM_SMEM <= 232448, "shared memory");
 constexpr long long GM_TIMEOUT_CYCLES = 8000000000ll;
 
 struct GemmI8Args {
     const void *  dA; long long dA_stride;      // weight block scales [M][dA_stride]: fp16 (WS = 0) or f32 (WS = 1)
-    const float * mA;                           // HASMIN: -(dmin * m_b) per weight block, f32 [M][dA_stride]
+    int acc_init;                               // 1: dst already holds a partial result (q4_K block-minimum term) to add to
     float * out; long long out_cs;              // dst[n * out_cs + m]
     int M, N, K;
     int mtiles, ntiles;
+    int ksplit; long long split_stride;        // split-K: work item = (tile, split); split sp accumulates its K range into out + sp * split_stride
 };
 
 // ------------------------------------------------------------------------------------------------ PTX helpers
@@ -115,14 +115,12 @@ __device__ __forceinline__ void gm_tmem_ld_wait() { asm volatile("tcgen05.wait::
 
 // ------------------------------------------------------------------------------------------------ kernel
 // WS: weight block scales are fp16 (0: q8_0 / q4_0, read where they lie in HBM) or f32 (1: products d * sc of the K-quants)
-// HASMIN: dst also gets sum_b mA[m, b] * sB[b, n] (q4_K: -(dmin * m_b) * (d_a * isum_a), ggml-cpu-quants.c:7535-7590)
-template <int WS, bool HASMIN, int KIND>
+template <int WS, int KIND>
 __global__ void __launch_bounds__(GM_THREADS, 1)
 gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
-               const __grid_constant__ CUtensorMap tmS2, const GemmI8Args p) {
-    constexpr int GM_STAGE_S = gm_stage_s(HASMIN), GM_OFF_BAR = gm_off_bar(HASMIN);
+               const GemmI8Args p) {
     constexpr int BPS = gm_bps(KIND), KPB = gm_kpb(KIND), MPB = gm_mpb(KIND), KSTAGE = BPS * KPB;      // KSTAGE: K elements per stage
-    constexpr uint32_t TX_S = (HASMIN ? 2u : 1u) * BPS * GM_BN * 4u;                                   // scale bytes per stage
+    constexpr uint32_t TX_S = BPS * GM_BN * 4u;                                   // scale bytes per stage
     extern __shared__ uint8_t gm_smem_raw[];
     const uint32_t base = (gm_smem_u32(gm_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
     uint8_t * smem = gm_smem_raw + (base - gm_smem_u32(gm_smem_raw));
@@ -132,7 +130,7 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t tfull0 = bars + 3 * GM_STAGES * 8, tempty0 = tfull0 + GM_NBUF * 8;
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + GM_OFF_BAR + 3 * GM_STAGES * 8 + 2 * GM_NBUF * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nks = (p.K + KSTAGE - 1) / KSTAGE, KB = p.K / KPB, ntiles_total = p.mtiles * p.ntiles;
+    const int nks = (p.K + KSTAGE - 1) / KSTAGE, KB = p.K / KPB, nwork = p.mtiles * p.ntiles * p.ksplit;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(sempty0 + i * 8, GM_EPI_WARPS); }
@@ -154,11 +152,12 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmS) : "memory");
-            if (HASMIN) asm volatile("prefetch.tensormap [%0];" :: "l"(&tmS2) : "memory");
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
+            for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
+                const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
                 const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
-                for (int ks = 0; ks < nks; ks++, it++) {
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
                     gm_mbar_wait(sempty0 + s * 8, ph ^ 1);
@@ -166,7 +165,6 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     gm_tma_2d(sA + s * GM_STAGE_A, &tmA, full0 + s * 8, ks * KSTAGE, mt * GM_BM);
                     gm_tma_2d(sB + s * GM_STAGE_B, &tmB, full0 + s * 8, ks * KSTAGE, nt * GM_BN);
                     gm_tma_2d(sS + s * GM_STAGE_S, &tmS, full0 + s * 8, nt * GM_BN, ks * BPS);
-                    if (HASMIN) gm_tma_2d(sS + s * GM_STAGE_S + GM_STAGE_S1, &tmS2, full0 + s * 8, nt * GM_BN, ks * BPS);
                 }
             }
         }
@@ -178,8 +176,10 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t idesc = (KIND == 0 ? (2u << 4) | (1u << 7) | (1u << 10) : (1u << 4)) |
                                    ((uint32_t) (GM_BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
             uint32_t it = 0, bc = 0;
-            for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
-                for (int ks = 0; ks < nks; ks++, it++) {
+            for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
+                const int sp = work % p.ksplit;
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
                     gm_mbar_wait(full0 + s * 8, ph);
                     gm_fence_after();
@@ -207,13 +207,24 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int m_local = q * 32 + lane;
         const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + cg * 32;
         uint32_t bc = 0, it = 0;
-        for (int tile = blockIdx.x; tile < ntiles_total; tile += gridDim.x) {
+        for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
+            const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
             const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            float * const outp = p.out + (long long) sp * p.split_stride;
             const int m = mt * GM_BM + m_local;
             const long long row_off = (long long) min(m, p.M - 1) * p.dA_stride;
             float2 acc[16];
             #pragma unroll
             for (int i = 0; i < 16; i++) acc[i] = make_float2(0.f, 0.f);
+            if (p.acc_init && m < p.M) {                                    // start from what dst holds (coalesced: 32 consecutive m)
+                const int n0 = nt * GM_BN + cg * 32;
+                #pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    if (n0 + 2 * i     < p.N) acc[i].x = outp[(long long) (n0 + 2 * i)     * p.out_cs + m];
+                    if (n0 + 2 * i + 1 < p.N) acc[i].y = outp[(long long) (n0 + 2 * i + 1) * p.out_cs + m];
+                }
+            }
             // weight scales of this row: the BPS blocks of one stage per load, fetched one stage ahead.  WS == 0 keeps them as
             // the packed fp16 they are in HBM until use (registers are tight).
             constexpr int DWB = BPS * (WS == 0 ? 2 : 4);                                  // bytes of weight scales per stage and row
@@ -251,20 +262,12 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const __half2 h01 = *(const __half2 *) &a, h23 = *(const __half2 *) &b;
                 return make_float4(__low2float(h01), __high2float(h01), __low2float(h23), __high2float(h23));
             };
-            auto load_mw = [&](int ks) -> float4 {          // HASMIN only: K-quant rows are always 16-B aligned (K % 256 == 0)
-                const float * mw_row = p.mA + row_off + ks * BPS;
-                if (BPS == 4) return *(const float4 *) mw_row;
-                const float2 t = *(const float2 *) mw_row;
-                return make_float4(t.x, t.y, 0.f, 0.f);
-            };
-            float4 dwn = load_dw(0), mwn = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (HASMIN) mwn = load_mw(0);
-            for (int ks = 0; ks < nks; ks++, it++) {
+            float4 dwn = load_dw(ks0);
+            for (int ks = ks0; ks < ks1; ks++, it++) {
                 const uint32_t s = it % GM_STAGES, ph = (it / GM_STAGES) & 1;
-                const float4 dwc = cvt_dw(dwn), mwc = mwn;
-                if (ks + 1 < nks) { dwn = load_dw(ks + 1); if (HASMIN) mwn = load_mw(ks + 1); }
+                const float4 dwc = cvt_dw(dwn);
+                if (ks + 1 < ks1) dwn = load_dw(ks + 1);
                 const float dws[4] = {dwc.x, dwc.y, dwc.z, dwc.w};
-                const float mws[4] = {mwc.x, mwc.y, mwc.z, mwc.w};
                 gm_mbar_wait(full0 + s * 8, ph);                            // scales of this stage are in shared memory
                 const float4 * sc = (const float4 *) (smem + GM_OFF_S + s * GM_STAGE_S) + cg * 8;
                 const int nb = min(BPS, KB - ks * BPS);
@@ -296,12 +299,6 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                                         : make_float2(__int_as_float(v[4 * i + 2]), __int_as_float(v[4 * i + 3]));
                             acc[2 * i + 0] = __ffma2_rn(f0, __fmul2_rn(dw2, make_float2(d.x, d.y)), acc[2 * i + 0]);
                             acc[2 * i + 1] = __ffma2_rn(f1, __fmul2_rn(dw2, make_float2(d.z, d.w)), acc[2 * i + 1]);
-                            if (HASMIN) {
-                                const float4 sb = sc[GM_STAGE_S1 / 16 + j * (GM_BN / 4) + i];      // d_a * isum_a, same columns
-                                const float2 mw2 = make_float2(mws[j], mws[j]);
-                                acc[2 * i + 0] = __ffma2_rn(mw2, make_float2(sb.x, sb.y), acc[2 * i + 0]);
-                                acc[2 * i + 1] = __ffma2_rn(mw2, make_float2(sb.z, sb.w), acc[2 * i + 1]);
-                            }
                         }
                     }
                 }
@@ -312,8 +309,8 @@ gemm_i8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int n0 = nt * GM_BN + cg * 32;
                 #pragma unroll
                 for (int i = 0; i < 16; i++) {                              // 32 lanes = 32 consecutive m: coalesced
-                    if (n0 + 2 * i     < p.N) p.out[(long long) (n0 + 2 * i)     * p.out_cs + m] = acc[i].x;
-                    if (n0 + 2 * i + 1 < p.N) p.out[(long long) (n0 + 2 * i + 1) * p.out_cs + m] = acc[i].y;
+                    if (n0 + 2 * i     < p.N) outp[(long long) (n0 + 2 * i)     * p.out_cs + m] = acc[i].x;
+                    if (n0 + 2 * i + 1 < p.N) outp[(long long) (n0 + 2 * i + 1) * p.out_cs + m] = acc[i].y;
                 }
             }
         }
@@ -647,47 +644,132 @@ static bool make_map_scales(CUtensorMap * m, const void * base, long long KB, lo
 
 int gemm_i8_ldb(int N) { return (N + GM_BN - 1) / GM_BN * GM_BN; }      // leading dimension the caller must give dB
 
+// ------------------------------------------------------------------------------------------------ q4_K block-minimum term
+// dst[n * cs + m] = sum_g mA[m][g] * sB[g][n]    (mA = -(dmin * m_g), sB = d_a * isum_a; ggml-cpu-quants.c:7535-7590 folds the
+// same products into its per-super-block sum).  A plain f32 product with a short contraction (K / 32 terms, 1/32 of the main
+// GEMM's multiply-adds) on the CUDA cores: 64 x 64 tile per CTA, 4 x 4 per thread; the tensor-core kernel then starts its
+// accumulators from dst.  (Folding the term into the tensor-core epilogue, one more packed FFMA and a second scale tile per
+// block, measured 121 us against 68 us for the 4096 x 4096 x 512 kernel: that loop has no slack.)
+__global__ void __launch_bounds__(256)
+min_term_kernel(const float * __restrict__ mA, const float * __restrict__ sB, const long long ldb, float * __restrict__ out,
+                const long long out_cs, const int M, const int N, const int KB) {
+    __shared__ float As[32][64 + 4];       // [g][m]
+    __shared__ float Bs[32][64];           // [g][n]
+    const int m0 = blockIdx.x * 64, n0 = blockIdx.y * 64, tid = threadIdx.x;
+    const int tm = (tid & 15) * 4, tn = (tid >> 4) * 4;
+    float acc[4][4];                        // [n][m]
+    #pragma unroll
+    for (int i = 0; i < 4; i++)
+        #pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    for (int g0 = 0; g0 < KB; g0 += 32) {
+        // mA tile: 64 rows x 32 g, read along g (coalesced), stored transposed
+        #pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const int row = (tid >> 5) + r * 8, g = tid & 31;
+            const int m = m0 + row;
+            As[g][row] = (m < M && g0 + g < KB) ? mA[(long long) m * KB + g0 + g] : 0.f;
+        }
+        #pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const int g = (tid >> 6) + r * 4, n = tid & 63;
+            Bs[g][n] = (g0 + g < KB && n0 + n < N) ? sB[(long long) (g0 + g) * ldb + n0 + n] : 0.f;
+        }
+        __syncthreads();
+        #pragma unroll 8
+        for (int g = 0; g < 32; g++) {
+            const float4 a = *(const float4 *) &As[g][tm], b = *(const float4 *) &Bs[g][tn];
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+            #pragma unroll
+            for (int i = 0; i < 4; i++)
+                #pragma unroll
+                for (int j = 0; j < 4; j++) acc[i][j] = fmaf(av[j], bv[i], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    #pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int n = n0 + tn + i;
+        if (n >= N) continue;
+        #pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int m = m0 + tm + j;
+            if (m < M) out[(long long) n * out_cs + m] = acc[i][j];
+        }
+    }
+}
+
 // A: [M][K] int8 (kind 0) or fp16 (kind 1, 2), 16-B aligned rows; dA_h: fp16 [M][KB] or dA_f: f32 [M][KB] (exactly one), KB = K / 32
-// (kind 2: K / 16); mA: f32 [M][KB] or nullptr; B: [N][K] like A; dB: f32 [KB][ldb] (+ [KB][ldb] of d * isum behind it when mA is
-// given); out[n * out_cs + m].  K is the MMA-side contraction length (kind 0 with q6_K: 2 x the tensor's, zero padded).
-template <int WS, bool HASMIN, int KIND>
-static cudaError_t gemm_i8_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const CUtensorMap & tmS, const CUtensorMap & tmS2,
+// (kind 2: K / 16); mA: f32 [M][KB] or nullptr (q4_K: the block-minimum term, with d * isum in the [KB][ldb] floats behind dB);
+// B: [N][K] like A; dB: f32 [KB][ldb]; out[n * out_cs + m].
+// K is the MMA-side contraction length (kind 0 with q6_K: 2 x the tensor's, zero padded).
+template <int WS, int KIND>
+static cudaError_t gemm_i8_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const CUtensorMap & tmS,
                                     const GemmI8Args & p, int grid, cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, HASMIN, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, gm_smem(HASMIN));
+        cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    gemm_i8_kernel<WS, HASMIN, KIND><<<(unsigned) grid, GM_THREADS, gm_smem(HASMIN), st>>>(tmA, tmB, tmS, tmS2, p);
+    gemm_i8_kernel<WS, KIND><<<(unsigned) grid, GM_THREADS, GM_SMEM, st>>>(tmA, tmB, tmS, p);
     return cudaGetLastError();
 }
 
+// split-K for shapes with few output tiles (e.g. the 1024-row k / v projections of grouped-query models: 32 tiles for 148 SMs):
+// every (tile, split) is a work item, the partial results go to a workspace [S][N][M] and a second kernel adds them up in split
+// order (deterministic).
+int gemm_i8_ksplit(int M, int N, int K, int kind, int sms) {
+    const int tiles = ((M + GM_BM - 1) / GM_BM) * ((N + GM_BN - 1) / GM_BN);
+    const int nks = (K + gm_bps(kind) * gm_kpb(kind) - 1) / (gm_bps(kind) * gm_kpb(kind));
+    int s = sms / (tiles > 0 ? tiles : 1);
+    if (s > nks / 8) s = nks / 8;
+    if (s > 8) s = 8;
+    return s < 2 ? 1 : s;
+}
+__global__ void __launch_bounds__(256)
+reduce_splits_kernel(const float * __restrict__ ws, const int S, const long long MN, const int M, float * __restrict__ out, const long long out_cs,
+                     const int add_to_out) {
+    const long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= MN) return;
+    const long long n = i / M; const int m = (int) (i - n * M);
+    float * o = out + n * out_cs + m;
+    float v = add_to_out ? *o : 0.f;
+    for (int sp = 0; sp < S; sp++) v += ws[(long long) sp * MN + i];
+    *o = v;
+}
+
+// split_ws: workspace of gemm_i8_ksplit(...) * N * M floats, or nullptr (no split)
 cudaError_t launch_gemm_i8(int kind, const void * A, const __half * dA_h, const float * dA_f, const float * mA, const void * B, const float * dB,
-                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, cudaStream_t st) {
-    CUtensorMap tmA, tmB, tmS, tmS2;
+                           long long ldb, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st) {
+    CUtensorMap tmA, tmB, tmS;
     const long long KB = K / gm_kpb(kind);
     const int esize = kind == 0 ? 1 : 2, bps = gm_bps(kind);
     if (!make_map_operand(&tmA, A, M, K, esize) || !make_map_operand(&tmB, B, N, K, esize) || !make_map_scales(&tmS, dB, KB, ldb, bps)) return cudaErrorInvalidValue;
-    if (!make_map_scales(&tmS2, mA ? dB + KB * ldb : dB, KB, ldb, bps)) return cudaErrorInvalidValue;
     GemmI8Args p{};
-    p.dA = dA_h ? (const void *) dA_h : (const void *) dA_f; p.dA_stride = KB; p.mA = mA; p.out = out; p.out_cs = out_cs;
+    p.dA = dA_h ? (const void *) dA_h : (const void *) dA_f; p.dA_stride = KB; p.out = out; p.out_cs = out_cs;
     p.M = M; p.N = N; p.K = K;
     p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + GM_BN - 1) / GM_BN;
-    const int tiles = p.mtiles * p.ntiles;
-    const int grid = tiles < sms ? tiles : sms;
-    if (kind == 0) {
-        if (dA_h) return gemm_i8_launch_t<0, false, 0>(tmA, tmB, tmS, tmS2, p, grid, st);
-        if (mA)   return gemm_i8_launch_t<1, true,  0>(tmA, tmB, tmS, tmS2, p, grid, st);
-        return gemm_i8_launch_t<1, false, 0>(tmA, tmB, tmS, tmS2, p, grid, st);
+    p.ksplit = split_ws ? gemm_i8_ksplit(M, N, K, kind, sms) : 1;
+    if (mA) {
+        min_term_kernel<<<dim3((unsigned) ((M + 63) / 64), (unsigned) ((N + 63) / 64)), 256, 0, st>>>(mA, dB + KB * ldb, ldb, out, out_cs, M, N, (int) KB);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        p.acc_init = 1;
     }
-    if (kind == 1) {
-        if (dA_h) return gemm_i8_launch_t<0, false, 1>(tmA, tmB, tmS, tmS2, p, grid, st);
-        if (mA)   return gemm_i8_launch_t<1, true,  1>(tmA, tmB, tmS, tmS2, p, grid, st);
-        return cudaErrorInvalidValue;
-    }
-    if (dA_f && !mA) return gemm_i8_launch_t<1, false, 2>(tmA, tmB, tmS, tmS2, p, grid, st);
-    return cudaErrorInvalidValue;
+    const int add_to_out = p.acc_init;
+    if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; p.acc_init = 0; }
+    const int work = p.mtiles * p.ntiles * p.ksplit;
+    const int grid = work < sms ? work : sms;
+    cudaError_t e;
+    if (kind == 0)      e = dA_h ? gemm_i8_launch_t<0, 0>(tmA, tmB, tmS, p, grid, st) : gemm_i8_launch_t<1, 0>(tmA, tmB, tmS, p, grid, st);
+    else if (kind == 1) e = dA_h ? gemm_i8_launch_t<0, 1>(tmA, tmB, tmS, p, grid, st) : gemm_i8_launch_t<1, 1>(tmA, tmB, tmS, p, grid, st);
+    else if (dA_f && !mA) e = gemm_i8_launch_t<1, 2>(tmA, tmB, tmS, p, grid, st);
+    else e = cudaErrorInvalidValue;
+    if (e != cudaSuccess || p.ksplit == 1) return e;
+    const long long MN = (long long) M * N;
+    reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(split_ws, p.ksplit, MN, M, out, out_cs, add_to_out);
+    return cudaGetLastError();
 }
 
 }  // namespace b200

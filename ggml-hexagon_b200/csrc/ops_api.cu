@@ -83,7 +83,8 @@ struct Ctx {
     int8_t * gm_qb = nullptr; size_t gm_qb_cap = 0;
     float *  gm_db = nullptr; size_t gm_db_cap = 0;
     int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;
-    float *  gm_ws = nullptr; size_t gm_ws_cap = 0;      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
+    float *  gm_ws = nullptr; size_t gm_ws_cap = 0;
+    float *  gm_sp = nullptr; size_t gm_sp_cap = 0;      // split-K partial results      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
@@ -181,7 +182,7 @@ extern "C" int b200_close(b200_handle h) {
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
-    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws);
+    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp);
     cudaStreamDestroy(c->st);
     c->magic = 0;
     delete c;
@@ -420,7 +421,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     dA_f = c->gm_ws;
                     CU(launch_unpack_q6_K_i8(wp, M * (K / 256), c->gm_a, c->gm_ws, c->st)); c->launches++;
                 }
-                CU(launch_gemm_i8(0, A, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) Kg, c->sms, c->st)); c->launches++;
+                const int ksp = gemm_i8_ksplit((int) M, (int) N, (int) Kg, 0, c->sms);
+                if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+                CU(launch_gemm_i8(0, A, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) Kg, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st));
+                c->launches += 1 + (mA ? 1 : 0) + (ksp > 1 ? 1 : 0);
             } else {
                 const int kind = t == T_Q6_K ? 2 : 1;
                 const long long KBg = K / (kind == 2 ? 16 : 32);
@@ -434,7 +438,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     dA_f = c->gm_ws; if (t == T_Q4_K) mA = c->gm_ws + M * KBg;
                 }
                 CU(launch_unpack_f16(t, wp, M * (K / block_elems(t)), (__half *) c->gm_a, c->gm_ws, c->gm_ws + M * KBg, c->st)); c->launches++;
-                CU(launch_gemm_i8(kind, c->gm_a, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) K, c->sms, c->st)); c->launches++;
+                const int ksp = gemm_i8_ksplit((int) M, (int) N, (int) K, kind, c->sms);
+                if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+                CU(launch_gemm_i8(kind, c->gm_a, dA_h, dA_f, mA, c->gm_qb, c->gm_db, ldb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st));
+                c->launches += 1 + (mA ? 1 : 0) + (ksp > 1 ? 1 : 0);
             }
             c->q_ptr = nullptr;
         } else if (q) {

@@ -116,3 +116,16 @@ def test_gemm_both_mma_kinds(sess, monkeypatch, kind, t):
     got = sess.mulmat(w, x)
     assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-10
     w.free()
+
+
+@pytest.mark.parametrize("t", [O.Q8_0, O.Q4_K, O.Q6_K])
+def test_gemm_split_k_small_m(sess, t):
+    """few output tiles (M = 256, N = 96 -> 2 tiles): the K range is split over work items and reduced in a second kernel"""
+    rng = np.random.default_rng(23 + t)
+    M, K, N = 256, 8192, 96
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    got = sess.mulmat(w, x)
+    assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-10
+    w.free()
