@@ -21,6 +21,7 @@ SYMBOLS = [
     "b200_open", "b200_close", "b200_setclocks", "b200_last_error", "b200_device_count", "b200_device_info",
     "b200_add", "b200_mulmat", "b200_graph_compute", "b200_synchronize", "b200_quantize_q8_1", "b200_block_dots",
     "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d", "b200_memset",
+    "b200_memcpy_h2d_async", "b200_memcpy_d2h_async",
     "b200_host_alloc", "b200_host_free", "b200_weights_upload", "b200_weights_download", "b200_block_elems",
     "b200_block_bytes", "b200_event_create", "b200_event_record", "b200_event_elapsed_ms", "b200_event_destroy",
     "b200_launch_count", "b200_flush_l2", "b200_rowsplit_unique_id", "b200_rowsplit_init", "b200_rowsplit_finalize",
@@ -75,6 +76,8 @@ def lib():
         L.b200_free.argtypes = [H, VP]
         L.b200_memcpy_h2d.argtypes = [H, VP, VP, C.c_size_t]
         L.b200_memcpy_d2h.argtypes = [H, VP, VP, C.c_size_t]
+        L.b200_memcpy_h2d_async.argtypes = [H, VP, VP, C.c_size_t]
+        L.b200_memcpy_d2h_async.argtypes = [H, VP, VP, C.c_size_t]
         L.b200_memcpy_d2d.argtypes = [H, VP, VP, C.c_size_t]
         L.b200_memset.argtypes = [H, VP, C.c_int, C.c_size_t]
         L.b200_host_alloc.argtypes = [H, C.c_size_t, C.POINTER(VP)]

@@ -269,11 +269,26 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     if (rc) { fprintf(stderr, "[ggml-b200] graph_compute: %s\n", b200_last_error()); return GGML_STATUS_FAILED; }
     return GGML_STATUS_SUCCESS;
 }
+// Stream-ordered tensor copies (the hexagon backend leaves these slots empty, ggml-hexagon.cpp:5836-5850; a GPU backend wants
+// them so that the scheduler's input copies queue behind / in front of graph_compute without a host round trip).
+// Quantised tensors are repacked on the way in and out, which the synchronous buffer path does.
+static void b200_backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * t, const void * data, size_t offset, size_t size) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    if (is_qweight(t->type)) { buf->iface.set_tensor(buf, t, data, offset, size); return; }
+    if (b200_memcpy_h2d_async(c->h, (char *) t->data + offset, data, size)) GGML_ABORT("b200 set_tensor_async: %s", b200_last_error());
+}
+static void b200_backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * t, void * data, size_t offset, size_t size) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    if (is_qweight(t->type)) { buf->iface.get_tensor(buf, t, data, offset, size); return; }
+    if (b200_memcpy_d2h_async(c->h, data, (const char *) t->data + offset, size)) GGML_ABORT("b200 get_tensor_async: %s", b200_last_error());
+}
 static const ggml_backend_i b200_backend_iface = {
     /* get_name           */ b200_backend_name,
     /* free               */ b200_backend_free,
-    /* set_tensor_async   */ nullptr,
-    /* get_tensor_async   */ nullptr,
+    /* set_tensor_async   */ b200_backend_set_tensor_async,
+    /* get_tensor_async   */ b200_backend_get_tensor_async,
     /* cpy_tensor_async   */ nullptr,
     /* synchronize        */ b200_backend_synchronize,
     /* graph_plan_create  */ nullptr,

@@ -128,6 +128,11 @@ B200_API int b200_free(b200_handle h, void * ptr);
 B200_API int b200_memcpy_h2d(b200_handle h, void * dst_dev, const void * src_host, size_t n);
 B200_API int b200_memcpy_d2h(b200_handle h, void * dst_host, const void * src_dev, size_t n);
 B200_API int b200_memcpy_d2d(b200_handle h, void * dst_dev, const void * src_dev, size_t n);
+/* stream-ordered variants (backend.set_tensor_async / get_tensor_async, ggml-backend-impl.h:93-94; the hexagon backend leaves
+ * these slots empty): they return at once, the copy is ordered with the ops of the session and is complete after
+ * b200_synchronize().  Host memory should come from b200_host_alloc for the copy to overlap. */
+B200_API int b200_memcpy_h2d_async(b200_handle h, void * dst_dev, const void * src_host, size_t n);
+B200_API int b200_memcpy_d2h_async(b200_handle h, void * dst_host, const void * src_dev, size_t n);
 B200_API int b200_memset(b200_handle h, void * dst_dev, int value, size_t n);
 /* pinned host staging memory for the host-buffer (e2e) path */
 B200_API int b200_host_alloc(b200_handle h, size_t size, void ** ptr);

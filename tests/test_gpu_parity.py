@@ -228,3 +228,24 @@ def test_graph_compute_matches_direct(sess):
         y = O.mul_mat(t, w.download(), y, 1)
     assert nmse(direct, (y + x).reshape(-1)) <= 1e-6
     assert sess.launch_count() > 0
+
+
+def test_async_copies_are_stream_ordered():
+    """b200_memcpy_h2d_async -> op -> b200_memcpy_d2h_async -> b200_synchronize: the seat of set/get_tensor_async"""
+    import ctypes as C
+    with B.Session(0) as s:
+        n = 1 << 16
+        hx, hy = C.c_void_p(), C.c_void_p()
+        B._ck(B.lib().b200_host_alloc(s.h, 4 * n, C.byref(hx)))
+        B._ck(B.lib().b200_host_alloc(s.h, 4 * n, C.byref(hy)))
+        a = np.random.default_rng(0).standard_normal(n).astype(np.float32)
+        C.memmove(hx, a.ctypes.data, 4 * n)
+        da, dd = s.malloc(4 * n), s.malloc(4 * n)
+        B._ck(B.lib().b200_memcpy_h2d_async(s.h, da.ptr, hx, 4 * n))
+        t0, t1, td = B.f32_tensor(da.ptr, [n]), B.f32_tensor(da.ptr, [n]), B.f32_tensor(dd.ptr, [n], op=B.OP_ADD)
+        B._ck(B.lib().b200_add(s.h, C.byref(t0), C.byref(t1), C.byref(td)))
+        B._ck(B.lib().b200_memcpy_d2h_async(s.h, hy, dd.ptr, 4 * n))
+        s.sync()
+        got = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(n,)).copy()
+        assert np.array_equal(got, a + a)
+        B._ck(B.lib().b200_host_free(s.h, hx)); B._ck(B.lib().b200_host_free(s.h, hy))
