@@ -84,7 +84,6 @@ struct GemvArgs {
     int steps; int64_t K; int64_t dcs;
     const float * x; int64_t x_col_stride;     // FUSEQ: f32 activations, column stride in bytes
     ActView act;                                // !FUSEQ: pre-quantised scratch
-    int l2_prefetch;                            // each CTA bulk-prefetches its row slice into L2 first
     // row split over the GPUs of one box: every result is also stored into the peers' copies of dst over NVLink
     // (peer address = local address + peer_delta[p]; dst lies in the symmetric heap every rank allocated alike)
     int npeers; long long peer_delta[7];
