@@ -90,7 +90,19 @@ struct GemvArgs {
     // the LAST CTA of the launch publishes "op n of this rank is in your memory" to every peer (release, system scope):
     // rs_ctrl[0] = CTA arrival counter, rs_ctrl[1] = ops signalled so far; peer_flag[p] = this rank's slot in peer p's flags
     int rs_signal; uint32_t * rs_ctrl; long long peer_flag[7];
+    // "LL" protocol (default for vector ops): instead of plain stores + a flag exchange, every result goes to the peers as ONE
+    // 8-byte store {value, sequence number} into a staging area of the symmetric heap; the receivers poll the slots themselves
+    // (ll_gather_kernel), so no fence, no flag and no second NVLink round trip.  seq = *ll_count + ll_op (ops of this submission
+    // so far + 1); slot = ll_slots + (seq & 1) * LL_HALF_ELEMS + ll_off[mat] + ll_rank * M + row  (two halves: a rank can be at
+    // most one exchange ahead of the slowest reader)
+    uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_op; int ll_off[3]; int ll_rank;
 };
+constexpr int LL_HALF_ELEMS = 131072;                     // {value, seq} slots per staging half
+struct LlGatherArgs { uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_op; int nmat; float * dst[3]; int M[3]; int ll_off[3]; int world, rank; };
+// polls the peers' slots of one exchange and writes the values into the local dst vectors; starts while the GEMV still runs (PDL)
+cudaError_t launch_ll_gather(const LlGatherArgs & a, cudaStream_t st);
+// end of a submission: *ll_count += nops
+cudaError_t launch_ll_bump(uint32_t * ll_count, uint32_t nops, cudaStream_t st);
 // one warp: tell every peer "my slice of the op is in your memory" (release, system scope), then wait for theirs
 cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr /* [npeers] */,
                                      const int * peer_rank /* [npeers] */, cudaStream_t st);

@@ -104,6 +104,12 @@ gemv4_kernel(const GemvArgs a) {
             mt.dst[o] = v;
             float s = 0.f;
             if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
+            if (a.ll_slots) {                                 // row split, LL protocol: {value, seq} in one 8-byte NVLink store per peer
+                const uint32_t seq = *a.ll_count + a.ll_op;
+                const uint2 * slot = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + a.ll_off[m] + (int64_t) a.ll_rank * M + row0 + r;
+                for (int pi = 0; pi < a.npeers; pi++)
+                    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"((const char *) slot + a.peer_delta[pi]), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+            } else
             for (int pi = 0; pi < a.npeers; pi++) {           // row split: the same values into every peer's dst (NVLink stores)
                 *(float *) ((char *) (mt.dst + o) + a.peer_delta[pi]) = v;
                 if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;

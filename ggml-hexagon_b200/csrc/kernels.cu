@@ -314,6 +314,53 @@ cudaError_t launch_rowsplit_wait(uint32_t * local_flags, uint32_t * counter, int
     return cudaLaunchKernelEx(&cfg, rowsplit_wait_kernel, local_flags, counter, a);
 }
 
+// ---- LL protocol receiver: one thread per (matrix, peer row); spins on the slot until the peer's store of THIS exchange (sequence
+// number) has landed, copies the value into the local dst vector.  Launched with programmatic dependent launch right behind the
+// GEMV, so it polls while the local GEMV still runs; its completion implies the GEMV's (grid dependency at the end).
+__global__ void __launch_bounds__(1024)
+ll_gather_kernel(const LlGatherArgs a) {
+#if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();           // the next quantise / GEMV may launch and fetch its weights meanwhile
+#endif
+    const uint32_t seq = *a.ll_count + a.ll_op;
+    const uint2 * half = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    for (int m = 0; m < a.nmat; m++) {
+        const int M = a.M[m], total = M * a.world;
+        const uint2 * slots = half + a.ll_off[m];
+        for (int i = gtid; i < total; i += gsize) {
+            if (i / M == a.rank) continue;
+            uint32_t v, f;
+            const long long t0 = clock64();
+            do {
+                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(slots + i) : "memory");
+                if (f != seq && clock64() - t0 > 8000000000ll) __trap();
+            } while (f != seq);
+            a.dst[m][i] = __uint_as_float(v);
+        }
+    }
+#if __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();                      // the local slice (plain stores of the GEMV before us) is complete too
+#endif
+}
+cudaError_t launch_ll_gather(const LlGatherArgs & a, cudaStream_t st) {
+    long long total = 0;
+    for (int m = 0; m < a.nmat; m++) total += (long long) a.M[m] * a.world;
+    int blocks = (int) ((total + 1023) / 1024); if (blocks > 64) blocks = 64; if (blocks < 1) blocks = 1;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) blocks); cfg.blockDim = dim3(1024); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, ll_gather_kernel, a);
+}
+__global__ void ll_bump_kernel(uint32_t * ll_count, const uint32_t nops) { *ll_count += nops; }
+cudaError_t launch_ll_bump(uint32_t * ll_count, uint32_t nops, cudaStream_t st) {
+    ll_bump_kernel<<<1, 1, 0, st>>>(ll_count, nops);
+    return cudaGetLastError();
+}
+
 __global__ void fill_kernel(uint4 * p, size_t n16, uint32_t v) {
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t) gridDim.x * blockDim.x)
         p[i] = make_uint4(v, v, v, v);

@@ -92,6 +92,8 @@ struct Ctx {
     char * rs_heap = nullptr; size_t rs_heap_bytes = 0;
     char * rs_peer[8] = {nullptr}; bool rs_ipc[8] = {false};
     bool rs_attached = false, rs_on = false;
+    // LL protocol bookkeeping of the submission being built: exchanges so far, and what the gather after the current GEMV collects
+    uint32_t rs_ops = 0; int ll_nmat = 0; float * ll_dst[3] = {}; int ll_M[3] = {}; int ll_off[3] = {}; uint32_t ll_op = 0;
 };
 
 static Ctx * ctx_of(b200_handle h) {
@@ -336,19 +338,38 @@ static int mulmat_check(const b200_tensor * s0, const b200_tensor * s1, const b2
 
 struct FusedAdd { const float * src = nullptr; float * dst = nullptr; };
 
+// symmetric heap: [4096 B control: flags +0, op counter +256, ctrl +260/+264, LL submission base count +320][2 LL staging halves][user]
+constexpr size_t RS_LL_BYTES = (size_t) 2 * LL_HALF_ELEMS * sizeof(uint2);
+constexpr size_t RS_HDR = 4096 + RS_LL_BYTES;
+static bool rs_proto_ll() { static const bool ll = !(getenv("B200_RS_PROTO") && strcmp(getenv("B200_RS_PROTO"), "flag") == 0); return ll; }
+
 // ---- fused row split: peer deltas for the GEMV stores, and the exchange that follows each row-split op
-static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64_t * bytes, int n) {
-    a.npeers = 0;
+// dsts[i]: this rank's slice of matrix i's dst; rows[i]: rows per rank; vec: one activation column (LL protocol possible)
+static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64_t * bytes, int n, const int64_t * rows = nullptr, bool vec = false) {
+    a.npeers = 0; a.ll_slots = nullptr; c->ll_nmat = 0;
     if (!c->rs_on || c->world == 1) return 0;
     for (int i = 0; i < n; i++) {
         const char * p = (const char *) dsts[i];
-        if (p < c->rs_heap + 4096 || p + bytes[i] > c->rs_heap + c->rs_heap_bytes) return fail(B200_EINVAL, "rowsplit: dst is outside the symmetric heap (b200_rowsplit_heap_create)");
+        if (p < c->rs_heap + RS_HDR || p + bytes[i] > c->rs_heap + c->rs_heap_bytes) return fail(B200_EINVAL, "rowsplit: dst is outside the symmetric heap (b200_rowsplit_heap_create)");
     }
     for (int r = 0; r < c->world; r++) if (r != c->rank) {
         a.peer_flag[a.npeers] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank);
         a.peer_delta[a.npeers++] = (long long) (c->rs_peer[r] - c->rs_heap);
     }
-    // default: a separate 32-thread exchange kernel after the GEMV (signal + wait).  B200_RS_INLINE=1: the GEMV's last CTA
+    if (vec && rows && rs_proto_ll()) {
+        // LL protocol: {value, seq} slots in the staging area, polled by ll_gather_kernel on every peer
+        int64_t off = 0;
+        for (int i = 0; i < n; i++) { c->ll_off[i] = (int) off; off += rows[i] * c->world; }
+        if (off <= LL_HALF_ELEMS) {
+            c->rs_ops++;
+            a.ll_slots = (uint2 *) (c->rs_heap + 4096); a.ll_count = (const uint32_t *) (c->rs_heap + 320); a.ll_op = c->rs_ops; a.ll_rank = c->rank;
+            c->ll_nmat = n; c->ll_op = c->rs_ops;
+            for (int i = 0; i < n; i++) { a.ll_off[i] = c->ll_off[i]; c->ll_M[i] = (int) rows[i]; c->ll_dst[i] = (float *) dsts[i] - (int64_t) c->rank * rows[i]; }
+            a.rs_signal = 0;
+            return 0;
+        }
+    }
+    // flag protocol: a separate 32-thread exchange kernel after the GEMV (signal + wait).  B200_RS_INLINE=1: the GEMV's last CTA
     // signals (heap + 260: CTA arrivals, + 264: ops signalled) and a PDL wait kernel follows -- measured SLOWER on 2 GPUs
     // (9.2 vs 7.6 ms per Llama-3-70B token: the per-CTA fences wait for NVLink store acknowledgements), kept for study
     static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
@@ -357,6 +378,15 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
 }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
+    if (c->ll_nmat > 0) {
+        LlGatherArgs g{};
+        g.ll_slots = (uint2 *) (c->rs_heap + 4096); g.ll_count = (const uint32_t *) (c->rs_heap + 320); g.ll_op = c->ll_op;
+        g.nmat = c->ll_nmat; g.world = c->world; g.rank = c->rank;
+        for (int i = 0; i < c->ll_nmat; i++) { g.dst[i] = c->ll_dst[i]; g.M[i] = c->ll_M[i]; g.ll_off[i] = c->ll_off[i]; }
+        c->ll_nmat = 0;
+        CU(launch_ll_gather(g, c->st)); c->launches++;
+        return 0;
+    }
     long long addr[7]; int ranks[7]; int np = 0;
     for (int r = 0; r < c->world; r++) if (r != c->rank) { addr[np] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank); ranks[np] = r; np++; }
     static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
@@ -467,7 +497,8 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
                 }
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
-                { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; rc = rs_fill(c, a, dp, db_, 1); if (rc) return rc; }
+                { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; const int64_t rw[1] = {M};
+                  rc = rs_fill(c, a, dp, db_, 1, rw, N == 1 && s1->ne[2] == 1 && s1->ne[3] == 1); if (rc) return rc; }
                 const int rs_signal = a.rs_signal;
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
@@ -556,7 +587,8 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
         a.mat[j].dst = (float *) nodes[j].dst.data + (c->rs_on ? c->rank * nodes[j].src0.ne[1] : 0);
         dsts[j] = a.mat[j].dst; dbytes[j] = a.mat[j].M * 4;
     }
-    { int rc = rs_fill(c, a, dsts, dbytes, len); if (rc) return rc; }
+    { int64_t rw[3]; for (int j = 0; j < len; j++) rw[j] = a.mat[j].M;
+      int rc = rs_fill(c, a, dsts, dbytes, len, rw, true); if (rc) return rc; }
     if (gemv_fuseq_enabled()) {
         a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
         CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
@@ -738,7 +770,7 @@ extern "C" int b200_mulmat(b200_handle h, const b200_tensor * s0, const b200_ten
 // ------------------------------------------------------------------------------------------------ graph compute
 static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
     static const bool fuse = !(getenv("B200_FUSE") && atoi(getenv("B200_FUSE")) == 0);
-    c->in_graph = true; c->q_ptr = nullptr;
+    c->in_graph = true; c->q_ptr = nullptr; c->rs_ops = 0;
     int rc = 0;
     for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
@@ -763,6 +795,11 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             default: rc = fail(B200_ENOTSUP, "graph node %d: op %d not offloaded", i, d.op);
         }
         i += used;
+    }
+    if (!rc && c->rs_on && c->rs_ops > 0) {      // LL protocol: the sequence numbers of the next submission continue after this one's
+        cudaError_t e = launch_ll_bump((uint32_t *) (c->rs_heap + 320), c->rs_ops, c->st);
+        if (e != cudaSuccess) rc = fail(B200_ECUDA, "ll_bump: %s", cudaGetErrorString(e));
+        c->launches++;
     }
     c->in_graph = false; c->q_ptr = nullptr;
     return rc;
@@ -941,7 +978,7 @@ extern "C" int b200_rowsplit_heap_create(b200_handle h, size_t bytes, void ** us
     CTX(h);
     if (c->rs_heap) return fail(B200_EINVAL, "rowsplit heap already created");
     if (!user_base) return fail(B200_EINVAL, "user_base is NULL");
-    const size_t total = ((bytes + 255) & ~(size_t) 255) + 4096;
+    const size_t total = ((bytes + 255) & ~(size_t) 255) + RS_HDR;
     CU(cudaMalloc((void **) &c->rs_heap, total));
     CU(cudaMemsetAsync(c->rs_heap, 0, total, c->st));
     CU(cudaStreamSynchronize(c->st));
@@ -952,7 +989,7 @@ extern "C" int b200_rowsplit_heap_create(b200_handle h, size_t bytes, void ** us
         CU(cudaIpcGetMemHandle(&hd, c->rs_heap));
         memcpy(ipc_handle64, &hd, 64);
     }
-    *user_base = c->rs_heap + 4096;
+    *user_base = c->rs_heap + RS_HDR;
     return 0;
 }
 static int rs_check_attach(Ctx * c, int rank, int world) {
@@ -984,7 +1021,7 @@ extern "C" int b200_rowsplit_heap_attach_ptrs(b200_handle h, void * const * peer
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(B200_ECUDA, "cudaDeviceEnablePeerAccess(%d): %s", peer_devices[r], cudaGetErrorString(e));
             cudaGetLastError();
         }
-        c->rs_peer[r] = (char *) peer_user_bases[r] - 4096;
+        c->rs_peer[r] = (char *) peer_user_bases[r] - RS_HDR;
     }
     c->rank = rank; c->world = world; c->rs_attached = true;
     return 0;
