@@ -517,7 +517,7 @@ def run_b200(args, rank, world):
                        "layers": wl.L, "mul_mat_per_step": wl.n_mulmat, "add_per_step": 2 * wl.L,
                        "weight_bytes_per_gpu": wl.weight_bytes_local, "l2": "inputs larger than L2 (weights streamed once per step)",
                        "submit": "one b200_graph_compute (CUDA graph + PDL)" if world == 1 else
-                       ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores slices into peer HBM over NVLink, flag exchange per op)"
+                       ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores {value, seq} slots into peer HBM over NVLink, polled by a gather kernel per op; B200_RS_PROTO=flag: plain stores + flag exchange)"
                         if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                          "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv4_kernel<q4_0,1,R>",

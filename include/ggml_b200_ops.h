@@ -170,9 +170,11 @@ B200_API int b200_mulmat_rowsplit(b200_handle h, const b200_tensor * src0_slice,
                                   b200_tensor * dst_full);
 
 
-/* ---- fused row split over peer memory (NVLink P2P stores from inside the GEMV + a flag exchange per op instead of the
- *      ncclAllGather).  Every rank: heap_create (same size everywhere), exchange the 64-byte IPC handles by any means,
- *      heap_attach, carve its activation vectors out of the heap at the same offsets on every rank. */
+/* ---- fused row split over peer memory, instead of the ncclAllGather: the GEMV stores its results into every peer's heap over
+ *      NVLink as {value, sequence number} pairs which a gather kernel on the peer polls ("LL" protocol; B200_RS_PROTO=flag and
+ *      ops with several columns: plain stores + a flag exchange per op).  Every rank: heap_create (same size everywhere),
+ *      exchange the 64-byte IPC handles by any means, heap_attach, carve its activation vectors out of the heap at the same
+ *      offsets on every rank.  All ranks must submit the same node lists in the same order. */
 B200_API int b200_rowsplit_heap_create(b200_handle h, size_t bytes, void ** user_base, void * ipc_handle64);
 B200_API int b200_rowsplit_heap_attach(b200_handle h, const void * all_handles /* world x 64 bytes, by rank */, int32_t rank, int32_t world);
 /* same-process variant: the peers' user_base pointers and CUDA ordinals */
