@@ -136,6 +136,110 @@ gemv4_kernel(const GemvArgs a) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------ gemv5: TMA-staged tiles
+// Same lane / warp roles as gemv4, but the weights of the CTA's RT rows do not travel through registers: thread 0 issues one
+// cp.async.bulk per SoA field (the rows of a tile are contiguous in every field array) into shared memory, BEFORE the
+// dependency wait, and the lanes read their fragments from shared memory once the mbarrier flips.  What this buys is bytes
+// in flight: a resident CTA holds its whole tile (18-50 KB) in flight at the cost of ~48 registers per thread, so an SM has
+// ~200 KB outstanding instead of ~80 KB -- the difference between 3.5-4.2 TB/s and what a plain read kernel of the same
+// launch size reaches under programmatic dependent launch (tools/ubench_stream.cu: 25 MB in 3.9 us, 51 MB in 8.9 us).
+struct Gemv5Tile { int nfields; int rowbytes[4]; int foff[4]; int tile_bytes; };
+
+__device__ __forceinline__ uint32_t g5_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+template <int TYPE, int RT, int ITERS>
+__global__ void __launch_bounds__(512)
+gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
+    using W = WT<TYPE>;
+    using A = WR<TYPE>;
+    extern __shared__ __align__(128) uint8_t g5_sm[];
+    float (*part)[RT + 1] = (float (*)[RT + 1]) (g5_sm + t.tile_bytes);
+    const uint32_t mbar = g5_smem(g5_sm + t.tile_bytes + 16 * (RT + 1) * 4);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int steps = a.steps;
+#if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();
+#endif
+    int m = 0, cta = blockIdx.x;
+    if (a.nmat > 1 && cta >= a.cta_end[0]) { m = 1; if (a.nmat > 2 && cta >= a.cta_end[1]) m = 2; }
+    if (m > 0) cta -= a.cta_end[m - 1];
+    const GemvMat & mt = a.mat[m];
+    const int64_t M = mt.M;
+    const int64_t row0 = (int64_t) cta * RT;
+    const int nrows = (int) (M - row0 < RT ? M - row0 : RT);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        uint32_t total = 0;
+        for (int i = 0; i < t.nfields; i++) total += (uint32_t) (nrows * t.rowbytes[i]);
+        asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(mbar), "r"(total) : "memory");
+        for (int i = 0; i < t.nfields; i++) {
+            const uint8_t * src = mt.w.p[i] + row0 * t.rowbytes[i];
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         :: "r"(g5_smem(g5_sm + t.foff[i])), "l"(src), "r"((uint32_t) (nrows * t.rowbytes[i])), "r"(mbar) : "memory");
+        }
+    }
+    __syncthreads();                             // the barrier is initialised for everyone
+#if __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();             // activations (and add_src) come from the kernels before us
+#endif
+    // this lane's activations: step s of slice warp (+ nwarps) of the row
+    const ActCol ac(a.act, 0);
+    typename A::Act av[ITERS];
+    int sidx[ITERS];
+    #pragma unroll
+    for (int it = 0; it < ITERS; it++) {
+        sidx[it] = (warp + it * nwarps) * 32 + lane;
+        if (sidx[it] < steps) av[it] = A::load_act(ac, sidx[it]);
+    }
+    WPtrs sw;
+    #pragma unroll
+    for (int i = 0; i < 4; i++) sw.p[i] = g5_sm + t.foff[i < t.nfields ? i : 0];
+    {   // wait for the tile
+        uint32_t ok = 0;
+        while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar) : "memory");
+    }
+    float acc[RT];
+    #pragma unroll
+    for (int r = 0; r < RT; r++) acc[r] = 0.f;
+    #pragma unroll
+    for (int it = 0; it < ITERS; it++) {
+        const int s = sidx[it];
+        if (s < steps) {
+            #pragma unroll
+            for (int r = 0; r < RT; r++)
+                if (r < nrows) acc[r] += wr_dot<TYPE>(W::loads(sw, r * steps + s), av[it], s);
+        }
+    }
+    constexpr int SH = 5 - Log2<RT>::v;
+    {
+        const float v = reduce_rows<RT>(acc, lane);
+        if ((lane & ((1 << SH) - 1)) == 0) part[warp][lane >> SH] = v;
+    }
+    __syncthreads();
+    if (tid < RT) {
+        float v = 0.f;
+        for (int q = 0; q < nwarps; q++) v += part[q][tid];
+        const int r = tid;
+        if (row0 + r < M) {
+            const int64_t o = row0 + r;
+            mt.dst[o] = v;
+            float s = 0.f;
+            if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
+            if (a.ll_slots) {
+                const uint32_t seq = *a.ll_count + a.ll_op;
+                const uint2 * slot = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + a.ll_off[m] + (int64_t) a.ll_rank * M + row0 + r;
+                for (int pi = 0; pi < a.npeers; pi++)
+                    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"((const char *) slot + a.peer_delta[pi]), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+            } else
+            for (int pi = 0; pi < a.npeers; pi++) {
+                *(float *) ((char *) (mt.dst + o) + a.peer_delta[pi]) = v;
+                if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ launch
 struct Tune { int rows = 0; bool pdl = true; };    // rows 0 = per-shape heuristic
 static const Tune & tune() {
@@ -172,9 +276,70 @@ static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false, FQ>, a);
 }
 
+// gemv5 eligibility: one column, pre-quantised activations, every field's row is a multiple of 16 bytes and 16-byte aligned
+// (bulk copies), at most 2 slices per warp, no in-kernel completion signal
+template <int TYPE, int RT, int ITERS>
+static cudaError_t launch_g5(GemvArgs & a, const Gemv5Tile & t, int nwarps, cudaStream_t st, bool pdl) {
+    static int smem_set = 0;
+    const int smem = t.tile_bytes + 16 * (RT + 1) * 4 + 16;
+    if (smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemv5_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        smem_set = smem;
+    }
+    int total = 0;
+    for (int i = 0; i < a.nmat; i++) { total += (int) ((a.mat[i].M + RT - 1) / RT); a.cta_end[i] = total; }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) total); cfg.blockDim = dim3(nwarps * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, gemv5_kernel<TYPE, RT, ITERS>, a, t);
+}
+template <int TYPE>
+static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
+    static const int mode = getenv("B200_GEMV5") ? atoi(getenv("B200_GEMV5")) : 1;       // 0: off (gemv4 only)
+    if (!mode || a.rs_signal) return false;
+    const WFields f = wfields(TYPE);
+    const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);            // native blocks per row
+    Gemv5Tile t{};
+    t.nfields = f.n;
+    int rowsum = 0;
+    for (int i = 0; i < f.n; i++) {
+        const int64_t rb = bpr * f.size[i];
+        if (rb % 16 != 0 || rb > (1 << 20)) return false;
+        t.rowbytes[i] = (int) rb; rowsum += (int) rb;
+        for (int mi = 0; mi < a.nmat; mi++) if (((uintptr_t) a.mat[mi].w.p[i] & 15) != 0) return false;
+    }
+    const int nslices = (a.steps + 31) / 32;
+    const int iters = (nslices + 15) / 16;
+    if (iters > 2) return false;
+    const int nwarps = (nslices + iters - 1) / iters;
+    // small launches (a 4096 x 4096 q4_0 matrix is 64 KB per SM) are pure latency: the register path of gemv4 is quicker there
+    const double min_mb = getenv("B200_GEMV5_MIN_MB") ? atof(getenv("B200_GEMV5_MIN_MB")) : 12.0;     // (read per launch: tests switch it)
+    int64_t mtot = 0; for (int i = 0; i < a.nmat; i++) mtot += a.mat[i].M;
+    if ((double) mtot * rowsum < min_mb * 1e6) return false;
+    const int rt_env = getenv("B200_GEMV5_ROWS") ? atoi(getenv("B200_GEMV5_ROWS")) : 0;
+    int rt = rt_env == 4 || rt_env == 8 || rt_env == 16 ? rt_env : 8;                                                         // B200 sweep: 8 rows (18-65 KB tiles)
+    if (rt * rowsum > 72 * 1024) rt = 4;
+    if (rt * rowsum > 72 * 1024) return false;
+    int off = 0;
+    for (int i = 0; i < f.n; i++) { t.foff[i] = off; off += rt * t.rowbytes[i]; }
+    t.tile_bytes = (off + 15) & ~15;
+    if (rt == 16)     *err = iters == 1 ? launch_g5<TYPE, 16, 1>(a, t, nwarps, st, pdl) : launch_g5<TYPE, 16, 2>(a, t, nwarps, st, pdl);
+    else if (rt == 8) *err = iters == 1 ? launch_g5<TYPE, 8, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 8, 2>(a, t, nwarps, st, pdl);
+    else              *err = iters == 1 ? launch_g5<TYPE, 4, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 4, 2>(a, t, nwarps, st, pdl);
+    return true;
+}
+
 template <int TYPE, int NCOLS, bool FQ = false>
 static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
     constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
+    if constexpr (NCOLS == 1 && !FQ) {
+        cudaError_t e5 = cudaSuccess;
+        if (try_gemv5<TYPE>(a, st, pdl, &e5)) return e5;
+    }
     if constexpr (NCOLS == 1) {
         // rows per CTA, from the B200 sweep (profiles/r01_b_gemv_rows_sweep.txt): tall matrices want 8, long rows 2, else 4
         int64_t mtot = 0; for (int i = 0; i < a.nmat; i++) mtot += a.mat[i].M;

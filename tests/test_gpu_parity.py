@@ -249,3 +249,24 @@ def test_async_copies_are_stream_ordered():
         got = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(n,)).copy()
         assert np.array_equal(got, a + a)
         B._ck(B.lib().b200_host_free(s.h, hx)); B._ck(B.lib().b200_host_free(s.h, hy))
+
+
+@pytest.mark.parametrize("rows", [4, 8, 16])
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q8_0, O.Q4_K, O.Q6_K])
+@pytest.mark.parametrize("M,K", [(301, 4096), (64, 2048), (130, 14336), (40, 28672)])
+def test_gemv5_tma_tiles(monkeypatch, t, rows, M, K):
+    """the TMA-staged GEMV (gemv5: one bulk copy per SoA field into shared memory) is normally used from 12 MB per launch up;
+    forced here for small matrices, ragged last tiles (M % rows != 0), two slices per warp (K = 28672) and every tile height.
+    Same integer dots and scales as gemv4 -> same bar against the oracle."""
+    monkeypatch.setenv("B200_GEMV5_MIN_MB", "0")
+    monkeypatch.setenv("B200_GEMV5_ROWS", str(rows))
+    rng = np.random.default_rng(M + K + t + rows)
+    raw = O.random_blocks(t, M, K, rng)
+    x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    with B.Session(0) as s:
+        w = s.weights(t, raw, K)
+        got = s.mulmat(w, x)
+        ref1 = O.mul_mat(t, raw, x, 1)
+        assert nmse(got, ref1) <= 1e-9, nmse(got, ref1)
+        assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
+        w.free()
