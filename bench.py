@@ -28,7 +28,7 @@ for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "ggml-hexagon_b200"))
 
 Q4_0 = 2
 METRIC = "tokens/s Llama Q4_0 decode (tg, MUL_MAT+ADD path, batch 1)"
-# dram__bytes_read + dram__bytes_write of the step's gemv4_kernel launches / 225 MUL_MAT ops (129 grouped launches), from the
+# dram__bytes_read + dram__bytes_write of the step's GEMV launches / 225 MUL_MAT ops (129 grouped launches), from the
 # ncu --set full capture of this bench command (profiles/r01_e_ncu_gemv4_full_llama2_7b.txt: 113.966 MB per layer + the
 # 73.73 MB output matrix) -- equal to the algorithmic bytes within 0.2 %
 TRAFFIC_PER_LAUNCH = int((32 * 113.966e6 + 73.73e6) / 225)
@@ -520,7 +520,7 @@ def run_b200(args, rank, world):
                        ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores {value, seq} slots into peer HBM over NVLink, polled by a gather kernel per op; B200_RS_PROTO=flag: plain stores + flag exchange)"
                         if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv4_kernel<q4_0,1,R>",
+                         "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv5_kernel<q4_0,8,1> (launches >= 12 MB; gemv4_kernel<q4_0,1,4> for wo)",
                          "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
             "e2e": {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
                     "timer": "host perf_counter around K x (h2d_async from pinned memory + graph_compute + d2h_async + synchronize)"},
