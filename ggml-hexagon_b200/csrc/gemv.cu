@@ -170,13 +170,18 @@ gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // (static indices into the kernel parameters: a run-time index makes the compiler copy them to local memory)
         uint32_t total = 0;
-        for (int i = 0; i < t.nfields; i++) total += (uint32_t) (nrows * t.rowbytes[i]);
+        #pragma unroll
+        for (int i = 0; i < 4; i++) total += (uint32_t) (nrows * t.rowbytes[i]);           // unused fields have rowbytes 0
         asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(mbar), "r"(total) : "memory");
-        for (int i = 0; i < t.nfields; i++) {
-            const uint8_t * src = mt.w.p[i] + row0 * t.rowbytes[i];
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                         :: "r"(g5_smem(g5_sm + t.foff[i])), "l"(src), "r"((uint32_t) (nrows * t.rowbytes[i])), "r"(mbar) : "memory");
+        #pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < t.nfields) {
+                const uint8_t * src = mt.w.p[i] + row0 * t.rowbytes[i];
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"(g5_smem(g5_sm + t.foff[i])), "l"(src), "r"((uint32_t) (nrows * t.rowbytes[i])), "r"(mbar) : "memory");
+            }
         }
     }
     __syncthreads();                             // the barrier is initialised for everyone
@@ -194,7 +199,7 @@ gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
     }
     WPtrs sw;
     #pragma unroll
-    for (int i = 0; i < 4; i++) sw.p[i] = g5_sm + t.foff[i < t.nfields ? i : 0];
+    for (int i = 0; i < 4; i++) sw.p[i] = g5_sm + t.foff[i];
     {   // wait for the tile
         uint32_t ok = 0;
         while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar) : "memory");
