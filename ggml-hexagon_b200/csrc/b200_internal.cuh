@@ -111,6 +111,8 @@ cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter,
 cudaError_t launch_rowsplit_wait(uint32_t * local_flags, uint32_t * counter, int npeers, const int * peer_rank, cudaStream_t st);
 // fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
 cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
+// all ncols (2 .. 31) columns of a.act in ONE launch over shared-memory tiles (gemv5n); false: not eligible, *err untouched
+bool launch_gemv_cols(int type, GemvArgs & a, int ncols, cudaStream_t st, cudaError_t * err);
 bool gemv_pdl_enabled();
 bool gemv_fuseq_enabled();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)

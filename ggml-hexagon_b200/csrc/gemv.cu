@@ -245,6 +245,101 @@ gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
     }
 }
 
+// ------------------------------------------------------------------------------------------------ gemv5n: several columns per tile
+// 2 .. 31 activation columns (small batches, speculative decoding; test-backend-ops n = 2..8): the tile is fetched ONCE and
+// stays in shared memory while the CTA walks over all columns, NC at a time (a weight fragment is read from shared memory once
+// per NC columns; the lane keeps NC activation blocks in registers).  The register-path gemv4 re-reads the weights from
+// HBM / L2 for every chunk of 8 columns and the activations of every column for every group of R rows.
+template <int TYPE, int RT, int ITERS, int NC>
+__global__ void __launch_bounds__(512)
+gemv5n_kernel(const GemvArgs a, const Gemv5Tile t, const int ncols) {
+    using W = WT<TYPE>;
+    using A = WR<TYPE>;
+    extern __shared__ __align__(128) uint8_t g5_sm[];
+    float (*part)[NC * RT + 1] = (float (*)[NC * RT + 1]) (g5_sm + t.tile_bytes);
+    const uint32_t mbar = g5_smem(g5_sm + t.tile_bytes + 16 * (NC * RT + 1) * 4);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int steps = a.steps;
+#if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();
+#endif
+    const GemvMat & mt = a.mat[0];
+    const int64_t M = mt.M;
+    const int64_t row0 = (int64_t) blockIdx.x * RT;
+    const int nrows = (int) (M - row0 < RT ? M - row0 : RT);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        uint32_t total = 0;
+        #pragma unroll
+        for (int i = 0; i < 4; i++) total += (uint32_t) (nrows * t.rowbytes[i]);
+        asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(mbar), "r"(total) : "memory");
+        #pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (i < t.nfields) {
+                const uint8_t * src = mt.w.p[i] + row0 * t.rowbytes[i];
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"(g5_smem(g5_sm + t.foff[i])), "l"(src), "r"((uint32_t) (nrows * t.rowbytes[i])), "r"(mbar) : "memory");
+            }
+        }
+    }
+    __syncthreads();
+#if __CUDA_ARCH__ >= 900
+    cudaGridDependencySynchronize();
+#endif
+    WPtrs sw;
+    #pragma unroll
+    for (int i = 0; i < 4; i++) sw.p[i] = g5_sm + t.foff[i];
+    int sidx[ITERS];
+    #pragma unroll
+    for (int it = 0; it < ITERS; it++) sidx[it] = (warp + it * nwarps) * 32 + lane;
+    {
+        uint32_t ok = 0;
+        while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar) : "memory");
+    }
+    constexpr int SH = 5 - Log2<RT>::v;
+    for (int c0 = 0; c0 < ncols; c0 += NC) {
+        float acc[NC][RT];
+        #pragma unroll
+        for (int c = 0; c < NC; c++)
+            #pragma unroll
+            for (int r = 0; r < RT; r++) acc[c][r] = 0.f;
+        #pragma unroll
+        for (int it = 0; it < ITERS; it++) {
+            const int s = sidx[it];
+            if (s < steps) {
+                typename A::Act av[NC];
+                #pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    const ActCol ac(a.act, c0 + c < ncols ? c0 + c : c0);       // (past the end: a valid column, result unused)
+                    av[c] = A::load_act(ac, s);
+                }
+                #pragma unroll
+                for (int r = 0; r < RT; r++) {
+                    if (r < nrows) {
+                        const typename W::Frag f = W::loads(sw, r * steps + s);
+                        #pragma unroll
+                        for (int c = 0; c < NC; c++) acc[c][r] += wr_dot<TYPE>(f, av[c], s);
+                    }
+                }
+            }
+        }
+        #pragma unroll
+        for (int c = 0; c < NC; c++) {
+            const float v = reduce_rows<RT>(acc[c], lane);
+            if ((lane & ((1 << SH) - 1)) == 0) part[warp][c * RT + (lane >> SH)] = v;
+        }
+        __syncthreads();
+        if (tid < NC * RT) {
+            float v = 0.f;
+            for (int q = 0; q < nwarps; q++) v += part[q][tid];
+            const int c = tid / RT, r = tid - c * RT;
+            if (row0 + r < M && c0 + c < ncols) mt.dst[(int64_t) (c0 + c) * a.dcs + row0 + r] = v;
+        }
+        __syncthreads();                         // part is reused by the next column group
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ launch
 struct Tune { int rows = 0; bool pdl = true; };    // rows 0 = per-shape heuristic
 static const Tune & tune() {
@@ -336,6 +431,67 @@ static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err
     else if (rt == 8) *err = iters == 1 ? launch_g5<TYPE, 8, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 8, 2>(a, t, nwarps, st, pdl);
     else              *err = iters == 1 ? launch_g5<TYPE, 4, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 4, 2>(a, t, nwarps, st, pdl);
     return true;
+}
+
+// several columns in one launch (gemv5n); false = not eligible, the caller falls back to 8-column gemv4 chunks
+template <int TYPE, int RT, int ITERS, int NC>
+static cudaError_t launch_g5n(GemvArgs & a, const Gemv5Tile & t, int nwarps, int ncols, cudaStream_t st, bool pdl) {
+    static int smem_set = 0;
+    const int smem = t.tile_bytes + 16 * (NC * RT + 1) * 4 + 16;
+    if (smem > smem_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemv5n_kernel<TYPE, RT, ITERS, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        smem_set = smem;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) ((a.mat[0].M + RT - 1) / RT)); cfg.blockDim = dim3(nwarps * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, gemv5n_kernel<TYPE, RT, ITERS, NC>, a, t, ncols);
+}
+template <int TYPE>
+static bool try_gemv5n(GemvArgs & a, int ncols, cudaStream_t st, bool pdl, cudaError_t * err) {
+    const int mode = getenv("B200_GEMV5N") ? atoi(getenv("B200_GEMV5N")) : 1;            // 0: off (gemv4 chunks)
+    // (2 and 3 columns: the register path is as fast or faster -- 13.1 / 14.7 us against 14.8 / 14.9 us for q4_0 4096 x 14336)
+    if (!mode || a.nmat != 1 || a.npeers > 0 || a.mat[0].add_dst || ncols < (mode == 2 ? 2 : 4)) return false;
+    const WFields f = wfields(TYPE);
+    const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);
+    Gemv5Tile t{};
+    t.nfields = f.n;
+    int rowsum = 0;
+    for (int i = 0; i < f.n; i++) {
+        const int64_t rb = bpr * f.size[i];
+        if (rb % 16 != 0 || rb > (1 << 20) || ((uintptr_t) a.mat[0].w.p[i] & 15) != 0) return false;
+        t.rowbytes[i] = (int) rb; rowsum += (int) rb;
+    }
+    const int nslices = (a.steps + 31) / 32;
+    const int iters = (nslices + 15) / 16;
+    if (iters > 2) return false;
+    const int nwarps = (nslices + iters - 1) / iters;
+    int rt = 8;
+    if (rt * rowsum > 72 * 1024) rt = 4;
+    if (rt * rowsum > 72 * 1024) return false;
+    int off = 0;
+    for (int i = 0; i < f.n; i++) { t.foff[i] = off; off += rt * t.rowbytes[i]; }
+    t.tile_bytes = (off + 15) & ~15;
+    constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
+    constexpr int NC = KQ ? 2 : 4;                                                        // columns per pass (registers)
+    if (rt == 8) *err = iters == 1 ? launch_g5n<TYPE, 8, 1, NC>(a, t, nwarps, ncols, st, pdl) : launch_g5n<TYPE, 8, 2, NC>(a, t, nwarps, ncols, st, pdl);
+    else         *err = iters == 1 ? launch_g5n<TYPE, 4, 1, NC>(a, t, nwarps, ncols, st, pdl) : launch_g5n<TYPE, 4, 2, NC>(a, t, nwarps, ncols, st, pdl);
+    return true;
+}
+bool launch_gemv_cols(int type, GemvArgs & a, int ncols, cudaStream_t st, cudaError_t * err) {
+    a.steps = (int) (a.K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
+    const bool pdl = tune().pdl;
+    switch (type) {
+        case T_Q4_0: return try_gemv5n<T_Q4_0>(a, ncols, st, pdl, err);
+        case T_Q8_0: return try_gemv5n<T_Q8_0>(a, ncols, st, pdl, err);
+        case T_Q4_K: return try_gemv5n<T_Q4_K>(a, ncols, st, pdl, err);
+        case T_Q6_K: return try_gemv5n<T_Q6_K>(a, ncols, st, pdl, err);
+    }
+    return false;
 }
 
 template <int TYPE, int NCOLS, bool FQ = false>

@@ -500,6 +500,15 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; const int64_t rw[1] = {M};
                   rc = rs_fill(c, a, dp, db_, 1, rw, N == 1 && s1->ne[2] == 1 && s1->ne[3] == 1); if (rc) return rc; }
                 const int rs_signal = a.rs_signal;
+                bool done = false;
+                if (N > 1 && N < 0x7fff) {                  // small batch: one launch over shared-memory tiles, weights read once
+                    a.act = ActView{c->act_qs, c->act_ds, NB};
+                    a.mat[0].dst = y;
+                    cudaError_t e5 = cudaSuccess;
+                    done = launch_gemv_cols(s0->type, a, (int) N, c->st, &e5);
+                    if (done) { CU(e5); c->launches++; }
+                }
+                if (!done)
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
                     a.rs_signal = (c0 + 8 >= N && i12 == s1->ne[2] - 1 && i13 == s1->ne[3] - 1) ? rs_signal : 0;   // once per op

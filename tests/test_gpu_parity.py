@@ -270,3 +270,22 @@ def test_gemv5_tma_tiles(monkeypatch, t, rows, M, K):
         assert nmse(got, ref1) <= 1e-9, nmse(got, ref1)
         assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
         w.free()
+
+
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q8_0, O.Q4_K, O.Q6_K])
+@pytest.mark.parametrize("M,K,N", [(200, 2048, 2), (301, 4096, 5), (64, 4096, 13), (130, 14336, 8), (96, 28672, 31)])
+def test_small_batch_columns(monkeypatch, t, M, K, N):
+    """2 .. 31 activation columns: one launch over shared-memory weight tiles (gemv5n), all columns from one copy of the tile;
+    must equal the single-column results column by column (same integer dots and scales; float sums in the same order)."""
+    monkeypatch.setenv("B200_GEMV5N", "2")        # also for 2 and 3 columns (default: from 4 up)
+    rng = np.random.default_rng(M + K + N + t)
+    raw = O.random_blocks(t, M, K, rng)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    with B.Session(0) as s:
+        w = s.weights(t, raw, K)
+        got = s.mulmat(w, x)
+        one = np.concatenate([s.mulmat(w, x[i:i + 1]) for i in range(N)])
+        assert got.shape == (N, M)
+        assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-9
+        assert nmse(got, one) <= 1e-12
+        w.free()
