@@ -414,8 +414,11 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
     const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
-    // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N, development knob)
-    static const int gemm_min_n = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : 32;
+    // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N overrides).  Measured crossover
+    // against the shared-memory-tile GEMV (gemv5n) on B200: q4_0 4096 x 4096 33 vs 37 us at 48 columns, 43 vs 37 us at 64;
+    // q4_K 44 vs 50 us at 32 columns, 77 vs 50 us at 48
+    const int gemm_min_env = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : -1;
+    const int gemm_min_n = gemm_min_env >= 0 ? gemm_min_env : (s0->type == T_Q4_K || s0->type == T_Q6_K ? 36 : 52);
     const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
                           M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 && !c->rs_on;
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }

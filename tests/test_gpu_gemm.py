@@ -15,6 +15,12 @@ def nmse(a, b):
     return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
 
 
+@pytest.fixture(autouse=True)
+def _gemm_from_16_columns(monkeypatch):
+    """the tensor-core path normally takes over at 36 (K-quants) / 52 columns; these tests want it for the small shapes too"""
+    monkeypatch.setenv("B200_GEMM_MIN_N", "16")
+
+
 @pytest.fixture(scope="module")
 def sess():
     s = B.Session(0)
