@@ -341,6 +341,29 @@ def time_prefill(B, s, model, N=512, mixes=(("q8_0", lambda name: Q8_0), ("q4_0"
     return res
 
 
+def time_add(B, s, iters=50):
+    """GGML_OP_ADD: f32 ne=[4096] (launch latency: report us) and [4096, 512] (HBM-bound: 3 x nbytes / time)"""
+    import ctypes as C
+    out = []
+    for ne in ([4096], [4096, 512]):
+        n = int(np.prod(ne))
+        a, b, d = s.malloc(4 * n), s.malloc(4 * n), s.malloc(4 * n)
+        t0, t1, td = B.f32_tensor(a.ptr, ne), B.f32_tensor(b.ptr, ne), B.f32_tensor(d.ptr, ne, op=B.OP_ADD)
+        for _ in range(3):
+            B._ck(B.lib().b200_add(s.h, C.byref(t0), C.byref(t1), C.byref(td)))
+        s.sync()
+        e0, e1 = s.event(), s.event()
+        s.record(e0)
+        for _ in range(iters):
+            B._ck(B.lib().b200_add(s.h, C.byref(t0), C.byref(t1), C.byref(td)))
+        s.record(e1)
+        us = s.elapsed_ms(e0, e1) * 1e3 / iters
+        out.append({"ne": ne, "us": round(us, 2), "GB/s": round(3 * 4 * n / us / 1e3, 1)})
+        for x in (a, b, d):
+            x.free()
+    return out
+
+
 def time_kquant(B, s, steps):
     """BASELINE.json configs[3]: Llama-3-8B shapes with a Q4_K_M-like q4_K / q6_K mix: decode step (same node list shape as the
     headline workload) and pp512"""
@@ -498,6 +521,7 @@ def run_b200(args, rank, world):
     shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
     prefill = time_prefill(B, s, model) if world == 1 and not args.no_shapes and rank == 0 else None
     kquant = None
+    adds = time_add(B, s) if world == 1 and not args.no_shapes and rank == 0 else None
     if world == 1 and not args.no_shapes and rank == 0:
         wl.free()
         kquant = time_kquant(B, s, args.steps)
@@ -519,7 +543,7 @@ def run_b200(args, rank, world):
                        "submit": "one b200_graph_compute (CUDA graph + PDL)" if world == 1 else
                        ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores {value, seq} slots into peer HBM over NVLink, polled by a gather kernel per op; B200_RS_PROTO=flag: plain stores + flag exchange)"
                         if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "frac_of_nominal_8000": round(achieved / 8000.0, 4),
                          "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv5_kernel<q4_0,8,1> (launches >= 12 MB; gemv4_kernel<q4_0,1,4> for wo)",
                          "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
             "e2e": {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
@@ -531,6 +555,8 @@ def run_b200(args, rank, world):
         line["pp512"] = prefill
     if kquant:
         line["kquant"] = kquant
+    if adds:
+        line["add"] = adds
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
     sys.stdout.flush()
