@@ -706,11 +706,12 @@ min_term_kernel(const float * __restrict__ mA, const float * __restrict__ sB, co
 template <int WS, int KIND>
 static cudaError_t gemm_i8_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const CUtensorMap & tmS,
                                     const GemmI8Args & p, int grid, cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
+    static bool attr_done[64] = {false};          // per device
+    int dev = 0; cudaGetDevice(&dev); dev &= 63;
+    if (!attr_done[dev]) {
         cudaError_t e = cudaFuncSetAttribute(gemm_i8_kernel<WS, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, GM_SMEM);
         if (e != cudaSuccess) return e;
-        attr_done = true;
+        attr_done[dev] = true;
     }
     gemm_i8_kernel<WS, KIND><<<(unsigned) grid, GM_THREADS, GM_SMEM, st>>>(tmA, tmB, tmS, p);
     return cudaGetLastError();

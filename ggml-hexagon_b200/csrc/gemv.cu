@@ -380,12 +380,13 @@ static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
 // (bulk copies), at most 2 slices per warp, no in-kernel completion signal
 template <int TYPE, int RT, int ITERS>
 static cudaError_t launch_g5(GemvArgs & a, const Gemv5Tile & t, int nwarps, cudaStream_t st, bool pdl) {
-    static int smem_set = 0;
+    static int smem_set[64] = {0};                // per device: the attribute belongs to the device's copy of the function
+    int dev = 0; cudaGetDevice(&dev); dev &= 63;
     const int smem = t.tile_bytes + 16 * (RT + 1) * 4 + 16;
-    if (smem > smem_set) {
+    if (smem > smem_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(gemv5_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     int total = 0;
     for (int i = 0; i < a.nmat; i++) { total += (int) ((a.mat[i].M + RT - 1) / RT); a.cta_end[i] = total; }
@@ -436,12 +437,13 @@ static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err
 // several columns in one launch (gemv5n); false = not eligible, the caller falls back to 8-column gemv4 chunks
 template <int TYPE, int RT, int ITERS, int NC>
 static cudaError_t launch_g5n(GemvArgs & a, const Gemv5Tile & t, int nwarps, int ncols, cudaStream_t st, bool pdl) {
-    static int smem_set = 0;
+    static int smem_set[64] = {0};
+    int dev = 0; cudaGetDevice(&dev); dev &= 63;
     const int smem = t.tile_bytes + 16 * (NC * RT + 1) * 4 + 16;
-    if (smem > smem_set) {
+    if (smem > smem_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(gemv5n_kernel<TYPE, RT, ITERS, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) ((a.mat[0].M + RT - 1) / RT)); cfg.blockDim = dim3(nwarps * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;

@@ -61,3 +61,22 @@ def test_rowsplit_two_ranks(t, use_graph):
     assert np.array_equal(sess[0].to_host(bufs[0][3], (M,), np.float32), sess[1].to_host(bufs[1][3], (M,), np.float32))
     for s in sess:
         s.close()
+
+
+def test_second_device_large_shared_memory_kernels(monkeypatch):
+    """kernels that opt in to more than 48 KB of dynamic shared memory (gemv5 tiles of long rows, the tensor-core GEMM) carry that
+    attribute per device: a session on device 1 of the same process must work after device 0 has used them"""
+    if B.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    monkeypatch.setenv("B200_GEMV5_MIN_MB", "0")
+    rng = np.random.default_rng(5)
+    M, K = 64, 14336                                  # q4_0 row = 8064 B -> 8-row tile = 64.5 KB
+    raw = O.random_blocks(O.Q4_0, M, K, rng)
+    x1 = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    xn = rng.uniform(-1, 1, (64, K)).astype(np.float32)
+    for dev in (0, 1):
+        with B.Session(dev) as s:
+            w = s.weights(O.Q4_0, raw, K)
+            assert nmse(s.mulmat(w, x1), O.mul_mat(O.Q4_0, raw, x1, 1)) <= 1e-9
+            assert nmse(s.mulmat(w, xn), O.mul_mat(O.Q4_0, raw, xn, 1)) <= 1e-9
+            w.free()
