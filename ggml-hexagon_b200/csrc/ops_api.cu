@@ -75,6 +75,7 @@ struct Ctx {
     uint8_t * flush = nullptr; size_t flush_bytes = 0;
     int64_t launches = 0;
     bool in_graph = false;        // inside b200_graph_compute: src1 quantisation may be reused between nodes
+    uint64_t scratch_gen = 0;     // bumped whenever a scratch buffer moves: captured graphs hold the old addresses and must not match any more
     const void * q_ptr = nullptr; int64_t q_K = 0, q_N = 0, q_stride = 0;
     std::unordered_map<uint64_t, GraphEntry> graphs;
     std::unordered_map<uint64_t, StreamProgram> programs;
@@ -112,6 +113,7 @@ static int ensure_act(Ctx * c, int64_t blocks) {
     CU(cudaMalloc((void **) &c->act_ds, (size_t) cap * sizeof(ActDS)));
     c->act_cap = cap;
     c->q_ptr = nullptr;
+    c->scratch_gen++;
     return 0;
 }
 template <typename T>
@@ -120,6 +122,7 @@ static int ensure_buf(Ctx * c, T ** p, size_t * cap, size_t bytes) {
     if (*p) { CU(cudaStreamSynchronize(c->st)); cudaFree(*p); *p = nullptr; *cap = 0; }
     CU(cudaMalloc((void **) p, bytes + 256));
     *cap = bytes;
+    c->scratch_gen++;
     return 0;
 }
 static int ensure_stage(Ctx * c, size_t bytes) {
@@ -403,6 +406,33 @@ static WPtrs wptrs_offset(const b200_tensor * s0, WPtrs wp, int64_t byte_off) {
     return wp;
 }
 
+// column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N overrides).  Measured crossover
+// against the shared-memory-tile GEMV (gemv5n) on B200: q4_0 4096 x 4096 33 vs 37 us at 48 columns, 43 vs 37 us at 64;
+// q4_K 44 vs 50 us at 32 columns, 77 vs 50 us at 48
+static int gemm_min_cols(int type) {
+    const int env = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : -1;
+    return env >= 0 ? env : (type == T_Q4_K || type == T_Q6_K ? 36 : 52);
+}
+// Scratch of the GEMM path for one MUL_MAT, sized for either MMA kind, allocated BEFORE a stream capture starts
+// (cudaMalloc / cudaStreamSynchronize are not allowed inside one); mulmat_dev's own ensure_buf calls then never reallocate.
+static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1) {
+    const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
+    const int mn = gemm_min_cols(s0->type);
+    if (!is_qweight(s0->type) || mn <= 0 || N < mn || K % 32 != 0 || M >= 0x7fffffff || N >= 0x7fffffff || K >= 0x3fffffff) return 0;
+    const size_t ldb = (size_t) gemm_i8_ldb((int) N);
+    int rc;
+    rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+    rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) 2 * (K / 16) * ldb * sizeof(float)); if (rc) return rc;
+    rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc;
+    rc = ensure_buf(c, &c->gm_ws, &c->gm_ws_cap, (size_t) 2 * M * (K / 16) * sizeof(float)); if (rc) return rc;
+    int ksp = gemm_i8_ksplit((int) M, (int) N, (int) K, 1, c->sms);
+    const int k0 = gemm_i8_ksplit((int) M, (int) N, (int) (2 * K), 0, c->sms), k2 = gemm_i8_ksplit((int) M, (int) N, (int) K, 2, c->sms);
+    if (k0 > ksp) ksp = k0;
+    if (k2 > ksp) ksp = k2;
+    if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+    return 0;
+}
+
 static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst /*rowsplit*/,
                       const FusedAdd * fa = nullptr) {
     int rc = mulmat_check(s0, s1, d); if (rc) return rc;
@@ -414,11 +444,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
     const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
-    // column count from which the tensor-core GEMM takes over from the GEMV (B200_GEMM_MIN_N overrides).  Measured crossover
-    // against the shared-memory-tile GEMV (gemv5n) on B200: q4_0 4096 x 4096 33 vs 37 us at 48 columns, 43 vs 37 us at 64;
-    // q4_K 44 vs 50 us at 32 columns, 77 vs 50 us at 48
-    const int gemm_min_env = getenv("B200_GEMM_MIN_N") ? atoi(getenv("B200_GEMM_MIN_N")) : -1;
-    const int gemm_min_n = gemm_min_env >= 0 ? gemm_min_env : (s0->type == T_Q4_K || s0->type == T_Q6_K ? 36 : 52);
+    const int gemm_min_n = gemm_min_cols(s0->type);
     const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
                           M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 && !c->rs_on;
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
@@ -854,9 +880,12 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     }
     if (any_host) return fail(B200_ENOTSUP, "graph_compute takes device tensors only");
     int rc = ensure_act(c, need_act); if (rc) return rc;
+    if (use_cuda_graph && !c->rs_on)
+        for (int i = 0; i < n; i++)
+            if (nodes[i].dst.op == B200_OP_MUL_MAT) { rc = presize_gemm(c, &nodes[i].src0, &nodes[i].src1); if (rc) return rc; }
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
 
-    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->act_qs, sizeof(void *))) ^ (c->rs_on ? 0x9e3779b97f4a7c15ull : 0);
+    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->scratch_gen, sizeof(c->scratch_gen))) ^ (c->rs_on ? 0x9e3779b97f4a7c15ull : 0);
     // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
     // opt-in while it is slower than the CUDA-graph replay of the per-node kernels (DESIGN.md has the trace numbers)
     static const bool stream_on = getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) != 0;

@@ -135,3 +135,54 @@ def test_gemm_split_k_small_m(sess, t):
     got = sess.mulmat(w, x)
     assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-10
     w.free()
+
+
+def test_gemm_inside_a_captured_graph(sess):
+    """a node list with tensor-core MUL_MATs submitted with use_cuda_graph: the GEMM scratch is sized before the stream
+    capture starts (allocations are not allowed inside one), the replay gives the same result as the direct launch"""
+    import ctypes as C
+    rng = np.random.default_rng(31)
+    M, K, N = 384, 2048, 96
+    ws, xs = [], rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    xb = sess.to_device(xs)
+    nodes, outs, raws = [], [], []
+    for t in (O.Q8_0, O.Q4_K, O.Q6_K):
+        raw = O.random_blocks(t, M, K, rng)
+        w = sess.weights(t, raw, K)
+        d = sess.malloc(4 * M * N)
+        n = B.Node()
+        n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(d.ptr, [M, N], op=B.OP_MUL_MAT)
+        nodes.append(n); ws.append(w); outs.append(d); raws.append((t, raw))
+    arr = (B.Node * len(nodes))(*nodes)
+    for _ in range(2):                                    # capture, then replay
+        sess.graph_compute(arr, 2)
+    sess.sync()
+    for (t, raw), d in zip(raws, outs):
+        got = sess.to_host(d, (N, M), np.float32)
+        assert nmse(got, O.mul_mat(t, raw, xs, 1)) <= 1e-10
+    for b in ws + outs + [xb]:
+        b.free()
+
+
+def test_captured_graph_survives_scratch_growth():
+    """a captured graph bakes the scratch addresses in; when a later, bigger op moves the scratch, the old graph must not be
+    replayed (the cache key carries a scratch generation) -- the same node list is captured again and stays correct"""
+    rng = np.random.default_rng(37)
+    with B.Session(0) as s:
+        M, K, N = 128, 1024, 64
+        raw = O.random_blocks(O.Q4_0, M, K, rng)
+        w = s.weights(O.Q4_0, raw, K)
+        x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+        xb, d = s.to_device(x), s.malloc(4 * M * N)
+        n = B.Node()
+        n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(d.ptr, [M, N], op=B.OP_MUL_MAT)
+        arr = (B.Node * 1)(n)
+        s.graph_compute(arr, 2); s.graph_compute(arr, 2)
+        ref = O.mul_mat(O.Q4_0, raw, x, 1)
+        assert nmse(s.to_host(d, (N, M), np.float32), ref) <= 1e-10
+        big = O.random_blocks(O.Q4_K, 1024, 4096, rng)
+        wb = s.weights(O.Q4_K, big, 4096)
+        s.mulmat(wb, rng.uniform(-1, 1, (256, 4096)).astype(np.float32))        # grows every GEMM scratch buffer
+        s.h2d(d, np.zeros((N, M), np.float32))
+        s.graph_compute(arr, 2)
+        assert nmse(s.to_host(d, (N, M), np.float32), ref) <= 1e-10
