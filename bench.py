@@ -157,9 +157,12 @@ def measured_peak_hbm():
 class DecodeWorkload:
     """All MUL_MAT/ADD nodes of one decoded token, device resident.  Row r-th slice of every weight when world > 1."""
 
-    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0"):
+    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0", ncols=1, share=None):
+        """ncols > 1: the same node list over ncols activation columns (prefill); share: another workload of the same model and
+        quant whose HBM weights are used instead of uploading a second copy"""
         import ctypes as C
         self.mode = mode
+        self.ncols, self.share = ncols, share
         wt = quant_mix(quant)
         self.quant = quant
         self.B, self.s, self.C = B, sess, C
@@ -175,10 +178,14 @@ class DecodeWorkload:
             assert M % world == 0, (name, M, world)
             full_rows = M // world
             # one random host matrix per shape; every layer gets its own HBM copy (distinct addresses, no L2 reuse)
-            host[name] = random_weights(wt(name), full_rows, K, rng)
-        for _ in range(L):
-            self.weights.append({name: sess.weights(wt(name), host[name], K) for name, M, K in layer})
-        self.w_out = sess.weights(wt(out[0]), host[out[0]], out[2])
+            if share is None:
+                host[name] = random_weights(wt(name), full_rows, K, rng)
+        if share is not None:
+            self.weights, self.w_out = share.weights, share.w_out
+        else:
+            for _ in range(L):
+                self.weights.append({name: sess.weights(wt(name), host[name], K) for name, M, K in layer})
+            self.w_out = sess.weights(wt(out[0]), host[out[0]], out[2])
         self.layer, self.out = layer, out
         for name, M, K in layer:
             self.alg_bytes += L * gemv_bytes(M, K, blk=BLK[wt(name)])
@@ -191,19 +198,20 @@ class DecodeWorkload:
         # row split: activations live in the symmetric heap (same offsets on every rank) so that the GEMVs can store
         # their slices straight into every peer's copy over NVLink
         self.heap = B.SymHeap(sess, 4 * (8 * h + 2 * kv + 2 * f + out[1]) + 64 * 256) if world > 1 else None
-        mk = (lambda n: self.heap.malloc(4 * n)) if world > 1 else (lambda n: sess.malloc(4 * n))
+        mk = (lambda n: self.heap.malloc(4 * n)) if world > 1 else (lambda n: sess.malloc(4 * n * ncols))
         self.x = mk(h); self.q = mk(h); self.k = mk(kv); self.v = mk(kv); self.o = mk(h); self.hres = mk(h)
         self.g = mk(f); self.u = mk(f); self.dn = mk(h); self.x2 = mk(h); self.x3 = mk(h); self.logits = mk(out[1])
-        self.x_host = np.random.default_rng(seed + 1).uniform(-1, 1, h).astype(np.float32)
+        self.x_host = np.random.default_rng(seed + 1).uniform(-1, 1, h * ncols).astype(np.float32)
         sess.h2d(self.x, self.x_host)
         self._nodes = None
         self._build()
 
     def free(self):
-        for lw in self.weights:
-            for w in lw.values():
-                w.free()
-        self.w_out.free()
+        if self.share is None:
+            for lw in self.weights:
+                for w in lw.values():
+                    w.free()
+            self.w_out.free()
         if self.heap is None:
             for b in (self.x, self.q, self.k, self.v, self.o, self.hres, self.g, self.u, self.dn, self.x2, self.x3, self.logits):
                 b.free()
@@ -212,14 +220,15 @@ class DecodeWorkload:
         B = self.B
         n = B.Node()
         n.src0 = w.tensor()
-        n.src1 = B.f32_tensor(src.ptr, [K, 1])
-        n.dst = B.f32_tensor(dst.ptr, [M, 1], op=B.OP_MUL_MAT)
+        n.src1 = B.f32_tensor(src.ptr, [K, self.ncols])
+        n.dst = B.f32_tensor(dst.ptr, [M, self.ncols], op=B.OP_MUL_MAT)
         return n
 
     def _add(self, a, b, dst, n_el):
         B = self.B
         n = B.Node()
-        n.src0, n.src1, n.dst = B.f32_tensor(a.ptr, [n_el]), B.f32_tensor(b.ptr, [n_el]), B.f32_tensor(dst.ptr, [n_el], op=B.OP_ADD)
+        ne = [n_el] if self.ncols == 1 else [n_el, self.ncols]
+        n.src0, n.src1, n.dst = B.f32_tensor(a.ptr, ne), B.f32_tensor(b.ptr, ne), B.f32_tensor(dst.ptr, ne, op=B.OP_ADD)
         return n
 
     def _build(self):
@@ -335,10 +344,61 @@ def time_prefill(B, s, model, N=512, mixes=(("q8_0", lambda name: Q8_0), ("q4_0"
             flops += reps * 2.0 * M * N * K
         res[name] = {"tokens_per_s": round(N / tot_s, 1), "ms": round(tot_s * 1e3, 3), "TOPS": round(flops / tot_s / 1e12, 1),
                      "frac_of_int8_nominal_4500": round(flops / tot_s / 4.5e15, 4), "shapes": per_shape}
-    res["note"] = ("N=%d columns, MUL_MAT only, operand preparation (activation quantise, weight unpack) inside the timed region; exact "
-                   "per-block tcgen05.mma sums + fp32 scale-accumulate: bound by the epilogue's issue slots, not the tensor pipe "
-                   "(DESIGN.md section 6)" % N)
+    mode = os.environ.get("B200_GEMM_MODE", "dense")
+    res["mode"] = mode
+    res["note"] = ("N=%d columns, MUL_MAT only, per shape back to back on one matrix (operand preparation inside the timed region); " % N +
+                   ("dense fp16 tcgen05.mma over the whole K with the block scales folded into the operands, weights from their cached fp16 "
+                    "shadow: bound by the L2 -> shared-memory operand feed of 128-row tiles (DESIGN.md section 6)" if mode != "exact" else
+                    "exact per-block tcgen05.mma sums + fp32 scale-accumulate: bound by the epilogue's issue slots, not the tensor pipe "
+                    "(DESIGN.md section 6)"))
     return res
+
+
+def with_env(name, value, fn):
+    old = os.environ.get(name)
+    os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        if old is None:
+            del os.environ[name]
+        else:
+            os.environ[name] = old
+
+
+def time_prefill_model(B, s, wl, N=512, steps=5):
+    """pp512 as llama-bench runs it, restricted to this path: ALL MUL_MAT + residual ADD nodes of the model over N = 512 columns
+    as one b200_graph_compute, every layer with its own weights (no L2 reuse between layers or steps).  The first call is timed
+    separately: it builds the fp16 weight shadows of the dense GEMM (2 bytes per weight beside the native blocks)."""
+    pw = DecodeWorkload(B, s, wl.model, quant=wl.quant, ncols=N, share=wl)
+    s.sync()
+    t0 = time.perf_counter()
+    pw.step()
+    s.sync()
+    first_s = time.perf_counter() - t0
+    for _ in range(2):
+        pw.step()
+    s.sync()
+    l0 = s.launch_count()
+    e0, e1 = s.event(), s.event()
+    s.record(e0)
+    for _ in range(steps):
+        pw.step()
+    s.record(e1)
+    sec = s.elapsed_ms(e0, e1) * 1e-3 / steps
+    launches = (s.launch_count() - l0) // steps
+    flops = 2.0 * N * (sum(m * k for _, m, k in wl.layer) * wl.L + wl.out[1] * wl.out[2])
+    tc_peak = None
+    try:
+        tc_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except (OSError, KeyError, ValueError):
+        pass
+    pw.free()
+    return {"tokens_per_s": round(N / sec, 1), "ms": round(sec * 1e3, 3), "TFLOPS": round(flops / sec / 1e12, 1),
+            "frac_of_measured_16bit_tensor_peak": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "tensor_peak_TFLOPS": tc_peak,
+            "kernels_per_step": int(launches), "first_call_ms": round(first_s * 1e3, 1),
+            "note": "whole node list (%d MUL_MAT + %d ADD) over N=%d columns, one graph_compute per step, distinct weights per layer; "
+                    "peak = MEASURED_PEAKS.json bf16_tflops_sustained (fp16 and bf16 run at the same tensor rate)" % (wl.n_mulmat, 2 * wl.L, N)}
 
 
 def time_add(B, s, iters=50):
@@ -381,8 +441,9 @@ def time_kquant(B, s, steps):
     out = {"workload": "llama3-8b-q4_K_M-like-decode (q6_K: wv, down, output; q4_K: the rest)", "tokens_per_s": round(1.0 / step_s, 2),
            "ms_per_step": round(step_s * 1e3, 4), "GB/s": round(wl.alg_bytes / step_s / 1e9, 1),
            "hbm_frac": round(wl.alg_bytes / step_s / 1e9 / peak, 4), "weight_bytes": wl.weight_bytes_local}
-    wl.free()
     out["pp512"] = time_prefill(B, s, "llama3-8b", mixes=(("q4_K_M", quant_mix("q4_K_M")),))["q4_K_M"]
+    out["pp512"]["model"] = time_prefill_model(B, s, wl)
+    wl.free()
     return out
 
 
@@ -519,7 +580,11 @@ def run_b200(args, rank, world):
     clocks = sampler.stop()
     logits = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(wl.out[1],)).copy()
     shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
-    prefill = time_prefill(B, s, model) if world == 1 and not args.no_shapes and rank == 0 else None
+    prefill = None
+    if world == 1 and not args.no_shapes and rank == 0:
+        prefill = time_prefill(B, s, model)
+        prefill["exact_mode"] = with_env("B200_GEMM_MODE", "exact", lambda: time_prefill(B, s, model, iters=3))
+        prefill["model"] = time_prefill_model(B, s, wl)
     kquant = None
     adds = time_add(B, s) if world == 1 and not args.no_shapes and rank == 0 else None
     if world == 1 and not args.no_shapes and rank == 0:

@@ -1,0 +1,350 @@
+// gemm_dense.cu — prefill MUL_MAT as a DENSE fp16 tensor-core contraction: tcgen05.mma kind::f16 accumulating the whole K in
+// TMEM, operands staged by TMA, one TMEM read per output tile.
+//
+// Same seat as gemm_i8.cu (ggml_compute_forward_mul_mat_one_chunk for src1 with many columns, ggml-dsp.c:1091-1189 /
+// ggml-cpu.c:6655-6743), different contract.  gemm_i8.cu keeps every per-block integer sum exact and therefore has to pull each
+// 32-element block's 128 x 128 sums out of the tensor core and scale them on the CUDA cores: it is bound by that epilogue, not
+// by the tensor pipe.  Here the block scales are folded into the OPERANDS instead:
+//     A[m, k] = fp16( d_w[m, b(k)] * q_w[m, k] )      = dequantize_row_<type> (ggml-quants.c:307-325, 347-363, 1352-1374,
+//                                                        1681-1710) rounded to fp16
+//     B[n, k] = fp16( d_a[n, b(k)] * q_a[n, k] )      = the q8_1 quantisation the reference applies to src1
+//                                                        (quantize_row_q8_1_ref, ggml-quants.c:220-253), dequantised again
+//     dst[m, n] = sum_k A[m, k] * B[n, k]             f32 accumulation in TMEM
+// so the contraction is dense and the accumulator runs over the whole K.  What changes against the reference is only the
+// rounding of the two dequantised operands to fp16 (relative 2^-12 each; NMSE against ggml-cpu ~1e-7, the bar is 5e-4) and the
+// f32 summation order.  The q8_1 step is kept so that the result follows the reference's own quantisation of the activations.
+// |B| saturates at the fp16 maximum (activations beyond 65504 do not occur in the model families of the task).
+//
+// CTA (1 per SM, persistent over 128 x BN output tiles), 10 warps:
+//   warp 0      TMA producer: A = fp16 weights [M][K], B = fp16 activations [N][K]; boxes of 64 k (128 bytes) x 128 / BN rows,
+//               128-B swizzle, ring of GD_STAGES stages
+//   warp 1      TMEM allocation + MMA issue (one elected lane): 4 K16 MMAs per stage into one of two accumulator buffers,
+//               tcgen05.commit per stage (frees the ring slot) and per tile (hands the buffer to the epilogue)
+//   warps 2..9  epilogue: tcgen05.ld 32 lanes x 32 columns, coalesced f32 stores (32 consecutive m per column); the other
+//               buffer is being accumulated meanwhile
+#include "tc_common.cuh"
+
+#include <stdio.h>
+
+namespace b200 {
+
+constexpr int GD_KS = 64;                                    // fp16 elements of K per stage = one 128-B swizzle row
+constexpr int GD_EPI_WARPS = 8;                              // 4 TMEM lane quarters x 2 column halves
+constexpr int GD_THREADS = 64 + GD_EPI_WARPS * 32;
+__host__ __device__ constexpr int gd_stages(int bn) { return bn == 128 ? 6 : 4; }
+__host__ __device__ constexpr int gd_smem(int bn) { return gd_stages(bn) * (GM_BM * 128 + bn * 128) + 256 + 1024; }
+static_assert(gd_smem(128) <= 232448 && gd_smem(256) <= 232448, "shared memory");
+
+struct GemmDenseArgs {
+    float * out; long long out_cs;              // dst[n * out_cs + m]
+    int M, N, K;
+    int mtiles, ntiles;
+    int ksplit; long long split_stride;        // split-K: work item = (tile, split); split sp writes its partial sums to out + sp * split_stride
+};
+
+template <int BN>
+__global__ void __launch_bounds__(GD_THREADS, 1)
+gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
+    constexpr int STAGES = gd_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = BN * 128;
+    constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
+    extern __shared__ uint8_t gd_smem_raw[];
+    const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
+    uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
+    const uint32_t sA = base, sB = base + OFF_B, bars = base + OFF_BAR;
+    // full: TMA landed; empty: the stage's MMAs have read it; tfull: a tile's accumulator is complete; tempty: the epilogue has read it
+    const uint32_t full0 = bars, empty0 = bars + STAGES * 8, tfull0 = bars + 2 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 2 * STAGES * 8 + 4 * 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.mtiles * p.ntiles * p.ksplit;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
+        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, GD_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {            // two f32 accumulator buffers of BN columns
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(gm_smem_u32((const void *) tmem_slot)), "n"(2 * BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    gm_fence_before();
+    __syncthreads();
+    gm_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer.  Work items are numbered m-tile fastest: the CTAs running at the same time share their B tile
+        // (activations, small) in L2 and stream different weight rows
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
+            uint32_t it = 0;
+            for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
+                const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+                const int nt = tile / p.mtiles, mt = tile - nt * p.mtiles;
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                for (int ks = ks0; ks < ks1; ks++, it++) {
+                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                    gm_mbar_wait(empty0 + s * 8, ph ^ 1);
+                    gm_mbar_expect_tx(full0 + s * 8, STAGE_A + STAGE_B);
+                    gm_tma_2d(sA + s * STAGE_A, &tmA, full0 + s * 8, ks * GD_KS, mt * GM_BM);
+                    gm_tma_2d(sB + s * STAGE_B, &tmB, full0 + s * 8, ks * GD_KS, nt * BN);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer
+        if (lane == 0) {
+            // instruction descriptor: D = f32 (bits 4-5 = 1), A / B = fp16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+            const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
+            uint32_t it = 0, tc = 0;
+            for (int work = blockIdx.x; work < nwork; work += gridDim.x, tc++) {
+                const int sp = work % p.ksplit;
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
+                gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
+                gm_fence_after();
+                for (int ks = ks0; ks < ks1; ks++, it++) {
+                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                    gm_mbar_wait(full0 + s * 8, ph);
+                    gm_fence_after();
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++) {                 // every MMA consumes 16 fp16 = 32 bytes of K per row
+                        const uint64_t ad = gm_smem_desc(sA + s * STAGE_A + j * 32u), bd = gm_smem_desc(sB + s * STAGE_B + j * 32u);
+                        gm_mma_f16(tmem + buf * BN, ad, bd, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
+                    }
+                    gm_commit(empty0 + s * 8);                    // arrives when the stage's MMAs have read shared memory
+                }
+                gm_commit(tfull0 + buf * 8);                      // arrives when the tile's sums are in TMEM
+            }
+        }
+    } else {
+        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), column half (w - 2) / 4
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int m_local = q * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + half * (BN / 2);
+        uint32_t tc = 0;
+        for (int work = blockIdx.x; work < nwork; work += gridDim.x, tc++) {
+            const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+            const int nt = tile / p.mtiles, mt = tile - nt * p.mtiles;
+            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            float * const outp = p.out + (long long) sp * p.split_stride;
+            const int m = mt * GM_BM + m_local;
+            const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
+            if (ks1 > ks0) {
+                gm_mbar_wait(tfull0 + buf * 8, bph);
+                gm_fence_after();
+            }
+            #pragma unroll
+            for (int c = 0; c < BN / 64; c++) {
+                int v[32];
+                if (ks1 > ks0) { gm_tmem_ld32(tbase + buf * BN + c * 32, v); gm_tmem_ld_wait(); }
+                else {
+                    #pragma unroll
+                    for (int i = 0; i < 32; i++) v[i] = 0;
+                }
+                const int n0 = nt * BN + half * (BN / 2) + c * 32;
+                if (m < p.M) {
+                    #pragma unroll
+                    for (int i = 0; i < 32; i++)
+                        if (n0 + i < p.N) outp[(long long) (n0 + i) * p.out_cs + m] = __int_as_float(v[i]);
+                }
+            }
+            gm_fence_before();
+            __syncwarp();
+            if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);      // buffer free for the MMA issuer
+        }
+    }
+    gm_fence_before();
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(2 * BN) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ operand preparation
+__device__ __forceinline__ uint32_t gd_pack_h2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *(const uint32_t *) &h;
+}
+// 4 signed bytes of w times d -> 4 halfs
+__device__ __forceinline__ uint2 gd_s8x4(uint32_t w, float d) {
+    return make_uint2(gd_pack_h2(d * (float) (int8_t) (w & 0xFF), d * (float) (int8_t) ((w >> 8) & 0xFF)),
+                      gd_pack_h2(d * (float) (int8_t) ((w >> 16) & 0xFF), d * (float) (int8_t) (w >> 24)));
+}
+// 4 unsigned bytes: d * (q - bias) - mn
+__device__ __forceinline__ uint2 gd_u8x4(uint32_t w, float d, float bias, float mn) {
+    return make_uint2(gd_pack_h2(d * ((float) (w & 0xFF) - bias) - mn, d * ((float) ((w >> 8) & 0xFF) - bias) - mn),
+                      gd_pack_h2(d * ((float) ((w >> 16) & 0xFF) - bias) - mn, d * ((float) (w >> 24) - bias) - mn));
+}
+__device__ __forceinline__ void gd_store16(__half * out, const uint2 a, const uint2 b, const uint2 c, const uint2 d) {
+    ((uint4 *) out)[0] = make_uint4(a.x, a.y, b.x, b.y);
+    ((uint4 *) out)[1] = make_uint4(c.x, c.y, d.x, d.y);
+}
+
+// q8_0 (SoA: qs 32 B, d f16 per block; y = d * q, dequantize_row_q8_0 ggml-quants.c:347-363): one thread per 16 elements
+__global__ void __launch_bounds__(256)
+dequant_q8_0_f16_kernel(const uint4 * __restrict__ qs, const __half * __restrict__ dd, const long long n16, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long) gridDim.x * blockDim.x) {
+        const uint4 v = qs[i];
+        const float d = __half2float(dd[i >> 1]);
+        gd_store16(out + i * 16, gd_s8x4(v.x, d), gd_s8x4(v.y, d), gd_s8x4(v.z, d), gd_s8x4(v.w, d));
+    }
+}
+// q4_0 (qs 16 B: low nibbles = elements 0..15, high = 16..31; y = d * (q - 8), dequantize_row_q4_0 ggml-quants.c:307-325): one thread per block
+__global__ void __launch_bounds__(256)
+dequant_q4_0_f16_kernel(const uint4 * __restrict__ qs, const __half * __restrict__ dd, const long long nblocks, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nblocks; i += (long long) gridDim.x * blockDim.x) {
+        const uint4 v = qs[i];
+        const float d = __half2float(dd[i]);
+        const uint32_t m = 0x0F0F0F0Fu;
+        gd_store16(out + i * 32,      gd_u8x4(v.x & m, d, 8.f, 0.f), gd_u8x4(v.y & m, d, 8.f, 0.f), gd_u8x4(v.z & m, d, 8.f, 0.f), gd_u8x4(v.w & m, d, 8.f, 0.f));
+        gd_store16(out + i * 32 + 16, gd_u8x4((v.x >> 4) & m, d, 8.f, 0.f), gd_u8x4((v.y >> 4) & m, d, 8.f, 0.f),
+                                      gd_u8x4((v.z >> 4) & m, d, 8.f, 0.f), gd_u8x4((v.w >> 4) & m, d, 8.f, 0.f));
+    }
+}
+// q4_K (qs 128 B + header {f16 d, f16 dmin, 12 B packed 6-bit scales / mins}; y = (d * sc_g) * q - dmin * m_g,
+// dequantize_row_q4_K ggml-quants.c:1352-1374): one thread per 64 elements (low nibbles = sub-block 2j, high = 2j + 1)
+__global__ void __launch_bounds__(256)
+dequant_q4_K_f16_kernel(const uint4 * __restrict__ qs, const uint4 * __restrict__ hdr, const long long nsuper, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 4; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 2; const int j = (int) (i & 3);
+        const uint4 v0 = qs[sb * 8 + 2 * j], v1 = qs[sb * 8 + 2 * j + 1];
+        const uint4 h = hdr[sb];
+        const __half2 dd = *(const __half2 *) &h.x;
+        const float d = __low2float(dd), dmin = __high2float(dd);
+        const uint32_t w[3] = {h.y, h.z, h.w};
+        auto byte = [&](int k) -> uint32_t { return (w[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
+        float ds[2], ms[2];
+        #pragma unroll
+        for (int e = 0; e < 2; e++) {
+            const int g = 2 * j + e;
+            uint32_t sc, mn;
+            if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
+            else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
+            ds[e] = __fmul_rn(d, (float) sc); ms[e] = __fmul_rn(dmin, (float) mn);
+        }
+        const uint32_t m = 0x0F0F0F0Fu;
+        __half * o = out + sb * 256 + j * 64;
+        gd_store16(o,      gd_u8x4(v0.x & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.y & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.z & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.w & m, ds[0], 0.f, ms[0]));
+        gd_store16(o + 16, gd_u8x4(v1.x & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.y & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.z & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.w & m, ds[0], 0.f, ms[0]));
+        gd_store16(o + 32, gd_u8x4((v0.x >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v0.y >> 4) & m, ds[1], 0.f, ms[1]),
+                           gd_u8x4((v0.z >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v0.w >> 4) & m, ds[1], 0.f, ms[1]));
+        gd_store16(o + 48, gd_u8x4((v1.x >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v1.y >> 4) & m, ds[1], 0.f, ms[1]),
+                           gd_u8x4((v1.z >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v1.w >> 4) & m, ds[1], 0.f, ms[1]));
+    }
+}
+// q6_K (ql 128 B, qh 64 B, 16 int8 scales, f16 d; y = d * sc_g * (q - 32), bit layout as dequantize_row_q6_K
+// ggml-quants.c:1681-1710): 16 threads per super-block, thread t handles l = 4 (t & 7) .. +3 of half (t >> 3)
+__global__ void __launch_bounds__(256)
+dequant_q6_K_f16_kernel(const uint32_t * __restrict__ ql, const uint32_t * __restrict__ qh, const int8_t * __restrict__ sc,
+                        const __half * __restrict__ dd, const long long nsuper, __half * __restrict__ out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 16; i += (long long) gridDim.x * blockDim.x) {
+        const long long sb = i >> 4; const int t = (int) (i & 15), half = t >> 3, l4 = t & 7;
+        const uint32_t a = ql[sb * 32 + half * 16 + l4], b = ql[sb * 32 + half * 16 + 8 + l4], h = qh[sb * 16 + half * 8 + l4];
+        const uint32_t v[4] = {
+            (a & 0x0F0F0F0Fu)        | ((h << 4) & 0x30303030u),
+            (b & 0x0F0F0F0Fu)        | ((h << 2) & 0x30303030u),
+            ((a >> 4) & 0x0F0F0F0Fu) | ( h       & 0x30303030u),
+            ((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)};
+        const float d = __half2float(dd[sb]);
+        #pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int e = half * 128 + r * 32 + l4 * 4;          // element index inside the super-block
+            const float dg = __fmul_rn(d, (float) sc[sb * 16 + (e >> 4)]);
+            *(uint2 *) (out + sb * 256 + e) = gd_u8x4(v[r], dg, 32.f, 0.f);
+        }
+    }
+}
+
+// activations: f32 [N][K] -> q8_1 (d = amax / 127 rounded to fp16, q = round(x / d); quantize_row_q8_1_ref ggml-quants.c:220-253)
+// -> fp16(d * q), saturating.  8 lanes per 32-element block, one float4 each.
+__global__ void __launch_bounds__(256)
+dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N, __half * __restrict__ out) {
+    const int NB = K / 32;
+    const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    const long long blk = gid >> 3;
+    if (blk >= (long long) NB * N) return;
+    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 7);
+    const float4 v = *(const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 4) * 4);
+    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const float dh = __half2float(__float2half_rn(d));
+    const float r0 = dh * roundf(__fmul_rn(v.x, id)), r1 = dh * roundf(__fmul_rn(v.y, id));
+    const float r2 = dh * roundf(__fmul_rn(v.z, id)), r3 = dh * roundf(__fmul_rn(v.w, id));
+    uint32_t h01, h23;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h01) : "f"(r1), "f"(r0));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h23) : "f"(r3), "f"(r2));
+    *(uint2 *) (out + (long long) row * K + b * 32 + sub * 4) = make_uint2(h01, h23);
+}
+
+cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st) {
+    const long long threads = (long long) (K / 4) * N;
+    dequant_act_f16_kernel<<<(unsigned) ((threads + 255) / 256), 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, out);
+    return cudaGetLastError();
+}
+// weights of `type` (SoA field pointers w, nblocks native blocks) -> dequantised fp16 [M][K]
+cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st) {
+    auto grid_for = [](long long threads) { long long b = (threads + 255) / 256; return (unsigned) (b > 148 * 32 ? 148 * 32 : (b < 1 ? 1 : b)); };
+    switch (type) {
+        case T_Q8_0: dequant_q8_0_f16_kernel<<<grid_for(nblocks * 2), 256, 0, st>>>((const uint4 *) w.p[0], (const __half *) w.p[1], nblocks * 2, out); break;
+        case T_Q4_0: dequant_q4_0_f16_kernel<<<grid_for(nblocks), 256, 0, st>>>((const uint4 *) w.p[0], (const __half *) w.p[1], nblocks, out); break;
+        case T_Q4_K: dequant_q4_K_f16_kernel<<<grid_for(nblocks * 4), 256, 0, st>>>((const uint4 *) w.p[0], (const uint4 *) w.p[1], nblocks, out); break;
+        case T_Q6_K: dequant_q6_K_f16_kernel<<<grid_for(nblocks * 16), 256, 0, st>>>((const uint32_t *) w.p[0], (const uint32_t *) w.p[1], (const int8_t *) w.p[2],
+                                                                                    (const __half *) w.p[3], nblocks, out); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ host: launch
+// N tile: 256 columns halve the number of times the weights travel from L2 to the SMs, but only pay when the 128 x 256 tiles
+// still fill the machine
+int gemm_dense_bn(int M, int N, int sms) {
+    if (getenv("B200_GEMM_BN")) return atoi(getenv("B200_GEMM_BN")) == 256 ? 256 : 128;
+    const long long t256 = (long long) ((M + GM_BM - 1) / GM_BM) * ((N + 255) / 256);
+    return N > 128 && t256 >= sms ? 256 : 128;
+}
+int gemm_dense_ksplit(int M, int N, int K, int sms) {
+    const int bn = gemm_dense_bn(M, N, sms);
+    const int tiles = ((M + GM_BM - 1) / GM_BM) * ((N + bn - 1) / bn);
+    const int nks = (K + GD_KS - 1) / GD_KS;
+    int s = sms / (tiles > 0 ? tiles : 1);
+    if (s > nks / 8) s = nks / 8;
+    if (s > 8) s = 8;
+    return s < 2 ? 1 : s;
+}
+
+template <int BN>
+static cudaError_t gemm_dense_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+    static bool attr_done[64] = {false};          // per device
+    int dev = 0; cudaGetDevice(&dev); dev &= 63;
+    if (!attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_dense_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd_smem(BN));
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    gemm_dense_kernel<BN><<<(unsigned) grid, GD_THREADS, gd_smem(BN), st>>>(tmA, tmB, p);
+    return cudaGetLastError();
+}
+
+// A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
+// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
+cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st) {
+    const int bn = gemm_dense_bn(M, N, sms);
+    CUtensorMap tmA, tmB;
+    if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, bn)) return cudaErrorInvalidValue;
+    GemmDenseArgs p{};
+    p.out = out; p.out_cs = out_cs; p.M = M; p.N = N; p.K = K;
+    p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + bn - 1) / bn;
+    p.ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
+    if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; }
+    const int work = p.mtiles * p.ntiles * p.ksplit;
+    const int grid = work < sms ? work : sms;
+    const cudaError_t e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
+    if (e != cudaSuccess || p.ksplit == 1) return e;
+    return launch_reduce_splits(split_ws, p.ksplit, (long long) M * N, M, out, out_cs, 0, st);
+}
+
+}  // namespace b200

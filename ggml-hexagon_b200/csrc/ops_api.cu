@@ -5,6 +5,8 @@
 #include "../../include/ggml_b200_ops.h"
 #include "b200_internal.cuh"
 
+#include <cuda.h>
+
 #include <dlfcn.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -77,6 +79,7 @@ struct Ctx {
     bool in_graph = false;        // inside b200_graph_compute: src1 quantisation may be reused between nodes
     uint64_t scratch_gen = 0;     // bumped whenever a scratch buffer moves: captured graphs hold the old addresses and must not match any more
     const void * q_ptr = nullptr; int64_t q_K = 0, q_N = 0, q_stride = 0;
+    int q_kind = 0;               // what the cached conversion of q_ptr is: 0 = q8_1 planes in act_qs / act_ds, 1 = fp16 d * q in gm_qb (dense GEMM)
     std::unordered_map<uint64_t, GraphEntry> graphs;
     std::unordered_map<uint64_t, StreamProgram> programs;
     int ds_grid = -1;             // CTAs of the decode stream kernel (-1: not probed yet, 0: unavailable)
@@ -86,6 +89,13 @@ struct Ctx {
     int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;
     float *  gm_ws = nullptr; size_t gm_ws_cap = 0;
     float *  gm_sp = nullptr; size_t gm_sp_cap = 0;      // split-K partial results      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
+    // dense GEMM (gemm_dense.cu): dequantised fp16 copies of quantised weight matrices, keyed by the device address of the
+    // matrix's first field.  180 GB of HBM hold them beside the native weights (2 bytes per weight); without one (budget
+    // spent, or first use inside a stream capture) the weights are dequantised per call into gm_a.
+    struct Shadow { __half * p; size_t bytes; const char * src_lo, * src_hi; int type; int64_t M, K; };
+    std::unordered_map<const void *, Shadow> shadows;
+    size_t shadow_bytes = 0, shadow_budget = 0; bool shadow_budget_set = false;
+    bool capturing = false;       // inside cudaStreamBeginCapture .. EndCapture: no allocation, no synchronisation
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
@@ -123,6 +133,7 @@ static int ensure_buf(Ctx * c, T ** p, size_t * cap, size_t bytes) {
     CU(cudaMalloc((void **) p, bytes + 256));
     *cap = bytes;
     c->scratch_gen++;
+    c->q_ptr = nullptr;
     return 0;
 }
 static int ensure_stage(Ctx * c, size_t bytes) {
@@ -132,6 +143,50 @@ static int ensure_stage(Ctx * c, size_t bytes) {
     CU(cudaMalloc((void **) &c->stage, cap));
     c->stage_cap = cap;
     return 0;
+}
+
+// ---- fp16 weight shadows of the dense GEMM
+// B200_GEMM_MODE=exact keeps the per-block exact int8 path (gemm_i8.cu) for many-column MUL_MATs; default: dense (gemm_dense.cu)
+static bool gemm_dense_enabled() { const char * e = getenv("B200_GEMM_MODE"); return !(e && strcmp(e, "exact") == 0); }
+static void shadow_drop_range(Ctx * c, const void * lo_, size_t n) {
+    if (c->shadows.empty() || n == 0) return;
+    const char * lo = (const char *) lo_, * hi = lo + n;
+    bool any = false;
+    for (auto it = c->shadows.begin(); it != c->shadows.end(); ) {
+        if (it->second.src_lo < hi && lo < it->second.src_hi) {
+            if (!any) { cudaStreamSynchronize(c->st); any = true; }
+            cudaFree(it->second.p); c->shadow_bytes -= it->second.bytes; it = c->shadows.erase(it);
+        } else ++it;
+    }
+    if (any) c->scratch_gen++;          // captured graphs hold the shadow's address
+}
+static void shadow_drop_all(Ctx * c) { shadow_drop_range(c, nullptr, ~(size_t) 0 >> 1); }
+// the shadow of the M x K matrix whose fields start at wp (a slice of the tensor stored at [src_lo, src_hi)), built on first use;
+// nullptr: none (and none can be made now)
+static const __half * shadow_get(Ctx * c, int type, const WPtrs & wp, int64_t M, int64_t K, const void * src_lo, size_t src_bytes, bool create) {
+    auto it = c->shadows.find(wp.p[0]);
+    if (it != c->shadows.end()) {
+        if (it->second.type == type && it->second.M == M && it->second.K == K) return it->second.p;
+        if (c->capturing) return nullptr;
+        shadow_drop_range(c, it->second.src_lo, (size_t) (it->second.src_hi - it->second.src_lo));
+    }
+    if (!create || c->capturing) return nullptr;
+    if (!c->shadow_budget_set) {
+        c->shadow_budget_set = true;
+        c->shadow_budget = getenv("B200_GEMM_SHADOW_MB") ? (size_t) atoll(getenv("B200_GEMM_SHADOW_MB")) << 20 : (size_t) 64 << 30;
+    }
+    const size_t bytes = (size_t) M * K * sizeof(__half);
+    if (c->shadow_bytes + bytes > c->shadow_budget) return nullptr;
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < bytes + ((size_t) 4 << 30)) { cudaGetLastError(); return nullptr; }
+    Ctx::Shadow sh{};
+    if (cudaMalloc((void **) &sh.p, bytes + 256) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (launch_dequant_weights_f16(type, wp, M * (K / block_elems(type)), sh.p, c->st) != cudaSuccess) { cudaGetLastError(); cudaFree(sh.p); return nullptr; }
+    c->launches++;
+    sh.bytes = bytes; sh.src_lo = (const char *) src_lo; sh.src_hi = sh.src_lo + src_bytes; sh.type = type; sh.M = M; sh.K = K;
+    c->shadows.emplace(wp.p[0], sh);
+    c->shadow_bytes += bytes;
+    return sh.p;
 }
 
 extern "C" int b200_device_count(void) {
@@ -187,6 +242,7 @@ extern "C" int b200_close(b200_handle h) {
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
+    for (auto & kv : c->shadows) cudaFree(kv.second.p);
     cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp);
     cudaStreamDestroy(c->st);
     c->magic = 0;
@@ -215,24 +271,38 @@ extern "C" int b200_malloc(b200_handle h, size_t size, void ** ptr) {
     if (e != cudaSuccess) { cudaGetLastError(); return fail(B200_ENOMEM, "cudaMalloc(%zu): %s", size, cudaGetErrorString(e)); }
     return 0;
 }
-extern "C" int b200_free(b200_handle h, void * ptr) { CTX(h); CU(cudaStreamSynchronize(c->st)); CU(cudaFree(ptr)); return 0; }
+extern "C" int b200_free(b200_handle h, void * ptr) {
+    CTX(h);
+    if (!c->shadows.empty()) {   // shadows of weights that live in the allocation being freed
+        typedef CUresult (*range_t)(CUdeviceptr *, size_t *, CUdeviceptr);
+        static range_t range = [] {
+            void * p = nullptr; cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+            return (range_t) p;
+        }();
+        CUdeviceptr lo = 0; size_t n = 0;
+        if (range && range(&lo, &n, (CUdeviceptr) (uintptr_t) ptr) == CUDA_SUCCESS) shadow_drop_range(c, (const void *) (uintptr_t) lo, n);
+        else shadow_drop_all(c);
+    }
+    CU(cudaStreamSynchronize(c->st)); CU(cudaFree(ptr)); return 0;
+}
 extern "C" int b200_memcpy_h2d(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2h(b200_handle h, void * d, const void * s, size_t n) {
     CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_h2d_async(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2h_async(b200_handle h, void * d, const void * s, size_t n) {
     CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2d(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, c->st)); return 0;
 }
 extern "C" int b200_memset(b200_handle h, void * d, int v, size_t n) {
-    CTX(h); c->q_ptr = nullptr; CU(cudaMemsetAsync(d, v, n, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemsetAsync(d, v, n, c->st)); return 0;
 }
 extern "C" int b200_host_alloc(b200_handle h, size_t size, void ** ptr) { CTX(h); CU(cudaMallocHost(ptr, size ? size : 1)); return 0; }
 extern "C" int b200_host_free(b200_handle h, void * ptr) { CTX(h); CU(cudaFreeHost(ptr)); return 0; }
@@ -252,6 +322,7 @@ extern "C" int b200_weights_upload(b200_handle h, int32_t type, void * base, int
     if (!is_qweight(type)) return fail(B200_EINVAL, "weights_upload: type %d is not a quantised weight type", type);
     if (first < 0 || n < 0 || first + n > T) return fail(B200_EINVAL, "weights_upload: block range [%lld,+%lld) outside %lld", (long long) first, (long long) n, (long long) T);
     const size_t bytes = (size_t) n * block_bytes(type);
+    shadow_drop_range(c, base, (size_t) T * block_bytes(type));
     int rc = ensure_stage(c, bytes); if (rc) return rc;
     CU(cudaMemcpyAsync(c->stage, host, bytes, cudaMemcpyHostToDevice, c->st));
     CU(launch_repack(type, true, (uint8_t *) base, T, first, n, c->stage, c->st)); c->launches++;
@@ -421,6 +492,21 @@ static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1)
     if (!is_qweight(s0->type) || mn <= 0 || N < mn || K % 32 != 0 || M >= 0x7fffffff || N >= 0x7fffffff || K >= 0x3fffffff) return 0;
     const size_t ldb = (size_t) gemm_i8_ldb((int) N);
     int rc;
+    if (gemm_dense_enabled()) {
+        rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+        const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
+        if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+        bool all = true;                 // every weight matrix of the tensor has (or now gets) its fp16 shadow?
+        WPtrs wp0{};
+        if (wptrs_of(s0, &wp0) == 0 && ((uintptr_t) wp0.p[0] & 15) == 0)
+            for (int64_t i03 = 0; i03 < s0->ne[3]; i03++)
+            for (int64_t i02 = 0; i02 < s0->ne[2]; i02++)
+                all &= shadow_get(c, s0->type, wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]), M, K, s0->w_base,
+                                  (size_t) s0->w_blocks * block_bytes(s0->type), true) != nullptr;
+        else all = false;
+        if (!all) { rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc; }
+        return 0;
+    }
     rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
     rc = ensure_buf(c, &c->gm_db, &c->gm_db_cap, (size_t) 2 * (K / 16) * ldb * sizeof(float)); if (rc) return rc;
     rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc;
@@ -454,8 +540,28 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
         const char * x = (const char *) s1->data + i12 * s1->nb[2] + i13 * s1->nb[3];
         float * y = (float *) ((char *) d->data + i12 * d->nb[2] + i13 * d->nb[3]) + row_off_dst;
         const int64_t i02 = i12 / r2, i03 = i13 / r3;
-        if (q && use_gemm) {
-            // ---- many columns: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
+        if (q && use_gemm && gemm_dense_enabled()) {
+            // ---- many columns: dense fp16 tensor-core GEMM, block scales folded into the operands (gemm_dense.cu)
+            const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
+            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+            // (consecutive MUL_MATs of a node list over the same activations -- q / k / v, gate / up -- convert them once)
+            const bool reuse = c->in_graph && c->q_kind == 1 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
+            if (!reuse) {
+                CU(launch_dequant_act_f16((const float *) x, s1->nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
+                c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 1;
+            }
+            const __half * A = shadow_get(c, s0->type, wp, M, K, s0->w_base, (size_t) s0->w_blocks * block_bytes(s0->type), true);
+            if (!A) {
+                rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc;
+                CU(launch_dequant_weights_f16(s0->type, wp, M * (K / block_elems(s0->type)), (__half *) c->gm_a, c->st)); c->launches++;
+                A = (const __half *) c->gm_a;
+            }
+            const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
+            if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+            CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st));
+            c->launches += 1 + (ksp > 1 ? 1 : 0);
+        } else if (q && use_gemm) {
+            // ---- many columns, B200_GEMM_MODE=exact: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
             const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
             const long long ldb = gemm_i8_ldb((int) N);
             const int t = s0->type;
@@ -520,10 +626,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 a.x = (const float *) x; a.x_col_stride = s1->nb[1];
                 CU(launch_gemv2(s0->type, a, (int) N, true, c->st)); c->launches++;
             } else {
-                const bool reuse = c->in_graph && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
+                const bool reuse = c->in_graph && c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
                 if (!reuse) {
                     CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
-                    c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1];
+                    c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 0;
                 }
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
                 { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; const int64_t rw[1] = {M};
@@ -559,7 +665,8 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     {
         const char * lo = (const char *) d->data; const char * hi = lo + d->data_len;
         const char * qp = (const char *) c->q_ptr;
-        if (qp && (d->data_len <= 0 || (qp >= lo && qp < hi))) c->q_ptr = nullptr;
+        const char * qe = qp ? qp + (c->q_N > 1 ? (c->q_N - 1) * c->q_stride : 0) + c->q_K * 4 : nullptr;
+        if (qp && (d->data_len <= 0 || (qp < hi && lo < qe))) c->q_ptr = nullptr;
     }
     return 0;
 }
@@ -633,10 +740,10 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
         return 0;
     }
     int rc = ensure_act(c, NB); if (rc) return rc;
-    const bool reuse = c->q_ptr == (const void *) x && c->q_K == K && c->q_N == 1;
+    const bool reuse = c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == 1;
     if (!reuse) {
         CU(launch_quantize_q8_1_soa(x, K * 4, K, 1, c->act_qs, c->act_ds, c->st)); c->launches++;
-        c->q_ptr = x; c->q_K = K; c->q_N = 1; c->q_stride = nodes[0].src1.nb[1];
+        c->q_ptr = x; c->q_K = K; c->q_N = 1; c->q_stride = nodes[0].src1.nb[1]; c->q_kind = 0;
     }
     a.act = ActView{c->act_qs, c->act_ds, NB};
     CU(launch_gemv2(nodes[0].src0.type, a, 1, false, c->st)); c->launches++;
@@ -936,7 +1043,9 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     if (it == c->graphs.end()) {
         const int64_t before = c->launches;
         CU(cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal));
+        c->capturing = true;
         rc = run_nodes(c, nodes, n);
+        c->capturing = false;
         cudaGraph_t g = nullptr;
         cudaError_t e = cudaStreamEndCapture(c->st, &g);
         const int64_t captured = c->launches - before;

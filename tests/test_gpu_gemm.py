@@ -1,4 +1,4 @@
-"""GPU parity tests of the tensor-core prefill path (gemm_i8.cu: int8 tcgen05.mma per 32-element block, fp32
+"""GPU parity tests of the exact tensor-core prefill path (B200_GEMM_MODE=exact, gemm_i8.cu: int8 tcgen05.mma per 32-element block, fp32
 scale-accumulate), called through b200_mulmat with many activation columns, against the oracle:
 mode 1 = the same q8_1 block algebra (only float rounding of the running sum can differ), mode 0 = ggml-cpu
 semantics with the test-backend-ops bar NMSE <= 5e-4 (tests/test-backend-ops.cpp:1982-1984)."""
@@ -19,6 +19,7 @@ def nmse(a, b):
 def _gemm_from_16_columns(monkeypatch):
     """the tensor-core path normally takes over at 36 (K-quants) / 52 columns; these tests want it for the small shapes too"""
     monkeypatch.setenv("B200_GEMM_MIN_N", "16")
+    monkeypatch.setenv("B200_GEMM_MODE", "exact")          # this file: the exact-block-sum kernel; tests/test_gpu_gemm_dense.py: the default
 
 
 @pytest.fixture(scope="module")

@@ -1,0 +1,183 @@
+"""GPU parity tests of the default prefill path (gemm_dense.cu: block scales folded into fp16 operands, the whole K
+accumulated in TMEM by tcgen05.mma kind::f16), called through b200_mulmat with many activation columns, against the oracle.
+Bars: against the oracle's q8_1 block algebra (mode 1) only the fp16 rounding of the two dequantised operands differs
+(relative 2^-12 per element -> NMSE ~4e-8; bar 1e-6); against ggml-cpu semantics (mode 0) the test-backend-ops bar
+NMSE <= 5e-4 (tests/test-backend-ops.cpp:1982-1984)."""
+import numpy as np
+import pytest
+
+import pyoracle as O
+import b200ops as B
+
+pytestmark = pytest.mark.gpu
+
+ALL = [(O.Q8_0, "q8_0"), (O.Q4_0, "q4_0"), (O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")]
+DENSE_BAR = 1e-6
+
+
+def nmse(a, b):
+    return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
+
+
+@pytest.fixture(autouse=True)
+def _dense_from_16_columns(monkeypatch):
+    monkeypatch.setenv("B200_GEMM_MIN_N", "16")
+    monkeypatch.delenv("B200_GEMM_MODE", raising=False)
+    monkeypatch.delenv("B200_GEMM_BN", raising=False)
+    monkeypatch.delenv("B200_GEMM_SHADOW_MB", raising=False)
+
+
+@pytest.fixture(scope="module")
+def sess():
+    s = B.Session(0)
+    yield s
+    s.close()
+
+
+@pytest.mark.parametrize("t,name", ALL)
+@pytest.mark.parametrize("M,K,N", [(128, 256, 128), (16, 256, 32), (200, 1024, 77), (384, 4096, 512), (130, 512, 33), (257, 11008, 129)])
+def test_dense_vs_oracle(sess, t, name, M, K, N):
+    rng = np.random.default_rng(M + 3 * K + 7 * N + t)
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    before = sess.launch_count()
+    got = sess.mulmat(w, x)
+    assert sess.launch_count() > before
+    assert got.shape == (N, M)
+    e1 = nmse(got, O.mul_mat(t, raw, x, 1))
+    assert e1 <= DENSE_BAR, (name, M, K, N, e1)
+    assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
+    again = sess.mulmat(w, x)                               # second call: the cached fp16 shadow of the weights
+    assert np.array_equal(got, again)
+    w.free()
+
+
+@pytest.mark.parametrize("t,name", [(O.Q8_0, "q8_0"), (O.Q4_0, "q4_0")])
+def test_dense_ragged_k(sess, t, name):
+    """K = 96: the last 64-element stage is half out of range (TMA zero fill on both operands)"""
+    rng = np.random.default_rng(41 + t)
+    M, K, N = 130, 96, 33
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    assert nmse(sess.mulmat(w, x), O.mul_mat(t, raw, x, 1)) <= DENSE_BAR
+    w.free()
+
+
+@pytest.mark.parametrize("bn", ["128", "256"])
+@pytest.mark.parametrize("t,name", ALL)
+def test_dense_both_tile_widths(sess, monkeypatch, bn, t, name):
+    monkeypatch.setenv("B200_GEMM_BN", bn)
+    rng = np.random.default_rng(43 + t)
+    M, K, N = 300, 1280, 300
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    assert nmse(sess.mulmat(w, x), O.mul_mat(t, raw, x, 1)) <= DENSE_BAR
+    w.free()
+
+
+def test_dense_integer_product_is_exact(sess):
+    """integers that fp16 holds exactly (|w| <= 15 with d = 1, |x| <= 127 with d_a = 1): every product and every partial sum
+    is an integer below 2^24, so the f32 accumulation in TMEM must reproduce the int64 matrix product bit for bit"""
+    rng = np.random.default_rng(11)
+    M, K, N = 256, 2048, 96
+    wq = rng.integers(-15, 16, size=(M, K // 32, 32), dtype=np.int8)
+    raw = np.zeros((M, K // 32, 34), dtype=np.uint8)
+    raw[:, :, 0:2] = np.frombuffer(np.float16(1.0).tobytes(), dtype=np.uint8)
+    raw[:, :, 2:] = wq.view(np.uint8)
+    raw = raw.reshape(M, -1)
+    x = rng.integers(-127, 128, size=(N, K // 32, 32)).astype(np.float32)
+    x[:, :, 5] = 127.0 * rng.choice([-1.0, 1.0], size=(N, K // 32))
+    x = x.reshape(N, K)
+    w = sess.weights(O.Q8_0, raw, K)
+    got = sess.mulmat(w, x)
+    want = x.astype(np.int64) @ wq.reshape(M, K).astype(np.int64).T
+    assert np.array_equal(got, want.astype(np.float32))
+    w.free()
+
+
+@pytest.mark.parametrize("t,name", [(O.Q8_0, "q8_0"), (O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")])
+def test_dense_split_k_small_m(sess, t, name):
+    """few output tiles (M = 256, N = 96 -> 2 tiles): the K range is split over work items and reduced in a second kernel"""
+    rng = np.random.default_rng(23 + t)
+    M, K, N = 256, 8192, 96
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    assert nmse(sess.mulmat(w, x), O.mul_mat(t, raw, x, 1)) <= DENSE_BAR
+    w.free()
+
+
+def test_dense_shadow_follows_a_new_upload(sess):
+    """the fp16 shadow is keyed by the weights' device address: uploading other weights into the same buffer must drop it"""
+    import ctypes as C
+    rng = np.random.default_rng(47)
+    M, K, N = 256, 1024, 64
+    raw1, raw2 = O.random_blocks(O.Q4_0, M, K, rng), O.random_blocks(O.Q4_0, M, K, rng)
+    w = sess.weights(O.Q4_0, raw1, K)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    assert nmse(sess.mulmat(w, x), O.mul_mat(O.Q4_0, raw1, x, 1)) <= DENSE_BAR
+    raw2 = np.ascontiguousarray(raw2)
+    B._ck(B.lib().b200_weights_upload(sess.h, O.Q4_0, w.buf.ptr, w.blocks, 0, w.blocks, B._p(raw2)))
+    assert nmse(sess.mulmat(w, x), O.mul_mat(O.Q4_0, raw2, x, 1)) <= DENSE_BAR
+    w.free()
+
+
+def test_dense_without_shadow_budget(monkeypatch):
+    """B200_GEMM_SHADOW_MB=0: no shadows, the weights are dequantised per call into scratch"""
+    monkeypatch.setenv("B200_GEMM_SHADOW_MB", "0")
+    rng = np.random.default_rng(53)
+    with B.Session(0) as s:
+        for t, _ in ALL:
+            M, K, N = 200, 1024, 77
+            raw = O.random_blocks(t, M, K, rng)
+            w = s.weights(t, raw, K)
+            x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+            for _ in range(2):
+                assert nmse(s.mulmat(w, x), O.mul_mat(t, raw, x, 1)) <= DENSE_BAR
+            w.free()
+
+
+@pytest.mark.parametrize("shadow_mb", [None, "0"])
+def test_dense_inside_a_captured_graph(monkeypatch, shadow_mb):
+    """node list with dense MUL_MATs submitted with use_cuda_graph: shadows and scratch are made before the capture starts"""
+    if shadow_mb is not None:
+        monkeypatch.setenv("B200_GEMM_SHADOW_MB", shadow_mb)
+    rng = np.random.default_rng(31)
+    M, K, N = 384, 2048, 96
+    with B.Session(0) as sess:
+        ws, xs = [], rng.uniform(-1, 1, (N, K)).astype(np.float32)
+        xb = sess.to_device(xs)
+        nodes, outs, raws = [], [], []
+        for t in (O.Q8_0, O.Q4_0, O.Q4_K, O.Q6_K):
+            raw = O.random_blocks(t, M, K, rng)
+            w = sess.weights(t, raw, K)
+            d = sess.malloc(4 * M * N)
+            n = B.Node()
+            n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(d.ptr, [M, N], op=B.OP_MUL_MAT)
+            nodes.append(n); ws.append(w); outs.append(d); raws.append((t, raw))
+        arr = (B.Node * len(nodes))(*nodes)
+        for _ in range(3):                                    # capture, then replays
+            sess.graph_compute(arr, 2)
+        sess.sync()
+        for (t, raw), d in zip(raws, outs):
+            got = sess.to_host(d, (N, M), np.float32)
+            assert nmse(got, O.mul_mat(t, raw, xs, 1)) <= DENSE_BAR
+        for b in ws + outs + [xb]:
+            b.free()
+
+
+def test_dense_close_to_exact_mode(sess, monkeypatch):
+    """the two prefill kernels on the same inputs: they differ by the fp16 rounding of the operands only"""
+    rng = np.random.default_rng(59)
+    M, K, N = 512, 4096, 128
+    raw = O.random_blocks(O.Q4_0, M, K, rng)
+    w = sess.weights(O.Q4_0, raw, K)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    dense = sess.mulmat(w, x)
+    monkeypatch.setenv("B200_GEMM_MODE", "exact")
+    exact = sess.mulmat(w, x)
+    assert nmse(dense, exact) <= DENSE_BAR and not np.array_equal(dense, exact)
+    w.free()
