@@ -25,6 +25,7 @@
 #include "tc_common.cuh"
 
 #include <stdio.h>
+#include <vector>
 
 namespace b200 {
 
@@ -40,7 +41,45 @@ struct GemmDenseArgs {
     int M, N, K;
     int mtiles, ntiles;
     int ksplit; long long split_stride;        // split-K: work item = (tile, split); split sp writes its partial sums to out + sp * split_stride
+    unsigned long long * trace;                // B200_GEMM_TRACE=1: 8 globaltimer stamps per CTA (pair kernel), else nullptr
 };
+__device__ __forceinline__ void gd_stamp(const GemmDenseArgs & p, int slot) {
+    if (p.trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(size_t) blockIdx.x * 8 + slot] = t;
+    }
+}
+
+// Epilogue of one warp: its 32 TMEM lanes (= 32 consecutive rows m, one per lane) x NCH chunks of 32 columns, written to
+// colp[i * cs] (a column of dst is contiguous in m, so every store instruction is one 128-byte line).  The pointer walks by cs:
+// recomputing (n0 + i) * cs + m with its bounds test per element cost ~18 instructions and a branch per store, 7 us per
+// 128 x 256 tile (B200_GEMM_TRACE timeline); the next chunk's tcgen05.ld is in flight while a chunk is stored.
+__device__ __forceinline__ void gd_store_chunk(float * colp, const long long cs, const int (&v)[32], const int ncols) {
+    if (ncols >= 32) {
+        #pragma unroll
+        for (int i = 0; i < 32; i++) { *colp = __int_as_float(v[i]); colp += cs; }
+    } else {
+        #pragma unroll
+        for (int i = 0; i < 32; i++) { if (i < ncols) *colp = __int_as_float(v[i]); colp += cs; }
+    }
+}
+template <int NCH>
+__device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * colp, const long long cs, const int ncols, const bool row_ok) {
+    static_assert(NCH % 2 == 0, "chunks are processed in pairs");
+    int va[32], vb[32];
+    gm_tmem_ld32(taddr, va);
+    gm_tmem_ld_wait();
+    #pragma unroll
+    for (int c = 0; c < NCH; c += 2) {
+        gm_tmem_ld32(taddr + (c + 1) * 32, vb);
+        if (row_ok && ncols > c * 32) gd_store_chunk(colp + (long long) c * 32 * cs, cs, va, ncols - c * 32);
+        gm_tmem_ld_wait();
+        if (c + 2 < NCH) gm_tmem_ld32(taddr + (c + 2) * 32, va);
+        if (row_ok && ncols > (c + 1) * 32) gd_store_chunk(colp + (long long) (c + 1) * 32 * cs, cs, vb, ncols - (c + 1) * 32);
+        if (c + 2 < NCH) gm_tmem_ld_wait();
+    }
+}
 
 template <int BN>
 __global__ void __launch_bounds__(GD_THREADS, 1)
@@ -77,6 +116,9 @@ gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
+        }
+        __syncwarp();
+        {   // whole warp, one elected lane issues (as the MMA warp)
             uint32_t it = 0;
             for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
                 const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
@@ -85,15 +127,15 @@ gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
-                    gm_mbar_expect_tx(full0 + s * 8, STAGE_A + STAGE_B);
-                    gm_tma_2d(sA + s * STAGE_A, &tmA, full0 + s * 8, ks * GD_KS, mt * GM_BM);
-                    gm_tma_2d(sB + s * STAGE_B, &tmB, full0 + s * 8, ks * GD_KS, nt * BN);
+                    gm_mbar_expect_tx_elect(full0 + s * 8, STAGE_A + STAGE_B);
+                    gm_tma_2d_elect(sA + s * STAGE_A, &tmA, full0 + s * 8, ks * GD_KS, mt * GM_BM);
+                    gm_tma_2d_elect(sB + s * STAGE_B, &tmB, full0 + s * 8, ks * GD_KS, nt * BN);
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer
-        if (lane == 0) {
+        // ===== MMA issuer: the whole warp runs the loop (uniform control flow), one elected lane issues (tc_common.cuh)
+        {
             // instruction descriptor: D = f32 (bits 4-5 = 1), A / B = fp16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
             const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
             uint32_t it = 0, tc = 0;
@@ -107,14 +149,13 @@ gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(full0 + s * 8, ph);
                     gm_fence_after();
+                    const uint64_t ad = gm_smem_desc(sA + s * STAGE_A), bd = gm_smem_desc(sB + s * STAGE_B);
                     #pragma unroll
-                    for (int j = 0; j < 4; j++) {                 // every MMA consumes 16 fp16 = 32 bytes of K per row
-                        const uint64_t ad = gm_smem_desc(sA + s * STAGE_A + j * 32u), bd = gm_smem_desc(sB + s * STAGE_B + j * 32u);
-                        gm_mma_f16(tmem + buf * BN, ad, bd, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
-                    }
-                    gm_commit(empty0 + s * 8);                    // arrives when the stage's MMAs have read shared memory
+                    for (int j = 0; j < 4; j++)                   // every MMA consumes 16 fp16 = 32 bytes of K per row: start address field + 2
+                        gm_mma_f16_elect(tmem + buf * BN, ad + 2u * j, bd + 2u * j, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
+                    gm_commit_elect(empty0 + s * 8);              // arrives when the stage's MMAs have read shared memory
                 }
-                gm_commit(tfull0 + buf * 8);                      // arrives when the tile's sums are in TMEM
+                gm_commit_elect(tfull0 + buf * 8);                // arrives when the tile's sums are in TMEM
             }
         }
     } else {
@@ -126,29 +167,13 @@ gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int work = blockIdx.x; work < nwork; work += gridDim.x, tc++) {
             const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
             const int nt = tile / p.mtiles, mt = tile - nt * p.mtiles;
-            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
             float * const outp = p.out + (long long) sp * p.split_stride;
             const int m = mt * GM_BM + m_local;
             const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
-            if (ks1 > ks0) {
-                gm_mbar_wait(tfull0 + buf * 8, bph);
-                gm_fence_after();
-            }
-            #pragma unroll
-            for (int c = 0; c < BN / 64; c++) {
-                int v[32];
-                if (ks1 > ks0) { gm_tmem_ld32(tbase + buf * BN + c * 32, v); gm_tmem_ld_wait(); }
-                else {
-                    #pragma unroll
-                    for (int i = 0; i < 32; i++) v[i] = 0;
-                }
-                const int n0 = nt * BN + half * (BN / 2) + c * 32;
-                if (m < p.M) {
-                    #pragma unroll
-                    for (int i = 0; i < 32; i++)
-                        if (n0 + i < p.N) outp[(long long) (n0 + i) * p.out_cs + m] = __int_as_float(v[i]);
-                }
-            }
+            gm_mbar_wait(tfull0 + buf * 8, bph);            // every work item has k-steps: ksplit <= nks / 8
+            gm_fence_after();
+            const int n0 = nt * BN + half * (BN / 2);
+            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * p.out_cs + m, p.out_cs, p.N - n0, m < p.M);
             gm_fence_before();
             __syncwarp();
             if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);      // buffer free for the MMA issuer
@@ -157,6 +182,163 @@ gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     gm_fence_before();
     __syncthreads();
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(2 * BN) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ CTA-pair variant
+// The 1-CTA kernel above is bound by the L2 -> shared-memory operand feed, not by the tensor pipe: a 128 x 128 tile wants
+// 8 KB of operands per 64-clock MMA (128 B/clk/SM) while all of L2 delivers ~6300 B/clk (~43 B/clk/SM); ncu: tensor pipe 27 %
+// busy (profiles/r01_l_ncu_gemm_dense_1cta_*).  Here two CTAs of one TPC (cluster of 2) share one 256 x BN tile through
+// tcgen05.mma.cta_group::2: every CTA stages its own 128 weight rows and HALF of the activation rows, the MMA of the leader
+// reads B from both shared memories, and each CTA's TMEM receives its 128 rows x BN columns.  With BN = 256 that is 8 KB per
+// 128-clock MMA and SM = 64 B/clk/SM, and the total L2 traffic M N K 2 (1/256 + 1/256) is half of the 128 x 128 kernel's.
+//   full[s]   leader only; both CTAs' TMA loads (.cta_group::2) complete_tx on it, the leader posts the expected bytes of both
+//   empty[s]  per CTA; tcgen05.commit.multicast arrives on both when the stage's MMAs have read shared memory
+//   tfull[b]  per CTA; multicast commit after a tile's last MMA
+//   tempty[b] leader only; the epilogue warps of BOTH CTAs arrive on it (remote arrive from the peer)
+__host__ __device__ constexpr int gd2_stage_bytes(int bn) { return GM_BM * 128 + (bn / 2) * 128; }
+__host__ __device__ constexpr int gd2_stages(int bn) { return (232448 - 1280) / gd2_stage_bytes(bn); }
+__host__ __device__ constexpr int gd2_smem(int bn) { return gd2_stages(bn) * gd2_stage_bytes(bn) + 256 + 1024; }
+static_assert(gd2_stages(256) == 7 && gd2_stages(128) == 9, "stage count");
+
+__device__ __forceinline__ uint32_t gd2_mapa(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void gd2_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void gd2_tma_2d(uint32_t dst, const CUtensorMap * map, uint32_t bar_cluster, int c0, int c1) {
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+                 :: "r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+// whole-warp forms (one elected lane issues), see tc_common.cuh
+__device__ __forceinline__ void gd2_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|e, 0xffffffff;\n\t@e tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void gd2_commit_both(uint32_t bar) {          // same barrier offset in both CTAs of the pair
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+                 :: "r"(bar), "h"((uint16_t) 3) : "memory");
+}
+__device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(bar_cluster) : "memory");
+}
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
+gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
+    constexpr int STAGES = gd2_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
+    constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
+    extern __shared__ uint8_t gd_smem_raw[];
+    const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;
+    uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
+    const uint32_t sA = base, sB = base + OFF_B, bars = base + OFF_BAR;
+    const uint32_t full0 = bars, empty0 = bars + STAGES * 8, tfull0 = bars + 2 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 2 * STAGES * 8 + 4 * 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    if (threadIdx.x == 0) gd_stamp(p, 0);
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.mtiles * p.ntiles * p.ksplit;     // p.mtiles counts 256-row tiles
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
+        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, 2 * GD_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {            // one warp of each CTA of the pair, collectively
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(gm_smem_u32((const void *) tmem_slot)), "n"(2 * BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    gm_fence_before();
+    gd2_cluster_sync();
+    gm_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0) gd_stamp(p, 1);
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs).  Work items are numbered n-tile fastest: the pairs that share a weight tile run at the
+        // same time, so the fp16 weights come from HBM once (the activations stay in L2 anyway)
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
+        }
+        __syncwarp();
+        {   // whole warp, one elected lane issues
+            const uint32_t lfull0 = gd2_mapa(full0, 0);
+            uint32_t it = 0;
+            for (int work = pair; work < nwork; work += npairs) {
+                const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+                const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                for (int ks = ks0; ks < ks1; ks++, it++) {
+                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                    gm_mbar_wait(empty0 + s * 8, ph ^ 1);
+                    if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, 2 * (STAGE_A + STAGE_B));
+                    gd2_tma_2d(sA + s * STAGE_A, &tmA, lfull0 + s * 8, ks * GD_KS, mt * 2 * GM_BM + (int) rank * GM_BM);
+                    gd2_tma_2d(sB + s * STAGE_B, &tmB, lfull0 + s * 8, ks * GD_KS, nt * BN + (int) rank * (BN / 2));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: warp 1 of the leader CTA (whole warp, one elected lane issues), M = 256 over the pair
+        if (rank == 0) {
+            const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) ((2 * GM_BM) >> 4) << 24);
+            uint32_t it = 0, tc = 0;
+            for (int work = pair; work < nwork; work += npairs, tc++) {
+                const int sp = work % p.ksplit;
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
+                gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
+                gm_fence_after();
+                for (int ks = ks0; ks < ks1; ks++, it++) {
+                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                    gm_mbar_wait(full0 + s * 8, ph);
+                    gm_fence_after();
+                    if (it == 0 && lane == 0) gd_stamp(p, 2);
+                    const uint64_t ad = gm_smem_desc(sA + s * STAGE_A), bd = gm_smem_desc(sB + s * STAGE_B);
+                    #pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        gd2_mma_f16(tmem + buf * BN, ad + 2u * j, bd + 2u * j, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
+                    gd2_commit_both(empty0 + s * 8);
+                }
+                gd2_commit_both(tfull0 + buf * 8);
+            }
+            if (lane == 0) gd_stamp(p, 3);
+        }
+    } else {
+        // ===== epilogue (both CTAs): this CTA's TMEM holds rows rank * 128 .. +127 of the pair tile, all BN columns
+        const int q = warp & 3, half = (warp - 2) >> 2;
+        const int m_local = q * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + half * (BN / 2);
+        const uint32_t ltempty0 = gd2_mapa(tempty0, 0);
+        uint32_t tc = 0;
+        for (int work = pair; work < nwork; work += npairs, tc++) {
+            const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+            const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+            float * const outp = p.out + (long long) sp * p.split_stride;
+            const int m = mt * 2 * GM_BM + (int) rank * GM_BM + m_local;
+            const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
+            gm_mbar_wait(tfull0 + buf * 8, bph);
+            gm_fence_after();
+            if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
+            const int n0 = nt * BN + half * (BN / 2);
+            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * p.out_cs + m, p.out_cs, p.N - n0, m < p.M);
+            gm_fence_before();
+            __syncwarp();
+            if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
+        }
+        if (warp == 2 && lane == 0) gd_stamp(p, 6);
+    }
+    __syncwarp();                // the cluster barrier is warp-aligned: the single-lane roles rejoin their warps first
+    gm_fence_before();
+    gd2_cluster_sync();          // the peer's shared memory and barriers stay alive until the leader's MMAs and commits are done
+    if (threadIdx.x == 0) gd_stamp(p, 7);
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(2 * BN) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------------ operand preparation
@@ -299,18 +481,22 @@ cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblo
 }
 
 // ------------------------------------------------------------------------------------------------ host: launch
-// N tile: 256 columns halve the number of times the weights travel from L2 to the SMs, but only pay when the 128 x 256 tiles
-// still fill the machine
+// B200_GEMM_CTA=1 keeps the 1-CTA kernel (128 x BN tiles); default: the CTA-pair kernel (256 x BN tiles)
+bool gemm_dense_pair() { const char * e = getenv("B200_GEMM_CTA"); return !(e && atoi(e) == 1); }
+// N tile: 256 columns halve the number of times the weights travel from L2 to the SMs.  1-CTA kernel: only where the 128 x 256
+// tiles still fill the machine; pair kernel: always (few tiles are spread with split-K instead, the L2 feed is what binds)
 int gemm_dense_bn(int M, int N, int sms) {
     if (getenv("B200_GEMM_BN")) return atoi(getenv("B200_GEMM_BN")) == 256 ? 256 : 128;
+    if (gemm_dense_pair()) return N > 128 ? 256 : 128;
     const long long t256 = (long long) ((M + GM_BM - 1) / GM_BM) * ((N + 255) / 256);
     return N > 128 && t256 >= sms ? 256 : 128;
 }
 int gemm_dense_ksplit(int M, int N, int K, int sms) {
     const int bn = gemm_dense_bn(M, N, sms);
-    const int tiles = ((M + GM_BM - 1) / GM_BM) * ((N + bn - 1) / bn);
+    const int bm = gemm_dense_pair() ? 2 * GM_BM : GM_BM, units = gemm_dense_pair() ? sms / 2 : sms;
+    const int tiles = ((M + bm - 1) / bm) * ((N + bn - 1) / bn);
     const int nks = (K + GD_KS - 1) / GD_KS;
-    int s = sms / (tiles > 0 ? tiles : 1);
+    int s = units / (tiles > 0 ? tiles : 1);
     if (s > nks / 8) s = nks / 8;
     if (s > 8) s = 8;
     return s < 2 ? 1 : s;
@@ -329,20 +515,58 @@ static cudaError_t gemm_dense_launch_t(const CUtensorMap & tmA, const CUtensorMa
     return cudaGetLastError();
 }
 
+template <int BN>
+static cudaError_t gemm_dense2_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+    static bool attr_done[64] = {false};          // per device
+    int dev = 0; cudaGetDevice(&dev); dev &= 63;
+    if (!attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN));
+        if (e != cudaSuccess) return e;
+        attr_done[dev] = true;
+    }
+    gemm_dense2_kernel<BN><<<(unsigned) grid, GD_THREADS, gd2_smem(BN), st>>>(tmA, tmB, p);      // __cluster_dims__(2): grid is even
+    return cudaGetLastError();
+}
+
 // A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
 // split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
 cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st) {
     const int bn = gemm_dense_bn(M, N, sms);
+    const bool pair = gemm_dense_pair();
+    const int bm = pair ? 2 * GM_BM : GM_BM;
     CUtensorMap tmA, tmB;
-    if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, bn)) return cudaErrorInvalidValue;
+    if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, pair ? bn / 2 : bn)) return cudaErrorInvalidValue;
     GemmDenseArgs p{};
     p.out = out; p.out_cs = out_cs; p.M = M; p.N = N; p.K = K;
-    p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + bn - 1) / bn;
+    p.mtiles = (M + bm - 1) / bm; p.ntiles = (N + bn - 1) / bn;
     p.ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
     if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; }
     const int work = p.mtiles * p.ntiles * p.ksplit;
-    const int grid = work < sms ? work : sms;
-    const cudaError_t e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
+    cudaError_t e;
+    if (pair) {
+        const int pairs = work < sms / 2 ? work : sms / 2;
+        static const bool trace = getenv("B200_GEMM_TRACE") && atoi(getenv("B200_GEMM_TRACE")) > 0;
+        if (trace && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess) cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
+        e = bn == 256 ? gemm_dense2_launch_t<256>(tmA, tmB, p, 2 * pairs, st) : gemm_dense2_launch_t<128>(tmA, tmB, p, 2 * pairs, st);
+        if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
+            std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
+            cudaStreamSynchronize(st);
+            cudaMemcpy(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+            cudaFree(p.trace);
+            unsigned long long t0 = ~0ull;
+            for (int c = 0; c < 2 * pairs; c++) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
+            static const char * names[8] = {"start", "setup done", "first stage landed", "last MMA issued", "tile 0 complete", "last tile complete", "epilogue done", "end"};
+            fprintf(stderr, "[gemm_dense2 trace] M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d\n", M, N, K, bn, p.ksplit, pairs, work);
+            for (int sl = 0; sl < 8; sl++) {
+                double mn = 1e30, mx = 0, sum = 0; int n = 0;
+                for (int c = 0; c < 2 * pairs; c++) { const unsigned long long v = h[c * 8 + sl]; if (!v) continue; const double u = (double) (v - t0) * 1e-3; mn = u < mn ? u : mn; mx = u > mx ? u : mx; sum += u; n++; }
+                if (n) fprintf(stderr, "  %-20s min %7.2f  avg %7.2f  max %7.2f us  (%d CTAs)\n", names[sl], mn, sum / n, mx, n);
+            }
+        }
+    } else {
+        const int grid = work < sms ? work : sms;
+        e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
+    }
     if (e != cudaSuccess || p.ksplit == 1) return e;
     return launch_reduce_splits(split_ws, p.ksplit, (long long) M * N, M, out, out_cs, 0, st);
 }

@@ -659,7 +659,30 @@ reduce_splits_kernel(const float * __restrict__ ws, const int S, const long long
     *o = v;
 }
 
+// four consecutive m per thread (M, out_cs multiples of 4, 16-byte aligned buffers): 128-bit loads and stores, no division per element
+__global__ void __launch_bounds__(256)
+reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long long MN4, const int M4, float4 * __restrict__ out, const long long out_cs4,
+                      const int add_to_out) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < MN4; i += (long long) gridDim.x * blockDim.x) {
+        const long long n = i / M4; const int m = (int) (i - n * M4);
+        float4 * o = out + n * out_cs4 + m;
+        float4 v = add_to_out ? *o : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int sp = 0; sp < S; sp++) {               // split order: deterministic
+            const float4 w = ws[(long long) sp * MN4 + i];
+            v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
+        }
+        *o = v;
+    }
+}
+
 cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st) {
+    if (M % 4 == 0 && out_cs % 4 == 0 && (((uintptr_t) ws | (uintptr_t) out) & 15) == 0) {
+        const long long MN4 = MN / 4;
+        long long blocks = (MN4 + 255) / 256;
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        reduce_splits4_kernel<<<(unsigned) blocks, 256, 0, st>>>((const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out);
+        return cudaGetLastError();
+    }
     reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(ws, S, MN, M, out, out_cs, add_to_out);
     return cudaGetLastError();
 }
@@ -692,9 +715,7 @@ cudaError_t launch_gemm_i8(int kind, const void * A, const __half * dA_h, const 
     else if (dA_f && !mA) e = gemm_i8_launch_t<1, 2>(tmA, tmB, tmS, p, grid, st);
     else e = cudaErrorInvalidValue;
     if (e != cudaSuccess || p.ksplit == 1) return e;
-    const long long MN = (long long) M * N;
-    reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(split_ws, p.ksplit, MN, M, out, out_cs, add_to_out);
-    return cudaGetLastError();
+    return launch_reduce_splits(split_ws, p.ksplit, (long long) M * N, M, out, out_cs, add_to_out, st);
 }
 
 }  // namespace b200

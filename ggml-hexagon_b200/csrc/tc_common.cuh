@@ -51,6 +51,29 @@ __device__ __forceinline__ void gm_mma_f16(uint32_t tmem_d, uint64_t adesc, uint
 __device__ __forceinline__ void gm_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
+// Whole-warp forms for a convergent MMA-issue loop: every lane executes the statement, elect.sync picks the (always same) lane
+// that issues.  With `if (lane == 0) { ... tcgen05.mma ... }` the operands are per-thread values for the compiler, and every MMA
+// costs an ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" of ~27 dependent instructions in a one-thread loop: ~190 clocks per
+// 64-clock MMA (ncu source page, profiles/r01_l: the issuer never waits for data, the TMA producer waits for the issuer).
+// Convergent code keeps descriptors in uniform registers and the loop at a few instructions per MMA.
+__device__ __forceinline__ void gm_mma_f16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void gm_mbar_expect_tx_elect(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void gm_tma_2d_elect(uint32_t dst, const CUtensorMap * map, uint32_t bar, int c0, int c1) {
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+                 :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void gm_commit_elect(uint32_t bar) {
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" :: "r"(bar) : "memory");
+}
 __device__ __forceinline__ void gm_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void gm_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, int (&v)[32]) {

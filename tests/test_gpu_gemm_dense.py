@@ -19,9 +19,11 @@ def nmse(a, b):
     return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
 
 
-@pytest.fixture(autouse=True)
-def _dense_from_16_columns(monkeypatch):
+# every test runs on both dense kernels: "2" = CTA-pair tiles (tcgen05.mma.cta_group::2, the default), "1" = one CTA per tile
+@pytest.fixture(autouse=True, params=["2", "1"], ids=["pair", "1cta"])
+def _dense_from_16_columns(monkeypatch, request):
     monkeypatch.setenv("B200_GEMM_MIN_N", "16")
+    monkeypatch.setenv("B200_GEMM_CTA", request.param)
     monkeypatch.delenv("B200_GEMM_MODE", raising=False)
     monkeypatch.delenv("B200_GEMM_BN", raising=False)
     monkeypatch.delenv("B200_GEMM_SHADOW_MB", raising=False)
