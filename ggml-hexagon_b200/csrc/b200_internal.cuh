@@ -180,6 +180,10 @@ cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, 
 cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st);
 int gemm_dense_ksplit(int M, int N, int K, int sms);            // > 1: launch_gemm_dense wants a workspace of that many x N x M floats
 cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st);
+bool gemm_dense_pair();                                         // the CTA-pair kernel is selected (default; B200_GEMM_CTA=1: one CTA per tile)
+// 2..3 weight matrices over the same activations in one launch (q / k / v, gate / up); cudaErrorNotSupported without the pair kernel
+cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+                                    const __half * B, int N, int K, int sms, cudaStream_t st);
 
 struct AddArgs {
     const char * a; const char * b; char * d;

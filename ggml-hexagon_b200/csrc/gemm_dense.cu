@@ -42,7 +42,13 @@ struct GemmDenseArgs {
     int mtiles, ntiles;
     int ksplit; long long split_stride;        // split-K: work item = (tile, split); split sp writes its partial sums to out + sp * split_stride
     unsigned long long * trace;                // B200_GEMM_TRACE=1: 8 globaltimer stamps per CTA (pair kernel), else nullptr
+    // pair kernel: up to GD_MAXMAT weight matrices over the same activations in one launch (q / k / v, gate / up): the tile list
+    // runs through all of them, which fills the waves that one 4096-row matrix cannot (32 tiles for 74 CTA pairs)
+    int nmat;
+    float * outs[3]; long long out_css[3]; int Ms[3];
+    int tile_end[3];                           // tiles (m-tile x n-tile) up to and including matrix j; INT_MAX past nmat
 };
+constexpr int GD_MAXMAT = 3;
 __device__ __forceinline__ void gd_stamp(const GemmDenseArgs & p, int slot) {
     if (p.trace) {
         unsigned long long t;
@@ -229,7 +235,8 @@ __device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
 
 template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
-gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
+gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+                   const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
     constexpr int STAGES = gd2_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
     constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
     extern __shared__ uint8_t gd_smem_raw[];
@@ -243,7 +250,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     if (threadIdx.x == 0) gd_stamp(p, 0);
     const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
-    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.mtiles * p.ntiles * p.ksplit;     // p.mtiles counts 256-row tiles
+    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.tile_end[p.nmat - 1] * p.ksplit;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
@@ -264,7 +271,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         // ===== TMA producer (both CTAs).  Work items are numbered n-tile fastest: the pairs that share a weight tile run at the
         // same time, so the fp16 weights come from HBM once (the activations stay in L2 anyway)
         if (lane == 0) {
-            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA0) : "memory");
             asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
         }
         __syncwarp();
@@ -273,13 +280,16 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             uint32_t it = 0;
             for (int work = pair; work < nwork; work += npairs) {
                 const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
-                const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
+                const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
+                const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
+                const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
+                const CUtensorMap * const tmA = j == 0 ? &tmA0 : (j == 1 ? &tmA1 : &tmA2);
                 const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
                     if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, 2 * (STAGE_A + STAGE_B));
-                    gd2_tma_2d(sA + s * STAGE_A, &tmA, lfull0 + s * 8, ks * GD_KS, mt * 2 * GM_BM + (int) rank * GM_BM);
+                    gd2_tma_2d(sA + s * STAGE_A, tmA, lfull0 + s * 8, ks * GD_KS, mt * 2 * GM_BM + (int) rank * GM_BM);
                     gd2_tma_2d(sB + s * STAGE_B, &tmB, lfull0 + s * 8, ks * GD_KS, nt * BN + (int) rank * (BN / 2));
                 }
             }
@@ -319,15 +329,18 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         uint32_t tc = 0;
         for (int work = pair; work < nwork; work += npairs, tc++) {
             const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
-            const int mt = tile / p.ntiles, nt = tile - mt * p.ntiles;
-            float * const outp = p.out + (long long) sp * p.split_stride;
+            const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
+            const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
+            const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
+            float * const outp = p.outs[j] + (long long) sp * p.split_stride;
+            const long long ocs = p.out_css[j];
             const int m = mt * 2 * GM_BM + (int) rank * GM_BM + m_local;
             const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
             gm_mbar_wait(tfull0 + buf * 8, bph);
             gm_fence_after();
             if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
             const int n0 = nt * BN + half * (BN / 2);
-            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * p.out_cs + m, p.out_cs, p.N - n0, m < p.M);
+            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * ocs + m, ocs, p.N - n0, m < p.Ms[j]);
             gm_fence_before();
             __syncwarp();
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
@@ -516,7 +529,7 @@ static cudaError_t gemm_dense_launch_t(const CUtensorMap & tmA, const CUtensorMa
 }
 
 template <int BN>
-static cudaError_t gemm_dense2_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
     static bool attr_done[64] = {false};          // per device
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (!attr_done[dev]) {
@@ -524,51 +537,81 @@ static cudaError_t gemm_dense2_launch_t(const CUtensorMap & tmA, const CUtensorM
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
-    gemm_dense2_kernel<BN><<<(unsigned) grid, GD_THREADS, gd2_smem(BN), st>>>(tmA, tmB, p);      // __cluster_dims__(2): grid is even
+    gemm_dense2_kernel<BN><<<(unsigned) grid, GD_THREADS, gd2_smem(BN), st>>>(tmA[0], tmA[1], tmA[2], tmB, p);      // __cluster_dims__(2): grid is even
     return cudaGetLastError();
 }
 
 // A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
 // split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
-cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st) {
-    const int bn = gemm_dense_bn(M, N, sms);
-    const bool pair = gemm_dense_pair();
-    const int bm = pair ? 2 * GM_BM : GM_BM;
-    CUtensorMap tmA, tmB;
-    if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, pair ? bn / 2 : bn)) return cudaErrorInvalidValue;
+// pair kernel: nmat weight matrices A[j] (fp16 [M[j]][K]) over the same activations B (fp16 [N][K]); out[j][n * out_cs[j] + m]
+static cudaError_t launch_pair(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+                               const __half * B, int N, int K, int sms, int ksplit, float * split_ws, cudaStream_t st) {
+    const int bn = gemm_dense_bn(M[0], N, sms);
+    CUtensorMap tmA[GD_MAXMAT], tmB;
     GemmDenseArgs p{};
-    p.out = out; p.out_cs = out_cs; p.M = M; p.N = N; p.K = K;
-    p.mtiles = (M + bm - 1) / bm; p.ntiles = (N + bn - 1) / bn;
-    p.ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
-    if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; }
-    const int work = p.mtiles * p.ntiles * p.ksplit;
-    cudaError_t e;
-    if (pair) {
-        const int pairs = work < sms / 2 ? work : sms / 2;
-        static const bool trace = getenv("B200_GEMM_TRACE") && atoi(getenv("B200_GEMM_TRACE")) > 0;
-        if (trace && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess) cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
-        e = bn == 256 ? gemm_dense2_launch_t<256>(tmA, tmB, p, 2 * pairs, st) : gemm_dense2_launch_t<128>(tmA, tmB, p, 2 * pairs, st);
-        if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
-            std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
-            cudaStreamSynchronize(st);
-            cudaMemcpy(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost);
-            cudaFree(p.trace);
-            unsigned long long t0 = ~0ull;
-            for (int c = 0; c < 2 * pairs; c++) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
-            static const char * names[8] = {"start", "setup done", "first stage landed", "last MMA issued", "tile 0 complete", "last tile complete", "epilogue done", "end"};
-            fprintf(stderr, "[gemm_dense2 trace] M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d\n", M, N, K, bn, p.ksplit, pairs, work);
-            for (int sl = 0; sl < 8; sl++) {
-                double mn = 1e30, mx = 0, sum = 0; int n = 0;
-                for (int c = 0; c < 2 * pairs; c++) { const unsigned long long v = h[c * 8 + sl]; if (!v) continue; const double u = (double) (v - t0) * 1e-3; mn = u < mn ? u : mn; mx = u > mx ? u : mx; sum += u; n++; }
-                if (n) fprintf(stderr, "  %-20s min %7.2f  avg %7.2f  max %7.2f us  (%d CTAs)\n", names[sl], mn, sum / n, mx, n);
-            }
+    p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit;
+    int tiles = 0;
+    for (int j = 0; j < GD_MAXMAT; j++) {
+        const int jj = j < nmat ? j : 0;
+        if (!make_map_operand(&tmA[j], A[jj], M[jj], K, 2, GM_BM)) return cudaErrorInvalidValue;
+        if (j < nmat) { tiles += ((M[j] + 2 * GM_BM - 1) / (2 * GM_BM)) * p.ntiles; p.outs[j] = out[j]; p.out_css[j] = out_cs[j]; p.Ms[j] = M[j]; p.tile_end[j] = tiles; }
+        else { p.outs[j] = nullptr; p.out_css[j] = 0; p.Ms[j] = 0; p.tile_end[j] = 0x7fffffff; }
+    }
+    if (!make_map_operand(&tmB, B, N, K, 2, bn / 2)) return cudaErrorInvalidValue;
+    if (ksplit > 1) { p.outs[0] = split_ws; p.out_css[0] = M[0]; p.split_stride = (long long) M[0] * N; }      // nmat == 1
+    const int work = tiles * ksplit;
+    const int pairs = work < sms / 2 ? work : sms / 2;
+    static const bool trace = getenv("B200_GEMM_TRACE") && atoi(getenv("B200_GEMM_TRACE")) > 0;
+    if (trace && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess) cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
+    const cudaError_t e = bn == 256 ? gemm_dense2_launch_t<256>(tmA, tmB, p, 2 * pairs, st) : gemm_dense2_launch_t<128>(tmA, tmB, p, 2 * pairs, st);
+    if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
+        std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
+        cudaStreamSynchronize(st);
+        cudaMemcpy(h.data(), p.trace, h.size() * 8, cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        unsigned long long t0 = ~0ull;
+        for (int c = 0; c < 2 * pairs; c++) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
+        static const char * names[8] = {"start", "setup done", "first stage landed", "last MMA issued", "tile 0 complete", "last tile complete", "epilogue done", "end"};
+        fprintf(stderr, "[gemm_dense2 trace] nmat=%d M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d\n", nmat, M[0], N, K, bn, ksplit, pairs, work);
+        for (int sl = 0; sl < 8; sl++) {
+            double mn = 1e30, mx = 0, sum = 0; int n = 0;
+            for (int c = 0; c < 2 * pairs; c++) { const unsigned long long v = h[c * 8 + sl]; if (!v) continue; const double u = (double) (v - t0) * 1e-3; mn = u < mn ? u : mn; mx = u > mx ? u : mx; sum += u; n++; }
+            if (n) fprintf(stderr, "  %-20s min %7.2f  avg %7.2f  max %7.2f us  (%d CTAs)\n", names[sl], mn, sum / n, mx, n);
         }
+    }
+    return e;
+}
+
+// A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
+// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
+cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st) {
+    const int ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
+    cudaError_t e;
+    if (gemm_dense_pair()) {
+        e = launch_pair(&A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, st);
     } else {
+        const int bn = gemm_dense_bn(M, N, sms);
+        CUtensorMap tmA, tmB;
+        if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, bn)) return cudaErrorInvalidValue;
+        GemmDenseArgs p{};
+        p.out = out; p.out_cs = out_cs; p.M = M; p.N = N; p.K = K;
+        p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + bn - 1) / bn;
+        p.ksplit = ksplit;
+        if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; }
+        const int work = p.mtiles * p.ntiles * p.ksplit;
         const int grid = work < sms ? work : sms;
         e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
     }
-    if (e != cudaSuccess || p.ksplit == 1) return e;
-    return launch_reduce_splits(split_ws, p.ksplit, (long long) M * N, M, out, out_cs, 0, st);
+    if (e != cudaSuccess || ksplit == 1) return e;
+    return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st);
+}
+
+// Several weight matrices over the same activations in ONE launch of the pair kernel (no split-K): 2 <= nmat <= 3.
+// Returns cudaErrorNotSupported when the 1-CTA kernel is selected (the caller then launches the matrices one by one).
+cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+                                    const __half * B, int N, int K, int sms, cudaStream_t st) {
+    if (!gemm_dense_pair() || nmat < 1 || nmat > GD_MAXMAT) return cudaErrorNotSupported;
+    return launch_pair(A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, st);
 }
 
 }  // namespace b200

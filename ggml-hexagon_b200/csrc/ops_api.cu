@@ -519,6 +519,7 @@ static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1)
     return 0;
 }
 
+struct FusedAdd;
 static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst /*rowsplit*/,
                       const FusedAdd * fa = nullptr) {
     int rc = mulmat_check(s0, s1, d); if (rc) return rc;
@@ -718,6 +719,64 @@ static int group_len(const b200_node * nodes, int i, int n) {
                     overlap(nodes[i].dst.data, nodes[i].src0.ne[1] * 4 * g_rs_world, nodes[i].src1.data, nodes[i].src0.ne[0] * 4))) return 1;
     return len;
 }
+// consecutive many-column MUL_MATs over the same activations on the dense GEMM (prefill q / k / v, gate / up): one grouped launch of the
+// CTA-pair kernel.  One 4096-row matrix has 32 tiles for 74 CTA pairs; the group's tile list fills the waves and needs no split-K.
+static bool is_dense_mulmat(Ctx * c, const b200_node & n) {
+    if (n.dst.op != B200_OP_MUL_MAT || !is_qweight(n.src0.type) || !(n.src0.flags & B200_TENSOR_REPACKED) || c->rs_on || g_rs_world > 1) return false;
+    const b200_tensor & s0 = n.src0; const b200_tensor & s1 = n.src1;
+    if (s0.ne[2] != 1 || s0.ne[3] != 1 || s1.ne[2] != 1 || s1.ne[3] != 1 || s1.nb[0] != 4 || n.dst.nb[0] != 4) return false;
+    const int64_t K = s0.ne[0], M = s0.ne[1], N = s1.ne[1];
+    const int mn = gemm_min_cols(s0.type);
+    return mn > 0 && N >= mn && K % 32 == 0 && M > 0 && M < 0x7fffffff && N < 0x7fffffff && K < 0x3fffffff;
+}
+static int dense_group_len(Ctx * c, const b200_node * nodes, int i, int n) {
+    if (!gemm_dense_enabled() || !gemm_dense_pair() || !is_dense_mulmat(c, nodes[i])) return 1;
+    const b200_node & a = nodes[i];
+    const int64_t K = a.src0.ne[0], N = a.src1.ne[1];
+    const int64_t xspan = (N - 1) * a.src1.nb[1] + K * 4;
+    auto dspan = [](const b200_node & x) { return (int64_t) ((x.src1.ne[1] - 1) * x.dst.nb[1] + x.src0.ne[1] * 4); };
+    if (overlap(a.dst.data, dspan(a), a.src1.data, xspan)) return 1;
+    int len = 1;
+    while (len < 3 && i + len < n) {
+        const b200_node & b = nodes[i + len];
+        if (!is_dense_mulmat(c, b) || b.src1.data != a.src1.data || b.src0.ne[0] != K || b.src1.ne[1] != N || b.src1.nb[1] != a.src1.nb[1]) break;
+        // no member may write what another member (or the shared activations) occupies
+        bool clash = overlap(b.dst.data, dspan(b), a.src1.data, xspan);
+        for (int j = 0; j < len && !clash; j++) clash = overlap(b.dst.data, dspan(b), nodes[i + j].dst.data, dspan(nodes[i + j]));
+        if (clash) break;
+        len++;
+    }
+    return len;
+}
+static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst, const FusedAdd * fa);
+static int mulmat_dense_group_dev(Ctx * c, const b200_node * nodes, int len) {
+    const int64_t K = nodes[0].src0.ne[0], N = nodes[0].src1.ne[1];
+    const __half * A[3]; float * out[3]; long long ocs[3]; int Ms[3];
+    bool ok = true;
+    for (int j = 0; j < len && ok; j++) {
+        b200_tensor d = nodes[j].dst;
+        int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &d); if (rc) return rc;
+        WPtrs wp; rc = wptrs_of(&nodes[j].src0, &wp); if (rc) return rc;
+        const b200_tensor & s0 = nodes[j].src0;
+        A[j] = ((uintptr_t) wp.p[0] & 15) ? nullptr : shadow_get(c, s0.type, wp, s0.ne[1], K, s0.w_base, (size_t) s0.w_blocks * block_bytes(s0.type), true);
+        ok = A[j] != nullptr;
+        out[j] = (float *) d.data; ocs[j] = d.nb[1] / 4; Ms[j] = (int) s0.ne[1];
+    }
+    if (!ok) {          // no room for a shadow: the members go one by one (weights dequantised per call)
+        for (int j = 0; j < len; j++) { b200_tensor d = nodes[j].dst; int rc = mulmat_dev(c, &nodes[j].src0, &nodes[j].src1, &d, 0, nullptr); if (rc) return rc; }
+        return 0;
+    }
+    int rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+    const b200_tensor & s1 = nodes[0].src1;
+    const bool reuse = c->q_kind == 1 && c->q_ptr == (const void *) s1.data && c->q_K == K && c->q_N == N && c->q_stride == s1.nb[1];
+    if (!reuse) {
+        CU(launch_dequant_act_f16((const float *) s1.data, s1.nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
+        c->q_ptr = s1.data; c->q_K = K; c->q_N = N; c->q_stride = s1.nb[1]; c->q_kind = 1;
+    }
+    CU(launch_gemm_dense_group(A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->st)); c->launches++;
+    return 0;           // (dense_group_len made sure that no dst touches the activations the cached conversion came from)
+}
+
 static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     GemvArgs a{};
     const int64_t K = nodes[0].src0.ne[0], NB = K / 32;
@@ -926,7 +985,9 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             case B200_OP_MUL_MAT: {
                 FusedAdd fa;
                 const int gl = fuse ? group_len(nodes, i, n) : 1;
+                const int dgl = fuse && gl == 1 ? dense_group_len(c, nodes, i, n) : 1;
                 if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
+                else if (dgl > 1) { rc = mulmat_dense_group_dev(c, nodes + i, dgl); used = dgl; }
                 else if (fuse && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
                 else if (c->rs_on) {
                     const int64_t rows = nodes[i].src0.ne[1];

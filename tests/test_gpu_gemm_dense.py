@@ -3,6 +3,7 @@ accumulated in TMEM by tcgen05.mma kind::f16), called through b200_mulmat with m
 Bars: against the oracle's q8_1 block algebra (mode 1) only the fp16 rounding of the two dequantised operands differs
 (relative 2^-12 per element -> NMSE ~4e-8; bar 1e-6); against ggml-cpu semantics (mode 0) the test-backend-ops bar
 NMSE <= 5e-4 (tests/test-backend-ops.cpp:1982-1984)."""
+import os
 import numpy as np
 import pytest
 
@@ -168,6 +169,40 @@ def test_dense_inside_a_captured_graph(monkeypatch, shadow_mb):
             got = sess.to_host(d, (N, M), np.float32)
             assert nmse(got, O.mul_mat(t, raw, xs, 1)) <= DENSE_BAR
         for b in ws + outs + [xb]:
+            b.free()
+
+
+@pytest.mark.parametrize("use_graph", [0, 2])
+@pytest.mark.parametrize("N", [300, 64])
+def test_dense_grouped_launch(use_graph, N):
+    """consecutive MUL_MATs over the same activations (q / k / v, gate / up) go out as one launch of the pair kernel: members of
+    different row counts (ragged against the 256-row tiles) and weight types, every dst checked against the oracle"""
+    rng = np.random.default_rng(67 + N)
+    K = 1536
+    members = [(O.Q4_K, 700), (O.Q6_K, 130), (O.Q4_0, 1024), (O.Q8_0, 256), (O.Q4_0, 257)]      # groups of 3 + 2
+    with B.Session(0) as sess:
+        xs = rng.standard_normal((N, K)).astype(np.float32)
+        xb = sess.to_device(xs)
+        nodes, keep, outs = [], [], []
+        for t, M in members:
+            raw = O.random_blocks(t, M, K, rng)
+            w = sess.weights(t, raw, K)
+            d = sess.malloc(4 * M * N)
+            n = B.Node()
+            n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(d.ptr, [M, N], op=B.OP_MUL_MAT)
+            nodes.append(n); keep.append(w); outs.append((t, raw, M, d))
+        arr = (B.Node * len(nodes))(*nodes)
+        sess.graph_compute(arr, use_graph)                     # first call: builds the fp16 weight shadows
+        sess.sync()
+        before = sess.launch_count()
+        sess.graph_compute(arr, use_graph)
+        sess.sync()
+        if os.environ.get("B200_GEMM_CTA") == "2":
+            assert sess.launch_count() - before <= 3          # one activation conversion + two grouped GEMMs
+        for t, raw, M, d in outs:
+            got = sess.to_host(d, (N, M), np.float32)
+            assert nmse(got, O.mul_mat(t, raw, xs, 1)) <= DENSE_BAR, (t, M)
+        for b in keep + [d for _, _, _, d in outs] + [xb]:
             b.free()
 
 
