@@ -47,7 +47,20 @@ struct GemmDenseArgs {
     int nmat;
     float * outs[3]; long long out_css[3]; int Ms[3];
     int tile_end[3];                           // tiles (m-tile x n-tile) up to and including matrix j; INT_MAX past nmat
+    // the last, partial wave in narrow units: work items >= full_units are 256 x (BN / narrow_f) column slices of the remaining tiles,
+    // so that a wave with few tiles left takes 1/2 or 1/4 of a tile time instead of a whole one (narrow_f = 1: none; ksplit == 1)
+    int full_units, narrow_f;
 };
+struct GdUnit { int tile, sp, n_off, n_w; };    // n_off: first column inside the tile; n_w: columns = N of the MMA
+__device__ __forceinline__ GdUnit gd2_unit(const GemmDenseArgs & p, const int work, const int BN) {
+    GdUnit u;
+    if (work < p.full_units) { u.tile = work / p.ksplit; u.sp = work - u.tile * p.ksplit; u.n_off = 0; u.n_w = BN; }
+    else {
+        const int r = work - p.full_units, t = r / p.narrow_f;
+        u.tile = p.full_units + t; u.sp = 0; u.n_w = BN / p.narrow_f; u.n_off = (r - t * p.narrow_f) * u.n_w;
+    }
+    return u;
+}
 constexpr int GD_MAXMAT = 3;
 __device__ __forceinline__ void gd_stamp(const GemmDenseArgs & p, int slot) {
     if (p.trace) {
@@ -85,6 +98,13 @@ __device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * c
         if (row_ok && ncols > (c + 1) * 32) gd_store_chunk(colp + (long long) (c + 1) * 32 * cs, cs, vb, ncols - (c + 1) * 32);
         if (c + 2 < NCH) gm_tmem_ld_wait();
     }
+}
+
+__device__ __forceinline__ void gd_epilogue_warp1(const uint32_t taddr, float * colp, const long long cs, const int ncols, const bool row_ok) {
+    int va[32];
+    gm_tmem_ld32(taddr, va);
+    gm_tmem_ld_wait();
+    if (row_ok && ncols > 0) gd_store_chunk(colp, cs, va, ncols);
 }
 
 template <int BN>
@@ -236,7 +256,8 @@ __device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
 template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
 gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-                   const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
+                   const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBq,
+                   const GemmDenseArgs p) {
     constexpr int STAGES = gd2_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
     constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
     extern __shared__ uint8_t gd_smem_raw[];
@@ -249,8 +270,12 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     uint32_t rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     if (threadIdx.x == 0) gd_stamp(p, 0);
+    // programmatic dependent launch: the next kernel of the stream may be scheduled as soon as SMs free up (its prologue runs beside our
+    // tail); we ourselves set up barriers and TMEM beside the previous kernel's tail and wait for its results only before the first load
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
-    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.tile_end[p.nmat - 1] * p.ksplit;
+    const int nks = (p.K + GD_KS - 1) / GD_KS;
+    const int nwork = p.full_units + (p.tile_end[p.nmat - 1] * p.ksplit - p.full_units) * p.narrow_f;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
@@ -265,6 +290,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     gd2_cluster_sync();
     gm_fence_after();
     const uint32_t tmem = *tmem_slot;
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // every role: loads of B, stores of dst / the split workspace
     if (threadIdx.x == 0) gd_stamp(p, 1);
 
     if (warp == 0) {
@@ -279,28 +305,33 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
             const uint32_t lfull0 = gd2_mapa(full0, 0);
             uint32_t it = 0;
             for (int work = pair; work < nwork; work += npairs) {
-                const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+                const GdUnit u = gd2_unit(p, work, BN);
+                const int tile = u.tile, sp = u.sp;
                 const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
                 const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
                 const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
                 const CUtensorMap * const tmA = j == 0 ? &tmA0 : (j == 1 ? &tmA1 : &tmA2);
+                const CUtensorMap * const tmBu = u.n_w == BN ? &tmB : (u.n_w == BN / 2 ? &tmBh : &tmBq);      // box rows = n_w / 2
+                const uint32_t tx = 2u * (STAGE_A + (uint32_t) (u.n_w / 2) * 128u);
+                const int brow = nt * BN + u.n_off + (int) rank * (u.n_w / 2);
                 const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
-                    if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, 2 * (STAGE_A + STAGE_B));
+                    if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, tx);
                     gd2_tma_2d(sA + s * STAGE_A, tmA, lfull0 + s * 8, ks * GD_KS, mt * 2 * GM_BM + (int) rank * GM_BM);
-                    gd2_tma_2d(sB + s * STAGE_B, &tmB, lfull0 + s * 8, ks * GD_KS, nt * BN + (int) rank * (BN / 2));
+                    gd2_tma_2d(sB + s * STAGE_B, tmBu, lfull0 + s * 8, ks * GD_KS, brow);
                 }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer: warp 1 of the leader CTA (whole warp, one elected lane issues), M = 256 over the pair
         if (rank == 0) {
-            const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) ((2 * GM_BM) >> 4) << 24);
             uint32_t it = 0, tc = 0;
             for (int work = pair; work < nwork; work += npairs, tc++) {
-                const int sp = work % p.ksplit;
+                const GdUnit u = gd2_unit(p, work, BN);
+                const int sp = u.sp;
+                const uint32_t idesc = (1u << 4) | ((uint32_t) (u.n_w >> 3) << 17) | ((uint32_t) ((2 * GM_BM) >> 4) << 24);
                 const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
                 const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
                 gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
@@ -324,11 +355,12 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
         // ===== epilogue (both CTAs): this CTA's TMEM holds rows rank * 128 .. +127 of the pair tile, all BN columns
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int m_local = q * 32 + lane;
-        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + half * (BN / 2);
+        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16);
         const uint32_t ltempty0 = gd2_mapa(tempty0, 0);
         uint32_t tc = 0;
         for (int work = pair; work < nwork; work += npairs, tc++) {
-            const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
+            const GdUnit u = gd2_unit(p, work, BN);
+            const int tile = u.tile, sp = u.sp;
             const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
             const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
             const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
@@ -339,8 +371,16 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
             gm_mbar_wait(tfull0 + buf * 8, bph);
             gm_fence_after();
             if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
-            const int n0 = nt * BN + half * (BN / 2);
-            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * ocs + m, ocs, p.N - n0, m < p.Ms[j]);
+            // this warp: TMEM lanes q * 32 .. +31, columns half * (n_w / 2) .. + n_w / 2 of the unit
+            const int c0 = half * (u.n_w / 2), n0 = nt * BN + u.n_off + c0;
+            const uint32_t ta = tbase + buf * BN + c0;
+            float * const colp = outp + (long long) n0 * ocs + m;
+            const bool row_ok = m < p.Ms[j];
+            if (u.n_w == BN)               gd_epilogue_warp<BN / 64>(ta, colp, ocs, p.N - n0, row_ok);
+            else if (u.n_w == BN / 2) {
+                if constexpr (BN == 256)   gd_epilogue_warp<BN / 128>(ta, colp, ocs, p.N - n0, row_ok);
+                else                       gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
+            } else                         gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
             gm_fence_before();
             __syncwarp();
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
@@ -456,6 +496,8 @@ dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, 
     const int NB = K / 32;
     const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
     const long long blk = gid >> 3;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // x comes from the kernels before us; out may still be read by the GEMM before us
     if (blk >= (long long) NB * N) return;
     const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 7);
     const float4 v = *(const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 4) * 4);
@@ -476,8 +518,13 @@ dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, 
 
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st) {
     const long long threads = (long long) (K / 4) * N;
-    dequant_act_f16_kernel<<<(unsigned) ((threads + 255) / 256), 256, 0, st>>>((const char *) x, row_stride_bytes, K, N, out);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) ((threads + 255) / 256)); cfg.blockDim = dim3(256); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel, (const char *) x, row_stride_bytes, K, N, out);
 }
 // weights of `type` (SoA field pointers w, nblocks native blocks) -> dequantised fp16 [M][K]
 cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st) {
@@ -529,7 +576,7 @@ static cudaError_t gemm_dense_launch_t(const CUtensorMap & tmA, const CUtensorMa
 }
 
 template <int BN>
-static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
     static bool attr_done[64] = {false};          // per device
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (!attr_done[dev]) {
@@ -537,8 +584,13 @@ static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorM
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
-    gemm_dense2_kernel<BN><<<(unsigned) grid, GD_THREADS, gd2_smem(BN), st>>>(tmA[0], tmA[1], tmA[2], tmB, p);      // __cluster_dims__(2): grid is even
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GD_THREADS); cfg.dynamicSmemBytes = gd2_smem(BN); cfg.stream = st;      // __cluster_dims__(2): grid is even
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, gemm_dense2_kernel<BN>, tmA[0], tmA[1], tmA[2], tmB[0], tmB[1], tmB[2], p);
 }
 
 // A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
@@ -547,7 +599,7 @@ static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorM
 static cudaError_t launch_pair(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
                                const __half * B, int N, int K, int sms, int ksplit, float * split_ws, cudaStream_t st) {
     const int bn = gemm_dense_bn(M[0], N, sms);
-    CUtensorMap tmA[GD_MAXMAT], tmB;
+    CUtensorMap tmA[GD_MAXMAT], tmB[3];
     GemmDenseArgs p{};
     p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit;
     int tiles = 0;
@@ -557,12 +609,24 @@ static cudaError_t launch_pair(const __half * const * A, float * const * out, co
         if (j < nmat) { tiles += ((M[j] + 2 * GM_BM - 1) / (2 * GM_BM)) * p.ntiles; p.outs[j] = out[j]; p.out_css[j] = out_cs[j]; p.Ms[j] = M[j]; p.tile_end[j] = tiles; }
         else { p.outs[j] = nullptr; p.out_css[j] = 0; p.Ms[j] = 0; p.tile_end[j] = 0x7fffffff; }
     }
-    if (!make_map_operand(&tmB, B, N, K, 2, bn / 2)) return cudaErrorInvalidValue;
+    for (int f = 0; f < 3; f++)                 // activation boxes for full units and for the 1/2 and 1/4 wide units of the last wave
+        if (!make_map_operand(&tmB[f], B, N, K, 2, (bn / 2) >> f)) return cudaErrorInvalidValue;
     if (ksplit > 1) { p.outs[0] = split_ws; p.out_css[0] = M[0]; p.split_stride = (long long) M[0] * N; }      // nmat == 1
-    const int work = tiles * ksplit;
-    const int pairs = work < sms / 2 ? work : sms / 2;
+    const int P = sms / 2;
+    p.full_units = tiles * ksplit; p.narrow_f = 1;
+    static const bool narrow_on = !(getenv("B200_GEMM_NARROW") && atoi(getenv("B200_GEMM_NARROW")) == 0);
+    if (narrow_on && ksplit == 1 && bn == 256 && tiles > P) {
+        const int rem = tiles % P;
+        const int f = rem == 0 ? 1 : (4 * rem <= P ? 4 : (2 * rem <= P ? 2 : 1));
+        if (f > 1) { p.full_units = tiles - rem; p.narrow_f = f; }
+    }
+    const int work = p.full_units + (tiles * ksplit - p.full_units) * p.narrow_f;
+    const int pairs = work < P ? work : P;
     static const bool trace = getenv("B200_GEMM_TRACE") && atoi(getenv("B200_GEMM_TRACE")) > 0;
-    if (trace && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess) cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (trace) cudaStreamIsCapturing(st, &cap);                 // the trace allocates and synchronises: not inside a stream capture
+    if (trace && cap == cudaStreamCaptureStatusNone && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess)
+        cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
     const cudaError_t e = bn == 256 ? gemm_dense2_launch_t<256>(tmA, tmB, p, 2 * pairs, st) : gemm_dense2_launch_t<128>(tmA, tmB, p, 2 * pairs, st);
     if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
         std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
@@ -572,7 +636,7 @@ static cudaError_t launch_pair(const __half * const * A, float * const * out, co
         unsigned long long t0 = ~0ull;
         for (int c = 0; c < 2 * pairs; c++) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
         static const char * names[8] = {"start", "setup done", "first stage landed", "last MMA issued", "tile 0 complete", "last tile complete", "epilogue done", "end"};
-        fprintf(stderr, "[gemm_dense2 trace] nmat=%d M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d\n", nmat, M[0], N, K, bn, ksplit, pairs, work);
+        fprintf(stderr, "[gemm_dense2 trace] nmat=%d M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d (full %d, narrow x%d)\n", nmat, M[0], N, K, bn, ksplit, pairs, work, p.full_units, p.narrow_f);
         for (int sl = 0; sl < 8; sl++) {
             double mn = 1e30, mx = 0, sum = 0; int n = 0;
             for (int c = 0; c < 2 * pairs; c++) { const unsigned long long v = h[c * 8 + sl]; if (!v) continue; const double u = (double) (v - t0) * 1e-3; mn = u < mn ? u : mn; mx = u > mx ? u : mx; sum += u; n++; }

@@ -663,6 +663,8 @@ reduce_splits_kernel(const float * __restrict__ ws, const int S, const long long
 __global__ void __launch_bounds__(256)
 reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long long MN4, const int M4, float4 * __restrict__ out, const long long out_cs4,
                       const int add_to_out) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < MN4; i += (long long) gridDim.x * blockDim.x) {
         const long long n = i / M4; const int m = (int) (i - n * M4);
         float4 * o = out + n * out_cs4 + m;
@@ -680,8 +682,13 @@ cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, f
         const long long MN4 = MN / 4;
         long long blocks = (MN4 + 255) / 256;
         if (blocks > 148 * 8) blocks = 148 * 8;
-        reduce_splits4_kernel<<<(unsigned) blocks, 256, 0, st>>>((const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out);
-        return cudaGetLastError();
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned) blocks); cfg.blockDim = dim3(256); cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+        return cudaLaunchKernelEx(&cfg, reduce_splits4_kernel, (const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out);
     }
     reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(ws, S, MN, M, out, out_cs, add_to_out);
     return cudaGetLastError();

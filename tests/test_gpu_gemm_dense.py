@@ -206,6 +206,21 @@ def test_dense_grouped_launch(use_graph, N):
             b.free()
 
 
+@pytest.mark.parametrize("M,what", [(10000, "80 pair tiles: 6 left after a wave of 74 -> quarter-width units"),
+                                    (13200, "104 pair tiles: 30 left -> half-width units"),
+                                    (9500, "76 pair tiles: 2 left -> quarter-width units")])
+def test_dense_narrow_units_of_the_last_wave(sess, M, what):
+    """more tiles than CTA pairs: the tiles left over after the full waves are cut into 256 x 128 / 256 x 64 units"""
+    rng = np.random.default_rng(71 + M)
+    K, N = 256, 300
+    raw = O.random_blocks(O.Q4_0, M, K, rng)
+    w = sess.weights(O.Q4_0, raw, K)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    got = sess.mulmat(w, x)
+    assert nmse(got, O.mul_mat(O.Q4_0, raw, x, 1)) <= DENSE_BAR, what
+    w.free()
+
+
 def test_dense_close_to_exact_mode(sess, monkeypatch):
     """the two prefill kernels on the same inputs: they differ by the fp16 rounding of the operands only"""
     rng = np.random.default_rng(59)
