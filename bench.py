@@ -347,8 +347,9 @@ def time_prefill(B, s, model, N=512, mixes=(("q8_0", lambda name: Q8_0), ("q4_0"
     mode = os.environ.get("B200_GEMM_MODE", "dense")
     res["mode"] = mode
     res["note"] = ("N=%d columns, MUL_MAT only, per shape back to back on one matrix (operand preparation inside the timed region); " % N +
-                   ("dense fp16 tcgen05.mma over the whole K with the block scales folded into the operands, weights from their cached fp16 "
-                    "shadow: bound by the L2 -> shared-memory operand feed of 128-row tiles (DESIGN.md section 6)" if mode != "exact" else
+                   ("dense fp16 tcgen05.mma.cta_group::2 over the whole K (256 x 256 tiles per CTA pair) with the block scales folded into the "
+                    "operands, weights from their cached fp16 shadow; a single matrix alone pays wave quantisation and split-K, the whole-model "
+                    "leg ('model') groups q/k/v and gate/up into one launch (DESIGN.md section 6)" if mode != "exact" else
                     "exact per-block tcgen05.mma sums + fp32 scale-accumulate: bound by the epilogue's issue slots, not the tensor pipe "
                     "(DESIGN.md section 6)"))
     return res

@@ -490,34 +490,39 @@ dequant_q6_K_f16_kernel(const uint32_t * __restrict__ ql, const uint32_t * __res
 }
 
 // activations: f32 [N][K] -> q8_1 (d = amax / 127 rounded to fp16, q = round(x / d); quantize_row_q8_1_ref ggml-quants.c:220-253)
-// -> fp16(d * q), saturating.  8 lanes per 32-element block, one float4 each.
+// -> fp16(d * q), saturating.  4 lanes per 32-element block, two float4 loads and one 16-byte store each.
 __global__ void __launch_bounds__(256)
 dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N, __half * __restrict__ out) {
     const int NB = K / 32;
     const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    const long long blk = gid >> 3;
+    const long long blk = gid >> 2;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");      // x comes from the kernels before us; out may still be read by the GEMM before us
-    if (blk >= (long long) NB * N) return;
-    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 7);
-    const float4 v = *(const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 4) * 4);
-    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+    if (blk >= (long long) NB * N) return;                   // (whole groups of 4 lanes leave together: NB * N blocks, 4 lanes each)
+    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 3);
+    const float4 * src = (const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 8) * 4);
+    const float4 v = src[0], w = src[1];
+    float amax = fmaxf(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))),
+                       fmaxf(fmaxf(fabsf(w.x), fabsf(w.y)), fmaxf(fabsf(w.z), fabsf(w.w))));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
     const float d  = __fdiv_rn(amax, 127.0f);
     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
     const float dh = __half2float(__float2half_rn(d));
     const float r0 = dh * roundf(__fmul_rn(v.x, id)), r1 = dh * roundf(__fmul_rn(v.y, id));
     const float r2 = dh * roundf(__fmul_rn(v.z, id)), r3 = dh * roundf(__fmul_rn(v.w, id));
-    uint32_t h01, h23;
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h01) : "f"(r1), "f"(r0));
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h23) : "f"(r3), "f"(r2));
-    *(uint2 *) (out + (long long) row * K + b * 32 + sub * 4) = make_uint2(h01, h23);
+    const float r4 = dh * roundf(__fmul_rn(w.x, id)), r5 = dh * roundf(__fmul_rn(w.y, id));
+    const float r6 = dh * roundf(__fmul_rn(w.z, id)), r7 = dh * roundf(__fmul_rn(w.w, id));
+    uint4 h;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.x) : "f"(r1), "f"(r0));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.y) : "f"(r3), "f"(r2));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.z) : "f"(r5), "f"(r4));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.w) : "f"(r7), "f"(r6));
+    *(uint4 *) (out + (long long) row * K + b * 32 + sub * 8) = h;
 }
 
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st) {
-    const long long threads = (long long) (K / 4) * N;
+    const long long threads = (long long) (K / 8) * N;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) ((threads + 255) / 256)); cfg.blockDim = dim3(256); cfg.stream = st;
     cudaLaunchAttribute at[1];

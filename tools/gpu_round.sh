@@ -14,7 +14,10 @@ if [ $rc -eq 0 ]; then
       python bench.py --steps 2 --warmup 3 --no-cpu --no-shapes > $O/ncu_launch.log 2>&1; echo "ncu launches rc=$?" | tee -a $O/rc.log
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:gemv5_kernel -s 200 -c 4 -f -o $O/gemv5_full \
       python bench.py --steps 2 --warmup 3 --no-cpu --no-shapes > $O/ncu_gemv5.log 2>&1; echo "ncu gemv5 rc=$?" | tee -a $O/rc.log
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:gemm_dense -s 4 -c 3 -f -o $O/gemm_dense_full \
-      python tools/gemm_bench.py 512 q4_0 2 > $O/ncu_dense.log 2>&1; echo "ncu dense rc=$?" | tee -a $O/rc.log
+  timeout 300 python tools/pp_model.py llama2-7b q4_0 512 5 > $O/pp_model.log 2>&1; echo "pp_model rc=$?" | tee -a $O/rc.log
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 1200 -c 800 --csv --log-file $O/pp_launches.csv \
+      python tools/pp_model.py llama2-7b q4_0 512 3 > $O/ncu_pp_launch.log 2>&1; echo "ncu pp launches rc=$?" | tee -a $O/rc.log
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:gemm_dense2 -s 300 -c 4 -f -o $O/gemm_dense2_full \
+      python tools/pp_model.py llama2-7b q4_0 512 2 > $O/ncu_dense.log 2>&1; echo "ncu dense2 rc=$?" | tee -a $O/rc.log
 fi
 tail -3 $O/pytest_gpu.log; cat $O/bench.json | cut -c1-600
