@@ -103,6 +103,8 @@ struct LlGatherArgs { uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_o
 cudaError_t launch_ll_gather(const LlGatherArgs & a, cudaStream_t st);
 // end of a submission: *ll_count += nops
 cudaError_t launch_ll_bump(uint32_t * ll_count, uint32_t nops, cudaStream_t st);
+// row-split prefill: copy this rank's rows x N slice of dst (local, column stride dcs floats) into every peer's dst (heap offset + delta)
+cudaError_t launch_rowsplit_push(const float * slice, long long rows, long long N, long long dcs, int npeers, const long long * peer_delta, cudaStream_t st);
 // one warp: tell every peer "my slice of the op is in your memory" (release, system scope), then wait for theirs
 cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr /* [npeers] */,
                                      const int * peer_rank /* [npeers] */, cudaStream_t st);

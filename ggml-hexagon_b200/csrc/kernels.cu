@@ -274,6 +274,38 @@ __global__ void rowsplit_exchange_kernel(uint32_t * local_flags, uint32_t * coun
     __syncwarp();
     if (p == 0) *counter = n;
 }
+// Row-split prefill: the dense GEMM wrote this rank's rows x N slice of dst (column stride dcs) into LOCAL memory; copy it into every
+// peer's dst at the same heap offset over NVLink (plain 16-byte stores; the flag exchange that follows publishes them)
+struct PushPeers { long long delta[7]; };
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+rowsplit_push_kernel(const float * __restrict__ src, const long long rows, const long long N, const long long dcs, const int npeers, const PushPeers pp) {
+    const long long per = VEC ? rows / 4 : rows, total = per * N;
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long) gridDim.x * blockDim.x) {
+        const long long n = i / per, m = i - n * per;
+        if (VEC) {
+            const float4 * p = (const float4 *) (src + n * dcs) + m;
+            const float4 v = *p;
+            for (int q = 0; q < npeers; q++) *(float4 *) ((char *) p + pp.delta[q]) = v;
+        } else {
+            const float * p = src + n * dcs + m;
+            const float v = *p;
+            for (int q = 0; q < npeers; q++) *(float *) ((char *) p + pp.delta[q]) = v;
+        }
+    }
+}
+cudaError_t launch_rowsplit_push(const float * slice, long long rows, long long N, long long dcs, int npeers, const long long * peer_delta, cudaStream_t st) {
+    if (npeers <= 0 || rows <= 0 || N <= 0) return cudaSuccess;
+    PushPeers pp{};
+    for (int i = 0; i < npeers && i < 7; i++) pp.delta[i] = peer_delta[i];
+    const bool vec = rows % 4 == 0 && dcs % 4 == 0 && ((uintptr_t) slice & 15) == 0;
+    const long long total = (vec ? rows / 4 : rows) * N;
+    long long blocks = (total + 255) / 256; if (blocks > 148 * 8) blocks = 148 * 8;
+    if (vec) rowsplit_push_kernel<true><<<(unsigned) blocks, 256, 0, st>>>(slice, rows, N, dcs, npeers, pp);
+    else     rowsplit_push_kernel<false><<<(unsigned) blocks, 256, 0, st>>>(slice, rows, N, dcs, npeers, pp);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr,
                                      const int * peer_rank, cudaStream_t st) {
     ExchangeArgs a{};

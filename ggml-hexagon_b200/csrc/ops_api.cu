@@ -450,6 +450,7 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
     a.rs_signal = sep ? 0 : 1; a.rs_ctrl = (uint32_t *) (c->rs_heap + 260);
     return 0;
 }
+static bool rs_flag_exchange_separate() { return !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0); }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
     if (c->ll_nmat > 0) {
@@ -533,7 +534,8 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
     const int gemm_min_n = gemm_min_cols(s0->type);
     const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
-                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 && !c->rs_on;
+                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 &&
+                          (!c->rs_on || (gemm_dense_enabled() && rs_flag_exchange_separate()));   // row split: dense path + slice push
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
@@ -561,6 +563,16 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
             CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st));
             c->launches += 1 + (ksp > 1 ? 1 : 0);
+            if (c->rs_on && c->world > 1) {
+                // row split: y is this rank's M rows of every dst column; the slice goes into every peer's copy over NVLink, and the
+                // flag exchange at the end of the op (rs_exchange below) publishes it
+                const char * p = (const char *) y; const int64_t span = ((N - 1) * dcs + M) * 4;
+                if (p < c->rs_heap + RS_HDR || p + span > c->rs_heap + c->rs_heap_bytes)
+                    return fail(B200_EINVAL, "rowsplit: dst is outside the symmetric heap (b200_rowsplit_heap_create)");
+                long long deltas[7]; int np = 0;
+                for (int r = 0; r < c->world; r++) if (r != c->rank) deltas[np++] = (long long) (c->rs_peer[r] - c->rs_heap);
+                CU(launch_rowsplit_push(y, M, N, dcs, np, deltas, c->st)); c->launches++;
+            }
         } else if (q && use_gemm) {
             // ---- many columns, B200_GEMM_MODE=exact: int8 tensor-core GEMM with exact per-block sums (gemm_i8.cu)
             const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
@@ -1048,7 +1060,7 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     }
     if (any_host) return fail(B200_ENOTSUP, "graph_compute takes device tensors only");
     int rc = ensure_act(c, need_act); if (rc) return rc;
-    if (use_cuda_graph && !c->rs_on)
+    if (use_cuda_graph && (!c->rs_on || gemm_dense_enabled()))      // (row split: src0 is the rank's slice, so the sizes are the slice's)
         for (int i = 0; i < n; i++)
             if (nodes[i].dst.op == B200_OP_MUL_MAT) { rc = presize_gemm(c, &nodes[i].src0, &nodes[i].src1); if (rc) return rc; }
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
