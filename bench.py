@@ -157,9 +157,10 @@ def measured_peak_hbm():
 class DecodeWorkload:
     """All MUL_MAT/ADD nodes of one decoded token, device resident.  Row r-th slice of every weight when world > 1."""
 
-    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0", ncols=1, share=None):
+    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0", ncols=1, share=None, heap_cols=0):
         """ncols > 1: the same node list over ncols activation columns (prefill); share: another workload of the same model and
-        quant whose HBM weights are used instead of uploading a second copy"""
+        quant whose HBM weights (and, under row split, symmetric heap) are used instead of making a second copy; heap_cols: room in
+        the symmetric heap for a later workload of that many columns sharing it"""
         import ctypes as C
         self.mode = mode
         self.ncols, self.share = ncols, share
@@ -197,8 +198,12 @@ class DecodeWorkload:
         kv = dict((n, m) for n, m, _ in layer)["wk"]
         # row split: activations live in the symmetric heap (same offsets on every rank) so that the GEMVs can store
         # their slices straight into every peer's copy over NVLink
-        self.heap = B.SymHeap(sess, 4 * (8 * h + 2 * kv + 2 * f + out[1]) + 64 * 256) if world > 1 else None
-        mk = (lambda n: self.heap.malloc(4 * n)) if world > 1 else (lambda n: sess.malloc(4 * n * ncols))
+        act_floats = 8 * h + 2 * kv + 2 * f + out[1]
+        if world > 1:
+            self.heap = share.heap if share is not None else B.SymHeap(sess, 4 * act_floats * (ncols + heap_cols) + 2 * 64 * 256)
+        else:
+            self.heap = None
+        mk = (lambda n: self.heap.malloc(4 * n * ncols)) if world > 1 else (lambda n: sess.malloc(4 * n * ncols))
         self.x = mk(h); self.q = mk(h); self.k = mk(kv); self.v = mk(kv); self.o = mk(h); self.hres = mk(h)
         self.g = mk(f); self.u = mk(f); self.dn = mk(h); self.x2 = mk(h); self.x3 = mk(h); self.logits = mk(out[1])
         self.x_host = np.random.default_rng(seed + 1).uniform(-1, 1, h * ncols).astype(np.float32)
@@ -519,7 +524,8 @@ def run_b200(args, rank, world):
         dist.broadcast(idb, 0)
         idh = (C.c_uint8 * 128)(*idb.cpu().tolist())
         B._ck(B.lib().b200_rowsplit_init(s.h, idh, rank, world))
-    wl = DecodeWorkload(B, s, model, rank, world, mode=args.rowsplit)
+    rs_prefill_cols = 512 if world > 1 and args.rowsplit == "p2p" else 0
+    wl = DecodeWorkload(B, s, model, rank, world, mode=args.rowsplit, heap_cols=rs_prefill_cols)
     if world > 1:
         import torch
         mine = torch.tensor(list(wl.heap.handle), dtype=torch.uint8, device="cuda")
@@ -586,6 +592,29 @@ def run_b200(args, rank, world):
         prefill = time_prefill(B, s, model)
         prefill["exact_mode"] = with_env("B200_GEMM_MODE", "exact", lambda: time_prefill(B, s, model, iters=3))
         prefill["model"] = time_prefill_model(B, s, wl)
+    rs_prefill = None
+    if rs_prefill_cols:
+        # BASELINE.json configs[4] with N = 512 columns: every rank runs the dense GEMM on its row slices and pushes them into the
+        # peers' dst over NVLink (every rank takes part: the flag exchange per op is collective)
+        pw = DecodeWorkload(B, s, model, rank, world, mode=args.rowsplit, ncols=rs_prefill_cols, share=wl)
+        for _ in range(2):
+            pw.step()
+        barrier()
+        pe0, pe1 = s.event(), s.event()
+        s.record(pe0)
+        for _ in range(3):
+            pw.step()
+        s.record(pe1)
+        pms = s.elapsed_ms(pe0, pe1) / 3
+        barrier()
+        import torch
+        t = torch.tensor([pms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        pms = float(t.item())
+        pflops = 2.0 * rs_prefill_cols * (sum(m * k for _, m, k in wl.layer) * wl.L + wl.out[1] * wl.out[2])
+        rs_prefill = {"tokens_per_s": round(rs_prefill_cols / pms * 1e3, 1), "ms": round(pms, 3), "TFLOPS_all_gpus": round(pflops / pms / 1e9, 1),
+                      "note": "pp%d of the same model under row split: dense GEMM on each rank's row slices + slice push over NVLink + flag "
+                              "exchange per op, one CUDA graph per rank; max over ranks" % rs_prefill_cols}
     kquant = None
     adds = time_add(B, s) if world == 1 and not args.no_shapes and rank == 0 else None
     if world == 1 and not args.no_shapes and rank == 0:
@@ -619,6 +648,8 @@ def run_b200(args, rank, world):
         line["shapes"] = shapes
     if prefill:
         line["pp512"] = prefill
+    if rs_prefill is not None:
+        line["pp512_rowsplit"] = rs_prefill
     if kquant:
         line["kquant"] = kquant
     if adds:

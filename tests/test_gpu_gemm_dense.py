@@ -221,6 +221,42 @@ def test_dense_narrow_units_of_the_last_wave(sess, M, what):
     w.free()
 
 
+@pytest.mark.parametrize("model_shape", [("llama2-7b gate+up", O.Q4_0, [11008, 11008], 4096), ("llama2-7b q+k+v", O.Q4_0, [4096, 4096, 4096], 4096),
+                                         ("llama3-8b q+k+v", O.Q4_K, [4096, 1024, 1024], 4096), ("llama3-8b gate+up", O.Q4_K, [14336, 14336], 4096),
+                                         ("llama2-7b down", O.Q8_0, [4096], 11008)])
+def test_dense_full_size_against_exact_mode(monkeypatch, model_shape):
+    """BASELINE.json's prefill shapes at full size (N = 512), as the node list submits them (grouped launches, narrow units of the last
+    wave, split-K): the oracle is too slow here, so the check is against the exact per-block GEMM (gemm_i8.cu, itself oracle-checked at
+    small sizes): only the fp16 rounding of the operands may differ"""
+    name, t, Ms, K = model_shape
+    N = 512
+    rng = np.random.default_rng(len(name) + K)
+    with B.Session(0) as sess:
+        xs = rng.standard_normal((N, K)).astype(np.float32)
+        xb = sess.to_device(xs)
+        nodes, keep, outs = [], [], []
+        for M in Ms:
+            raw = np.tile(O.random_blocks(t, 256, K, rng), (M // 256, 1))
+            w = sess.weights(t, raw, K)
+            d = sess.malloc(4 * M * N)
+            n = B.Node()
+            n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(d.ptr, [M, N], op=B.OP_MUL_MAT)
+            nodes.append(n); keep.append(w); outs.append((M, d))
+        arr = (B.Node * len(nodes))(*nodes)
+        sess.graph_compute(arr, 0)
+        sess.sync()
+        dense = [sess.to_host(d, (N, M), np.float32) for M, d in outs]
+        monkeypatch.setenv("B200_GEMM_MODE", "exact")
+        sess.graph_compute(arr, 0)
+        sess.sync()
+        for (M, d), got in zip(outs, dense):
+            exact = sess.to_host(d, (N, M), np.float32)
+            assert np.isfinite(got).all()
+            assert nmse(got, exact) <= DENSE_BAR, (name, M)
+        for b in keep + [d for _, d in outs] + [xb]:
+            b.free()
+
+
 def test_dense_close_to_exact_mode(sess, monkeypatch):
     """the two prefill kernels on the same inputs: they differ by the fp16 rounding of the operands only"""
     rng = np.random.default_rng(59)
