@@ -402,6 +402,10 @@ def time_prefill_model(B, s, wl, N=512, steps=5):
     pw.free()
     return {"tokens_per_s": round(N / sec, 1), "ms": round(sec * 1e3, 3), "TFLOPS": round(flops / sec / 1e12, 1),
             "frac_of_measured_16bit_tensor_peak": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "tensor_peak_TFLOPS": tc_peak,
+            "roofline": {"bound": "tensor", "achieved": round(flops / sec / 1e12, 1), "peak": tc_peak, "unit": "TFLOP/s",
+                         "frac": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "traffic": None,
+                         "kernel": "gemm_dense2_kernel<256> (tcgen05.mma.cta_group::2 kind::f16)",
+                         "note": "2*M*N*K of every MUL_MAT of the step / device time of the whole step (conversions, reduces, ADDs included)"},
             "kernels_per_step": int(launches), "first_call_ms": round(first_s * 1e3, 1),
             "note": "whole node list (%d MUL_MAT + %d ADD) over N=%d columns, one graph_compute per step, distinct weights per layer; "
                     "peak = MEASURED_PEAKS.json bf16_tflops_sustained (fp16 and bf16 run at the same tensor rate)" % (wl.n_mulmat, 2 * wl.L, N)}

@@ -176,12 +176,16 @@ int gemm_i8_ksplit(int M, int N, int K, int kind, int sms);     // > 1: launch_g
 // fp16 operand preparation for kind 1 / 2 (modes as launch_quantize_rows_i8, without the q6_K padding)
 cudaError_t launch_quantize_rows_f16(const float * x, long long row_stride_bytes, int K, int N, __half * q, float * dB, long long ldb, int mode, cudaStream_t st);
 cudaError_t launch_unpack_f16(int type, const WPtrs & w, long long nblocks, __half * out, float * wS, float * wM, cudaStream_t st);
-cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st);
+// res_dst != null: also res_dst[i] = res_src[i] + out[i] over [N][M] contiguous (the residual ADD node behind the MUL_MAT, fused)
+cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st,
+                                 const float * res_src = nullptr, float * res_dst = nullptr);
+bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst);
 // ---- dense prefill GEMM (gemm_dense.cu): block scales folded into fp16 operands, the whole K accumulated in TMEM
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st);
 cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st);
 int gemm_dense_ksplit(int M, int N, int K, int sms);            // > 1: launch_gemm_dense wants a workspace of that many x N x M floats
-cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st);
+cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
+                              const float * res_src = nullptr, float * res_dst = nullptr);   // residual ADD fused into the split-K reduce (needs split_ws and ksplit > 1)
 bool gemm_dense_pair();                                         // the CTA-pair kernel is selected (default; B200_GEMM_CTA=1: one CTA per tile)
 // 2..3 weight matrices over the same activations in one launch (q / k / v, gate / up); cudaErrorNotSupported without the pair kernel
 cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,

@@ -662,7 +662,7 @@ reduce_splits_kernel(const float * __restrict__ ws, const int S, const long long
 // four consecutive m per thread (M, out_cs multiples of 4, 16-byte aligned buffers): 128-bit loads and stores, no division per element
 __global__ void __launch_bounds__(256)
 reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long long MN4, const int M4, float4 * __restrict__ out, const long long out_cs4,
-                      const int add_to_out) {
+                      const int add_to_out, const float4 * __restrict__ res_src, float4 * __restrict__ res_dst /* fused residual ADD: [N][M] contiguous, or null */) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < MN4; i += (long long) gridDim.x * blockDim.x) {
@@ -674,10 +674,19 @@ reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long lo
             v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
         }
         *o = v;
+        if (res_dst) {                                  // the GGML_OP_ADD node that consumes this MUL_MAT (same IEEE add as add_f32_*)
+            const float4 r = res_src[i];
+            res_dst[i] = make_float4(r.x + v.x, r.y + v.y, r.z + v.z, r.w + v.w);
+        }
     }
 }
 
-cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st) {
+bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst) {
+    return M % 4 == 0 && out_cs % 4 == 0 && (((uintptr_t) out | (uintptr_t) res_src | (uintptr_t) res_dst) & 15) == 0;
+}
+cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st,
+                                 const float * res_src, float * res_dst) {
+    if (res_dst && !reduce_splits_can_fuse_residual(M, out_cs, out, res_src, res_dst)) return cudaErrorInvalidValue;
     if (M % 4 == 0 && out_cs % 4 == 0 && (((uintptr_t) ws | (uintptr_t) out) & 15) == 0) {
         const long long MN4 = MN / 4;
         long long blocks = (MN4 + 255) / 256;
@@ -688,7 +697,8 @@ cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, f
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
-        return cudaLaunchKernelEx(&cfg, reduce_splits4_kernel, (const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out);
+        return cudaLaunchKernelEx(&cfg, reduce_splits4_kernel, (const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out,
+                                  (const float4 *) res_src, (float4 *) res_dst);
     }
     reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(ws, S, MN, M, out, out_cs, add_to_out);
     return cudaGetLastError();

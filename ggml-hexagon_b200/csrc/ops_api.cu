@@ -534,8 +534,9 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
     const int gemm_min_n = gemm_min_cols(s0->type);
     const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
-                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && !fa && ((uintptr_t) wp0.p[0] & 15) == 0 &&
+                          M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && (!fa || N > 1) && ((uintptr_t) wp0.p[0] & 15) == 0 &&
                           (!c->rs_on || (gemm_dense_enabled() && rs_flag_exchange_separate()));   // row split: dense path + slice push
+    if (fa && N > 1 && !(use_gemm && gemm_dense_enabled())) return fail(B200_EINVAL, "fused residual ADD needs the dense GEMM path");
     if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
@@ -561,7 +562,9 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             }
             const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
             if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
-            CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st));
+            if (fa && ksp <= 1) return fail(B200_EINVAL, "fused residual ADD on a dense MUL_MAT without split-K");      // (can_fuse_add_dense checks)
+            CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st,
+                                 fa ? fa->src : nullptr, fa ? fa->dst : nullptr));
             c->launches += 1 + (ksp > 1 ? 1 : 0);
             if (c->rs_on && c->world > 1) {
                 // row split: y is this rank's M rows of every dst column; the slice goes into every peer's copy over NVLink, and the
@@ -740,6 +743,24 @@ static bool is_dense_mulmat(Ctx * c, const b200_node & n) {
     const int64_t K = s0.ne[0], M = s0.ne[1], N = s1.ne[1];
     const int mn = gemm_min_cols(s0.type);
     return mn > 0 && N >= mn && K % 32 == 0 && M > 0 && M < 0x7fffffff && N < 0x7fffffff && K < 0x3fffffff;
+}
+// many-column MUL_MAT on the dense GEMM with split-K, followed by the ADD that consumes its dst (wo / down + residual in prefill): the
+// split-K reduce writes both results, the ADD launch disappears
+static bool can_fuse_add_dense(Ctx * c, const b200_node & mm, const b200_node & ad, FusedAdd * fa) {
+    if (!gemm_dense_enabled() || !gemm_dense_pair() || !is_dense_mulmat(c, mm) || ad.dst.op != B200_OP_ADD) return false;
+    const int64_t K = mm.src0.ne[0], M = mm.src0.ne[1], N = mm.src1.ne[1];
+    if (gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms) <= 1) return false;
+    auto plain = [&](const b200_tensor & t) { return t.type == T_F32 && t.ne[0] == M && t.ne[1] == N && t.ne[2] == 1 && t.ne[3] == 1 && t.nb[0] == 4 && t.nb[1] == M * 4; };
+    if (!plain(ad.src0) || !plain(ad.src1) || !plain(ad.dst) || !plain(mm.dst)) return false;
+    const void * other;
+    if (ad.src0.data == mm.dst.data) other = ad.src1.data; else if (ad.src1.data == mm.dst.data) other = ad.src0.data; else return false;
+    const int64_t bytes = M * N * 4, xspan = (N - 1) * mm.src1.nb[1] + K * 4;
+    if (overlap(ad.dst.data, bytes, mm.src1.data, xspan) || overlap(ad.dst.data, bytes, mm.dst.data, bytes)) return false;
+    if (other != ad.dst.data && overlap(ad.dst.data, bytes, other, bytes)) return false;      // in place on the residual is fine (element-wise)
+    if (overlap(mm.dst.data, bytes, other, bytes) || overlap(mm.dst.data, bytes, mm.src1.data, xspan)) return false;
+    if (!reduce_splits_can_fuse_residual(M, M, mm.dst.data, other, ad.dst.data)) return false;
+    fa->src = (const float *) other; fa->dst = (float *) ad.dst.data;
+    return true;
 }
 static int dense_group_len(Ctx * c, const b200_node * nodes, int i, int n) {
     if (!gemm_dense_enabled() || !gemm_dense_pair() || !is_dense_mulmat(c, nodes[i])) return 1;
@@ -1000,6 +1021,7 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                 const int dgl = fuse && gl == 1 ? dense_group_len(c, nodes, i, n) : 1;
                 if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
                 else if (dgl > 1) { rc = mulmat_dense_group_dev(c, nodes + i, dgl); used = dgl; }
+                else if (fuse && i + 1 < n && can_fuse_add_dense(c, nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
                 else if (fuse && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
                 else if (c->rs_on) {
                     const int64_t rows = nodes[i].src0.ne[1];

@@ -257,6 +257,41 @@ def test_dense_full_size_against_exact_mode(monkeypatch, model_shape):
             b.free()
 
 
+@pytest.mark.parametrize("in_place", [False, True])
+@pytest.mark.parametrize("use_graph", [0, 2])
+def test_dense_residual_add_fused_into_the_split_k_reduce(in_place, use_graph):
+    """MUL_MAT (few tiles -> split-K) followed by the ADD that consumes it (wo / down + residual): with the pair kernel the reduce
+    writes both results; both must equal the oracle's MUL_MAT and the IEEE sum bit for bit"""
+    rng = np.random.default_rng(83)
+    M, K, N = 512, 4096, 128
+    with B.Session(0) as sess:
+        raw = O.random_blocks(O.Q4_0, M, K, rng)
+        w = sess.weights(O.Q4_0, raw, K)
+        xs = rng.standard_normal((N, K)).astype(np.float32)
+        res = rng.standard_normal((N, M)).astype(np.float32)
+        xb, rb = sess.to_device(xs), sess.to_device(res)
+        y, z = sess.malloc(4 * M * N), sess.malloc(4 * M * N)
+        zt = rb if in_place else z
+        mm, ad = B.Node(), B.Node()
+        mm.src0, mm.src1, mm.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(y.ptr, [M, N], op=B.OP_MUL_MAT)
+        ad.src0, ad.src1, ad.dst = B.f32_tensor(rb.ptr, [M, N]), B.f32_tensor(y.ptr, [M, N]), B.f32_tensor(zt.ptr, [M, N], op=B.OP_ADD)
+        arr = (B.Node * 2)(mm, ad)
+        sess.graph_compute(arr, use_graph)
+        sess.sync()
+        before = sess.launch_count()
+        if not in_place:
+            sess.graph_compute(arr, use_graph)              # (in place the residual has already moved on)
+            sess.sync()
+            if os.environ.get("B200_GEMM_CTA") == "2":
+                assert sess.launch_count() - before == 3    # conversion, GEMM, reduce (+ ADD fused)
+        got_y, got_z = sess.to_host(y, (N, M), np.float32), sess.to_host(zt, (N, M), np.float32)
+        assert nmse(got_y, O.mul_mat(O.Q4_0, raw, xs, 1)) <= DENSE_BAR
+        assert np.array_equal(got_z, res + got_y)
+        for b in (xb, rb, y, z):
+            b.free()
+        w.free()
+
+
 def test_dense_close_to_exact_mode(sess, monkeypatch):
     """the two prefill kernels on the same inputs: they differ by the fp16 rounding of the operands only"""
     rng = np.random.default_rng(59)
