@@ -178,14 +178,15 @@ cudaError_t launch_quantize_rows_f16(const float * x, long long row_stride_bytes
 cudaError_t launch_unpack_f16(int type, const WPtrs & w, long long nblocks, __half * out, float * wS, float * wM, cudaStream_t st);
 // res_dst != null: also res_dst[i] = res_src[i] + out[i] over [N][M] contiguous (the residual ADD node behind the MUL_MAT, fused)
 cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st,
-                                 const float * res_src = nullptr, float * res_dst = nullptr);
+                                 const float * res_src = nullptr, float * res_dst = nullptr, void * act_out = nullptr);
 bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst);
 // ---- dense prefill GEMM (gemm_dense.cu): block scales folded into fp16 operands, the whole K accumulated in TMEM
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st);
 cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st);
 int gemm_dense_ksplit(int M, int N, int K, int sms);            // > 1: launch_gemm_dense wants a workspace of that many x N x M floats
 cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
-                              const float * res_src = nullptr, float * res_dst = nullptr);   // residual ADD fused into the split-K reduce (needs split_ws and ksplit > 1)
+                              const float * res_src = nullptr, float * res_dst = nullptr,   // residual ADD fused into the split-K reduce (needs split_ws and ksplit > 1)
+                              void * act_out = nullptr);   // + fp16(q8_1(res_dst)) [N][M] for the next dense GEMM (M % 32 == 0)
 bool gemm_dense_pair();                                         // the CTA-pair kernel is selected (default; B200_GEMM_CTA=1: one CTA per tile)
 // 2..3 weight matrices over the same activations in one launch (q / k / v, gate / up); cudaErrorNotSupported without the pair kernel
 cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,

@@ -654,7 +654,7 @@ static cudaError_t launch_pair(const __half * const * A, float * const * out, co
 // A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
 // split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
 cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
-                              const float * res_src, float * res_dst) {
+                              const float * res_src, float * res_dst, void * act_out) {
     const int ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
     if (res_dst && ksplit == 1) return cudaErrorInvalidValue;
     cudaError_t e;
@@ -674,7 +674,7 @@ cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, l
         e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
     }
     if (e != cudaSuccess || ksplit == 1) return e;
-    return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst);
+    return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst, act_out);
 }
 
 // Several weight matrices over the same activations in ONE launch of the pair kernel (no split-K): 2 <= nmat <= 3.

@@ -662,10 +662,15 @@ reduce_splits_kernel(const float * __restrict__ ws, const int S, const long long
 // four consecutive m per thread (M, out_cs multiples of 4, 16-byte aligned buffers): 128-bit loads and stores, no division per element
 __global__ void __launch_bounds__(256)
 reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long long MN4, const int M4, float4 * __restrict__ out, const long long out_cs4,
-                      const int add_to_out, const float4 * __restrict__ res_src, float4 * __restrict__ res_dst /* fused residual ADD: [N][M] contiguous, or null */) {
+                      const int add_to_out, const float4 * __restrict__ res_src, float4 * __restrict__ res_dst /* fused residual ADD: [N][M] contiguous, or null */,
+                      uint2 * __restrict__ act_out /* with res_dst, M % 32 == 0: fp16(q8_1(res_dst)) for the next dense GEMM, or null */) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < MN4; i += (long long) gridDim.x * blockDim.x) {
+    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; ; i += (long long) gridDim.x * blockDim.x) {
+        const bool active = i < MN4;
+        const unsigned mask = __ballot_sync(0xffffffffu, active);       // (whole groups of 8 lanes = one 32-element block: MN4 % 8 == 0 with act_out)
+        if (mask == 0) break;
+        if (!active) continue;
         const long long n = i / M4; const int m = (int) (i - n * M4);
         float4 * o = out + n * out_cs4 + m;
         float4 v = add_to_out ? *o : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -676,7 +681,25 @@ reduce_splits4_kernel(const float4 * __restrict__ ws, const int S, const long lo
         *o = v;
         if (res_dst) {                                  // the GGML_OP_ADD node that consumes this MUL_MAT (same IEEE add as add_f32_*)
             const float4 r = res_src[i];
-            res_dst[i] = make_float4(r.x + v.x, r.y + v.y, r.z + v.z, r.w + v.w);
+            const float4 z = make_float4(r.x + v.x, r.y + v.y, r.z + v.z, r.w + v.w);
+            res_dst[i] = z;
+            if (act_out) {
+                // the sum is the next MUL_MAT's src1 (its K runs along m): convert it here as dequant_act_f16_kernel would
+                // (quantize_row_q8_1_ref ggml-quants.c:220-253, then d * q rounded to fp16), 8 lanes per 32-element block
+                float amax = fmaxf(fmaxf(fabsf(z.x), fabsf(z.y)), fmaxf(fabsf(z.z), fabsf(z.w)));
+                amax = fmaxf(amax, __shfl_xor_sync(mask, amax, 1));
+                amax = fmaxf(amax, __shfl_xor_sync(mask, amax, 2));
+                amax = fmaxf(amax, __shfl_xor_sync(mask, amax, 4));
+                const float d  = __fdiv_rn(amax, 127.0f);
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                const float dh = __half2float(__float2half_rn(d));
+                const float r0 = dh * roundf(__fmul_rn(z.x, id)), r1 = dh * roundf(__fmul_rn(z.y, id));
+                const float r2 = dh * roundf(__fmul_rn(z.z, id)), r3 = dh * roundf(__fmul_rn(z.w, id));
+                uint2 h;
+                asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.x) : "f"(r1), "f"(r0));
+                asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.y) : "f"(r3), "f"(r2));
+                act_out[i] = h;
+            }
         }
     }
 }
@@ -685,8 +708,9 @@ bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void *
     return M % 4 == 0 && out_cs % 4 == 0 && (((uintptr_t) out | (uintptr_t) res_src | (uintptr_t) res_dst) & 15) == 0;
 }
 cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st,
-                                 const float * res_src, float * res_dst) {
+                                 const float * res_src, float * res_dst, void * act_out) {
     if (res_dst && !reduce_splits_can_fuse_residual(M, out_cs, out, res_src, res_dst)) return cudaErrorInvalidValue;
+    if (act_out && (!res_dst || M % 32 != 0 || ((uintptr_t) act_out & 7) != 0)) return cudaErrorInvalidValue;
     if (M % 4 == 0 && out_cs % 4 == 0 && (((uintptr_t) ws | (uintptr_t) out) & 15) == 0) {
         const long long MN4 = MN / 4;
         long long blocks = (MN4 + 255) / 256;
@@ -698,7 +722,7 @@ cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, f
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
         return cudaLaunchKernelEx(&cfg, reduce_splits4_kernel, (const float4 *) ws, S, MN4, M / 4, (float4 *) out, out_cs / 4, add_to_out,
-                                  (const float4 *) res_src, (float4 *) res_dst);
+                                  (const float4 *) res_src, (float4 *) res_dst, (uint2 *) act_out);
     }
     reduce_splits_kernel<<<(unsigned) ((MN + 255) / 256), 256, 0, st>>>(ws, S, MN, M, out, out_cs, add_to_out);
     return cudaGetLastError();

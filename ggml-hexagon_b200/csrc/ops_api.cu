@@ -450,6 +450,7 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
     a.rs_signal = sep ? 0 : 1; a.rs_ctrl = (uint32_t *) (c->rs_heap + 260);
     return 0;
 }
+static bool act_fusion_enabled() { static const bool on = !(getenv("B200_GEMM_ACTFUSE") && atoi(getenv("B200_GEMM_ACTFUSE")) == 0); return on; }
 static bool rs_flag_exchange_separate() { return !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0); }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
@@ -563,9 +564,14 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
             if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
             if (fa && ksp <= 1) return fail(B200_EINVAL, "fused residual ADD on a dense MUL_MAT without split-K");      // (can_fuse_add_dense checks)
+            // the fused ADD's result is usually the next MUL_MAT's src1 (K = M): the reduce converts it into gm_qb on the way (the GEMM of this
+            // op has read gm_qb by then), and the next op finds its activations converted.  Only where gm_qb already has the room (no
+            // reallocation under a capture) and inside a node list.
+            const bool next_act = fa && c->in_graph && M % 32 == 0 && c->gm_qb_cap >= (size_t) N * M * 2 && act_fusion_enabled();
             CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st,
-                                 fa ? fa->src : nullptr, fa ? fa->dst : nullptr));
+                                 fa ? fa->src : nullptr, fa ? fa->dst : nullptr, next_act ? c->gm_qb : nullptr));
             c->launches += 1 + (ksp > 1 ? 1 : 0);
+            if (next_act) { c->q_ptr = fa->dst; c->q_K = M; c->q_N = N; c->q_stride = M * 4; c->q_kind = 1; }
             if (c->rs_on && c->world > 1) {
                 // row split: y is this rank's M rows of every dst column; the slice goes into every peer's copy over NVLink, and the
                 // flag exchange at the end of the op (rs_exchange below) publishes it

@@ -272,10 +272,16 @@ def test_dense_residual_add_fused_into_the_split_k_reduce(in_place, use_graph):
         xb, rb = sess.to_device(xs), sess.to_device(res)
         y, z = sess.malloc(4 * M * N), sess.malloc(4 * M * N)
         zt = rb if in_place else z
-        mm, ad = B.Node(), B.Node()
+        # a second MUL_MAT consumes the sum (K2 = M): its activations were converted by the reduce of the first
+        M2 = 384
+        raw2 = O.random_blocks(O.Q6_K, M2, M, rng)
+        w2 = sess.weights(O.Q6_K, raw2, M)
+        o2 = sess.malloc(4 * M2 * N)
+        mm, ad, m2 = B.Node(), B.Node(), B.Node()
         mm.src0, mm.src1, mm.dst = w.tensor(), B.f32_tensor(xb.ptr, [K, N]), B.f32_tensor(y.ptr, [M, N], op=B.OP_MUL_MAT)
         ad.src0, ad.src1, ad.dst = B.f32_tensor(rb.ptr, [M, N]), B.f32_tensor(y.ptr, [M, N]), B.f32_tensor(zt.ptr, [M, N], op=B.OP_ADD)
-        arr = (B.Node * 2)(mm, ad)
+        m2.src0, m2.src1, m2.dst = w2.tensor(), B.f32_tensor(zt.ptr, [M, N]), B.f32_tensor(o2.ptr, [M2, N], op=B.OP_MUL_MAT)
+        arr = (B.Node * 3)(mm, ad, m2)
         sess.graph_compute(arr, use_graph)
         sess.sync()
         before = sess.launch_count()
@@ -283,13 +289,16 @@ def test_dense_residual_add_fused_into_the_split_k_reduce(in_place, use_graph):
             sess.graph_compute(arr, use_graph)              # (in place the residual has already moved on)
             sess.sync()
             if os.environ.get("B200_GEMM_CTA") == "2":
-                assert sess.launch_count() - before == 3    # conversion, GEMM, reduce (+ ADD fused)
+                # conversion, GEMM, reduce (+ ADD + the second MUL_MAT's conversion), GEMM (8 k-stages: no split)
+                assert sess.launch_count() - before == 4
         got_y, got_z = sess.to_host(y, (N, M), np.float32), sess.to_host(zt, (N, M), np.float32)
+        got_o = sess.to_host(o2, (N, M2), np.float32)
         assert nmse(got_y, O.mul_mat(O.Q4_0, raw, xs, 1)) <= DENSE_BAR
         assert np.array_equal(got_z, res + got_y)
-        for b in (xb, rb, y, z):
+        assert nmse(got_o, O.mul_mat(O.Q6_K, raw2, got_z, 1)) <= DENSE_BAR
+        for b in (xb, rb, y, z, o2):
             b.free()
-        w.free()
+        w.free(); w2.free()
 
 
 def test_dense_close_to_exact_mode(sess, monkeypatch):
