@@ -26,7 +26,7 @@ SYMBOLS = [
     "b200_block_bytes", "b200_event_create", "b200_event_record", "b200_event_elapsed_ms", "b200_event_destroy",
     "b200_launch_count", "b200_flush_l2", "b200_rowsplit_unique_id", "b200_rowsplit_init", "b200_rowsplit_finalize",
     "b200_mulmat_rowsplit", "b200_rowsplit_heap_create", "b200_rowsplit_heap_attach", "b200_rowsplit_heap_attach_ptrs",
-    "b200_rowsplit_heap_destroy", "b200_graph_compute_rowsplit",
+    "b200_rowsplit_heap_destroy", "b200_graph_compute_rowsplit", "b200_debug_trace_begin", "b200_debug_trace_read",
 ]
 
 
@@ -97,6 +97,8 @@ def lib():
         L.b200_rowsplit_heap_attach_ptrs.argtypes = [H, C.POINTER(VP), C.POINTER(I32), I32, I32]
         L.b200_rowsplit_heap_destroy.argtypes = [H]
         L.b200_graph_compute_rowsplit.argtypes = [H, C.POINTER(Node), I32, I32]
+        L.b200_debug_trace_begin.argtypes = [H, I32]
+        L.b200_debug_trace_read.argtypes = [H, VP, I32]
         _lib = L
     return _lib
 

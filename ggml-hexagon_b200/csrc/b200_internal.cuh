@@ -116,6 +116,11 @@ cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStre
 // all ncols (2 .. 31) columns of a.act in ONE launch over shared-memory tiles (gemv5n); false: not eligible, *err untouched
 bool launch_gemv_cols(int type, GemvArgs & a, int ncols, cudaStream_t st, cudaError_t * err);
 bool gemv_pdl_enabled();
+// gemv6.cu: ONE f32 activation column a.x, quantised inside the kernel; persistent CTAs (one per SM), per-warp cp.async.bulk rings.
+// false: not eligible (*err untouched) -- the caller quantises into a.act and runs gemv4 / gemv5
+bool launch_gemv6(int type, GemvArgs & a, int sms, cudaStream_t st, cudaError_t * err);
+void gemv6_trace(long long * buf, int cap_launches);      // development: 4 x %globaltimer per CTA of the next launches (4096 values per launch)
+int  gemv6_trace_count();
 bool gemv_fuseq_enabled();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)
 cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, int64_t K,

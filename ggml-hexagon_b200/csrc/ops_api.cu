@@ -648,16 +648,22 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 a.x = (const float *) x; a.x_col_stride = s1->nb[1];
                 CU(launch_gemv2(s0->type, a, (int) N, true, c->st)); c->launches++;
             } else {
-                const bool reuse = c->in_graph && c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
-                if (!reuse) {
-                    CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
-                    c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 0;
-                }
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
                 { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; const int64_t rw[1] = {M};
                   rc = rs_fill(c, a, dp, db_, 1, rw, N == 1 && s1->ne[2] == 1 && s1->ne[3] == 1); if (rc) return rc; }
                 const int rs_signal = a.rs_signal;
                 bool done = false;
+                if (N == 1) {                               // one column: persistent ring GEMV, quantises the activations itself (gemv6.cu)
+                    a.mat[0].dst = y; a.x = (const float *) x; a.x_col_stride = s1->nb[1];
+                    cudaError_t e6 = cudaSuccess;
+                    done = launch_gemv6(s0->type, a, c->sms, c->st, &e6);
+                    if (done) { CU(e6); c->launches++; continue; }
+                }
+                const bool reuse = c->in_graph && c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
+                if (!reuse) {
+                    CU(launch_quantize_q8_1_soa((const float *) x, s1->nb[1], K, N, c->act_qs, c->act_ds, c->st)); c->launches++;
+                    c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 0;
+                }
                 if (N > 1 && N < 0x7fff) {                  // small batch: one launch over shared-memory tiles, weights read once
                     a.act = ActView{c->act_qs, c->act_ds, NB};
                     a.mat[0].dst = y;
@@ -836,6 +842,16 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
         a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
         CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
         return 0;
+    }
+    {   // persistent ring GEMV over the whole group, activations quantised inside the kernel (gemv6.cu)
+        a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
+        cudaError_t e6 = cudaSuccess;
+        if (launch_gemv6(nodes[0].src0.type, a, c->sms, c->st, &e6)) {
+            CU(e6); c->launches++;
+            for (int j = 0; j < len; j++)            // a dst may overwrite the memory an earlier cached quantisation was taken from
+                if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4 * g_rs_world, c->q_ptr, c->q_K * 4)) c->q_ptr = nullptr;
+            return rs_exchange(c);
+        }
     }
     int rc = ensure_act(c, NB); if (rc) return rc;
     const bool reuse = c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == 1;
@@ -1163,6 +1179,29 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     CU(cudaGraphLaunch(it->second.exec, c->st));
     c->launches += it->second.n_kernels;      // a replay runs exactly the kernels captured
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ development: gemv6 timeline
+// 4 x %globaltimer per CTA (start, dependency resolved, activations quantised, done) for the next max_launches gemv6 launches
+static long long * g_trace_buf = nullptr; static int g_trace_cap = 0;
+extern "C" int b200_debug_trace_begin(b200_handle h, int32_t max_launches) {
+    CTX(h);
+    if (g_trace_buf) { cudaFree(g_trace_buf); g_trace_buf = nullptr; }
+    if (max_launches <= 0) { gemv6_trace(nullptr, 0); return 0; }
+    const size_t bytes = (size_t) max_launches * 4096 * sizeof(long long);
+    CU(cudaMalloc((void **) &g_trace_buf, bytes));
+    CU(cudaMemsetAsync(g_trace_buf, 0, bytes, c->st));
+    g_trace_cap = max_launches;
+    gemv6_trace(g_trace_buf, max_launches);
+    return 0;
+}
+extern "C" int b200_debug_trace_read(b200_handle h, int64_t * out, int32_t max_launches) {
+    CTX(h);
+    CU(cudaStreamSynchronize(c->st));
+    int n = gemv6_trace_count(); if (n > max_launches) n = max_launches;
+    if (n > 0) CU(cudaMemcpy(out, g_trace_buf, (size_t) n * 4096 * sizeof(long long), cudaMemcpyDeviceToHost));
+    gemv6_trace(nullptr, 0);
+    return n;
 }
 
 // ------------------------------------------------------------------------------------------------ events

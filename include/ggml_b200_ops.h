@@ -158,6 +158,12 @@ B200_API int64_t b200_launch_count(b200_handle h);
 /* overwrite a >L2-sized scratch buffer so the next kernel starts from a cold L2 */
 B200_API int b200_flush_l2(b200_handle h);
 
+/* ---- development instrumentation: %globaltimer stamps of the decode GEMV's CTAs (tools/g6_trace.py).  begin(n): record the next n
+ *      launches (captured CUDA graphs keep recording into the same buffer on every replay); read: 4096 int64 per launch
+ *      = 4 stamps {start, dependency resolved, activations quantised, done} per CTA; returns the number of launches recorded */
+B200_API int b200_debug_trace_begin(b200_handle h, int32_t max_launches);
+B200_API int b200_debug_trace_read(b200_handle h, int64_t * out, int32_t max_launches);
+
 /* ---- row-split MUL_MAT across the GPUs of one box: one process per GPU, NCCL over NVLink
  *      (takes the seat of ggml-cuda's split buffers, ggml-cuda.cu:727-753,1365-1673) */
 B200_API int b200_rowsplit_unique_id(void * id128);                       /* 128 bytes, rank 0 creates, all ranks get */
