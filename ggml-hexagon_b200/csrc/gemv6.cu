@@ -49,7 +49,7 @@ __device__ __forceinline__ uint32_t g6_smem(const void * p) { return (uint32_t) 
 __device__ __forceinline__ long long g6_now() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 
 template <int TYPE, int NJ, int RU, bool TEAM>
-__global__ void __maxnreg__(TEAM ? 96 : 80)
+__global__ void __maxnreg__(TEAM ? (NJ >= 6 ? 112 : 96) : 80)
 b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
     using W = WT<TYPE>;
     using A = WR<TYPE>;
@@ -167,7 +167,14 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         locate(u0 + team + i * nteams, m, row0, nrows);
         {   // the slot has landed
             uint32_t ok = 0; const uint32_t bar = bar0 + slot * 8;
-            while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(phase) : "memory");
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(phase) : "memory");
+            if (!ok) {                                 // bounded: a copy that never lands traps instead of hanging the GPU
+                const long long t0 = clock64();
+                while (!ok) {
+                    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(phase) : "memory");
+                    if (!ok && clock64() - t0 > 4000000000ll) __trap();
+                }
+            }
         }
         WPtrs sw;
         #pragma unroll
@@ -305,8 +312,8 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     g.slot_bytes = (off + 15) & ~15;
     // warps and ring depth from the shared-memory budget (two kernels of this kind are meant to fit one SM together)
     const int act_bytes = (int) (a.K / 32 * 40);
-    // registers: 80 per thread (teams 96): 12 (10) warps keep the kernel under half of the SM's register file
-    int nw = tn.warps > 0 ? tn.warps : (ks > 1 ? 10 : 12);
+    // registers: 80 per thread (teams 96, 112 with 6 steps per lane): 12 (10, 8) warps keep the kernel under half of the SM's register file
+    int nw = tn.warps > 0 ? tn.warps : (ks > 1 ? (nj >= 6 ? 8 : 10) : 12);
     nw = nw / ks * ks; if (nw < ks) nw = ks;
     if (nw > 16) nw = 16 / ks * ks;
     if (ks > 1 && nw / ks > 15) nw = 15 * ks;                                             // named barriers 1 .. 15
