@@ -23,7 +23,7 @@ SYMBOLS = [
     "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d", "b200_memset",
     "b200_memcpy_h2d_async", "b200_memcpy_d2h_async",
     "b200_host_alloc", "b200_host_free", "b200_weights_upload", "b200_weights_download", "b200_block_elems",
-    "b200_block_bytes", "b200_event_create", "b200_event_record", "b200_event_elapsed_ms", "b200_event_destroy",
+    "b200_block_bytes", "b200_event_create", "b200_event_record", "b200_event_elapsed_ms", "b200_event_destroy", "b200_event_wait", "b200_event_synchronize",
     "b200_launch_count", "b200_flush_l2", "b200_rowsplit_unique_id", "b200_rowsplit_init", "b200_rowsplit_finalize",
     "b200_mulmat_rowsplit", "b200_rowsplit_heap_create", "b200_rowsplit_heap_attach", "b200_rowsplit_heap_attach_ptrs",
     "b200_rowsplit_heap_destroy", "b200_graph_compute_rowsplit", "b200_debug_trace_begin", "b200_debug_trace_read",
@@ -88,6 +88,8 @@ def lib():
         L.b200_event_record.argtypes = [H, VP]
         L.b200_event_elapsed_ms.argtypes = [H, VP, VP, C.POINTER(C.c_float)]
         L.b200_event_destroy.argtypes = [H, VP]
+        L.b200_event_wait.argtypes = [H, VP]
+        L.b200_event_synchronize.argtypes = [H, VP]
         L.b200_flush_l2.argtypes = [H]
         L.b200_rowsplit_unique_id.argtypes = [VP]
         L.b200_rowsplit_init.argtypes = [H, VP, I32, I32]

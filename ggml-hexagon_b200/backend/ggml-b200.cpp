@@ -21,20 +21,25 @@
 #include <string>
 #include <vector>
 
-#define B200_LOG(...) do { if (getenv("GGML_B200_VERBOSE")) { fprintf(stderr, "[ggml-b200] " __VA_ARGS__); fputc('\n', stderr); } } while (0)
+// everything goes through ggml's logger (GGML_LOG_*, ggml-impl.h), so a host's ggml_log_set callback sees the backend
+#define B200_LOG(...)  do { if (getenv("GGML_B200_VERBOSE")) { GGML_LOG_INFO("[ggml-b200] " __VA_ARGS__); GGML_LOG_INFO("\n"); } } while (0)
+#define B200_ERR(...)  do { GGML_LOG_ERROR("[ggml-b200] " __VA_ARGS__); GGML_LOG_ERROR("\n"); } while (0)
 
 // ------------------------------------------------------------------------------------------------ contexts
+// ONE op-layer session (= one CUDA stream, one scratch set, one CUDA-graph cache) per device, shared by the device's buffers and
+// by every backend instance on it: buffer copies, uploads and graph_compute are ordered on that stream, and anything the op layer
+// caches per weight address (graphs, scratch) is invalidated by the same session that rewrites the weights.  `mu` serialises the
+// entry points (callers are single-threaded per backend, but buffers of one device may be touched from several threads).
 struct b200_device_ctx {
     int         ordinal = 0;
     std::string name;            // "B200_<ordinal>"   (ggml_backend_hexagon_get_devname)
     std::string desc;            // CUDA device name
-    b200_handle mem = 0;         // session used by the buffers of this device (set/get/memset/clear)
+    b200_handle h = 0;
     std::mutex  mu;
     ggml_backend_buffer_type buft;
 };
 struct b200_backend_ctx {
     b200_device_ctx * dev = nullptr;
-    b200_handle       h   = 0;   // own stream, scratch and CUDA-graph cache
     std::string       name;
     std::vector<b200_node> nodes;
 };
@@ -44,14 +49,14 @@ struct b200_buffer_ctx {
     size_t            size = 0;
 };
 
-static b200_handle dev_session(b200_device_ctx * d) {
-    std::lock_guard<std::mutex> lk(d->mu);
-    if (!d->mem) {
+static b200_handle dev_session(b200_device_ctx * d) {          // call with d->mu held
+    if (!d->h) {
         char uri[32]; snprintf(uri, sizeof(uri), "cuda:%d", d->ordinal);
-        if (b200_open(uri, &d->mem) != 0) { fprintf(stderr, "[ggml-b200] %s\n", b200_last_error()); d->mem = 0; }
+        if (b200_open(uri, &d->h) != 0) { B200_ERR("%s", b200_last_error()); d->h = 0; }
     }
-    return d->mem;
+    return d->h;
 }
+#define DEV_LOCK(d) std::lock_guard<std::mutex> lk_((d)->mu)
 
 static bool is_qweight(enum ggml_type t) {
     return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K;
@@ -97,6 +102,7 @@ static bool b200_supports_mul_mat(const ggml_tensor * op) {
         if (a->nb[0] != bb || a->nb[1] != ggml_row_size(a->type, a->ne[0])) return false;      // contiguous rows
         if (a->nb[2] % bb || a->nb[3] % bb) return false;
         if ((b->nb[1] | b->nb[2] | b->nb[3]) & 15) return false;                                // 128-bit activation loads
+        if (b->data && ((uintptr_t) b->data & 15)) return false;                                // (views at odd offsets, once allocated)
         const ggml_tensor * r = root_of(a);
         if (a->data && r->data && (((const char *) a->data - (const char *) r->data) % (ptrdiff_t) bb)) return false;
     } else {
@@ -126,7 +132,7 @@ static bool b200_device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) 
 // callers reach the data only through set/get, which lets quantised tensors be kept in the SoA layout.
 static void b200_buffer_free(ggml_backend_buffer_t buffer) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
-    if (c->base) b200_free(dev_session(c->dev), c->base);
+    if (c->base) { DEV_LOCK(c->dev); b200_free(dev_session(c->dev), c->base); }
     delete c;
 }
 static void * b200_buffer_get_base(ggml_backend_buffer_t buffer) { return ((b200_buffer_ctx *) buffer->context)->base; }
@@ -140,6 +146,7 @@ static void qrange(const ggml_tensor * t, size_t offset, size_t size, void ** ba
 }
 static void b200_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, const void * data, size_t offset, size_t size) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    DEV_LOCK(c->dev);
     b200_handle h = dev_session(c->dev);
     int rc;
     if (is_qweight(t->type)) {
@@ -152,6 +159,7 @@ static void b200_buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t
 }
 static void b200_buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor * t, void * data, size_t offset, size_t size) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    DEV_LOCK(c->dev);
     b200_handle h = dev_session(c->dev);
     int rc;
     if (is_qweight(t->type)) {
@@ -164,6 +172,7 @@ static void b200_buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tens
 }
 static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor * t, uint8_t value, size_t offset, size_t size) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    DEV_LOCK(c->dev);
     b200_handle h = dev_session(c->dev);
     // a constant byte pattern is the same in the native and in the SoA layout only over whole tensors; partial
     // fills of a quantised tensor are not a thing callers do (ggml-backend.cpp uses memset for f32/kv zeroing)
@@ -172,6 +181,7 @@ static void b200_buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor 
 }
 static void b200_buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) buffer->context;
+    DEV_LOCK(c->dev);
     b200_handle h = dev_session(c->dev);
     if (b200_memset(h, c->base, value, c->size) || b200_synchronize(h)) GGML_ABORT("b200 clear: %s", b200_last_error());
 }
@@ -192,6 +202,7 @@ static const ggml_backend_buffer_i b200_buffer_iface = {
 static const char * b200_buft_name(ggml_backend_buffer_type_t buft) { return ((b200_device_ctx *) buft->context)->name.c_str(); }
 static ggml_backend_buffer_t b200_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
     b200_device_ctx * d = (b200_device_ctx *) buft->context;
+    DEV_LOCK(d);
     b200_handle h = dev_session(d);
     if (!h) return nullptr;
     void * p = nullptr;
@@ -226,16 +237,27 @@ static ggml_guid_t b200_guid(void) {
 static const char * b200_backend_name(ggml_backend_t backend) { return ((b200_backend_ctx *) backend->context)->name.c_str(); }
 static void b200_backend_free(ggml_backend_t backend) {
     b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
-    if (c->h) b200_close(c->h);
+    {   // the session belongs to the device (its buffers outlive backends); only drain it
+        DEV_LOCK(c->dev);
+        if (c->dev->h) b200_synchronize(c->dev->h);
+    }
     delete c;
     delete backend;
 }
 static void b200_backend_synchronize(ggml_backend_t backend) {
     b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
-    if (b200_synchronize(c->h)) GGML_ABORT("b200 synchronize: %s", b200_last_error());
+    DEV_LOCK(c->dev);
+    if (b200_synchronize(dev_session(c->dev))) GGML_ABORT("b200 synchronize: %s", b200_last_error());
 }
 static bool is_view_op(enum ggml_op op) {
     return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE;
+}
+static int b200_op_of(const ggml_tensor * node) {
+    switch (node->op) {
+        case GGML_OP_ADD:      return B200_OP_ADD;
+        case GGML_OP_MUL_MAT:  return B200_OP_MUL_MAT;
+        default:               return -1;
+    }
 }
 // node loop of ggmlhexagon_backend_graph_compute_general (ggml-hexagon.cpp:5555-5574): view ops are no-ops, every other
 // node is dst = op(src0, src1).  The whole list goes down in ONE call; asynchronous (ggml_backend_graph_compute adds
@@ -246,17 +268,15 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor * node = cgraph->nodes[i];
         if (is_view_op(node->op) || ggml_is_empty(node)) continue;
-        int op;
-        switch (node->op) {
-            case GGML_OP_ADD:     op = B200_OP_ADD; break;
-            case GGML_OP_MUL_MAT: op = B200_OP_MUL_MAT; break;
-            default:
-                fprintf(stderr, "[ggml-b200] graph_compute: op %s was never admitted by supports_op\n", ggml_op_name(node->op));
-                return GGML_STATUS_FAILED;
+        const int op = b200_op_of(node);
+        if (op < 0) {
+            B200_ERR("graph_compute: op %s was never admitted by supports_op", ggml_op_name(node->op));
+            return GGML_STATUS_FAILED;
         }
         b200_node n;
-        if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || !to_b200(node->src[1], &n.src1, B200_OP_NONE) || !to_b200(node, &n.dst, op)) {
-            fprintf(stderr, "[ggml-b200] graph_compute: node %s has a layout supports_op declines\n", node->name);
+        memset(&n, 0, sizeof(n));
+        if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || (node->src[1] && !to_b200(node->src[1], &n.src1, B200_OP_NONE)) || !to_b200(node, &n.dst, op)) {
+            B200_ERR("graph_compute: node %s has a layout supports_op declines", node->name);
             return GGML_STATUS_FAILED;
         }
         c->nodes.push_back(n);
@@ -264,40 +284,84 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     if (c->nodes.empty()) return GGML_STATUS_SUCCESS;
     // long node lists (a decode step) are captured once as a CUDA graph and replayed; short ones are launched directly
     static const int graph_min = getenv("GGML_B200_GRAPH_MIN") ? atoi(getenv("GGML_B200_GRAPH_MIN")) : 8;
-    const int rc = b200_graph_compute(c->h, c->nodes.data(), (int32_t) c->nodes.size(), (int) c->nodes.size() >= graph_min);
+    DEV_LOCK(c->dev);
+    const int rc = b200_graph_compute(dev_session(c->dev), c->nodes.data(), (int32_t) c->nodes.size(), (int) c->nodes.size() >= graph_min);
     if (rc == B200_ENOMEM) return GGML_STATUS_ALLOC_FAILED;
-    if (rc) { fprintf(stderr, "[ggml-b200] graph_compute: %s\n", b200_last_error()); return GGML_STATUS_FAILED; }
+    if (rc) { B200_ERR("graph_compute: %s", b200_last_error()); return GGML_STATUS_FAILED; }
     return GGML_STATUS_SUCCESS;
 }
 // Stream-ordered tensor copies (the hexagon backend leaves these slots empty, ggml-hexagon.cpp:5836-5850; a GPU backend wants
-// them so that the scheduler's input copies queue behind / in front of graph_compute without a host round trip).
-// Quantised tensors are repacked on the way in and out, which the synchronous buffer path does.
+// them so that the scheduler's input copies queue behind / in front of graph_compute without a host round trip).  The device has
+// ONE stream, so the quantised path (repack kernel, synchronous) is ordered with them too.
 static void b200_backend_set_tensor_async(ggml_backend_t backend, ggml_tensor * t, const void * data, size_t offset, size_t size) {
     b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
     ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
     if (is_qweight(t->type)) { buf->iface.set_tensor(buf, t, data, offset, size); return; }
-    if (b200_memcpy_h2d_async(c->h, (char *) t->data + offset, data, size)) GGML_ABORT("b200 set_tensor_async: %s", b200_last_error());
+    DEV_LOCK(c->dev);
+    if (b200_memcpy_h2d_async(dev_session(c->dev), (char *) t->data + offset, data, size)) GGML_ABORT("b200 set_tensor_async: %s", b200_last_error());
 }
 static void b200_backend_get_tensor_async(ggml_backend_t backend, const ggml_tensor * t, void * data, size_t offset, size_t size) {
     b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
     ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
     if (is_qweight(t->type)) { buf->iface.get_tensor(buf, t, data, offset, size); return; }
-    if (b200_memcpy_d2h_async(c->h, data, (const char *) t->data + offset, size)) GGML_ABORT("b200 get_tensor_async: %s", b200_last_error());
+    DEV_LOCK(c->dev);
+    if (b200_memcpy_d2h_async(dev_session(c->dev), data, (const char *) t->data + offset, size)) GGML_ABORT("b200 get_tensor_async: %s", b200_last_error());
+}
+static const char * b200_buft_name(ggml_backend_buffer_type_t buft);
+// device-to-device copy between two b200 backends (same or different GPU) without a host round trip: the source stream records an
+// event, the destination stream waits for it and copies (ggml_backend_i::cpy_tensor_async, ggml-backend-impl.h:97-98; the
+// scheduler's fallback is synchronize + get + set through host memory, ggml-backend.cpp:1379-1388).  Quantised tensors keep their
+// SoA layout relative to their root tensor, so only whole contiguous non-quantised tensors travel this way; false = declined.
+static bool b200_backend_cpy_tensor_async(ggml_backend_t backend_src, ggml_backend_t backend_dst, const ggml_tensor * src, ggml_tensor * dst) {
+    if (!ggml_backend_is_b200(backend_src) || !ggml_backend_is_b200(backend_dst)) return false;
+    ggml_backend_buffer_t bs = src->view_src ? src->view_src->buffer : src->buffer;
+    ggml_backend_buffer_t bd = dst->view_src ? dst->view_src->buffer : dst->buffer;
+    if (!bs || !bd || bs->buft->iface.get_name != b200_buft_name || bd->buft->iface.get_name != b200_buft_name) return false;
+    if (is_qweight(src->type) || src->type != dst->type || !ggml_is_contiguous(src) || !ggml_is_contiguous(dst) || ggml_nbytes(src) != ggml_nbytes(dst)) return false;
+    b200_device_ctx * ds = ((b200_backend_ctx *) backend_src->context)->dev;
+    b200_device_ctx * dd = ((b200_backend_ctx *) backend_dst->context)->dev;
+    if (ds == dd) {
+        DEV_LOCK(dd);
+        return b200_memcpy_d2d(dev_session(dd), dst->data, src->data, ggml_nbytes(src)) == 0;
+    }
+    void * ev = nullptr;
+    {
+        DEV_LOCK(ds);
+        if (b200_event_create(dev_session(ds), &ev) || b200_event_record(dev_session(ds), ev)) return false;
+    }
+    bool ok;
+    {
+        DEV_LOCK(dd);
+        ok = b200_event_wait(dev_session(dd), ev) == 0 && b200_memcpy_d2d(dev_session(dd), dst->data, src->data, ggml_nbytes(src)) == 0;
+    }
+    { DEV_LOCK(ds); b200_event_destroy(dev_session(ds), ev); }       // (destruction is deferred by CUDA until the event has completed)
+    return ok;
+}
+// events (ggml_backend_i::event_record / event_wait, ggml-backend-impl.h:112-116): CUDA events on the device's stream
+static void b200_backend_event_record(ggml_backend_t backend, ggml_backend_event_t event) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    DEV_LOCK(c->dev);
+    if (b200_event_record(dev_session(c->dev), event->context)) GGML_ABORT("b200 event_record: %s", b200_last_error());
+}
+static void b200_backend_event_wait(ggml_backend_t backend, ggml_backend_event_t event) {
+    b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
+    DEV_LOCK(c->dev);
+    if (b200_event_wait(dev_session(c->dev), event->context)) GGML_ABORT("b200 event_wait: %s", b200_last_error());
 }
 static const ggml_backend_i b200_backend_iface = {
     /* get_name           */ b200_backend_name,
     /* free               */ b200_backend_free,
     /* set_tensor_async   */ b200_backend_set_tensor_async,
     /* get_tensor_async   */ b200_backend_get_tensor_async,
-    /* cpy_tensor_async   */ nullptr,
+    /* cpy_tensor_async   */ b200_backend_cpy_tensor_async,
     /* synchronize        */ b200_backend_synchronize,
     /* graph_plan_create  */ nullptr,
     /* graph_plan_free    */ nullptr,
     /* graph_plan_update  */ nullptr,
     /* graph_plan_compute */ nullptr,
     /* graph_compute      */ b200_backend_graph_compute,
-    /* event_record       */ nullptr,
-    /* event_wait         */ nullptr,
+    /* event_record       */ b200_backend_event_record,
+    /* event_wait         */ b200_backend_event_wait,
 };
 
 // ------------------------------------------------------------------------------------------------ device
@@ -315,19 +379,37 @@ static void b200_device_props(ggml_backend_dev_t dev, ggml_backend_dev_props * p
     props->description = b200_device_desc(dev);
     props->type = b200_device_type(dev);
     b200_device_memory(dev, &props->memory_free, &props->memory_total);
-    props->caps = { /* async */ false, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ false };
+    props->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ true };
 }
 static ggml_backend_t b200_device_init_backend(ggml_backend_dev_t dev, const char *) {
     b200_device_ctx * d = (b200_device_ctx *) dev->context;
+    {
+        DEV_LOCK(d);
+        if (!dev_session(d)) { B200_ERR("init_backend: %s", b200_last_error()); return nullptr; }
+    }
     b200_backend_ctx * c = new b200_backend_ctx();
     c->dev = d; c->name = d->name;
-    char uri[32]; snprintf(uri, sizeof(uri), "cuda:%d", d->ordinal);
-    if (b200_open(uri, &c->h) != 0) {
-        fprintf(stderr, "[ggml-b200] init_backend: %s\n", b200_last_error());
-        delete c;
-        return nullptr;
-    }
     return new ggml_backend{ /* guid */ b200_guid(), /* iface */ b200_backend_iface, /* device */ dev, /* context */ c };
+}
+// events (ggml_backend_device_i::event_new / event_free / event_synchronize, ggml-backend-impl.h:170-178)
+static ggml_backend_event_t b200_device_event_new(ggml_backend_dev_t dev) {
+    b200_device_ctx * d = (b200_device_ctx *) dev->context;
+    DEV_LOCK(d);
+    void * ev = nullptr;
+    if (!dev_session(d) || b200_event_create(d->h, &ev)) { B200_ERR("event_new: %s", b200_last_error()); return nullptr; }
+    return new ggml_backend_event{ /* device */ dev, /* context */ ev };
+}
+static void b200_device_event_free(ggml_backend_dev_t dev, ggml_backend_event_t event) {
+    b200_device_ctx * d = (b200_device_ctx *) dev->context;
+    DEV_LOCK(d);
+    if (d->h) b200_event_destroy(d->h, event->context);
+    delete event;
+}
+static void b200_device_event_synchronize(ggml_backend_dev_t dev, ggml_backend_event_t event) {
+    b200_device_ctx * d = (b200_device_ctx *) dev->context;
+    b200_handle h;
+    { DEV_LOCK(d); h = dev_session(d); }
+    if (b200_event_synchronize(h, event->context)) GGML_ABORT("b200 event_synchronize: %s", b200_last_error());   // (blocks: not under the lock)
 }
 static ggml_backend_buffer_type_t b200_device_buffer_type(ggml_backend_dev_t dev) { return &((b200_device_ctx *) dev->context)->buft; }
 static bool b200_device_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
@@ -350,9 +432,9 @@ static const ggml_backend_device_i b200_device_iface = {
     /* supports_op          */ b200_device_supports_op,
     /* supports_buft        */ b200_device_supports_buft,
     /* offload_op           */ b200_device_offload_op,
-    /* event_new            */ nullptr,
-    /* event_free           */ nullptr,
-    /* event_synchronize    */ nullptr,
+    /* event_new            */ b200_device_event_new,
+    /* event_free           */ b200_device_event_free,
+    /* event_synchronize    */ b200_device_event_synchronize,
 };
 
 // ------------------------------------------------------------------------------------------------ registry

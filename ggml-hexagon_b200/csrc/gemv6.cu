@@ -42,6 +42,8 @@ struct G6Cfg {
     int unit_end[3];      // running unit count over the matrices of the launch
     int total_units;
     int act_off, part_off, bar_off;
+    int pf_piece;         // L2 prefetch of the CTA's own weights at kernel start: bytes per request (0 = off)
+    long long pf_max;     // ... at most this many bytes per (matrix, field)
     long long * trace;    // development: 4 x %globaltimer per CTA
 };
 
@@ -108,6 +110,38 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         }
     };
 
+    // ---- this CTA's whole share of the weights into L2, requested before anything else: the HBM -> L2 stream of a launch then
+    // runs while the kernel before it still computes (programmatic dependent launch), bounded by the memory system and not by
+    // the shared memory this CTA can hold; the ring below only has to cover the L2 -> SM latency
+    if (g.pf_piece > 0) {
+        #pragma unroll
+        for (int mi = 0; mi < 3; mi++) {
+            if (mi < a.nmat) {
+                const int ub = mi == 0 ? 0 : g.unit_end[mi - 1], ue = g.unit_end[mi];
+                const int lo = u0 > ub ? u0 : ub, hi = u1 < ue ? u1 : ue;
+                if (lo < hi) {
+                    const int64_t M = a.mat[mi].M;
+                    const int64_t ra = (int64_t) (lo - ub) * RU;
+                    int64_t rb = (int64_t) (hi - ub) * RU; if (rb > M) rb = M;
+                    #pragma unroll
+                    for (int f = 0; f < 4; f++) {
+                        if (f < g.nfields) {
+                            const int64_t rowb = (int64_t) (steps >> 2) * g.b4[f];
+                            const uint8_t * p = a.mat[mi].w.p[f] + ra * rowb;
+                            int64_t bytes = (rb - ra) * rowb;
+                            if (bytes > g.pf_max) bytes = g.pf_max;
+                            // (UBLKPF takes uniform registers: one lane per warp issues, pieces go round the warps)
+                            if (lane == 0)
+                            for (int64_t o = (int64_t) ((warp + f + 2 * mi) % nwarps) * g.pf_piece; o < bytes; o += (int64_t) nwarps * g.pf_piece) {
+                                const uint32_t n = (uint32_t) (bytes - o < g.pf_piece ? bytes - o : g.pf_piece);
+                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p + o), "r"(n) : "memory");
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
     if (lane == 0) {
         for (int s = 0; s < g.S; s++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar0 + s * 8));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -126,24 +160,37 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         ActDS * ads = (ActDS *) (g6_sm + g.act_off + (size_t) NB * 32);
         const float4 * x4 = (const float4 *) a.x;
         const int K4 = (int) (a.K >> 2);
-        for (int i = tid; i < K4; i += blockDim.x) {          // K % 128 == 0: whole warps enter and leave together
-            const float4 v = __ldcg(x4 + i);
-            const int blk = i >> 3, sub = i & 7;
-            float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-            const float d  = __fdiv_rn(amax, 127.0f);
-            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-            const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
-            const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
-            int sum = q0 + q1 + q2 + q3;
-            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-            const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
-            const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
-            *(uint32_t *) (aq + ((size_t) (sub >> 2) * NB + blk) * 16 + (sub & 3) * 4) = packed;
-            if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; ads[blk] = o; }
+        // all of a thread's loads of a round are in flight together: under load an L2 round trip is ~0.75 us (measured), and the
+        // vector sits on the critical path of the whole decode step
+        constexpr int QB = 6;
+        const int nthr = blockDim.x;
+        for (int base = 0; base < K4; base += nthr * QB) {      // K % 128 == 0: whole warps enter and leave together
+            float4 vv[QB];
+            #pragma unroll
+            for (int q = 0; q < QB; q++) { const int i = base + q * nthr + tid; if (i < K4) vv[q] = __ldcg(x4 + i); }
+            #pragma unroll
+            for (int q = 0; q < QB; q++) {
+                const int i = base + q * nthr + tid;
+                if (i < K4) {
+                    const float4 v = vv[q];
+                    const int blk = i >> 3, sub = i & 7;
+                    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+                    const float d  = __fdiv_rn(amax, 127.0f);
+                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                    const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
+                    const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
+                    int sum = q0 + q1 + q2 + q3;
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                    const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
+                    const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
+                    *(uint32_t *) (aq + ((size_t) (sub >> 2) * NB + blk) * 16 + (sub & 3) * 4) = packed;
+                    if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; ads[blk] = o; }
+                }
+            }
         }
     }
     __syncthreads();
@@ -165,6 +212,14 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
     for (int i = 0; i < nmine; i++) {
         int m, nrows; int64_t row0;
         locate(u0 + team + i * nteams, m, row0, nrows);
+        const bool holder = (lane & ((1 << SH) - 1)) == 0;
+        const int r = lane >> SH;
+        float * add_dst = m == 0 ? a.mat[0].add_dst : m == 1 ? a.mat[1].add_dst : a.mat[2].add_dst;
+        float addv = 0.f;                               // the residual of the fused ADD: requested now, used after the dots
+        if (kseg == 0 && holder && r < nrows && add_dst) {
+            const float * add_src = m == 0 ? a.mat[0].add_src : m == 1 ? a.mat[1].add_src : a.mat[2].add_src;
+            addv = __ldcg(add_src + row0 + r);
+        }
         {   // the slot has landed
             uint32_t ok = 0; const uint32_t bar = bar0 + slot * 8;
             asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(phase) : "memory");
@@ -194,8 +249,6 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         float v = reduce_rows<RU>(acc, lane);       // (uses every loaded value: the slot is free once this returns)
         __syncwarp();
         if (lane == 0 && i + g.S < nmine) issue(i + g.S, slot);
-        const bool holder = (lane & ((1 << SH) - 1)) == 0;
-        const int r = lane >> SH;
         if (TEAM) {
             float * mine = part + ((size_t) (i & 1) * nwarps + warp) * RU;
             if (kseg != 0 && holder) mine[r] = v;
@@ -206,13 +259,9 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         if (kseg == 0 && holder && r < nrows) {
             const int64_t o = row0 + r;
             float * dst = m == 0 ? a.mat[0].dst : m == 1 ? a.mat[1].dst : a.mat[2].dst;
-            float * add_dst = m == 0 ? a.mat[0].add_dst : m == 1 ? a.mat[1].add_dst : a.mat[2].add_dst;
             dst[o] = v;
             float s = 0.f;
-            if (add_dst) {
-                const float * add_src = m == 0 ? a.mat[0].add_src : m == 1 ? a.mat[1].add_src : a.mat[2].add_src;
-                s = __ldcg(add_src + o) + v; add_dst[o] = s;
-            }
+            if (add_dst) { s = addv + v; add_dst[o] = s; }
             if (a.ll_slots) {                         // row split, LL protocol: {value, seq} in one 8-byte NVLink store per peer
                 const int64_t M = m == 0 ? a.mat[0].M : m == 1 ? a.mat[1].M : a.mat[2].M;
                 const int lloff = m == 0 ? a.ll_off[0] : m == 1 ? a.ll_off[1] : a.ll_off[2];
@@ -232,7 +281,7 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
 }
 
 // ------------------------------------------------------------------------------------------------ launch
-struct G6Tune { int warps = 0, ru = 0, smem_kb = 100, cps = 1, maxnj = 0, slots = 0; long long * trace = nullptr; int trace_cap = 0, trace_n = 0; };
+struct G6Tune { int pf_piece = 8192, pf_kb = 1 << 20; int warps = 0, ru = 0, smem_kb = 100, cps = 1, maxnj = 0, slots = 0; long long * trace = nullptr; int trace_cap = 0, trace_n = 0; };
 static G6Tune & g6_tune() {
     static G6Tune t = [] {
         G6Tune x;
@@ -242,6 +291,8 @@ static G6Tune & g6_tune() {
         if (const char * e = getenv("B200_G6_CPS")) x.cps = atoi(e);
         if (const char * e = getenv("B200_G6_MAXNJ")) x.maxnj = atoi(e);
         if (const char * e = getenv("B200_G6_SLOTS")) x.slots = atoi(e);
+        if (const char * e = getenv("B200_G6_PF_PIECE")) x.pf_piece = atoi(e) / 16 * 16;
+        if (const char * e = getenv("B200_G6_PF_KB")) x.pf_kb = atoi(e);
         return x;
     }();
     return t;
@@ -326,6 +377,7 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     int64_t units = 0;
     for (int i = 0; i < a.nmat; i++) { units += (a.mat[i].M + ru - 1) / ru; if (units > 0x7fffffff) return false; g.unit_end[i] = (int) units; }
     g.total_units = (int) units;
+    g.pf_piece = tn.pf_piece; g.pf_max = (long long) tn.pf_kb * 1024;
     int grid = sms * (tn.cps > 0 ? tn.cps : 1);
     if (grid > g.total_units) grid = g.total_units;
     if (grid < 1) return false;

@@ -1210,6 +1210,8 @@ extern "C" int b200_event_record(b200_handle h, void * ev) { CTX(h); CU(cudaEven
 extern "C" int b200_event_elapsed_ms(b200_handle h, void * a, void * b, float * ms) {
     CTX(h); CU(cudaEventSynchronize((cudaEvent_t) b)); CU(cudaEventElapsedTime(ms, (cudaEvent_t) a, (cudaEvent_t) b)); return 0;
 }
+extern "C" int b200_event_wait(b200_handle h, void * ev) { CTX(h); CU(cudaStreamWaitEvent(c->st, (cudaEvent_t) ev, 0)); return 0; }
+extern "C" int b200_event_synchronize(b200_handle h, void * ev) { CTX(h); CU(cudaEventSynchronize((cudaEvent_t) ev)); return 0; }
 extern "C" int b200_event_destroy(b200_handle h, void * ev) { CTX(h); CU(cudaEventDestroy((cudaEvent_t) ev)); return 0; }
 
 // ------------------------------------------------------------------------------------------------ row split (NCCL)

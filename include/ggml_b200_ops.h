@@ -153,6 +153,10 @@ B200_API int b200_event_create(b200_handle h, void ** ev);
 B200_API int b200_event_record(b200_handle h, void * ev);
 B200_API int b200_event_elapsed_ms(b200_handle h, void * start, void * stop, float * ms); /* syncs on stop */
 B200_API int b200_event_destroy(b200_handle h, void * ev);
+/* ordering between sessions / devices (ggml_backend_i::event_wait, ggml_backend_device_i::event_synchronize,
+ * ggml-backend-impl.h:112-116, 170-178): the session's stream waits for an event recorded on any session; the host waits for it */
+B200_API int b200_event_wait(b200_handle h, void * ev);
+B200_API int b200_event_synchronize(b200_handle h, void * ev);
 /* kernels launched through this handle since open (the `gpu_launches` evidence of bench.py) */
 B200_API int64_t b200_launch_count(b200_handle h);
 /* overwrite a >L2-sized scratch buffer so the next kernel starts from a cold L2 */

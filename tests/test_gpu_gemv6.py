@@ -58,8 +58,9 @@ def test_gemv6_shapes_vs_oracle(t, M, K):
         w = s.weights(t, raw, K)
         l0 = s.launch_count()
         got = s.mulmat(w, x)
-        # (one launch: no separate quantize kernel in front of it)
-        assert s.launch_count() - l0 == 1
+        # one launch (no separate quantize kernel in front of it) wherever every row of every SoA field starts 16-byte aligned
+        # (bulk copies): q6_K's 2-byte scale array needs K % 2048 == 0, the others K % 256 == 0
+        assert s.launch_count() - l0 == (1 if K % (2048 if t == O.Q6_K else 256) == 0 else 2)
         assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-9
         assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
         w.free()
