@@ -42,13 +42,31 @@ struct G6Cfg {
     int unit_end[3];      // running unit count over the matrices of the launch
     int total_units;
     int act_off, part_off, bar_off;
-    int pf_piece;         // L2 prefetch of the CTA's own weights at kernel start: bytes per request (0 = off)
-    long long pf_max;     // ... at most this many bytes per (matrix, field)
     long long * trace;    // development: 4 x %globaltimer per CTA
 };
 
 __device__ __forceinline__ uint32_t g6_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
 __device__ __forceinline__ long long g6_now() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+// row split over the GPUs of one box (rare path, kept out of line): the result also goes into every peer's memory over NVLink, as
+// {value, sequence number} in one 8-byte store (LL protocol) or as plain stores into the peer's dst / add_dst
+__device__ __noinline__ void g6_peer_stores(const GemvArgs & a, int m, int64_t o, float v, float s, float * dst, float * add_dst) {
+    if (a.ll_slots) {
+        const int64_t M = m == 0 ? a.mat[0].M : m == 1 ? a.mat[1].M : a.mat[2].M;
+        const int lloff = m == 0 ? a.ll_off[0] : m == 1 ? a.ll_off[1] : a.ll_off[2];
+        const uint32_t seq = *a.ll_count + a.ll_op;
+        const uint2 * sl = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + lloff + (int64_t) a.ll_rank * M + o;
+        #pragma unroll 1
+        for (int pi = 0; pi < a.npeers; pi++)
+            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"((const char *) sl + a.peer_delta[pi]), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+    } else {
+        #pragma unroll 1
+        for (int pi = 0; pi < a.npeers; pi++) {
+            *(float *) ((char *) (dst + o) + a.peer_delta[pi]) = v;
+            if (add_dst) *(float *) ((char *) (add_dst + o) + a.peer_delta[pi]) = s;
+        }
+    }
+}
 
 template <int TYPE, int NJ, int RU, bool TEAM>
 __global__ void __maxnreg__(TEAM ? (NJ >= 6 ? 112 : 96) : 80)
@@ -110,38 +128,6 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         }
     };
 
-    // ---- this CTA's whole share of the weights into L2, requested before anything else: the HBM -> L2 stream of a launch then
-    // runs while the kernel before it still computes (programmatic dependent launch), bounded by the memory system and not by
-    // the shared memory this CTA can hold; the ring below only has to cover the L2 -> SM latency
-    if (g.pf_piece > 0) {
-        #pragma unroll
-        for (int mi = 0; mi < 3; mi++) {
-            if (mi < a.nmat) {
-                const int ub = mi == 0 ? 0 : g.unit_end[mi - 1], ue = g.unit_end[mi];
-                const int lo = u0 > ub ? u0 : ub, hi = u1 < ue ? u1 : ue;
-                if (lo < hi) {
-                    const int64_t M = a.mat[mi].M;
-                    const int64_t ra = (int64_t) (lo - ub) * RU;
-                    int64_t rb = (int64_t) (hi - ub) * RU; if (rb > M) rb = M;
-                    #pragma unroll
-                    for (int f = 0; f < 4; f++) {
-                        if (f < g.nfields) {
-                            const int64_t rowb = (int64_t) (steps >> 2) * g.b4[f];
-                            const uint8_t * p = a.mat[mi].w.p[f] + ra * rowb;
-                            int64_t bytes = (rb - ra) * rowb;
-                            if (bytes > g.pf_max) bytes = g.pf_max;
-                            // (UBLKPF takes uniform registers: one lane per warp issues, pieces go round the warps)
-                            if (lane == 0)
-                            for (int64_t o = (int64_t) ((warp + f + 2 * mi) % nwarps) * g.pf_piece; o < bytes; o += (int64_t) nwarps * g.pf_piece) {
-                                const uint32_t n = (uint32_t) (bytes - o < g.pf_piece ? bytes - o : g.pf_piece);
-                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p + o), "r"(n) : "memory");
-                            }
-                        }
-                    }
-                }
-            }
-        }
-    }
     if (lane == 0) {
         for (int s = 0; s < g.S; s++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar0 + s * 8));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -196,14 +182,17 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
     __syncthreads();
     if (g.trace && tid == 0) g.trace[blockIdx.x * 4 + 2] = g6_now();
     // this lane's activations: steps seg0 + lane + 32 j of the row
+    // (steps past the end of the segment: clamped to a valid step, their products are dropped -- no branch in the dot loop)
     typename A::Act av[NJ];
+    int sidx[NJ];
     {
         const uint4 * p0 = (const uint4 *) (g6_sm + g.act_off);
         const ActCol ac(p0, p0 + NB, (const int2 *) (g6_sm + g.act_off + (size_t) NB * 32));
         #pragma unroll
         for (int j = 0; j < NJ; j++) {
             const int s = lane + 32 * j;
-            av[j] = A::load_act(ac, seg0 + (s < seglen ? s : 0));
+            sidx[j] = s < seglen ? s : seglen - 1;
+            av[j] = A::load_act(ac, seg0 + sidx[j]);
         }
     }
     float * part = (float *) (g6_sm + g.part_off);
@@ -237,13 +226,13 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         float acc[RU];
         #pragma unroll
         for (int r = 0; r < RU; r++) acc[r] = 0.f;
+        // rows past the end of the matrix (last unit only) are computed from whatever the slot holds and never stored
         #pragma unroll
         for (int j = 0; j < NJ; j++) {
-            const int s = lane + 32 * j;
-            if (s < seglen) {
-                #pragma unroll
-                for (int r = 0; r < RU; r++)
-                    if (r < nrows) acc[r] += wr_dot<TYPE>(W::loads(sw, r * seglen + s), av[j], s);
+            #pragma unroll
+            for (int r = 0; r < RU; r++) {
+                const float d = wr_dot<TYPE>(W::loads(sw, r * seglen + sidx[j]), av[j], sidx[j]);
+                acc[r] += lane + 32 * j < seglen ? d : 0.f;
             }
         }
         float v = reduce_rows<RU>(acc, lane);       // (uses every loaded value: the slot is free once this returns)
@@ -262,18 +251,7 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
             dst[o] = v;
             float s = 0.f;
             if (add_dst) { s = addv + v; add_dst[o] = s; }
-            if (a.ll_slots) {                         // row split, LL protocol: {value, seq} in one 8-byte NVLink store per peer
-                const int64_t M = m == 0 ? a.mat[0].M : m == 1 ? a.mat[1].M : a.mat[2].M;
-                const int lloff = m == 0 ? a.ll_off[0] : m == 1 ? a.ll_off[1] : a.ll_off[2];
-                const uint32_t seq = *a.ll_count + a.ll_op;
-                const uint2 * sl = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + lloff + (int64_t) a.ll_rank * M + o;
-                for (int pi = 0; pi < a.npeers; pi++)
-                    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"((const char *) sl + a.peer_delta[pi]), "r"(__float_as_uint(v)), "r"(seq) : "memory");
-            } else
-            for (int pi = 0; pi < a.npeers; pi++) {   // row split: the same values into every peer's dst (NVLink stores)
-                *(float *) ((char *) (dst + o) + a.peer_delta[pi]) = v;
-                if (add_dst) *(float *) ((char *) (add_dst + o) + a.peer_delta[pi]) = s;
-            }
+            if (a.npeers > 0) g6_peer_stores(a, m, o, v, s, dst, add_dst);
         }
         if (++slot == g.S) { slot = 0; phase ^= 1u; }
     }
@@ -281,7 +259,7 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
 }
 
 // ------------------------------------------------------------------------------------------------ launch
-struct G6Tune { int pf_piece = 8192, pf_kb = 1 << 20; int warps = 0, ru = 0, smem_kb = 100, cps = 1, maxnj = 0, slots = 0; long long * trace = nullptr; int trace_cap = 0, trace_n = 0; };
+struct G6Tune { int warps = 0, ru = 0, smem_kb = 100, cps = 1, maxnj = 0, slots = 0; long long * trace = nullptr; int trace_cap = 0, trace_n = 0; };
 static G6Tune & g6_tune() {
     static G6Tune t = [] {
         G6Tune x;
@@ -291,8 +269,6 @@ static G6Tune & g6_tune() {
         if (const char * e = getenv("B200_G6_CPS")) x.cps = atoi(e);
         if (const char * e = getenv("B200_G6_MAXNJ")) x.maxnj = atoi(e);
         if (const char * e = getenv("B200_G6_SLOTS")) x.slots = atoi(e);
-        if (const char * e = getenv("B200_G6_PF_PIECE")) x.pf_piece = atoi(e) / 16 * 16;
-        if (const char * e = getenv("B200_G6_PF_KB")) x.pf_kb = atoi(e);
         return x;
     }();
     return t;
@@ -377,7 +353,6 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     int64_t units = 0;
     for (int i = 0; i < a.nmat; i++) { units += (a.mat[i].M + ru - 1) / ru; if (units > 0x7fffffff) return false; g.unit_end[i] = (int) units; }
     g.total_units = (int) units;
-    g.pf_piece = tn.pf_piece; g.pf_max = (long long) tn.pf_kb * 1024;
     int grid = sms * (tn.cps > 0 ? tn.cps : 1);
     if (grid > g.total_units) grid = g.total_units;
     if (grid < 1) return false;

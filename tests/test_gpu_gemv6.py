@@ -85,7 +85,7 @@ with B.Session(0) as s:
     w = s.weights(t, raw, K)
     l0 = s.launch_count()
     got = s.mulmat(w, x)
-    assert s.launch_count() - l0 == 1
+    assert s.launch_count() - l0 in (1, 2)       # (2: a forced geometry that does not fit shared memory falls back to quantise + gemv4)
     ref = O.mul_mat(t, raw, x, 1)
     e = float(((got.astype(np.float64) - ref) ** 2).sum() / (ref.astype(np.float64) ** 2).sum())
     assert e <= 1e-9, e
