@@ -68,11 +68,16 @@ __device__ __noinline__ void g6_peer_stores(const GemvArgs & a, int m, int64_t o
     }
 }
 
-template <int TYPE, int NJ, int RU, bool TEAM>
-__global__ void __maxnreg__(TEAM ? (NJ >= 6 ? 112 : 96) : 80)
+// FULL: every K segment has exactly 32 x NJ steps (K = 4096 q4_0 with NJ = 4, ...): segment length, row pitch and field offsets
+// inside a slot are compile-time constants, every shared-memory load of the dot loop has an immediate offset and no lane is masked
+#define G6_REGS(TEAM, FULL, NJ, KQ) ((TEAM) ? ((NJ) >= 6 ? 112 : 96) : ((FULL) && !((KQ) && (NJ) > 1) ? 64 : 80))
+template <int TYPE, int NJ, int RU, bool TEAM, bool FULL>
+__global__ void __maxnreg__(G6_REGS(TEAM, FULL, NJ, TYPE == T_Q4_K || TYPE == T_Q6_K))
 b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
     using W = WT<TYPE>;
     using A = WR<TYPE>;
+    constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
+    constexpr int SEG = 32 * NJ;
     extern __shared__ __align__(128) uint8_t g6_sm[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
 #if __CUDA_ARCH__ >= 900
@@ -83,7 +88,14 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
     const int team = TEAM ? warp / KS : warp, kseg = TEAM ? warp - team * KS : 0, nteams = TEAM ? nwarps / KS : nwarps;
     const int steps = g.steps;
     const int seg0 = kseg * g.seg_steps;
-    const int seglen = TEAM ? (steps - seg0 < g.seg_steps ? steps - seg0 : g.seg_steps) : steps;
+    const int seglen = FULL ? SEG : TEAM ? (steps - seg0 < g.seg_steps ? steps - seg0 : g.seg_steps) : steps;
+    // bytes per 4 steps of every SoA field, offsets of the fields inside a ring slot (compile-time when FULL)
+    constexpr int NF = TYPE == T_Q6_K ? 4 : 2;
+    int b4[4], foff[4];
+    #pragma unroll
+    for (int f = 0; f < 4; f++) { b4[f] = f < NF ? (KQ ? wfields(TYPE).size[f] : wfields(TYPE).size[f] * 4) : 0; }
+    #pragma unroll
+    for (int f = 0, off = 0; f < 4; f++) { foff[f] = FULL ? off : g.foff[f]; off += RU * (SEG / 4) * b4[f]; }
     // this CTA's units, this team's share of them: u0 + team, u0 + team + nteams, ...
     const int u0 = (int) ((long long) g.total_units * blockIdx.x / gridDim.x);
     const int u1 = (int) ((long long) g.total_units * (blockIdx.x + 1) / gridDim.x);
@@ -106,22 +118,22 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         const uint32_t dst = g6_smem(ring + (size_t) slot * g.slot_bytes), bar = bar0 + slot * 8;
         uint32_t total = 0;
         #pragma unroll
-        for (int f = 0; f < 4; f++) if (f < g.nfields) total += (uint32_t) (nrows * (seglen >> 2) * g.b4[f]);
+        for (int f = 0; f < 4; f++) if (f < NF) total += (uint32_t) (nrows * (seglen >> 2) * b4[f]);
         asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(bar), "r"(total) : "memory");
         #pragma unroll
         for (int f = 0; f < 4; f++) {
-            if (f < g.nfields) {
+            if (f < NF) {
                 const uint8_t * base = m == 0 ? a.mat[0].w.p[f] : m == 1 ? a.mat[1].w.p[f] : a.mat[2].w.p[f];
-                const uint32_t segb = (uint32_t) ((seglen >> 2) * g.b4[f]);
+                const uint32_t segb = (uint32_t) ((seglen >> 2) * b4[f]);
                 if (!TEAM) {         // whole rows: the unit is one contiguous range of the field array
-                    const uint8_t * src = base + ((row0 * steps) >> 2) * g.b4[f];
+                    const uint8_t * src = base + ((row0 * steps) >> 2) * b4[f];
                     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                 :: "r"(dst + g.foff[f]), "l"(src), "r"((uint32_t) nrows * segb), "r"(bar) : "memory");
+                                 :: "r"(dst + foff[f]), "l"(src), "r"((uint32_t) nrows * segb), "r"(bar) : "memory");
                 } else {
                     for (int r = 0; r < nrows; r++) {
-                        const uint8_t * src = base + (((row0 + r) * steps + seg0) >> 2) * g.b4[f];
+                        const uint8_t * src = base + (((row0 + r) * steps + seg0) >> 2) * b4[f];
                         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                     :: "r"(dst + g.foff[f] + r * segb), "l"(src), "r"(segb), "r"(bar) : "memory");
+                                     :: "r"(dst + foff[f] + r * segb), "l"(src), "r"(segb), "r"(bar) : "memory");
                     }
                 }
             }
@@ -146,34 +158,37 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         ActDS * ads = (ActDS *) (g6_sm + g.act_off + (size_t) NB * 32);
         const float4 * x4 = (const float4 *) a.x;
         const int K4 = (int) (a.K >> 2);
-        // all of a thread's loads of a round are in flight together: under load an L2 round trip is ~0.75 us (measured), and the
-        // vector sits on the critical path of the whole decode step
-        constexpr int QB = 6;
-        const int nthr = blockDim.x;
-        for (int base = 0; base < K4; base += nthr * QB) {      // K % 128 == 0: whole warps enter and leave together
-            float4 vv[QB];
+        // 4 lanes per 32-element block, 8 elements (one 32-byte sector) per lane.  All loads of a round are in flight together:
+        // the vector sits on the critical path of the whole decode step and an L2 round trip under load is ~1 us (measured)
+        constexpr int QB = 3;
+        const int nthr = blockDim.x, K8 = K4 >> 1;             // K % 256 == 0: whole warps enter and leave together
+        for (int base = 0; base < K8; base += nthr * QB) {
+            float4 va[QB], vb[QB];
             #pragma unroll
-            for (int q = 0; q < QB; q++) { const int i = base + q * nthr + tid; if (i < K4) vv[q] = __ldcg(x4 + i); }
+            for (int q = 0; q < QB; q++) { const int i = base + q * nthr + tid; if (i < K8) { va[q] = __ldcg(x4 + 2 * i); vb[q] = __ldcg(x4 + 2 * i + 1); } }
             #pragma unroll
             for (int q = 0; q < QB; q++) {
                 const int i = base + q * nthr + tid;
-                if (i < K4) {
-                    const float4 v = vv[q];
-                    const int blk = i >> 3, sub = i & 7;
-                    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+                if (i < K8) {
+                    const float4 v = va[q], w = vb[q];
+                    const int blk = i >> 2, sub = i & 3;           // sub 0, 1: elements 0..15 (plane 0); 2, 3: plane 1
+                    float amax = fmaxf(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))),
+                                       fmaxf(fmaxf(fabsf(w.x), fabsf(w.y)), fmaxf(fabsf(w.z), fabsf(w.w))));
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
                     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
                     const float d  = __fdiv_rn(amax, 127.0f);
                     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
                     const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
                     const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
-                    int sum = q0 + q1 + q2 + q3;
-                    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                    const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
-                    const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
-                    *(uint32_t *) (aq + ((size_t) (sub >> 2) * NB + blk) * 16 + (sub & 3) * 4) = packed;
+                    const int q4 = (int) roundf(__fmul_rn(w.x, id)), q5 = (int) roundf(__fmul_rn(w.y, id));
+                    const int q6 = (int) roundf(__fmul_rn(w.z, id)), q7 = (int) roundf(__fmul_rn(w.w, id));
+                    int sum = (q0 + q1) + (q2 + q3) + (q4 + q5) + (q6 + q7);
+                    sum += __shfl_xor_sync(0xffffffffu, sum, 1);           // lanes 0, 1: plane 0 sum; lanes 2, 3: plane 1 sum
+                    const int other = __shfl_xor_sync(0xffffffffu, sum, 2);
+                    uint2 pk;
+                    pk.x = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
+                    pk.y = (uint32_t) (q4 & 0xFF) | ((uint32_t) (q5 & 0xFF) << 8) | ((uint32_t) (q6 & 0xFF) << 16) | ((uint32_t) (q7 & 0xFF) << 24);
+                    *(uint2 *) (aq + ((size_t) (sub >> 1) * NB + blk) * 16 + (sub & 1) * 8) = pk;
                     if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; ads[blk] = o; }
                 }
             }
@@ -191,7 +206,7 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         #pragma unroll
         for (int j = 0; j < NJ; j++) {
             const int s = lane + 32 * j;
-            sidx[j] = s < seglen ? s : seglen - 1;
+            sidx[j] = FULL || s < seglen ? s : seglen - 1;
             av[j] = A::load_act(ac, seg0 + sidx[j]);
         }
     }
@@ -222,17 +237,19 @@ b200_gemv6_kernel(const GemvArgs a, const G6Cfg g) {
         }
         WPtrs sw;
         #pragma unroll
-        for (int f = 0; f < 4; f++) sw.p[f] = ring + (size_t) slot * g.slot_bytes + g.foff[f];
+        for (int f = 0; f < 4; f++) sw.p[f] = ring + (size_t) slot * g.slot_bytes + foff[f];
         float acc[RU];
         #pragma unroll
         for (int r = 0; r < RU; r++) acc[r] = 0.f;
         // rows past the end of the matrix (last unit only) are computed from whatever the slot holds and never stored
         #pragma unroll
         for (int j = 0; j < NJ; j++) {
-            #pragma unroll
-            for (int r = 0; r < RU; r++) {
-                const float d = wr_dot<TYPE>(W::loads(sw, r * seglen + sidx[j]), av[j], sidx[j]);
-                acc[r] += lane + 32 * j < seglen ? d : 0.f;
+            if (FULL || 32 * j < seglen) {                       // (warp-uniform: a short last segment skips whole steps)
+                #pragma unroll
+                for (int r = 0; r < RU; r++) {
+                    const float d = wr_dot<TYPE>(W::loads(sw, r * seglen + sidx[j]), av[j], sidx[j]);
+                    if (FULL) acc[r] += d; else acc[r] += lane + 32 * j < seglen ? d : 0.f;
+                }
             }
         }
         float v = reduce_rows<RU>(acc, lane);       // (uses every loaded value: the slot is free once this returns)
@@ -277,12 +294,12 @@ static G6Tune & g6_tune() {
 void gemv6_trace(long long * buf, int cap_launches) { G6Tune & t = g6_tune(); t.trace = buf; t.trace_cap = cap_launches; t.trace_n = 0; }
 int gemv6_trace_count() { return g6_tune().trace_n; }
 
-template <int TYPE, int NJ, int RU, bool TEAM>
+template <int TYPE, int NJ, int RU, bool TEAM, bool FULL>
 static cudaError_t g6_go(const GemvArgs & a, const G6Cfg & g, int grid, int nwarps, int smem, cudaStream_t st, bool pdl) {
     static int smem_set[64] = {0};
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(b200_gemv6_kernel<TYPE, NJ, RU, TEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(b200_gemv6_kernel<TYPE, NJ, RU, TEAM, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         smem_set[dev] = smem;
     }
@@ -292,12 +309,18 @@ static cudaError_t g6_go(const GemvArgs & a, const G6Cfg & g, int grid, int nwar
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, b200_gemv6_kernel<TYPE, NJ, RU, TEAM>, a, g);
+    return cudaLaunchKernelEx(&cfg, b200_gemv6_kernel<TYPE, NJ, RU, TEAM, FULL>, a, g);
 }
 template <int TYPE, int NJ>
-static cudaError_t g6_pick(const GemvArgs & a, const G6Cfg & g, int ru, bool team, int grid, int nwarps, int smem, cudaStream_t st, bool pdl) {
-    if (team) return ru == 2 ? g6_go<TYPE, NJ, 2, true>(a, g, grid, nwarps, smem, st, pdl)  : g6_go<TYPE, NJ, 1, true>(a, g, grid, nwarps, smem, st, pdl);
-    return           ru == 2 ? g6_go<TYPE, NJ, 2, false>(a, g, grid, nwarps, smem, st, pdl) : g6_go<TYPE, NJ, 1, false>(a, g, grid, nwarps, smem, st, pdl);
+static cudaError_t g6_pick(const GemvArgs & a, const G6Cfg & g, int ru, bool team, bool full, int grid, int nwarps, int smem, cudaStream_t st, bool pdl) {
+    if (full) {
+        if constexpr (NJ <= 4) {
+            if (team) return ru == 2 ? g6_go<TYPE, NJ, 2, true, true>(a, g, grid, nwarps, smem, st, pdl)  : g6_go<TYPE, NJ, 1, true, true>(a, g, grid, nwarps, smem, st, pdl);
+            return           ru == 2 ? g6_go<TYPE, NJ, 2, false, true>(a, g, grid, nwarps, smem, st, pdl) : g6_go<TYPE, NJ, 1, false, true>(a, g, grid, nwarps, smem, st, pdl);
+        }
+    }
+    if (team) return ru == 2 ? g6_go<TYPE, NJ, 2, true, false>(a, g, grid, nwarps, smem, st, pdl)  : g6_go<TYPE, NJ, 1, true, false>(a, g, grid, nwarps, smem, st, pdl);
+    return           ru == 2 ? g6_go<TYPE, NJ, 2, false, false>(a, g, grid, nwarps, smem, st, pdl) : g6_go<TYPE, NJ, 1, false, false>(a, g, grid, nwarps, smem, st, pdl);
 }
 
 template <int TYPE>
@@ -339,8 +362,9 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     g.slot_bytes = (off + 15) & ~15;
     // warps and ring depth from the shared-memory budget (two kernels of this kind are meant to fit one SM together)
     const int act_bytes = (int) (a.K / 32 * 40);
-    // registers: 80 per thread (teams 96, 112 with 6 steps per lane): 12 (10, 8) warps keep the kernel under half of the SM's register file
-    int nw = tn.warps > 0 ? tn.warps : (ks > 1 ? (nj >= 6 ? 8 : 10) : 12);
+    // registers: 64 per thread when FULL, else 80 (teams 96, 112 with 6 steps per lane): 16 / 12 (10, 8) warps keep the kernel under half of the SM's register file
+    const bool full = steps == ks * 32 * nj && nj <= 4;              // every segment exactly 32 x NJ steps
+    int nw = tn.warps > 0 ? tn.warps : (ks > 1 ? (nj >= 6 ? 8 : 10) : full && !(KQ && nj > 1) ? 16 : 12);
     nw = nw / ks * ks; if (nw < ks) nw = ks;
     if (nw > 16) nw = 16 / ks * ks;
     if (ks > 1 && nw / ks > 15) nw = 15 * ks;                                             // named barriers 1 .. 15
@@ -366,10 +390,10 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     if (tn.trace && tn.trace_n < tn.trace_cap) { g.trace = tn.trace + (size_t) tn.trace_n * 4 * 1024; tn.trace_n++; }
     const bool team = ks > 1;
     if constexpr (KQ) {
-        *err = nj <= 1 ? g6_pick<TYPE, 1>(a, g, ru, team, grid, nw, smem, st, pdl) : g6_pick<TYPE, 2>(a, g, ru, team, grid, nw, smem, st, pdl);
+        *err = nj <= 1 ? g6_pick<TYPE, 1>(a, g, ru, team, full, grid, nw, smem, st, pdl) : g6_pick<TYPE, 2>(a, g, ru, team, full, grid, nw, smem, st, pdl);
     } else {
-        *err = nj <= 2 ? g6_pick<TYPE, 2>(a, g, ru, team, grid, nw, smem, st, pdl) :
-               nj <= 4 ? g6_pick<TYPE, 4>(a, g, ru, team, grid, nw, smem, st, pdl) : g6_pick<TYPE, 6>(a, g, ru, team, grid, nw, smem, st, pdl);
+        *err = nj <= 2 ? g6_pick<TYPE, 2>(a, g, ru, team, full, grid, nw, smem, st, pdl) :
+               nj <= 4 ? g6_pick<TYPE, 4>(a, g, ru, team, full, grid, nw, smem, st, pdl) : g6_pick<TYPE, 6>(a, g, ru, team, full, grid, nw, smem, st, pdl);
     }
     return true;
 }
