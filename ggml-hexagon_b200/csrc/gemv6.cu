@@ -327,7 +327,9 @@ template <int TYPE>
 static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaError_t * err) {
     G6Tune & tn = g6_tune();
     constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
-    const int on = getenv("B200_GEMV6") ? atoi(getenv("B200_GEMV6")) : 1;                 // (read per launch: tests switch it)
+    // opt-in (B200_GEMV6=1) while it is slower than the quantize + gemv4 / gemv5 launches on the whole decode step (measured on B200:
+    // 1.38 against 0.955 ms per Llama-2-7B token); read per launch: tests switch it
+    const int on = getenv("B200_GEMV6") ? atoi(getenv("B200_GEMV6")) : 0;
     if (!on || a.rs_signal || !a.x || ((uintptr_t) a.x & 15) || a.K % 256) return false;
     const WFields wf = wfields(TYPE);
     const int steps = (int) (a.K / (KQ ? 64 : 32));
@@ -364,9 +366,10 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     const int act_bytes = (int) (a.K / 32 * 40);
     // registers: 64 per thread when FULL, else 80 (teams 96, 112 with 6 steps per lane): 16 / 12 (10, 8) warps keep the kernel under half of the SM's register file
     const bool full = steps == ks * 32 * nj && nj <= 4;              // every segment exactly 32 x NJ steps
+    const bool team_ = ks > 1;
     int nw = tn.warps > 0 ? tn.warps : (ks > 1 ? (nj >= 6 ? 8 : 10) : full && !(KQ && nj > 1) ? 16 : 12);
     nw = nw / ks * ks; if (nw < ks) nw = ks;
-    if (nw > 16) nw = 16 / ks * ks;
+    { const int cap = !team_ && full ? 24 : 16; if (nw > cap) nw = cap / ks * ks; }
     if (ks > 1 && nw / ks > 15) nw = 15 * ks;                                             // named barriers 1 .. 15
     const int budget = tn.smem_kb * 1024 - act_bytes - 1024;
     int S = tn.slots > 0 ? tn.slots : budget / (nw * g.slot_bytes);

@@ -16,6 +16,11 @@ pytestmark = pytest.mark.gpu
 WTYPES = [O.Q4_0, O.Q8_0, O.Q4_K, O.Q6_K]
 
 
+@pytest.fixture(autouse=True)
+def _gemv6_on(monkeypatch):
+    monkeypatch.setenv("B200_GEMV6", "1")        # opt-in kernel (read per launch)
+
+
 def nmse(a, b):
     return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
 
@@ -91,7 +96,7 @@ with B.Session(0) as s:
     assert e <= 1e-9, e
 print("ok")
 """ % (os.path.dirname(O.__file__), os.path.dirname(B.__file__), t, M, K)
-    env = dict(os.environ, B200_G6_RU=str(ru), B200_G6_WARPS=str(warps), B200_G6_SLOTS=str(slots))
+    env = dict(os.environ, B200_GEMV6="1", B200_G6_RU=str(ru), B200_G6_WARPS=str(warps), B200_G6_SLOTS=str(slots))
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
 
