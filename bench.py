@@ -25,13 +25,19 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "ggml-hexagon_b200")):
     if p not in sys.path:
         sys.path.insert(0, p)
+import rowsplit as RS          # host-side partition helpers of the row split (ggml-hexagon_b200/rowsplit.py)
 
 Q4_0 = 2
 METRIC = "tokens/s Llama Q4_0 decode (tg, MUL_MAT+ADD path, batch 1)"
-# dram__bytes_read + dram__bytes_write of the step's GEMV launches / 225 MUL_MAT ops (129 grouped launches), from the
-# ncu --set full capture of this bench command (profiles/r01_e_ncu_gemv4_full_llama2_7b.txt: 113.966 MB per layer + the
-# 73.73 MB output matrix) -- equal to the algorithmic bytes within 0.2 %
-TRAFFIC_PER_LAUNCH = int((32 * 113.966e6 + 73.73e6) / 225)
+def measured_traffic():
+    """dram__bytes_read + dram__bytes_write per MUL_MAT launch of the decode step, parsed from the ncu --set full capture of THIS bench
+    command that tools/ncu_traffic.py summarised into profiles/ (with the commit it was taken at); None when there is none"""
+    p = os.path.join(ROOT, "profiles", "r02_ncu_decode_traffic.json")
+    try:
+        d = json.load(open(p))
+        return int(d["dram_bytes_per_mulmat"]), "profiles/r02_ncu_decode_traffic.json (ncu --set full, commit %s)" % d.get("commit", "?")
+    except (OSError, KeyError, ValueError):
+        return None, None
 
 
 # ------------------------------------------------------------------------------------------------ workloads
@@ -157,7 +163,7 @@ def measured_peak_hbm():
 class DecodeWorkload:
     """All MUL_MAT/ADD nodes of one decoded token, device resident.  Row r-th slice of every weight when world > 1."""
 
-    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0", ncols=1, share=None, heap_cols=0):
+    def __init__(self, B, sess, model, rank=0, world=1, seed=1234, mode="p2p", quant="q4_0", ncols=1, share=None, heap_cols=0, host_override=None):
         """ncols > 1: the same node list over ncols activation columns (prefill); share: another workload of the same model and
         quant whose HBM weights (and, under row split, symmetric heap) are used instead of making a second copy; heap_cols: room in
         the symmetric heap for a later workload of that many columns sharing it"""
@@ -175,12 +181,23 @@ class DecodeWorkload:
         self.alg_bytes = 0
         self.n_mulmat = 0
         host = {}
+        self.host_full = {}                          # world > 1: the FULL matrices (rank 0 checks sampled rows of every rank's slice)
         for name, M, K in layer + [out]:
             assert M % world == 0, (name, M, world)
-            full_rows = M // world
-            # one random host matrix per shape; every layer gets its own HBM copy (distinct addresses, no L2 reuse)
+            # one random host matrix per shape; every layer gets its own HBM copy (distinct addresses, no L2 reuse).
+            # Row split: every rank generates the same full matrix (same seed) and keeps ITS rows [rank * M / world, (rank + 1) * M / world)
             if share is None:
-                host[name] = random_weights(wt(name), full_rows, K, rng)
+                full = host_override[name] if host_override is not None else random_weights(wt(name), M, K, rng)
+                if world > 1:
+                    lo, hi = RS.row_range(M, rank, world)
+                    host[name] = np.ascontiguousarray(RS.slice_rows(full, rank, world))
+                    assert host[name].shape[0] == hi - lo
+                    if rank == 0:
+                        self.host_full[name] = full
+                else:
+                    host[name] = full
+        if share is not None:
+            self.host_full = share.host_full
         if share is not None:
             self.weights, self.w_out = share.weights, share.w_out
         else:
@@ -411,25 +428,72 @@ def time_prefill_model(B, s, wl, N=512, steps=5):
                     "peak = MEASURED_PEAKS.json bf16_tflops_sustained (fp16 and bf16 run at the same tensor rate)" % (wl.n_mulmat, 2 * wl.L, N)}
 
 
+def rowsplit_parity(B, s, wl, nsample=256, seed=99):
+    """Rank 0, after a row-split step: every kind of op of the LAST layer (and the output matrix) is recomputed on this GPU alone for
+    `nsample` rows drawn over the WHOLE matrix (= every rank's slice) from the full host copy, with the op's actual input vector as it
+    stands in the symmetric heap, and compared with what the row-split step left in the output vector.  A permuted, stale or missing
+    slice of any rank shows up here (NMSE bar 1e-9: same integers and scales, float summation order may differ)."""
+    rng = np.random.default_rng(seed)
+    dims = dict((n, (m, k)) for n, m, k in wl.layer)
+    last_in = wl.x3 if wl.final_x is wl.x2 else wl.x2          # input of the last layer (the ping-pong partner of its output)
+    if wl.L == 1:
+        last_in = wl.x
+    ops = [("wq", last_in, wl.q), ("wk", last_in, wl.k), ("wv", last_in, wl.v), ("wo", wl.q, wl.o), ("gate", wl.hres, wl.g),
+           ("up", wl.hres, wl.u), ("down", wl.g, wl.dn), (wl.out[0], wl.final_x, wl.logits)]
+    worst, detail = 0.0, {}
+    for name, src, dst in ops:
+        M, K = (wl.out[1], wl.out[2]) if name == wl.out[0] else dims[name]
+        rows = np.sort(rng.choice(M, size=min(nsample, M), replace=False))
+        w = s.weights(Q4_0, np.ascontiguousarray(wl.host_full[name][rows]), K)
+        x = s.to_host(src, (1, K), np.float32)
+        ref = s.mulmat(w, x).reshape(-1)
+        got = s.to_host(dst, (M,), np.float32)[rows]
+        e = float(((got.astype(np.float64) - ref) ** 2).sum() / max(float((ref.astype(np.float64) ** 2).sum()), 1e-30))
+        detail[name] = e
+        worst = max(worst, e)
+        w.free()
+    return {"parity_ok": bool(worst <= 1e-9), "nmse_max": worst, "rows_sampled_per_op": int(nsample), "per_op": detail,
+            "what": "rank 0 recomputes sampled rows of every op of the last layer + the output matrix on one GPU from the full host matrices"}
+
+
+def time_decode(B, s, wl, steps):
+    for _ in range(3):
+        wl.step()
+    s.sync()
+    e0, e1 = s.event(), s.event()
+    s.record(e0)
+    for _ in range(steps):
+        wl.step()
+    s.record(e1)
+    return s.elapsed_ms(e0, e1) * 1e-3 / steps
+
+
 def time_add(B, s, iters=50):
-    """GGML_OP_ADD: f32 ne=[4096] (launch latency: report us) and [4096, 512] (HBM-bound: 3 x nbytes / time)"""
-    import ctypes as C
+    """GGML_OP_ADD as KERNEL time: 64 ADD nodes over rotating, distinct buffers (no L2 reuse at 8 MB each) submitted as one
+    captured CUDA graph, device time / 64.  ne=[4096]: launch-latency bound (report us); [4096, 512]: HBM-bound (3 x nbytes / time)"""
     out = []
     for ne in ([4096], [4096, 512]):
         n = int(np.prod(ne))
-        a, b, d = s.malloc(4 * n), s.malloc(4 * n), s.malloc(4 * n)
-        t0, t1, td = B.f32_tensor(a.ptr, ne), B.f32_tensor(b.ptr, ne), B.f32_tensor(d.ptr, ne, op=B.OP_ADD)
+        nn = 64
+        bufs = [s.malloc(4 * n) for _ in range(3 * nn)]
+        nodes = []
+        for i in range(nn):
+            nd = B.Node()
+            a, b, d = bufs[3 * i], bufs[3 * i + 1], bufs[3 * i + 2]
+            nd.src0, nd.src1, nd.dst = B.f32_tensor(a.ptr, ne), B.f32_tensor(b.ptr, ne), B.f32_tensor(d.ptr, ne, op=B.OP_ADD)
+            nodes.append(nd)
+        arr = (B.Node * nn)(*nodes)
         for _ in range(3):
-            B._ck(B.lib().b200_add(s.h, C.byref(t0), C.byref(t1), C.byref(td)))
+            s.graph_compute(arr, True)
         s.sync()
         e0, e1 = s.event(), s.event()
         s.record(e0)
         for _ in range(iters):
-            B._ck(B.lib().b200_add(s.h, C.byref(t0), C.byref(t1), C.byref(td)))
+            s.graph_compute(arr, True)
         s.record(e1)
-        us = s.elapsed_ms(e0, e1) * 1e3 / iters
-        out.append({"ne": ne, "us": round(us, 2), "GB/s": round(3 * 4 * n / us / 1e3, 1)})
-        for x in (a, b, d):
+        us = s.elapsed_ms(e0, e1) * 1e3 / (iters * nn)
+        out.append({"ne": ne, "us": round(us, 3), "GB/s": round(3 * 4 * n / us / 1e3, 1), "how": "64 ADD nodes per captured CUDA graph, distinct buffers"})
+        for x in bufs:
             x.free()
     return out
 
@@ -457,6 +521,77 @@ def time_kquant(B, s, steps):
     return out
 
 
+def plugin_e2e(model, steps, x_host):
+    """The headline e2e: the SAME node list through the drop-in seat, libggml-b200.so, called the way a ggml host calls a backend
+    (the reference's public C API from its own libggml, tests/ggmlapi.py): per step ggml_backend_tensor_set(x, host buffer) ->
+    ggml_backend_graph_compute (= graph_compute_async + synchronize, ggml-backend.cpp:327-335) -> ggml_backend_tensor_get(logits).
+    The host library is the caller, not the thing measured; it comes from oracle/_ref because the plugin API needs a ggml host."""
+    import ctypes as C
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ggmlapi as GA
+    G = GA.lib()
+    reg, devs = GA.load_plugin()
+    be = G.ggml_backend_dev_init(devs[0], None)
+    layer, L, out, h, f = llama_shapes(model)
+    ctx = GA.Ctx(L * 20 + 16)
+    gf = G.ggml_new_graph(ctx.ctx)
+    x = ctx.tensor(GA.F32, h, 1)
+    weights, cur = [], x
+    dims = dict((n, (m, k)) for n, m, k in layer)
+
+    def W(name):
+        m, k = dims[name] if name != out[0] else (out[1], out[2])
+        t = ctx.tensor(GA.Q4_0, k, m)
+        weights.append((name, t))
+        return t
+
+    def node(t):
+        G.ggml_build_forward_expand(gf, t)
+        return t
+    for _ in range(L):
+        q = node(G.ggml_mul_mat(ctx.ctx, W("wq"), cur))
+        node(G.ggml_mul_mat(ctx.ctx, W("wk"), cur))
+        node(G.ggml_mul_mat(ctx.ctx, W("wv"), cur))
+        o = node(G.ggml_mul_mat(ctx.ctx, W("wo"), q))
+        hres = node(G.ggml_add(ctx.ctx, cur, o))
+        g = node(G.ggml_mul_mat(ctx.ctx, W("gate"), hres))
+        node(G.ggml_mul_mat(ctx.ctx, W("up"), hres))
+        dn = node(G.ggml_mul_mat(ctx.ctx, W("down"), g))
+        cur = node(G.ggml_add(ctx.ctx, hres, dn))
+    logits_t = node(G.ggml_mul_mat(ctx.ctx, W(out[0]), cur))
+    buf = G.ggml_backend_alloc_ctx_tensors(ctx.ctx, be)
+    assert buf, "alloc_ctx_tensors failed"
+    rng = np.random.default_rng(1234)
+    host = {}
+    for name, m, k in layer + [out]:
+        host[name] = random_q4_0(m, k, rng)
+    for name, t in weights:
+        a = host[name]
+        G.ggml_backend_tensor_set(t, a.ctypes.data_as(C.c_void_p), 0, a.nbytes)
+    xh = np.ascontiguousarray(x_host[:h], dtype=np.float32)
+    logits = np.empty(out[1], dtype=np.float32)
+
+    def step():
+        G.ggml_backend_tensor_set(x, xh.ctypes.data_as(C.c_void_p), 0, xh.nbytes)
+        rc = G.ggml_backend_graph_compute(be, gf)
+        assert rc == 0, rc
+        G.ggml_backend_tensor_get(logits_t, logits.ctypes.data_as(C.c_void_p), 0, logits.nbytes)
+    for _ in range(5):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    sec = (time.perf_counter() - t0) / steps
+    res = {"value": round(1.0 / sec, 3), "unit": "tokens/s", "ms_per_step": round(sec * 1e3, 5), "h2d_bytes_per_step": int(xh.nbytes),
+           "d2h_bytes_per_step": int(logits.nbytes), "logits_finite": bool(np.isfinite(logits).all()),
+           "call": "ggml_backend_tensor_set(x) -> ggml_backend_graph_compute(libggml-b200.so, %d nodes) -> ggml_backend_tensor_get(logits); pageable host "
+                   "buffers, host perf_counter" % (9 * L + 1)}
+    G.ggml_backend_buffer_free(buf)
+    ctx.free()
+    G.ggml_backend_free(be)
+    return res, logits
+
+
 def cpu_baseline(model, budget_s):
     """reference ggml-cpu (oracle/_ref) on the host cores; falls back to the single-threaded C port only if _ref is absent"""
     import pyref
@@ -464,7 +599,7 @@ def cpu_baseline(model, budget_s):
     cores = os.cpu_count() or 1
     try:
         R = pyref.Ref()
-        per_tok, desc = pyref.bench_decode(R, layer, out, L, 2, Q4_0, cores, budget_s=budget_s)
+        per_tok, desc = pyref.bench_decode(R, layer, out, L, 8, Q4_0, cores, budget_s=budget_s)
         return {"value": round(1.0 / per_tok, 4), "unit": "tokens/s", "cores": cores, "kind": "reference",
                 "sample": desc + "; oracle/_ref/%s ggml-cpu, llamafile on, OpenMP off" % R.variant}
     except (FileNotFoundError, OSError):
@@ -590,6 +725,30 @@ def run_b200(args, rank, world):
         e2e_s = float(t.item())
     clocks = sampler.stop()
     logits = np.ctypeslib.as_array(C.cast(hy, C.POINTER(C.c_float)), shape=(wl.out[1],)).copy()
+    parity = None
+    single = None
+    if world > 1:
+        # (rank 0 works alone here; the other ranks wait in the barrier below)
+        wl.step()              # one more step on every rank: the vectors the parity check reads are this step's
+        barrier()
+        if rank == 0:
+            parity = rowsplit_parity(B, s, wl)
+            if not args.no_shapes:
+                # the SAME model on ONE GPU (39 GB of q4_0 fit): the denominator of the strong-scaling efficiency of this line
+                one = DecodeWorkload(B, s, model, 0, 1, host_override=wl.host_full)
+                t1 = time_decode(B, s, one, max(5, args.steps // 2))
+                single = {"tokens_per_s": round(1.0 / t1, 3), "ms_per_step": round(t1 * 1e3, 4),
+                          "note": "llama3-70b-q4_0 decode node list on rank 0's GPU alone (same kernels, no split), measured in this run"}
+                one.free()
+        barrier()
+    plugin = plugin_logits = None
+    if world == 1 and rank == 0 and not args.no_plugin:
+        try:
+            plugin, plugin_logits = plugin_e2e(model, args.steps, wl.x_host)
+            # same weights (same generator, same order), same kernels: the seat must reproduce the op layer bit for bit
+            plugin["matches_op_layer_bitwise"] = bool(np.array_equal(plugin_logits, logits))
+        except (FileNotFoundError, OSError, RuntimeError, AssertionError) as e:
+            plugin = {"unavailable": "%s: %s" % (type(e).__name__, e)}
     shapes = time_shapes(B, s, wl) if world == 1 and not args.no_shapes else None
     prefill = None
     if world == 1 and not args.no_shapes and rank == 0:
@@ -621,9 +780,19 @@ def run_b200(args, rank, world):
                               "exchange per op, one CUDA graph per rank; max over ranks" % rs_prefill_cols}
     kquant = None
     adds = time_add(B, s) if world == 1 and not args.no_shapes and rank == 0 else None
+    rowsplit_n1 = None
     if world == 1 and not args.no_shapes and rank == 0:
         wl.free()
         kquant = time_kquant(B, s, args.steps)
+        # the N >= 2 lines run Llama-3-70B under row split; its single-GPU number belongs to the N = 1 line as well (the driver's own
+        # 1 -> N efficiency divides by the 7B headline, which is another workload)
+        w70 = DecodeWorkload(B, s, "llama3-70b", seed=1234)
+        t70 = time_decode(B, s, w70, max(5, args.steps // 2))
+        peak70, _ = measured_peak_hbm()
+        rowsplit_n1 = {"workload": "llama3-70b-q4_0-decode on one GPU (the N >= 2 workload, unsplit)", "tokens_per_s": round(1.0 / t70, 3),
+                       "ms_per_step": round(t70 * 1e3, 4), "GB/s": round(w70.alg_bytes / t70 / 1e9, 1), "hbm_frac": round(w70.alg_bytes / t70 / 1e9 / peak70, 4),
+                       "weight_bytes": w70.weight_bytes_local}
+        w70.free()
     if rank != 0:
         s.close()
         return
@@ -643,11 +812,29 @@ def run_b200(args, rank, world):
                        ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores {value, seq} slots into peer HBM over NVLink, polled by a gather kernel per op; B200_RS_PROTO=flag: plain stores + flag exchange)"
                         if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "frac_of_nominal_8000": round(achieved / 8000.0, 4),
-                         "traffic": TRAFFIC_PER_LAUNCH if world == 1 else None, "peak_source": peak_src, "kernel": "gemv5_kernel<q4_0,8,1> (launches >= 12 MB; gemv4_kernel<q4_0,1,4> for wo)",
+                         "traffic": measured_traffic()[0] if world == 1 else None, "traffic_source": measured_traffic()[1] if world == 1 else None, "peak_source": peak_src, "kernel": "gemv5_kernel<q4_0,8,1> (launches >= 12 MB; gemv4_kernel<q4_0,1,4> for wo)",
                          "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
-            "e2e": {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
-                    "timer": "host perf_counter around K x (h2d_async from pinned memory + graph_compute + d2h_async + synchronize)"},
             "gpu_launches": int(launches), "clocks": clocks, "logits_finite": bool(np.isfinite(logits).all())}
+    e2e_ops = {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],
+               "call": "op-layer C-ABI (libb200ops.so): b200_memcpy_h2d_async from pinned memory + b200_graph_compute + b200_memcpy_d2h_async + b200_synchronize",
+               "timer": "host perf_counter around K steps"}
+    if plugin and "value" in plugin:
+        # headline e2e = the reference-facing plugin call (ggml_backend_graph_compute on libggml-b200.so); the op-layer figure explains it
+        line["e2e"] = dict(plugin, through="libggml-b200.so (ggml backend plugin API)")
+        line["e2e_op_layer"] = e2e_ops
+        line["e2e"]["ratio_to_op_layer"] = round(plugin["value"] / e2e_ops["value"], 4)
+    else:
+        line["e2e"] = e2e_ops
+        if plugin:
+            line["e2e_plugin"] = plugin
+    if parity is not None:
+        line["parity_ok"] = parity["parity_ok"]
+        line["parity"] = parity
+    if single is not None:
+        line["single_gpu_same_model"] = single
+        line["strong_scaling_eff"] = round((1.0 / step_s) / (world * single["tokens_per_s"]), 4)
+    if rowsplit_n1 is not None:
+        line["rowsplit_n1"] = rowsplit_n1
     if shapes:
         line["shapes"] = shapes
     if prefill:
@@ -676,6 +863,7 @@ def main():
                     help="N > 1: p2p = GEMV stores into peer memory + flag exchange (default); nccl = ncclAllGather per MUL_MAT")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-shapes", action="store_true", help="skip the per-shape GEMV table")
+    ap.add_argument("--no-plugin", action="store_true", help="skip the e2e leg through libggml-b200.so (needs oracle/_ref as the ggml host)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

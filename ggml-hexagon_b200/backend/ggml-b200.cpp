@@ -17,8 +17,11 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <atomic>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 // everything goes through ggml's logger (GGML_LOG_*, ggml-impl.h), so a host's ggml_log_set callback sees the backend
@@ -38,10 +41,22 @@ struct b200_device_ctx {
     std::mutex  mu;
     ggml_backend_buffer_type buft;
 };
+// a node list already marshalled for one ggml_cgraph: what ggmlhexagon_compute rebuilds per op and per call (string op key + three
+// dsptensor structs, ggml-hexagon.cpp:4975-5049) is built once per distinct graph here.  `fp` is the fingerprint of everything the
+// marshalling read (tensor addresses, data addresses, types, shapes, strides, op parameters); a call whose graph has the same
+// fingerprint reuses `nodes` and hands the op layer `key`, so neither side re-hashes 160 KB of descriptors per token.
+struct b200_graph_entry {
+    std::vector<uint64_t>  fp;
+    std::vector<b200_node> nodes;
+    uint64_t               key = 0;
+    uint64_t               last_use = 0;
+};
 struct b200_backend_ctx {
     b200_device_ctx * dev = nullptr;
     std::string       name;
-    std::vector<b200_node> nodes;
+    std::unordered_map<const ggml_cgraph *, b200_graph_entry> graphs;
+    std::vector<uint64_t> fp;        // scratch
+    uint64_t          tick = 0;
 };
 struct b200_buffer_ctx {
     b200_device_ctx * dev = nullptr;
@@ -262,30 +277,63 @@ static int b200_op_of(const ggml_tensor * node) {
 // node loop of ggmlhexagon_backend_graph_compute_general (ggml-hexagon.cpp:5555-5574): view ops are no-ops, every other
 // node is dst = op(src0, src1).  The whole list goes down in ONE call; asynchronous (ggml_backend_graph_compute adds
 // the synchronize, ggml-backend.cpp:327-335).
+static std::atomic<uint64_t> g_graph_key{1};
+static void fp_tensor(std::vector<uint64_t> & fp, const ggml_tensor * t) {
+    if (!t) { fp.push_back(0); return; }
+    fp.push_back((uint64_t) (uintptr_t) t); fp.push_back((uint64_t) (uintptr_t) t->data); fp.push_back((uint64_t) (uintptr_t) t->view_src);
+    fp.push_back((uint64_t) t->type | ((uint64_t) t->op << 32));
+    for (int i = 0; i < 4; i++) { fp.push_back((uint64_t) t->ne[i]); fp.push_back((uint64_t) t->nb[i]); }
+    fp.push_back(t->view_src ? (uint64_t) (uintptr_t) t->view_src->data : 0);
+}
 static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_cgraph * cgraph) {
     b200_backend_ctx * c = (b200_backend_ctx *) backend->context;
-    c->nodes.clear();
+    // ---- fingerprint of the graph as this function would read it
+    std::vector<uint64_t> & fp = c->fp;
+    fp.clear();
     for (int i = 0; i < cgraph->n_nodes; i++) {
-        ggml_tensor * node = cgraph->nodes[i];
+        const ggml_tensor * node = cgraph->nodes[i];
         if (is_view_op(node->op) || ggml_is_empty(node)) continue;
-        const int op = b200_op_of(node);
-        if (op < 0) {
-            B200_ERR("graph_compute: op %s was never admitted by supports_op", ggml_op_name(node->op));
-            return GGML_STATUS_FAILED;
-        }
-        b200_node n;
-        memset(&n, 0, sizeof(n));
-        if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || (node->src[1] && !to_b200(node->src[1], &n.src1, B200_OP_NONE)) || !to_b200(node, &n.dst, op)) {
-            B200_ERR("graph_compute: node %s has a layout supports_op declines", node->name);
-            return GGML_STATUS_FAILED;
-        }
-        c->nodes.push_back(n);
+        fp_tensor(fp, node); fp_tensor(fp, node->src[0]); fp_tensor(fp, node->src[1]); fp_tensor(fp, node->src[2]);
+        uint64_t prm[2]; memcpy(prm, node->op_params, sizeof(prm));
+        fp.push_back(prm[0]); fp.push_back(prm[1]);
     }
-    if (c->nodes.empty()) return GGML_STATUS_SUCCESS;
+    if (fp.empty()) return GGML_STATUS_SUCCESS;
+    b200_graph_entry & e = c->graphs[cgraph];
+    e.last_use = ++c->tick;
+    if (e.fp != fp) {
+        e.nodes.clear();
+        for (int i = 0; i < cgraph->n_nodes; i++) {
+            ggml_tensor * node = cgraph->nodes[i];
+            if (is_view_op(node->op) || ggml_is_empty(node)) continue;
+            const int op = b200_op_of(node);
+            if (op < 0) {
+                B200_ERR("graph_compute: op %s was never admitted by supports_op", ggml_op_name(node->op));
+                c->graphs.erase(cgraph);
+                return GGML_STATUS_FAILED;
+            }
+            b200_node n;
+            memset(&n, 0, sizeof(n));
+            if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || (node->src[1] && !to_b200(node->src[1], &n.src1, B200_OP_NONE)) || !to_b200(node, &n.dst, op)) {
+                B200_ERR("graph_compute: node %s has a layout supports_op declines", node->name);
+                c->graphs.erase(cgraph);
+                return GGML_STATUS_FAILED;
+            }
+            e.nodes.push_back(n);
+        }
+        e.fp = fp;
+        e.key = g_graph_key.fetch_add(1);          // a new key per distinct list: the op layer's caches never see one key with two lists
+        if (c->graphs.size() > 512) {              // (a scheduler keeps a few dozen split graphs alive; drop the oldest half beyond that)
+            std::vector<std::pair<uint64_t, const ggml_cgraph *>> age;
+            for (auto & kv : c->graphs) age.push_back({kv.second.last_use, kv.first});
+            std::sort(age.begin(), age.end());
+            for (size_t i = 0; i < age.size() / 2; i++) if (age[i].second != cgraph) c->graphs.erase(age[i].second);
+        }
+    }
+    b200_graph_entry & g = c->graphs[cgraph];
     // long node lists (a decode step) are captured once as a CUDA graph and replayed; short ones are launched directly
     static const int graph_min = getenv("GGML_B200_GRAPH_MIN") ? atoi(getenv("GGML_B200_GRAPH_MIN")) : 8;
     DEV_LOCK(c->dev);
-    const int rc = b200_graph_compute(dev_session(c->dev), c->nodes.data(), (int32_t) c->nodes.size(), (int) c->nodes.size() >= graph_min);
+    const int rc = b200_graph_compute_keyed(dev_session(c->dev), g.nodes.data(), (int32_t) g.nodes.size(), (int) g.nodes.size() >= graph_min, g.key);
     if (rc == B200_ENOMEM) return GGML_STATUS_ALLOC_FAILED;
     if (rc) { B200_ERR("graph_compute: %s", b200_last_error()); return GGML_STATUS_FAILED; }
     return GGML_STATUS_SUCCESS;

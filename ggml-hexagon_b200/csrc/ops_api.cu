@@ -62,7 +62,7 @@ static int nccl_load() {
 #define NC(call) do { int r_ = (call); if (r_ != 0) return fail(B200_ENCCL, "%s -> %s", #call, g_nccl.GetErrorString(r_)); } while (0)
 
 // ------------------------------------------------------------------------------------------------ context
-struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; };
+struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; int32_t n_nodes = 0; uint64_t check = 0; /* second, independent hash of the node list */ };
 // a node list compiled for the decode stream kernel (decode_stream.cu); dev == nullptr: not compilable, use the graph path
 struct StreamProgram { DsStage * dev = nullptr; uint32_t * counters = nullptr; int nstages = 0; uint32_t epoch = 0; int type_mask = 0; };
 
@@ -1087,6 +1087,13 @@ static uint64_t fnv1a(const void * p, size_t n, uint64_t hsh = 14695981039346656
     return hh;
 }
 
+static thread_local uint64_t g_caller_key = 0;     // b200_graph_compute_keyed: the caller vouches that this key names exactly this node list
+extern "C" int b200_graph_compute_keyed(b200_handle h, const b200_node * nodes, int32_t n, int32_t use_cuda_graph, uint64_t key) {
+    g_caller_key = key;
+    const int rc = b200_graph_compute(h, nodes, n, use_cuda_graph);
+    g_caller_key = 0;
+    return rc;
+}
 extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n, int32_t use_cuda_graph) {
     CTX(h);
     if (n < 0 || (n > 0 && !nodes)) return fail(B200_EINVAL, "bad node list");
@@ -1109,7 +1116,12 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
             if (nodes[i].dst.op == B200_OP_MUL_MAT) { rc = presize_gemm(c, &nodes[i].src0, &nodes[i].src1); if (rc) return rc; }
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
 
-    const uint64_t key = fnv1a(nodes, sizeof(b200_node) * (size_t) n, fnv1a(&c->scratch_gen, sizeof(c->scratch_gen))) ^ (c->rs_on ? 0x9e3779b97f4a7c15ull : 0);
+    // cache key: the caller's (b200_graph_compute_keyed) or a hash of the whole list; a hit on a hashed key is confirmed by the node
+    // count and a second, independent hash before anything captured for another list could be replayed
+    const uint64_t salt = fnv1a(&c->scratch_gen, sizeof(c->scratch_gen)) ^ (c->rs_on ? 0x9e3779b97f4a7c15ull : 0);
+    const bool keyed = g_caller_key != 0;
+    const uint64_t key = keyed ? (g_caller_key * 0x9e3779b97f4a7c15ull) ^ salt ^ 0x5bd1e995 : fnv1a(nodes, sizeof(b200_node) * (size_t) n, salt);
+    const uint64_t check = keyed ? g_caller_key : fnv1a(nodes, sizeof(b200_node) * (size_t) n, 0x243f6a8885a308d3ull);
     // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
     // opt-in while it is slower than the CUDA-graph replay of the per-node kernels (DESIGN.md has the trace numbers)
     static const bool stream_on = getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) != 0;
@@ -1157,6 +1169,9 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     }
     if (use_cuda_graph == 3) return fail(B200_ENOTSUP, "graph_compute: this node list does not compile to the decode stream kernel");
     auto it = c->graphs.find(key);
+    if (it != c->graphs.end() && (it->second.n_nodes != n || it->second.check != check)) {        // key collision: never replay another list's graph
+        cudaGraphExecDestroy(it->second.exec); c->graphs.erase(it); it = c->graphs.end();
+    }
     if (it == c->graphs.end()) {
         const int64_t before = c->launches;
         CU(cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal));
@@ -1169,7 +1184,7 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         c->launches = before;
         if (rc) { if (g) cudaGraphDestroy(g); return rc; }
         if (e != cudaSuccess) return fail(B200_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
-        GraphEntry ge; ge.n_kernels = captured;
+        GraphEntry ge; ge.n_kernels = captured; ge.n_nodes = n; ge.check = check;
         e = cudaGraphInstantiate(&ge.exec, g, 0);
         cudaGraphDestroy(g);
         if (e != cudaSuccess) return fail(B200_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));

@@ -112,6 +112,9 @@ B200_API int b200_mulmat(b200_handle h, const b200_tensor * src0, const b200_ten
  * use_cuda_graph = 2: CUDA-graph replay only.
  * use_cuda_graph = 3: decode stream kernel only; B200_ENOTSUP if the list does not compile to it. */
 B200_API int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph);
+/* the same, for a caller that keeps its own cache of marshalled node lists (the ggml plugin): `key` != 0 names this exact list --
+ * the caller guarantees one key never stands for two different lists -- so the library does not hash the descriptors again */
+B200_API int b200_graph_compute_keyed(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph, uint64_t key);
 B200_API int b200_synchronize(b200_handle h);
 
 /* ---- activation quantiser, exposed for parity tests (= quantize_row_q8_1_ref, ggml-quants.c:220-253)

@@ -259,9 +259,24 @@ def bench_decode(ref, layer_shapes, out_shape, n_layers_total, n_layers_sample, 
     cpu.ggml_graph_plan.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     cpu.ggml_graph_compute.restype = C.c_int
     cpu.ggml_graph_compute.argtypes = [C.c_void_p, C.POINTER(CPlan)]
+    # ONE thread pool for the whole measurement (with threadpool = NULL ggml-cpu creates and joins n_threads threads inside every
+    # ggml_graph_compute call), as llama.cpp keeps one per context
+    class TPParams(C.Structure):
+        _fields_ = [("cpumask", C.c_bool * 512), ("n_threads", C.c_int), ("prio", C.c_int), ("poll", C.c_uint32),
+                    ("strict_cpu", C.c_bool), ("paused", C.c_bool)]
+    b.ggml_threadpool_params_init.restype = None
+    b.ggml_threadpool_params_init.argtypes = [C.POINTER(TPParams), C.c_int]
+    cpu.ggml_threadpool_new.restype = C.c_void_p
+    cpu.ggml_threadpool_new.argtypes = [C.POINTER(TPParams)]
+    cpu.ggml_threadpool_free.restype = None
+    cpu.ggml_threadpool_free.argtypes = [C.c_void_p]
+    tpp = TPParams()
+    b.ggml_threadpool_params_init(C.byref(tpp), n_threads)
+    pool = cpu.ggml_threadpool_new(C.byref(tpp))
+    assert pool
     plans = []
     for gr in (g, g_out):
-        p = cpu.ggml_graph_plan(gr, n_threads, None)
+        p = cpu.ggml_graph_plan(gr, n_threads, pool)
         buf = np.empty(max(p.work_size, 16), dtype=np.uint8)
         p.work_data = buf.ctypes.data
         plans.append((gr, p, buf))
@@ -284,8 +299,9 @@ def bench_decode(ref, layer_shapes, out_shape, n_layers_total, n_layers_sample, 
         reps += 1
         if time.perf_counter() - t_start > budget_s or reps >= 200:
             break
+    cpu.ggml_threadpool_free(pool)
     b.ggml_free(ctx)
     per_token = t_layers / reps * (n_layers_total / n_layers_sample) + t_out / reps
-    desc = ("%d of %d layers (7 MUL_MAT + 2 ADD each) + output matrix, %d reps, extrapolated x%.1f on the layer part"
+    desc = ("%d of %d layers (7 MUL_MAT + 2 ADD each) + output matrix, one persistent ggml threadpool, %d reps, extrapolated x%.1f on the layer part"
             % (n_layers_sample, n_layers_total, reps, n_layers_total / n_layers_sample))
     return per_token, desc
