@@ -10,8 +10,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "lib", "libb200ops.so")     # B200_LIB: development builds
 
-F32, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K = 0, 2, 8, 9, 12, 14
-OP_NONE, OP_ADD, OP_MUL_MAT = 0, 2, 27
+F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K = 0, 1, 2, 8, 9, 12, 14
+OP_NONE, OP_ADD, OP_RMS_NORM, OP_MUL_MAT, OP_SOFT_MAX, OP_POOL_2D = 0, 2, 23, 27, 43, 53
 TENSOR_HOST, TENSOR_REPACKED = 1, 2
 BLOCK = {F32: (1, 4), Q4_0: (32, 18), Q8_0: (32, 34), Q8_1: (32, 36), Q4_K: (256, 144), Q6_K: (256, 210)}
 TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"}
@@ -19,7 +19,7 @@ TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"
 # every symbol include/ggml_b200_ops.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b200_open", "b200_close", "b200_setclocks", "b200_last_error", "b200_device_count", "b200_device_info",
-    "b200_add", "b200_mulmat", "b200_graph_compute", "b200_graph_compute_keyed", "b200_synchronize", "b200_quantize_q8_1", "b200_block_dots",
+    "b200_add", "b200_mulmat", "b200_rms_norm", "b200_soft_max", "b200_pool_2d", "b200_graph_compute", "b200_graph_compute_keyed", "b200_synchronize", "b200_quantize_q8_1", "b200_block_dots",
     "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d", "b200_memset",
     "b200_memcpy_h2d_async", "b200_memcpy_d2h_async",
     "b200_host_alloc", "b200_host_free", "b200_weights_upload", "b200_weights_download", "b200_block_elems",
@@ -67,6 +67,9 @@ def lib():
         L.b200_device_info.argtypes = [C.c_int, C.c_char_p, C.c_int, C.POINTER(I64), C.POINTER(I64), C.POINTER(I32)]
         L.b200_add.argtypes = [H, TP, TP, TP]
         L.b200_mulmat.argtypes = [H, TP, TP, TP]
+        L.b200_rms_norm.argtypes = [H, TP, TP]
+        L.b200_soft_max.argtypes = [H, TP, TP, TP]
+        L.b200_pool_2d.argtypes = [H, TP, TP]
         L.b200_mulmat_rowsplit.argtypes = [H, TP, TP, TP]
         L.b200_graph_compute.argtypes = [H, C.POINTER(Node), I32, I32]
         L.b200_synchronize.argtypes = [H]
@@ -324,6 +327,64 @@ class Session:
         out = self.to_host(db, a.shape, np.float32)
         for x in (ab, bb, db):
             x.free()
+        return out
+
+    def rms_norm(self, x, eps):
+        """x: float32 numpy order [..., ne00]"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        xb, db = self.to_device(x), self.malloc(max(x.nbytes, 16))
+        ne = list(x.shape[::-1])
+        s, d = f32_tensor(xb.ptr, ne), f32_tensor(db.ptr, ne, op=OP_RMS_NORM)
+        d.op_params[0] = int(np.float32(eps).view(np.int32))
+        _ck(lib().b200_rms_norm(self.h, C.byref(s), C.byref(d)))
+        out = self.to_host(db, x.shape, np.float32)
+        xb.free(); db.free()
+        return out
+
+    def soft_max(self, x, mask=None, scale=1.0, max_bias=0.0):
+        """x: float32 [ne03, ne02, ne01, ne00] (numpy order); mask: float32 or float16 [>= ne01, ne00] or None"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        xb, db = self.to_device(x), self.malloc(max(x.nbytes, 16))
+        ne = list(x.shape[::-1])
+        s, d = f32_tensor(xb.ptr, ne), f32_tensor(db.ptr, ne, op=OP_SOFT_MAX)
+        d.op_params[0] = int(np.float32(scale).view(np.int32))
+        d.op_params[1] = int(np.float32(max_bias).view(np.int32))
+        mb, mt = None, None
+        if mask is not None:
+            mask = np.ascontiguousarray(mask)
+            assert mask.dtype in (np.float32, np.float16)
+            mb = self.to_device(mask)
+            es = mask.dtype.itemsize
+            mt = Tensor()
+            mt.type = F32 if es == 4 else F16
+            mt.ne[:] = [mask.shape[1], mask.shape[0], 1, 1]
+            mt.nb[:] = [es, es * mask.shape[1], mask.nbytes, mask.nbytes]
+            mt.data, mt.data_len = mb.ptr, mask.nbytes
+        _ck(lib().b200_soft_max(self.h, C.byref(s), C.byref(mt) if mt is not None else None, C.byref(d)))
+        out = self.to_host(db, x.shape, np.float32)
+        for b in (xb, db, mb):
+            if b is not None:
+                b.free()
+        return out
+
+    def pool_2d(self, x, op, k0, k1, s0, s1, p0, p1):
+        """x: float32 or float16 [ne3, ne2, ne1, ne0] -> float32 [ne3, ne2, py, px]; op 0 = max, 1 = avg"""
+        x = np.ascontiguousarray(x)
+        ne3, ne2, ne1, ne0 = x.shape
+        px, py = (ne0 + 2 * p0 - k0) // s0 + 1, (ne1 + 2 * p1 - k1) // s1 + 1
+        xb, db = self.to_device(x), self.malloc(4 * ne3 * ne2 * px * py + 16)
+        es = x.dtype.itemsize
+        s = Tensor()
+        s.type = F32 if es == 4 else F16
+        s.ne[:] = [ne0, ne1, ne2, ne3]
+        s.nb[:] = [es, es * ne0, es * ne0 * ne1, es * ne0 * ne1 * ne2]
+        s.data, s.data_len = xb.ptr, x.nbytes
+        d = f32_tensor(db.ptr, [px, py, ne2, ne3], op=OP_POOL_2D)
+        for i, v in enumerate((op, k0, k1, s0, s1, p0, p1)):
+            d.op_params[i] = int(v)
+        _ck(lib().b200_pool_2d(self.h, C.byref(s), C.byref(d)))
+        out = self.to_host(db, (ne3, ne2, py, px), np.float32)
+        xb.free(); db.free()
         return out
 
     def quantize_q8_1(self, x):

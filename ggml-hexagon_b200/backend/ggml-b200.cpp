@@ -132,13 +132,36 @@ static bool b200_supports_add(const ggml_tensor * op) {
     if (!ggml_are_same_shape(a, op) || !ggml_can_repeat(b, a)) return false;
     return true;
 }
+// The three ops the hexagon caps table lists next to ADD / MUL_MAT without a kernel behind them (ggml-hexagon.cpp:619, 639, 649;
+// empty stubs ggmlop_dsp_rmsnorm / _softmax / _pool2d, kernels/ggml-dsp.c:1353-1372): admitted here in the layouts ggml-cpu itself
+// asserts (ggml-cpu.c:6260-6262, 8268-8269, 9764)
+static bool b200_supports_rms_norm(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    return a && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ggml_are_same_shape(a, op) && a->nb[0] == sizeof(float) && op->nb[0] == sizeof(float);
+}
+static bool b200_supports_soft_max(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0]; const ggml_tensor * m = op->src[1];
+    if (!a || a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || !ggml_are_same_shape(a, op) || !ggml_is_contiguous(a) || !ggml_is_contiguous(op)) return false;
+    if (m && !((m->type == GGML_TYPE_F32 || m->type == GGML_TYPE_F16) && ggml_is_contiguous(m) && m->ne[0] == a->ne[0] && m->ne[1] >= a->ne[1])) return false;
+    return true;
+}
+static bool b200_supports_pool_2d(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0];
+    if (!a || !(a->type == GGML_TYPE_F32 || a->type == GGML_TYPE_F16) || op->type != GGML_TYPE_F32 || !ggml_is_contiguous(op)) return false;
+    const int32_t * o = op->op_params;
+    if (o[0] != GGML_OP_POOL_MAX && o[0] != GGML_OP_POOL_AVG) return false;
+    return a->nb[0] == ggml_type_size(a->type) && a->nb[3] == a->nb[2] * (size_t) a->ne[2];
+}
 static bool b200_device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
     switch (op->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
             return true;
-        case GGML_OP_ADD:     return b200_supports_add(op);
-        case GGML_OP_MUL_MAT: return b200_supports_mul_mat(op);
-        default:              return false;
+        case GGML_OP_ADD:      return b200_supports_add(op);
+        case GGML_OP_MUL_MAT:  return b200_supports_mul_mat(op);
+        case GGML_OP_RMS_NORM: return b200_supports_rms_norm(op);
+        case GGML_OP_SOFT_MAX: return b200_supports_soft_max(op);
+        case GGML_OP_POOL_2D:  return b200_supports_pool_2d(op);
+        default:               return false;
     }
 }
 
@@ -271,6 +294,9 @@ static int b200_op_of(const ggml_tensor * node) {
     switch (node->op) {
         case GGML_OP_ADD:      return B200_OP_ADD;
         case GGML_OP_MUL_MAT:  return B200_OP_MUL_MAT;
+        case GGML_OP_RMS_NORM: return B200_OP_RMS_NORM;
+        case GGML_OP_SOFT_MAX: return B200_OP_SOFT_MAX;
+        case GGML_OP_POOL_2D:  return B200_OP_POOL_2D;
         default:               return -1;
     }
 }

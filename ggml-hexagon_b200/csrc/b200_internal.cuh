@@ -7,7 +7,7 @@
 
 namespace b200 {
 
-enum : int { T_F32 = 0, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q6_K = 14 };
+enum : int { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q6_K = 14 };
 
 // ---------------------------------------------------------------- HBM layout of quantised weights
 // A weight allocation of T blocks keeps the native byte count (T * block_bytes) but stores the
@@ -204,6 +204,11 @@ struct AddArgs {
     int64_t nba[4], nbb[4], nbd[4];   // byte strides
 };
 cudaError_t launch_add_f32(const AddArgs & a, cudaStream_t st);
+
+// ---- norm_ops.cu: RMS_NORM / SOFT_MAX / POOL_2D (ne, nb: ggml order, bytes)
+cudaError_t launch_rms_norm_f32(const void * x, void * y, const int64_t * ne, const int64_t * nb_src, const int64_t * nb_dst, float eps, cudaStream_t st);
+cudaError_t launch_soft_max_f32(const float * x, const void * mask, bool mask_f16, float * y, const int64_t * ne, float scale, float max_bias, cudaStream_t st);
+cudaError_t launch_pool_2d(const void * x, bool src_f16, float * y, const int64_t * ne, const int64_t * nb, int64_t px, int64_t py, const int32_t * opts, cudaStream_t st);
 
 cudaError_t launch_repack(int type, bool to_soa, uint8_t * soa_base, int64_t T, int64_t first, int64_t n,
                           uint8_t * native, cudaStream_t st);

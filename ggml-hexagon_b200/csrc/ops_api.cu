@@ -388,6 +388,68 @@ static int add_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ RMS_NORM / SOFT_MAX / POOL_2D
+static float f32_param(const b200_tensor * t, int i) { float f; memcpy(&f, &t->op_params[i], 4); return f; }
+static int rms_norm_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
+    if (s->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "rms_norm: f32 only");
+    for (int i = 0; i < 4; i++) if (s->ne[i] != d->ne[i]) return fail(B200_EINVAL, "rms_norm: src and dst shapes differ");
+    if (s->nb[0] != 4 || d->nb[0] != 4) return fail(B200_ENOTSUP, "rms_norm: rows must be contiguous");
+    const float eps = f32_param(d, 0);
+    if (!(eps >= 0.0f)) return fail(B200_EINVAL, "rms_norm: eps < 0");
+    CU(launch_rms_norm_f32(s->data, d->data, s->ne, s->nb, d->nb, eps, c->st)); c->launches++;
+    c->q_ptr = nullptr;
+    return 0;
+}
+static bool contiguous_f32_t(const b200_tensor * t) {
+    int64_t st = 4;
+    for (int i = 0; i < 4; i++) { if (t->ne[i] != 1 && t->nb[i] != st) return false; st *= t->ne[i]; }
+    return true;
+}
+static int soft_max_dev(Ctx * c, const b200_tensor * s, const b200_tensor * m, b200_tensor * d) {
+    if (s->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "soft_max: f32 only");
+    for (int i = 0; i < 4; i++) if (s->ne[i] != d->ne[i]) return fail(B200_EINVAL, "soft_max: src and dst shapes differ");
+    if (!contiguous_f32_t(s) || !contiguous_f32_t(d)) return fail(B200_ENOTSUP, "soft_max: src and dst must be contiguous");
+    const bool has_mask = m && m->data;
+    if (has_mask) {
+        if (m->type != T_F32 && m->type != T_F16) return fail(B200_ENOTSUP, "soft_max: mask must be f32 or f16");
+        const int64_t es = m->type == T_F16 ? 2 : 4;
+        if (m->ne[0] != s->ne[0] || m->ne[1] < s->ne[1] || m->nb[0] != es || m->nb[1] != es * m->ne[0]) return fail(B200_EINVAL, "soft_max: mask must be a contiguous [ne00, >= ne01] matrix");
+    }
+    CU(launch_soft_max_f32((const float *) s->data, has_mask ? m->data : nullptr, has_mask && m->type == T_F16, (float *) d->data, s->ne,
+                           f32_param(d, 0), f32_param(d, 1), c->st)); c->launches++;
+    c->q_ptr = nullptr;
+    return 0;
+}
+static int pool_2d_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
+    if ((s->type != T_F32 && s->type != T_F16) || d->type != T_F32) return fail(B200_ENOTSUP, "pool_2d: f32 / f16 in, f32 out");
+    const int32_t * o = d->op_params;
+    if ((o[0] != 0 && o[0] != 1) || o[1] <= 0 || o[2] <= 0 || o[3] <= 0 || o[4] <= 0 || o[5] < 0 || o[6] < 0) return fail(B200_EINVAL, "pool_2d: bad parameters");
+    const int64_t es = s->type == T_F16 ? 2 : 4;
+    if (s->nb[0] != es || s->nb[3] != s->nb[2] * s->ne[2]) return fail(B200_ENOTSUP, "pool_2d: src planes must be evenly strided");
+    if (!contiguous_f32_t(d) || d->ne[2] != s->ne[2] || d->ne[3] != s->ne[3]) return fail(B200_EINVAL, "pool_2d: dst must be contiguous [px, py, ne2, ne3]");
+    CU(launch_pool_2d(s->data, s->type == T_F16, (float *) d->data, s->ne, s->nb, d->ne[0], d->ne[1], o, c->st)); c->launches++;
+    c->q_ptr = nullptr;
+    return 0;
+}
+static bool any_host(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
+    return ((a ? a->flags : 0) | (b ? b->flags : 0) | (d ? d->flags : 0)) & B200_TENSOR_HOST;
+}
+extern "C" int b200_rms_norm(b200_handle h, const b200_tensor * s, b200_tensor * d) {
+    CTX(h); if (!s || !d) return fail(B200_EINVAL, "NULL tensor");
+    if (any_host(s, nullptr, d)) return fail(B200_ENOTSUP, "rms_norm takes device tensors only");
+    return rms_norm_dev(c, s, d);
+}
+extern "C" int b200_soft_max(b200_handle h, const b200_tensor * s, const b200_tensor * m, b200_tensor * d) {
+    CTX(h); if (!s || !d) return fail(B200_EINVAL, "NULL tensor");
+    if (any_host(s, m, d)) return fail(B200_ENOTSUP, "soft_max takes device tensors only");
+    return soft_max_dev(c, s, m, d);
+}
+extern "C" int b200_pool_2d(b200_handle h, const b200_tensor * s, b200_tensor * d) {
+    CTX(h); if (!s || !d) return fail(B200_EINVAL, "NULL tensor");
+    if (any_host(s, nullptr, d)) return fail(B200_ENOTSUP, "pool_2d takes device tensors only");
+    return pool_2d_dev(c, s, d);
+}
+
 // ------------------------------------------------------------------------------------------------ MUL_MAT
 static int mulmat_check(const b200_tensor * s0, const b200_tensor * s1, const b200_tensor * d) {
     if (s1->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "mulmat: src1 and dst must be f32");
@@ -1037,6 +1099,9 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
         switch (d.op) {
             case B200_OP_NONE: break;
             case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_RMS_NORM: rc = rms_norm_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_SOFT_MAX: rc = soft_max_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_POOL_2D:  rc = pool_2d_dev(c, &nodes[i].src0, &d); break;
             case B200_OP_MUL_MAT: {
                 FusedAdd fa;
                 const int gl = fuse ? group_len(nodes, i, n) : 1;

@@ -26,6 +26,7 @@ extern "C" {
 /* tensor element types: numeric values of enum ggml_type (ggml/include/ggml.h:349-390) */
 enum b200_type {
     B200_TYPE_F32  = 0,
+    B200_TYPE_F16  = 1,   /* SOFT_MAX mask, POOL_2D input only */
     B200_TYPE_Q4_0 = 2,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
@@ -36,9 +37,12 @@ enum b200_type {
 /* ops: numeric values of enum ggml_op for the two ops the cDSP path offloads
  * (ggml-hexagon.cpp:5079-5098; ggml/include/ggml.h:426-, GGML_OP_ADD = 2, GGML_OP_MUL_MAT = 27) */
 enum b200_op {
-    B200_OP_NONE    = 0,
-    B200_OP_ADD     = 2,
-    B200_OP_MUL_MAT = 27,
+    B200_OP_NONE     = 0,
+    B200_OP_ADD      = 2,
+    B200_OP_RMS_NORM = 23,   /* the three ops the cDSP table lists and leaves as stubs (ggml-hexagon.cpp:619,639,649; ggml-dsp.c:1353-1372) */
+    B200_OP_MUL_MAT  = 27,
+    B200_OP_SOFT_MAX = 43,
+    B200_OP_POOL_2D  = 53,
 };
 
 enum b200_err {
@@ -103,6 +107,16 @@ B200_API int b200_add(b200_handle h, const b200_tensor * src0, const b200_tensor
  * src0: q4_0/q8_0/q4_K/q6_K REPACKED device weights, or f32; src1, dst: f32. Asynchronous on the handle's stream
  * unless a tensor carries B200_TENSOR_HOST (then the call returns after dst is back in host memory). */
 B200_API int b200_mulmat(b200_handle h, const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst);
+/* ---- the ops ggml-hexagon lists beside them without an implementation (ggmlop_dsp_rmsnorm / _softmax / _pool2d, ggml-dsp.c:1353-1372);
+ *      device tensors only; parameters travel in dst->op_params exactly as in ggml_tensor.op_params
+ * RMS_NORM: y = x / sqrt(mean(x^2) + eps) per row, f32, src nb[0] = 4 (ggml-cpu.c:6254-6300); eps = op_params[0] (float bits) */
+B200_API int b200_rms_norm(b200_handle h, const b200_tensor * src, b200_tensor * dst);
+/* SOFT_MAX(x * scale + slope(head) * mask) per row; x, dst contiguous f32; mask NULL, f32 or f16 [ne00, >= ne01] (ggml-cpu.c:8261-8357);
+ * scale = op_params[0], max_bias = op_params[1] (float bits) */
+B200_API int b200_soft_max(b200_handle h, const b200_tensor * src, const b200_tensor * mask, b200_tensor * dst);
+/* POOL_2D max / average over [ne0, ne1] planes, f32 or f16 in, f32 out (ggml-cpu.c:9758-9830); op_params[0..6] = op, k0, k1, s0, s1, p0, p1 */
+B200_API int b200_pool_2d(b200_handle h, const b200_tensor * src, b200_tensor * dst);
+
 /* a whole node list in one call (graph_compute, ggml-hexagon.cpp:5555-5574); asynchronous.
  * use_cuda_graph = 0: one launch per node (fused where adjacent nodes allow).
  * use_cuda_graph = 1: replayable fast path, cached per distinct node list: the per-node launches are captured once as a

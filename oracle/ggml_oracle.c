@@ -422,3 +422,73 @@ void oracle_add_f32(const float *a, const float *b, float *dst, const int64_t ne
         for (int64_t i0 = 0; i0 < ne0[0]; i0++) dst[ra + i0] = a[ra + i0] + b[rb + i0 % ne1[0]];
     }
 }
+
+/* ------------------------------------------------------------------ RMS_NORM */
+/* ggml_compute_forward_rms_norm_f32 (ggml-cpu/ggml-cpu.c:6254-6300); the op ggml-hexagon lists at ggml-hexagon.cpp:619 and leaves
+ * as an empty stub in kernels/ggml-dsp.c:1353-1372.  Per row of ne00 floats: sum of squares of the f32 products in double,
+ * mean = (float) (sum / ne00), scale = 1 / sqrtf(mean + eps), y = x * scale (ggml_vec_scale_f32). */
+void oracle_rms_norm_f32(const float *x, float *y, int64_t ne00, int64_t nrows, float eps) {
+    for (int64_t r = 0; r < nrows; r++) {
+        const float *xr = x + r * ne00; float *yr = y + r * ne00;
+        double sum = 0.0;
+        for (int64_t i = 0; i < ne00; i++) sum += (double) (xr[i] * xr[i]);
+        const float mean = (float) (sum / (double) ne00);
+        const float scale = 1.0f / sqrtf(mean + eps);
+        for (int64_t i = 0; i < ne00; i++) yr[i] = xr[i] * scale;
+    }
+}
+
+/* ------------------------------------------------------------------ SOFT_MAX */
+/* ggml_compute_forward_soft_max_f32 (ggml-cpu/ggml-cpu.c:8261-8357) with the scalar ggml_vec_soft_max_f32: per row of src0
+ * [ne00, ne01, ne02, ne03]: wp = x * scale + slope * mask[row % ne01]  (mask: f32 [ne00, >= ne01], optional; ALiBi slope from max_bias
+ * and the head index (row / ne01) % ne02), max, val = expf(wp - max), sum of the vals in double, y = val * (float) (1 / sum). */
+void oracle_soft_max_f32(const float *x, const float *mask, float *y, int64_t ne00, int64_t ne01, int64_t ne02, int64_t ne03,
+                         float scale, float max_bias) {
+    const uint32_t n_head = (uint32_t) ne02;
+    const uint32_t n_head_log2 = 1u << (uint32_t) floor(log2((double) n_head));
+    const float m0 = powf(2.0f, -(max_bias) / n_head_log2);
+    const float m1 = powf(2.0f, -(max_bias / 2.0f) / n_head_log2);
+    const int64_t nr = ne01 * ne02 * ne03;
+    float *wp = (float *) malloc(sizeof(float) * (size_t) (ne00 > 0 ? ne00 : 1));
+    for (int64_t i1 = 0; i1 < nr; i1++) {
+        const uint32_t h = (uint32_t) ((i1 / ne01) % ne02);
+        const float slope = (max_bias > 0.0f) ? (h < n_head_log2 ? powf(m0, h + 1) : powf(m1, 2 * (h - n_head_log2) + 1)) : 1.0f;
+        const float *sp = x + i1 * ne00; float *dp = y + i1 * ne00;
+        const float *mp = mask ? mask + (i1 % ne01) * ne00 : NULL;
+        for (int64_t i = 0; i < ne00; i++) wp[i] = sp[i] * scale;
+        if (mp) for (int64_t i = 0; i < ne00; i++) wp[i] += slope * mp[i];
+        float max = -INFINITY;
+        for (int64_t i = 0; i < ne00; i++) if (wp[i] > max) max = wp[i];
+        double sum = 0.0;
+        for (int64_t i = 0; i < ne00; i++) { const float v = expf(wp[i] - max); sum += (double) v; dp[i] = v; }
+        const float inv = (float) (1.0 / sum);
+        for (int64_t i = 0; i < ne00; i++) dp[i] *= inv;
+    }
+    free(wp);
+}
+
+/* ------------------------------------------------------------------ POOL_2D */
+/* ggml_compute_forward_pool_2d (ggml-cpu/ggml-cpu.c:9758-9830), f32 input: for every plane [ne00, ne01] of src (ne02 * ne03 of them) and
+ * every output (ox, oy): op 0 = max (start -FLT_MAX), op 1 = average: sum in ky-outer / kx-inner order of the taps inside the input,
+ * divided by k0 * k1 (padding taps count in the divisor).  Output plane [px, py]. */
+void oracle_pool_2d_f32(const float *x, float *y, const int64_t ne[4], int64_t px, int64_t py, int op, int k0, int k1, int s0, int s1, int p0, int p1) {
+    const int64_t planes = ne[2] * ne[3];
+    for (int64_t pl = 0; pl < planes; pl++) {
+        const float *src = x + pl * ne[0] * ne[1]; float *dst = y + pl * px * py;
+        for (int64_t oy = 0; oy < py; oy++) for (int64_t ox = 0; ox < px; ox++) {
+            float out = op == 1 ? 0.0f : -3.402823466e+38f;
+            const int64_t ix = -p0 + ox * s0, iy = -p1 + oy * s1;
+            for (int ky = 0; ky < k1; ky++) {
+                if (iy + ky < 0 || iy + ky >= ne[1]) continue;
+                for (int kx = 0; kx < k0; kx++) {
+                    const int64_t j = ix + kx;
+                    if (j < 0 || j >= ne[0]) continue;
+                    const float v = src[(iy + ky) * ne[0] + j];
+                    if (op == 1) out += v; else if (v > out) out = v;
+                }
+            }
+            if (op == 1) out /= (float) (k0 * k1);
+            dst[oy * px + ox] = out;
+        }
+    }
+}

@@ -150,3 +150,35 @@ def random_blocks(t, rows, k, rng, scale=1.0):
     else:
         raise ValueError(t)
     return raw.reshape(rows, nb * by)
+
+
+def rms_norm(x, eps):
+    """x: float32 [..., ne00] -> same shape (ggml_compute_forward_rms_norm_f32)"""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    y = np.empty_like(x)
+    lib().oracle_rms_norm_f32(_p(x), _p(y), C.c_int64(x.shape[-1]), C.c_int64(x.size // max(x.shape[-1], 1)), C.c_float(eps))
+    return y
+
+
+def soft_max(x, mask=None, scale=1.0, max_bias=0.0):
+    """x: float32 numpy order [ne03, ne02, ne01, ne00]; mask: float32 [>= ne01, ne00] or None (ggml_compute_forward_soft_max_f32)"""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    x4 = x.reshape((1,) * (4 - x.ndim) + x.shape)
+    y = np.empty_like(x4)
+    m = None if mask is None else np.ascontiguousarray(mask, dtype=np.float32)
+    ne3, ne2, ne1, ne0 = x4.shape
+    lib().oracle_soft_max_f32(_p(x4), _p(m) if m is not None else None, _p(y), C.c_int64(ne0), C.c_int64(ne1), C.c_int64(ne2), C.c_int64(ne3),
+                              C.c_float(scale), C.c_float(max_bias))
+    return y.reshape(x.shape)
+
+
+def pool_2d(x, op, k0, k1, s0, s1, p0, p1):
+    """x: float32 numpy order [ne3, ne2, ne1, ne0]; op 0 = max, 1 = avg -> [ne3, ne2, py, px] (ggml_compute_forward_pool_2d)"""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    ne3, ne2, ne1, ne0 = x.shape
+    px = (ne0 + 2 * p0 - k0) // s0 + 1
+    py = (ne1 + 2 * p1 - k1) // s1 + 1
+    y = np.empty((ne3, ne2, py, px), dtype=np.float32)
+    ne = np.array([ne0, ne1, ne2, ne3], dtype=np.int64)
+    lib().oracle_pool_2d_f32(_p(x), _p(y), _p(ne), C.c_int64(px), C.c_int64(py), int(op), int(k0), int(k1), int(s0), int(s1), int(p0), int(p1))
+    return y

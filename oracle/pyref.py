@@ -191,6 +191,59 @@ class Ref:
         return out.reshape(a.shape)
 
 
+def _unary_graph(ref, x4, build):
+    """run one op on ggml-cpu: x4 float32 [ne3, ne2, ne1, ne0] -> output array of the op's shape"""
+    b = ref.base
+    ctx = ref._ctx(8 * x4.nbytes + (64 << 20))
+    ta = b.ggml_new_tensor_4d(ctx, F32, *x4.shape[::-1])
+    C.memmove(b.ggml_get_data(ta), x4.ctypes.data, x4.nbytes)
+    td = build(ctx, ta)
+    g = b.ggml_new_graph(ctx)
+    b.ggml_build_forward_expand(g, td)
+    assert ref.cpu.ggml_graph_compute_with_ctx(ctx, g, 1) == 0
+    n = b.ggml_nbytes(td) // 4
+    out = np.empty(n, dtype=np.float32)
+    C.memmove(out.ctypes.data, b.ggml_get_data(td), 4 * n)
+    b.ggml_free(ctx)
+    return out
+
+
+def ref_rms_norm(ref, x, eps):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    x4 = x.reshape((1,) * (4 - x.ndim) + x.shape)
+    b = ref.base
+    b.ggml_rms_norm.restype = C.c_void_p
+    b.ggml_rms_norm.argtypes = [C.c_void_p, C.c_void_p, C.c_float]
+    return _unary_graph(ref, x4, lambda ctx, ta: b.ggml_rms_norm(ctx, ta, eps)).reshape(x.shape)
+
+
+def ref_soft_max(ref, x, mask=None, scale=1.0, max_bias=0.0):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    x4 = x.reshape((1,) * (4 - x.ndim) + x.shape)
+    b = ref.base
+    b.ggml_soft_max_ext.restype = C.c_void_p
+    b.ggml_soft_max_ext.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float]
+
+    def build(ctx, ta):
+        tm = None
+        if mask is not None:
+            m = np.ascontiguousarray(mask, dtype=np.float32)
+            tm = b.ggml_new_tensor_2d(ctx, F32, m.shape[1], m.shape[0])
+            C.memmove(b.ggml_get_data(tm), m.ctypes.data, m.nbytes)
+        return b.ggml_soft_max_ext(ctx, ta, tm, scale, max_bias)
+    return _unary_graph(ref, x4, build).reshape(x.shape)
+
+
+def ref_pool_2d(ref, x, op, k0, k1, s0, s1, p0, p1):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    b = ref.base
+    b.ggml_pool_2d.restype = C.c_void_p
+    b.ggml_pool_2d.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float]
+    ne3, ne2, ne1, ne0 = x.shape
+    px, py = (ne0 + 2 * p0 - k0) // s0 + 1, (ne1 + 2 * p1 - k1) // s1 + 1
+    return _unary_graph(ref, x, lambda ctx, ta: b.ggml_pool_2d(ctx, ta, op, k0, k1, s0, s1, float(p0), float(p1))).reshape(ne3, ne2, py, px)
+
+
 def bench_decode(ref, layer_shapes, out_shape, n_layers_total, n_layers_sample, wtype, n_threads, budget_s=15.0, seed=7):
     """Timed CPU baseline: the reference's ggml-cpu runs the decode MUL_MAT/ADD node list (batch 1) of
     `n_layers_sample` layers (+ the output matrix), all `n_threads` host threads, repeated until `budget_s`.

@@ -43,3 +43,32 @@ b = rng.standard_normal((1, 3, 1, 64)).astype(np.float32)
 out["add_a"], out["add_b"], out["add_out"] = a, b, R.add(a, b)
 np.savez_compressed(os.path.join(HERE, "ref_scalar.npz"), **out)
 print("wrote", os.path.join(HERE, "ref_scalar.npz"), {k: v.shape for k, v in out.items()})
+
+# ---- the ops ggml-hexagon lists but leaves as stubs: RMS_NORM, SOFT_MAX, POOL_2D on ggml-cpu
+ops = {}
+rng = np.random.default_rng(20251105)
+x = rng.standard_normal((3, 4, 5, 64)).astype(np.float32)
+x[0, 0, 0] = 0.0                                    # an all-zero row: scale = 1 / sqrt(eps)
+x[0, 0, 1] *= 1e4
+ops["rms_x"] = x
+ops["rms_out_eps1e-6"] = pyref.ref_rms_norm(R, x, 1e-6)
+ops["rms_out_eps0"] = pyref.ref_rms_norm(R, x[1:], 0.0)
+xl = rng.standard_normal((2, 4096)).astype(np.float32)
+ops["rms_xl"], ops["rms_outl"] = xl, pyref.ref_rms_norm(R, xl, 1e-5)
+s = rng.standard_normal((2, 8, 5, 77)).astype(np.float32) * 3
+m = rng.standard_normal((5, 77)).astype(np.float32)
+m[m > 1.0] = -np.inf                                # causal-mask style -inf entries
+ops["sm_x"], ops["sm_mask"] = s, m
+ops["sm_plain"] = pyref.ref_soft_max(R, s, None, 1.0, 0.0)
+ops["sm_mask_scale"] = pyref.ref_soft_max(R, s, m, 0.1, 0.0)
+ops["sm_alibi"] = pyref.ref_soft_max(R, s, m, 0.1, 8.0)
+sl = rng.standard_normal((1, 1, 3, 4100)).astype(np.float32)
+ops["sm_xl"], ops["sm_outl"] = sl, pyref.ref_soft_max(R, sl, None, 0.125, 0.0)
+p = rng.standard_normal((2, 3, 10, 11)).astype(np.float32)
+ops["pool_x"] = p
+for name, (op, k0, k1, s0, s1, p0, p1) in {"max_3311": (0, 3, 3, 1, 1, 1, 1), "avg_3322": (1, 3, 3, 2, 2, 1, 1), "avg_2321": (1, 2, 3, 2, 1, 0, 1),
+                                          "max_1122": (0, 1, 1, 2, 2, 0, 0)}.items():
+    ops["pool_" + name] = pyref.ref_pool_2d(R, p, op, k0, k1, s0, s1, p0, p1)
+    ops["poolargs_" + name] = np.array([op, k0, k1, s0, s1, p0, p1], dtype=np.int32)
+np.savez_compressed(os.path.join(HERE, "ref_scalar_ops.npz"), **ops)
+print("wrote", os.path.join(HERE, "ref_scalar_ops.npz"), {k: v.shape for k, v in ops.items()})

@@ -54,7 +54,7 @@ def test_tbo_mul_mat_through_plugin():
     assert "load_backend: loaded b200 backend" in err + out or "B200_0" in out, (out[-2000:], err[-2000:])
     ok, fail = tbo_counts(out)
     assert rc == 0 and not fail, (fail[:5], out[-1500:])
-    assert len(ok) >= 140, len(ok)
+    assert len(ok) >= 138, len(ok)           # (138 cases + the two summary lines = the 140 'OK' of the round-1 logs)
     for t in ("q4_0", "q8_0", "q4_K", "q6_K", "f32"):
         n = sum(1 for l in ok if "type_a=%s," % t in l)
         assert n >= 10, (t, n)
@@ -65,7 +65,7 @@ def test_tbo_add_through_plugin():
     rc, out, err = run_tbo("ADD")
     ok, fail = tbo_counts(out)
     assert rc == 0 and not fail, (fail[:5], out[-1500:])
-    assert len(ok) >= 28, len(ok)
+    assert len(ok) >= 26, len(ok)            # (26 cases + the two summary lines)
 
 
 @pytest.mark.parametrize("mode", ["dense", "exact"])
@@ -79,7 +79,16 @@ def test_tbo_mul_mat_gemm_paths(mode):
     rc, out, err = run_tbo("MUL_MAT", env)
     ok, fail = tbo_counts(out)
     assert rc == 0 and not fail, (fail[:5], out[-1500:])
-    assert len(ok) >= 140, len(ok)
+    assert len(ok) >= 138, len(ok)
+
+
+@pytest.mark.parametrize("op,min_ok", [("RMS_NORM", 2), ("SOFT_MAX", 20), ("POOL_2D", 20)])
+def test_tbo_stub_ops_through_plugin(op, min_ok):
+    """the ops ggml-hexagon lists without a kernel (ggml-hexagon.cpp:619, 639, 649), vs ggml-cpu by the reference's own harness"""
+    rc, out, err = run_tbo(op)
+    ok, fail = tbo_counts(out)
+    assert rc == 0 and not fail, (fail[:5], out[-1500:])
+    assert len(ok) >= min_ok, (len(ok), out[-1500:])
 
 
 # ------------------------------------------------------------------------------------------------ in-process, public ggml API

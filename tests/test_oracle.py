@@ -137,3 +137,49 @@ def test_q8_1_vs_live_reference():
     rng = np.random.default_rng(13)
     x = (rng.standard_normal((8, 4096)) * rng.choice([1e-4, 1.0, 50.0], (8, 1))).astype(np.float32)
     assert np.array_equal(O.quantize(O.Q8_1, x), R.quantize_row_ref(O.Q8_1, x))
+
+
+# ------------------------------------------------------------------ RMS_NORM / SOFT_MAX / POOL_2D
+GO = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_scalar_ops.npz"))
+
+
+def _nmse(a, b):
+    a, b = a.astype(np.float64), b.astype(np.float64)
+    return float(((a - b) ** 2).sum() / max((b ** 2).sum(), 1e-30))
+
+
+def test_oracle_rms_norm_golden_bit_exact():
+    assert np.array_equal(O.rms_norm(GO["rms_x"], 1e-6), GO["rms_out_eps1e-6"])
+    assert np.array_equal(O.rms_norm(GO["rms_x"][1:], 0.0), GO["rms_out_eps0"])
+    assert np.array_equal(O.rms_norm(GO["rms_xl"], 1e-5), GO["rms_outl"])
+
+
+def test_oracle_soft_max_golden():
+    # the reference's x86 builds run their own polynomial expf (ggml_v_expf, ggml-cpu.c:2181-2209) on groups of 4 and libm expf on
+    # the tail; the restatement follows the scalar tail.  Floating point: the bar is test-backend-ops' NMSE (1e-7), far from binding
+    for got, key in ((O.soft_max(GO["sm_x"]), "sm_plain"), (O.soft_max(GO["sm_x"], GO["sm_mask"], 0.1, 0.0), "sm_mask_scale"),
+                     (O.soft_max(GO["sm_x"], GO["sm_mask"], 0.1, 8.0), "sm_alibi"), (O.soft_max(GO["sm_xl"], None, 0.125, 0.0), "sm_outl")):
+        assert _nmse(got, GO[key]) <= 1e-12, key
+        assert np.abs(got - GO[key]).max() <= 3e-7, key
+        assert np.allclose(got.sum(-1), 1.0, atol=1e-5)
+
+
+def test_oracle_pool_2d_golden_bit_exact():
+    for name in ("max_3311", "avg_3322", "avg_2321", "max_1122"):
+        a = [int(v) for v in GO["poolargs_" + name]]
+        assert np.array_equal(O.pool_2d(GO["pool_x"], *a), GO["pool_" + name]), name
+
+
+def test_oracle_new_ops_vs_live_reference():
+    import pyref
+    try:
+        R = pyref.Ref("scalar")
+    except FileNotFoundError:
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((2, 3, 7, 96)).astype(np.float32)
+    assert np.array_equal(O.rms_norm(x, 1e-6), pyref.ref_rms_norm(R, x, 1e-6))
+    m = rng.standard_normal((7, 96)).astype(np.float32)
+    assert _nmse(O.soft_max(x, m, 0.5, 4.0), pyref.ref_soft_max(R, x, m, 0.5, 4.0)) <= 1e-12
+    p = rng.standard_normal((1, 2, 9, 13)).astype(np.float32)
+    assert np.array_equal(O.pool_2d(p, 1, 3, 2, 2, 1, 1, 0), pyref.ref_pool_2d(R, p, 1, 3, 2, 2, 1, 1, 0))
