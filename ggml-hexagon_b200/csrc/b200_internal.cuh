@@ -119,6 +119,8 @@ bool gemv_pdl_enabled();
 // gemv6.cu: ONE f32 activation column a.x, quantised inside the kernel; persistent CTAs (one per SM), per-warp cp.async.bulk rings.
 // false: not eligible (*err untouched) -- the caller quantises into a.act and runs gemv4 / gemv5
 bool launch_gemv6(int type, GemvArgs & a, int sms, cudaStream_t st, cudaError_t * err);
+// gemv.cu: gemv5 tiles run as thread-block clusters that quantise a.x (f32) among themselves; same contract as launch_gemv6
+bool launch_gemv5c(int type, GemvArgs & a, cudaStream_t st, cudaError_t * err);
 void gemv6_trace(long long * buf, int cap_launches);      // development: 4 x %globaltimer per CTA of the next launches (4096 values per launch)
 int  gemv6_trace_count();
 bool gemv_fuseq_enabled();

@@ -259,7 +259,8 @@ def test_gemv5_tma_tiles(monkeypatch, t, rows, M, K):
     forced here for small matrices, ragged last tiles (M % rows != 0), two slices per warp (K = 28672) and every tile height.
     Same integer dots and scales as gemv4 -> same bar against the oracle."""
     monkeypatch.setenv("B200_GEMV5_MIN_MB", "0")
-    monkeypatch.setenv("B200_GEMV6", "0")          # (the persistent ring GEMV would take every one-column MUL_MAT)
+    monkeypatch.setenv("B200_GEMV6", "0")          # (the kernels that quantise in-kernel would take every one-column MUL_MAT)
+    monkeypatch.setenv("B200_GEMV5C", "0")
     monkeypatch.setenv("B200_GEMV5_ROWS", str(rows))
     rng = np.random.default_rng(M + K + t + rows)
     raw = O.random_blocks(t, M, K, rng)
