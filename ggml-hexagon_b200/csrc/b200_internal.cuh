@@ -82,14 +82,12 @@ struct GemvMat {
 struct GemvArgs {
     GemvMat mat[3]; int nmat; int cta_end[3];
     int steps; int64_t K; int64_t dcs;
-    const float * x; int64_t x_col_stride;     // FUSEQ: f32 activations, column stride in bytes
-    ActView act;                                // !FUSEQ: pre-quantised scratch
+    const float * x; int64_t x_col_stride;     // gemv5c / gemv6: the f32 activation column (quantised inside the kernel)
+    ActView act;                                // gemv4 / gemv5 / gemv5n: pre-quantised scratch
     // row split over the GPUs of one box: every result is also stored into the peers' copies of dst over NVLink
     // (peer address = local address + peer_delta[p]; dst lies in the symmetric heap every rank allocated alike)
     int npeers; long long peer_delta[7];
-    // the LAST CTA of the launch publishes "op n of this rank is in your memory" to every peer (release, system scope):
-    // rs_ctrl[0] = CTA arrival counter, rs_ctrl[1] = ops signalled so far; peer_flag[p] = this rank's slot in peer p's flags
-    int rs_signal; uint32_t * rs_ctrl; long long peer_flag[7];
+    long long peer_flag[7];                  // (flag protocol: this rank's slot in peer p's flag array; used by the exchange kernel)
     // "LL" protocol (default for vector ops): instead of plain stores + a flag exchange, every result goes to the peers as ONE
     // 8-byte store {value, sequence number} into a staging area of the symmetric heap; the receivers poll the slots themselves
     // (ll_gather_kernel), so no fence, no flag and no second NVLink round trip.  seq = *ll_count + ll_op (ops of this submission
@@ -108,11 +106,8 @@ cudaError_t launch_rowsplit_push(const float * slice, long long rows, long long 
 // one warp: tell every peer "my slice of the op is in your memory" (release, system scope), then wait for theirs
 cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter, int npeers, const long long * peer_flag_addr /* [npeers] */,
                                      const int * peer_rank /* [npeers] */, cudaStream_t st);
-// wait half only (the GEMV signalled): one warp, programmatic dependent launch, spins on the peers' flags while the GEMV
-// before it still runs, then waits for that GEMV's completion
-cudaError_t launch_rowsplit_wait(uint32_t * local_flags, uint32_t * counter, int npeers, const int * peer_rank, cudaStream_t st);
-// fuseq: quantise inside the kernel (ncols <= 2); else read a.act. Launches with PDL unless B200_PDL=0.
-cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st);
+// 1 .. 8 columns of a.act (gemv5 tiles for large one-column launches, else the register path gemv4).  PDL unless B200_PDL=0.
+cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, cudaStream_t st);
 // all ncols (2 .. 31) columns of a.act in ONE launch over shared-memory tiles (gemv5n); false: not eligible, *err untouched
 bool launch_gemv_cols(int type, GemvArgs & a, int ncols, cudaStream_t st, cudaError_t * err);
 bool gemv_pdl_enabled();
@@ -123,7 +118,6 @@ bool launch_gemv6(int type, GemvArgs & a, int sms, cudaStream_t st, cudaError_t 
 bool launch_gemv5c(int type, GemvArgs & a, cudaStream_t st, cudaError_t * err);
 void gemv6_trace(long long * buf, int cap_launches);      // development: 4 x %globaltimer per CTA of the next launches (4096 values per launch)
 int  gemv6_trace_count();
-bool gemv_fuseq_enabled();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)
 cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, int64_t K,
                             const float * x, int64_t x_col_stride, int ncols,
@@ -131,42 +125,6 @@ cudaError_t launch_gemv_f32(const float * w, int64_t w_row_stride, int64_t M, in
 // scratch: sq = int8[K], sd = ActDS[K/32] (two-plane copy of a_qs built inside the kernel)
 cudaError_t launch_block_dots_impl(int type, WPtrs w, int64_t K, const int8_t * a_qs, int32_t * out,
                                    int8_t * sq, ActDS * sd, cudaStream_t st);
-
-// ---- decode stream kernel (decode_stream.cu): a whole decode node list as ONE persistent cooperative launch.
-// The host compiles the node list into stages; a stage is up to 3 vector MUL_MATs that share one activation vector
-// (optionally each with a fused residual ADD), or one plain vector ADD.
-enum : int { DS_GEMV = 0, DS_ADD = 1 };
-constexpr int DS_SLOT_BYTES = 18432 + 128;   // one ring slot: R weight rows of one matrix (all SoA fields)
-constexpr int DS_NSLOTS     = 10;
-constexpr int DS_ACT_BYTES  = 35840;         // q8_1 activations of one stage: K*1.25 bytes -> K <= 28672
-constexpr int DS_KMAX       = 28672;
-struct DsOp {
-    const uint8_t * f[4];        // SoA field pointers at the first block of the matrix
-    float * dst;                 // [M]
-    const float * add_src;       // fused GGML_OP_ADD (nullptr = none): add_dst[r] = add_src[r] + dst[r]
-    float * add_dst;
-    int M; int pad;
-};
-struct DsStage {
-    int kind, type, nops, K;
-    int steps;                   // lane-steps per row (K/32, K-quants K/64)
-    int R;                       // rows per ring slot (1, 2, 4 or 8)
-    int wait_prev;               // all CTAs must have finished every earlier stage before this one reads its inputs
-    int nfields;
-    int rw, pad0;                // rows of a slot one consumer warp handles (1 or 2)
-    int rowbytes[4];             // bytes of one row in each field array
-    int foff[4];                 // offset of each field inside a slot
-    int flead[4];                // 1: 2-byte field whose row start may be only 2-byte aligned (copy starts 16-B aligned, lead kept)
-    const float * x;             // GEMV: activations [K];  ADD: src0
-    DsOp op[3];                  // ADD: op[0].add_src = src1, op[0].dst = dst, op[0].M = n
-};
-int  ds_smem_bytes();
-int  ds_block_threads();
-int  ds_grid(int device);
-// cooperative launch, grid = number of SMs; counters: one uint32 per stage, zeroed once; epoch: 1, 2, 3 ... per launch
-int  ds_type_bit(int type);
-cudaError_t launch_decode_stream(const DsStage * prog_dev, int nstages, uint32_t * counters, uint32_t epoch, int grid, int type_mask,
-                                 long long * trace /* development: 4 clocks per (CTA, stage), or nullptr */, cudaStream_t st);
 
 // ---- prefill GEMM on the tensor cores (gemm_i8.cu): int8 tcgen05.mma per 32-element block, fp32 scale-accumulate
 // mode 0: q [N][K], dB [K/32][ldb];  1: + d * isum in [K/32][ldb] behind dB (q4_K);  2: 16-element groups spread to 32-byte
@@ -189,14 +147,13 @@ cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, f
 bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst);
 // ---- dense prefill GEMM (gemm_dense.cu): block scales folded into fp16 operands, the whole K accumulated in TMEM
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st);
-cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st);
 int gemm_dense_ksplit(int M, int N, int K, int sms);            // > 1: launch_gemm_dense wants a workspace of that many x N x M floats
-cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
+// A: quantised weights of `type` in the SoA layout (dequantised inside the kernel); B: fp16 activations [N][K]
+cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
                               const float * res_src = nullptr, float * res_dst = nullptr,   // residual ADD fused into the split-K reduce (needs split_ws and ksplit > 1)
                               void * act_out = nullptr);   // + fp16(q8_1(res_dst)) [N][M] for the next dense GEMM (M % 32 == 0)
-bool gemm_dense_pair();                                         // the CTA-pair kernel is selected (default; B200_GEMM_CTA=1: one CTA per tile)
-// 2..3 weight matrices over the same activations in one launch (q / k / v, gate / up); cudaErrorNotSupported without the pair kernel
-cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+// 2..3 weight matrices of one type over the same activations in one launch (q / k / v, gate / up)
+cudaError_t launch_gemm_dense_group(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
                                     const __half * B, int N, int K, int sms, cudaStream_t st);
 
 struct AddArgs {

@@ -1,5 +1,5 @@
 // gemm_dense.cu — prefill MUL_MAT as a DENSE fp16 tensor-core contraction: tcgen05.mma kind::f16 accumulating the whole K in
-// TMEM, operands staged by TMA, one TMEM read per output tile.
+// TMEM, one TMEM read per output tile, the quantised weights dequantised INSIDE the kernel.
 //
 // Same seat as gemm_i8.cu (ggml_compute_forward_mul_mat_one_chunk for src1 with many columns, ggml-dsp.c:1091-1189 /
 // ggml-cpu.c:6655-6743), different contract.  gemm_i8.cu keeps every per-block integer sum exact and therefore has to pull each
@@ -13,16 +13,21 @@
 // so the contraction is dense and the accumulator runs over the whole K.  What changes against the reference is only the
 // rounding of the two dequantised operands to fp16 (relative 2^-12 each; NMSE against ggml-cpu ~1e-7, the bar is 5e-4) and the
 // f32 summation order.  The q8_1 step is kept so that the result follows the reference's own quantisation of the activations.
-// |B| saturates at the fp16 maximum (activations beyond 65504 do not occur in the model families of the task).
+// Operand ranges fp16 cannot hold (|d_a q_a| > 65504, |d_w q_w| below the fp16 normal range) are detected by the caller, which
+// routes such a MUL_MAT to the exact int8 kernel (ops_api.cu, dense_range_ok).
 //
-// CTA (1 per SM, persistent over 128 x BN output tiles), 10 warps:
-//   warp 0      TMA producer: A = fp16 weights [M][K], B = fp16 activations [N][K]; boxes of 64 k (128 bytes) x 128 / BN rows,
-//               128-B swizzle, ring of GD_STAGES stages
-//   warp 1      TMEM allocation + MMA issue (one elected lane): 4 K16 MMAs per stage into one of two accumulator buffers,
-//               tcgen05.commit per stage (frees the ring slot) and per tile (hands the buffer to the epilogue)
-//   warps 2..9  epilogue: tcgen05.ld 32 lanes x 32 columns, coalesced f32 stores (32 consecutive m per column); the other
-//               buffer is being accumulated meanwhile
+// A never exists in HBM as fp16 (round 1 kept 2-byte "shadows" of every weight matrix: 3.6x the q4_0 bytes in HBM and in L2 -> SM
+// traffic): eight CONVERTER warps per CTA read the native SoA blocks (16 - 64 bytes per row and 64-element K slab, 128-bit loads,
+// two slabs ahead in registers), dequantise with packed fp16 / fp32 arithmetic and write the K-major, 128-byte-swizzled fp16 stage
+// the MMA descriptor expects -- the layout a TMA tile load would have produced.
+//
+// CTA pair (cluster of 2, one TPC), 256 x BN tile per pair, 18 warps per CTA:
+//   warp 0        TMA producer: B = fp16 activations [N][K], boxes of 64 k (128 bytes) x BN / 2 rows, 128-B swizzle
+//   warp 1        (leader CTA) MMA issue: tcgen05.mma.cta_group::2 kind::f16, M = 256, 4 K16 MMAs per stage
+//   warps 2..9    epilogue: tcgen05.ld 32 lanes x 32 columns, coalesced f32 stores; the other accumulator buffer is in use meanwhile
+//   warps 10..17  converters: thread = (row, half slab): native blocks -> fp16 -> swizzled stage; fence.proxy.async; arrive
 #include "tc_common.cuh"
+#include "wtypes.cuh"
 
 #include <stdio.h>
 #include <vector>
@@ -31,10 +36,9 @@ namespace b200 {
 
 constexpr int GD_KS = 64;                                    // fp16 elements of K per stage = one 128-B swizzle row
 constexpr int GD_EPI_WARPS = 8;                              // 4 TMEM lane quarters x 2 column halves
-constexpr int GD_THREADS = 64 + GD_EPI_WARPS * 32;
-__host__ __device__ constexpr int gd_stages(int bn) { return bn == 128 ? 6 : 4; }
-__host__ __device__ constexpr int gd_smem(int bn) { return gd_stages(bn) * (GM_BM * 128 + bn * 128) + 256 + 1024; }
-static_assert(gd_smem(128) <= 232448 && gd_smem(256) <= 232448, "shared memory");
+constexpr int GD_CVT_WARPS = 8;                              // converters: 128 rows x 2 half slabs of 32 elements
+constexpr int GD_CVT_WARP0 = 2 + GD_EPI_WARPS;
+constexpr int GD_THREADS = 64 + GD_EPI_WARPS * 32 + GD_CVT_WARPS * 32;
 
 struct GemmDenseArgs {
     float * out; long long out_cs;              // dst[n * out_cs + m]
@@ -45,6 +49,7 @@ struct GemmDenseArgs {
     // pair kernel: up to GD_MAXMAT weight matrices over the same activations in one launch (q / k / v, gate / up): the tile list
     // runs through all of them, which fills the waves that one 4096-row matrix cannot (32 tiles for 74 CTA pairs)
     int nmat;
+    const uint8_t * w[3][4];                   // SoA field arrays of each weight matrix (b200_internal.cuh), at the matrix's first block
     float * outs[3]; long long out_css[3]; int Ms[3];
     int tile_end[3];                           // tiles (m-tile x n-tile) up to and including matrix j; INT_MAX past nmat
     // the last, partial wave in narrow units: work items >= full_units are 256 x (BN / narrow_f) column slices of the remaining tiles,
@@ -107,117 +112,12 @@ __device__ __forceinline__ void gd_epilogue_warp1(const uint32_t taddr, float * 
     if (row_ok && ncols > 0) gd_store_chunk(colp, cs, va, ncols);
 }
 
-template <int BN>
-__global__ void __launch_bounds__(GD_THREADS, 1)
-gemm_dense_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDenseArgs p) {
-    constexpr int STAGES = gd_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = BN * 128;
-    constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
-    extern __shared__ uint8_t gd_smem_raw[];
-    const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;           // 128-B swizzle atoms want 1024-B alignment
-    uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
-    const uint32_t sA = base, sB = base + OFF_B, bars = base + OFF_BAR;
-    // full: TMA landed; empty: the stage's MMAs have read it; tfull: a tile's accumulator is complete; tempty: the epilogue has read it
-    const uint32_t full0 = bars, empty0 = bars + STAGES * 8, tfull0 = bars + 2 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
-    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 2 * STAGES * 8 + 4 * 8);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nks = (p.K + GD_KS - 1) / GD_KS, nwork = p.mtiles * p.ntiles * p.ksplit;
-
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
-        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, GD_EPI_WARPS); }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 1) {            // two f32 accumulator buffers of BN columns
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(gm_smem_u32((const void *) tmem_slot)), "n"(2 * BN) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    gm_fence_before();
-    __syncthreads();
-    gm_fence_after();
-    const uint32_t tmem = *tmem_slot;
-
-    if (warp == 0) {
-        // ===== TMA producer.  Work items are numbered m-tile fastest: the CTAs running at the same time share their B tile
-        // (activations, small) in L2 and stream different weight rows
-        if (lane == 0) {
-            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA) : "memory");
-            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
-        }
-        __syncwarp();
-        {   // whole warp, one elected lane issues (as the MMA warp)
-            uint32_t it = 0;
-            for (int work = blockIdx.x; work < nwork; work += gridDim.x) {
-                const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
-                const int nt = tile / p.mtiles, mt = tile - nt * p.mtiles;
-                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
-                for (int ks = ks0; ks < ks1; ks++, it++) {
-                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                    gm_mbar_wait(empty0 + s * 8, ph ^ 1);
-                    gm_mbar_expect_tx_elect(full0 + s * 8, STAGE_A + STAGE_B);
-                    gm_tma_2d_elect(sA + s * STAGE_A, &tmA, full0 + s * 8, ks * GD_KS, mt * GM_BM);
-                    gm_tma_2d_elect(sB + s * STAGE_B, &tmB, full0 + s * 8, ks * GD_KS, nt * BN);
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer: the whole warp runs the loop (uniform control flow), one elected lane issues (tc_common.cuh)
-        {
-            // instruction descriptor: D = f32 (bits 4-5 = 1), A / B = fp16 (0), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
-            const uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (GM_BM >> 4) << 24);
-            uint32_t it = 0, tc = 0;
-            for (int work = blockIdx.x; work < nwork; work += gridDim.x, tc++) {
-                const int sp = work % p.ksplit;
-                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
-                const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
-                gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
-                gm_fence_after();
-                for (int ks = ks0; ks < ks1; ks++, it++) {
-                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                    gm_mbar_wait(full0 + s * 8, ph);
-                    gm_fence_after();
-                    const uint64_t ad = gm_smem_desc(sA + s * STAGE_A), bd = gm_smem_desc(sB + s * STAGE_B);
-                    #pragma unroll
-                    for (int j = 0; j < 4; j++)                   // every MMA consumes 16 fp16 = 32 bytes of K per row: start address field + 2
-                        gm_mma_f16_elect(tmem + buf * BN, ad + 2u * j, bd + 2u * j, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
-                    gm_commit_elect(empty0 + s * 8);              // arrives when the stage's MMAs have read shared memory
-                }
-                gm_commit_elect(tfull0 + buf * 8);                // arrives when the tile's sums are in TMEM
-            }
-        }
-    } else {
-        // ===== epilogue: warp w reads TMEM lanes 32 * (w % 4) .. +31 (hardware rule), column half (w - 2) / 4
-        const int q = warp & 3, half = (warp - 2) >> 2;
-        const int m_local = q * 32 + lane;
-        const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16) + half * (BN / 2);
-        uint32_t tc = 0;
-        for (int work = blockIdx.x; work < nwork; work += gridDim.x, tc++) {
-            const int tile = work / p.ksplit, sp = work - tile * p.ksplit;
-            const int nt = tile / p.mtiles, mt = tile - nt * p.mtiles;
-            float * const outp = p.out + (long long) sp * p.split_stride;
-            const int m = mt * GM_BM + m_local;
-            const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
-            gm_mbar_wait(tfull0 + buf * 8, bph);            // every work item has k-steps: ksplit <= nks / 8
-            gm_fence_after();
-            const int n0 = nt * BN + half * (BN / 2);
-            gd_epilogue_warp<BN / 64>(tbase + buf * BN, outp + (long long) n0 * p.out_cs + m, p.out_cs, p.N - n0, m < p.M);
-            gm_fence_before();
-            __syncwarp();
-            if (lane == 0) gm_mbar_arrive(tempty0 + buf * 8);      // buffer free for the MMA issuer
-        }
-    }
-    gm_fence_before();
-    __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(2 * BN) : "memory");
-}
-
-// ------------------------------------------------------------------------------------------------ CTA-pair variant
-// The 1-CTA kernel above is bound by the L2 -> shared-memory operand feed, not by the tensor pipe: a 128 x 128 tile wants
-// 8 KB of operands per 64-clock MMA (128 B/clk/SM) while all of L2 delivers ~6300 B/clk (~43 B/clk/SM); ncu: tensor pipe 27 %
-// busy (profiles/r01_l_ncu_gemm_dense_1cta_*).  Here two CTAs of one TPC (cluster of 2) share one 256 x BN tile through
-// tcgen05.mma.cta_group::2: every CTA stages its own 128 weight rows and HALF of the activation rows, the MMA of the leader
-// reads B from both shared memories, and each CTA's TMEM receives its 128 rows x BN columns.  With BN = 256 that is 8 KB per
-// 128-clock MMA and SM = 64 B/clk/SM, and the total L2 traffic M N K 2 (1/256 + 1/256) is half of the 128 x 128 kernel's.
-//   full[s]   leader only; both CTAs' TMA loads (.cta_group::2) complete_tx on it, the leader posts the expected bytes of both
+// ------------------------------------------------------------------------------------------------ the CTA-pair kernel
+// Two CTAs of one TPC (cluster of 2) share one 256 x BN tile through tcgen05.mma.cta_group::2: every CTA converts its own 128 weight
+// rows and stages HALF of the activation rows, the MMA of the leader reads B from both shared memories, and each CTA's TMEM receives
+// its 128 rows x BN columns.  (A 128 x 128 tile per SM wants 128 B/clk/SM of operands out of L2, which delivers ~43: round 1.)
+//   full[s]   leader only; both CTAs' TMA loads of B (.cta_group::2) complete_tx on it, the leader posts the expected bytes of both
+//   afull[s]  leader only; the 8 converter warps of BOTH CTAs arrive on it when their part of the stage's A tile is written and fenced
 //   empty[s]  per CTA; tcgen05.commit.multicast arrives on both when the stage's MMAs have read shared memory
 //   tfull[b]  per CTA; multicast commit after a tile's last MMA
 //   tempty[b] leader only; the epilogue warps of BOTH CTAs arrive on it (remote arrive from the peer)
@@ -252,11 +152,121 @@ __device__ __forceinline__ void gd2_commit_both(uint32_t bar) {          // same
 __device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(bar_cluster) : "memory");
 }
+__device__ __forceinline__ void gd2_mbar_wait_cluster(uint32_t bar, uint32_t parity) {          // acquire at cluster scope: the arrivals are remote
+    uint32_t ok = 0;
+    const long long t0 = clock64();
+    while (!ok) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && clock64() - t0 > GM_TIMEOUT_CYCLES) __trap();
+    }
+}
 
-template <int BN>
+// ---- converters: native SoA blocks -> fp16(d * q), 32 consecutive elements of one row per thread and stage.
+// Small unsigned integers become fp16 by OR-ing them into the mantissa of 1024.0 (0x6400): exact, one PRMT per two values; the
+// bias is removed by an exact HSUB2, the scale applied by ONE rounding HMUL2 -- the same single rounding as fp16(float(d) * q).
+__device__ __forceinline__ uint32_t gd_prmt(uint32_t a, uint32_t b, uint32_t sel) { uint32_t r; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel)); return r; }
+__device__ __forceinline__ uint32_t gd_h2sub(uint32_t a, uint32_t b) { uint32_t r; asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+__device__ __forceinline__ uint32_t gd_h2mul(uint32_t a, uint32_t b) { uint32_t r; asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+// 4 bytes of w (values 0 .. 255) -> 4 halfs (v - bias) * d2; bias2 = {1024 + bias, 1024 + bias}
+__device__ __forceinline__ uint2 gd_u8x4_h(uint32_t w, uint32_t bias2, uint32_t d2) {
+    const uint32_t lo = gd_prmt(w, 0x64646464u, 0x5140u), hi = gd_prmt(w, 0x64646464u, 0x5342u);
+    return make_uint2(gd_h2mul(gd_h2sub(lo, bias2), d2), gd_h2mul(gd_h2sub(hi, bias2), d2));
+}
+__device__ __forceinline__ uint32_t gd_pack_h2f(float a, float b) { uint32_t r; asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }
+// 4 bytes of w (values 0 .. 255) -> 4 halfs of fp16(ds * v - ms), the product and difference in fp32 (one FFMA: a single rounding)
+__device__ __forceinline__ uint2 gd_u8x4_f(uint32_t w, float ds, float ms) {
+    const float f0 = __fmaf_rn(ds, (float) (w & 0xFFu), -ms), f1 = __fmaf_rn(ds, (float) ((w >> 8) & 0xFFu), -ms);
+    const float f2 = __fmaf_rn(ds, (float) ((w >> 16) & 0xFFu), -ms), f3 = __fmaf_rn(ds, (float) (w >> 24), -ms);
+    return make_uint2(gd_pack_h2f(f0, f1), gd_pack_h2f(f2, f3));
+}
+struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // what one thread keeps per stage in flight (unused members cost nothing)
+template <int TYPE> struct GdCvt;
+// q4_0: one 16-byte block = the thread's 32 elements (low nibbles = elements 0..15, high = 16..31); y = d * (q - 8)
+template <> struct GdCvt<T_Q4_0> {
+    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long blk = row * (K >> 5) + ks * 2 + hk;
+        r.a = ldg_stream(w[0] + blk * 16);
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s0) : "l"(w[1] + blk * 2));
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
+        const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64086408u, m = 0x0F0F0F0Fu;          // 1032 = 1024 + 8
+        const uint2 a = gd_u8x4_h(r.a.x & m, bias, d2), b = gd_u8x4_h(r.a.y & m, bias, d2), c = gd_u8x4_h(r.a.z & m, bias, d2), d = gd_u8x4_h(r.a.w & m, bias, d2);
+        const uint2 e = gd_u8x4_h((r.a.x >> 4) & m, bias, d2), f = gd_u8x4_h((r.a.y >> 4) & m, bias, d2), g = gd_u8x4_h((r.a.z >> 4) & m, bias, d2), h = gd_u8x4_h((r.a.w >> 4) & m, bias, d2);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
+    }
+};
+// q8_0: one 32-byte block; y = d * q, q signed: q + 128 is the unsigned byte q ^ 0x80
+template <> struct GdCvt<T_Q8_0> {
+    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long blk = row * (K >> 5) + ks * 2 + hk;
+        r.a = ldg_stream(w[0] + blk * 32); r.b = ldg_stream(w[0] + blk * 32 + 16);
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s0) : "l"(w[1] + blk * 2));
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
+        const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64806480u, x = 0x80808080u;          // 1152 = 1024 + 128
+        const uint2 a = gd_u8x4_h(r.a.x ^ x, bias, d2), b = gd_u8x4_h(r.a.y ^ x, bias, d2), c = gd_u8x4_h(r.a.z ^ x, bias, d2), d = gd_u8x4_h(r.a.w ^ x, bias, d2);
+        const uint2 e = gd_u8x4_h(r.b.x ^ x, bias, d2), f = gd_u8x4_h(r.b.y ^ x, bias, d2), g = gd_u8x4_h(r.b.z ^ x, bias, d2), h = gd_u8x4_h(r.b.w ^ x, bias, d2);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
+    }
+};
+// q4_K: the slab is 32 bytes of super-block ks / 4, sub-blocks 2j (low nibbles, hk = 0) and 2j + 1 (high nibbles), j = ks % 4;
+// y = (d * sc_g) * q - dmin * m_g, scales / mins 6-bit packed in the 16-byte header (get_scale_min_k4, ggml-quants.c:631-638)
+template <> struct GdCvt<T_Q4_K> {
+    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int) {
+        const long long sb = row * (K >> 8) + (ks >> 2);
+        const uint8_t * q = w[0] + sb * 128 + (ks & 3) * 32;
+        r.a = ldg_stream(q); r.b = ldg_stream(q + 16);
+        r.c = __ldg((const uint4 *) (w[1] + sb * 16));
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
+        const int g = 2 * (ks & 3) + hk;
+        const uint32_t wsc[3] = {r.c.y, r.c.z, r.c.w};
+        auto byte = [&](int k) -> uint32_t { return (wsc[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
+        uint32_t sc, mn;
+        if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
+        else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
+        const __half2 dd = *(const __half2 *) &r.c.x;
+        const float ds = __fmul_rn(__low2float(dd), (float) sc), ms = __fmul_rn(__high2float(dd), (float) mn);
+        const uint32_t m = 0x0F0F0F0Fu; const int sh = hk * 4;
+        const uint2 a = gd_u8x4_f((r.a.x >> sh) & m, ds, ms), b = gd_u8x4_f((r.a.y >> sh) & m, ds, ms), c = gd_u8x4_f((r.a.z >> sh) & m, ds, ms), d = gd_u8x4_f((r.a.w >> sh) & m, ds, ms);
+        const uint2 e = gd_u8x4_f((r.b.x >> sh) & m, ds, ms), f = gd_u8x4_f((r.b.y >> sh) & m, ds, ms), gg = gd_u8x4_f((r.b.z >> sh) & m, ds, ms), h = gd_u8x4_f((r.b.w >> sh) & m, ds, ms);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(gg.x, gg.y, h.x, h.y);
+    }
+};
+// q6_K: slab ks = 64 elements 128 h + 64 c + e of super-block ks / 4 (h = (ks / 2) % 2, c = ks % 2); the thread's e = 32 hk .. + 31 are
+// l = 0 .. 31 of ql[64 h + 32 hk + l] (low nibble for c = 0, high for c = 1) and bits 2 (2 c + hk) .. + 1 of qh[32 h + l];
+// y = d * sc[8 h + 4 c + 2 hk + l / 16] * (q - 32)   (dequantize_row_q6_K, ggml-quants.c:1681-1710)
+template <> struct GdCvt<T_Q6_K> {
+    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long sb = row * (K >> 8) + (ks >> 2);
+        const int h = (ks >> 1) & 1, c = ks & 1;
+        const uint8_t * ql = w[0] + sb * 128 + 64 * h + 32 * hk;
+        const uint8_t * qh = w[1] + sb * 64 + 32 * h;
+        r.a = __ldg((const uint4 *) ql); r.b = __ldg((const uint4 *) (ql + 16));          // (read again by the c = 1 slab: keep them in L1)
+        r.c = __ldg((const uint4 *) qh); r.e = __ldg((const uint4 *) (qh + 16));
+        r.s0 = __ldg((const unsigned short *) (w[2] + sb * 16 + 8 * h + 4 * c + 2 * hk));
+        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s1) : "l"(w[3] + sb * 2));
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
+        const int c = ks & 1, sh = 2 * (2 * c + hk), ns = 4 * c;
+        const uint32_t m = 0x0F0F0F0Fu, m3 = 0x03030303u;
+        auto q = [&](uint32_t l, uint32_t hh) { return ((l >> ns) & m) | (((hh >> sh) & m3) << 4); };
+        const float d = __half2float(__ushort_as_half((unsigned short) r.s1));
+        const float d0 = __fmul_rn(d, (float) (int8_t) (r.s0 & 0xFF)), d1 = __fmul_rn(d, (float) (int8_t) ((r.s0 >> 8) & 0xFF));
+        const float m0 = d0 * 32.f, m1 = d1 * 32.f;                      // (exact: power of two)
+        const uint2 a = gd_u8x4_f(q(r.a.x, r.c.x), d0, m0), b = gd_u8x4_f(q(r.a.y, r.c.y), d0, m0), cc = gd_u8x4_f(q(r.a.z, r.c.z), d0, m0), dd = gd_u8x4_f(q(r.a.w, r.c.w), d0, m0);
+        const uint2 e = gd_u8x4_f(q(r.b.x, r.e.x), d1, m1), f = gd_u8x4_f(q(r.b.y, r.e.y), d1, m1), g = gd_u8x4_f(q(r.b.z, r.e.z), d1, m1), h = gd_u8x4_f(q(r.b.w, r.e.w), d1, m1);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(cc.x, cc.y, dd.x, dd.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
+    }
+};
+
+template <int BN, int TYPE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
-gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-                   const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBq,
+gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBq,
                    const GemmDenseArgs p) {
     constexpr int STAGES = gd2_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
     constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
@@ -264,8 +274,8 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;
     uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
     const uint32_t sA = base, sB = base + OFF_B, bars = base + OFF_BAR;
-    const uint32_t full0 = bars, empty0 = bars + STAGES * 8, tfull0 = bars + 2 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
-    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 2 * STAGES * 8 + 4 * 8);
+    const uint32_t full0 = bars, empty0 = bars + STAGES * 8, afull0 = bars + 2 * STAGES * 8, tfull0 = bars + 3 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
@@ -278,7 +288,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     const int nwork = p.full_units + (p.tile_end[p.nmat - 1] * p.ksplit - p.full_units) * p.narrow_f;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); }
+        for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(afull0 + i * 8, 2 * GD_CVT_WARPS); }
         for (int i = 0; i < 2; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, 2 * GD_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -290,16 +300,13 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     gd2_cluster_sync();
     gm_fence_after();
     const uint32_t tmem = *tmem_slot;
-    asm volatile("griddepcontrol.wait;" ::: "memory");      // every role: loads of B, stores of dst / the split workspace
+    if (warp < GD_CVT_WARP0) asm volatile("griddepcontrol.wait;" ::: "memory");      // loads of B, stores of dst / the split workspace (weights depend on nothing)
     if (threadIdx.x == 0) gd_stamp(p, 1);
 
     if (warp == 0) {
-        // ===== TMA producer (both CTAs).  Work items are numbered n-tile fastest: the pairs that share a weight tile run at the
-        // same time, so the fp16 weights come from HBM once (the activations stay in L2 anyway)
-        if (lane == 0) {
-            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmA0) : "memory");
-            asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
-        }
+        // ===== TMA producer of the activations (both CTAs).  Work items are numbered n-tile fastest: the pairs that share a weight tile
+        // run at the same time, so the weights come from HBM once (the activations stay in L2 anyway)
+        if (lane == 0) asm volatile("prefetch.tensormap [%0];" :: "l"(&tmB) : "memory");
         __syncwarp();
         {   // whole warp, one elected lane issues
             const uint32_t lfull0 = gd2_mapa(full0, 0);
@@ -310,16 +317,14 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
                 const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
                 const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
                 const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
-                const CUtensorMap * const tmA = j == 0 ? &tmA0 : (j == 1 ? &tmA1 : &tmA2);
                 const CUtensorMap * const tmBu = u.n_w == BN ? &tmB : (u.n_w == BN / 2 ? &tmBh : &tmBq);      // box rows = n_w / 2
-                const uint32_t tx = 2u * (STAGE_A + (uint32_t) (u.n_w / 2) * 128u);
+                const uint32_t tx = 2u * ((uint32_t) (u.n_w / 2) * 128u);
                 const int brow = nt * BN + u.n_off + (int) rank * (u.n_w / 2);
                 const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
                     if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, tx);
-                    gd2_tma_2d(sA + s * STAGE_A, tmA, lfull0 + s * 8, ks * GD_KS, mt * 2 * GM_BM + (int) rank * GM_BM);
                     gd2_tma_2d(sB + s * STAGE_B, tmBu, lfull0 + s * 8, ks * GD_KS, brow);
                 }
             }
@@ -338,7 +343,8 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
                 gm_fence_after();
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                    gm_mbar_wait(full0 + s * 8, ph);
+                    gd2_mbar_wait_cluster(afull0 + s * 8, ph);       // both CTAs' converted weight rows are in shared memory (async-proxy visible)
+                    gm_mbar_wait(full0 + s * 8, ph);                 // both halves of the activation tile have landed
                     gm_fence_after();
                     if (it == 0 && lane == 0) gd_stamp(p, 2);
                     const uint64_t ad = gm_smem_desc(sA + s * STAGE_A), bd = gm_smem_desc(sB + s * STAGE_B);
@@ -351,7 +357,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
             }
             if (lane == 0) gd_stamp(p, 3);
         }
-    } else {
+    } else if (warp < GD_CVT_WARP0) {
         // ===== epilogue (both CTAs): this CTA's TMEM holds rows rank * 128 .. +127 of the pair tile, all BN columns
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int m_local = q * 32 + lane;
@@ -386,6 +392,50 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
         }
         if (warp == 2 && lane == 0) gd_stamp(p, 6);
+    } else {
+        // ===== converters (both CTAs): thread = row r of this CTA's 128, half slab hk; native blocks -> swizzled fp16 stage.
+        // 128-byte swizzle of a K-major tile: row r lies at (r / 8) * 1024 + (r % 8) * 128, its 16-byte chunk c at ((c ^ (r % 8)) * 16):
+        // the 8 lanes of a store phase (8 consecutive rows, same c) hit 8 different chunk positions = all 32 banks once.
+        const int cw = warp - GD_CVT_WARP0, r = (cw & 3) * 32 + lane, hk = cw >> 2;
+        const uint32_t rowoff = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
+        uint32_t choff[4];
+        #pragma unroll
+        for (int c = 0; c < 4; c++) choff[c] = rowoff + (uint32_t) (((hk * 4 + c) ^ (r & 7)) << 4);
+        const uint32_t lafull0 = gd2_mapa(afull0, 0);
+        uint32_t it = 0;
+        for (int work = pair; work < nwork; work += npairs) {
+            const GdUnit u = gd2_unit(p, work, BN);
+            const int tile = u.tile, sp = u.sp;
+            const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
+            const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
+            const int mt = local / p.ntiles;
+            const long long m = (long long) mt * 2 * GM_BM + (int) rank * GM_BM + r;
+            const bool row_ok = m < p.Ms[j];
+            const uint8_t * w[4];
+            #pragma unroll
+            for (int f = 0; f < 4; f++) w[f] = j == 0 ? p.w[0][f] : (j == 1 ? p.w[1][f] : p.w[2][f]);
+            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
+            auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
+            GdRaw cur, nxt;
+            if (live(ks0)) GdCvt<TYPE>::load(cur, w, m, p.K, ks0, hk);
+            for (int ks = ks0; ks < ks1; ks++, it++) {
+                if (ks + 1 < ks1 && live(ks + 1)) GdCvt<TYPE>::load(nxt, w, m, p.K, ks + 1, hk);      // one slab ahead, in registers
+                uint4 o[4];
+                if (live(ks)) GdCvt<TYPE>::convert(cur, ks, hk, o);
+                else { o[0] = o[1] = o[2] = o[3] = make_uint4(0, 0, 0, 0); }
+                const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                               // the MMAs that read this slot are done
+                const uint32_t dst = sA + s * STAGE_A;
+                #pragma unroll
+                for (int c = 0; c < 4; c++)
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                        // generic-proxy stores -> visible to the tensor core
+                __syncwarp();
+                if (lane == 0) gd2_arrive_cluster(lafull0 + s * 8);
+                cur = nxt;
+            }
+        }
     }
     __syncwarp();                // the cluster barrier is warp-aligned: the single-lane roles rejoin their warps first
     gm_fence_before();
@@ -395,100 +445,6 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------------ operand preparation
-__device__ __forceinline__ uint32_t gd_pack_h2(float a, float b) {
-    const __half2 h = __floats2half2_rn(a, b);
-    return *(const uint32_t *) &h;
-}
-// 4 signed bytes of w times d -> 4 halfs
-__device__ __forceinline__ uint2 gd_s8x4(uint32_t w, float d) {
-    return make_uint2(gd_pack_h2(d * (float) (int8_t) (w & 0xFF), d * (float) (int8_t) ((w >> 8) & 0xFF)),
-                      gd_pack_h2(d * (float) (int8_t) ((w >> 16) & 0xFF), d * (float) (int8_t) (w >> 24)));
-}
-// 4 unsigned bytes: d * (q - bias) - mn
-__device__ __forceinline__ uint2 gd_u8x4(uint32_t w, float d, float bias, float mn) {
-    return make_uint2(gd_pack_h2(d * ((float) (w & 0xFF) - bias) - mn, d * ((float) ((w >> 8) & 0xFF) - bias) - mn),
-                      gd_pack_h2(d * ((float) ((w >> 16) & 0xFF) - bias) - mn, d * ((float) (w >> 24) - bias) - mn));
-}
-__device__ __forceinline__ void gd_store16(__half * out, const uint2 a, const uint2 b, const uint2 c, const uint2 d) {
-    ((uint4 *) out)[0] = make_uint4(a.x, a.y, b.x, b.y);
-    ((uint4 *) out)[1] = make_uint4(c.x, c.y, d.x, d.y);
-}
-
-// q8_0 (SoA: qs 32 B, d f16 per block; y = d * q, dequantize_row_q8_0 ggml-quants.c:347-363): one thread per 16 elements
-__global__ void __launch_bounds__(256)
-dequant_q8_0_f16_kernel(const uint4 * __restrict__ qs, const __half * __restrict__ dd, const long long n16, __half * __restrict__ out) {
-    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long) gridDim.x * blockDim.x) {
-        const uint4 v = qs[i];
-        const float d = __half2float(dd[i >> 1]);
-        gd_store16(out + i * 16, gd_s8x4(v.x, d), gd_s8x4(v.y, d), gd_s8x4(v.z, d), gd_s8x4(v.w, d));
-    }
-}
-// q4_0 (qs 16 B: low nibbles = elements 0..15, high = 16..31; y = d * (q - 8), dequantize_row_q4_0 ggml-quants.c:307-325): one thread per block
-__global__ void __launch_bounds__(256)
-dequant_q4_0_f16_kernel(const uint4 * __restrict__ qs, const __half * __restrict__ dd, const long long nblocks, __half * __restrict__ out) {
-    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nblocks; i += (long long) gridDim.x * blockDim.x) {
-        const uint4 v = qs[i];
-        const float d = __half2float(dd[i]);
-        const uint32_t m = 0x0F0F0F0Fu;
-        gd_store16(out + i * 32,      gd_u8x4(v.x & m, d, 8.f, 0.f), gd_u8x4(v.y & m, d, 8.f, 0.f), gd_u8x4(v.z & m, d, 8.f, 0.f), gd_u8x4(v.w & m, d, 8.f, 0.f));
-        gd_store16(out + i * 32 + 16, gd_u8x4((v.x >> 4) & m, d, 8.f, 0.f), gd_u8x4((v.y >> 4) & m, d, 8.f, 0.f),
-                                      gd_u8x4((v.z >> 4) & m, d, 8.f, 0.f), gd_u8x4((v.w >> 4) & m, d, 8.f, 0.f));
-    }
-}
-// q4_K (qs 128 B + header {f16 d, f16 dmin, 12 B packed 6-bit scales / mins}; y = (d * sc_g) * q - dmin * m_g,
-// dequantize_row_q4_K ggml-quants.c:1352-1374): one thread per 64 elements (low nibbles = sub-block 2j, high = 2j + 1)
-__global__ void __launch_bounds__(256)
-dequant_q4_K_f16_kernel(const uint4 * __restrict__ qs, const uint4 * __restrict__ hdr, const long long nsuper, __half * __restrict__ out) {
-    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 4; i += (long long) gridDim.x * blockDim.x) {
-        const long long sb = i >> 2; const int j = (int) (i & 3);
-        const uint4 v0 = qs[sb * 8 + 2 * j], v1 = qs[sb * 8 + 2 * j + 1];
-        const uint4 h = hdr[sb];
-        const __half2 dd = *(const __half2 *) &h.x;
-        const float d = __low2float(dd), dmin = __high2float(dd);
-        const uint32_t w[3] = {h.y, h.z, h.w};
-        auto byte = [&](int k) -> uint32_t { return (w[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
-        float ds[2], ms[2];
-        #pragma unroll
-        for (int e = 0; e < 2; e++) {
-            const int g = 2 * j + e;
-            uint32_t sc, mn;
-            if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
-            else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
-            ds[e] = __fmul_rn(d, (float) sc); ms[e] = __fmul_rn(dmin, (float) mn);
-        }
-        const uint32_t m = 0x0F0F0F0Fu;
-        __half * o = out + sb * 256 + j * 64;
-        gd_store16(o,      gd_u8x4(v0.x & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.y & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.z & m, ds[0], 0.f, ms[0]), gd_u8x4(v0.w & m, ds[0], 0.f, ms[0]));
-        gd_store16(o + 16, gd_u8x4(v1.x & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.y & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.z & m, ds[0], 0.f, ms[0]), gd_u8x4(v1.w & m, ds[0], 0.f, ms[0]));
-        gd_store16(o + 32, gd_u8x4((v0.x >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v0.y >> 4) & m, ds[1], 0.f, ms[1]),
-                           gd_u8x4((v0.z >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v0.w >> 4) & m, ds[1], 0.f, ms[1]));
-        gd_store16(o + 48, gd_u8x4((v1.x >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v1.y >> 4) & m, ds[1], 0.f, ms[1]),
-                           gd_u8x4((v1.z >> 4) & m, ds[1], 0.f, ms[1]), gd_u8x4((v1.w >> 4) & m, ds[1], 0.f, ms[1]));
-    }
-}
-// q6_K (ql 128 B, qh 64 B, 16 int8 scales, f16 d; y = d * sc_g * (q - 32), bit layout as dequantize_row_q6_K
-// ggml-quants.c:1681-1710): 16 threads per super-block, thread t handles l = 4 (t & 7) .. +3 of half (t >> 3)
-__global__ void __launch_bounds__(256)
-dequant_q6_K_f16_kernel(const uint32_t * __restrict__ ql, const uint32_t * __restrict__ qh, const int8_t * __restrict__ sc,
-                        const __half * __restrict__ dd, const long long nsuper, __half * __restrict__ out) {
-    for (long long i = (long long) blockIdx.x * blockDim.x + threadIdx.x; i < nsuper * 16; i += (long long) gridDim.x * blockDim.x) {
-        const long long sb = i >> 4; const int t = (int) (i & 15), half = t >> 3, l4 = t & 7;
-        const uint32_t a = ql[sb * 32 + half * 16 + l4], b = ql[sb * 32 + half * 16 + 8 + l4], h = qh[sb * 16 + half * 8 + l4];
-        const uint32_t v[4] = {
-            (a & 0x0F0F0F0Fu)        | ((h << 4) & 0x30303030u),
-            (b & 0x0F0F0F0Fu)        | ((h << 2) & 0x30303030u),
-            ((a >> 4) & 0x0F0F0F0Fu) | ( h       & 0x30303030u),
-            ((b >> 4) & 0x0F0F0F0Fu) | ((h >> 2) & 0x30303030u)};
-        const float d = __half2float(dd[sb]);
-        #pragma unroll
-        for (int r = 0; r < 4; r++) {
-            const int e = half * 128 + r * 32 + l4 * 4;          // element index inside the super-block
-            const float dg = __fmul_rn(d, (float) sc[sb * 16 + (e >> 4)]);
-            *(uint2 *) (out + sb * 256 + e) = gd_u8x4(v[r], dg, 32.f, 0.f);
-        }
-    }
-}
-
 // activations: f32 [N][K] -> q8_1 (d = amax / 127 rounded to fp16, q = round(x / d); quantize_row_q8_1_ref ggml-quants.c:220-253)
 // -> fp16(d * q), saturating.  4 lanes per 32-element block, two float4 loads and one 16-byte store each.
 __global__ void __launch_bounds__(256)
@@ -531,34 +487,16 @@ cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, 
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel, (const char *) x, row_stride_bytes, K, N, out);
 }
-// weights of `type` (SoA field pointers w, nblocks native blocks) -> dequantised fp16 [M][K]
-cudaError_t launch_dequant_weights_f16(int type, const WPtrs & w, long long nblocks, __half * out, cudaStream_t st) {
-    auto grid_for = [](long long threads) { long long b = (threads + 255) / 256; return (unsigned) (b > 148 * 32 ? 148 * 32 : (b < 1 ? 1 : b)); };
-    switch (type) {
-        case T_Q8_0: dequant_q8_0_f16_kernel<<<grid_for(nblocks * 2), 256, 0, st>>>((const uint4 *) w.p[0], (const __half *) w.p[1], nblocks * 2, out); break;
-        case T_Q4_0: dequant_q4_0_f16_kernel<<<grid_for(nblocks), 256, 0, st>>>((const uint4 *) w.p[0], (const __half *) w.p[1], nblocks, out); break;
-        case T_Q4_K: dequant_q4_K_f16_kernel<<<grid_for(nblocks * 4), 256, 0, st>>>((const uint4 *) w.p[0], (const uint4 *) w.p[1], nblocks, out); break;
-        case T_Q6_K: dequant_q6_K_f16_kernel<<<grid_for(nblocks * 16), 256, 0, st>>>((const uint32_t *) w.p[0], (const uint32_t *) w.p[1], (const int8_t *) w.p[2],
-                                                                                    (const __half *) w.p[3], nblocks, out); break;
-        default: return cudaErrorInvalidValue;
-    }
-    return cudaGetLastError();
-}
-
 // ------------------------------------------------------------------------------------------------ host: launch
-// B200_GEMM_CTA=1 keeps the 1-CTA kernel (128 x BN tiles); default: the CTA-pair kernel (256 x BN tiles)
-bool gemm_dense_pair() { const char * e = getenv("B200_GEMM_CTA"); return !(e && atoi(e) == 1); }
-// N tile: 256 columns halve the number of times the weights travel from L2 to the SMs.  1-CTA kernel: only where the 128 x 256
-// tiles still fill the machine; pair kernel: always (few tiles are spread with split-K instead, the L2 feed is what binds)
+// N tile: 256 columns halve the number of times the weights travel from L2 to the SMs (few tiles are spread with split-K instead)
 int gemm_dense_bn(int M, int N, int sms) {
+    (void) M; (void) sms;
     if (getenv("B200_GEMM_BN")) return atoi(getenv("B200_GEMM_BN")) == 256 ? 256 : 128;
-    if (gemm_dense_pair()) return N > 128 ? 256 : 128;
-    const long long t256 = (long long) ((M + GM_BM - 1) / GM_BM) * ((N + 255) / 256);
-    return N > 128 && t256 >= sms ? 256 : 128;
+    return N > 128 ? 256 : 128;
 }
 int gemm_dense_ksplit(int M, int N, int K, int sms) {
     const int bn = gemm_dense_bn(M, N, sms);
-    const int bm = gemm_dense_pair() ? 2 * GM_BM : GM_BM, units = gemm_dense_pair() ? sms / 2 : sms;
+    const int bm = 2 * GM_BM, units = sms / 2;
     const int tiles = ((M + bm - 1) / bm) * ((N + bn - 1) / bn);
     const int nks = (K + GD_KS - 1) / GD_KS;
     int s = units / (tiles > 0 ? tiles : 1);
@@ -567,25 +505,12 @@ int gemm_dense_ksplit(int M, int N, int K, int sms) {
     return s < 2 ? 1 : s;
 }
 
-template <int BN>
-static cudaError_t gemm_dense_launch_t(const CUtensorMap & tmA, const CUtensorMap & tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+template <int BN, int TYPE>
+static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
     static bool attr_done[64] = {false};          // per device
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (!attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_dense_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd_smem(BN));
-        if (e != cudaSuccess) return e;
-        attr_done[dev] = true;
-    }
-    gemm_dense_kernel<BN><<<(unsigned) grid, GD_THREADS, gd_smem(BN), st>>>(tmA, tmB, p);
-    return cudaGetLastError();
-}
-
-template <int BN>
-static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
-    static bool attr_done[64] = {false};          // per device
-    int dev = 0; cudaGetDevice(&dev); dev &= 63;
-    if (!attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN));
+        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN, TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN));
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
@@ -595,22 +520,34 @@ static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmA, const CUtensorM
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, gemm_dense2_kernel<BN>, tmA[0], tmA[1], tmA[2], tmB[0], tmB[1], tmB[2], p);
+    return cudaLaunchKernelEx(&cfg, gemm_dense2_kernel<BN, TYPE>, tmB[0], tmB[1], tmB[2], p);
+}
+template <int BN>
+static cudaError_t gemm_dense2_launch(int type, const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+    switch (type) {
+        case T_Q4_0: return gemm_dense2_launch_t<BN, T_Q4_0>(tmB, p, grid, st);
+        case T_Q8_0: return gemm_dense2_launch_t<BN, T_Q8_0>(tmB, p, grid, st);
+        case T_Q4_K: return gemm_dense2_launch_t<BN, T_Q4_K>(tmB, p, grid, st);
+        case T_Q6_K: return gemm_dense2_launch_t<BN, T_Q6_K>(tmB, p, grid, st);
+    }
+    return cudaErrorInvalidValue;
 }
 
-// A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
-// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
-// pair kernel: nmat weight matrices A[j] (fp16 [M[j]][K]) over the same activations B (fp16 [N][K]); out[j][n * out_cs[j] + m]
-static cudaError_t launch_pair(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+// nmat weight matrices A[j] (type `type`, SoA fields, M[j] rows of K) over the same activations B (fp16 [N][K], 16-B aligned rows);
+// out[j][n * out_cs[j] + m]; split_ws: workspace of ksplit * N * M floats (nmat == 1), or nullptr (no split)
+static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
                                const __half * B, int N, int K, int sms, int ksplit, float * split_ws, cudaStream_t st) {
     const int bn = gemm_dense_bn(M[0], N, sms);
-    CUtensorMap tmA[GD_MAXMAT], tmB[3];
+    CUtensorMap tmB[3];
     GemmDenseArgs p{};
     p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit;
     int tiles = 0;
     for (int j = 0; j < GD_MAXMAT; j++) {
         const int jj = j < nmat ? j : 0;
-        if (!make_map_operand(&tmA[j], A[jj], M[jj], K, 2, GM_BM)) return cudaErrorInvalidValue;
+        for (int f = 0; f < 4; f++) {
+            p.w[j][f] = A[jj].p[f];
+            if (((uintptr_t) p.w[j][f] & 15) != 0 && f < wfields(type).n && wfields(type).size[f] >= 16) return cudaErrorInvalidValue;      // 128-bit loads
+        }
         if (j < nmat) { tiles += ((M[j] + 2 * GM_BM - 1) / (2 * GM_BM)) * p.ntiles; p.outs[j] = out[j]; p.out_css[j] = out_cs[j]; p.Ms[j] = M[j]; p.tile_end[j] = tiles; }
         else { p.outs[j] = nullptr; p.out_css[j] = 0; p.Ms[j] = 0; p.tile_end[j] = 0x7fffffff; }
     }
@@ -632,7 +569,7 @@ static cudaError_t launch_pair(const __half * const * A, float * const * out, co
     if (trace) cudaStreamIsCapturing(st, &cap);                 // the trace allocates and synchronises: not inside a stream capture
     if (trace && cap == cudaStreamCaptureStatusNone && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess)
         cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
-    const cudaError_t e = bn == 256 ? gemm_dense2_launch_t<256>(tmA, tmB, p, 2 * pairs, st) : gemm_dense2_launch_t<128>(tmA, tmB, p, 2 * pairs, st);
+    const cudaError_t e = bn == 256 ? gemm_dense2_launch<256>(type, tmB, p, 2 * pairs, st) : gemm_dense2_launch<128>(type, tmB, p, 2 * pairs, st);
     if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
         std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
         cudaStreamSynchronize(st);
@@ -651,38 +588,22 @@ static cudaError_t launch_pair(const __half * const * A, float * const * out, co
     return e;
 }
 
-// A: fp16 [M][K], B: fp16 [N][K] (16-B aligned rows: K % 8 == 0); out[n * out_cs + m]
+// A: quantised weights (type, SoA fields) [M][K]; B: fp16 [N][K] (K % 8 == 0); out[n * out_cs + m]
 // split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
-cudaError_t launch_gemm_dense(const __half * A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
+cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
                               const float * res_src, float * res_dst, void * act_out) {
     const int ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
     if (res_dst && ksplit == 1) return cudaErrorInvalidValue;
-    cudaError_t e;
-    if (gemm_dense_pair()) {
-        e = launch_pair(&A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, st);
-    } else {
-        const int bn = gemm_dense_bn(M, N, sms);
-        CUtensorMap tmA, tmB;
-        if (!make_map_operand(&tmA, A, M, K, 2, GM_BM) || !make_map_operand(&tmB, B, N, K, 2, bn)) return cudaErrorInvalidValue;
-        GemmDenseArgs p{};
-        p.out = out; p.out_cs = out_cs; p.M = M; p.N = N; p.K = K;
-        p.mtiles = (M + GM_BM - 1) / GM_BM; p.ntiles = (N + bn - 1) / bn;
-        p.ksplit = ksplit;
-        if (p.ksplit > 1) { p.out = split_ws; p.out_cs = M; p.split_stride = (long long) M * N; }
-        const int work = p.mtiles * p.ntiles * p.ksplit;
-        const int grid = work < sms ? work : sms;
-        e = bn == 256 ? gemm_dense_launch_t<256>(tmA, tmB, p, grid, st) : gemm_dense_launch_t<128>(tmA, tmB, p, grid, st);
-    }
+    const cudaError_t e = launch_pair(type, &A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, st);
     if (e != cudaSuccess || ksplit == 1) return e;
     return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst, act_out);
 }
 
-// Several weight matrices over the same activations in ONE launch of the pair kernel (no split-K): 2 <= nmat <= 3.
-// Returns cudaErrorNotSupported when the 1-CTA kernel is selected (the caller then launches the matrices one by one).
-cudaError_t launch_gemm_dense_group(const __half * const * A, float * const * out, const long long * out_cs, const int * M, int nmat,
+// Several weight matrices of one type over the same activations in ONE launch (no split-K): 2 <= nmat <= 3
+cudaError_t launch_gemm_dense_group(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
                                     const __half * B, int N, int K, int sms, cudaStream_t st) {
-    if (!gemm_dense_pair() || nmat < 1 || nmat > GD_MAXMAT) return cudaErrorNotSupported;
-    return launch_pair(A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, st);
+    if (nmat < 1 || nmat > GD_MAXMAT) return cudaErrorNotSupported;
+    return launch_pair(type, A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, st);
 }
 
 }  // namespace b200

@@ -26,9 +26,7 @@ namespace b200 {
 
 // ITERS > 1: the row has more than 32*nwarps steps; warp w then owns slices w, w+nwarps, ... and the fragments of the
 // next slice are requested before the current one is consumed (DB = register double buffer).
-// FQ: the activations are the f32 vector itself; every lane quantises the q8_1 block(s) of its own step (wtypes.cuh),
-// which removes the separate quantise launch (and its dependency latency) in front of every decode GEMV.
-template <int TYPE, int NCOLS, int R, bool DB, bool FQ>
+template <int TYPE, int NCOLS, int R, bool DB>
 __global__ void __launch_bounds__(512)
 gemv4_kernel(const GemvArgs a) {
     using W = WT<TYPE>;
@@ -76,9 +74,8 @@ gemv4_kernel(const GemvArgs a) {
         }
         #pragma unroll
         for (int c = 0; c < NCOLS; c++) {
-            typename A::Act av;
-            if constexpr (FQ) av = A::quant_act((const float *) ((const char *) a.x + (int64_t) c * a.x_col_stride), s, 0);
-            else { const ActCol ac(a.act, c); av = A::load_act(ac, s); }
+            const ActCol ac(a.act, c);
+            const typename A::Act av = A::load_act(ac, s);
             #pragma unroll
             for (int r = 0; r < R; r++) acc[c][r] += wr_dot<TYPE>(f[r], av, s);
         }
@@ -113,24 +110,6 @@ gemv4_kernel(const GemvArgs a) {
             for (int pi = 0; pi < a.npeers; pi++) {           // row split: the same values into every peer's dst (NVLink stores)
                 *(float *) ((char *) (mt.dst + o) + a.peer_delta[pi]) = v;
                 if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
-            }
-        }
-        // gpu-scope fence + the gpu-scope arrive below order this thread's peer stores before the last CTA's system-scope
-        // release (PTX causality order is transitive over scopes); a system fence here costs an NVLink round trip per CTA
-        if (a.rs_signal) __threadfence();
-    }
-    if (a.rs_signal) {
-        // last-CTA pattern: when every CTA of the launch has arrived, one thread tells the peers the op is complete
-        __syncthreads();
-        if (tid == 0) {
-            const unsigned prev = atomicAdd(a.rs_ctrl, 1u);
-            if (prev == gridDim.x - 1) {
-                a.rs_ctrl[0] = 0;
-                __threadfence_system();
-                const uint32_t n = a.rs_ctrl[1] + 1;
-                a.rs_ctrl[1] = n;
-                for (int pi = 0; pi < a.npeers; pi++)
-                    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag[pi]), "r"(n) : "memory");
             }
         }
     }
@@ -506,9 +485,8 @@ static const Tune & tune() {
     return t;
 }
 bool gemv_pdl_enabled() { return tune().pdl; }
-bool gemv_fuseq_enabled() { static const bool on = getenv("B200_FUSEQ") && atoi(getenv("B200_FUSEQ")) != 0; return on; }   // opt-in: measured 2-3x slower (every CTA re-quantises its lanes' blocks)
 
-template <int TYPE, int NCOLS, int R, bool FQ = false>
+template <int TYPE, int NCOLS, int R>
 static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     const int nslices = (a.steps + 31) / 32;
     const int iters = (nslices + 15) / 16;                  // at most 16 warps (512 threads) per CTA
@@ -525,9 +503,9 @@ static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
     // the register double buffer only where it fits without spills (ptxas -v): q4_0 / q8_0, one column
     if constexpr ((TYPE == T_Q4_0 || TYPE == T_Q8_0) && NCOLS == 1) {
-        if (iters > 1) return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, true, FQ>, a);
+        if (iters > 1) return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, true>, a);
     }
-    return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false, FQ>, a);
+    return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false>, a);
 }
 
 // gemv5 eligibility: one column, pre-quantised activations, every field's row is a multiple of 16 bytes and 16-byte aligned
@@ -555,7 +533,7 @@ static cudaError_t launch_g5(GemvArgs & a, const Gemv5Tile & t, int nwarps, cuda
 template <int TYPE>
 static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
     static const int mode = getenv("B200_GEMV5") ? atoi(getenv("B200_GEMV5")) : 1;       // 0: off (gemv4 only)
-    if (!mode || a.rs_signal) return false;
+    if (!mode) return false;
     const WFields f = wfields(TYPE);
     const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);            // native blocks per row
     Gemv5Tile t{};
@@ -617,7 +595,7 @@ static cudaError_t launch_g5c(GemvArgs & a, const Gemv5Tile & t, int nwarps, int
 template <int TYPE>
 static bool try_gemv5c(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
     const int mode = getenv("B200_GEMV5C") ? atoi(getenv("B200_GEMV5C")) : 1;            // 0: off; (read per launch: tests switch it)
-    if (!mode || a.rs_signal || !a.x || ((uintptr_t) a.x & 15) || a.K % 128) return false;
+    if (!mode || !a.x || ((uintptr_t) a.x & 15) || a.K % 128) return false;
     const WFields f = wfields(TYPE);
     const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);
     Gemv5Tile t{};
@@ -721,10 +699,10 @@ bool launch_gemv_cols(int type, GemvArgs & a, int ncols, cudaStream_t st, cudaEr
     return false;
 }
 
-template <int TYPE, int NCOLS, bool FQ = false>
+template <int TYPE, int NCOLS>
 static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
     constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
-    if constexpr (NCOLS == 1 && !FQ) {
+    if constexpr (NCOLS == 1) {
         cudaError_t e5 = cudaSuccess;
         if (try_gemv5<TYPE>(a, st, pdl, &e5)) return e5;
     }
@@ -733,12 +711,12 @@ static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
         int64_t mtot = 0; for (int i = 0; i < a.nmat; i++) mtot += a.mat[i].M;
         const int r = tune().rows > 0 ? tune().rows : (mtot >= 8192 ? 8 : (a.K >= 8192 ? 2 : 4));
         if constexpr (TYPE == T_Q4_0) {
-            if (r == 2) return launch_cfg<TYPE, 1, 2, FQ>(a, st, pdl);
-            if (r == 4) return launch_cfg<TYPE, 1, 4, FQ>(a, st, pdl);
-            return launch_cfg<TYPE, 1, 8, FQ>(a, st, pdl);
+            if (r == 2) return launch_cfg<TYPE, 1, 2>(a, st, pdl);
+            if (r == 4) return launch_cfg<TYPE, 1, 4>(a, st, pdl);
+            return launch_cfg<TYPE, 1, 8>(a, st, pdl);
         } else {
-            if (r == 2) return launch_cfg<TYPE, 1, 2, FQ>(a, st, pdl);
-            return launch_cfg<TYPE, 1, 4, FQ>(a, st, pdl);
+            if (r == 2) return launch_cfg<TYPE, 1, 2>(a, st, pdl);
+            return launch_cfg<TYPE, 1, 4>(a, st, pdl);
         }
     } else if constexpr (NCOLS == 2) {
         return launch_cfg<TYPE, NCOLS, (KQ ? 2 : 4)>(a, st, pdl);
@@ -750,8 +728,7 @@ static cudaError_t launch_ncols(GemvArgs & a, cudaStream_t st, bool pdl) {
 }
 
 template <int TYPE>
-static cudaError_t launch_type(GemvArgs & a, int ncols, bool fuseq, cudaStream_t st, bool pdl) {
-    if (fuseq) return ncols == 1 ? launch_ncols<TYPE, 1, true>(a, st, pdl) : cudaErrorInvalidValue;
+static cudaError_t launch_type(GemvArgs & a, int ncols, cudaStream_t st, bool pdl) {
     switch (ncols) {
         case 1: return launch_ncols<TYPE, 1>(a, st, pdl);
         case 2: return launch_ncols<TYPE, 2>(a, st, pdl);
@@ -765,14 +742,14 @@ static cudaError_t launch_type(GemvArgs & a, int ncols, bool fuseq, cudaStream_t
     return cudaErrorInvalidValue;
 }
 
-cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, bool fuseq, cudaStream_t st) {
+cudaError_t launch_gemv2(int type, GemvArgs & a, int ncols, cudaStream_t st) {
     a.steps = (int) (a.K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
     const bool pdl = tune().pdl;
     switch (type) {
-        case T_Q4_0: return launch_type<T_Q4_0>(a, ncols, fuseq, st, pdl);
-        case T_Q8_0: return launch_type<T_Q8_0>(a, ncols, fuseq, st, pdl);
-        case T_Q4_K: return launch_type<T_Q4_K>(a, ncols, fuseq, st, pdl);
-        case T_Q6_K: return launch_type<T_Q6_K>(a, ncols, fuseq, st, pdl);
+        case T_Q4_0: return launch_type<T_Q4_0>(a, ncols, st, pdl);
+        case T_Q8_0: return launch_type<T_Q8_0>(a, ncols, st, pdl);
+        case T_Q4_K: return launch_type<T_Q4_K>(a, ncols, st, pdl);
+        case T_Q6_K: return launch_type<T_Q6_K>(a, ncols, st, pdl);
     }
     return cudaErrorInvalidValue;
 }

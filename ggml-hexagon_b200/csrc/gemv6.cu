@@ -330,7 +330,7 @@ static bool try_gemv6(GemvArgs & a, int sms, cudaStream_t st, bool pdl, cudaErro
     // opt-in (B200_GEMV6=1) while it is slower than the quantize + gemv4 / gemv5 launches on the whole decode step (measured on B200:
     // 1.38 against 0.955 ms per Llama-2-7B token); read per launch: tests switch it
     const int on = getenv("B200_GEMV6") ? atoi(getenv("B200_GEMV6")) : 0;
-    if (!on || a.rs_signal || !a.x || ((uintptr_t) a.x & 15) || a.K % 256) return false;
+    if (!on || !a.x || ((uintptr_t) a.x & 15) || a.K % 256) return false;
     const WFields wf = wfields(TYPE);
     const int steps = (int) (a.K / (KQ ? 64 : 32));
     G6Cfg g{};

@@ -315,37 +315,6 @@ cudaError_t launch_rowsplit_exchange(uint32_t * local_flags, uint32_t * counter,
     return cudaGetLastError();
 }
 
-__global__ void rowsplit_wait_kernel(uint32_t * local_flags, uint32_t * counter, const ExchangeArgs a) {
-    const int p = threadIdx.x;
-    const uint32_t n = *counter + 1;
-    __syncwarp();
-    if (p < a.npeers) {
-        const long long t0 = clock64();
-        uint32_t v;
-        do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(local_flags + a.peer_rank[p]) : "memory");
-            if (clock64() - t0 > 8000000000ll) __trap();
-        } while ((int) (v - n) < 0);
-    }
-    __syncwarp();
-    if (p == 0) *counter = n;
-#if __CUDA_ARCH__ >= 900
-    cudaGridDependencySynchronize();     // the GEMV of this op (launched before us, still running when we started) is complete
-#endif
-}
-cudaError_t launch_rowsplit_wait(uint32_t * local_flags, uint32_t * counter, int npeers, const int * peer_rank, cudaStream_t st) {
-    ExchangeArgs a{};
-    a.npeers = npeers;
-    for (int i = 0; i < npeers; i++) a.peer_rank[i] = peer_rank[i];
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(1); cfg.blockDim = dim3(32); cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, rowsplit_wait_kernel, local_flags, counter, a);
-}
-
 // ---- LL protocol receiver: one thread per (matrix, peer row); spins on the slot until the peer's store of THIS exchange (sequence
 // number) has landed, copies the value into the local dst vector.  Launched with programmatic dependent launch right behind the
 // GEMV, so it polls while the local GEMV still runs; its completion implies the GEMV's (grid dependency at the end).

@@ -63,8 +63,6 @@ static int nccl_load() {
 
 // ------------------------------------------------------------------------------------------------ context
 struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; int32_t n_nodes = 0; uint64_t check = 0; /* second, independent hash of the node list */ };
-// a node list compiled for the decode stream kernel (decode_stream.cu); dev == nullptr: not compilable, use the graph path
-struct StreamProgram { DsStage * dev = nullptr; uint32_t * counters = nullptr; int nstages = 0; uint32_t epoch = 0; int type_mask = 0; };
 
 struct Ctx {
     uint64_t magic = 0xB200B200B200B200ull;
@@ -81,20 +79,12 @@ struct Ctx {
     const void * q_ptr = nullptr; int64_t q_K = 0, q_N = 0, q_stride = 0;
     int q_kind = 0;               // what the cached conversion of q_ptr is: 0 = q8_1 planes in act_qs / act_ds, 1 = fp16 d * q in gm_qb (dense GEMM)
     std::unordered_map<uint64_t, GraphEntry> graphs;
-    std::unordered_map<uint64_t, StreamProgram> programs;
-    int ds_grid = -1;             // CTAs of the decode stream kernel (-1: not probed yet, 0: unavailable)
     // tensor-core GEMM scratch (gemm_i8.cu): int8 activations [N][K], their block scales, unpacked q4_0 weights [M][K]
     int8_t * gm_qb = nullptr; size_t gm_qb_cap = 0;
     float *  gm_db = nullptr; size_t gm_db_cap = 0;
-    int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;
+    int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;       // exact mode only: unpacked integer weights of one MUL_MAT
     float *  gm_ws = nullptr; size_t gm_ws_cap = 0;
     float *  gm_sp = nullptr; size_t gm_sp_cap = 0;      // split-K partial results      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
-    // dense GEMM (gemm_dense.cu): dequantised fp16 copies of quantised weight matrices, keyed by the device address of the
-    // matrix's first field.  180 GB of HBM hold them beside the native weights (2 bytes per weight); without one (budget
-    // spent, or first use inside a stream capture) the weights are dequantised per call into gm_a.
-    struct Shadow { __half * p; size_t bytes; const char * src_lo, * src_hi; int type; int64_t M, K; };
-    std::unordered_map<const void *, Shadow> shadows;
-    size_t shadow_bytes = 0, shadow_budget = 0; bool shadow_budget_set = false;
     bool capturing = false;       // inside cudaStreamBeginCapture .. EndCapture: no allocation, no synchronisation
     int sms = 0;
     // row split
@@ -145,49 +135,9 @@ static int ensure_stage(Ctx * c, size_t bytes) {
     return 0;
 }
 
-// ---- fp16 weight shadows of the dense GEMM
-// B200_GEMM_MODE=exact keeps the per-block exact int8 path (gemm_i8.cu) for many-column MUL_MATs; default: dense (gemm_dense.cu)
+// B200_GEMM_MODE=exact keeps the per-block exact int8 path (gemm_i8.cu) for many-column MUL_MATs; default: dense (gemm_dense.cu),
+// which dequantises the native blocks inside the kernel -- no converted copy of any weight exists in HBM
 static bool gemm_dense_enabled() { const char * e = getenv("B200_GEMM_MODE"); return !(e && strcmp(e, "exact") == 0); }
-static void shadow_drop_range(Ctx * c, const void * lo_, size_t n) {
-    if (c->shadows.empty() || n == 0) return;
-    const char * lo = (const char *) lo_, * hi = lo + n;
-    bool any = false;
-    for (auto it = c->shadows.begin(); it != c->shadows.end(); ) {
-        if (it->second.src_lo < hi && lo < it->second.src_hi) {
-            if (!any) { cudaStreamSynchronize(c->st); any = true; }
-            cudaFree(it->second.p); c->shadow_bytes -= it->second.bytes; it = c->shadows.erase(it);
-        } else ++it;
-    }
-    if (any) c->scratch_gen++;          // captured graphs hold the shadow's address
-}
-static void shadow_drop_all(Ctx * c) { shadow_drop_range(c, nullptr, ~(size_t) 0 >> 1); }
-// the shadow of the M x K matrix whose fields start at wp (a slice of the tensor stored at [src_lo, src_hi)), built on first use;
-// nullptr: none (and none can be made now)
-static const __half * shadow_get(Ctx * c, int type, const WPtrs & wp, int64_t M, int64_t K, const void * src_lo, size_t src_bytes, bool create) {
-    auto it = c->shadows.find(wp.p[0]);
-    if (it != c->shadows.end()) {
-        if (it->second.type == type && it->second.M == M && it->second.K == K) return it->second.p;
-        if (c->capturing) return nullptr;
-        shadow_drop_range(c, it->second.src_lo, (size_t) (it->second.src_hi - it->second.src_lo));
-    }
-    if (!create || c->capturing) return nullptr;
-    if (!c->shadow_budget_set) {
-        c->shadow_budget_set = true;
-        c->shadow_budget = getenv("B200_GEMM_SHADOW_MB") ? (size_t) atoll(getenv("B200_GEMM_SHADOW_MB")) << 20 : (size_t) 64 << 30;
-    }
-    const size_t bytes = (size_t) M * K * sizeof(__half);
-    if (c->shadow_bytes + bytes > c->shadow_budget) return nullptr;
-    size_t free_b = 0, total_b = 0;
-    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < bytes + ((size_t) 4 << 30)) { cudaGetLastError(); return nullptr; }
-    Ctx::Shadow sh{};
-    if (cudaMalloc((void **) &sh.p, bytes + 256) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-    if (launch_dequant_weights_f16(type, wp, M * (K / block_elems(type)), sh.p, c->st) != cudaSuccess) { cudaGetLastError(); cudaFree(sh.p); return nullptr; }
-    c->launches++;
-    sh.bytes = bytes; sh.src_lo = (const char *) src_lo; sh.src_hi = sh.src_lo + src_bytes; sh.type = type; sh.M = M; sh.K = K;
-    c->shadows.emplace(wp.p[0], sh);
-    c->shadow_bytes += bytes;
-    return sh.p;
-}
 
 extern "C" int b200_device_count(void) {
     int n = 0;
@@ -237,12 +187,10 @@ extern "C" int b200_close(b200_handle h) {
     CTX(h);
     cudaStreamSynchronize(c->st);
     for (auto & kv : c->graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
-    for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); }
     for (int r = 0; r < 8; r++) if (c->rs_ipc[r] && c->rs_peer[r]) cudaIpcCloseMemHandle(c->rs_peer[r]);
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
-    for (auto & kv : c->shadows) cudaFree(kv.second.p);
     cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp);
     cudaStreamDestroy(c->st);
     c->magic = 0;
@@ -273,36 +221,25 @@ extern "C" int b200_malloc(b200_handle h, size_t size, void ** ptr) {
 }
 extern "C" int b200_free(b200_handle h, void * ptr) {
     CTX(h);
-    if (!c->shadows.empty()) {   // shadows of weights that live in the allocation being freed
-        typedef CUresult (*range_t)(CUdeviceptr *, size_t *, CUdeviceptr);
-        static range_t range = [] {
-            void * p = nullptr; cudaDriverEntryPointQueryResult q;
-            if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
-            return (range_t) p;
-        }();
-        CUdeviceptr lo = 0; size_t n = 0;
-        if (range && range(&lo, &n, (CUdeviceptr) (uintptr_t) ptr) == CUDA_SUCCESS) shadow_drop_range(c, (const void *) (uintptr_t) lo, n);
-        else shadow_drop_all(c);
-    }
     CU(cudaStreamSynchronize(c->st)); CU(cudaFree(ptr)); return 0;
 }
 extern "C" int b200_memcpy_h2d(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2h(b200_handle h, void * d, const void * s, size_t n) {
     CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_h2d_async(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2h_async(b200_handle h, void * d, const void * s, size_t n) {
     CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2d(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToDevice, c->st)); return 0;
 }
 extern "C" int b200_memset(b200_handle h, void * d, int v, size_t n) {
-    CTX(h); c->q_ptr = nullptr; shadow_drop_range(c, d, n); CU(cudaMemsetAsync(d, v, n, c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr; CU(cudaMemsetAsync(d, v, n, c->st)); return 0;
 }
 extern "C" int b200_host_alloc(b200_handle h, size_t size, void ** ptr) { CTX(h); CU(cudaMallocHost(ptr, size ? size : 1)); return 0; }
 extern "C" int b200_host_free(b200_handle h, void * ptr) { CTX(h); CU(cudaFreeHost(ptr)); return 0; }
@@ -322,7 +259,6 @@ extern "C" int b200_weights_upload(b200_handle h, int32_t type, void * base, int
     if (!is_qweight(type)) return fail(B200_EINVAL, "weights_upload: type %d is not a quantised weight type", type);
     if (first < 0 || n < 0 || first + n > T) return fail(B200_EINVAL, "weights_upload: block range [%lld,+%lld) outside %lld", (long long) first, (long long) n, (long long) T);
     const size_t bytes = (size_t) n * block_bytes(type);
-    shadow_drop_range(c, base, (size_t) T * block_bytes(type));
     int rc = ensure_stage(c, bytes); if (rc) return rc;
     CU(cudaMemcpyAsync(c->stage, host, bytes, cudaMemcpyHostToDevice, c->st));
     CU(launch_repack(type, true, (uint8_t *) base, T, first, n, c->stage, c->st)); c->launches++;
@@ -501,19 +437,13 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
             a.ll_slots = (uint2 *) (c->rs_heap + 4096); a.ll_count = (const uint32_t *) (c->rs_heap + 320); a.ll_op = c->rs_ops; a.ll_rank = c->rank;
             c->ll_nmat = n; c->ll_op = c->rs_ops;
             for (int i = 0; i < n; i++) { a.ll_off[i] = c->ll_off[i]; c->ll_M[i] = (int) rows[i]; c->ll_dst[i] = (float *) dsts[i] - (int64_t) c->rank * rows[i]; }
-            a.rs_signal = 0;
             return 0;
         }
     }
-    // flag protocol: a separate 32-thread exchange kernel after the GEMV (signal + wait).  B200_RS_INLINE=1: the GEMV's last CTA
-    // signals (heap + 260: CTA arrivals, + 264: ops signalled) and a PDL wait kernel follows -- measured SLOWER on 2 GPUs
-    // (9.2 vs 7.6 ms per Llama-3-70B token: the per-CTA fences wait for NVLink store acknowledgements), kept for study
-    static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
-    a.rs_signal = sep ? 0 : 1; a.rs_ctrl = (uint32_t *) (c->rs_heap + 260);
+    // flag protocol: a separate 32-thread exchange kernel after the op (signal + wait), launched by rs_exchange
     return 0;
 }
 static bool act_fusion_enabled() { static const bool on = !(getenv("B200_GEMM_ACTFUSE") && atoi(getenv("B200_GEMM_ACTFUSE")) == 0); return on; }
-static bool rs_flag_exchange_separate() { return !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0); }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
     if (c->ll_nmat > 0) {
@@ -527,9 +457,7 @@ static int rs_exchange(Ctx * c) {
     }
     long long addr[7]; int ranks[7]; int np = 0;
     for (int r = 0; r < c->world; r++) if (r != c->rank) { addr[np] = (long long) (uintptr_t) (c->rs_peer[r] + 4 * c->rank); ranks[np] = r; np++; }
-    static const bool sep = !(getenv("B200_RS_INLINE") && atoi(getenv("B200_RS_INLINE")) != 0);
-    if (sep) { CU(launch_rowsplit_exchange((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, addr, ranks, c->st)); }
-    else     { CU(launch_rowsplit_wait((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, ranks, c->st)); }
+    CU(launch_rowsplit_exchange((uint32_t *) c->rs_heap, (uint32_t *) (c->rs_heap + 256), np, addr, ranks, c->st));
     c->launches++;
     return 0;
 }
@@ -560,15 +488,6 @@ static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1)
         rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
         const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
         if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
-        bool all = true;                 // every weight matrix of the tensor has (or now gets) its fp16 shadow?
-        WPtrs wp0{};
-        if (wptrs_of(s0, &wp0) == 0 && ((uintptr_t) wp0.p[0] & 15) == 0)
-            for (int64_t i03 = 0; i03 < s0->ne[3]; i03++)
-            for (int64_t i02 = 0; i02 < s0->ne[2]; i02++)
-                all &= shadow_get(c, s0->type, wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]), M, K, s0->w_base,
-                                  (size_t) s0->w_blocks * block_bytes(s0->type), true) != nullptr;
-        else all = false;
-        if (!all) { rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc; }
         return 0;
     }
     rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
@@ -594,13 +513,12 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
     WPtrs wp0{};
     if (q) { rc = wptrs_of(s0, &wp0); if (rc) return rc; }
     const int64_t NB = K / 32;
-    const bool fuseq = q && N == 1 && gemv_fuseq_enabled();
     const int gemm_min_n = gemm_min_cols(s0->type);
     const bool use_gemm = q && N >= gemm_min_n && gemm_min_n > 0 && K % 32 == 0 &&
                           M < 0x7fffffff && N < 0x7fffffff && K < 0x7fffffff && (!fa || N > 1) && ((uintptr_t) wp0.p[0] & 15) == 0 &&
-                          (!c->rs_on || (gemm_dense_enabled() && rs_flag_exchange_separate()));   // row split: dense path + slice push
+                          (!c->rs_on || gemm_dense_enabled());   // row split: dense path + slice push
     if (fa && N > 1 && !(use_gemm && gemm_dense_enabled())) return fail(B200_EINVAL, "fused residual ADD needs the dense GEMM path");
-    if (q && !fuseq) { rc = ensure_act(c, NB * N); if (rc) return rc; }
+    if (q) { rc = ensure_act(c, NB * N); if (rc) return rc; }
     const int64_t dcs = d->nb[1] / 4;
     for (int64_t i13 = 0; i13 < s1->ne[3]; i13++)
     for (int64_t i12 = 0; i12 < s1->ne[2]; i12++) {
@@ -617,12 +535,6 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 CU(launch_dequant_act_f16((const float *) x, s1->nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
                 c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 1;
             }
-            const __half * A = shadow_get(c, s0->type, wp, M, K, s0->w_base, (size_t) s0->w_blocks * block_bytes(s0->type), true);
-            if (!A) {
-                rc = ensure_buf(c, &c->gm_a, &c->gm_a_cap, (size_t) M * K * 2); if (rc) return rc;
-                CU(launch_dequant_weights_f16(s0->type, wp, M * (K / block_elems(s0->type)), (__half *) c->gm_a, c->st)); c->launches++;
-                A = (const __half *) c->gm_a;
-            }
             const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
             if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
             if (fa && ksp <= 1) return fail(B200_EINVAL, "fused residual ADD on a dense MUL_MAT without split-K");      // (can_fuse_add_dense checks)
@@ -630,7 +542,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             // op has read gm_qb by then), and the next op finds its activations converted.  Only where gm_qb already has the room (no
             // reallocation under a capture) and inside a node list.
             const bool next_act = fa && c->in_graph && M % 32 == 0 && c->gm_qb_cap >= (size_t) N * M * 2 && act_fusion_enabled();
-            CU(launch_gemm_dense(A, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st,
+            CU(launch_gemm_dense(s0->type, wp, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st,
                                  fa ? fa->src : nullptr, fa ? fa->dst : nullptr, next_act ? c->gm_qb : nullptr));
             c->launches += 1 + (ksp > 1 ? 1 : 0);
             if (next_act) { c->q_ptr = fa->dst; c->q_K = M; c->q_N = N; c->q_stride = M * 4; c->q_kind = 1; }
@@ -704,16 +616,10 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             a.nmat = 1; a.K = K; a.dcs = dcs;
             a.mat[0].w = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
             a.mat[0].M = M;
-            if (fuseq) {
-                a.mat[0].dst = y;
-                if (fa) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
-                a.x = (const float *) x; a.x_col_stride = s1->nb[1];
-                CU(launch_gemv2(s0->type, a, (int) N, true, c->st)); c->launches++;
-            } else {
+            {
                 if (fa && N == 1) { a.mat[0].add_src = fa->src; a.mat[0].add_dst = fa->dst; }
                 { const void * dp[1] = {y}; const int64_t db_[1] = {(N - 1) * dcs * 4 + M * 4}; const int64_t rw[1] = {M};
                   rc = rs_fill(c, a, dp, db_, 1, rw, N == 1 && s1->ne[2] == 1 && s1->ne[3] == 1); if (rc) return rc; }
-                const int rs_signal = a.rs_signal;
                 bool done = false;
                 if (N == 1) {                               // one column: persistent ring GEMV, quantises the activations itself (gemv6.cu)
                     a.mat[0].dst = y; a.x = (const float *) x; a.x_col_stride = s1->nb[1];
@@ -736,10 +642,9 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 if (!done)
                 for (int64_t c0 = 0; c0 < N; c0 += 8) {
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
-                    a.rs_signal = (c0 + 8 >= N && i12 == s1->ne[2] - 1 && i13 == s1->ne[3] - 1) ? rs_signal : 0;   // once per op
                     a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
                     a.mat[0].dst = y + c0 * dcs;
-                    CU(launch_gemv2(s0->type, a, nc, false, c->st)); c->launches++;
+                    CU(launch_gemv2(s0->type, a, nc, c->st)); c->launches++;
                 }
             }
         } else {
@@ -821,7 +726,7 @@ static bool is_dense_mulmat(Ctx * c, const b200_node & n) {
 // many-column MUL_MAT on the dense GEMM with split-K, followed by the ADD that consumes its dst (wo / down + residual in prefill): the
 // split-K reduce writes both results, the ADD launch disappears
 static bool can_fuse_add_dense(Ctx * c, const b200_node & mm, const b200_node & ad, FusedAdd * fa) {
-    if (!gemm_dense_enabled() || !gemm_dense_pair() || !is_dense_mulmat(c, mm) || ad.dst.op != B200_OP_ADD) return false;
+    if (!gemm_dense_enabled() || !is_dense_mulmat(c, mm) || ad.dst.op != B200_OP_ADD) return false;
     const int64_t K = mm.src0.ne[0], M = mm.src0.ne[1], N = mm.src1.ne[1];
     if (gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms) <= 1) return false;
     auto plain = [&](const b200_tensor & t) { return t.type == T_F32 && t.ne[0] == M && t.ne[1] == N && t.ne[2] == 1 && t.ne[3] == 1 && t.nb[0] == 4 && t.nb[1] == M * 4; };
@@ -837,7 +742,7 @@ static bool can_fuse_add_dense(Ctx * c, const b200_node & mm, const b200_node & 
     return true;
 }
 static int dense_group_len(Ctx * c, const b200_node * nodes, int i, int n) {
-    if (!gemm_dense_enabled() || !gemm_dense_pair() || !is_dense_mulmat(c, nodes[i])) return 1;
+    if (!gemm_dense_enabled() || !is_dense_mulmat(c, nodes[i])) return 1;
     const b200_node & a = nodes[i];
     const int64_t K = a.src0.ne[0], N = a.src1.ne[1];
     const int64_t xspan = (N - 1) * a.src1.nb[1] + K * 4;
@@ -846,7 +751,7 @@ static int dense_group_len(Ctx * c, const b200_node * nodes, int i, int n) {
     int len = 1;
     while (len < 3 && i + len < n) {
         const b200_node & b = nodes[i + len];
-        if (!is_dense_mulmat(c, b) || b.src1.data != a.src1.data || b.src0.ne[0] != K || b.src1.ne[1] != N || b.src1.nb[1] != a.src1.nb[1]) break;
+        if (!is_dense_mulmat(c, b) || b.src0.type != a.src0.type || b.src1.data != a.src1.data || b.src0.ne[0] != K || b.src1.ne[1] != N || b.src1.nb[1] != a.src1.nb[1]) break;
         // no member may write what another member (or the shared activations) occupies
         bool clash = overlap(b.dst.data, dspan(b), a.src1.data, xspan);
         for (int j = 0; j < len && !clash; j++) clash = overlap(b.dst.data, dspan(b), nodes[i + j].dst.data, dspan(nodes[i + j]));
@@ -858,20 +763,12 @@ static int dense_group_len(Ctx * c, const b200_node * nodes, int i, int n) {
 static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, int64_t row_off_dst, const FusedAdd * fa);
 static int mulmat_dense_group_dev(Ctx * c, const b200_node * nodes, int len) {
     const int64_t K = nodes[0].src0.ne[0], N = nodes[0].src1.ne[1];
-    const __half * A[3]; float * out[3]; long long ocs[3]; int Ms[3];
-    bool ok = true;
-    for (int j = 0; j < len && ok; j++) {
+    WPtrs A[3]; float * out[3]; long long ocs[3]; int Ms[3];
+    for (int j = 0; j < len; j++) {
         b200_tensor d = nodes[j].dst;
         int rc = mulmat_check(&nodes[j].src0, &nodes[j].src1, &d); if (rc) return rc;
-        WPtrs wp; rc = wptrs_of(&nodes[j].src0, &wp); if (rc) return rc;
-        const b200_tensor & s0 = nodes[j].src0;
-        A[j] = ((uintptr_t) wp.p[0] & 15) ? nullptr : shadow_get(c, s0.type, wp, s0.ne[1], K, s0.w_base, (size_t) s0.w_blocks * block_bytes(s0.type), true);
-        ok = A[j] != nullptr;
-        out[j] = (float *) d.data; ocs[j] = d.nb[1] / 4; Ms[j] = (int) s0.ne[1];
-    }
-    if (!ok) {          // no room for a shadow: the members go one by one (weights dequantised per call)
-        for (int j = 0; j < len; j++) { b200_tensor d = nodes[j].dst; int rc = mulmat_dev(c, &nodes[j].src0, &nodes[j].src1, &d, 0, nullptr); if (rc) return rc; }
-        return 0;
+        rc = wptrs_of(&nodes[j].src0, &A[j]); if (rc) return rc;
+        out[j] = (float *) d.data; ocs[j] = d.nb[1] / 4; Ms[j] = (int) nodes[j].src0.ne[1];
     }
     int rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
     const b200_tensor & s1 = nodes[0].src1;
@@ -880,7 +777,7 @@ static int mulmat_dense_group_dev(Ctx * c, const b200_node * nodes, int len) {
         CU(launch_dequant_act_f16((const float *) s1.data, s1.nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
         c->q_ptr = s1.data; c->q_K = K; c->q_N = N; c->q_stride = s1.nb[1]; c->q_kind = 1;
     }
-    CU(launch_gemm_dense_group(A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->st)); c->launches++;
+    CU(launch_gemm_dense_group(nodes[0].src0.type, A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->st)); c->launches++;
     return 0;           // (dense_group_len made sure that no dst touches the activations the cached conversion came from)
 }
 
@@ -900,11 +797,6 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     }
     { int64_t rw[3]; for (int j = 0; j < len; j++) rw[j] = a.mat[j].M;
       int rc = rs_fill(c, a, dsts, dbytes, len, rw, true); if (rc) return rc; }
-    if (gemv_fuseq_enabled()) {
-        a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
-        CU(launch_gemv2(nodes[0].src0.type, a, 1, true, c->st)); c->launches++;
-        return 0;
-    }
     {   // persistent ring GEMV over the whole group, activations quantised inside the kernel (gemv6.cu)
         a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
         cudaError_t e6 = cudaSuccess;
@@ -922,117 +814,11 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
         c->q_ptr = x; c->q_K = K; c->q_N = 1; c->q_stride = nodes[0].src1.nb[1]; c->q_kind = 0;
     }
     a.act = ActView{c->act_qs, c->act_ds, NB};
-    CU(launch_gemv2(nodes[0].src0.type, a, 1, false, c->st)); c->launches++;
+    CU(launch_gemv2(nodes[0].src0.type, a, 1, c->st)); c->launches++;
     { int rc2 = rs_exchange(c); if (rc2) return rc2; }
     for (int j = 0; j < len; j++)
         if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4, c->q_ptr, K * 4)) c->q_ptr = nullptr;
     return 0;
-}
-
-// ------------------------------------------------------------------------------------------------ decode stream program
-// Compile a node list into stages for decode_stream.cu.  Returns false when any node falls outside what the stream
-// kernel takes (then the per-node kernels run, as a CUDA graph): it takes vector MUL_MATs (one f32 column) over
-// REPACKED q4_0/q8_0/q4_K/q6_K weights with K <= DS_KMAX, and contiguous same-shape f32 vector ADDs.
-struct Span { const char * p; int64_t n; };
-static bool spans_clash(const std::vector<Span> & a, const std::vector<Span> & b) {
-    for (const Span & x : a) for (const Span & y : b) if (x.n > 0 && y.n > 0 && overlap(x.p, x.n, y.p, y.n)) return true;
-    return false;
-}
-static bool ds_fill_gemv(DsStage & st, const b200_node * nodes, int len, const FusedAdd * fa) {
-    const b200_tensor & w0 = nodes[0].src0;
-    const int type = w0.type;
-    const int64_t K = w0.ne[0];
-    const int be = block_elems(type);
-    if (K <= 0 || K > DS_KMAX || K % 32 || K % be) return false;
-    if ((uintptr_t) nodes[0].src1.data & 15) return false;
-    const WFields wf = wfields(type);
-    st = DsStage{};
-    st.kind = DS_GEMV; st.type = type; st.nops = len; st.K = (int) K;
-    st.steps = (int) (K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
-    st.nfields = wf.n;
-    st.x = (const float *) nodes[0].src1.data;
-    const int64_t bpr = K / be;                                    // blocks per row
-    for (int f = 0; f < wf.n; f++) {
-        st.rowbytes[f] = (int) (bpr * wf.size[f]);
-        st.flead[f] = (st.rowbytes[f] % 16) != 0;
-        if (st.flead[f]) return false;      // rows of a 2-byte scale array that are not 16-B multiples: per-node kernels
-    }
-    int R = 8;
-    for (; R >= 1; R >>= 1) {
-        int off = 0;
-        for (int f = 0; f < wf.n; f++) { st.foff[f] = off; off += ((R * st.rowbytes[f] + (st.flead[f] ? 16 : 0) + 15) & ~15); off = (off + 127) & ~127; }
-        if (off <= DS_SLOT_BYTES) break;
-    }
-    if (R < 1) return false;
-    // consumer mapping (decode_stream.cu): nsl K-slices of 32 lanes; up to 16 warps = nsl slices x rg row groups
-    {
-        const int nsl = (st.steps + 31) / 32;
-        if (nsl > 32) return false;
-        if (nsl > 16) { while (R > 1) R >>= 1; st.rw = 1; }             // two slices per warp, one row per slot
-        else {
-            int rgc = 16 / nsl, p2 = 1; while (p2 * 2 <= rgc) p2 *= 2;
-            while (R / (R < p2 ? R : p2) > 2) R >>= 1;                 // at most 2 rows of a slot per warp
-            st.rw = R / (R < p2 ? R : p2);
-            if (st.rw == 2 && type != T_Q4_0) { R >>= 1; st.rw = 1; }   // only the q4_0 kernels carry the 2-row variant
-        }
-        int off = 0;
-        for (int f = 0; f < wf.n; f++) { st.foff[f] = off; off += ((R * st.rowbytes[f] + (st.flead[f] ? 16 : 0) + 15) & ~15); off = (off + 127) & ~127; }
-    }
-    st.R = R;
-    for (int j = 0; j < len; j++) {
-        const b200_tensor & w = nodes[j].src0;
-        if (w.ne[1] <= 0 || w.ne[1] > 0x7fffffff) return false;
-        WPtrs wp; if (wptrs_of(&w, &wp)) return false;
-        for (int f = 0; f < wf.n; f++) {
-            if (!st.flead[f] && ((uintptr_t) wp.p[f] & 15)) return false;
-            st.op[j].f[f] = wp.p[f];
-        }
-        st.op[j].M = (int) w.ne[1];
-        st.op[j].dst = (float *) nodes[j].dst.data;
-    }
-    if (fa) { st.op[0].add_src = fa->src; st.op[0].add_dst = fa->dst; }
-    return true;
-}
-static bool ds_compile(const b200_node * nodes, int n, std::vector<DsStage> & out) {
-    out.clear();
-    std::vector<Span> reads_since, writes_since;                   // of the stages since the last grid-wide wait
-    for (int i = 0; i < n; ) {
-        const b200_node & nd = nodes[i];
-        DsStage st{};
-        std::vector<Span> rd, wr;
-        int used = 1;
-        if (nd.dst.op == B200_OP_NONE) { i++; continue; }
-        if (nd.dst.op == B200_OP_MUL_MAT) {
-            if (!is_vec_mulmat(nd) || mulmat_check(&nd.src0, &nd.src1, &nd.dst)) return false;
-            if (!is_vec_f32(nd.dst, nd.src0.ne[1]) || nd.src1.nb[0] != 4) return false;
-            FusedAdd fa; bool fused = false;
-            int gl = group_len(nodes, i, n);
-            if (gl == 1 && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fa)) fused = true;
-            for (int j = 1; j < gl; j++) if (mulmat_check(&nodes[i + j].src0, &nodes[i + j].src1, &nodes[i + j].dst)) return false;
-            if (!ds_fill_gemv(st, nodes + i, gl, fused ? &fa : nullptr)) return false;
-            used = fused ? 2 : gl;
-            rd.push_back({(const char *) st.x, (int64_t) st.K * 4});
-            for (int j = 0; j < gl; j++) wr.push_back({(const char *) st.op[j].dst, (int64_t) st.op[j].M * 4});
-            if (fused) { rd.push_back({(const char *) fa.src, (int64_t) st.op[0].M * 4}); wr.push_back({(const char *) fa.dst, (int64_t) st.op[0].M * 4}); }
-        } else if (nd.dst.op == B200_OP_ADD) {
-            const int64_t ne = nd.dst.ne[0];
-            if (!is_vec_f32(nd.dst, ne) || !is_vec_f32(nd.src0, ne) || !is_vec_f32(nd.src1, ne) || ne % 4 || ne > 0x7fffffff) return false;
-            if (nd.src0.type != T_F32 || (((uintptr_t) nd.src0.data | (uintptr_t) nd.src1.data | (uintptr_t) nd.dst.data) & 15)) return false;
-            st.kind = DS_ADD; st.x = (const float *) nd.src0.data;
-            st.op[0].add_src = (const float *) nd.src1.data; st.op[0].dst = (float *) nd.dst.data; st.op[0].M = (int) ne;
-            rd.push_back({(const char *) nd.src0.data, ne * 4}); rd.push_back({(const char *) nd.src1.data, ne * 4});
-            wr.push_back({(const char *) nd.dst.data, ne * 4});
-        } else return false;
-        // RAW, WAR and WAW against every stage that may still be running somewhere on the grid
-        const bool hazard = spans_clash(rd, writes_since) || spans_clash(wr, reads_since) || spans_clash(wr, writes_since);
-        st.wait_prev = !out.empty() && hazard;
-        if (st.wait_prev) { reads_since.clear(); writes_since.clear(); }
-        reads_since.insert(reads_since.end(), rd.begin(), rd.end());
-        writes_since.insert(writes_since.end(), wr.begin(), wr.end());
-        out.push_back(st);
-        i += used;
-    }
-    return !out.empty();
 }
 
 // ---- host-pointer tensors: stage in, run, stage out, synchronise (FastRPC semantics: dsptensor.data is host memory)
@@ -1187,52 +973,6 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     const bool keyed = g_caller_key != 0;
     const uint64_t key = keyed ? (g_caller_key * 0x9e3779b97f4a7c15ull) ^ salt ^ 0x5bd1e995 : fnv1a(nodes, sizeof(b200_node) * (size_t) n, salt);
     const uint64_t check = keyed ? g_caller_key : fnv1a(nodes, sizeof(b200_node) * (size_t) n, 0x243f6a8885a308d3ull);
-    // ---- first choice: the whole list as one persistent launch (decode_stream.cu)
-    // opt-in while it is slower than the CUDA-graph replay of the per-node kernels (DESIGN.md has the trace numbers)
-    static const bool stream_on = getenv("B200_STREAM") && atoi(getenv("B200_STREAM")) != 0;
-    if ((stream_on || use_cuda_graph == 3) && use_cuda_graph != 2 && c->ds_grid != 0 && !c->rs_on) {
-        if (c->ds_grid < 0) c->ds_grid = ds_grid(c->dev);
-        auto ps = c->programs.find(key);
-        if (ps == c->programs.end() && c->ds_grid > 0) {
-            StreamProgram sp;
-            std::vector<DsStage> stages;
-            if (ds_compile(nodes, n, stages)) {
-                sp.nstages = (int) stages.size();
-                for (const DsStage & g : stages) if (g.kind == DS_GEMV) sp.type_mask |= ds_type_bit(g.type) | (g.steps > 512 ? 16 : 0);
-                CU(cudaMalloc((void **) &sp.dev, stages.size() * sizeof(DsStage)));
-                CU(cudaMalloc((void **) &sp.counters, stages.size() * sizeof(uint32_t)));
-                CU(cudaMemcpyAsync(sp.dev, stages.data(), stages.size() * sizeof(DsStage), cudaMemcpyHostToDevice, c->st));
-                CU(cudaMemsetAsync(sp.counters, 0, stages.size() * sizeof(uint32_t), c->st));
-                CU(cudaStreamSynchronize(c->st));            // `stages` is pageable host memory
-            }
-            if (c->programs.size() > 64) { CU(cudaStreamSynchronize(c->st)); for (auto & kv : c->programs) { cudaFree(kv.second.dev); cudaFree(kv.second.counters); } c->programs.clear(); }
-            ps = c->programs.emplace(key, sp).first;
-        }
-        if (ps != c->programs.end() && ps->second.dev) {
-            StreamProgram & sp = ps->second;
-            sp.epoch++;
-            // development aid: B200_STREAM_TRACE=<file> dumps the per-(CTA, stage) clocks of every launch (synchronous!)
-            static const char * trace_path = getenv("B200_STREAM_TRACE");
-            long long * trace = nullptr;
-            const size_t trace_n = (size_t) c->ds_grid * sp.nstages * 4;
-            if (trace_path) { CU(cudaMalloc((void **) &trace, trace_n * sizeof(long long))); CU(cudaMemsetAsync(trace, 0, trace_n * sizeof(long long), c->st)); }
-            CU(launch_decode_stream(sp.dev, sp.nstages, sp.counters, sp.epoch, c->ds_grid, sp.type_mask, trace, c->st));
-            if (trace_path) {
-                std::vector<long long> hbuf(trace_n);
-                CU(cudaMemcpyAsync(hbuf.data(), trace, trace_n * sizeof(long long), cudaMemcpyDeviceToHost, c->st));
-                CU(cudaStreamSynchronize(c->st));
-                cudaFree(trace);
-                if (FILE * fp = fopen(trace_path, "wb")) {
-                    int hdr[2] = { c->ds_grid, sp.nstages };
-                    fwrite(hdr, sizeof(int), 2, fp); fwrite(hbuf.data(), sizeof(long long), trace_n, fp); fclose(fp);
-                }
-            }
-            c->launches++;
-            c->q_ptr = nullptr;
-            return 0;
-        }
-    }
-    if (use_cuda_graph == 3) return fail(B200_ENOTSUP, "graph_compute: this node list does not compile to the decode stream kernel");
     auto it = c->graphs.find(key);
     if (it != c->graphs.end() && (it->second.n_nodes != n || it->second.check != check)) {        // key collision: never replay another list's graph
         cudaGraphExecDestroy(it->second.exec); c->graphs.erase(it); it = c->graphs.end();

@@ -72,7 +72,7 @@ template <> struct WT<T_Q4_0> {
     static __device__ __forceinline__ Frag load(const WPtrs & w, int64_t blk) {
         Frag f; f.q = ldg_stream(w.p[0] + blk * 16); f.d = ldg_stream_h(w.p[1] + blk * 2); return f;
     }
-    // same fragment from a shared-memory copy of the SoA fields (decode_stream.cu); plain loads -> LDS
+    // same fragment from a shared-memory copy of the SoA fields (gemv5 / gemv5c / gemv5n tiles); plain loads -> LDS
     static __device__ __forceinline__ Frag loads(const WPtrs & w, int blk) {
         Frag f; f.q = *(const uint4 *) (w.p[0] + blk * 16); f.d = __half2float(*(const __half *) (w.p[1] + blk * 2)); return f;
     }
@@ -240,39 +240,6 @@ __device__ __forceinline__ int dot16_hi16(const uint4 & q, const uint4 & a) {   
     s = dp4a_u8s8(q.z & 0xF0F0F0F0u, a.z, s); return dp4a_u8s8(q.w & 0xF0F0F0F0u, a.w, s);
 }
 
-// ---- fused activation quantisation (GEMV with f32 activations): a lane quantises exactly the q8_1 blocks of ITS step
-// from the f32 vector, bit-identical to quantize_row_q8_1_ref (ggml-quants.c:220-253): d = amax / 127, id = 1 / d,
-// q = roundf(x * id), the scale rounded through fp16.  No shared memory, no other lane involved (q6_K: the lane pair
-// that shares a block exchanges its half-block amax by one shuffle).
-struct QBlk { uint4 lo, hi; float d; int isum0, isum1; };      // planes 0..15 / 16..31, scale, plane sums
-__device__ __forceinline__ float amax4(const float4 v) { return fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))); }
-__device__ __forceinline__ uint32_t quant4(const float4 v, const float id, int & sum) {
-    const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
-    const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
-    sum += q0 + q1 + q2 + q3;
-    return (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
-}
-__device__ __forceinline__ void scale_of(const float amax, float & d16, float & id) {
-    const float d = __fdiv_rn(amax, 127.0f);
-    id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    d16 = __half2float(__float2half_rn(d));
-}
-// one whole 32-element block at x (16-B aligned)
-__device__ __forceinline__ QBlk quant_block32(const float * x) {
-    const float4 * p = (const float4 *) x;
-    float4 v[8];
-    #pragma unroll
-    for (int i = 0; i < 8; i++) v[i] = p[i];
-    float amax = 0.f;
-    #pragma unroll
-    for (int i = 0; i < 8; i++) amax = fmaxf(amax, amax4(v[i]));
-    QBlk r; float id; scale_of(amax, r.d, id);
-    r.isum0 = 0; r.isum1 = 0;
-    r.lo = make_uint4(quant4(v[0], id, r.isum0), quant4(v[1], id, r.isum0), quant4(v[2], id, r.isum0), quant4(v[3], id, r.isum0));
-    r.hi = make_uint4(quant4(v[4], id, r.isum1), quant4(v[5], id, r.isum1), quant4(v[6], id, r.isum1), quant4(v[7], id, r.isum1));
-    return r;
-}
-
 template <int TYPE> struct WR;
 
 template <> struct WR<T_Q4_0> {
@@ -281,10 +248,6 @@ template <> struct WR<T_Q4_0> {
         Act r; r.a0 = a.p0[s]; r.a1 = a.p1[s];
         const ADesc ad = load_adesc(a.ds + s); r.d = ad.d; r.isum8 = 8 * (ad.isum0 + ad.isum1);
         return r;
-    }
-    static __device__ __forceinline__ Act quant_act(const float * x, int s, int) {
-        const QBlk b = quant_block32(x + s * 32);
-        Act r; r.a0 = b.lo; r.a1 = b.hi; r.d = b.d; r.isum8 = 8 * (b.isum0 + b.isum1); return r;
     }
     static __device__ __forceinline__ float dot(const WT<T_Q4_0>::Frag & f, const Act & a) {
         const int sumi = dot16_lo(f.q, a.a0) + (dot16_hi16(f.q, a.a1) >> 4) - a.isum8;
@@ -296,10 +259,6 @@ template <> struct WR<T_Q8_0> {
     struct Act { uint4 a0, a1; float d; };
     static __device__ __forceinline__ Act load_act(const ActCol & a, int s) {
         Act r; r.a0 = a.p0[s]; r.a1 = a.p1[s]; r.d = load_adesc(a.ds + s).d; return r;
-    }
-    static __device__ __forceinline__ Act quant_act(const float * x, int s, int) {
-        const QBlk b = quant_block32(x + s * 32);
-        Act r; r.a0 = b.lo; r.a1 = b.hi; r.d = b.d; return r;
     }
     static __device__ __forceinline__ float dot(const WT<T_Q8_0>::Frag & f, const Act & a) {
         const int sumi = dot16_ss(f.q0, a.a0) + dot16_ss(f.q1, a.a1);
@@ -314,12 +273,6 @@ template <> struct WR<T_Q4_K> {
         r.a00 = a.p0[b0]; r.a01 = a.p1[b0]; r.a10 = a.p0[b1]; r.a11 = a.p1[b1];
         const ADesc x = load_adesc(a.ds + b0), y = load_adesc(a.ds + b1);
         r.d0 = x.d; r.d1 = y.d; r.isum0 = x.isum0 + x.isum1; r.isum1 = y.isum0 + y.isum1;
-        return r;
-    }
-    static __device__ __forceinline__ Act quant_act(const float * x, int s, int) {
-        const QBlk b0 = quant_block32(x + s * 64), b1 = quant_block32(x + s * 64 + 32);
-        Act r; r.a00 = b0.lo; r.a01 = b0.hi; r.a10 = b1.lo; r.a11 = b1.hi;
-        r.d0 = b0.d; r.d1 = b1.d; r.isum0 = b0.isum0 + b0.isum1; r.isum1 = b1.isum0 + b1.isum1;
         return r;
     }
     // s = step index within the row (only s & 3 matters: which 64-element chunk of the super-block)
@@ -347,25 +300,6 @@ template <> struct WR<T_Q6_K> {
             r.a[q] = pl[sbh + q];
             const ADesc ad = load_adesc(a.ds + sbh + q);
             r.d[q] = ad.d; r.isum32[q] = 32 * (j ? ad.isum1 : ad.isum0);
-        }
-        return r;
-    }
-    // step s = (super-block s/4, half h, j): the four 16-element runs at 128h + 32r + 16j are plane j of the q8_1 blocks
-    // 8 sb + 4h + r; lane s ^ 1 (the neighbour lane, same warp) holds the other plane of the same four blocks.
-    // `live`: the partner shuffle needs every lane of the warp to take part, lanes past the row end pass a valid s.
-    static __device__ __forceinline__ Act quant_act(const float * x, int s, int) {
-        const int sb = s >> 2, h = (s & 3) >> 1, j = s & 1;
-        Act r;
-        #pragma unroll
-        for (int q = 0; q < 4; q++) {
-            const float4 * p = (const float4 *) (x + sb * 256 + 128 * h + 32 * q + 16 * j);
-            const float4 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
-            float amax = fmaxf(fmaxf(amax4(v0), amax4(v1)), fmaxf(amax4(v2), amax4(v3)));
-            amax = fmaxf(amax, __shfl_xor_sync(__activemask(), amax, 1));       // the block's other half (pairs leave the loop together)
-            float id; scale_of(amax, r.d[q], id);
-            int sum = 0;
-            r.a[q] = make_uint4(quant4(v0, id, sum), quant4(v1, id, sum), quant4(v2, id, sum), quant4(v3, id, sum));
-            r.isum32[q] = 32 * sum;
         }
         return r;
     }

@@ -119,12 +119,8 @@ B200_API int b200_pool_2d(b200_handle h, const b200_tensor * src, b200_tensor * 
 
 /* a whole node list in one call (graph_compute, ggml-hexagon.cpp:5555-5574); asynchronous.
  * use_cuda_graph = 0: one launch per node (fused where adjacent nodes allow).
- * use_cuda_graph = 1: replayable fast path, cached per distinct node list: the per-node launches are captured once as a
- *                     CUDA graph and replayed.  With B200_STREAM=1 in the environment a list made only of vector MUL_MATs
- *                     (one f32 column, REPACKED weights) and contiguous vector ADDs is instead compiled into ONE persistent
- *                     cooperative launch that streams all weights through shared memory (decode_stream.cu).
- * use_cuda_graph = 2: CUDA-graph replay only.
- * use_cuda_graph = 3: decode stream kernel only; B200_ENOTSUP if the list does not compile to it. */
+ * use_cuda_graph != 0: replayable fast path, cached per distinct node list: the per-node launches are captured once as a CUDA graph
+ *                     (programmatic dependent launch edges) and replayed. */
 B200_API int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_t n_nodes, int32_t use_cuda_graph);
 /* the same, for a caller that keeps its own cache of marshalled node lists (the ggml plugin): `key` != 0 names this exact list --
  * the caller guarantees one key never stands for two different lists -- so the library does not hash the descriptors again */
