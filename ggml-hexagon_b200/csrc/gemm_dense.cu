@@ -183,6 +183,7 @@ struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // what one thread kee
 template <int TYPE> struct GdCvt;
 // q4_0: one 16-byte block = the thread's 32 elements (low nibbles = elements 0..15, high = 16..31); y = d * (q - 8)
 template <> struct GdCvt<T_Q4_0> {
+    static constexpr int DEPTH = 6;
     static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long blk = row * (K >> 5) + ks * 2 + hk;
         r.a = ldg_stream(w[0] + blk * 16);
@@ -198,6 +199,7 @@ template <> struct GdCvt<T_Q4_0> {
 };
 // q8_0: one 32-byte block; y = d * q, q signed: q + 128 is the unsigned byte q ^ 0x80
 template <> struct GdCvt<T_Q8_0> {
+    static constexpr int DEPTH = 4;
     static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long blk = row * (K >> 5) + ks * 2 + hk;
         r.a = ldg_stream(w[0] + blk * 32); r.b = ldg_stream(w[0] + blk * 32 + 16);
@@ -214,6 +216,7 @@ template <> struct GdCvt<T_Q8_0> {
 // q4_K: the slab is 32 bytes of super-block ks / 4, sub-blocks 2j (low nibbles, hk = 0) and 2j + 1 (high nibbles), j = ks % 4;
 // y = (d * sc_g) * q - dmin * m_g, scales / mins 6-bit packed in the 16-byte header (get_scale_min_k4, ggml-quants.c:631-638)
 template <> struct GdCvt<T_Q4_K> {
+    static constexpr int DEPTH = 3;
     static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int) {
         const long long sb = row * (K >> 8) + (ks >> 2);
         const uint8_t * q = w[0] + sb * 128 + (ks & 3) * 32;
@@ -240,6 +243,7 @@ template <> struct GdCvt<T_Q4_K> {
 // l = 0 .. 31 of ql[64 h + 32 hk + l] (low nibble for c = 0, high for c = 1) and bits 2 (2 c + hk) .. + 1 of qh[32 h + l];
 // y = d * sc[8 h + 4 c + 2 hk + l / 16] * (q - 32)   (dequantize_row_q6_K, ggml-quants.c:1681-1710)
 template <> struct GdCvt<T_Q6_K> {
+    static constexpr int DEPTH = 2;
     static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long sb = row * (K >> 8) + (ks >> 2);
         const int h = (ks >> 1) & 1, c = ks & 1;
@@ -417,23 +421,33 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
             // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
             auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
-            GdRaw cur, nxt;
-            if (live(ks0)) GdCvt<TYPE>::load(cur, w, m, p.K, ks0, hk);
-            for (int ks = ks0; ks < ks1; ks++, it++) {
-                if (ks + 1 < ks1 && live(ks + 1)) GdCvt<TYPE>::load(nxt, w, m, p.K, ks + 1, hk);      // one slab ahead, in registers
-                uint4 o[4];
-                if (live(ks)) GdCvt<TYPE>::convert(cur, ks, hk, o);
-                else { o[0] = o[1] = o[2] = o[3] = make_uint4(0, 0, 0, 0); }
-                const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                               // the MMAs that read this slot are done
-                const uint32_t dst = sA + s * STAGE_A;
+            // D slabs in flight per thread (registers): the loads of slab ks + D are issued before slab ks is converted, so one
+            // L2 / HBM latency (~1 - 2 us under load) is spread over D stage times (~0.3 us each)
+            constexpr int D = GdCvt<TYPE>::DEPTH;
+            GdRaw buf[D];
+            #pragma unroll
+            for (int d = 0; d < D; d++) if (ks0 + d < ks1 && live(ks0 + d)) GdCvt<TYPE>::load(buf[d], w, m, p.K, ks0 + d, hk);
+            for (int kb = ks0; kb < ks1; kb += D) {
                 #pragma unroll
-                for (int c = 0; c < 4; c++)
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                        // generic-proxy stores -> visible to the tensor core
-                __syncwarp();
-                if (lane == 0) gd2_arrive_cluster(lafull0 + s * 8);
-                cur = nxt;
+                for (int d = 0; d < D; d++) {
+                    const int ks = kb + d;
+                    if (ks < ks1) {
+                        uint4 o[4];
+                        if (live(ks)) GdCvt<TYPE>::convert(buf[d], ks, hk, o);
+                        else { o[0] = o[1] = o[2] = o[3] = make_uint4(0, 0, 0, 0); }
+                        if (ks + D < ks1 && live(ks + D)) GdCvt<TYPE>::load(buf[d], w, m, p.K, ks + D, hk);
+                        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                        gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                       // the MMAs that read this slot are done
+                        const uint32_t dst = sA + s * STAGE_A;
+                        #pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                // generic-proxy stores -> visible to the tensor core
+                        __syncwarp();
+                        if (lane == 0) gd2_arrive_cluster(lafull0 + s * 8);
+                        it++;
+                    }
+                }
             }
         }
     }
