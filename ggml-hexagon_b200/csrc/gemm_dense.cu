@@ -152,6 +152,12 @@ __device__ __forceinline__ void gd2_commit_both(uint32_t bar) {          // same
 __device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(bar_cluster) : "memory");
 }
+// remote arrive for the converters, once per stage and warp: default (.release.cta) semantics, as CUTLASS' ClusterBarrier::arrive(cta_id).
+// The .release.cluster form above compiles to MEMBAR.ALL.GPU + ERRBAR + CGAERRBAR (seen in SASS) -- about a microsecond per stage; what the
+// arrive has to order is this CTA's own shared-memory stores, already made visible to the async proxy by fence.proxy.async.
+__device__ __forceinline__ void gd2_arrive_remote(uint32_t bar_cluster) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(bar_cluster) : "memory");
+}
 __device__ __forceinline__ void gd2_mbar_wait_cluster(uint32_t bar, uint32_t parity) {          // acquire at cluster scope: the arrivals are remote
     uint32_t ok = 0;
     const long long t0 = clock64();
@@ -347,7 +353,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
                 gm_fence_after();
                 for (int ks = ks0; ks < ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                    gd2_mbar_wait_cluster(afull0 + s * 8, ph);       // both CTAs' converted weight rows are in shared memory (async-proxy visible)
+                    gm_mbar_wait(afull0 + s * 8, ph);                // both CTAs' converted weight rows are in shared memory (async-proxy visible)
                     gm_mbar_wait(full0 + s * 8, ph);                 // both halves of the activation tile have landed
                     gm_fence_after();
                     if (it == 0 && lane == 0) gd_stamp(p, 2);
@@ -444,7 +450,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
                             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                // generic-proxy stores -> visible to the tensor core
                         __syncwarp();
-                        if (lane == 0) gd2_arrive_cluster(lafull0 + s * 8);
+                        if (lane == 0) gd2_arrive_remote(lafull0 + s * 8);
                         it++;
                     }
                 }
