@@ -121,10 +121,18 @@ __device__ __forceinline__ void gd_epilogue_warp1(const uint32_t taddr, float * 
 //   empty[s]  per CTA; tcgen05.commit.multicast arrives on both when the stage's MMAs have read shared memory
 //   tfull[b]  per CTA; multicast commit after a tile's last MMA
 //   tempty[b] leader only; the epilogue warps of BOTH CTAs arrive on it (remote arrive from the peer)
+// Native blocks reach the converters through per-thread rings of cp.async copies (LDGSTS): DEPTH slabs in flight per thread cost no
+// registers and -- unlike plain loads -- are not waited for by the MEMBAR that fence.proxy.async carries (with register-resident
+// prefetches every stage's fence waited for the loads of the slab DEPTH stages ahead: 0.63 us per stage against 0.3 for the MMAs).
+// Ring layout: N16 arrays [DEPTH][256 threads][16 B] and N4 arrays [DEPTH][256][4 B]: consecutive lanes, consecutive 16 B.
+__host__ __device__ constexpr int gd2_n16(int type) { return type == T_Q4_0 ? 1 : type == T_Q8_0 ? 2 : type == T_Q4_K ? 3 : 4; }
+__host__ __device__ constexpr int gd2_n4(int type)  { return type == T_Q4_K ? 0 : type == T_Q6_K ? 2 : 1; }
+__host__ __device__ constexpr int gd2_depth(int type) { return type == T_Q4_0 ? 6 : type == T_Q8_0 ? 6 : type == T_Q4_K ? 5 : 3; }
+__host__ __device__ constexpr int gd2_raw_bytes(int type) { return gd2_depth(type) * GD_CVT_WARPS * 32 * (16 * gd2_n16(type) + 4 * gd2_n4(type)); }
 __host__ __device__ constexpr int gd2_stage_bytes(int bn) { return GM_BM * 128 + (bn / 2) * 128; }
-__host__ __device__ constexpr int gd2_stages(int bn) { return (232448 - 1280) / gd2_stage_bytes(bn); }
-__host__ __device__ constexpr int gd2_smem(int bn) { return gd2_stages(bn) * gd2_stage_bytes(bn) + 256 + 1024; }
-static_assert(gd2_stages(256) == 7 && gd2_stages(128) == 9, "stage count");
+__host__ __device__ constexpr int gd2_stages(int bn, int type) { return (232448 - 1280 - gd2_raw_bytes(type)) / gd2_stage_bytes(bn); }
+__host__ __device__ constexpr int gd2_smem(int bn, int type) { return gd2_stages(bn, type) * gd2_stage_bytes(bn) + gd2_raw_bytes(type) + 256 + 1024; }
+static_assert(gd2_stages(256, T_Q4_0) == 6 && gd2_stages(256, T_Q8_0) >= 5 && gd2_stages(256, T_Q4_K) >= 5 && gd2_stages(256, T_Q6_K) >= 5, "stage count");
 
 __device__ __forceinline__ uint32_t gd2_mapa(uint32_t saddr, uint32_t rank) {
     uint32_t r;
@@ -185,15 +193,25 @@ __device__ __forceinline__ uint2 gd_u8x4_f(uint32_t w, float ds, float ms) {
     const float f2 = __fmaf_rn(ds, (float) ((w >> 16) & 0xFFu), -ms), f3 = __fmaf_rn(ds, (float) (w >> 24), -ms);
     return make_uint2(gd_pack_h2f(f0, f1), gd_pack_h2f(f2, f3));
 }
-struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // what one thread keeps per stage in flight (unused members cost nothing)
+struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // one slab's native bytes of a thread (unused members cost nothing)
+__device__ __forceinline__ void gd_cpa16(uint32_t dst, const void * src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory"); }
+__device__ __forceinline__ void gd_cpa4(uint32_t dst, const void * src)  { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory"); }
+__device__ __forceinline__ uint4 gd_lds16(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t gd_lds4(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+// slot addressing: q16[i] / q4[i] = this thread's 16-byte / 4-byte cell of field i in ring slot `slot`
+struct GdSlot { uint32_t q16[4], q4[2]; };
 template <int TYPE> struct GdCvt;
 // q4_0: one 16-byte block = the thread's 32 elements (low nibbles = elements 0..15, high = 16..31); y = d * (q - 8)
 template <> struct GdCvt<T_Q4_0> {
-    static constexpr int DEPTH = 6;
-    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long blk = row * (K >> 5) + ks * 2 + hk;
-        r.a = ldg_stream(w[0] + blk * 16);
-        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s0) : "l"(w[1] + blk * 2));
+        gd_cpa16(sl.q16[0], w[0] + blk * 16);
+        gd_cpa4(sl.q4[0], w[1] + ((blk * 2) & ~3ll));              // the aligned word that holds the block's 2-byte scale
+    }
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]);
+        const uint32_t wd = gd_lds4(sl.q4[0]);
+        r.s0 = ((row * (K >> 5) + ks * 2 + hk) & 1) ? wd >> 16 : wd & 0xFFFFu;
     }
     static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
         const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64086408u, m = 0x0F0F0F0Fu;          // 1032 = 1024 + 8
@@ -205,11 +223,15 @@ template <> struct GdCvt<T_Q4_0> {
 };
 // q8_0: one 32-byte block; y = d * q, q signed: q + 128 is the unsigned byte q ^ 0x80
 template <> struct GdCvt<T_Q8_0> {
-    static constexpr int DEPTH = 4;
-    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long blk = row * (K >> 5) + ks * 2 + hk;
-        r.a = ldg_stream(w[0] + blk * 32); r.b = ldg_stream(w[0] + blk * 32 + 16);
-        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s0) : "l"(w[1] + blk * 2));
+        gd_cpa16(sl.q16[0], w[0] + blk * 32); gd_cpa16(sl.q16[1], w[0] + blk * 32 + 16);
+        gd_cpa4(sl.q4[0], w[1] + ((blk * 2) & ~3ll));
+    }
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]);
+        const uint32_t wd = gd_lds4(sl.q4[0]);
+        r.s0 = ((row * (K >> 5) + ks * 2 + hk) & 1) ? wd >> 16 : wd & 0xFFFFu;
     }
     static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
         const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64806480u, x = 0x80808080u;          // 1152 = 1024 + 128
@@ -222,12 +244,13 @@ template <> struct GdCvt<T_Q8_0> {
 // q4_K: the slab is 32 bytes of super-block ks / 4, sub-blocks 2j (low nibbles, hk = 0) and 2j + 1 (high nibbles), j = ks % 4;
 // y = (d * sc_g) * q - dmin * m_g, scales / mins 6-bit packed in the 16-byte header (get_scale_min_k4, ggml-quants.c:631-638)
 template <> struct GdCvt<T_Q4_K> {
-    static constexpr int DEPTH = 3;
-    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int) {
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int) {
         const long long sb = row * (K >> 8) + (ks >> 2);
         const uint8_t * q = w[0] + sb * 128 + (ks & 3) * 32;
-        r.a = ldg_stream(q); r.b = ldg_stream(q + 16);
-        r.c = __ldg((const uint4 *) (w[1] + sb * 16));
+        gd_cpa16(sl.q16[0], q); gd_cpa16(sl.q16[1], q + 16); gd_cpa16(sl.q16[2], w[1] + sb * 16);
+    }
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long, int, int, int) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]); r.c = gd_lds16(sl.q16[2]);
     }
     static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
         const int g = 2 * (ks & 3) + hk;
@@ -249,16 +272,20 @@ template <> struct GdCvt<T_Q4_K> {
 // l = 0 .. 31 of ql[64 h + 32 hk + l] (low nibble for c = 0, high for c = 1) and bits 2 (2 c + hk) .. + 1 of qh[32 h + l];
 // y = d * sc[8 h + 4 c + 2 hk + l / 16] * (q - 32)   (dequantize_row_q6_K, ggml-quants.c:1681-1710)
 template <> struct GdCvt<T_Q6_K> {
-    static constexpr int DEPTH = 2;
-    static __device__ __forceinline__ void load(GdRaw & r, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
         const long long sb = row * (K >> 8) + (ks >> 2);
-        const int h = (ks >> 1) & 1, c = ks & 1;
+        const int h = (ks >> 1) & 1;
         const uint8_t * ql = w[0] + sb * 128 + 64 * h + 32 * hk;
         const uint8_t * qh = w[1] + sb * 64 + 32 * h;
-        r.a = __ldg((const uint4 *) ql); r.b = __ldg((const uint4 *) (ql + 16));          // (read again by the c = 1 slab: keep them in L1)
-        r.c = __ldg((const uint4 *) qh); r.e = __ldg((const uint4 *) (qh + 16));
-        r.s0 = __ldg((const unsigned short *) (w[2] + sb * 16 + 8 * h + 4 * c + 2 * hk));
-        asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r.s1) : "l"(w[3] + sb * 2));
+        gd_cpa16(sl.q16[0], ql); gd_cpa16(sl.q16[1], ql + 16); gd_cpa16(sl.q16[2], qh); gd_cpa16(sl.q16[3], qh + 16);
+        gd_cpa4(sl.q4[0], w[2] + sb * 16 + 8 * h + 4 * (ks & 1));  // the 4 scales of this slab (the thread uses 2 hk, 2 hk + 1)
+        gd_cpa4(sl.q4[1], w[3] + ((sb * 2) & ~3ll));
+    }
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]); r.c = gd_lds16(sl.q16[2]); r.e = gd_lds16(sl.q16[3]);
+        const uint32_t sc4 = gd_lds4(sl.q4[0]), dw = gd_lds4(sl.q4[1]);
+        r.s0 = hk ? sc4 >> 16 : sc4 & 0xFFFFu;
+        r.s1 = ((row * (K >> 8) + (ks >> 2)) & 1) ? dw >> 16 : dw & 0xFFFFu;
     }
     static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
         const int c = ks & 1, sh = 2 * (2 * c + hk), ns = 4 * c;
@@ -278,12 +305,12 @@ template <int BN, int TYPE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
 gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBq,
                    const GemmDenseArgs p) {
-    constexpr int STAGES = gd2_stages(BN), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
-    constexpr int OFF_B = STAGES * STAGE_A, OFF_BAR = OFF_B + STAGES * STAGE_B;
+    constexpr int STAGES = gd2_stages(BN, TYPE), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
+    constexpr int OFF_B = STAGES * STAGE_A, OFF_RAW = OFF_B + STAGES * STAGE_B, OFF_BAR = OFF_RAW + gd2_raw_bytes(TYPE);
     extern __shared__ uint8_t gd_smem_raw[];
     const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;
     uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
-    const uint32_t sA = base, sB = base + OFF_B, bars = base + OFF_BAR;
+    const uint32_t sA = base, sB = base + OFF_B, sRaw = base + OFF_RAW, bars = base + OFF_BAR;
     const uint32_t full0 = bars, empty0 = bars + STAGES * 8, afull0 = bars + 2 * STAGES * 8, tfull0 = bars + 3 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -406,7 +433,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
         // ===== converters (both CTAs): thread = row r of this CTA's 128, half slab hk; native blocks -> swizzled fp16 stage.
         // 128-byte swizzle of a K-major tile: row r lies at (r / 8) * 1024 + (r % 8) * 128, its 16-byte chunk c at ((c ^ (r % 8)) * 16):
         // the 8 lanes of a store phase (8 consecutive rows, same c) hit 8 different chunk positions = all 32 banks once.
-        const int cw = warp - GD_CVT_WARP0, r = (cw & 3) * 32 + lane, hk = cw >> 2;
+        const int cw = warp - GD_CVT_WARP0, r = (cw & 3) * 32 + lane, hk = cw >> 2, ct = cw * 32 + lane;
         const uint32_t rowoff = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
         uint32_t choff[4];
         #pragma unroll
@@ -427,34 +454,45 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
             // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
             auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
-            // D slabs in flight per thread (registers): the loads of slab ks + D are issued before slab ks is converted, so one
-            // L2 / HBM latency (~1 - 2 us under load) is spread over D stage times (~0.3 us each)
-            constexpr int D = GdCvt<TYPE>::DEPTH;
-            GdRaw buf[D];
-            #pragma unroll
-            for (int d = 0; d < D; d++) if (ks0 + d < ks1 && live(ks0 + d)) GdCvt<TYPE>::load(buf[d], w, m, p.K, ks0 + d, hk);
-            for (int kb = ks0; kb < ks1; kb += D) {
+            // D slabs in flight per thread: cp.async copies into the thread's ring cells, one commit group per slab (empty groups keep
+            // the count uniform), wait_group D - 1 before a slab is read
+            constexpr int D = gd2_depth(TYPE);
+            auto slot_of = [&](int i) {
+                GdSlot sl;
+                const uint32_t cell = (uint32_t) ((i % D) * (GD_CVT_WARPS * 32) + ct);
                 #pragma unroll
-                for (int d = 0; d < D; d++) {
-                    const int ks = kb + d;
-                    if (ks < ks1) {
-                        uint4 o[4];
-                        if (live(ks)) GdCvt<TYPE>::convert(buf[d], ks, hk, o);
-                        else { o[0] = o[1] = o[2] = o[3] = make_uint4(0, 0, 0, 0); }
-                        if (ks + D < ks1 && live(ks + D)) GdCvt<TYPE>::load(buf[d], w, m, p.K, ks + D, hk);
-                        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                        gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                       // the MMAs that read this slot are done
-                        const uint32_t dst = sA + s * STAGE_A;
-                        #pragma unroll
-                        for (int c = 0; c < 4; c++)
-                            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                // generic-proxy stores -> visible to the tensor core
-                        __syncwarp();
-                        if (lane == 0) gd2_arrive_remote(lafull0 + s * 8);
-                        it++;
-                    }
-                }
+                for (int f = 0; f < 4; f++) sl.q16[f] = sRaw + (uint32_t) (f * D * GD_CVT_WARPS * 32 * 16) + cell * 16;
+                #pragma unroll
+                for (int f = 0; f < 2; f++) sl.q4[f] = sRaw + (uint32_t) (gd2_n16(TYPE) * D * GD_CVT_WARPS * 32 * 16 + f * D * GD_CVT_WARPS * 32 * 4) + cell * 4;
+                return sl;
+            };
+            #pragma unroll 1
+            for (int d = 0; d < D; d++) {
+                if (ks0 + d < ks1 && live(ks0 + d)) GdCvt<TYPE>::issue(slot_of(d), w, m, p.K, ks0 + d, hk);
+                asm volatile("cp.async.commit_group;" ::: "memory");
             }
+            #pragma unroll 1
+            for (int ks = ks0; ks < ks1; ks++, it++) {
+                const int i = ks - ks0;
+                asm volatile("cp.async.wait_group %0;" :: "n"(D - 1) : "memory");
+                const GdSlot sl = slot_of(i);
+                uint4 o[4];
+                if (live(ks)) { GdRaw raw; GdCvt<TYPE>::fetch(raw, sl, w, m, p.K, ks, hk); GdCvt<TYPE>::convert(raw, ks, hk, o); }
+                else { o[0] = o[1] = o[2] = o[3] = make_uint4(0, 0, 0, 0); }
+                const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
+                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                               // the MMAs that read this slot are done
+                const uint32_t dst = sA + s * STAGE_A;
+                #pragma unroll
+                for (int c = 0; c < 4; c++)
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[c].x), "r"(o[c].y), "r"(o[c].z), "r"(o[c].w) : "memory");
+                // (the ring cell was read into registers and used above: the copy of slab ks + D may overwrite it now)
+                if (ks + D < ks1 && live(ks + D)) GdCvt<TYPE>::issue(sl, w, m, p.K, ks + D, hk);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                        // generic-proxy stores -> visible to the tensor core
+                __syncwarp();
+                if (lane == 0) gd2_arrive_remote(lafull0 + s * 8);
+            }
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
     }
     __syncwarp();                // the cluster barrier is warp-aligned: the single-lane roles rejoin their warps first
@@ -530,12 +568,12 @@ static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmB, const GemmDense
     static bool attr_done[64] = {false};          // per device
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (!attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN, TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN));
+        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN, TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN, TYPE));
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GD_THREADS); cfg.dynamicSmemBytes = gd2_smem(BN); cfg.stream = st;      // __cluster_dims__(2): grid is even
+    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GD_THREADS); cfg.dynamicSmemBytes = gd2_smem(BN, TYPE); cfg.stream = st;      // __cluster_dims__(2): grid is even
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
