@@ -35,8 +35,8 @@
 namespace b200 {
 
 constexpr int GD_KS = 64;                                    // fp16 elements of K per stage = one 128-B swizzle row
-constexpr int GD_EPI_WARPS = 4;                              // one per TMEM lane quarter, all BN columns each
-constexpr int GD_CVT_WARPS = 16;                             // converters: 128 rows x 4 quarter slabs of 16 elements
+constexpr int GD_EPI_WARPS = 8;                              // 4 TMEM lane quarters x 2 column halves
+constexpr int GD_CVT_WARPS = 8;                              // converters: 128 rows x 2 half slabs of 32 elements
 constexpr int GD_CVT_WARP0 = 2 + GD_EPI_WARPS;
 constexpr int GD_THREADS = 64 + GD_EPI_WARPS * 32 + GD_CVT_WARPS * 32;
 
@@ -125,14 +125,14 @@ __device__ __forceinline__ void gd_epilogue_warp1(const uint32_t taddr, float * 
 // registers and -- unlike plain loads -- are not waited for by the MEMBAR that fence.proxy.async carries (with register-resident
 // prefetches every stage's fence waited for the loads of the slab DEPTH stages ahead: 0.63 us per stage against 0.3 for the MMAs).
 // Ring layout: N16 arrays [DEPTH][256 threads][16 B] and N4 arrays [DEPTH][256][4 B]: consecutive lanes, consecutive 16 B.
-__host__ __device__ constexpr int gd2_n16(int type) { return type == T_Q4_0 || type == T_Q8_0 ? 1 : 2; }
+__host__ __device__ constexpr int gd2_n16(int type) { return type == T_Q4_0 ? 1 : type == T_Q8_0 ? 2 : type == T_Q4_K ? 3 : 4; }
 __host__ __device__ constexpr int gd2_n4(int type)  { return type == T_Q4_K ? 0 : type == T_Q6_K ? 2 : 1; }
-__host__ __device__ constexpr int gd2_depth(int type) { return type == T_Q4_0 || type == T_Q8_0 ? 6 : 3; }
+__host__ __device__ constexpr int gd2_depth(int type) { return type == T_Q4_0 ? 6 : type == T_Q8_0 ? 6 : type == T_Q4_K ? 5 : 3; }
 __host__ __device__ constexpr int gd2_raw_bytes(int type) { return gd2_depth(type) * GD_CVT_WARPS * 32 * (16 * gd2_n16(type) + 4 * gd2_n4(type)); }
 __host__ __device__ constexpr int gd2_stage_bytes(int bn) { return GM_BM * 128 + (bn / 2) * 128; }
 __host__ __device__ constexpr int gd2_stages(int bn, int type) { return (232448 - 1280 - gd2_raw_bytes(type)) / gd2_stage_bytes(bn); }
 __host__ __device__ constexpr int gd2_smem(int bn, int type) { return gd2_stages(bn, type) * gd2_stage_bytes(bn) + gd2_raw_bytes(type) + 256 + 1024; }
-static_assert(gd2_stages(256, T_Q4_0) >= 5 && gd2_stages(256, T_Q8_0) >= 5 && gd2_stages(256, T_Q4_K) >= 5 && gd2_stages(256, T_Q6_K) >= 5, "stage count");
+static_assert(gd2_stages(256, T_Q4_0) == 6 && gd2_stages(256, T_Q8_0) >= 5 && gd2_stages(256, T_Q4_K) >= 5 && gd2_stages(256, T_Q6_K) >= 5, "stage count");
 
 __device__ __forceinline__ uint32_t gd2_mapa(uint32_t saddr, uint32_t rank) {
     uint32_t r;
@@ -193,97 +193,111 @@ __device__ __forceinline__ uint2 gd_u8x4_f(uint32_t w, float ds, float ms) {
     const float f2 = __fmaf_rn(ds, (float) ((w >> 16) & 0xFFu), -ms), f3 = __fmaf_rn(ds, (float) (w >> 24), -ms);
     return make_uint2(gd_pack_h2f(f0, f1), gd_pack_h2f(f2, f3));
 }
-struct GdRaw { uint4 a, b; uint32_t s0, s1; };            // one quarter slab's native bytes of a thread (unused members cost nothing)
+struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // one slab's native bytes of a thread (unused members cost nothing)
 __device__ __forceinline__ void gd_cpa16(uint32_t dst, const void * src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory"); }
 __device__ __forceinline__ void gd_cpa4(uint32_t dst, const void * src)  { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory"); }
 __device__ __forceinline__ uint4 gd_lds16(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t gd_lds4(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-// ring cells of one thread for one slab: q16[i] / q4[i] = its 16-byte / 4-byte cell of field i
-struct GdSlot { uint32_t q16[2], q4[2]; };
-// A converter thread owns (row, quarter qk) of every 64-element slab: elements 16 qk .. 16 qk + 15 = the two 16-byte chunks 2 qk, 2 qk + 1
-// of the row's 128-byte fp16 line.  rb = the row's first byte in each SoA field array (64-bit, once per tile); everything per slab
-// is a 32-bit offset from it.
+// slot addressing: q16[i] / q4[i] = this thread's 16-byte / 4-byte cell of field i in ring slot `slot`
+struct GdSlot { uint32_t q16[4], q4[2]; };
 template <int TYPE> struct GdCvt;
-// q4_0: slab = blocks 2 ks, 2 ks + 1 of the row; block hk = qk / 2, nibble plane qk % 2 (low nibbles = elements 0..15 of the block,
-// high = 16..31: both planes read the block's 16 bytes); y = d * (q - 8)
+// q4_0: one 16-byte block = the thread's 32 elements (low nibbles = elements 0..15, high = 16..31); y = d * (q - 8)
 template <> struct GdCvt<T_Q4_0> {
-    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk) {
-        const int blk = ks * 2 + (qk >> 1);
-        gd_cpa16(sl.q16[0], rb[0] + blk * 16);
-        gd_cpa4(sl.q4[0], (const uint8_t *) (((uintptr_t) rb[1] + blk * 2) & ~(uintptr_t) 3));      // the aligned word that holds the 2-byte scale
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long blk = row * (K >> 5) + ks * 2 + hk;
+        gd_cpa16(sl.q16[0], w[0] + blk * 16);
+        gd_cpa4(sl.q4[0], w[1] + ((blk * 2) & ~3ll));              // the aligned word that holds the block's 2-byte scale
     }
-    static __device__ __forceinline__ void convert(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk, uint4 (&o)[2]) {
-        const uint4 q = gd_lds16(sl.q16[0]);
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]);
         const uint32_t wd = gd_lds4(sl.q4[0]);
-        const uint32_t d = (((uintptr_t) rb[1] + (ks * 2 + (qk >> 1)) * 2) & 2) ? wd >> 16 : wd & 0xFFFFu;
-        const uint32_t d2 = d | (d << 16), bias = 0x64086408u, m = 0x0F0F0F0Fu;                       // 1032 = 1024 + 8
-        const int sh = (qk & 1) * 4;
-        const uint2 a = gd_u8x4_h((q.x >> sh) & m, bias, d2), b = gd_u8x4_h((q.y >> sh) & m, bias, d2);
-        const uint2 c = gd_u8x4_h((q.z >> sh) & m, bias, d2), e = gd_u8x4_h((q.w >> sh) & m, bias, d2);
-        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, e.x, e.y);
+        r.s0 = ((row * (K >> 5) + ks * 2 + hk) & 1) ? wd >> 16 : wd & 0xFFFFu;
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
+        const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64086408u, m = 0x0F0F0F0Fu;          // 1032 = 1024 + 8
+        const uint2 a = gd_u8x4_h(r.a.x & m, bias, d2), b = gd_u8x4_h(r.a.y & m, bias, d2), c = gd_u8x4_h(r.a.z & m, bias, d2), d = gd_u8x4_h(r.a.w & m, bias, d2);
+        const uint2 e = gd_u8x4_h((r.a.x >> 4) & m, bias, d2), f = gd_u8x4_h((r.a.y >> 4) & m, bias, d2), g = gd_u8x4_h((r.a.z >> 4) & m, bias, d2), h = gd_u8x4_h((r.a.w >> 4) & m, bias, d2);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
     }
 };
-// q8_0: 16 of the block's 32 signed bytes; y = d * q, q + 128 is the unsigned byte q ^ 0x80
+// q8_0: one 32-byte block; y = d * q, q signed: q + 128 is the unsigned byte q ^ 0x80
 template <> struct GdCvt<T_Q8_0> {
-    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk) {
-        const int blk = ks * 2 + (qk >> 1);
-        gd_cpa16(sl.q16[0], rb[0] + blk * 32 + (qk & 1) * 16);
-        gd_cpa4(sl.q4[0], (const uint8_t *) (((uintptr_t) rb[1] + blk * 2) & ~(uintptr_t) 3));
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long blk = row * (K >> 5) + ks * 2 + hk;
+        gd_cpa16(sl.q16[0], w[0] + blk * 32); gd_cpa16(sl.q16[1], w[0] + blk * 32 + 16);
+        gd_cpa4(sl.q4[0], w[1] + ((blk * 2) & ~3ll));
     }
-    static __device__ __forceinline__ void convert(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk, uint4 (&o)[2]) {
-        const uint4 q = gd_lds16(sl.q16[0]);
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]);
         const uint32_t wd = gd_lds4(sl.q4[0]);
-        const uint32_t d = (((uintptr_t) rb[1] + (ks * 2 + (qk >> 1)) * 2) & 2) ? wd >> 16 : wd & 0xFFFFu;
-        const uint32_t d2 = d | (d << 16), bias = 0x64806480u, x = 0x80808080u;                       // 1152 = 1024 + 128
-        const uint2 a = gd_u8x4_h(q.x ^ x, bias, d2), b = gd_u8x4_h(q.y ^ x, bias, d2), c = gd_u8x4_h(q.z ^ x, bias, d2), e = gd_u8x4_h(q.w ^ x, bias, d2);
-        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, e.x, e.y);
+        r.s0 = ((row * (K >> 5) + ks * 2 + hk) & 1) ? wd >> 16 : wd & 0xFFFFu;
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int, int, uint4 (&o)[4]) {
+        const uint32_t d2 = r.s0 | (r.s0 << 16), bias = 0x64806480u, x = 0x80808080u;          // 1152 = 1024 + 128
+        const uint2 a = gd_u8x4_h(r.a.x ^ x, bias, d2), b = gd_u8x4_h(r.a.y ^ x, bias, d2), c = gd_u8x4_h(r.a.z ^ x, bias, d2), d = gd_u8x4_h(r.a.w ^ x, bias, d2);
+        const uint2 e = gd_u8x4_h(r.b.x ^ x, bias, d2), f = gd_u8x4_h(r.b.y ^ x, bias, d2), g = gd_u8x4_h(r.b.z ^ x, bias, d2), h = gd_u8x4_h(r.b.w ^ x, bias, d2);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
     }
 };
-// q4_K: the slab is 32 bytes of super-block ks / 4 (j = ks % 4): low nibbles = sub-block 2 j (elements 0..31 of the slab), high = 2 j + 1;
-// the quarter: nibble plane qk / 2, bytes 16 (qk % 2) .. + 15.  y = (d * sc_g) * q - dmin * m_g, scales / mins 6-bit packed in the
-// 16-byte header (get_scale_min_k4, ggml-quants.c:631-638)
+// q4_K: the slab is 32 bytes of super-block ks / 4, sub-blocks 2j (low nibbles, hk = 0) and 2j + 1 (high nibbles), j = ks % 4;
+// y = (d * sc_g) * q - dmin * m_g, scales / mins 6-bit packed in the 16-byte header (get_scale_min_k4, ggml-quants.c:631-638)
 template <> struct GdCvt<T_Q4_K> {
-    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk) {
-        gd_cpa16(sl.q16[0], rb[0] + (ks >> 2) * 128 + (ks & 3) * 32 + (qk & 1) * 16);
-        gd_cpa16(sl.q16[1], rb[1] + (ks >> 2) * 16);
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int) {
+        const long long sb = row * (K >> 8) + (ks >> 2);
+        const uint8_t * q = w[0] + sb * 128 + (ks & 3) * 32;
+        gd_cpa16(sl.q16[0], q); gd_cpa16(sl.q16[1], q + 16); gd_cpa16(sl.q16[2], w[1] + sb * 16);
     }
-    static __device__ __forceinline__ void convert(const GdSlot & sl, const uint8_t * const *, int ks, int qk, uint4 (&o)[2]) {
-        const uint4 q = gd_lds16(sl.q16[0]), hd = gd_lds16(sl.q16[1]);
-        const int g = 2 * (ks & 3) + (qk >> 1);
-        const uint32_t wsc[3] = {hd.y, hd.z, hd.w};
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long, int, int, int) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]); r.c = gd_lds16(sl.q16[2]);
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
+        const int g = 2 * (ks & 3) + hk;
+        const uint32_t wsc[3] = {r.c.y, r.c.z, r.c.w};
         auto byte = [&](int k) -> uint32_t { return (wsc[k >> 2] >> (8 * (k & 3))) & 0xFFu; };
         uint32_t sc, mn;
         if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
         else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
-        const __half2 dd = *(const __half2 *) &hd.x;
+        const __half2 dd = *(const __half2 *) &r.c.x;
         const float ds = __fmul_rn(__low2float(dd), (float) sc), ms = __fmul_rn(__high2float(dd), (float) mn);
-        const uint32_t m = 0x0F0F0F0Fu; const int sh = (qk >> 1) * 4;
-        const uint2 a = gd_u8x4_f((q.x >> sh) & m, ds, ms), b = gd_u8x4_f((q.y >> sh) & m, ds, ms), c = gd_u8x4_f((q.z >> sh) & m, ds, ms), e = gd_u8x4_f((q.w >> sh) & m, ds, ms);
-        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, e.x, e.y);
+        const uint32_t m = 0x0F0F0F0Fu; const int sh = hk * 4;
+        const uint2 a = gd_u8x4_f((r.a.x >> sh) & m, ds, ms), b = gd_u8x4_f((r.a.y >> sh) & m, ds, ms), c = gd_u8x4_f((r.a.z >> sh) & m, ds, ms), d = gd_u8x4_f((r.a.w >> sh) & m, ds, ms);
+        const uint2 e = gd_u8x4_f((r.b.x >> sh) & m, ds, ms), f = gd_u8x4_f((r.b.y >> sh) & m, ds, ms), gg = gd_u8x4_f((r.b.z >> sh) & m, ds, ms), h = gd_u8x4_f((r.b.w >> sh) & m, ds, ms);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(gg.x, gg.y, h.x, h.y);
     }
 };
-// q6_K: slab ks = elements 128 h + 64 c + e of super-block ks / 4 (h = (ks / 2) % 2, c = ks % 2); the quarter's e = 16 qk .. + 15 are
-// ql[64 h + e] (low nibble for c = 0, high for c = 1) and bits 2 (2 c + qk / 2) .. + 1 of qh[32 h + e % 32];
-// y = d * sc[8 h + 4 c + qk] * (q - 32)   (dequantize_row_q6_K, ggml-quants.c:1681-1710)
+// q6_K: slab ks = 64 elements 128 h + 64 c + e of super-block ks / 4 (h = (ks / 2) % 2, c = ks % 2); the thread's e = 32 hk .. + 31 are
+// l = 0 .. 31 of ql[64 h + 32 hk + l] (low nibble for c = 0, high for c = 1) and bits 2 (2 c + hk) .. + 1 of qh[32 h + l];
+// y = d * sc[8 h + 4 c + 2 hk + l / 16] * (q - 32)   (dequantize_row_q6_K, ggml-quants.c:1681-1710)
 template <> struct GdCvt<T_Q6_K> {
-    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk) {
-        const int sb = ks >> 2, h = (ks >> 1) & 1;
-        gd_cpa16(sl.q16[0], rb[0] + sb * 128 + 64 * h + 16 * qk);
-        gd_cpa16(sl.q16[1], rb[1] + sb * 64 + 32 * h + 16 * (qk & 1));
-        gd_cpa4(sl.q4[0], rb[2] + sb * 16 + 8 * h + 4 * (ks & 1));                                   // the 4 scales of this slab
-        gd_cpa4(sl.q4[1], (const uint8_t *) (((uintptr_t) rb[3] + sb * 2) & ~(uintptr_t) 3));
+    static __device__ __forceinline__ void issue(const GdSlot & sl, const uint8_t * const * w, long long row, int K, int ks, int hk) {
+        const long long sb = row * (K >> 8) + (ks >> 2);
+        const int h = (ks >> 1) & 1;
+        const uint8_t * ql = w[0] + sb * 128 + 64 * h + 32 * hk;
+        const uint8_t * qh = w[1] + sb * 64 + 32 * h;
+        gd_cpa16(sl.q16[0], ql); gd_cpa16(sl.q16[1], ql + 16); gd_cpa16(sl.q16[2], qh); gd_cpa16(sl.q16[3], qh + 16);
+        gd_cpa4(sl.q4[0], w[2] + sb * 16 + 8 * h + 4 * (ks & 1));  // the 4 scales of this slab (the thread uses 2 hk, 2 hk + 1)
+        gd_cpa4(sl.q4[1], w[3] + ((sb * 2) & ~3ll));
     }
-    static __device__ __forceinline__ void convert(const GdSlot & sl, const uint8_t * const * rb, int ks, int qk, uint4 (&o)[2]) {
-        const uint4 l = gd_lds16(sl.q16[0]), hh = gd_lds16(sl.q16[1]);
+    static __device__ __forceinline__ void fetch(GdRaw & r, const GdSlot & sl, const uint8_t * const *, long long row, int K, int ks, int hk) {
+        r.a = gd_lds16(sl.q16[0]); r.b = gd_lds16(sl.q16[1]); r.c = gd_lds16(sl.q16[2]); r.e = gd_lds16(sl.q16[3]);
         const uint32_t sc4 = gd_lds4(sl.q4[0]), dw = gd_lds4(sl.q4[1]);
-        const int c = ks & 1, sh = 2 * (2 * c + (qk >> 1)), ns = 4 * c;
+        r.s0 = hk ? sc4 >> 16 : sc4 & 0xFFFFu;
+        r.s1 = ((row * (K >> 8) + (ks >> 2)) & 1) ? dw >> 16 : dw & 0xFFFFu;
+    }
+    static __device__ __forceinline__ void convert(const GdRaw & r, int ks, int hk, uint4 (&o)[4]) {
+        const int c = ks & 1, sh = 2 * (2 * c + hk), ns = 4 * c;
         const uint32_t m = 0x0F0F0F0Fu, m3 = 0x03030303u;
-        auto q = [&](uint32_t lo, uint32_t hi) { return ((lo >> ns) & m) | (((hi >> sh) & m3) << 4); };
-        const uint32_t dbits = (((uintptr_t) rb[3] + (ks >> 2) * 2) & 2) ? dw >> 16 : dw & 0xFFFFu;
-        const float d = __half2float(__ushort_as_half((unsigned short) dbits));
-        const float ds = __fmul_rn(d, (float) (int8_t) ((sc4 >> (8 * qk)) & 0xFF)), ms = ds * 32.f;      // (x 32: exact)
-        const uint2 a = gd_u8x4_f(q(l.x, hh.x), ds, ms), b = gd_u8x4_f(q(l.y, hh.y), ds, ms), cc = gd_u8x4_f(q(l.z, hh.z), ds, ms), e = gd_u8x4_f(q(l.w, hh.w), ds, ms);
-        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(cc.x, cc.y, e.x, e.y);
+        auto q = [&](uint32_t l, uint32_t hh) { return ((l >> ns) & m) | (((hh >> sh) & m3) << 4); };
+        const float d = __half2float(__ushort_as_half((unsigned short) r.s1));
+        const float d0 = __fmul_rn(d, (float) (int8_t) (r.s0 & 0xFF)), d1 = __fmul_rn(d, (float) (int8_t) ((r.s0 >> 8) & 0xFF));
+        const float m0 = d0 * 32.f, m1 = d1 * 32.f;                      // (exact: power of two)
+        const uint2 a = gd_u8x4_f(q(r.a.x, r.c.x), d0, m0), b = gd_u8x4_f(q(r.a.y, r.c.y), d0, m0), cc = gd_u8x4_f(q(r.a.z, r.c.z), d0, m0), dd = gd_u8x4_f(q(r.a.w, r.c.w), d0, m0);
+        const uint2 e = gd_u8x4_f(q(r.b.x, r.e.x), d1, m1), f = gd_u8x4_f(q(r.b.y, r.e.y), d1, m1), g = gd_u8x4_f(q(r.b.z, r.e.z), d1, m1), h = gd_u8x4_f(q(r.b.w, r.e.w), d1, m1);
+        o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(cc.x, cc.y, dd.x, dd.y);
+        o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
     }
 };
 
@@ -382,7 +396,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
         }
     } else if (warp < GD_CVT_WARP0) {
         // ===== epilogue (both CTAs): this CTA's TMEM holds rows rank * 128 .. +127 of the pair tile, all BN columns
-        const int q = warp & 3;
+        const int q = warp & 3, half = (warp - 2) >> 2;
         const int m_local = q * 32 + lane;
         const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16);
         const uint32_t ltempty0 = gd2_mapa(tempty0, 0);
@@ -400,43 +414,31 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             gm_mbar_wait(tfull0 + buf * 8, bph);
             gm_fence_after();
             if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
-            // this warp: TMEM lanes q * 32 .. +31, all n_w columns of the unit
-            const int n0 = nt * BN + u.n_off;
-            const uint32_t ta = tbase + buf * BN;
+            // this warp: TMEM lanes q * 32 .. +31, columns half * (n_w / 2) .. + n_w / 2 of the unit
+            const int c0 = half * (u.n_w / 2), n0 = nt * BN + u.n_off + c0;
+            const uint32_t ta = tbase + buf * BN + c0;
             float * const colp = outp + (long long) n0 * ocs + m;
             const bool row_ok = m < p.Ms[j];
-            if (u.n_w == BN)               gd_epilogue_warp<BN / 32>(ta, colp, ocs, p.N - n0, row_ok);
-            else if (u.n_w == BN / 2)      gd_epilogue_warp<BN / 64>(ta, colp, ocs, p.N - n0, row_ok);
-            else {
+            if (u.n_w == BN)               gd_epilogue_warp<BN / 64>(ta, colp, ocs, p.N - n0, row_ok);
+            else if (u.n_w == BN / 2) {
                 if constexpr (BN == 256)   gd_epilogue_warp<BN / 128>(ta, colp, ocs, p.N - n0, row_ok);
                 else                       gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
-            }
+            } else                         gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
             gm_fence_before();
             __syncwarp();
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
         }
         if (warp == 2 && lane == 0) gd_stamp(p, 6);
     } else {
-        // ===== converters (both CTAs): thread = row r of this CTA's 128, quarter qk of the slab; native blocks -> swizzled fp16 stage.
+        // ===== converters (both CTAs): thread = row r of this CTA's 128, half slab hk; native blocks -> swizzled fp16 stage.
         // 128-byte swizzle of a K-major tile: row r lies at (r / 8) * 1024 + (r % 8) * 128, its 16-byte chunk c at ((c ^ (r % 8)) * 16):
         // the 8 lanes of a store phase (8 consecutive rows, same c) hit 8 different chunk positions = all 32 banks once.
-        const int cw = warp - GD_CVT_WARP0, r = (cw & 3) * 32 + lane, qk = cw >> 2, ct = cw * 32 + lane;
+        const int cw = warp - GD_CVT_WARP0, r = (cw & 3) * 32 + lane, hk = cw >> 2, ct = cw * 32 + lane;
         const uint32_t rowoff = (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128);
-        const uint32_t choff0 = rowoff + (uint32_t) (((2 * qk) ^ (r & 7)) << 4), choff1 = rowoff + (uint32_t) (((2 * qk + 1) ^ (r & 7)) << 4);
+        uint32_t choff[4];
+        #pragma unroll
+        for (int c = 0; c < 4; c++) choff[c] = rowoff + (uint32_t) (((hk * 4 + c) ^ (r & 7)) << 4);
         const uint32_t lafull0 = gd2_mapa(afull0, 0);
-        constexpr int D = gd2_depth(TYPE), NT = GD_CVT_WARPS * 32;
-        // D slabs in flight per thread: cp.async copies into the thread's ring cells, one commit group per slab (empty groups keep the
-        // count uniform), wait_group D - 1 before a slab is read
-        auto slot_of = [&](int i) {
-            GdSlot sl;
-            const uint32_t cell = (uint32_t) ((i % D) * NT + ct);
-            #pragma unroll
-            for (int f = 0; f < 2; f++) sl.q16[f] = sRaw + (uint32_t) (f * D * NT * 16) + cell * 16;
-            #pragma unroll
-            for (int f = 0; f < 2; f++) sl.q4[f] = sRaw + (uint32_t) (gd2_n16(TYPE) * D * NT * 16 + f * D * NT * 4) + cell * 4;
-            return sl;
-        };
-        constexpr bool KQ = TYPE == T_Q4_K || TYPE == T_Q6_K;
         uint32_t it = 0;
         for (int work = pair; work < nwork; work += npairs) {
             const GdUnit u = gd2_unit(p, work, BN);
@@ -445,37 +447,70 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
             const int mt = local / p.ntiles;
             const long long m = (long long) mt * 2 * GM_BM + (int) rank * GM_BM + r;
-            // the row's first byte in every field array; slabs of the row that hold elements of this quarter (the last slab of a
-            // q4_0 / q8_0 row may be half empty: K % 64 == 32)
-            const uint8_t * rb[4];
-            const long long units = KQ ? m * (p.K >> 8) : m * (p.K >> 5);
+            const bool row_ok = m < p.Ms[j];
+            const uint8_t * w[4];
             #pragma unroll
-            for (int f = 0; f < 4; f++) rb[f] = (j == 0 ? p.w[0][f] : (j == 1 ? p.w[1][f] : p.w[2][f])) + units * wfields(TYPE).size[f];
-            const int nlive = m < p.Ms[j] ? (p.K - 16 * qk + GD_KS - 1) / GD_KS : 0;
+            for (int f = 0; f < 4; f++) w[f] = j == 0 ? p.w[0][f] : (j == 1 ? p.w[1][f] : p.w[2][f]);
             const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
+            auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
+            // D slabs in flight per thread: cp.async copies into the thread's ring cells, one commit group per slab (empty groups keep
+            // the count uniform), wait_group D - 1 before a slab is read
+            constexpr int D = gd2_depth(TYPE);
+            auto slot_of = [&](int i) {
+                GdSlot sl;
+                const uint32_t cell = (uint32_t) ((i % D) * (GD_CVT_WARPS * 32) + ct);
+                #pragma unroll
+                for (int f = 0; f < 4; f++) sl.q16[f] = sRaw + (uint32_t) (f * D * GD_CVT_WARPS * 32 * 16) + cell * 16;
+                #pragma unroll
+                for (int f = 0; f < 2; f++) sl.q4[f] = sRaw + (uint32_t) (gd2_n16(TYPE) * D * GD_CVT_WARPS * 32 * 16 + f * D * GD_CVT_WARPS * 32 * 4) + cell * 4;
+                return sl;
+            };
             #pragma unroll 1
             for (int d = 0; d < D; d++) {
-                if (ks0 + d < ks1 && ks0 + d < nlive) GdCvt<TYPE>::issue(slot_of(d), rb, ks0 + d, qk);
+                if (ks0 + d < ks1 && live(ks0 + d)) GdCvt<TYPE>::issue(slot_of(d), w, m, p.K, ks0 + d, hk);
                 asm volatile("cp.async.commit_group;" ::: "memory");
             }
+            // U slabs per iteration: their conversions interleave (two independent dependency chains per thread), and the fence --
+            // a MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC of ~250 clocks (ncu source page) -- is paid once per U stages
+            constexpr int U = 2;
             #pragma unroll 1
-            for (int ks = ks0; ks < ks1; ks++, it++) {
-                asm volatile("cp.async.wait_group %0;" :: "n"(D - 1) : "memory");
-                const GdSlot sl = slot_of(ks - ks0);
-                uint4 o[2];
-                if (ks < nlive) GdCvt<TYPE>::convert(sl, rb, ks, qk, o);
-                else { o[0] = o[1] = make_uint4(0, 0, 0, 0); }
-                const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
-                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                               // the MMAs that read this slot are done
-                const uint32_t dst = sA + s * STAGE_A;
-                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff0), "r"(o[0].x), "r"(o[0].y), "r"(o[0].z), "r"(o[0].w) : "memory");
-                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff1), "r"(o[1].x), "r"(o[1].y), "r"(o[1].z), "r"(o[1].w) : "memory");
-                // (the ring cells were read into registers and used above: the copies of slab ks + D may overwrite them now)
-                if (ks + D < ks1 && ks + D < nlive) GdCvt<TYPE>::issue(sl, rb, ks + D, qk);
-                asm volatile("cp.async.commit_group;" ::: "memory");
+            for (int kb = ks0; kb < ks1; kb += U) {
+                asm volatile("cp.async.wait_group %0;" :: "n"(D - U) : "memory");
+                uint4 o[U][4];
+                GdSlot sl[U];
+                #pragma unroll
+                for (int u2 = 0; u2 < U; u2++) {
+                    const int ks = kb + u2;
+                    sl[u2] = slot_of(ks - ks0);
+                    if (ks < ks1 && live(ks)) { GdRaw raw; GdCvt<TYPE>::fetch(raw, sl[u2], w, m, p.K, ks, hk); GdCvt<TYPE>::convert(raw, ks, hk, o[u2]); }
+                    else { o[u2][0] = o[u2][1] = o[u2][2] = o[u2][3] = make_uint4(0, 0, 0, 0); }
+                }
+                uint32_t sidx[U];
+                #pragma unroll
+                for (int u2 = 0; u2 < U; u2++) {
+                    if (kb + u2 < ks1) {
+                        const uint32_t s = (it + u2) % STAGES, ph = ((it + u2) / STAGES) & 1;
+                        sidx[u2] = s;
+                        gm_mbar_wait(empty0 + s * 8, ph ^ 1);                                       // the MMAs that read this slot are done
+                        const uint32_t dst = sA + s * STAGE_A;
+                        #pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[u2][c].x), "r"(o[u2][c].y), "r"(o[u2][c].z), "r"(o[u2][c].w) : "memory");
+                    }
+                }
+                // (the ring cells were read into registers and used above: the copies of the slabs D ahead may overwrite them now)
+                #pragma unroll
+                for (int u2 = 0; u2 < U; u2++) {
+                    const int ks = kb + u2;
+                    if (ks + D < ks1 && live(ks + D)) GdCvt<TYPE>::issue(sl[u2], w, m, p.K, ks + D, hk);
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                        // generic-proxy stores -> visible to the tensor core
                 __syncwarp();
-                if (lane == 0) gd2_arrive_remote(lafull0 + s * 8);
+                #pragma unroll
+                for (int u2 = 0; u2 < U; u2++)
+                    if (kb + u2 < ks1) { if (lane == 0) gd2_arrive_remote(lafull0 + sidx[u2] * 8); it++; }
             }
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
