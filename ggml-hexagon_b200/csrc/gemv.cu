@@ -576,7 +576,6 @@ static cudaError_t launch_g5c(GemvArgs & a, const Gemv5Tile & t, int nwarps, int
     if (smem > smem_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(b200_gemv5c_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (cluster > 8) { e = cudaFuncSetAttribute(b200_gemv5c_kernel<TYPE, RT, ITERS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1); if (e != cudaSuccess) return e; }
         smem_set[dev] = smem;
     }
     int total = 0;
@@ -594,7 +593,7 @@ static cudaError_t launch_g5c(GemvArgs & a, const Gemv5Tile & t, int nwarps, int
 }
 template <int TYPE>
 static bool try_gemv5c(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
-    const int mode = getenv("B200_GEMV5C") ? atoi(getenv("B200_GEMV5C")) : 1;            // 0: off; (read per launch: tests switch it)
+    const int mode = getenv("B200_GEMV5C") ? atoi(getenv("B200_GEMV5C")) : 0;            // opt-in (measured slower than quantise + gemv4/5); read per launch
     if (!mode || !a.x || ((uintptr_t) a.x & 15) || a.K % 128) return false;
     const WFields f = wfields(TYPE);
     const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);
@@ -619,7 +618,7 @@ static bool try_gemv5c(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * er
     for (int i = 0; i < f.n; i++) { t.foff[i] = off; off += rt * t.rowbytes[i]; }
     t.tile_bytes = (off + 15) & ~15;
     int cluster = getenv("B200_GEMV5C_CLUSTER") ? atoi(getenv("B200_GEMV5C_CLUSTER")) : 8;
-    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8 && cluster != 16) cluster = 8;
+    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) cluster = 8;            // portable cluster sizes only
     if (rt == 16)     *err = iters == 1 ? launch_g5c<TYPE, 16, 1>(a, t, nwarps, cluster, st, pdl) : launch_g5c<TYPE, 16, 2>(a, t, nwarps, cluster, st, pdl);
     else if (rt == 8) *err = iters == 1 ? launch_g5c<TYPE, 8, 1>(a, t, nwarps, cluster, st, pdl)  : launch_g5c<TYPE, 8, 2>(a, t, nwarps, cluster, st, pdl);
     else              *err = iters == 1 ? launch_g5c<TYPE, 4, 1>(a, t, nwarps, cluster, st, pdl)  : launch_g5c<TYPE, 4, 2>(a, t, nwarps, cluster, st, pdl);
