@@ -133,6 +133,28 @@ __host__ __device__ constexpr int gd2_stage_bytes(int bn) { return GM_BM * 128 +
 __host__ __device__ constexpr int gd2_stages(int bn, int type) { return (232448 - 1280 - gd2_raw_bytes(type)) / gd2_stage_bytes(bn); }
 __host__ __device__ constexpr int gd2_smem(int bn, int type) { return gd2_stages(bn, type) * gd2_stage_bytes(bn) + gd2_raw_bytes(type) + 256 + 1024; }
 static_assert(gd2_stages(256, T_Q4_0) == 6 && gd2_stages(256, T_Q8_0) >= 5 && gd2_stages(256, T_Q4_K) >= 5 && gd2_stages(256, T_Q6_K) >= 5, "stage count");
+// WTMA variant (the default): the native blocks arrive by TMA instead -- per-thread LDGSTS gathers of 16 + 4 bytes from 32 different rows cost
+// 32 L1 tag cycles per warp instruction, ~512 per stage against the 512 clocks the stage's MMAs take (without the 4-byte scale gather a
+// 4096^2 x 512 q4_0 GEMM went from 32.4 to 27.8 us).  One more warp per CTA loads RAW STAGES of gd3_rs slabs: for every SoA field a box
+// of 128 rows x the field's bytes of those slabs (128-byte rows 128-B swizzled, so that the converters' 16-byte reads of consecutive rows
+// spread over all banks), completing on rfull[rs]; the converter warps release a raw stage through rempty[rs] (8 arrivals).
+// Needs 16-byte aligned field rows (q4_0 / q8_0 scale rows: K % 256 == 0), else the ring variant above runs.
+// q6_K's d (2 bytes per row and super-block: no 16-byte box) stays a per-thread cp.async ring of GD3_DD super-blocks.
+constexpr int GD_W_WARP = GD_CVT_WARP0 + GD_CVT_WARPS;       // the weight producer warp of the WTMA variant
+constexpr int GD3_DD = 3;
+__host__ __device__ constexpr int gd3_rs(int type) { return type == T_Q8_0 ? 2 : 4; }          // slabs per raw stage (K-quants: one super-block)
+__host__ __device__ constexpr int gd3_rd(int type) { return type == T_Q6_K ? 2 : 3; }          // raw stages in flight
+__host__ __device__ constexpr int gd3_nf(int type) { return type == T_Q6_K ? 3 : 2; }          // fields that come by TMA (= SoA field index)
+__host__ __device__ constexpr int gd3_box(int type, int f) { return f == 0 ? 128 : (type == T_Q6_K && f == 1 ? 64 : 16); }      // box bytes along the row
+__host__ __device__ constexpr int gd3_adv(int type, int f) { return f == 0 ? 128 : (type == T_Q6_K && f == 1 ? 64 : (type == T_Q8_0 ? 8 : 16)); }      // row bytes per raw stage
+__host__ __device__ constexpr int gd3_foff(int f) { return f == 0 ? 0 : (f == 1 ? 16384 : 16384 + 8192); }
+__host__ __device__ constexpr int gd3_raw_stage(int type) { return type == T_Q6_K ? 16384 + 8192 + 2048 : 16384 + 2048; }
+__host__ __device__ constexpr int gd3_small_off(int type) { return type == T_Q6_K ? 16384 + 8192 : 16384; }      // the [128][16 B] scale / header tile
+__host__ __device__ constexpr int gd3_raw_bytes(int type) { return gd3_rd(type) * gd3_raw_stage(type) + (type == T_Q6_K ? GD3_DD * GD_CVT_WARPS * 32 * 4 : 0); }
+__host__ __device__ constexpr int gd3_stages(int bn, int type) { return (232448 - 1024 - 512 - gd3_raw_bytes(type)) / gd2_stage_bytes(bn); }
+__host__ __device__ constexpr int gd3_smem(int bn, int type) { return gd3_stages(bn, type) * gd2_stage_bytes(bn) + gd3_raw_bytes(type) + 512 + 1024; }
+static_assert(gd3_stages(256, T_Q4_0) >= 5 && gd3_stages(256, T_Q8_0) >= 5 && gd3_stages(256, T_Q4_K) >= 5 && gd3_stages(256, T_Q6_K) >= 5, "stage count");
+struct GdMaps { CUtensorMap b[3]; CUtensorMap w[3][3]; };      // activations (full / half / quarter boxes); weights [matrix][field]
 
 __device__ __forceinline__ uint32_t gd2_mapa(uint32_t saddr, uint32_t rank) {
     uint32_t r;
@@ -301,18 +323,21 @@ template <> struct GdCvt<T_Q6_K> {
     }
 };
 
-template <int BN, int TYPE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS, 1)
-gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmBh, const __grid_constant__ CUtensorMap tmBq,
-                   const GemmDenseArgs p) {
-    constexpr int STAGES = gd2_stages(BN, TYPE), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
-    constexpr int OFF_B = STAGES * STAGE_A, OFF_RAW = OFF_B + STAGES * STAGE_B, OFF_BAR = OFF_RAW + gd2_raw_bytes(TYPE);
+template <int BN, int TYPE, bool WTMA>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GD_THREADS + 32, 1)
+gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
+    constexpr int STAGES = WTMA ? gd3_stages(BN, TYPE) : gd2_stages(BN, TYPE), STAGE_A = GM_BM * 128, STAGE_B = (BN / 2) * 128;
+    constexpr int OFF_B = STAGES * STAGE_A, OFF_RAW = OFF_B + STAGES * STAGE_B, OFF_BAR = OFF_RAW + (WTMA ? gd3_raw_bytes(TYPE) : gd2_raw_bytes(TYPE));
+    constexpr int RD = WTMA ? gd3_rd(TYPE) : 0;
     extern __shared__ uint8_t gd_smem_raw[];
     const uint32_t base = (gm_smem_u32(gd_smem_raw) + 1023u) & ~1023u;
     uint8_t * smem = gd_smem_raw + (base - gm_smem_u32(gd_smem_raw));
     const uint32_t sA = base, sB = base + OFF_B, sRaw = base + OFF_RAW, bars = base + OFF_BAR;
     const uint32_t full0 = bars, empty0 = bars + STAGES * 8, afull0 = bars + 2 * STAGES * 8, tfull0 = bars + 3 * STAGES * 8, tempty0 = tfull0 + 2 * 8;
-    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8);
+    const uint32_t rfull0 = tempty0 + 2 * 8, rempty0 = rfull0 + RD * 8;                  // (WTMA only)
+    volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8 + 2 * RD * 8);
+    static_assert(3 * STAGES * 8 + 4 * 8 + 2 * RD * 8 + 4 <= (WTMA ? 512 : 256), "barrier area");
+    const CUtensorMap & tmB = maps.b[0]; const CUtensorMap & tmBh = maps.b[1]; const CUtensorMap & tmBq = maps.b[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
@@ -327,6 +352,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(afull0 + i * 8, 2 * GD_CVT_WARPS); }
         for (int i = 0; i < 2; i++) { gm_mbar_init(tfull0 + i * 8, 1); gm_mbar_init(tempty0 + i * 8, 2 * GD_EPI_WARPS); }
+        if (WTMA) for (int i = 0; i < RD; i++) { gm_mbar_init(rfull0 + i * 8, 1); gm_mbar_init(rempty0 + i * 8, GD_CVT_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {            // one warp of each CTA of the pair, collectively
@@ -429,7 +455,7 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
         }
         if (warp == 2 && lane == 0) gd_stamp(p, 6);
-    } else {
+    } else if (warp < GD_W_WARP) {
         // ===== converters (both CTAs): thread = row r of this CTA's 128, half slab hk; native blocks -> swizzled fp16 stage.
         // 128-byte swizzle of a K-major tile: row r lies at (r / 8) * 1024 + (r % 8) * 128, its 16-byte chunk c at ((c ^ (r % 8)) * 16):
         // the 8 lanes of a store phase (8 consecutive rows, same c) hit 8 different chunk positions = all 32 banks once.
@@ -440,6 +466,103 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
         for (int c = 0; c < 4; c++) choff[c] = rowoff + (uint32_t) (((hk * 4 + c) ^ (r & 7)) << 4);
         const uint32_t lafull0 = gd2_mapa(afull0, 0);
         uint32_t it = 0;
+        if constexpr (WTMA) {
+            constexpr int RS = gd3_rs(TYPE), RAWB = gd3_raw_stage(TYPE), SOFF = gd3_small_off(TYPE);
+            const uint32_t r7 = (uint32_t) (r & 7), r64 = (uint32_t) ((r >> 1) & 3);
+            const uint32_t dcell0 = sRaw + RD * RAWB + (uint32_t) ct * 4;                 // q6_K: this thread's d cells, GD_CVT_WARPS * 32 * 4 bytes apart
+            uint32_t rit = 0;
+            for (int work = pair; work < nwork; work += npairs) {
+                const GdUnit u = gd2_unit(p, work, BN);
+                const int tile = u.tile, sp = u.sp;
+                const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
+                const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
+                const int mt = local / p.ntiles;
+                const long long m = (long long) mt * 2 * GM_BM + (int) rank * GM_BM + r;
+                const bool row_ok = m < p.Ms[j];
+                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+                const int q0 = ks0 / RS, q1 = (ks1 + RS - 1) / RS;                         // raw stages are aligned in K (K-quants: super-blocks)
+                const uint8_t * const wd = j == 0 ? p.w[0][3] : (j == 1 ? p.w[1][3] : p.w[2][3]);
+                const long long sb0 = m * (p.K >> 8);
+                if constexpr (TYPE == T_Q6_K) {
+                    #pragma unroll 1
+                    for (int d = 0; d < GD3_DD; d++) {
+                        if (q0 + d < q1 && row_ok) gd_cpa4(dcell0 + (uint32_t) (d * GD_CVT_WARPS * 32 * 4), wd + (((sb0 + q0 + d) * 2) & ~3ll));
+                        asm volatile("cp.async.commit_group;" ::: "memory");
+                    }
+                }
+                #pragma unroll 1
+                for (int q = q0; q < q1; q++, rit++) {
+                    const uint32_t rs = rit % RD, rph = (rit / RD) & 1;
+                    gm_mbar_wait(rfull0 + rs * 8, rph);                                  // this raw stage's boxes have landed
+                    const uint32_t rb = sRaw + rs * RAWB, rowq = rb + (uint32_t) r * 128;
+                    const uint4 sc = gd_lds16(rb + SOFF + (uint32_t) r * 16);           // the row's 8 block scales / K-quant header / 16 q6_K scales
+                    const bool odd = TYPE == T_Q8_0 && (q & 1);                          // q8_0: the raw stage's 4 scales are the first or the second half of the 16 bytes
+                    const uint32_t scw[4] = {odd ? sc.z : sc.x, odd ? sc.w : sc.y, sc.z, sc.w};
+                    uint32_t dsel = 0;
+                    if constexpr (TYPE == T_Q6_K) {
+                        asm volatile("cp.async.wait_group %0;" :: "n"(GD3_DD - 1) : "memory");
+                        const uint32_t dw = gd_lds4(dcell0 + (uint32_t) (((q - q0) % GD3_DD) * GD_CVT_WARPS * 32 * 4));
+                        dsel = row_ok ? (((sb0 + q) & 1) ? dw >> 16 : dw & 0xFFFFu) : 0u;
+                    }
+                    #pragma unroll
+                    for (int jp = 0; jp < RS; jp += 2) {
+                        uint4 o[2][4];
+                        #pragma unroll
+                        for (int u2 = 0; u2 < 2; u2++) {
+                            const int jj = jp + u2, ks = q * RS + jj;
+                            GdRaw raw;
+                            if constexpr (TYPE == T_Q4_0) {
+                                raw.a = gd_lds16(rowq + (((uint32_t) (2 * jj + hk) ^ r7) << 4));
+                                raw.s0 = hk ? scw[jj] >> 16 : scw[jj] & 0xFFFFu;
+                            } else if constexpr (TYPE == T_Q8_0) {
+                                const uint32_t c = (uint32_t) (2 * (2 * jj + hk));
+                                raw.a = gd_lds16(rowq + ((c ^ r7) << 4)); raw.b = gd_lds16(rowq + (((c + 1) ^ r7) << 4));
+                                raw.s0 = hk ? scw[jj] >> 16 : scw[jj] & 0xFFFFu;
+                            } else if constexpr (TYPE == T_Q4_K) {
+                                raw.a = gd_lds16(rowq + (((uint32_t) (2 * jj) ^ r7) << 4)); raw.b = gd_lds16(rowq + (((uint32_t) (2 * jj + 1) ^ r7) << 4));
+                                raw.c = sc;
+                            } else {
+                                const uint32_t h = (uint32_t) (jj >> 1), c = 4 * h + 2 * (uint32_t) hk, rowh = rb + 16384 + (uint32_t) r * 64;
+                                raw.a = gd_lds16(rowq + ((c ^ r7) << 4)); raw.b = gd_lds16(rowq + (((c + 1) ^ r7) << 4));
+                                raw.c = gd_lds16(rowh + (((2 * h) ^ r64) << 4)); raw.e = gd_lds16(rowh + (((2 * h + 1) ^ r64) << 4));      // 64-byte swizzle
+                                raw.s0 = hk ? scw[jj] >> 16 : scw[jj] & 0xFFFFu;
+                                raw.s1 = dsel;
+                            }
+                            GdCvt<TYPE>::convert(raw, ks, hk, o[u2]);
+                        }
+                        uint32_t sidx[2];
+                        bool live[2];
+                        #pragma unroll
+                        for (int u2 = 0; u2 < 2; u2++) {
+                            const int ks = q * RS + jp + u2;
+                            live[u2] = ks >= ks0 && ks < ks1;                            // (a K split may begin or end inside a raw stage)
+                            if (live[u2]) {
+                                const uint32_t n = it + (u2 == 1 && live[0] ? 1u : 0u);
+                                const uint32_t s = n % STAGES, ph = (n / STAGES) & 1;
+                                sidx[u2] = s;
+                                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                    // the MMAs that read this slot are done
+                                const uint32_t dst = sA + s * STAGE_A;
+                                #pragma unroll
+                                for (int c = 0; c < 4; c++)
+                                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[u2][c].x), "r"(o[u2][c].y), "r"(o[u2][c].z), "r"(o[u2][c].w) : "memory");
+                            }
+                        }
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy stores -> visible to the tensor core
+                        __syncwarp();
+                        #pragma unroll
+                        for (int u2 = 0; u2 < 2; u2++)
+                            if (live[u2]) { if (lane == 0) gd2_arrive_remote(lafull0 + sidx[u2] * 8); it++; }
+                    }
+                    // (every lane's reads of the raw stage went into the conversions above, which the __syncwarp()s have seen through)
+                    if (lane == 0) gm_mbar_arrive(rempty0 + rs * 8);
+                    if constexpr (TYPE == T_Q6_K) {
+                        if (q + GD3_DD < q1 && row_ok) gd_cpa4(dcell0 + (uint32_t) (((q - q0) % GD3_DD) * GD_CVT_WARPS * 32 * 4), wd + (((sb0 + q + GD3_DD) * 2) & ~3ll));
+                        asm volatile("cp.async.commit_group;" ::: "memory");
+                    }
+                }
+                if constexpr (TYPE == T_Q6_K) asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+        } else
         for (int work = pair; work < nwork; work += npairs) {
             const GdUnit u = gd2_unit(p, work, BN);
             const int tile = u.tile, sp = u.sp;
@@ -514,6 +637,29 @@ gemm_dense2_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constan
             }
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
+    } else if (WTMA) {
+        // ===== weight producer (both CTAs, WTMA): this CTA's 128 rows of every SoA field, one raw stage (gd3_rs slabs) per barrier
+        constexpr int RS = gd3_rs(TYPE), RAWB = gd3_raw_stage(TYPE), NF = gd3_nf(TYPE);
+        constexpr uint32_t TX = 128u * (uint32_t) (gd3_box(TYPE, 0) + gd3_box(TYPE, 1) + (NF > 2 ? gd3_box(TYPE, 2) : 0));
+        uint32_t rit = 0;
+        for (int work = pair; work < nwork; work += npairs) {
+            const GdUnit u = gd2_unit(p, work, BN);
+            const int tile = u.tile, sp = u.sp;
+            const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
+            const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
+            const int mt = local / p.ntiles;
+            const int row0 = mt * 2 * GM_BM + (int) rank * GM_BM;
+            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            const int q0 = ks0 / RS, q1 = (ks1 + RS - 1) / RS;
+            for (int q = q0; q < q1; q++, rit++) {
+                const uint32_t rs = rit % RD, ph = (rit / RD) & 1;
+                gm_mbar_wait(rempty0 + rs * 8, ph ^ 1);
+                gm_mbar_expect_tx_elect(rfull0 + rs * 8, TX);
+                #pragma unroll
+                for (int f = 0; f < NF; f++)
+                    gm_tma_2d_elect(sRaw + rs * RAWB + gd3_foff(f), &maps.w[j][f], rfull0 + rs * 8, (q * gd3_adv(TYPE, f)) & ~15, row0);      // (box starts are 16-byte aligned: q8_0's 8 bytes of scales per raw stage come with their neighbours)
+            }
+        }
     }
     __syncwarp();                // the cluster barrier is warp-aligned: the single-lane roles rejoin their warps first
     gm_fence_before();
@@ -583,40 +729,56 @@ int gemm_dense_ksplit(int M, int N, int K, int sms) {
     return s < 2 ? 1 : s;
 }
 
-template <int BN, int TYPE>
-static cudaError_t gemm_dense2_launch_t(const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+template <int BN, int TYPE, bool WTMA>
+static cudaError_t gemm_dense2_launch_t(const GdMaps & maps, const GemmDenseArgs & p, int grid, cudaStream_t st) {
     static bool attr_done[64] = {false};          // per device
+    constexpr int smem = WTMA ? gd3_smem(BN, TYPE) : gd2_smem(BN, TYPE);
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     if (!attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN, TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd2_smem(BN, TYPE));
+        cudaError_t e = cudaFuncSetAttribute(gemm_dense2_kernel<BN, TYPE, WTMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         attr_done[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GD_THREADS); cfg.dynamicSmemBytes = gd2_smem(BN, TYPE); cfg.stream = st;      // __cluster_dims__(2): grid is even
+    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GD_THREADS + (WTMA ? 32 : 0)); cfg.dynamicSmemBytes = smem; cfg.stream = st;      // __cluster_dims__(2): grid is even
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, gemm_dense2_kernel<BN, TYPE>, tmB[0], tmB[1], tmB[2], p);
+    return cudaLaunchKernelEx(&cfg, gemm_dense2_kernel<BN, TYPE, WTMA>, maps, p);
 }
-template <int BN>
-static cudaError_t gemm_dense2_launch(int type, const CUtensorMap * tmB, const GemmDenseArgs & p, int grid, cudaStream_t st) {
+template <int BN, bool WTMA>
+static cudaError_t gemm_dense2_launch(int type, const GdMaps & maps, const GemmDenseArgs & p, int grid, cudaStream_t st) {
     switch (type) {
-        case T_Q4_0: return gemm_dense2_launch_t<BN, T_Q4_0>(tmB, p, grid, st);
-        case T_Q8_0: return gemm_dense2_launch_t<BN, T_Q8_0>(tmB, p, grid, st);
-        case T_Q4_K: return gemm_dense2_launch_t<BN, T_Q4_K>(tmB, p, grid, st);
-        case T_Q6_K: return gemm_dense2_launch_t<BN, T_Q6_K>(tmB, p, grid, st);
+        case T_Q4_0: return gemm_dense2_launch_t<BN, T_Q4_0, WTMA>(maps, p, grid, st);
+        case T_Q8_0: return gemm_dense2_launch_t<BN, T_Q8_0, WTMA>(maps, p, grid, st);
+        case T_Q4_K: return gemm_dense2_launch_t<BN, T_Q4_K, WTMA>(maps, p, grid, st);
+        case T_Q6_K: return gemm_dense2_launch_t<BN, T_Q6_K, WTMA>(maps, p, grid, st);
     }
     return cudaErrorInvalidValue;
 }
+// one SoA field of a weight matrix as a byte matrix [rows][rowbytes]: boxes of 128 rows x `box` bytes
+static bool make_map_field(CUtensorMap * m, const void * base, long long rows, long long rowbytes, int box) {
+    encode_tiled_t enc = encode_tiled();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t) rowbytes, (cuuint64_t) rows};
+    const cuuint64_t strides[1] = {(cuuint64_t) rowbytes};
+    const cuuint32_t bx[2] = {(cuuint32_t) box, (cuuint32_t) GM_BM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapSwizzle sw = box == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (box == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE);
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, bx, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+static int gd3_nf_rt(int type) { return type == T_Q6_K ? 3 : 2; }
+static int gd3_box_rt(int type, int f) { return gd3_box(type, f); }
 
 // nmat weight matrices A[j] (type `type`, SoA fields, M[j] rows of K) over the same activations B (fp16 [N][K], 16-B aligned rows);
 // out[j][n * out_cs[j] + m]; split_ws: workspace of ksplit * N * M floats (nmat == 1), or nullptr (no split)
 static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
                                const __half * B, int N, int K, int sms, int ksplit, float * split_ws, cudaStream_t st) {
     const int bn = gemm_dense_bn(M[0], N, sms);
-    CUtensorMap tmB[3];
+    GdMaps maps;
+    CUtensorMap * const tmB = maps.b;
     GemmDenseArgs p{};
     p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit;
     int tiles = 0;
@@ -631,6 +793,16 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
     }
     for (int f = 0; f < 3; f++)                 // activation boxes for full units and for the 1/2 and 1/4 wide units of the last wave
         if (!make_map_operand(&tmB[f], B, N, K, 2, (bn / 2) >> f)) return cudaErrorInvalidValue;
+    // weights by TMA wherever every field row starts 16-byte aligned (B200_GEMM_WTMA=0: the cp.async ring variant, read per launch for the tests)
+    bool wtma = !(getenv("B200_GEMM_WTMA") && atoi(getenv("B200_GEMM_WTMA")) == 0);
+    const WFields wf = wfields(type);
+    for (int j = 0; j < nmat && wtma; j++)
+        for (int f = 0; f < gd3_nf_rt(type) && wtma; f++) {
+            const long long rowbytes = (long long) (K / (type == T_Q4_K || type == T_Q6_K ? 256 : 32)) * wf.size[f];
+            wtma = rowbytes % 16 == 0 && ((uintptr_t) A[j].p[f] & 15) == 0 && make_map_field(&maps.w[j][f], A[j].p[f], M[j], rowbytes, gd3_box_rt(type, f));
+        }
+    for (int j = nmat; j < GD_MAXMAT && wtma; j++) for (int f = 0; f < 3; f++) maps.w[j][f] = maps.w[0][f];
+    if (wtma && gd3_nf_rt(type) == 2) for (int j = 0; j < GD_MAXMAT; j++) maps.w[j][2] = maps.w[j][0];
     if (ksplit > 1) { p.outs[0] = split_ws; p.out_css[0] = M[0]; p.split_stride = (long long) M[0] * N; }      // nmat == 1
     const int P = sms / 2;
     p.full_units = tiles * ksplit; p.narrow_f = 1;
@@ -647,7 +819,8 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
     if (trace) cudaStreamIsCapturing(st, &cap);                 // the trace allocates and synchronises: not inside a stream capture
     if (trace && cap == cudaStreamCaptureStatusNone && cudaMalloc((void **) &p.trace, (size_t) 2 * pairs * 8 * 8) == cudaSuccess)
         cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
-    const cudaError_t e = bn == 256 ? gemm_dense2_launch<256>(type, tmB, p, 2 * pairs, st) : gemm_dense2_launch<128>(type, tmB, p, 2 * pairs, st);
+    const cudaError_t e = wtma ? (bn == 256 ? gemm_dense2_launch<256, true>(type, maps, p, 2 * pairs, st) : gemm_dense2_launch<128, true>(type, maps, p, 2 * pairs, st))
+                               : (bn == 256 ? gemm_dense2_launch<256, false>(type, maps, p, 2 * pairs, st) : gemm_dense2_launch<128, false>(type, maps, p, 2 * pairs, st));
     if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
         std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
         cudaStreamSynchronize(st);

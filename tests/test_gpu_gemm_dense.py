@@ -28,6 +28,13 @@ def _dense_from_16_columns(monkeypatch):
     monkeypatch.delenv("B200_GEMM_BN", raising=False)
 
 
+@pytest.fixture(params=["tma", "ring"])
+def wpath(request, monkeypatch):
+    """how the native blocks reach the converter warps: TMA boxes (default) or per-thread cp.async rings (rows that are not 16-byte aligned)"""
+    monkeypatch.setenv("B200_GEMM_WTMA", "1" if request.param == "tma" else "0")
+    return request.param
+
+
 @pytest.fixture(scope="module")
 def sess():
     s = B.Session(0)
@@ -37,7 +44,7 @@ def sess():
 
 @pytest.mark.parametrize("t,name", ALL)
 @pytest.mark.parametrize("M,K,N", [(128, 256, 128), (16, 256, 32), (200, 1024, 77), (384, 4096, 512), (130, 512, 33), (257, 11008, 129)])
-def test_dense_vs_oracle(sess, t, name, M, K, N):
+def test_dense_vs_oracle(sess, wpath, t, name, M, K, N):
     rng = np.random.default_rng(M + 3 * K + 7 * N + t)
     raw = O.random_blocks(t, M, K, rng)
     w = sess.weights(t, raw, K)
@@ -68,7 +75,7 @@ def test_dense_ragged_k(sess, t, name):
 
 @pytest.mark.parametrize("bn", ["128", "256"])
 @pytest.mark.parametrize("t,name", ALL)
-def test_dense_both_tile_widths(sess, monkeypatch, bn, t, name):
+def test_dense_both_tile_widths(sess, monkeypatch, wpath, bn, t, name):
     monkeypatch.setenv("B200_GEMM_BN", bn)
     rng = np.random.default_rng(43 + t)
     M, K, N = 300, 1280, 300
@@ -99,11 +106,13 @@ def test_dense_integer_product_is_exact(sess):
     w.free()
 
 
-@pytest.mark.parametrize("t,name", [(O.Q8_0, "q8_0"), (O.Q4_K, "q4_K"), (O.Q6_K, "q6_K")])
-def test_dense_split_k_small_m(sess, t, name):
-    """few output tiles (M = 256, N = 96 -> 2 tiles): the K range is split over work items and reduced in a second kernel"""
+@pytest.mark.parametrize("K", [8192, 2304])
+@pytest.mark.parametrize("t,name", ALL)
+def test_dense_split_k_small_m(sess, wpath, t, name, K):
+    """few output tiles (M = 256, N = 96 -> 2 tiles): the K range is split over work items and reduced in a second kernel;
+    K = 2304: 36 slabs in 4 splits of 9 -> the splits begin and end inside the 4-slab raw stages (super-blocks) of the weight loads"""
     rng = np.random.default_rng(23 + t)
-    M, K, N = 256, 8192, 96
+    M, N = 256, 96
     raw = O.random_blocks(t, M, K, rng)
     w = sess.weights(t, raw, K)
     x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
