@@ -52,17 +52,26 @@ struct GemmDenseArgs {
     const uint8_t * w[3][4];                   // SoA field arrays of each weight matrix (b200_internal.cuh), at the matrix's first block
     float * outs[3]; long long out_css[3]; int Ms[3];
     int tile_end[3];                           // tiles (m-tile x n-tile) up to and including matrix j; INT_MAX past nmat
-    // the last, partial wave in narrow units: work items >= full_units are 256 x (BN / narrow_f) column slices of the remaining tiles,
-    // so that a wave with few tiles left takes 1/2 or 1/4 of a tile time instead of a whole one (narrow_f = 1: none; ksplit == 1)
-    int full_units, narrow_f;
+    // the last, partial wave as a stream-K tail (tail_T > 0; ksplit == 1): its `tail_T / nks` tiles are cut into one chunk of tail_L
+    // consecutive (tile, slab) steps per CTA pair, so that a wave with few tiles left costs tiles / pairs of a tile time instead of a whole
+    // one.  A chunk is at most two segments (the end of one tile, the beginning of the next); segment s of pair c leaves its 256 x BN
+    // partial sums in tail_ws slot 2 c + s, and gd_tail_fixup_kernel adds the slots of every tile in chunk order (deterministic).
+    int full_units, tail_T, tail_L;
+    float * tail_ws;
 };
-struct GdUnit { int tile, sp, n_off, n_w; };    // n_off: first column inside the tile; n_w: columns = N of the MMA
-__device__ __forceinline__ GdUnit gd2_unit(const GemmDenseArgs & p, const int work, const int BN) {
+struct GdUnit { int tile, sp, ks0, ks1, slot; };    // slabs [ks0, ks1) of `tile`; slot >= 0: partial sums to that tail_ws slot
+__device__ __forceinline__ GdUnit gd2_unit(const GemmDenseArgs & p, const int work, const int nks, const int pair, const int npairs) {
     GdUnit u;
-    if (work < p.full_units) { u.tile = work / p.ksplit; u.sp = work - u.tile * p.ksplit; u.n_off = 0; u.n_w = BN; }
-    else {
-        const int r = work - p.full_units, t = r / p.narrow_f;
-        u.tile = p.full_units + t; u.sp = 0; u.n_w = BN / p.narrow_f; u.n_off = (r - t * p.narrow_f) * u.n_w;
+    if (work < p.full_units) {
+        u.tile = work / p.ksplit; u.sp = work - u.tile * p.ksplit; u.slot = -1;
+        u.ks0 = (int) ((long long) nks * u.sp / p.ksplit); u.ks1 = (int) ((long long) nks * (u.sp + 1) / p.ksplit);
+    } else {
+        const int seg = work - p.full_units >= npairs ? 1 : 0;
+        const int a = pair * p.tail_L, b = min(a + p.tail_L, p.tail_T);
+        const int t0 = a / nks, e0 = (t0 + 1) * nks;
+        u.sp = 0; u.slot = 2 * pair + seg;
+        if (seg == 0) { u.tile = p.full_units + t0; u.ks0 = a - t0 * nks; u.ks1 = min(b, e0) - t0 * nks; }      // (a >= b: empty)
+        else          { u.tile = p.full_units + t0 + 1; u.ks0 = 0; u.ks1 = b - e0; }                             // (b <= e0: empty)
     }
     return u;
 }
@@ -103,13 +112,6 @@ __device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * c
         if (row_ok && ncols > (c + 1) * 32) gd_store_chunk(colp + (long long) (c + 1) * 32 * cs, cs, vb, ncols - (c + 1) * 32);
         if (c + 2 < NCH) gm_tmem_ld_wait();
     }
-}
-
-__device__ __forceinline__ void gd_epilogue_warp1(const uint32_t taddr, float * colp, const long long cs, const int ncols, const bool row_ok) {
-    int va[32];
-    gm_tmem_ld32(taddr, va);
-    gm_tmem_ld_wait();
-    if (row_ok && ncols > 0) gd_store_chunk(colp, cs, va, ncols);
 }
 
 // ------------------------------------------------------------------------------------------------ the CTA-pair kernel
@@ -154,7 +156,7 @@ __host__ __device__ constexpr int gd3_raw_bytes(int type) { return gd3_rd(type) 
 __host__ __device__ constexpr int gd3_stages(int bn, int type) { return (232448 - 1024 - 512 - gd3_raw_bytes(type)) / gd2_stage_bytes(bn); }
 __host__ __device__ constexpr int gd3_smem(int bn, int type) { return gd3_stages(bn, type) * gd2_stage_bytes(bn) + gd3_raw_bytes(type) + 512 + 1024; }
 static_assert(gd3_stages(256, T_Q4_0) >= 5 && gd3_stages(256, T_Q8_0) >= 5 && gd3_stages(256, T_Q4_K) >= 5 && gd3_stages(256, T_Q6_K) >= 5, "stage count");
-struct GdMaps { CUtensorMap b[3]; CUtensorMap w[3][3]; };      // activations (full / half / quarter boxes); weights [matrix][field]
+struct GdMaps { CUtensorMap b[1]; CUtensorMap w[3][3]; };      // activations; weights [matrix][field]
 
 __device__ __forceinline__ uint32_t gd2_mapa(uint32_t saddr, uint32_t rank) {
     uint32_t r;
@@ -187,6 +189,13 @@ __device__ __forceinline__ void gd2_arrive_cluster(uint32_t bar_cluster) {
 // arrive has to order is this CTA's own shared-memory stores, already made visible to the async proxy by fence.proxy.async.
 __device__ __forceinline__ void gd2_arrive_remote(uint32_t bar_cluster) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(bar_cluster) : "memory");
+}
+// predicated forms (no branch around the single-lane arrive: BSSY / BRA / BSYNC per use otherwise)
+__device__ __forceinline__ void gd2_arrive_remote_if(uint32_t bar_cluster, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %1, 0;\n\t@p mbarrier.arrive.shared::cluster.b64 _, [%0];\n\t}" :: "r"(bar_cluster), "r"((uint32_t) pred) : "memory");
+}
+__device__ __forceinline__ void gd2_arrive_local_if(uint32_t bar, bool pred) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .b64 st;\n\tsetp.ne.b32 p, %1, 0;\n\t@p mbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" :: "r"(bar), "r"((uint32_t) pred) : "memory");
 }
 __device__ __forceinline__ void gd2_mbar_wait_cluster(uint32_t bar, uint32_t parity) {          // acquire at cluster scope: the arrivals are remote
     uint32_t ok = 0;
@@ -337,7 +346,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
     const uint32_t rfull0 = tempty0 + 2 * 8, rempty0 = rfull0 + RD * 8;                  // (WTMA only)
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8 + 2 * RD * 8);
     static_assert(3 * STAGES * 8 + 4 * 8 + 2 * RD * 8 + 4 <= (WTMA ? 512 : 256), "barrier area");
-    const CUtensorMap & tmB = maps.b[0]; const CUtensorMap & tmBh = maps.b[1]; const CUtensorMap & tmBq = maps.b[2];
+    const CUtensorMap & tmB = maps.b[0];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t rank;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
@@ -347,7 +356,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
     const int nks = (p.K + GD_KS - 1) / GD_KS;
-    const int nwork = p.full_units + (p.tile_end[p.nmat - 1] * p.ksplit - p.full_units) * p.narrow_f;
+    const int nwork = p.full_units + (p.tail_T > 0 ? 2 * npairs : 0);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < STAGES; i++) { gm_mbar_init(full0 + i * 8, 1); gm_mbar_init(empty0 + i * 8, 1); gm_mbar_init(afull0 + i * 8, 2 * GD_CVT_WARPS); }
@@ -375,20 +384,18 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             const uint32_t lfull0 = gd2_mapa(full0, 0);
             uint32_t it = 0;
             for (int work = pair; work < nwork; work += npairs) {
-                const GdUnit u = gd2_unit(p, work, BN);
-                const int tile = u.tile, sp = u.sp;
+                const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+                const int tile = u.tile;
                 const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
                 const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
                 const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
-                const CUtensorMap * const tmBu = u.n_w == BN ? &tmB : (u.n_w == BN / 2 ? &tmBh : &tmBq);      // box rows = n_w / 2
-                const uint32_t tx = 2u * ((uint32_t) (u.n_w / 2) * 128u);
-                const int brow = nt * BN + u.n_off + (int) rank * (u.n_w / 2);
-                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
-                for (int ks = ks0; ks < ks1; ks++, it++) {
+                constexpr uint32_t tx = 2u * ((uint32_t) (BN / 2) * 128u);
+                const int brow = nt * BN + (int) rank * (BN / 2);
+                for (int ks = u.ks0; ks < u.ks1; ks++, it++) {
                     const uint32_t s = it % STAGES, ph = (it / STAGES) & 1;
                     gm_mbar_wait(empty0 + s * 8, ph ^ 1);
                     if (rank == 0) gm_mbar_expect_tx_elect(full0 + s * 8, tx);
-                    gd2_tma_2d(sB + s * STAGE_B, tmBu, lfull0 + s * 8, ks * GD_KS, brow);
+                    gd2_tma_2d(sB + s * STAGE_B, &tmB, lfull0 + s * 8, ks * GD_KS, brow);
                 }
             }
         }
@@ -396,11 +403,11 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
         // ===== MMA issuer: warp 1 of the leader CTA (whole warp, one elected lane issues), M = 256 over the pair
         if (rank == 0) {
             uint32_t it = 0, tc = 0;
-            for (int work = pair; work < nwork; work += npairs, tc++) {
-                const GdUnit u = gd2_unit(p, work, BN);
-                const int sp = u.sp;
-                const uint32_t idesc = (1u << 4) | ((uint32_t) (u.n_w >> 3) << 17) | ((uint32_t) ((2 * GM_BM) >> 4) << 24);
-                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
+            constexpr uint32_t idesc = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) ((2 * GM_BM) >> 4) << 24);
+            for (int work = pair; work < nwork; work += npairs) {
+                const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+                const int ks0 = u.ks0, ks1 = u.ks1;
+                if (ks0 >= ks1) continue;                            // (an empty tail segment: every role skips it)
                 const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
                 gm_mbar_wait(tempty0 + buf * 8, bph ^ 1);
                 gm_fence_after();
@@ -417,6 +424,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                     gd2_commit_both(empty0 + s * 8);
                 }
                 gd2_commit_both(tfull0 + buf * 8);
+                tc++;
             }
             if (lane == 0) gd_stamp(p, 3);
         }
@@ -427,32 +435,33 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
         const uint32_t tbase = tmem + ((uint32_t) (q * 32) << 16);
         const uint32_t ltempty0 = gd2_mapa(tempty0, 0);
         uint32_t tc = 0;
-        for (int work = pair; work < nwork; work += npairs, tc++) {
-            const GdUnit u = gd2_unit(p, work, BN);
-            const int tile = u.tile, sp = u.sp;
+        for (int work = pair; work < nwork; work += npairs) {
+            const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+            if (u.ks0 >= u.ks1) continue;
+            const int tile = u.tile;
             const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
             const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
             const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
-            float * const outp = p.outs[j] + (long long) sp * p.split_stride;
-            const long long ocs = p.out_css[j];
             const int m = mt * 2 * GM_BM + (int) rank * GM_BM + m_local;
             const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
             gm_mbar_wait(tfull0 + buf * 8, bph);
             gm_fence_after();
             if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
-            // this warp: TMEM lanes q * 32 .. +31, columns half * (n_w / 2) .. + n_w / 2 of the unit
-            const int c0 = half * (u.n_w / 2), n0 = nt * BN + u.n_off + c0;
+            // this warp: TMEM lanes q * 32 .. +31, columns half * (BN / 2) .. + BN / 2 of the tile
+            const int c0 = half * (BN / 2), n0 = nt * BN + c0;
             const uint32_t ta = tbase + buf * BN + c0;
-            float * const colp = outp + (long long) n0 * ocs + m;
-            const bool row_ok = m < p.Ms[j];
-            if (u.n_w == BN)               gd_epilogue_warp<BN / 64>(ta, colp, ocs, p.N - n0, row_ok);
-            else if (u.n_w == BN / 2) {
-                if constexpr (BN == 256)   gd_epilogue_warp<BN / 128>(ta, colp, ocs, p.N - n0, row_ok);
-                else                       gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
-            } else                         gd_epilogue_warp1(ta, colp, ocs, p.N - n0, row_ok);
+            if (u.slot < 0) {
+                float * const outp = p.outs[j] + (long long) u.sp * p.split_stride;
+                const long long ocs = p.out_css[j];
+                gd_epilogue_warp<BN / 64>(ta, outp + (long long) n0 * ocs + m, ocs, p.N - n0, m < p.Ms[j]);
+            } else {                                                // tail segment: the whole 256 x BN partial tile, column-major, into its slot
+                float * const slotp = p.tail_ws + (size_t) u.slot * (2 * GM_BM * BN);
+                gd_epilogue_warp<BN / 64>(ta, slotp + (size_t) c0 * (2 * GM_BM) + (int) rank * GM_BM + m_local, 2 * GM_BM, BN, true);
+            }
             gm_fence_before();
             __syncwarp();
             if (lane == 0) gd2_arrive_cluster(ltempty0 + buf * 8);
+            tc++;
         }
         if (warp == 2 && lane == 0) gd_stamp(p, 6);
     } else if (warp < GD_W_WARP) {
@@ -470,16 +479,18 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             constexpr int RS = gd3_rs(TYPE), RAWB = gd3_raw_stage(TYPE), SOFF = gd3_small_off(TYPE);
             const uint32_t r7 = (uint32_t) (r & 7), r64 = (uint32_t) ((r >> 1) & 3);
             const uint32_t dcell0 = sRaw + RD * RAWB + (uint32_t) ct * 4;                 // q6_K: this thread's d cells, GD_CVT_WARPS * 32 * 4 bytes apart
-            uint32_t rit = 0;
+            uint32_t rs = 0, rph = 0, st = 0, sph = 1;          // raw-stage ring position / parity; fp16 stage ring position / parity of its `empty` wait
+            const bool lane0 = lane == 0;
             for (int work = pair; work < nwork; work += npairs) {
-                const GdUnit u = gd2_unit(p, work, BN);
-                const int tile = u.tile, sp = u.sp;
+                const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+                const int ks0 = u.ks0, ks1 = u.ks1;
+                if (ks0 >= ks1) continue;
+                const int tile = u.tile;
                 const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
                 const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
                 const int mt = local / p.ntiles;
                 const long long m = (long long) mt * 2 * GM_BM + (int) rank * GM_BM + r;
                 const bool row_ok = m < p.Ms[j];
-                const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
                 const int q0 = ks0 / RS, q1 = (ks1 + RS - 1) / RS;                         // raw stages are aligned in K (K-quants: super-blocks)
                 const uint8_t * const wd = j == 0 ? p.w[0][3] : (j == 1 ? p.w[1][3] : p.w[2][3]);
                 const long long sb0 = m * (p.K >> 8);
@@ -491,8 +502,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                     }
                 }
                 #pragma unroll 1
-                for (int q = q0; q < q1; q++, rit++) {
-                    const uint32_t rs = rit % RD, rph = (rit / RD) & 1;
+                for (int q = q0; q < q1; q++) {
                     gm_mbar_wait(rfull0 + rs * 8, rph);                                  // this raw stage's boxes have landed
                     const uint32_t rb = sRaw + rs * RAWB, rowq = rb + (uint32_t) r * 128;
                     const uint4 sc = gd_lds16(rb + SOFF + (uint32_t) r * 16);           // the row's 8 block scales / K-quant header / 16 q6_K scales
@@ -536,25 +546,24 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                         for (int u2 = 0; u2 < 2; u2++) {
                             const int ks = q * RS + jp + u2;
                             live[u2] = ks >= ks0 && ks < ks1;                            // (a K split may begin or end inside a raw stage)
+                            sidx[u2] = st;
                             if (live[u2]) {
-                                const uint32_t n = it + (u2 == 1 && live[0] ? 1u : 0u);
-                                const uint32_t s = n % STAGES, ph = (n / STAGES) & 1;
-                                sidx[u2] = s;
-                                gm_mbar_wait(empty0 + s * 8, ph ^ 1);                    // the MMAs that read this slot are done
-                                const uint32_t dst = sA + s * STAGE_A;
+                                gm_mbar_wait(empty0 + st * 8, sph);                      // the MMAs that read this slot are done
+                                const uint32_t dst = sA + st * STAGE_A;
                                 #pragma unroll
                                 for (int c = 0; c < 4; c++)
                                     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(dst + choff[c]), "r"(o[u2][c].x), "r"(o[u2][c].y), "r"(o[u2][c].z), "r"(o[u2][c].w) : "memory");
+                                if (++st == STAGES) { st = 0; sph ^= 1; }
                             }
                         }
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy stores -> visible to the tensor core
                         __syncwarp();
                         #pragma unroll
-                        for (int u2 = 0; u2 < 2; u2++)
-                            if (live[u2]) { if (lane == 0) gd2_arrive_remote(lafull0 + sidx[u2] * 8); it++; }
+                        for (int u2 = 0; u2 < 2; u2++) gd2_arrive_remote_if(lafull0 + sidx[u2] * 8, lane0 && live[u2]);
                     }
                     // (every lane's reads of the raw stage went into the conversions above, which the __syncwarp()s have seen through)
-                    if (lane == 0) gm_mbar_arrive(rempty0 + rs * 8);
+                    gd2_arrive_local_if(rempty0 + rs * 8, lane0);
+                    if (++rs == RD) { rs = 0; rph ^= 1; }
                     if constexpr (TYPE == T_Q6_K) {
                         if (q + GD3_DD < q1 && row_ok) gd_cpa4(dcell0 + (uint32_t) (((q - q0) % GD3_DD) * GD_CVT_WARPS * 32 * 4), wd + (((sb0 + q + GD3_DD) * 2) & ~3ll));
                         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -564,8 +573,10 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             }
         } else
         for (int work = pair; work < nwork; work += npairs) {
-            const GdUnit u = gd2_unit(p, work, BN);
-            const int tile = u.tile, sp = u.sp;
+            const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+            const int ks0 = u.ks0, ks1 = u.ks1;
+            if (ks0 >= ks1) continue;
+            const int tile = u.tile;
             const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
             const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
             const int mt = local / p.ntiles;
@@ -574,7 +585,6 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             const uint8_t * w[4];
             #pragma unroll
             for (int f = 0; f < 4; f++) w[f] = j == 0 ? p.w[0][f] : (j == 1 ? p.w[1][f] : p.w[2][f]);
-            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
             // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
             auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
             // D slabs in flight per thread: cp.async copies into the thread's ring cells, one commit group per slab (empty groups keep
@@ -643,14 +653,14 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
         constexpr uint32_t TX = 128u * (uint32_t) (gd3_box(TYPE, 0) + gd3_box(TYPE, 1) + (NF > 2 ? gd3_box(TYPE, 2) : 0));
         uint32_t rit = 0;
         for (int work = pair; work < nwork; work += npairs) {
-            const GdUnit u = gd2_unit(p, work, BN);
-            const int tile = u.tile, sp = u.sp;
+            const GdUnit u = gd2_unit(p, work, nks, pair, npairs);
+            if (u.ks0 >= u.ks1) continue;
+            const int tile = u.tile;
             const int j = (tile >= p.tile_end[0]) + (tile >= p.tile_end[1]);
             const int local = tile - (j == 0 ? 0 : p.tile_end[j - 1]);
             const int mt = local / p.ntiles;
             const int row0 = mt * 2 * GM_BM + (int) rank * GM_BM;
-            const int ks0 = (int) ((long long) nks * sp / p.ksplit), ks1 = (int) ((long long) nks * (sp + 1) / p.ksplit);
-            const int q0 = ks0 / RS, q1 = (ks1 + RS - 1) / RS;
+            const int q0 = u.ks0 / RS, q1 = (u.ks1 + RS - 1) / RS;
             for (int q = q0; q < q1; q++, rit++) {
                 const uint32_t rs = rit % RD, ph = (rit / RD) & 1;
                 gm_mbar_wait(rempty0 + rs * 8, ph ^ 1);
@@ -711,6 +721,39 @@ cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, 
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel, (const char *) x, row_stride_bytes, K, N, out);
 }
+// ---- stream-K tail: dst tile = sum of the tail_ws slots of the chunks that cover it, in chunk order
+struct GdFixArgs {
+    const float * ws; int tail_T, tail_L, nks, full_tiles, ntiles, bn, N;
+    float * outs[3]; long long out_css[3]; int Ms[3]; int tile_end[3];
+};
+__global__ void __launch_bounds__(256)
+gd_tail_fixup_kernel(const GdFixArgs a) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int per_tile = a.bn * (2 * GM_BM / 4) / 256;                 // blocks per tile: one float4 (4 rows of a column) per thread
+    const int tt = blockIdx.x / per_tile, e = (blockIdx.x - tt * per_tile) * 256 + threadIdx.x;
+    const int n_local = e / (2 * GM_BM / 4), m4 = e - n_local * (2 * GM_BM / 4);
+    const int tile = a.full_tiles + tt;
+    const int j = (tile >= a.tile_end[0]) + (tile >= a.tile_end[1]);
+    const int local = tile - (j == 0 ? 0 : a.tile_end[j - 1]);
+    const int mt = local / a.ntiles, nt = local - mt * a.ntiles;
+    const int n = nt * a.bn + n_local, m = mt * 2 * GM_BM + m4 * 4;
+    if (n >= a.N || m >= a.Ms[j]) return;
+    const int u0 = tt * a.nks, u1 = min(u0 + a.nks, a.tail_T);
+    const int c0 = u0 / a.tail_L, c1 = (u1 - 1) / a.tail_L;
+    const size_t tile_elems = (size_t) 2 * GM_BM * a.bn;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int c = c0; c <= c1; c++) {
+        const int seg = (c * a.tail_L) / a.nks == tt ? 0 : 1;          // the chunk began in this tile, or in the one before
+        const float4 v = *(const float4 *) (a.ws + (size_t) (2 * c + seg) * tile_elems + (size_t) n_local * (2 * GM_BM) + m4 * 4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    float * o = a.outs[j] + (long long) n * a.out_css[j] + m;
+    if (m + 3 < a.Ms[j] && (((uintptr_t) o) & 15) == 0) *(float4 *) o = acc;
+    else { o[0] = acc.x; if (m + 1 < a.Ms[j]) o[1] = acc.y; if (m + 2 < a.Ms[j]) o[2] = acc.z; if (m + 3 < a.Ms[j]) o[3] = acc.w; }
+}
+size_t gemm_dense_tail_ws_bytes(int sms) { return (size_t) 2 * (sms / 2) * 2 * GM_BM * 256 * sizeof(float); }      // 2 slots per CTA pair, 256 x 256 floats
+
 // ------------------------------------------------------------------------------------------------ host: launch
 // N tile: 256 columns halve the number of times the weights travel from L2 to the SMs (few tiles are spread with split-K instead)
 int gemm_dense_bn(int M, int N, int sms) {
@@ -775,7 +818,7 @@ static int gd3_box_rt(int type, int f) { return gd3_box(type, f); }
 // nmat weight matrices A[j] (type `type`, SoA fields, M[j] rows of K) over the same activations B (fp16 [N][K], 16-B aligned rows);
 // out[j][n * out_cs[j] + m]; split_ws: workspace of ksplit * N * M floats (nmat == 1), or nullptr (no split)
 static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
-                               const __half * B, int N, int K, int sms, int ksplit, float * split_ws, cudaStream_t st) {
+                               const __half * B, int N, int K, int sms, int ksplit, float * split_ws, float * tail_ws, int * nlaunch, cudaStream_t st) {
     const int bn = gemm_dense_bn(M[0], N, sms);
     GdMaps maps;
     CUtensorMap * const tmB = maps.b;
@@ -791,8 +834,7 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
         if (j < nmat) { tiles += ((M[j] + 2 * GM_BM - 1) / (2 * GM_BM)) * p.ntiles; p.outs[j] = out[j]; p.out_css[j] = out_cs[j]; p.Ms[j] = M[j]; p.tile_end[j] = tiles; }
         else { p.outs[j] = nullptr; p.out_css[j] = 0; p.Ms[j] = 0; p.tile_end[j] = 0x7fffffff; }
     }
-    for (int f = 0; f < 3; f++)                 // activation boxes for full units and for the 1/2 and 1/4 wide units of the last wave
-        if (!make_map_operand(&tmB[f], B, N, K, 2, (bn / 2) >> f)) return cudaErrorInvalidValue;
+    if (!make_map_operand(&tmB[0], B, N, K, 2, bn / 2)) return cudaErrorInvalidValue;
     // weights by TMA wherever every field row starts 16-byte aligned (B200_GEMM_WTMA=0: the cp.async ring variant, read per launch for the tests)
     bool wtma = !(getenv("B200_GEMM_WTMA") && atoi(getenv("B200_GEMM_WTMA")) == 0);
     const WFields wf = wfields(type);
@@ -805,15 +847,18 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
     if (wtma && gd3_nf_rt(type) == 2) for (int j = 0; j < GD_MAXMAT; j++) maps.w[j][2] = maps.w[j][0];
     if (ksplit > 1) { p.outs[0] = split_ws; p.out_css[0] = M[0]; p.split_stride = (long long) M[0] * N; }      // nmat == 1
     const int P = sms / 2;
-    p.full_units = tiles * ksplit; p.narrow_f = 1;
-    static const bool narrow_on = !(getenv("B200_GEMM_NARROW") && atoi(getenv("B200_GEMM_NARROW")) == 0);
-    if (narrow_on && ksplit == 1 && bn == 256 && tiles > P) {
-        const int rem = tiles % P;
-        const int f = rem == 0 ? 1 : (4 * rem <= P ? 4 : (2 * rem <= P ? 2 : 1));
-        if (f > 1) { p.full_units = tiles - rem; p.narrow_f = f; }
+    // stream-K tail over the last, partial wave (B200_GEMM_TAIL=0: off; =<percent>: the fill of the last wave up to which it is cut up).
+    // Measured (q4_0, 512 columns): 11008 x 4096 (12 tiles left of 74) 55.9 -> 50.8 us; 14336 x 4096 (38 left) 58.1 -> 65.9 us: every partial
+    // tile is 256 KB written and read again, which eats the gain from about a third of a wave on -> default 25
+    p.full_units = tiles * ksplit; p.tail_T = 0; p.tail_L = 1; p.tail_ws = tail_ws;
+    const int nks = (K + GD_KS - 1) / GD_KS;
+    const int tail_pct = getenv("B200_GEMM_TAIL") ? atoi(getenv("B200_GEMM_TAIL")) : 25;
+    const int rem = tiles % P;
+    if (tail_ws && tail_pct > 0 && ksplit == 1 && rem > 0 && rem * 100 <= tail_pct * P && nks >= 16 && (tiles > P || 2 * rem > P)) {
+        p.full_units = tiles - rem; p.tail_T = rem * nks; p.tail_L = (p.tail_T + P - 1) / P;
     }
-    const int work = p.full_units + (tiles * ksplit - p.full_units) * p.narrow_f;
-    const int pairs = work < P ? work : P;
+    const int pairs = p.tail_T > 0 ? P : (p.full_units < P ? p.full_units : P);
+    const int work = p.full_units + (p.tail_T > 0 ? 2 * pairs : 0);
     static const bool trace = getenv("B200_GEMM_TRACE") && atoi(getenv("B200_GEMM_TRACE")) > 0;
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (trace) cudaStreamIsCapturing(st, &cap);                 // the trace allocates and synchronises: not inside a stream capture
@@ -821,6 +866,21 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
         cudaMemsetAsync(p.trace, 0, (size_t) 2 * pairs * 8 * 8, st);
     const cudaError_t e = wtma ? (bn == 256 ? gemm_dense2_launch<256, true>(type, maps, p, 2 * pairs, st) : gemm_dense2_launch<128, true>(type, maps, p, 2 * pairs, st))
                                : (bn == 256 ? gemm_dense2_launch<256, false>(type, maps, p, 2 * pairs, st) : gemm_dense2_launch<128, false>(type, maps, p, 2 * pairs, st));
+    if (nlaunch) *nlaunch = 1;
+    if (e == cudaSuccess && p.tail_T > 0) {
+        GdFixArgs fa{};
+        fa.ws = tail_ws; fa.tail_T = p.tail_T; fa.tail_L = p.tail_L; fa.nks = nks; fa.full_tiles = p.full_units; fa.ntiles = p.ntiles; fa.bn = bn; fa.N = N;
+        for (int j = 0; j < GD_MAXMAT; j++) { fa.outs[j] = p.outs[j]; fa.out_css[j] = p.out_css[j]; fa.Ms[j] = p.Ms[j]; fa.tile_end[j] = p.tile_end[j]; }
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned) (rem * (bn * (2 * GM_BM / 4) / 256))); cfg.blockDim = dim3(256); cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+        const cudaError_t e2 = cudaLaunchKernelEx(&cfg, gd_tail_fixup_kernel, fa);
+        if (e2 != cudaSuccess) return e2;
+        if (nlaunch) *nlaunch = 2;
+    }
     if (p.trace) {      // debugging aid (tools/gemm_bench.py under B200_GEMM_TRACE=1): per-CTA phase times in us since the first CTA started
         std::vector<unsigned long long> h((size_t) 2 * pairs * 8);
         cudaStreamSynchronize(st);
@@ -829,7 +889,7 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
         unsigned long long t0 = ~0ull;
         for (int c = 0; c < 2 * pairs; c++) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
         static const char * names[8] = {"start", "setup done", "first stage landed", "last MMA issued", "tile 0 complete", "last tile complete", "epilogue done", "end"};
-        fprintf(stderr, "[gemm_dense2 trace] nmat=%d M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d (full %d, narrow x%d)\n", nmat, M[0], N, K, bn, ksplit, pairs, work, p.full_units, p.narrow_f);
+        fprintf(stderr, "[gemm_dense2 trace] nmat=%d M=%d N=%d K=%d bn=%d ksplit=%d pairs=%d work=%d (full %d, tail %d steps in chunks of %d)\n", nmat, M[0], N, K, bn, ksplit, pairs, work, p.full_units, p.tail_T, p.tail_L);
         for (int sl = 0; sl < 8; sl++) {
             double mn = 1e30, mx = 0, sum = 0; int n = 0;
             for (int c = 0; c < 2 * pairs; c++) { const unsigned long long v = h[c * 8 + sl]; if (!v) continue; const double u = (double) (v - t0) * 1e-3; mn = u < mn ? u : mn; mx = u > mx ? u : mx; sum += u; n++; }
@@ -840,21 +900,23 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
 }
 
 // A: quantised weights (type, SoA fields) [M][K]; B: fp16 [N][K] (K % 8 == 0); out[n * out_cs + m]
-// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split)
-cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, cudaStream_t st,
-                              const float * res_src, float * res_dst, void * act_out) {
+// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split); tail_ws: gemm_dense_tail_ws_bytes(sms), or nullptr
+// (no stream-K tail); *nlaunch: kernels launched
+cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, float * tail_ws,
+                              int * nlaunch, cudaStream_t st, const float * res_src, float * res_dst, void * act_out) {
     const int ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
     if (res_dst && ksplit == 1) return cudaErrorInvalidValue;
-    const cudaError_t e = launch_pair(type, &A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, st);
+    const cudaError_t e = launch_pair(type, &A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, tail_ws, nlaunch, st);
     if (e != cudaSuccess || ksplit == 1) return e;
+    if (nlaunch) (*nlaunch)++;
     return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst, act_out);
 }
 
 // Several weight matrices of one type over the same activations in ONE launch (no split-K): 2 <= nmat <= 3
 cudaError_t launch_gemm_dense_group(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
-                                    const __half * B, int N, int K, int sms, cudaStream_t st) {
+                                    const __half * B, int N, int K, int sms, float * tail_ws, int * nlaunch, cudaStream_t st) {
     if (nmat < 1 || nmat > GD_MAXMAT) return cudaErrorNotSupported;
-    return launch_pair(type, A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, st);
+    return launch_pair(type, A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, tail_ws, nlaunch, st);
 }
 
 }  // namespace b200

@@ -84,6 +84,7 @@ struct Ctx {
     float *  gm_db = nullptr; size_t gm_db_cap = 0;
     int8_t * gm_a  = nullptr; size_t gm_a_cap = 0;       // exact mode only: unpacked integer weights of one MUL_MAT
     float *  gm_ws = nullptr; size_t gm_ws_cap = 0;
+    float *  gm_tail = nullptr; size_t gm_tail_cap = 0;  // stream-K tail partial tiles of the dense GEMM (gemm_dense_tail_ws_bytes)
     float *  gm_sp = nullptr; size_t gm_sp_cap = 0;      // split-K partial results      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
     bool capturing = false;       // inside cudaStreamBeginCapture .. EndCapture: no allocation, no synchronisation
     int sms = 0;
@@ -191,7 +192,7 @@ extern "C" int b200_close(b200_handle h) {
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
-    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp);
+    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp); cudaFree(c->gm_tail);
     cudaStreamDestroy(c->st);
     c->magic = 0;
     delete c;
@@ -488,6 +489,7 @@ static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1)
         rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
         const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
         if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
+        rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
         return 0;
     }
     rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
@@ -542,9 +544,11 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             // op has read gm_qb by then), and the next op finds its activations converted.  Only where gm_qb already has the room (no
             // reallocation under a capture) and inside a node list.
             const bool next_act = fa && c->in_graph && M % 32 == 0 && c->gm_qb_cap >= (size_t) N * M * 2 && act_fusion_enabled();
-            CU(launch_gemm_dense(s0->type, wp, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->st,
+            rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
+            int nl = 0;
+            CU(launch_gemm_dense(s0->type, wp, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->gm_tail, &nl, c->st,
                                  fa ? fa->src : nullptr, fa ? fa->dst : nullptr, next_act ? c->gm_qb : nullptr));
-            c->launches += 1 + (ksp > 1 ? 1 : 0);
+            c->launches += nl;
             if (next_act) { c->q_ptr = fa->dst; c->q_K = M; c->q_N = N; c->q_stride = M * 4; c->q_kind = 1; }
             if (c->rs_on && c->world > 1) {
                 // row split: y is this rank's M rows of every dst column; the slice goes into every peer's copy over NVLink, and the
@@ -777,7 +781,9 @@ static int mulmat_dense_group_dev(Ctx * c, const b200_node * nodes, int len) {
         CU(launch_dequant_act_f16((const float *) s1.data, s1.nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
         c->q_ptr = s1.data; c->q_K = K; c->q_N = N; c->q_stride = s1.nb[1]; c->q_kind = 1;
     }
-    CU(launch_gemm_dense_group(nodes[0].src0.type, A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->st)); c->launches++;
+    rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
+    int nl = 0;
+    CU(launch_gemm_dense_group(nodes[0].src0.type, A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->gm_tail, &nl, c->st)); c->launches += nl;
     return 0;           // (dense_group_len made sure that no dst touches the activations the cached conversion came from)
 }
 

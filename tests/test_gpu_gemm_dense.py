@@ -194,18 +194,31 @@ def test_dense_grouped_launch(use_graph, N):
             b.free()
 
 
-@pytest.mark.parametrize("M,what", [(10000, "80 pair tiles: 6 left after a wave of 74 -> quarter-width units"),
-                                    (13200, "104 pair tiles: 30 left -> half-width units"),
-                                    (9500, "76 pair tiles: 2 left -> quarter-width units")])
-def test_dense_narrow_units_of_the_last_wave(sess, M, what):
-    """more tiles than CTA pairs: the tiles left over after the full waves are cut into 256 x 128 / 256 x 64 units"""
-    rng = np.random.default_rng(71 + M)
-    K, N = 256, 300
-    raw = O.random_blocks(O.Q4_0, M, K, rng)
-    w = sess.weights(O.Q4_0, raw, K)
+@pytest.mark.parametrize("t,name", ALL)
+@pytest.mark.parametrize("M,what", [(10000, "80 pair tiles: 6 left after a wave of 74 -> 48 chunks of 2 slabs"),
+                                    (13203, "104 pair tiles: 30 left -> chunks of 7 slabs that cross tile boundaries; M odd: unaligned dst columns"),
+                                    (9500, "76 pair tiles: 2 left -> 32 chunks of one slab, 42 idle pairs"),
+                                    (5632, "44 tiles on 74 pairs, no full wave: everything is tail")])
+def test_dense_stream_k_tail_of_the_last_wave(sess, monkeypatch, t, name, M, what):
+    """more tiles than CTA pairs: the tiles left over after the full waves are cut into one chunk of consecutive (tile, slab) steps per
+    pair; partial tiles meet in gd_tail_fixup_kernel.  Deterministic, and the same matrix product as without the tail."""
+    monkeypatch.setenv("B200_GEMM_TAIL", "70")             # (default 25: only waves up to a quarter full)
+    rng = np.random.default_rng(71 + M + t)
+    K, N = 1024, 300
+    raw = O.random_blocks(t, M, K, rng)
+    w = sess.weights(t, raw, K)
     x = rng.standard_normal((N, K)).astype(np.float32)
+    l0 = sess.launch_count()
     got = sess.mulmat(w, x)
-    assert nmse(got, O.mul_mat(O.Q4_0, raw, x, 1)) <= DENSE_BAR, what
+    assert sess.launch_count() - l0 == 3, what            # activations -> fp16, GEMM, tail fix-up
+    ref = O.mul_mat(t, raw, x, 1)
+    assert nmse(got, ref) <= DENSE_BAR, what
+    assert np.array_equal(got, sess.mulmat(w, x))
+    monkeypatch.setenv("B200_GEMM_TAIL", "0")
+    l0 = sess.launch_count()
+    plain = sess.mulmat(w, x)
+    assert sess.launch_count() - l0 == 2
+    assert nmse(plain, ref) <= DENSE_BAR and nmse(got, plain) <= 1e-10
     w.free()
 
 
