@@ -82,7 +82,7 @@ struct GemvMat {
 struct GemvArgs {
     GemvMat mat[3]; int nmat; int cta_end[3];
     int steps; int64_t K; int64_t dcs;
-    const float * x; int64_t x_col_stride;     // gemv5c / gemv6: the f32 activation column (quantised inside the kernel)
+    const float * x; int64_t x_col_stride;     // gemv6: the f32 activation column (quantised inside the kernel)
     ActView act;                                // gemv4 / gemv5 / gemv5n: pre-quantised scratch
     // row split over the GPUs of one box: every result is also stored into the peers' copies of dst over NVLink
     // (peer address = local address + peer_delta[p]; dst lies in the symmetric heap every rank allocated alike)
@@ -114,8 +114,6 @@ bool gemv_pdl_enabled();
 // gemv6.cu: ONE f32 activation column a.x, quantised inside the kernel; persistent CTAs (one per SM), per-warp cp.async.bulk rings.
 // false: not eligible (*err untouched) -- the caller quantises into a.act and runs gemv4 / gemv5
 bool launch_gemv6(int type, GemvArgs & a, int sms, cudaStream_t st, cudaError_t * err);
-// gemv.cu: gemv5 tiles run as thread-block clusters that quantise a.x (f32) among themselves; same contract as launch_gemv6
-bool launch_gemv5c(int type, GemvArgs & a, cudaStream_t st, cudaError_t * err);
 void gemv6_trace(long long * buf, int cap_launches);      // development: 4 x %globaltimer per CTA of the next launches (4096 values per launch)
 int  gemv6_trace_count();
 // f32 weights (row stride in bytes), f32 activations (col stride bytes)

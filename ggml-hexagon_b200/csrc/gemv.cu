@@ -224,160 +224,6 @@ gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
     }
 }
 
-// ------------------------------------------------------------------------------------------------ gemv5c: gemv5 + the quantiser, per cluster
-// The decode chain paid TWO kernel boundaries per MUL_MAT: quantize_q8_1 (4 - 11 CTAs), then the GEMV whose CTAs each load their
-// activations from the quantiser's output -- ~0.6 us of boundary plus an L2 round trip (~1 us under load) that nothing hides.
-// gemv5c runs the same TMA-staged 8-row CTAs as thread-block CLUSTERS: after the dependency wait the C CTAs of a cluster quantise
-// 1 / C of the f32 activation vector each (the code of quantize_q8_1_kernel, bit-exact quantize_row_q8_1_ref), write their share
-// into the shared memory of every CTA of the cluster (st.shared::cluster) and meet at one cluster barrier; the lanes then read
-// their activations from their own shared memory.  One launch per MUL_MAT (group), one L2 round trip on the critical path.
-__device__ __forceinline__ uint32_t g5_mapa(uint32_t addr, uint32_t rank) {
-    uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
-}
-template <int TYPE, int RT, int ITERS>
-__global__ void __launch_bounds__(512)
-b200_gemv5c_kernel(const GemvArgs a, const Gemv5Tile t, const int act_off) {
-    using W = WT<TYPE>;
-    using A = WR<TYPE>;
-    extern __shared__ __align__(128) uint8_t g5_sm[];
-    float (*part)[RT + 1] = (float (*)[RT + 1]) (g5_sm + t.tile_bytes);
-    const uint32_t mbar = g5_smem(g5_sm + t.tile_bytes + 16 * (RT + 1) * 4);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const int steps = a.steps;
-    cudaTriggerProgrammaticLaunchCompletion();
-    uint32_t crank, csize;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
-    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
-    // every CTA of the cluster is running before anyone writes into a neighbour's shared memory: arrive now, wait before the stores
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    int m = 0, cta = blockIdx.x;
-    if (a.nmat > 1 && cta >= a.cta_end[0]) { m = 1; if (a.nmat > 2 && cta >= a.cta_end[1]) m = 2; }
-    const bool idle = cta >= a.cta_end[a.nmat - 1];           // (the grid is rounded up to whole clusters)
-    if (m > 0) cta -= a.cta_end[m - 1];
-    const GemvMat & mt = a.mat[m];
-    const int64_t M = mt.M;
-    const int64_t row0 = (int64_t) cta * RT;
-    const int nrows = idle ? 0 : (int) (M - row0 < RT ? M - row0 : RT);
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if (nrows > 0) {
-            uint32_t total = 0;
-            #pragma unroll
-            for (int i = 0; i < 4; i++) total += (uint32_t) (nrows * t.rowbytes[i]);
-            asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" :: "r"(mbar), "r"(total) : "memory");
-            #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                if (i < t.nfields) {
-                    const uint8_t * src = mt.w.p[i] + row0 * t.rowbytes[i];
-                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                 :: "r"(g5_smem(g5_sm + t.foff[i])), "l"(src), "r"((uint32_t) (nrows * t.rowbytes[i])), "r"(mbar) : "memory");
-                }
-            }
-        }
-    }
-    __syncthreads();
-    cudaGridDependencySynchronize();             // the activations (and add_src) come from the kernels before us
-    // ---- this CTA's share of quantize_row_q8_1_ref, into every CTA of the cluster: 8 lanes per 32-element block
-    const int NB = (int) (a.K >> 5);
-    {
-        const int T = (int) (a.K >> 2);                                     // float4 tasks of the whole vector
-        const int per = (int) (((T >> 3) + csize - 1) / csize) << 3;        // whole blocks per CTA
-        const int lo = (int) crank * per, hi = lo + per < T ? lo + per : T;
-        const float4 * x4 = (const float4 *) a.x;
-        const uint32_t act0 = g5_smem(g5_sm + act_off);
-        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-        for (int i0 = lo; i0 < hi; i0 += blockDim.x) {
-            const int i = i0 + tid;
-            const bool valid = i < hi;                                      // (whole 8-lane groups: lo, hi and T are multiples of 8)
-            const float4 v = __ldcg(x4 + (valid ? i : hi - 1));
-            const int blk = i >> 3, sub = i & 7;
-            float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-            const float d  = __fdiv_rn(amax, 127.0f);
-            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-            const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
-            const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
-            int sum = q0 + q1 + q2 + q3;
-            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-            const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
-            if (valid) {
-                const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
-                const uint32_t qoff = act0 + (uint32_t) (((sub >> 2) * NB + blk) * 16 + (sub & 3) * 4);
-                const uint32_t doff = act0 + (uint32_t) (NB * 32 + blk * 8);
-                const uint32_t dbits = __float_as_uint(__half2float(__float2half_rn(d)));
-                const uint32_t sbits = (uint32_t) (sum & 0xFFFF) | ((uint32_t) other << 16);
-                for (uint32_t p = 0; p < csize; p++) {
-                    asm volatile("st.shared::cluster.u32 [%0], %1;" :: "r"(g5_mapa(qoff, p)), "r"(packed) : "memory");
-                    if (sub == 0) asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" :: "r"(g5_mapa(doff, p)), "r"(dbits), "r"(sbits) : "memory");
-                }
-            }
-        }
-    }
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    if (idle) return;
-    // this lane's activations: step s of slice warp (+ nwarps) of the row
-    const uint4 * p0 = (const uint4 *) (g5_sm + act_off);
-    const ActCol ac(p0, p0 + NB, (const int2 *) (g5_sm + act_off + (size_t) NB * 32));
-    typename A::Act av[ITERS];
-    int sidx[ITERS];
-    #pragma unroll
-    for (int it = 0; it < ITERS; it++) {
-        sidx[it] = (warp + it * nwarps) * 32 + lane;
-        if (sidx[it] < steps) av[it] = A::load_act(ac, sidx[it]);
-    }
-    WPtrs sw;
-    #pragma unroll
-    for (int i = 0; i < 4; i++) sw.p[i] = g5_sm + t.foff[i];
-    {   // wait for the tile
-        uint32_t ok = 0;
-        while (!ok) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(mbar) : "memory");
-    }
-    float acc[RT];
-    #pragma unroll
-    for (int r = 0; r < RT; r++) acc[r] = 0.f;
-    #pragma unroll
-    for (int it = 0; it < ITERS; it++) {
-        const int s = sidx[it];
-        if (s < steps) {
-            #pragma unroll
-            for (int r = 0; r < RT; r++)
-                if (r < nrows) acc[r] += wr_dot<TYPE>(W::loads(sw, r * steps + s), av[it], s);
-        }
-    }
-    constexpr int SH = 5 - Log2<RT>::v;
-    {
-        const float v = reduce_rows<RT>(acc, lane);
-        if ((lane & ((1 << SH) - 1)) == 0) part[warp][lane >> SH] = v;
-    }
-    __syncthreads();
-    if (tid < RT) {
-        float v = 0.f;
-        for (int q = 0; q < nwarps; q++) v += part[q][tid];
-        const int r = tid;
-        if (row0 + r < M) {
-            const int64_t o = row0 + r;
-            mt.dst[o] = v;
-            float s = 0.f;
-            if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
-            if (a.ll_slots) {
-                const uint32_t seq = *a.ll_count + a.ll_op;
-                const uint2 * slot = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + a.ll_off[m] + (int64_t) a.ll_rank * M + row0 + r;
-                for (int pi = 0; pi < a.npeers; pi++)
-                    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"((const char *) slot + a.peer_delta[pi]), "r"(__float_as_uint(v)), "r"(seq) : "memory");
-            } else
-            for (int pi = 0; pi < a.npeers; pi++) {
-                *(float *) ((char *) (mt.dst + o) + a.peer_delta[pi]) = v;
-                if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
-            }
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------ gemv5n: several columns per tile
 // 2 .. 31 activation columns (small batches, speculative decoding; test-backend-ops n = 2..8): the tile is fetched ONCE and
 // stays in shared memory while the CTA walks over all columns, NC at a time (a weight fragment is read from shared memory once
@@ -564,76 +410,6 @@ static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err
     else if (rt == 8) *err = iters == 1 ? launch_g5<TYPE, 8, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 8, 2>(a, t, nwarps, st, pdl);
     else              *err = iters == 1 ? launch_g5<TYPE, 4, 1>(a, t, nwarps, st, pdl)  : launch_g5<TYPE, 4, 2>(a, t, nwarps, st, pdl);
     return true;
-}
-
-// gemv5c: one f32 activation column a.x, quantised per cluster inside the kernel
-template <int TYPE, int RT, int ITERS>
-static cudaError_t launch_g5c(GemvArgs & a, const Gemv5Tile & t, int nwarps, int cluster, cudaStream_t st, bool pdl) {
-    static int smem_set[64] = {0};
-    int dev = 0; cudaGetDevice(&dev); dev &= 63;
-    const int act_off = (t.tile_bytes + 16 * (RT + 1) * 4 + 16 + 15) & ~15;
-    const int smem = act_off + (int) (a.K / 32 * 40);
-    if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(b200_gemv5c_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        smem_set[dev] = smem;
-    }
-    int total = 0;
-    for (int i = 0; i < a.nmat; i++) { total += (int) ((a.mat[i].M + RT - 1) / RT); a.cta_end[i] = total; }
-    const int grid = (total + cluster - 1) / cluster * cluster;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(nwarps * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute at[2];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = (unsigned) cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[1].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = pdl ? 2 : 1;
-    return cudaLaunchKernelEx(&cfg, b200_gemv5c_kernel<TYPE, RT, ITERS>, a, t, act_off);
-}
-template <int TYPE>
-static bool try_gemv5c(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
-    const int mode = getenv("B200_GEMV5C") ? atoi(getenv("B200_GEMV5C")) : 0;            // opt-in (measured slower than quantise + gemv4/5); read per launch
-    if (!mode || !a.x || ((uintptr_t) a.x & 15) || a.K % 128) return false;
-    const WFields f = wfields(TYPE);
-    const int64_t bpr = a.K / (TYPE == T_Q4_K || TYPE == T_Q6_K ? 256 : 32);
-    Gemv5Tile t{};
-    t.nfields = f.n;
-    int rowsum = 0;
-    for (int i = 0; i < f.n; i++) {
-        const int64_t rb = bpr * f.size[i];
-        if (rb % 16 != 0 || rb > (1 << 20)) return false;
-        t.rowbytes[i] = (int) rb; rowsum += (int) rb;
-        for (int mi = 0; mi < a.nmat; mi++) if (((uintptr_t) a.mat[mi].w.p[i] & 15) != 0) return false;
-    }
-    const int nslices = (a.steps + 31) / 32;
-    const int iters = (nslices + 15) / 16;
-    if (iters > 2) return false;
-    const int nwarps = (nslices + iters - 1) / iters;
-    const int rt_env = getenv("B200_GEMV5_ROWS") ? atoi(getenv("B200_GEMV5_ROWS")) : 0;
-    int rt = rt_env == 4 || rt_env == 8 || rt_env == 16 ? rt_env : 8;
-    if (rt * rowsum > 72 * 1024) rt = 4;
-    if (rt * rowsum > 72 * 1024) return false;
-    int off = 0;
-    for (int i = 0; i < f.n; i++) { t.foff[i] = off; off += rt * t.rowbytes[i]; }
-    t.tile_bytes = (off + 15) & ~15;
-    int cluster = getenv("B200_GEMV5C_CLUSTER") ? atoi(getenv("B200_GEMV5C_CLUSTER")) : 8;
-    if (cluster != 1 && cluster != 2 && cluster != 4 && cluster != 8) cluster = 8;            // portable cluster sizes only
-    if (rt == 16)     *err = iters == 1 ? launch_g5c<TYPE, 16, 1>(a, t, nwarps, cluster, st, pdl) : launch_g5c<TYPE, 16, 2>(a, t, nwarps, cluster, st, pdl);
-    else if (rt == 8) *err = iters == 1 ? launch_g5c<TYPE, 8, 1>(a, t, nwarps, cluster, st, pdl)  : launch_g5c<TYPE, 8, 2>(a, t, nwarps, cluster, st, pdl);
-    else              *err = iters == 1 ? launch_g5c<TYPE, 4, 1>(a, t, nwarps, cluster, st, pdl)  : launch_g5c<TYPE, 4, 2>(a, t, nwarps, cluster, st, pdl);
-    return true;
-}
-bool launch_gemv5c(int type, GemvArgs & a, cudaStream_t st, cudaError_t * err) {
-    a.steps = (int) (a.K / (type == T_Q4_K || type == T_Q6_K ? 64 : 32));
-    const bool pdl = tune().pdl;
-    switch (type) {
-        case T_Q4_0: return try_gemv5c<T_Q4_0>(a, st, pdl, err);
-        case T_Q8_0: return try_gemv5c<T_Q8_0>(a, st, pdl, err);
-        case T_Q4_K: return try_gemv5c<T_Q4_K>(a, st, pdl, err);
-        case T_Q6_K: return try_gemv5c<T_Q6_K>(a, st, pdl, err);
-    }
-    return false;
 }
 
 // several columns in one launch (gemv5n); false = not eligible, the caller falls back to 8-column gemv4 chunks

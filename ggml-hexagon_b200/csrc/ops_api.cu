@@ -628,7 +628,7 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                 if (N == 1) {                               // one column: persistent ring GEMV, quantises the activations itself (gemv6.cu)
                     a.mat[0].dst = y; a.x = (const float *) x; a.x_col_stride = s1->nb[1];
                     cudaError_t e6 = cudaSuccess;
-                    done = launch_gemv6(s0->type, a, c->sms, c->st, &e6) || launch_gemv5c(s0->type, a, c->st, &e6);
+                    done = launch_gemv6(s0->type, a, c->sms, c->st, &e6);
                     if (done) { CU(e6); c->launches++; continue; }
                 }
                 const bool reuse = c->in_graph && c->q_kind == 0 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
@@ -806,7 +806,7 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
     {   // persistent ring GEMV over the whole group, activations quantised inside the kernel (gemv6.cu)
         a.x = x; a.x_col_stride = nodes[0].src1.nb[1];
         cudaError_t e6 = cudaSuccess;
-        if (launch_gemv6(nodes[0].src0.type, a, c->sms, c->st, &e6) || launch_gemv5c(nodes[0].src0.type, a, c->st, &e6)) {
+        if (launch_gemv6(nodes[0].src0.type, a, c->sms, c->st, &e6)) {
             CU(e6); c->launches++;
             for (int j = 0; j < len; j++)            // a dst may overwrite the memory an earlier cached quantisation was taken from
                 if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4 * g_rs_world, c->q_ptr, c->q_K * 4)) c->q_ptr = nullptr;

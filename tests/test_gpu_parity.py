@@ -256,7 +256,6 @@ def test_gemv5_tma_tiles(monkeypatch, t, rows, M, K):
     Same integer dots and scales as gemv4 -> same bar against the oracle."""
     monkeypatch.setenv("B200_GEMV5_MIN_MB", "0")
     monkeypatch.setenv("B200_GEMV6", "0")          # (the kernels that quantise in-kernel would take every one-column MUL_MAT)
-    monkeypatch.setenv("B200_GEMV5C", "0")
     monkeypatch.setenv("B200_GEMV5_ROWS", str(rows))
     rng = np.random.default_rng(M + K + t + rows)
     raw = O.random_blocks(t, M, K, rng)
