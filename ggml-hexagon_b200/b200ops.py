@@ -19,7 +19,7 @@ TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"
 # every symbol include/ggml_b200_ops.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "b200_open", "b200_close", "b200_setclocks", "b200_last_error", "b200_device_count", "b200_device_info",
-    "b200_add", "b200_mulmat", "b200_rms_norm", "b200_soft_max", "b200_pool_2d", "b200_graph_compute", "b200_graph_compute_keyed", "b200_synchronize", "b200_quantize_q8_1", "b200_block_dots",
+    "b200_add", "b200_mulmat", "b200_mulmat_noalloc", "b200_rms_norm", "b200_soft_max", "b200_pool_2d", "b200_graph_compute", "b200_graph_compute_keyed", "b200_synchronize", "b200_quantize_q8_1", "b200_block_dots",
     "b200_malloc", "b200_free", "b200_memcpy_h2d", "b200_memcpy_d2h", "b200_memcpy_d2d", "b200_memset",
     "b200_memcpy_h2d_async", "b200_memcpy_d2h_async",
     "b200_host_alloc", "b200_host_free", "b200_weights_upload", "b200_weights_download", "b200_block_elems",
@@ -294,6 +294,14 @@ class Session:
         xb.free()
         db.free()
         return out
+
+    def mulmat_noalloc(self, w, xb, db, N, stream=None):
+        """b200_mulmat_noalloc on device buffers the caller made beforehand (xb: f32 [N, K], db: f32 [N, M]); the call itself takes no
+        session and allocates nothing; asynchronous on `stream` (a cudaStream_t value; None = the default stream)"""
+        s0, s1, d = w.tensor(), f32_tensor(xb.ptr, [w.K, N]), f32_tensor(db.ptr, [w.M, N], op=OP_MUL_MAT)
+        L = lib()
+        L.b200_mulmat_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _ck(L.b200_mulmat_noalloc(C.byref(s0), C.byref(s1), C.byref(d), C.c_void_p(stream) if stream else None))
 
     def mulmat_host(self, t, w_raw, x, K):
         """Everything in host memory (FastRPC-style call): returns float32 [N, M]."""

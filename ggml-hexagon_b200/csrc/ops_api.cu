@@ -1162,3 +1162,66 @@ extern "C" int b200_graph_compute_rowsplit(b200_handle h, const b200_node * node
     c->rs_on = false; g_rs_world = 1;
     return rc;
 }
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT without allocations
+// b200_mulmat_noalloc: the few-column (decode) MUL_MAT for callers that cannot allocate device memory -- code under a stream capture,
+// serving loops, harnesses that forbid cudaMalloc.  Same two kernels as b200_mulmat's GEMV path (q8_1 quantiser, then gemv4 / gemv5),
+// but the quantised activations go into a file-scope device array instead of the session's cudaMalloc'ed scratch, and no session,
+// no stream and no event is created: the caller passes device pointers and its own stream.
+// Every GPU that loads this library holds the B200_NOALLOC_SCRATCH_BYTES of g_noalloc_scratch until the process exits.  All calls on a
+// device share it: calls that overlap on the GPU (different streams, no dependency between them) race on it.  The array keeps the last
+// call's contents; nothing has to start at zero -- the quantiser writes every block of every column before the GEMV reads it.
+// Layout: int8 quants [N][K] at offset 0, ActDS {d, block sums} [N][K / 32] behind them at the next multiple of 256 bytes.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is the host-side stand-in of the symbol, not a device address: the kernels get what
+// cudaGetSymbolAddress returns, asked once per device with that device current.
+static int noalloc_scratch_of_current_device(unsigned char ** out) {
+    static std::mutex mu;
+    static unsigned char * ptr[64] = {nullptr};
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(B200_EINVAL, "b200_mulmat_noalloc: device %d out of range", dev);
+    std::lock_guard<std::mutex> g(mu);
+    if (!ptr[dev]) {
+        void * p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return fail(B200_ECUDA, "b200_mulmat_noalloc: cudaGetSymbolAddress(g_noalloc_scratch) on device %d -> %s", dev, cudaGetErrorString(e));
+        ptr[dev] = (unsigned char *) p;
+    }
+    *out = ptr[dev];
+    return 0;
+}
+
+extern "C" int b200_mulmat_noalloc(const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d, void * stream) {
+    if (!s0 || !s1 || !d) return fail(B200_EINVAL, "b200_mulmat_noalloc: null tensor");
+    int rc = mulmat_check(s0, s1, d); if (rc) return rc;
+    if (!is_qweight(s0->type)) return fail(B200_ENOTSUP, "b200_mulmat_noalloc: src0 must be q4_0 / q8_0 / q4_K / q6_K REPACKED device weights");
+    if ((s0->flags | s1->flags | d->flags) & B200_TENSOR_HOST) return fail(B200_ENOTSUP, "b200_mulmat_noalloc: device tensors only (staging host tensors would allocate)");
+    if (s0->ne[2] != 1 || s0->ne[3] != 1 || s1->ne[2] != 1 || s1->ne[3] != 1) return fail(B200_ENOTSUP, "b200_mulmat_noalloc: 2-D operands only");
+    const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
+    if (M == 0 || N == 0 || K == 0) return 0;
+    const int64_t NB = K / 32;
+    const size_t qs_bytes = ((size_t) N * NB * 32 + 255) & ~(size_t) 255, need = qs_bytes + (size_t) N * NB * sizeof(ActDS);
+    if (need > (size_t) B200_NOALLOC_SCRATCH_BYTES)
+        return fail(B200_EINVAL, "b200_mulmat_noalloc: K = %lld x N = %lld needs %zu bytes of activation scratch, the static array holds %d (use b200_mulmat)",
+                    (long long) K, (long long) N, need, (int) B200_NOALLOC_SCRATCH_BYTES);
+    WPtrs wp{};
+    rc = wptrs_of(s0, &wp); if (rc) return rc;
+    unsigned char * scratch = nullptr;
+    rc = noalloc_scratch_of_current_device(&scratch); if (rc) return rc;
+    int8_t * qs = (int8_t *) scratch;
+    ActDS * ds = (ActDS *) (scratch + qs_bytes);
+    cudaStream_t st = (cudaStream_t) stream;
+    CU(launch_quantize_q8_1_soa((const float *) s1->data, s1->nb[1], K, N, qs, ds, st));
+    GemvArgs a{};
+    a.nmat = 1; a.K = K; a.dcs = d->nb[1] / 4;
+    a.mat[0].w = wp; a.mat[0].M = M;
+    for (int64_t c0 = 0; c0 < N; c0 += 8) {
+        const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
+        a.act = ActView{qs + c0 * NB * 32, ds + c0 * NB, NB};
+        a.mat[0].dst = (float *) d->data + c0 * a.dcs;
+        CU(launch_gemv2(s0->type, a, nc, st));
+    }
+    return 0;
+}

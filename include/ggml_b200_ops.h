@@ -107,6 +107,15 @@ B200_API int b200_add(b200_handle h, const b200_tensor * src0, const b200_tensor
  * src0: q4_0/q8_0/q4_K/q6_K REPACKED device weights, or f32; src1, dst: f32. Asynchronous on the handle's stream
  * unless a tensor carries B200_TENSOR_HOST (then the call returns after dst is back in host memory). */
 B200_API int b200_mulmat(b200_handle h, const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst);
+/* MUL_MAT that allocates nothing.  No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under a CUDA graph capture, tight serving loops, harnesses that forbid it).  No session handle: src0 = 2-D
+ * q4_0/q8_0/q4_K/q6_K REPACKED device weights, src1 / dst = 2-D f32 device tensors of the CURRENT device, `stream` = the caller's
+ * cudaStream_t (NULL: the default stream); asynchronous on it.  The q8_1 activations live in a static device array of
+ * B200_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit: (K * N rounded up to 256) + K / 32 * N * 8 bytes must fit
+ * (e.g. K = 4096: N <= 204; K = 28672: N <= 29), else B200_EINVAL with the sizes in b200_last_error.  Calls on one device share the
+ * array: calls that overlap on the GPU race.  Results are bit-identical to b200_mulmat's GEMV path. */
+#define B200_NOALLOC_SCRATCH_BYTES (1 << 20)
+B200_API int b200_mulmat_noalloc(const b200_tensor * src0, const b200_tensor * src1, b200_tensor * dst, void * stream);
 /* ---- the ops ggml-hexagon lists beside them without an implementation (ggmlop_dsp_rmsnorm / _softmax / _pool2d, ggml-dsp.c:1353-1372);
  *      device tensors only; parameters travel in dst->op_params exactly as in ggml_tensor.op_params
  * RMS_NORM: y = x / sqrt(mean(x^2) + eps) per row, f32, src nb[0] = 4 (ggml-cpu.c:6254-6300); eps = op_params[0] (float bits) */
