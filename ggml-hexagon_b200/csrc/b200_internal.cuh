@@ -144,18 +144,20 @@ cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, f
                                  const float * res_src = nullptr, float * res_dst = nullptr, void * act_out = nullptr);
 bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst);
 // ---- dense prefill GEMM (gemm_dense.cu): block scales folded into fp16 operands, the whole K accumulated in TMEM
-cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st);
+cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, float * colscale, cudaStream_t st);
 int gemm_dense_ksplit(int M, int N, int K, int sms);            // > 1: launch_gemm_dense wants a workspace of that many x N x M floats
-// A: quantised weights of `type` in the SoA layout (dequantised inside the kernel); B: fp16 activations [N][K]
-cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws,
+// A: quantised weights of `type` in the SoA layout (dequantised inside the kernel); B: fp16 activations [N][K] scaled per column, colscale: the
+// power of two each dst column is multiplied by (both from launch_dequant_act_f16; colscale holds N rounded up to 256 floats, 16-byte aligned)
+cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, const float * colscale, float * out, long long out_cs, int M, int N, int K, int sms,
+                              float * split_ws,
                               float * tail_ws,              // gemm_dense_tail_ws_bytes(sms) of scratch for the stream-K tail of the last wave, or nullptr (none)
                               int * nlaunch, cudaStream_t st,      // *nlaunch: kernels launched (GEMM, + tail fix-up, + split reduce)
                               const float * res_src = nullptr, float * res_dst = nullptr,   // residual ADD fused into the split-K reduce (needs split_ws and ksplit > 1)
-                              void * act_out = nullptr);   // + fp16(q8_1(res_dst)) [N][M] for the next dense GEMM (M % 32 == 0)
+                              void * act_out = nullptr, float * act_cs_out = nullptr);   // + the next dense GEMM's activations / column scales from res_dst (M % 32 == 0, M <= 8192)
 size_t gemm_dense_tail_ws_bytes(int sms);
 // 2..3 weight matrices of one type over the same activations in one launch (q / k / v, gate / up)
 cudaError_t launch_gemm_dense_group(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
-                                    const __half * B, int N, int K, int sms, float * tail_ws, int * nlaunch, cudaStream_t st);
+                                    const __half * B, const float * colscale, int N, int K, int sms, float * tail_ws, int * nlaunch, cudaStream_t st);
 
 struct AddArgs {
     const char * a; const char * b; char * d;

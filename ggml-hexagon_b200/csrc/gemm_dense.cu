@@ -13,8 +13,15 @@
 // so the contraction is dense and the accumulator runs over the whole K.  What changes against the reference is only the
 // rounding of the two dequantised operands to fp16 (relative 2^-12 each; NMSE against ggml-cpu ~1e-7, the bar is 5e-4) and the
 // f32 summation order.  The q8_1 step is kept so that the result follows the reference's own quantisation of the activations.
-// Operand ranges fp16 cannot hold (|d_a q_a| > 65504, |d_w q_w| below the fp16 normal range) are detected by the caller, which
-// routes such a MUL_MAT to the exact int8 kernel (ops_api.cu, dense_range_ok).
+// Operand ranges (the reference's f32 block dots have no such limits beyond the fp16 block scales themselves):
+//   * activations: every column n of B is scaled by a power of two 2^g(n) that brings its largest |d_a q_a| into [2^8, 2^9) (so that
+//     |x| up to the reference's own limit, d_a = amax / 127 <= 65504, does not saturate), the epilogue multiplies dst column n by 2^-g(n):
+//     exact, the product is the same as without the scale wherever fp16 could hold the unscaled operand;
+//   * q4_0 / q8_0 weights: d_w is an fp16 number already and |q| <= 128, so d_w q_w is exact in the subnormal range (an integer times
+//     2^-24) and rounds once above it; it overflows only for |d_w| > 511, which no quantiser produces for weights that fit fp16;
+//   * K-quant weights: d sc q - dmin m is computed in f32 and would lose bits below 2^-14: the converters scale a row whose super-block
+//     scale max(|d|, |dmin|) is below 2^-14 up by a power of two (taken from the first super-block of the work unit), the epilogue
+//     multiplies the row by its inverse.
 //
 // A never exists in HBM as fp16 (round 1 kept 2-byte "shadows" of every weight matrix: 3.6x the q4_0 bytes in HBM and in L2 -> SM
 // traffic): eight CONVERTER warps per CTA read the native SoA blocks (16 - 64 bytes per row and 64-element K slab, 128-bit loads,
@@ -58,6 +65,7 @@ struct GemmDenseArgs {
     // partial sums in tail_ws slot 2 c + s, and gd_tail_fixup_kernel adds the slots of every tile in chunk order (deterministic).
     int full_units, tail_T, tail_L;
     float * tail_ws;
+    const float * colscale;                    // [N rounded up to 256]: dst column n = accumulator x colscale[n] (launch_dequant_act_f16 wrote B x 1 / colscale)
 };
 struct GdUnit { int tile, sp, ks0, ks1, slot; };    // slabs [ks0, ks1) of `tile`; slot >= 0: partial sums to that tail_ws slot
 __device__ __forceinline__ GdUnit gd2_unit(const GemmDenseArgs & p, const int work, const int nks, const int pair, const int npairs) {
@@ -88,17 +96,24 @@ __device__ __forceinline__ void gd_stamp(const GemmDenseArgs & p, int slot) {
 // colp[i * cs] (a column of dst is contiguous in m, so every store instruction is one 128-byte line).  The pointer walks by cs:
 // recomputing (n0 + i) * cs + m with its bounds test per element cost ~18 instructions and a branch per store, 7 us per
 // 128 x 256 tile (B200_GEMM_TRACE timeline); the next chunk's tcgen05.ld is in flight while a chunk is stored.
-__device__ __forceinline__ void gd_store_chunk(float * colp, const long long cs, const int (&v)[32], const int ncols) {
-    if (ncols >= 32) {
+__device__ __forceinline__ uint4 gd_lds16(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+// csc: shared-memory address of the chunk's 32 column scales; rs: the row's scale; both powers of two
+__device__ __forceinline__ void gd_store_chunk(float * colp, const long long cs, const int (&v)[32], const int ncols, const uint32_t csc, const float rs) {
+    #pragma unroll
+    for (int i4 = 0; i4 < 8; i4++) {
+        const uint4 t = gd_lds16(csc + i4 * 16);                   // (warp-uniform address: a broadcast)
+        const float f[4] = {__uint_as_float(t.x) * rs, __uint_as_float(t.y) * rs, __uint_as_float(t.z) * rs, __uint_as_float(t.w) * rs};
         #pragma unroll
-        for (int i = 0; i < 32; i++) { *colp = __int_as_float(v[i]); colp += cs; }
-    } else {
-        #pragma unroll
-        for (int i = 0; i < 32; i++) { if (i < ncols) *colp = __int_as_float(v[i]); colp += cs; }
+        for (int k = 0; k < 4; k++) {
+            const int i = 4 * i4 + k;
+            if (ncols >= 32 || i < ncols) *colp = __int_as_float(v[i]) * f[k];
+            colp += cs;
+        }
     }
 }
 template <int NCH>
-__device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * colp, const long long cs, const int ncols, const bool row_ok) {
+__device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * colp, const long long cs, const int ncols, const bool row_ok,
+                                                 const uint32_t csc, const float rs) {
     static_assert(NCH % 2 == 0, "chunks are processed in pairs");
     int va[32], vb[32];
     gm_tmem_ld32(taddr, va);
@@ -106,12 +121,25 @@ __device__ __forceinline__ void gd_epilogue_warp(const uint32_t taddr, float * c
     #pragma unroll
     for (int c = 0; c < NCH; c += 2) {
         gm_tmem_ld32(taddr + (c + 1) * 32, vb);
-        if (row_ok && ncols > c * 32) gd_store_chunk(colp + (long long) c * 32 * cs, cs, va, ncols - c * 32);
+        if (row_ok && ncols > c * 32) gd_store_chunk(colp + (long long) c * 32 * cs, cs, va, ncols - c * 32, csc + c * 128, rs);
         gm_tmem_ld_wait();
         if (c + 2 < NCH) gm_tmem_ld32(taddr + (c + 2) * 32, va);
-        if (row_ok && ncols > (c + 1) * 32) gd_store_chunk(colp + (long long) (c + 1) * 32 * cs, cs, vb, ncols - (c + 1) * 32);
+        if (row_ok && ncols > (c + 1) * 32) gd_store_chunk(colp + (long long) (c + 1) * 32 * cs, cs, vb, ncols - (c + 1) * 32, csc + (c + 1) * 128, rs);
         if (c + 2 < NCH) gm_tmem_ld_wait();
     }
+}
+// K-quants: the power of two 2^f (f >= 0) that brings a row whose super-block scale dmax = max(|d|, |dmin|) lies below 2^-14 into [2^-14, 2^-13):
+// the smallest non-zero element d sc q (sc, q integers) is a normal fp16 number then, and the other super-blocks of the unit may have scales
+// up to 2^17 times the first one's before 127 x 32 x d' passes 65504 (the conversion saturates there)
+__device__ __forceinline__ float gd_row_up(const float dmax) {
+    if (!(dmax > 0.0f)) return 1.0f;
+    const int E = (int) ((__float_as_uint(dmax) >> 23) & 0xFFu) - 126;        // dmax = m 2^E, m in [0.5, 1)   (fp16 subnormals are normal f32 numbers)
+    const int f = -13 - E;
+    return f > 0 ? __uint_as_float((uint32_t) (f + 127) << 23) : 1.0f;
+}
+__device__ __forceinline__ float gd_hdr_dmax(const int type, const uint32_t w) {      // q4_K: w = {d, dmin} halfs; q6_K: w = d in the low half
+    const float d = fabsf(__half2float(__ushort_as_half((unsigned short) (w & 0xFFFFu))));
+    return type == T_Q4_K ? fmaxf(d, fabsf(__half2float(__ushort_as_half((unsigned short) (w >> 16))))) : d;
 }
 
 // ------------------------------------------------------------------------------------------------ the CTA-pair kernel
@@ -132,8 +160,8 @@ __host__ __device__ constexpr int gd2_n4(int type)  { return type == T_Q4_K ? 0 
 __host__ __device__ constexpr int gd2_depth(int type) { return type == T_Q4_0 ? 6 : type == T_Q8_0 ? 6 : type == T_Q4_K ? 5 : 3; }
 __host__ __device__ constexpr int gd2_raw_bytes(int type) { return gd2_depth(type) * GD_CVT_WARPS * 32 * (16 * gd2_n16(type) + 4 * gd2_n4(type)); }
 __host__ __device__ constexpr int gd2_stage_bytes(int bn) { return GM_BM * 128 + (bn / 2) * 128; }
-__host__ __device__ constexpr int gd2_stages(int bn, int type) { return (232448 - 1280 - gd2_raw_bytes(type)) / gd2_stage_bytes(bn); }
-__host__ __device__ constexpr int gd2_smem(int bn, int type) { return gd2_stages(bn, type) * gd2_stage_bytes(bn) + gd2_raw_bytes(type) + 256 + 1024; }
+__host__ __device__ constexpr int gd2_stages(int bn, int type) { return (232448 - 1280 - 2048 - gd2_raw_bytes(type)) / gd2_stage_bytes(bn); }
+__host__ __device__ constexpr int gd2_smem(int bn, int type) { return gd2_stages(bn, type) * gd2_stage_bytes(bn) + gd2_raw_bytes(type) + 256 + 2048 + 1024; }
 static_assert(gd2_stages(256, T_Q4_0) == 6 && gd2_stages(256, T_Q8_0) >= 5 && gd2_stages(256, T_Q4_K) >= 5 && gd2_stages(256, T_Q6_K) >= 5, "stage count");
 // WTMA variant (the default): the native blocks arrive by TMA instead -- per-thread LDGSTS gathers of 16 + 4 bytes from 32 different rows cost
 // 32 L1 tag cycles per warp instruction, ~512 per stage against the 512 clocks the stage's MMAs take (without the 4-byte scale gather a
@@ -153,8 +181,8 @@ __host__ __device__ constexpr int gd3_foff(int f) { return f == 0 ? 0 : (f == 1 
 __host__ __device__ constexpr int gd3_raw_stage(int type) { return type == T_Q6_K ? 16384 + 8192 + 2048 : 16384 + 2048; }
 __host__ __device__ constexpr int gd3_small_off(int type) { return type == T_Q6_K ? 16384 + 8192 : 16384; }      // the [128][16 B] scale / header tile
 __host__ __device__ constexpr int gd3_raw_bytes(int type) { return gd3_rd(type) * gd3_raw_stage(type) + (type == T_Q6_K ? GD3_DD * GD_CVT_WARPS * 32 * 4 : 0); }
-__host__ __device__ constexpr int gd3_stages(int bn, int type) { return (232448 - 1024 - 512 - gd3_raw_bytes(type)) / gd2_stage_bytes(bn); }
-__host__ __device__ constexpr int gd3_smem(int bn, int type) { return gd3_stages(bn, type) * gd2_stage_bytes(bn) + gd3_raw_bytes(type) + 512 + 1024; }
+__host__ __device__ constexpr int gd3_stages(int bn, int type) { return (232448 - 1024 - 512 - 2048 - gd3_raw_bytes(type)) / gd2_stage_bytes(bn); }
+__host__ __device__ constexpr int gd3_smem(int bn, int type) { return gd3_stages(bn, type) * gd2_stage_bytes(bn) + gd3_raw_bytes(type) + 512 + 2048 + 1024; }
 static_assert(gd3_stages(256, T_Q4_0) >= 5 && gd3_stages(256, T_Q8_0) >= 5 && gd3_stages(256, T_Q4_K) >= 5 && gd3_stages(256, T_Q6_K) >= 5, "stage count");
 struct GdMaps { CUtensorMap b[1]; CUtensorMap w[3][3]; };      // activations; weights [matrix][field]
 
@@ -217,17 +245,16 @@ __device__ __forceinline__ uint2 gd_u8x4_h(uint32_t w, uint32_t bias2, uint32_t 
     const uint32_t lo = gd_prmt(w, 0x64646464u, 0x5140u), hi = gd_prmt(w, 0x64646464u, 0x5342u);
     return make_uint2(gd_h2mul(gd_h2sub(lo, bias2), d2), gd_h2mul(gd_h2sub(hi, bias2), d2));
 }
-__device__ __forceinline__ uint32_t gd_pack_h2f(float a, float b) { uint32_t r; asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }
+__device__ __forceinline__ uint32_t gd_pack_h2f(float a, float b) { uint32_t r; asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }
 // 4 bytes of w (values 0 .. 255) -> 4 halfs of fp16(ds * v - ms), the product and difference in fp32 (one FFMA: a single rounding)
 __device__ __forceinline__ uint2 gd_u8x4_f(uint32_t w, float ds, float ms) {
     const float f0 = __fmaf_rn(ds, (float) (w & 0xFFu), -ms), f1 = __fmaf_rn(ds, (float) ((w >> 8) & 0xFFu), -ms);
     const float f2 = __fmaf_rn(ds, (float) ((w >> 16) & 0xFFu), -ms), f3 = __fmaf_rn(ds, (float) (w >> 24), -ms);
     return make_uint2(gd_pack_h2f(f0, f1), gd_pack_h2f(f2, f3));
 }
-struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; };      // one slab's native bytes of a thread (unused members cost nothing)
+struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; float fs; };      // fs: K-quant row scale (power of two)      // one slab's native bytes of a thread (unused members cost nothing)
 __device__ __forceinline__ void gd_cpa16(uint32_t dst, const void * src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory"); }
 __device__ __forceinline__ void gd_cpa4(uint32_t dst, const void * src)  { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory"); }
-__device__ __forceinline__ uint4 gd_lds16(uint32_t a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t gd_lds4(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 // slot addressing: q16[i] / q4[i] = this thread's 16-byte / 4-byte cell of field i in ring slot `slot`
 struct GdSlot { uint32_t q16[4], q4[2]; };
@@ -291,7 +318,7 @@ template <> struct GdCvt<T_Q4_K> {
         if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
         else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
         const __half2 dd = *(const __half2 *) &r.c.x;
-        const float ds = __fmul_rn(__low2float(dd), (float) sc), ms = __fmul_rn(__high2float(dd), (float) mn);
+        const float ds = __fmul_rn(__low2float(dd), (float) sc) * r.fs, ms = __fmul_rn(__high2float(dd), (float) mn) * r.fs;
         const uint32_t m = 0x0F0F0F0Fu; const int sh = hk * 4;
         const uint2 a = gd_u8x4_f((r.a.x >> sh) & m, ds, ms), b = gd_u8x4_f((r.a.y >> sh) & m, ds, ms), c = gd_u8x4_f((r.a.z >> sh) & m, ds, ms), d = gd_u8x4_f((r.a.w >> sh) & m, ds, ms);
         const uint2 e = gd_u8x4_f((r.b.x >> sh) & m, ds, ms), f = gd_u8x4_f((r.b.y >> sh) & m, ds, ms), gg = gd_u8x4_f((r.b.z >> sh) & m, ds, ms), h = gd_u8x4_f((r.b.w >> sh) & m, ds, ms);
@@ -322,7 +349,7 @@ template <> struct GdCvt<T_Q6_K> {
         const int c = ks & 1, sh = 2 * (2 * c + hk), ns = 4 * c;
         const uint32_t m = 0x0F0F0F0Fu, m3 = 0x03030303u;
         auto q = [&](uint32_t l, uint32_t hh) { return ((l >> ns) & m) | (((hh >> sh) & m3) << 4); };
-        const float d = __half2float(__ushort_as_half((unsigned short) r.s1));
+        const float d = __half2float(__ushort_as_half((unsigned short) r.s1)) * r.fs;
         const float d0 = __fmul_rn(d, (float) (int8_t) (r.s0 & 0xFF)), d1 = __fmul_rn(d, (float) (int8_t) ((r.s0 >> 8) & 0xFF));
         const float m0 = d0 * 32.f, m1 = d1 * 32.f;                      // (exact: power of two)
         const uint2 a = gd_u8x4_f(q(r.a.x, r.c.x), d0, m0), b = gd_u8x4_f(q(r.a.y, r.c.y), d0, m0), cc = gd_u8x4_f(q(r.a.z, r.c.z), d0, m0), dd = gd_u8x4_f(q(r.a.w, r.c.w), d0, m0);
@@ -346,6 +373,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
     const uint32_t rfull0 = tempty0 + 2 * 8, rempty0 = rfull0 + RD * 8;                  // (WTMA only)
     volatile uint32_t * tmem_slot = (volatile uint32_t *) (smem + OFF_BAR + 3 * STAGES * 8 + 4 * 8 + 2 * RD * 8);
     static_assert(3 * STAGES * 8 + 4 * 8 + 2 * RD * 8 + 4 <= (WTMA ? 512 : 256), "barrier area");
+    const uint32_t sCS = bars + (WTMA ? 512 : 256);                                    // column scales of the tile being drained: [2 TMEM buffers][BN] floats
     const CUtensorMap & tmB = maps.b[0];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t rank;
@@ -444,19 +472,37 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             const int mt = local / p.ntiles, nt = local - mt * p.ntiles;
             const int m = mt * 2 * GM_BM + (int) rank * GM_BM + m_local;
             const uint32_t buf = tc & 1, bph = (tc >> 1) & 1;
-            gm_mbar_wait(tfull0 + buf * 8, bph);
-            gm_fence_after();
-            if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
             // this warp: TMEM lanes q * 32 .. +31, columns half * (BN / 2) .. + BN / 2 of the tile
             const int c0 = half * (BN / 2), n0 = nt * BN + c0;
             const uint32_t ta = tbase + buf * BN + c0;
+            const bool row_ok = m < p.Ms[j];
+            // while the tile is still being accumulated: this warp's BN / 2 column scales into shared memory (the four warps of a half write the
+            // same values to the same places; each reads back only after its own stores)
+            const uint32_t csc = sCS + (uint32_t) ((buf * BN + c0) * 4);
+            if (lane < BN / 8) {
+                const float4 t = __ldg((const float4 *) (p.colscale + n0) + lane);
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(csc + lane * 16), "f"(t.x), "f"(t.y), "f"(t.z), "f"(t.w) : "memory");
+            }
+            __syncwarp();
+            float rs = 1.0f;
+            if constexpr (TYPE == T_Q4_K || TYPE == T_Q6_K) {      // undo the converters' row scale: same function of the same header
+                if (row_ok) {
+                    const uint8_t * const wh = TYPE == T_Q4_K ? (j == 0 ? p.w[0][1] : (j == 1 ? p.w[1][1] : p.w[2][1])) : (j == 0 ? p.w[0][3] : (j == 1 ? p.w[1][3] : p.w[2][3]));
+                    const long long sb = (long long) m * (p.K >> 8) + (u.ks0 >> 2);
+                    const uint32_t hw = TYPE == T_Q4_K ? __ldg((const uint32_t *) (wh + sb * 16)) : (uint32_t) __ldg((const unsigned short *) (wh + sb * 2));
+                    rs = __frcp_rn(gd_row_up(gd_hdr_dmax(TYPE, hw)));
+                }
+            }
+            gm_mbar_wait(tfull0 + buf * 8, bph);
+            gm_fence_after();
+            if (warp == 2 && lane == 0) gd_stamp(p, tc == 0 ? 4 : 5);
             if (u.slot < 0) {
                 float * const outp = p.outs[j] + (long long) u.sp * p.split_stride;
                 const long long ocs = p.out_css[j];
-                gd_epilogue_warp<BN / 64>(ta, outp + (long long) n0 * ocs + m, ocs, p.N - n0, m < p.Ms[j]);
+                gd_epilogue_warp<BN / 64>(ta, outp + (long long) n0 * ocs + m, ocs, p.N - n0, row_ok, csc, rs);
             } else {                                                // tail segment: the whole 256 x BN partial tile, column-major, into its slot
                 float * const slotp = p.tail_ws + (size_t) u.slot * (2 * GM_BM * BN);
-                gd_epilogue_warp<BN / 64>(ta, slotp + (size_t) c0 * (2 * GM_BM) + (int) rank * GM_BM + m_local, 2 * GM_BM, BN, true);
+                gd_epilogue_warp<BN / 64>(ta, slotp + (size_t) c0 * (2 * GM_BM) + (int) rank * GM_BM + m_local, 2 * GM_BM, BN, true, csc, rs);
             }
             gm_fence_before();
             __syncwarp();
@@ -494,6 +540,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                 const int q0 = ks0 / RS, q1 = (ks1 + RS - 1) / RS;                         // raw stages are aligned in K (K-quants: super-blocks)
                 const uint8_t * const wd = j == 0 ? p.w[0][3] : (j == 1 ? p.w[1][3] : p.w[2][3]);
                 const long long sb0 = m * (p.K >> 8);
+                float fs = 1.0f;
                 if constexpr (TYPE == T_Q6_K) {
                     #pragma unroll 1
                     for (int d = 0; d < GD3_DD; d++) {
@@ -514,6 +561,8 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                         const uint32_t dw = gd_lds4(dcell0 + (uint32_t) (((q - q0) % GD3_DD) * GD_CVT_WARPS * 32 * 4));
                         dsel = row_ok ? (((sb0 + q) & 1) ? dw >> 16 : dw & 0xFFFFu) : 0u;
                     }
+                    if constexpr (TYPE == T_Q4_K || TYPE == T_Q6_K)      // the unit's row scale, from its first super-block (the epilogue derives the same)
+                        if (q == q0) fs = gd_row_up(gd_hdr_dmax(TYPE, TYPE == T_Q4_K ? sc.x : dsel));
                     #pragma unroll
                     for (int jp = 0; jp < RS; jp += 2) {
                         uint4 o[2][4];
@@ -521,6 +570,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                         for (int u2 = 0; u2 < 2; u2++) {
                             const int jj = jp + u2, ks = q * RS + jj;
                             GdRaw raw;
+                            raw.fs = fs;
                             if constexpr (TYPE == T_Q4_0) {
                                 raw.a = gd_lds16(rowq + (((uint32_t) (2 * jj + hk) ^ r7) << 4));
                                 raw.s0 = hk ? scw[jj] >> 16 : scw[jj] & 0xFFFFu;
@@ -587,6 +637,7 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
             for (int f = 0; f < 4; f++) w[f] = j == 0 ? p.w[0][f] : (j == 1 ? p.w[1][f] : p.w[2][f]);
             // k range of a slab half that lies inside the row (q4_0 / q8_0 rows may end after the first half of the last slab)
             auto live = [&](int ks) { return row_ok && ks * GD_KS + hk * 32 < p.K; };
+            float fs = 1.0f;                      // K-quants: the unit's row scale (see the WTMA branch)
             // D slabs in flight per thread: cp.async copies into the thread's ring cells, one commit group per slab (empty groups keep
             // the count uniform), wait_group D - 1 before a slab is read
             constexpr int D = gd2_depth(TYPE);
@@ -616,7 +667,12 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
                 for (int u2 = 0; u2 < U; u2++) {
                     const int ks = kb + u2;
                     sl[u2] = slot_of(ks - ks0);
-                    if (ks < ks1 && live(ks)) { GdRaw raw; GdCvt<TYPE>::fetch(raw, sl[u2], w, m, p.K, ks, hk); GdCvt<TYPE>::convert(raw, ks, hk, o[u2]); }
+                    if (ks < ks1 && live(ks)) {
+                        GdRaw raw; GdCvt<TYPE>::fetch(raw, sl[u2], w, m, p.K, ks, hk);
+                        if constexpr (TYPE == T_Q4_K || TYPE == T_Q6_K) if (ks == ks0) fs = gd_row_up(gd_hdr_dmax(TYPE, TYPE == T_Q4_K ? raw.c.x : raw.s1));
+                        raw.fs = fs;
+                        GdCvt<TYPE>::convert(raw, ks, hk, o[u2]);
+                    }
                     else { o[u2][0] = o[u2][1] = o[u2][2] = o[u2][3] = make_uint4(0, 0, 0, 0); }
                 }
                 uint32_t sidx[U];
@@ -680,46 +736,169 @@ gemm_dense2_kernel(const __grid_constant__ GdMaps maps, const GemmDenseArgs p) {
 
 // ------------------------------------------------------------------------------------------------ operand preparation
 // activations: f32 [N][K] -> q8_1 (d = amax / 127 rounded to fp16, q = round(x / d); quantize_row_q8_1_ref ggml-quants.c:220-253)
-// -> fp16(d * q), saturating.  4 lanes per 32-element block, two float4 loads and one 16-byte store each.
-__global__ void __launch_bounds__(256)
-dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, const int K, const int N, __half * __restrict__ out) {
-    const int NB = K / 32;
-    const long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    const long long blk = gid >> 2;
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");      // x comes from the kernels before us; out may still be read by the GEMM before us
-    if (blk >= (long long) NB * N) return;                   // (whole groups of 4 lanes leave together: NB * N blocks, 4 lanes each)
-    const int row = (int) (blk / NB), b = (int) (blk - (long long) row * NB), sub = (int) (gid & 3);
-    const float4 * src = (const float4 *) (x + row * row_stride + ((long long) b * 32 + sub * 8) * 4);
-    const float4 v = src[0], w = src[1];
-    float amax = fmaxf(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))),
-                       fmaxf(fmaxf(fabsf(w.x), fabsf(w.y)), fmaxf(fabsf(w.z), fabsf(w.w))));
+// -> fp16(d * q * 2^g(n)), g(n) = the power of two that brings the column's largest |x| into [2^8, 2^9); colscale[n] = 2^-g(n).
+// One CTA per column: pass 1 finds the column's amax, pass 2 (the row comes from L1 / L2 now) converts, 8 lanes per 32-element block.
+__device__ __forceinline__ float gd_col_scale(const float amax, float * inv) {
+    if (!(amax > 0.0f) || !(amax <= 3.0e38f)) { *inv = 1.0f; return 1.0f; }
+    const int E = (int) ((__float_as_uint(amax) >> 23) & 0xFFu) - 126;        // amax = m 2^E, m in [0.5, 1)
+    int g = 9 - E;
+    g = g > 100 ? 100 : (g < -100 ? -100 : g);
+    *inv = __uint_as_float((uint32_t) (127 - g) << 23);
+    return __uint_as_float((uint32_t) (127 + g) << 23);
+}
+template <int NW>
+__device__ __forceinline__ float gd_block_max(float v, float * sh) {      // max over the NW warps of the CTA, the same value in every thread
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = sh[0];
+    #pragma unroll
+    for (int i = 1; i < NW; i++) r = fmaxf(r, sh[i]);
+    return r;
+}
+// one float4 of a 32-element block (8 consecutive lanes hold the block) -> 4 halfs of fp16(d q sc)
+__device__ __forceinline__ uint2 gd_q8_1_f16x4(const float4 v, const float sc) {
+    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
     amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
     const float d  = __fdiv_rn(amax, 127.0f);
     const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-    const float dh = __half2float(__float2half_rn(d));
+    const float dh = __half2float(__float2half_rn(d)) * sc;
     const float r0 = dh * roundf(__fmul_rn(v.x, id)), r1 = dh * roundf(__fmul_rn(v.y, id));
     const float r2 = dh * roundf(__fmul_rn(v.z, id)), r3 = dh * roundf(__fmul_rn(v.w, id));
-    const float r4 = dh * roundf(__fmul_rn(w.x, id)), r5 = dh * roundf(__fmul_rn(w.y, id));
-    const float r6 = dh * roundf(__fmul_rn(w.z, id)), r7 = dh * roundf(__fmul_rn(w.w, id));
-    uint4 h;
+    uint2 h;
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.x) : "f"(r1), "f"(r0));
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.y) : "f"(r3), "f"(r2));
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.z) : "f"(r5), "f"(r4));
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(h.w) : "f"(r7), "f"(r6));
-    *(uint4 *) (out + (long long) row * K + b * 32 + sub * 8) = h;
+    return h;
+}
+// One CTA of 256 threads per column.  The column (K floats, up to GD_ACT_SMEM_MAX bytes) arrives in shared memory by ONE bulk copy
+// (cp.async.bulk, mbarrier completion): HBM is read once, at full burst, and both passes -- the column's amax, then the conversion --
+// run out of shared memory.  Longer columns take two passes over global memory (STAGED = false).
+constexpr int GD_ACT_SMEM_MAX = 112 * 1024;
+template <bool STAGED>
+__global__ void __launch_bounds__(256)
+dequant_act_f16_kernel(const char * __restrict__ x, const long long row_stride, const int K, __half * __restrict__ out, float * __restrict__ colscale) {
+    __shared__ float sh[8];
+    __shared__ __align__(8) unsigned long long bar;
+    extern __shared__ __align__(16) uint8_t gd_act_smem[];
+    const int n = blockIdx.x, K4 = K >> 2;
+    const float4 * grow = (const float4 *) (x + (long long) n * row_stride);
+    const float4 * row = STAGED ? (const float4 *) gd_act_smem : grow;
+    if (STAGED && threadIdx.x == 0) { gm_mbar_init(gm_smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // x comes from the kernels before us; out may still be read by the GEMM before us
+    if (STAGED) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            gm_mbar_expect_tx(gm_smem_u32(&bar), (uint32_t) K * 4u);
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         :: "r"(gm_smem_u32(gd_act_smem)), "l"(grow), "r"((uint32_t) K * 4u), "r"(gm_smem_u32(&bar)) : "memory");
+        }
+        gm_mbar_wait(gm_smem_u32(&bar), 0);
+    }
+    uint2 * o = (uint2 *) (out + (long long) n * K);
+    float amax = 0.0f;
+    for (int base = 0; base < K4; base += 1024) {
+        float4 v[4];
+        #pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = base + u * 256 + threadIdx.x; v[u] = i < K4 ? row[i] : make_float4(0.f, 0.f, 0.f, 0.f); }
+        #pragma unroll
+        for (int u = 0; u < 4; u++) amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v[u].x), fabsf(v[u].y)), fmaxf(fabsf(v[u].z), fabsf(v[u].w))));
+    }
+    float inv;
+    const float sc = gd_col_scale(gd_block_max<8>(amax, sh), &inv);
+    if (threadIdx.x == 0) colscale[n] = inv;
+    for (int base = 0; base < K4; base += 1024) {            // (uniform trip counts: the shuffles inside want whole warps)
+        float4 v[4];
+        #pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = base + u * 256 + threadIdx.x; v[u] = i < K4 ? row[i] : make_float4(0.f, 0.f, 0.f, 0.f); }
+        #pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = base + u * 256 + threadIdx.x;
+            const uint2 h = gd_q8_1_f16x4(v[u], sc);
+            if (i < K4) o[i] = h;
+        }
+    }
 }
 
-cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, cudaStream_t st) {
-    const long long threads = (long long) (K / 8) * N;
+// out: fp16 [N][K]; colscale: [N rounded up to 256] floats (the entries past N are never written and only multiply results nobody keeps)
+cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, float * colscale, cudaStream_t st) {
+    const bool staged = (long long) K * 4 <= GD_ACT_SMEM_MAX && ((uintptr_t) x & 15) == 0 && row_stride_bytes % 16 == 0;
+    if (staged) {
+        static bool attr_done[64] = {false};
+        int dev = 0; cudaGetDevice(&dev); dev &= 63;
+        if (!attr_done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(dequant_act_f16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_ACT_SMEM_MAX);
+            if (e != cudaSuccess) return e;
+            attr_done[dev] = true;
+        }
+    }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned) ((threads + 255) / 256)); cfg.blockDim = dim3(256); cfg.stream = st;
+    cfg.gridDim = dim3((unsigned) N); cfg.blockDim = dim3(256); cfg.stream = st; cfg.dynamicSmemBytes = staged ? (size_t) K * 4 : 0;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel, (const char *) x, row_stride_bytes, K, N, out);
+    return staged ? cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel<true>, (const char *) x, (long long) row_stride_bytes, K, out, colscale)
+                  : cudaLaunchKernelEx(&cfg, dequant_act_f16_kernel<false>, (const char *) x, (long long) row_stride_bytes, K, out, colscale);
+}
+
+// split-K reduce with the residual ADD fused, one CTA per dst column, whose result is the next dense GEMM's src1: out = sum of the splits,
+// res_dst = res_src + out, act_out = fp16(q8_1(res_dst) 2^g) and colscale_out as dequant_act_f16_kernel would produce them (M <= 8192, M % 32 == 0)
+__global__ void __launch_bounds__(256)
+reduce_splits4_act_kernel(const float4 * __restrict__ ws, const int S, const long long MN4, const int M4, float4 * __restrict__ out, const long long out_cs4,
+                          const float4 * __restrict__ res_src, float4 * __restrict__ res_dst, uint2 * __restrict__ act_out, float * __restrict__ colscale_out) {
+    __shared__ float sh[8];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const long long n = blockIdx.x;
+    float4 z[8];
+    float amax = 0.0f;
+    #pragma unroll
+    for (int it = 0; it < 8; it++) {
+        const int m = it * 256 + threadIdx.x;
+        z[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m < M4) {
+            const long long i = n * M4 + m;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int sp = 0; sp < S; sp++) {               // split order: deterministic
+                const float4 w = ws[(long long) sp * MN4 + i];
+                v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
+            }
+            out[n * out_cs4 + m] = v;
+            const float4 r = res_src[i];
+            z[it] = make_float4(r.x + v.x, r.y + v.y, r.z + v.z, r.w + v.w);      // the GGML_OP_ADD node that consumes this MUL_MAT
+            res_dst[i] = z[it];
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(z[it].x), fabsf(z[it].y)), fmaxf(fabsf(z[it].z), fabsf(z[it].w))));
+        }
+    }
+    float inv;
+    const float sc = gd_col_scale(gd_block_max<8>(amax, sh), &inv);
+    if (threadIdx.x == 0) colscale_out[n] = inv;
+    #pragma unroll
+    for (int it = 0; it < 8; it++) {
+        if (it * 256 < M4) {                                // (uniform)
+            const int m = it * 256 + threadIdx.x;
+            const uint2 h = gd_q8_1_f16x4(z[it], sc);
+            if (m < M4) act_out[n * M4 + m] = h;
+        }
+    }
+}
+cudaError_t launch_reduce_splits_act(const float * ws, int S, int M, int N, float * out, long long out_cs, cudaStream_t st,
+                                     const float * res_src, float * res_dst, void * act_out, float * colscale_out) {
+    if (M % 32 != 0 || M > 8192 || out_cs % 4 != 0 || !res_dst || !act_out || !colscale_out ||
+        (((uintptr_t) ws | (uintptr_t) out | (uintptr_t) res_src | (uintptr_t) res_dst) & 15) != 0 || ((uintptr_t) act_out & 7) != 0) return cudaErrorInvalidValue;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) N); cfg.blockDim = dim3(256); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, reduce_splits4_act_kernel, (const float4 *) ws, S, (long long) M * N / 4, M / 4, (float4 *) out, out_cs / 4,
+                              (const float4 *) res_src, (float4 *) res_dst, (uint2 *) act_out, colscale_out);
 }
 // ---- stream-K tail: dst tile = sum of the tail_ws slots of the chunks that cover it, in chunk order
 struct GdFixArgs {
@@ -818,12 +997,13 @@ static int gd3_box_rt(int type, int f) { return gd3_box(type, f); }
 // nmat weight matrices A[j] (type `type`, SoA fields, M[j] rows of K) over the same activations B (fp16 [N][K], 16-B aligned rows);
 // out[j][n * out_cs[j] + m]; split_ws: workspace of ksplit * N * M floats (nmat == 1), or nullptr (no split)
 static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
-                               const __half * B, int N, int K, int sms, int ksplit, float * split_ws, float * tail_ws, int * nlaunch, cudaStream_t st) {
+                               const __half * B, const float * colscale, int N, int K, int sms, int ksplit, float * split_ws, float * tail_ws, int * nlaunch, cudaStream_t st) {
     const int bn = gemm_dense_bn(M[0], N, sms);
     GdMaps maps;
     CUtensorMap * const tmB = maps.b;
     GemmDenseArgs p{};
-    p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit;
+    p.N = N; p.K = K; p.ntiles = (N + bn - 1) / bn; p.nmat = nmat; p.ksplit = ksplit; p.colscale = colscale;
+    if (!colscale || ((uintptr_t) colscale & 15) != 0) return cudaErrorInvalidValue;
     int tiles = 0;
     for (int j = 0; j < GD_MAXMAT; j++) {
         const int jj = j < nmat ? j : 0;
@@ -899,24 +1079,26 @@ static cudaError_t launch_pair(int type, const WPtrs * A, float * const * out, c
     return e;
 }
 
-// A: quantised weights (type, SoA fields) [M][K]; B: fp16 [N][K] (K % 8 == 0); out[n * out_cs + m]
-// split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split); tail_ws: gemm_dense_tail_ws_bytes(sms), or nullptr
-// (no stream-K tail); *nlaunch: kernels launched
-cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, float * out, long long out_cs, int M, int N, int K, int sms, float * split_ws, float * tail_ws,
-                              int * nlaunch, cudaStream_t st, const float * res_src, float * res_dst, void * act_out) {
+// A: quantised weights (type, SoA fields) [M][K]; B: fp16 [N][K] (K % 8 == 0) and its column scales as launch_dequant_act_f16 wrote them;
+// out[n * out_cs + m].  split_ws: workspace of gemm_dense_ksplit(...) * N * M floats, or nullptr (no split); tail_ws:
+// gemm_dense_tail_ws_bytes(sms), or nullptr (no stream-K tail); *nlaunch: kernels launched.
+// act_out / act_cs_out: with res_dst, the next dense GEMM's activations (fp16 [N][M]) and column scales, converted by the reduce
+cudaError_t launch_gemm_dense(int type, const WPtrs & A, const __half * B, const float * colscale, float * out, long long out_cs, int M, int N, int K, int sms,
+                              float * split_ws, float * tail_ws, int * nlaunch, cudaStream_t st, const float * res_src, float * res_dst, void * act_out, float * act_cs_out) {
     const int ksplit = split_ws ? gemm_dense_ksplit(M, N, K, sms) : 1;
     if (res_dst && ksplit == 1) return cudaErrorInvalidValue;
-    const cudaError_t e = launch_pair(type, &A, &out, &out_cs, &M, 1, B, N, K, sms, ksplit, split_ws, tail_ws, nlaunch, st);
+    const cudaError_t e = launch_pair(type, &A, &out, &out_cs, &M, 1, B, colscale, N, K, sms, ksplit, split_ws, tail_ws, nlaunch, st);
     if (e != cudaSuccess || ksplit == 1) return e;
     if (nlaunch) (*nlaunch)++;
-    return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst, act_out);
+    if (act_out) return launch_reduce_splits_act(split_ws, ksplit, M, N, out, out_cs, st, res_src, res_dst, act_out, act_cs_out);
+    return launch_reduce_splits(split_ws, ksplit, (long long) M * N, M, out, out_cs, 0, st, res_src, res_dst, nullptr);
 }
 
 // Several weight matrices of one type over the same activations in ONE launch (no split-K): 2 <= nmat <= 3
 cudaError_t launch_gemm_dense_group(int type, const WPtrs * A, float * const * out, const long long * out_cs, const int * M, int nmat,
-                                    const __half * B, int N, int K, int sms, float * tail_ws, int * nlaunch, cudaStream_t st) {
+                                    const __half * B, const float * colscale, int N, int K, int sms, float * tail_ws, int * nlaunch, cudaStream_t st) {
     if (nmat < 1 || nmat > GD_MAXMAT) return cudaErrorNotSupported;
-    return launch_pair(type, A, out, out_cs, M, nmat, B, N, K, sms, 1, nullptr, tail_ws, nlaunch, st);
+    return launch_pair(type, A, out, out_cs, M, nmat, B, colscale, N, K, sms, 1, nullptr, tail_ws, nlaunch, st);
 }
 
 }  // namespace b200

@@ -444,6 +444,9 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
     // flag protocol: a separate 32-thread exchange kernel after the op (signal + wait), launched by rs_exchange
     return 0;
 }
+// dense GEMM activations in gm_qb: fp16 [N][K], then (256-byte aligned) the column scales, N rounded up to 256 floats
+static size_t dense_act_cs_off(int64_t N, int64_t K) { return ((size_t) N * K * 2 + 255) & ~(size_t) 255; }
+static size_t dense_act_bytes(int64_t N, int64_t K) { return dense_act_cs_off(N, K) + (size_t) ((N + 255) & ~(int64_t) 255) * sizeof(float); }
 static bool act_fusion_enabled() { static const bool on = !(getenv("B200_GEMM_ACTFUSE") && atoi(getenv("B200_GEMM_ACTFUSE")) == 0); return on; }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
@@ -486,7 +489,8 @@ static int presize_gemm(Ctx * c, const b200_tensor * s0, const b200_tensor * s1)
     const size_t ldb = (size_t) gemm_i8_ldb((int) N);
     int rc;
     if (gemm_dense_enabled()) {
-        rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+        rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, dense_act_bytes(N, K)); if (rc) return rc;
+        if (M % 32 == 0) { rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, dense_act_bytes(N, M)); if (rc) return rc; }      // (room for the fused conversion of a residual sum)
         const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
         if (ksp > 1) { rc = ensure_buf(c, &c->gm_sp, &c->gm_sp_cap, (size_t) ksp * M * N * sizeof(float)); if (rc) return rc; }
         rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
@@ -530,11 +534,12 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
         if (q && use_gemm && gemm_dense_enabled()) {
             // ---- many columns: dense fp16 tensor-core GEMM, block scales folded into the operands (gemm_dense.cu)
             const WPtrs wp = wptrs_offset(s0, wp0, i02 * s0->nb[2] + i03 * s0->nb[3]);
-            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+            rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, dense_act_bytes(N, K)); if (rc) return rc;
+            float * const colscale = (float *) (c->gm_qb + dense_act_cs_off(N, K));
             // (consecutive MUL_MATs of a node list over the same activations -- q / k / v, gate / up -- convert them once)
             const bool reuse = c->in_graph && c->q_kind == 1 && c->q_ptr == (const void *) x && c->q_K == K && c->q_N == N && c->q_stride == s1->nb[1];
             if (!reuse) {
-                CU(launch_dequant_act_f16((const float *) x, s1->nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
+                CU(launch_dequant_act_f16((const float *) x, s1->nb[1], (int) K, (int) N, (__half *) c->gm_qb, colscale, c->st)); c->launches++;
                 c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = s1->nb[1]; c->q_kind = 1;
             }
             const int ksp = gemm_dense_ksplit((int) M, (int) N, (int) K, c->sms);
@@ -543,11 +548,12 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
             // the fused ADD's result is usually the next MUL_MAT's src1 (K = M): the reduce converts it into gm_qb on the way (the GEMM of this
             // op has read gm_qb by then), and the next op finds its activations converted.  Only where gm_qb already has the room (no
             // reallocation under a capture) and inside a node list.
-            const bool next_act = fa && c->in_graph && M % 32 == 0 && c->gm_qb_cap >= (size_t) N * M * 2 && act_fusion_enabled();
+            const bool next_act = fa && c->in_graph && M % 32 == 0 && M <= 8192 && c->gm_qb_cap >= dense_act_bytes(N, M) && act_fusion_enabled();
             rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
             int nl = 0;
-            CU(launch_gemm_dense(s0->type, wp, (const __half *) c->gm_qb, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->gm_tail, &nl, c->st,
-                                 fa ? fa->src : nullptr, fa ? fa->dst : nullptr, next_act ? c->gm_qb : nullptr));
+            CU(launch_gemm_dense(s0->type, wp, (const __half *) c->gm_qb, colscale, y, dcs, (int) M, (int) N, (int) K, c->sms, ksp > 1 ? c->gm_sp : nullptr, c->gm_tail, &nl, c->st,
+                                 fa ? fa->src : nullptr, fa ? fa->dst : nullptr, next_act ? c->gm_qb : nullptr,
+                                 next_act ? (float *) (c->gm_qb + dense_act_cs_off(N, M)) : nullptr));
             c->launches += nl;
             if (next_act) { c->q_ptr = fa->dst; c->q_K = M; c->q_N = N; c->q_stride = M * 4; c->q_kind = 1; }
             if (c->rs_on && c->world > 1) {
@@ -774,16 +780,17 @@ static int mulmat_dense_group_dev(Ctx * c, const b200_node * nodes, int len) {
         rc = wptrs_of(&nodes[j].src0, &A[j]); if (rc) return rc;
         out[j] = (float *) d.data; ocs[j] = d.nb[1] / 4; Ms[j] = (int) nodes[j].src0.ne[1];
     }
-    int rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, (size_t) N * K * 2); if (rc) return rc;
+    int rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, dense_act_bytes(N, K)); if (rc) return rc;
+    float * const colscale = (float *) (c->gm_qb + dense_act_cs_off(N, K));
     const b200_tensor & s1 = nodes[0].src1;
     const bool reuse = c->q_kind == 1 && c->q_ptr == (const void *) s1.data && c->q_K == K && c->q_N == N && c->q_stride == s1.nb[1];
     if (!reuse) {
-        CU(launch_dequant_act_f16((const float *) s1.data, s1.nb[1], (int) K, (int) N, (__half *) c->gm_qb, c->st)); c->launches++;
+        CU(launch_dequant_act_f16((const float *) s1.data, s1.nb[1], (int) K, (int) N, (__half *) c->gm_qb, colscale, c->st)); c->launches++;
         c->q_ptr = s1.data; c->q_K = K; c->q_N = N; c->q_stride = s1.nb[1]; c->q_kind = 1;
     }
     rc = ensure_buf(c, &c->gm_tail, &c->gm_tail_cap, gemm_dense_tail_ws_bytes(c->sms)); if (rc) return rc;
     int nl = 0;
-    CU(launch_gemm_dense_group(nodes[0].src0.type, A, out, ocs, Ms, len, (const __half *) c->gm_qb, (int) N, (int) K, c->sms, c->gm_tail, &nl, c->st)); c->launches += nl;
+    CU(launch_gemm_dense_group(nodes[0].src0.type, A, out, ocs, Ms, len, (const __half *) c->gm_qb, colscale, (int) N, (int) K, c->sms, c->gm_tail, &nl, c->st)); c->launches += nl;
     return 0;           // (dense_group_len made sure that no dst touches the activations the cached conversion came from)
 }
 

@@ -313,3 +313,79 @@ def test_dense_close_to_exact_mode(sess, monkeypatch):
     exact = sess.mulmat(w, x)
     assert nmse(dense, exact) <= DENSE_BAR and not np.array_equal(dense, exact)
     w.free()
+
+
+# ------------------------------------------------------------------------------------------------ operand ranges
+def _col_nmse(got, ref):
+    """worst column: columns of very different magnitude must each be right, not only the largest"""
+    num = ((got.astype(np.float64) - ref) ** 2).sum(axis=1)
+    den = np.maximum((ref.astype(np.float64) ** 2).sum(axis=1), 1e-300)
+    return float((num / den).max())
+
+
+@pytest.mark.parametrize("N", [64, 512])
+@pytest.mark.parametrize("scale", [1e5, 3e6, 1e-3, 1e-6, "mixed"])
+@pytest.mark.parametrize("t,name", ALL)
+def test_dense_activation_range_vs_oracle(sess, t, name, scale, N):
+    """activations far outside what fp16(d_a q_a) could hold unscaled (|x| up to 3e6: the reference's own limit is d_a = amax / 127 <= 65504)
+    and far below (1e-6: the reference's fp16 d_a is zero there and so is ours); 'mixed': every column at its own magnitude, 1e-5 .. 3e6.
+    The per-column power-of-two scale of the conversion kernel keeps the dense path on the oracle for all of them."""
+    rng = np.random.default_rng(900 + t + N)
+    M, K = 300, 1024
+    raw = O.random_blocks(t, M, K, rng)
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    if scale == "mixed":
+        x *= (10.0 ** rng.uniform(-5, 6.4, (N, 1))).astype(np.float32)
+    else:
+        x *= np.float32(scale)
+    w = sess.weights(t, raw, K)
+    got = sess.mulmat(w, x)
+    ref = O.mul_mat(t, raw, x, 1)
+    assert np.isfinite(got).all()
+    if scale == 1e-6:
+        assert not ref.any() and not got.any()             # d_a = amax / 127 rounds to zero in fp16: quantize_row_q8_1_ref, and the oracle, say 0
+    else:
+        assert _col_nmse(got, ref) <= DENSE_BAR, (name, scale, N, _col_nmse(got, ref))
+        if scale != 1e-3:                                     # (1e-3: ggml-cpu keeps an f32 d for its q8_K activations, q8_1's fp16 d is subnormal there)
+            assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
+    w.free()
+
+
+def _with_scale(t, raw, M, K, d16, rows=slice(None), blocks=slice(None)):
+    """overwrite the fp16 block scale d (q4_K: d and dmin) of the given rows / blocks of a wire-format matrix"""
+    bpb, nb = B.BLOCK[t][1], K // B.BLOCK[t][0]
+    r = raw.reshape(M, nb, bpb).copy()
+    h = np.frombuffer(np.float16(d16).tobytes(), dtype=np.uint8)
+    off = 208 if t == O.Q6_K else 0
+    r[rows, blocks, off:off + 2] = h
+    if t == O.Q4_K:
+        r[rows, blocks, 2:4] = h
+    return r.reshape(M, nb * bpb)
+
+
+@pytest.mark.parametrize("N", [64, 512])
+@pytest.mark.parametrize("case", ["all 1e-7", "every other row 1e-7", "first block 1e-7, the rest 1e-5", "first block 6e-8, the rest 2e-3"])
+@pytest.mark.parametrize("t,name", ALL)
+def test_dense_tiny_weight_scales_vs_oracle(sess, t, name, case, N):
+    """block scales in fp16's subnormal range: q4_0 / q8_0 products d_w q_w stay exact (integers times 2^-24), K-quant rows are scaled up by a
+    power of two in the converters (taken from the first super-block) and scaled back in the epilogue"""
+    rng = np.random.default_rng(950 + t + N)
+    M, K = 300, 2048
+    raw = O.random_blocks(t, M, K, rng)
+    if case == "all 1e-7":
+        raw = _with_scale(t, raw, M, K, 1e-7)
+    elif case == "every other row 1e-7":
+        raw = _with_scale(t, raw, M, K, 1e-7, rows=slice(0, None, 2))
+    elif case == "first block 1e-7, the rest 1e-5":
+        raw = _with_scale(t, _with_scale(t, raw, M, K, 1e-5), M, K, 1e-7, blocks=slice(0, 1))
+    else:
+        raw = _with_scale(t, _with_scale(t, raw, M, K, 2e-3), M, K, 6e-8, blocks=slice(0, 1))
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    w = sess.weights(t, raw, K)
+    got = sess.mulmat(w, x)
+    ref = O.mul_mat(t, raw, x, 1)
+    assert np.isfinite(got).all()
+    rows_err = ((got.astype(np.float64) - ref) ** 2).sum(axis=0) / np.maximum((ref.astype(np.float64) ** 2).sum(axis=0), 1e-300)
+    assert float(rows_err.max()) <= DENSE_BAR, (name, case, N, float(rows_err.max()))      # every dst row (= weight row) on its own
+    assert nmse(got, O.mul_mat(t, raw, x, 0)) <= 5e-4
+    w.free()
