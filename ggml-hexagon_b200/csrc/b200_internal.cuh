@@ -99,6 +99,10 @@ constexpr int LL_HALF_ELEMS = 131072;                     // {value, seq} slots 
 struct LlGatherArgs { uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_op; int nmat; float * dst[3]; int M[3]; int ll_off[3]; int world, rank; };
 // polls the peers' slots of one exchange and writes the values into the local dst vectors; starts while the GEMV still runs (PDL)
 cudaError_t launch_ll_gather(const LlGatherArgs & a, cudaStream_t st);
+// the gather + what follows it in the node list: the residual ADD on vector qmat (add_dst = gathered + add_src, or null) and the q8_1
+// quantisation of the result into qs / ds for the MUL_MAT that consumes it (every M % 32 == 0)
+struct LlFuseArgs { int qmat; const float * add_src; float * add_dst; int8_t * qs; ActDS * ds; };
+cudaError_t launch_ll_gather_fused(const LlGatherArgs & a, const LlFuseArgs & f, cudaStream_t st);
 // end of a submission: *ll_count += nops
 cudaError_t launch_ll_bump(uint32_t * ll_count, uint32_t nops, cudaStream_t st);
 // row-split prefill: copy this rank's rows x N slice of dst (local, column stride dcs floats) into every peer's dst (heap offset + delta)

@@ -356,6 +356,85 @@ cudaError_t launch_ll_gather(const LlGatherArgs & a, cudaStream_t st) {
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, ll_gather_kernel, a);
 }
+// The same gather with the work of the next two nodes folded in (nmat vectors of M x world elements each, M % 32 == 0): for vector f.qmat,
+// optionally z = gathered + add_src (the residual GGML_OP_ADD that consumes it, stored to add_dst), then the q8_1 quantisation of the
+// result into the activation scratch of the MUL_MAT that reads it next (quantize_q8_1_kernel's arithmetic and layout, 8 lanes per block).
+// Per decode layer of a row split this leaves 2 launches per exchange (GEMV, gather) instead of 3 - 4 (+ ADD, + quantise).
+// The scratch may still be read by the local GEMV while we poll: it is written only after the grid dependency has resolved.
+__global__ void __launch_bounds__(1024)
+ll_gather_fused_kernel(const LlGatherArgs a, const LlFuseArgs f) {
+#if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();
+#endif
+    const uint32_t seq = *a.ll_count + a.ll_op;
+    const uint2 * half = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    bool synced = false;
+    for (int m = 0; m < a.nmat; m++) {
+        const int M = a.M[m], total4 = M * a.world / 4, NB = M * a.world / 32;
+        const uint2 * slots = half + a.ll_off[m];
+        for (int base = 0; base < total4; base += gsize) {           // (uniform trip count: the shuffles below want whole warps)
+            const int i4 = base + gtid, i = i4 * 4;
+            const bool on = i4 < total4, own = on && i / M == a.rank;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (on && !own) {
+                uint4 s0, s1;
+                const long long t0 = clock64();
+                for (;;) {
+                    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(s0.x), "=r"(s0.y), "=r"(s0.z), "=r"(s0.w) : "l"(slots + i) : "memory");
+                    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(s1.x), "=r"(s1.y), "=r"(s1.z), "=r"(s1.w) : "l"(slots + i + 2) : "memory");
+                    if (s0.y == seq && s0.w == seq && s1.y == seq && s1.w == seq) break;
+                    if (clock64() - t0 > 8000000000ll) __trap();
+                }
+                v = make_float4(__uint_as_float(s0.x), __uint_as_float(s0.z), __uint_as_float(s1.x), __uint_as_float(s1.z));
+                *(float4 *) (a.dst[m] + i) = v;
+            }
+#if __CUDA_ARCH__ >= 900
+            if (!synced) { cudaGridDependencySynchronize(); synced = true; }      // the local GEMV is complete: its slice, and the scratch, are ours
+#endif
+            if (own) v = __ldcg((const float4 *) (a.dst[m] + i));
+            if (m != f.qmat) continue;
+            if (f.add_dst && on) {
+                const float4 o = *(const float4 *) (f.add_src + i);
+                v = make_float4(v.x + o.x, v.y + o.y, v.z + o.z, v.w + o.w);
+                *(float4 *) (f.add_dst + i) = v;
+            }
+            const int sub = gtid & 7, b = i4 >> 3;
+            float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+            const float d  = __fdiv_rn(amax, 127.0f);
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
+            const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
+            int sum = q0 + q1 + q2 + q3;
+            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+            const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
+            if (on) {
+                const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
+                *(uint32_t *) (f.qs + ((int64_t) (sub >> 2) * NB + b) * 16 + (sub & 3) * 4) = packed;
+                if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; f.ds[b] = o; }
+            }
+        }
+    }
+#if __CUDA_ARCH__ >= 900
+    if (!synced) cudaGridDependencySynchronize();
+#endif
+}
+cudaError_t launch_ll_gather_fused(const LlGatherArgs & a, const LlFuseArgs & f, cudaStream_t st) {
+    long long most = 0;
+    for (int m = 0; m < a.nmat; m++) { const long long t = (long long) a.M[m] * a.world / 4; if (t > most) most = t; if (a.M[m] % 32) return cudaErrorInvalidValue; }
+    int blocks = (int) ((most + 1023) / 1024); if (blocks > 64) blocks = 64; if (blocks < 1) blocks = 1;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) blocks); cfg.blockDim = dim3(1024); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, ll_gather_fused_kernel, a, f);
+}
 __global__ void ll_bump_kernel(uint32_t * ll_count, const uint32_t nops) { *ll_count += nops; }
 cudaError_t launch_ll_bump(uint32_t * ll_count, uint32_t nops, cudaStream_t st) {
     ll_bump_kernel<<<1, 1, 0, st>>>(ll_count, nops);

@@ -95,6 +95,8 @@ struct Ctx {
     char * rs_peer[8] = {nullptr}; bool rs_ipc[8] = {false};
     bool rs_attached = false, rs_on = false;
     // LL protocol bookkeeping of the submission being built: exchanges so far, and what the gather after the current GEMV collects
+    // look-ahead of run_nodes for the next row-split exchange: fold the ADD / q8_1 quantisation that follow into the gather kernel
+    struct { bool on = false, done = false; const void * of = nullptr; int qmat = -1; const float * add_src = nullptr; float * add_dst = nullptr; } rs_hint;
     uint32_t rs_ops = 0; int ll_nmat = 0; float * ll_dst[3] = {}; int ll_M[3] = {}; int ll_off[3] = {}; uint32_t ll_op = 0;
 };
 
@@ -447,6 +449,7 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
 // dense GEMM activations in gm_qb: fp16 [N][K], then (256-byte aligned) the column scales, N rounded up to 256 floats
 static size_t dense_act_cs_off(int64_t N, int64_t K) { return ((size_t) N * K * 2 + 255) & ~(size_t) 255; }
 static size_t dense_act_bytes(int64_t N, int64_t K) { return dense_act_cs_off(N, K) + (size_t) ((N + 255) & ~(int64_t) 255) * sizeof(float); }
+static bool rs_fuse_enabled() { static const bool on = !(getenv("B200_RS_FUSE") && atoi(getenv("B200_RS_FUSE")) == 0); return on; }
 static bool act_fusion_enabled() { static const bool on = !(getenv("B200_GEMM_ACTFUSE") && atoi(getenv("B200_GEMM_ACTFUSE")) == 0); return on; }
 static int rs_exchange(Ctx * c) {
     if (!c->rs_on || c->world == 1) return 0;
@@ -456,6 +459,18 @@ static int rs_exchange(Ctx * c) {
         g.nmat = c->ll_nmat; g.world = c->world; g.rank = c->rank;
         for (int i = 0; i < c->ll_nmat; i++) { g.dst[i] = c->ll_dst[i]; g.M[i] = c->ll_M[i]; g.ll_off[i] = c->ll_off[i]; }
         c->ll_nmat = 0;
+        if (c->rs_hint.on) {
+            int qm = -1;
+            for (int i = 0; i < g.nmat; i++) if ((const void *) g.dst[i] == c->rs_hint.of && g.M[i] % 32 == 0) qm = i;
+            bool ok = qm >= 0;
+            for (int i = 0; i < g.nmat; i++) ok = ok && g.M[i] % 32 == 0;
+            if (ok && (int64_t) g.M[qm] * g.world / 32 <= c->act_cap) {
+                LlFuseArgs f{}; f.qmat = qm; f.add_src = c->rs_hint.add_src; f.add_dst = c->rs_hint.add_dst; f.qs = c->act_qs; f.ds = c->act_ds;
+                CU(launch_ll_gather_fused(g, f, c->st)); c->launches++;
+                c->rs_hint.done = true;
+                return 0;
+            }
+        }
         CU(launch_ll_gather(g, c->st)); c->launches++;
         return 0;
     }
@@ -904,6 +919,32 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             case B200_OP_MUL_MAT: {
                 FusedAdd fa;
                 const int gl = fuse ? group_len(nodes, i, n) : 1;
+                // row split: what consumes this op's gathered vectors next?  [ADD with a plain vector ->] vector MUL_MAT: the gather kernel
+                // does the ADD and quantises for that MUL_MAT (rs_exchange), the ADD node is skipped and the MUL_MAT finds its activations cached
+                const b200_node * nx = nullptr; bool skip_add = false;
+                c->rs_hint.on = false; c->rs_hint.done = false;
+                if (fuse && rs_fuse_enabled() && c->rs_on && c->world > 1 && is_vec_mulmat(nodes[i])) {
+                    const int j = i + gl;
+                    for (int mbr = 0; mbr < gl && !c->rs_hint.on && j < n; mbr++) {
+                        const b200_node & me = nodes[i + mbr];
+                        const int64_t full = me.src0.ne[1] * c->world;
+                        if (!is_vec_f32(me.dst, full)) continue;
+                        if (is_vec_mulmat(nodes[j]) && nodes[j].src1.data == me.dst.data && nodes[j].src0.ne[0] == full && nodes[j].src1.nb[0] == 4) {
+                            c->rs_hint.on = true; c->rs_hint.of = me.dst.data; c->rs_hint.add_src = nullptr; c->rs_hint.add_dst = nullptr; nx = &nodes[j];
+                        } else if (nodes[j].dst.op == B200_OP_ADD && j + 1 < n && is_vec_f32(nodes[j].src0, full) && is_vec_f32(nodes[j].src1, full) && is_vec_f32(nodes[j].dst, full) &&
+                                   (nodes[j].src0.data == me.dst.data) != (nodes[j].src1.data == me.dst.data) &&
+                                   is_vec_mulmat(nodes[j + 1]) && nodes[j + 1].src1.data == nodes[j].dst.data && nodes[j + 1].src0.ne[0] == full && nodes[j + 1].src1.nb[0] == 4) {
+                            const void * other = nodes[j].src0.data == me.dst.data ? nodes[j].src1.data : nodes[j].src0.data;
+                            bool clash = false;                  // the sum must not land on another member's gathered vector
+                            for (int o = 0; o < gl; o++) if (o != mbr) clash = clash || overlap(nodes[j].dst.data, full * 4, nodes[i + o].dst.data, nodes[i + o].src0.ne[1] * c->world * 4);
+                            if (!clash && (((uintptr_t) other | (uintptr_t) nodes[j].dst.data | (uintptr_t) me.dst.data) & 15) == 0) {
+                                c->rs_hint.on = true; c->rs_hint.of = me.dst.data; c->rs_hint.add_src = (const float *) other; c->rs_hint.add_dst = (float *) nodes[j].dst.data;
+                                nx = &nodes[j + 1]; skip_add = true;
+                            }
+                        }
+                    }
+                    if (c->rs_hint.on) { rc = ensure_act(c, nx->src0.ne[0] / 32); if (rc) break; }
+                }
                 const int dgl = fuse && gl == 1 ? dense_group_len(c, nodes, i, n) : 1;
                 if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
                 else if (dgl > 1) { rc = mulmat_dense_group_dev(c, nodes + i, dgl); used = dgl; }
@@ -916,6 +957,11 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                     rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &dl, c->rank * rows);
                 }
                 else rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0);
+                if (!rc && c->rs_hint.on && c->rs_hint.done) {       // the gather quantised for nx (and did the ADD in front of it)
+                    c->q_ptr = nx->src1.data; c->q_K = nx->src0.ne[0]; c->q_N = 1; c->q_stride = nx->src1.nb[1]; c->q_kind = 0;
+                    if (skip_add) used++;
+                }
+                c->rs_hint.on = false; c->rs_hint.done = false;
                 break;
             }
             default: rc = fail(B200_ENOTSUP, "graph node %d: op %d not offloaded", i, d.op);

@@ -14,12 +14,14 @@ def nmse(a, b):
     return float(((a.astype(np.float64) - b) ** 2).sum() / max((b.astype(np.float64) ** 2).sum(), 1e-30))
 
 
+@pytest.mark.parametrize("W", [2, 4, 8])
 @pytest.mark.parametrize("t", [O.Q4_0, O.Q8_0, O.Q4_K, O.Q6_K])
 @pytest.mark.parametrize("use_graph", [0, 1])
-def test_rowsplit_two_ranks(t, use_graph):
-    if B.device_count() < 2:
-        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
-    W = 2
+def test_rowsplit_ranks(t, use_graph, W):
+    """2, 4 and 8 ranks (every rank holds a DIFFERENT row slice: a gather that mixes ranks up cannot pass); five submissions in a row
+    walk the two halves of the LL staging area several times"""
+    if B.device_count() < W:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (W, W))
     rng = np.random.default_rng(11 + t)
     M = K = 2048
     raw1, raw2, raw3 = (O.random_blocks(t, M, K, rng, 0.05) for _ in range(3))
@@ -46,8 +48,8 @@ def test_rowsplit_two_ranks(t, use_graph):
         # y1 and y2 share the activation vector (one grouped launch, one exchange); z = y1 + x replicated; out = W3 z
         nodes_per_rank.append([mm(w1, xb, y1), mm(w2, xb, y2), add, mm(w3, z, out)])
         bufs.append((y1, y2, z, out))
-    for rep in range(3):
-        for r in range(W):                       # asynchronous launches: both ranks' kernels must be in flight together
+    for rep in range(5):
+        for r in range(W):                       # asynchronous launches: all ranks' kernels must be in flight together
             sess[r].graph_compute_rowsplit(nodes_per_rank[r], use_cuda_graph=use_graph)
         for r in range(W):
             sess[r].sync()
@@ -57,21 +59,23 @@ def test_rowsplit_two_ranks(t, use_graph):
         assert nmse(y1, mmo(raw1, x)) <= 1e-9 and nmse(y2, mmo(raw2, x)) <= 1e-9, r
         assert np.array_equal(z, y1 + x.reshape(-1))
         assert nmse(out, mmo(raw3, z)) <= 1e-9, r
-    # both ranks hold identical full vectors
-    assert np.array_equal(sess[0].to_host(bufs[0][3], (M,), np.float32), sess[1].to_host(bufs[1][3], (M,), np.float32))
+    # all ranks hold identical full vectors
+    for r in range(1, W):
+        assert np.array_equal(sess[0].to_host(bufs[0][3], (M,), np.float32), sess[r].to_host(bufs[r][3], (M,), np.float32))
     for s in sess:
         s.close()
 
 
+@pytest.mark.parametrize("W", [2, 4, 8])
 @pytest.mark.parametrize("t", [O.Q4_0, O.Q6_K])
 @pytest.mark.parametrize("use_graph", [0, 1])
-def test_rowsplit_prefill_two_ranks(monkeypatch, t, use_graph):
+def test_rowsplit_prefill_ranks(monkeypatch, t, use_graph, W):
     """N = 96 activation columns under row split: every rank runs the dense tensor-core GEMM on its row slice, pushes the slice into
     the peer's copy of dst over NVLink, and the flag exchange publishes it; a second MUL_MAT consumes the gathered result"""
-    if B.device_count() < 2:
-        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    if B.device_count() < W:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (W, W))
     monkeypatch.setenv("B200_GEMM_MIN_N", "16")
-    W, N = 2, 96
+    N = 96
     rng = np.random.default_rng(23 + t)
     M = K = 2048
     raw1, raw3 = (O.random_blocks(t, M, K, rng, 0.05) for _ in range(2))
@@ -107,7 +111,8 @@ def test_rowsplit_prefill_two_ranks(monkeypatch, t, use_graph):
         assert nmse(y1, O.mul_mat(t, raw1, x, 1)) <= 1e-6, r
         assert np.array_equal(z, y1 + x)
         assert nmse(out, O.mul_mat(t, raw3, z, 1)) <= 1e-6, r
-    assert np.array_equal(sess[0].to_host(bufs[0][2], (N, M), np.float32), sess[1].to_host(bufs[1][2], (N, M), np.float32))
+    for r in range(1, W):
+        assert np.array_equal(sess[0].to_host(bufs[0][2], (N, M), np.float32), sess[r].to_host(bufs[r][2], (N, M), np.float32))
     for s in sess:
         s.close()
 
