@@ -421,7 +421,7 @@ def time_prefill_model(B, s, wl, N=512, steps=5):
             "frac_of_measured_16bit_tensor_peak": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "tensor_peak_TFLOPS": tc_peak,
             "roofline": {"bound": "tensor", "achieved": round(flops / sec / 1e12, 1), "peak": tc_peak, "unit": "TFLOP/s",
                          "frac": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "traffic": None,
-                         "kernel": "gemm_dense2_kernel<256> (tcgen05.mma.cta_group::2 kind::f16)",
+                         "kernel": "gemm_dense2_kernel<256, q4_0, WTMA> (tcgen05.mma.cta_group::2 kind::f16; native q4_0 blocks by TMA, dequantised by converter warps)",
                          "note": "2*M*N*K of every MUL_MAT of the step / device time of the whole step (conversions, reduces, ADDs included)"},
             "kernels_per_step": int(launches), "first_call_ms": round(first_s * 1e3, 1),
             "note": "whole node list (%d MUL_MAT + %d ADD) over N=%d columns, one graph_compute per step, distinct weights per layer; "
@@ -812,7 +812,7 @@ def run_b200(args, rank, world):
                        ("one b200_graph_compute_rowsplit (CUDA graph; GEMV stores {value, seq} slots into peer HBM over NVLink, polled by a gather kernel per op; B200_RS_PROTO=flag: plain stores + flag exchange)"
                         if args.rowsplit == "p2p" else "per-node b200_mulmat_rowsplit + ncclAllGather")},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4), "frac_of_nominal_8000": round(achieved / 8000.0, 4),
-                         "traffic": measured_traffic()[0] if world == 1 else None, "traffic_source": measured_traffic()[1] if world == 1 else None, "peak_source": peak_src, "kernel": "gemv5_kernel<q4_0,8,1> (launches >= 12 MB; gemv4_kernel<q4_0,1,4> for wo)",
+                         "traffic": measured_traffic()[0] if world == 1 else None, "traffic_source": measured_traffic()[1] if world == 1 else None, "peak_source": peak_src, "kernel": "b200_gemv5_kernel<q4_0,8,1> (launches >= 12 MB: q/k/v, gate/up, down, output); b200_gemv4_kernel<q4_0,1,4> (wo)",
                          "note": "algorithmic MUL_MAT bytes of the step / device time of the whole step; per launch: %d B avg" % (alg // wl.n_mulmat)},
             "gpu_launches": int(launches), "clocks": clocks, "logits_finite": bool(np.isfinite(logits).all())}
     e2e_ops = {"value": round(1.0 / e2e_s, 3), "unit": "tokens/s", "h2d_bytes_per_step": 4 * wl.h, "d2h_bytes_per_step": 4 * wl.out[1],

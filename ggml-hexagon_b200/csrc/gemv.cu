@@ -28,7 +28,7 @@ namespace b200 {
 // next slice are requested before the current one is consumed (DB = register double buffer).
 template <int TYPE, int NCOLS, int R, bool DB>
 __global__ void __launch_bounds__(512)
-gemv4_kernel(const GemvArgs a) {
+b200_gemv4_kernel(const GemvArgs a) {
     using W = WT<TYPE>;
     using A = WR<TYPE>;
     __shared__ float part[16][R * NCOLS + 1];
@@ -128,7 +128,7 @@ __device__ __forceinline__ uint32_t g5_smem(const void * p) { return (uint32_t) 
 
 template <int TYPE, int RT, int ITERS>
 __global__ void __launch_bounds__(512)
-gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
+b200_gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
     using W = WT<TYPE>;
     using A = WR<TYPE>;
     extern __shared__ __align__(128) uint8_t g5_sm[];
@@ -231,7 +231,7 @@ gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
 // HBM / L2 for every chunk of 8 columns and the activations of every column for every group of R rows.
 template <int TYPE, int RT, int ITERS, int NC>
 __global__ void __launch_bounds__(512)
-gemv5n_kernel(const GemvArgs a, const Gemv5Tile t, const int ncols) {
+b200_gemv5n_kernel(const GemvArgs a, const Gemv5Tile t, const int ncols) {
     using W = WT<TYPE>;
     using A = WR<TYPE>;
     extern __shared__ __align__(128) uint8_t g5_sm[];
@@ -349,9 +349,9 @@ static cudaError_t launch_cfg(GemvArgs & a, cudaStream_t st, bool pdl) {
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
     // the register double buffer only where it fits without spills (ptxas -v): q4_0 / q8_0, one column
     if constexpr ((TYPE == T_Q4_0 || TYPE == T_Q8_0) && NCOLS == 1) {
-        if (iters > 1) return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, true>, a);
+        if (iters > 1) return cudaLaunchKernelEx(&cfg, b200_gemv4_kernel<TYPE, NCOLS, R, true>, a);
     }
-    return cudaLaunchKernelEx(&cfg, gemv4_kernel<TYPE, NCOLS, R, false>, a);
+    return cudaLaunchKernelEx(&cfg, b200_gemv4_kernel<TYPE, NCOLS, R, false>, a);
 }
 
 // gemv5 eligibility: one column, pre-quantised activations, every field's row is a multiple of 16 bytes and 16-byte aligned
@@ -362,7 +362,7 @@ static cudaError_t launch_g5(GemvArgs & a, const Gemv5Tile & t, int nwarps, cuda
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     const int smem = t.tile_bytes + 16 * (RT + 1) * 4 + 16;
     if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemv5_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(b200_gemv5_kernel<TYPE, RT, ITERS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         smem_set[dev] = smem;
     }
@@ -374,7 +374,7 @@ static cudaError_t launch_g5(GemvArgs & a, const Gemv5Tile & t, int nwarps, cuda
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, gemv5_kernel<TYPE, RT, ITERS>, a, t);
+    return cudaLaunchKernelEx(&cfg, b200_gemv5_kernel<TYPE, RT, ITERS>, a, t);
 }
 template <int TYPE>
 static bool try_gemv5(GemvArgs & a, cudaStream_t st, bool pdl, cudaError_t * err) {
@@ -419,7 +419,7 @@ static cudaError_t launch_g5n(GemvArgs & a, const Gemv5Tile & t, int nwarps, int
     int dev = 0; cudaGetDevice(&dev); dev &= 63;
     const int smem = t.tile_bytes + 16 * (NC * RT + 1) * 4 + 16;
     if (smem > smem_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(gemv5n_kernel<TYPE, RT, ITERS, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(b200_gemv5n_kernel<TYPE, RT, ITERS, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         smem_set[dev] = smem;
     }
@@ -429,7 +429,7 @@ static cudaError_t launch_g5n(GemvArgs & a, const Gemv5Tile & t, int nwarps, int
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, gemv5n_kernel<TYPE, RT, ITERS, NC>, a, t, ncols);
+    return cudaLaunchKernelEx(&cfg, b200_gemv5n_kernel<TYPE, RT, ITERS, NC>, a, t, ncols);
 }
 template <int TYPE>
 static bool try_gemv5n(GemvArgs & a, int ncols, cudaStream_t st, bool pdl, cudaError_t * err) {

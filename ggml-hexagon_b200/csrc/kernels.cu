@@ -16,7 +16,7 @@ namespace b200 {
 // ---- f32 weights (the only MUL_MAT the cDSP path runs by default: ggml_vec_dot_f32, ggml-dsp.c:360-372).
 // One warp per (row, column); float4 loads when 16-B aligned; fp32 accumulation.
 __global__ void __launch_bounds__(128)
-gemv_f32_kernel(const char * __restrict__ w, int64_t wrs, int64_t M, int64_t K,
+b200_gemv_f32_kernel(const char * __restrict__ w, int64_t wrs, int64_t M, int64_t K,
                 const char * __restrict__ x, int64_t xcs, int ncols, float * __restrict__ dst, int64_t dcs) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t) blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -43,7 +43,7 @@ gemv_f32_kernel(const char * __restrict__ w, int64_t wrs, int64_t M, int64_t K,
 }
 cudaError_t launch_gemv_f32(const float * w, int64_t wrs, int64_t M, int64_t K, const float * x, int64_t xcs, int ncols,
                             float * dst, int64_t dcs, cudaStream_t st) {
-    gemv_f32_kernel<<<(unsigned) ((M + 3) / 4), 128, 0, st>>>((const char *) w, wrs, M, K, (const char *) x, xcs, ncols, dst, dcs);
+    b200_gemv_f32_kernel<<<(unsigned) ((M + 3) / 4), 128, 0, st>>>((const char *) w, wrs, M, K, (const char *) x, xcs, ncols, dst, dcs);
     return cudaGetLastError();
 }
 
