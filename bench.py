@@ -417,7 +417,24 @@ def time_prefill_model(B, s, wl, N=512, steps=5):
     except (OSError, KeyError, ValueError):
         pass
     pw.free()
-    return {"tokens_per_s": round(N / sec, 1), "ms": round(sec * 1e3, 3), "TFLOPS": round(flops / sec / 1e12, 1),
+    umma = {}                                  # tools/ubench_umma.cu on a B200 of this pool: back-to-back tcgen05.mma on shared-memory operands, no loads
+    try:
+        for ln in open(os.path.join(ROOT, "profiles", "r02_e_ubench_umma.jsonl")):
+            d = json.loads(ln)
+            umma[d["kind"]] = d["TOPS_best"]
+    except (OSError, ValueError, KeyError):
+        pass
+    tf = flops / sec / 1e12
+    vs_peaks = {"bf16_cublas_sustained_measured": round(tf / tc_peak, 4) if tc_peak else None,
+                "fp16_mma_issue_peak_measured": round(tf / umma["f16"], 4) if "f16" in umma else None,
+                "int8_mma_issue_peak_measured": round(tf / umma["i8"], 4) if "i8" in umma else None,
+                "fp16_nominal_2250": round(tf / 2250.0, 4), "int8_nominal_4500": round(tf / 4500.0, 4),
+                "peaks": {"fp16_mma_TFLOPS": umma.get("f16"), "int8_mma_TOPS": umma.get("i8"), "source": "profiles/r02_e_ubench_umma.jsonl (tools/ubench_umma.cu)"}}
+    try:
+        vs_peaks["bf16_cublas_burst_measured"] = round(tf / float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]), 4)
+    except (OSError, KeyError, ValueError):
+        pass
+    return {"tokens_per_s": round(N / sec, 1), "ms": round(sec * 1e3, 3), "TFLOPS": round(flops / sec / 1e12, 1), "frac_of_peaks": vs_peaks,
             "frac_of_measured_16bit_tensor_peak": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "tensor_peak_TFLOPS": tc_peak,
             "roofline": {"bound": "tensor", "achieved": round(flops / sec / 1e12, 1), "peak": tc_peak, "unit": "TFLOP/s",
                          "frac": round(flops / sec / 1e12 / tc_peak, 4) if tc_peak else None, "traffic": None,
