@@ -94,6 +94,10 @@ struct GemvArgs {
     // so far + 1); slot = ll_slots + (seq & 1) * LL_HALF_ELEMS + ll_off[mat] + ll_rank * M + row  (two halves: a rank can be at
     // most one exchange ahead of the slowest reader)
     uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_op; int ll_off[3]; int ll_rank;
+    // quantise on exit (one column, qx_qs != null): the result vector of matrix qx_mat (the fused ADD's sum if it has one, else dst; M % 32 == 0)
+    // is the next MUL_MAT's src1: the last CTA of every 32-element block collects the block through qx_slots ({value, flag} per row, all
+    // zero between launches) and writes its q8_1 form into the OTHER activation scratch qx_qs / qx_ds -- no quantise launch in front of the next GEMV
+    int8_t * qx_qs; ActDS * qx_ds; uint2 * qx_slots; int qx_mat;
 };
 constexpr int LL_HALF_ELEMS = 131072;                     // {value, seq} slots per staging half
 struct LlGatherArgs { uint2 * ll_slots; const uint32_t * ll_count; uint32_t ll_op; int nmat; float * dst[3]; int M[3]; int ll_off[3]; int world, rank; };

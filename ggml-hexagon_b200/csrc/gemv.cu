@@ -24,6 +24,45 @@
 
 namespace b200 {
 
+// Quantise on exit (GemvArgs::qx_*), called by the whole warp 0 once lane r < rows holds result v of row row0 + r (rows divides 32).
+// The CTAs that share a 32-element block of the result vector hand their values to the block's LAST CTA through {value, 1} slots
+// (one 8-byte store each, no fence, no atomic: a CTA that is not the last one leaves at once); the last CTA -- dispatched after the
+// others, which are therefore running or done -- polls the slots, clears them for the next launch, and writes the block as
+// quantize_q8_1_kernel would (quantize_row_q8_1_ref, ggml-quants.c:220-253; SoA planes of wtypes.cuh).
+__device__ __forceinline__ void gemv_quant_on_exit(const GemvArgs & a, const int m, const int64_t row0, const int rows, const float v, const int64_t M) {
+    if (!a.qx_qs || m != a.qx_mat) return;
+    const int lane = threadIdx.x & 31, off = (int) (row0 & 31);
+    const int64_t blk = row0 >> 5, NB = M >> 5;
+    uint2 * slots = a.qx_slots + blk * 32;
+    if (off != 32 - rows) {
+        if (lane < rows) asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(slots + off + lane), "r"(__float_as_uint(v)), "r"(1u) : "memory");
+        return;
+    }
+    float x = __shfl_sync(0xffffffffu, v, lane >= off ? lane - off : 0);      // this CTA's rows sit at the end of the block
+    if (lane < off) {
+        uint32_t val, flag;
+        const long long t0 = clock64();
+        do {
+            asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(val), "=r"(flag) : "l"(slots + lane) : "memory");
+            if (!flag && clock64() - t0 > 8000000000ll) __trap();
+        } while (!flag);
+        asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(slots + lane), "r"(0u), "r"(0u) : "memory");
+        x = __uint_as_float(val);
+    }
+    float amax = fabsf(x);
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const int q = (int) roundf(__fmul_rn(x, id));
+    int sum = q;
+    #pragma unroll
+    for (int o = 8; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);      // lanes 0-15: plane 0, lanes 16-31: plane 1
+    const int other = __shfl_xor_sync(0xffffffffu, sum, 16);
+    a.qx_qs[((int64_t) (lane >> 4) * NB + blk) * 16 + (lane & 15)] = (int8_t) q;
+    if (lane == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; a.qx_ds[blk] = o; }
+}
+
 // ITERS > 1: the row has more than 32*nwarps steps; warp w then owns slices w, w+nwarps, ... and the fragments of the
 // next slice are requested before the current one is consumed (DB = register double buffer).
 template <int TYPE, int NCOLS, int R, bool DB>
@@ -92,7 +131,9 @@ b200_gemv4_kernel(const GemvArgs a) {
         if ((lane & ((1 << SH) - 1)) == 0) part[warp][c * R + (lane >> SH)] = v;
     }
     __syncthreads();
-    if (tid < R * NCOLS) {
+    if (warp == 0) {
+      float qv = 0.f;
+      if (tid < R * NCOLS) {
         float v = 0.f;
         for (int q = 0; q < nwarps; q++) v += part[q][tid];
         const int c = tid / R, r = tid - c * R;
@@ -101,6 +142,7 @@ b200_gemv4_kernel(const GemvArgs a) {
             mt.dst[o] = v;
             float s = 0.f;
             if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
+            qv = mt.add_dst ? s : v;
             if (a.ll_slots) {                                 // row split, LL protocol: {value, seq} in one 8-byte NVLink store per peer
                 const uint32_t seq = *a.ll_count + a.ll_op;
                 const uint2 * slot = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + a.ll_off[m] + (int64_t) a.ll_rank * M + row0 + r;
@@ -112,6 +154,8 @@ b200_gemv4_kernel(const GemvArgs a) {
                 if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
             }
         }
+      }
+      if (NCOLS == 1) gemv_quant_on_exit(a, m, row0, R, qv, M);
     }
 }
 
@@ -201,7 +245,9 @@ b200_gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
         if ((lane & ((1 << SH) - 1)) == 0) part[warp][lane >> SH] = v;
     }
     __syncthreads();
-    if (tid < RT) {
+    if (warp == 0) {
+      float qv = 0.f;
+      if (tid < RT) {
         float v = 0.f;
         for (int q = 0; q < nwarps; q++) v += part[q][tid];
         const int r = tid;
@@ -210,6 +256,7 @@ b200_gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
             mt.dst[o] = v;
             float s = 0.f;
             if (mt.add_dst) { s = mt.add_src[o] + v; mt.add_dst[o] = s; }
+            qv = mt.add_dst ? s : v;
             if (a.ll_slots) {
                 const uint32_t seq = *a.ll_count + a.ll_op;
                 const uint2 * slot = a.ll_slots + (size_t) (seq & 1u) * LL_HALF_ELEMS + a.ll_off[m] + (int64_t) a.ll_rank * M + row0 + r;
@@ -221,6 +268,8 @@ b200_gemv5_kernel(const GemvArgs a, const Gemv5Tile t) {
                 if (mt.add_dst) *(float *) ((char *) (mt.add_dst + o) + a.peer_delta[pi]) = s;
             }
         }
+      }
+      gemv_quant_on_exit(a, m, row0, RT, qv, M);
     }
 }
 

@@ -70,6 +70,9 @@ struct Ctx {
     cudaStream_t st = nullptr;
     // q8_1 activation scratch (two-plane SoA), capacity in 32-element blocks
     int8_t * act_qs = nullptr; ActDS * act_ds = nullptr; int64_t act_cap = 0;
+    // quantise on exit: the GEMV writes the NEXT op's q8_1 activations into the second scratch, which then becomes act_qs / act_ds (pointer swap)
+    int8_t * act_qs2 = nullptr; ActDS * act_ds2 = nullptr; uint2 * qx_slots = nullptr;
+    struct { bool on = false, done = false; const void * vec = nullptr; } qx_hint;
     // device staging (host tensors, repack)
     uint8_t * stage = nullptr; size_t stage_cap = 0;
     uint8_t * flush = nullptr; size_t flush_bytes = 0;
@@ -108,12 +111,19 @@ static Ctx * ctx_of(b200_handle h) {
 #define CTX(h) Ctx * c = ctx_of(h); if (!c) return fail(B200_EINVAL, "bad handle"); \
     { cudaError_t e_ = cudaSetDevice(c->dev); if (e_ != cudaSuccess) return fail(B200_ECUDA, "cudaSetDevice: %s", cudaGetErrorString(e_)); }
 
+constexpr int64_t QX_MAX_BLOCKS = 8192;            // 32-element blocks of a result vector that can be quantised on exit (262144 rows)
 static int ensure_act(Ctx * c, int64_t blocks) {
     if (blocks <= c->act_cap) return 0;
-    if (c->act_qs) { CU(cudaStreamSynchronize(c->st)); cudaFree(c->act_qs); cudaFree(c->act_ds); c->act_qs = nullptr; c->act_ds = nullptr; c->act_cap = 0; }
+    if (c->act_qs) {
+        CU(cudaStreamSynchronize(c->st)); cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->act_qs2); cudaFree(c->act_ds2);
+        c->act_qs = c->act_qs2 = nullptr; c->act_ds = c->act_ds2 = nullptr; c->act_cap = 0;
+    }
     int64_t cap = blocks < 4096 ? 4096 : blocks;
     CU(cudaMalloc((void **) &c->act_qs, (size_t) cap * 32));
     CU(cudaMalloc((void **) &c->act_ds, (size_t) cap * sizeof(ActDS)));
+    CU(cudaMalloc((void **) &c->act_qs2, (size_t) cap * 32));
+    CU(cudaMalloc((void **) &c->act_ds2, (size_t) cap * sizeof(ActDS)));
+    if (!c->qx_slots) { CU(cudaMalloc((void **) &c->qx_slots, QX_MAX_BLOCKS * 32 * sizeof(uint2))); CU(cudaMemsetAsync(c->qx_slots, 0, QX_MAX_BLOCKS * 32 * sizeof(uint2), c->st)); }
     c->act_cap = cap;
     c->q_ptr = nullptr;
     c->scratch_gen++;
@@ -193,7 +203,7 @@ extern "C" int b200_close(b200_handle h) {
     for (int r = 0; r < 8; r++) if (c->rs_ipc[r] && c->rs_peer[r]) cudaIpcCloseMemHandle(c->rs_peer[r]);
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->stage); cudaFree(c->flush);
+    cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->act_qs2); cudaFree(c->act_ds2); cudaFree(c->qx_slots); cudaFree(c->stage); cudaFree(c->flush);
     cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp); cudaFree(c->gm_tail);
     cudaStreamDestroy(c->st);
     c->magic = 0;
@@ -449,6 +459,25 @@ static int rs_fill(Ctx * c, GemvArgs & a, const void * const * dsts, const int64
 // dense GEMM activations in gm_qb: fp16 [N][K], then (256-byte aligned) the column scales, N rounded up to 256 floats
 static size_t dense_act_cs_off(int64_t N, int64_t K) { return ((size_t) N * K * 2 + 255) & ~(size_t) 255; }
 static size_t dense_act_bytes(int64_t N, int64_t K) { return dense_act_cs_off(N, K) + (size_t) ((N + 255) & ~(int64_t) 255) * sizeof(float); }
+static bool qx_enabled() { return !(getenv("B200_QX") && atoi(getenv("B200_QX")) == 0); }      // (read per submission: the tests switch it)
+// quantise on exit: if run_nodes announced that the result vector `qx_hint.vec` feeds the next MUL_MAT, let the GEMV that produces it
+// write its q8_1 form into the second scratch (one column, M % 32 == 0, no row split)
+static void qx_arm(Ctx * c, GemvArgs & a) {
+    a.qx_qs = nullptr;
+    if (!c->qx_hint.on || c->rs_on || !c->act_qs2) return;
+    for (int m = 0; m < a.nmat; m++) {
+        const float * v = a.mat[m].add_dst ? a.mat[m].add_dst : a.mat[m].dst;
+        if ((const void *) v == c->qx_hint.vec && a.mat[m].M % 32 == 0 && a.mat[m].M / 32 <= QX_MAX_BLOCKS && a.mat[m].M / 32 <= c->act_cap) {
+            a.qx_qs = c->act_qs2; a.qx_ds = c->act_ds2; a.qx_slots = c->qx_slots; a.qx_mat = m;
+            return;
+        }
+    }
+}
+static void qx_launched(Ctx * c, const GemvArgs & a) {      // the armed GEMV is in the stream: the second scratch is the current one from here on
+    if (!a.qx_qs) return;
+    std::swap(c->act_qs, c->act_qs2); std::swap(c->act_ds, c->act_ds2);
+    c->qx_hint.done = true;
+}
 static bool rs_fuse_enabled() { static const bool on = !(getenv("B200_RS_FUSE") && atoi(getenv("B200_RS_FUSE")) == 0); return on; }
 static bool act_fusion_enabled() { static const bool on = !(getenv("B200_GEMM_ACTFUSE") && atoi(getenv("B200_GEMM_ACTFUSE")) == 0); return on; }
 static int rs_exchange(Ctx * c) {
@@ -669,7 +698,9 @@ static int mulmat_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b
                     const int nc = (int) (N - c0 < 8 ? N - c0 : 8);
                     a.act = ActView{c->act_qs + c0 * NB * 32, c->act_ds + c0 * NB, NB};
                     a.mat[0].dst = y + c0 * dcs;
+                    if (N == 1) qx_arm(c, a);
                     CU(launch_gemv2(s0->type, a, nc, c->st)); c->launches++;
+                    if (N == 1) qx_launched(c, a);
                 }
             }
         } else {
@@ -842,7 +873,9 @@ static int mulmat_group_dev(Ctx * c, const b200_node * nodes, int len) {
         c->q_ptr = x; c->q_K = K; c->q_N = 1; c->q_stride = nodes[0].src1.nb[1]; c->q_kind = 0;
     }
     a.act = ActView{c->act_qs, c->act_ds, NB};
+    qx_arm(c, a);
     CU(launch_gemv2(nodes[0].src0.type, a, 1, c->st)); c->launches++;
+    qx_launched(c, a);
     { int rc2 = rs_exchange(c); if (rc2) return rc2; }
     for (int j = 0; j < len; j++)
         if (c->q_ptr && overlap(nodes[j].dst.data, nodes[j].src0.ne[1] * 4, c->q_ptr, K * 4)) c->q_ptr = nullptr;
@@ -946,6 +979,23 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                     if (c->rs_hint.on) { rc = ensure_act(c, nx->src0.ne[0] / 32); if (rc) break; }
                 }
                 const int dgl = fuse && gl == 1 ? dense_group_len(c, nodes, i, n) : 1;
+                // one GPU: which result vector of this op (a member's dst, or the sum of the ADD fused into it) is the next vector MUL_MAT's src1?
+                // The GEMV then quantises it on exit (gemv.cu, gemv_quant_on_exit) and that MUL_MAT finds its activations cached.
+                c->qx_hint.on = false; c->qx_hint.done = false;
+                const b200_node * qx_next = nullptr;
+                if (fuse && qx_enabled() && !c->rs_on && is_vec_mulmat(nodes[i])) {
+                    FusedAdd fq;
+                    const bool add_fused = gl == 1 && i + 1 < n && can_fuse_add(nodes[i], nodes[i + 1], &fq);
+                    const int j = i + (gl > 1 ? gl : (add_fused ? 2 : 1));
+                    if (j < n && is_vec_mulmat(nodes[j]) && nodes[j].src1.nb[0] == 4) {
+                        const void * want = nodes[j].src1.data;
+                        const int64_t Kn = nodes[j].src0.ne[0];
+                        if (add_fused) { if ((const void *) fq.dst == want && nodes[i].src0.ne[1] == Kn) c->qx_hint.on = true; }
+                        else for (int mbr = 0; mbr < gl; mbr++) if (nodes[i + mbr].dst.data == want && nodes[i + mbr].src0.ne[1] == Kn && is_vec_f32(nodes[i + mbr].dst, Kn)) c->qx_hint.on = true;
+                        if (c->qx_hint.on && Kn % 32 == 0) { c->qx_hint.vec = want; qx_next = &nodes[j]; rc = ensure_act(c, Kn / 32); if (rc) break; }
+                        else c->qx_hint.on = false;
+                    }
+                }
                 if (gl > 1) { rc = mulmat_group_dev(c, nodes + i, gl); used = gl; }
                 else if (dgl > 1) { rc = mulmat_dense_group_dev(c, nodes + i, dgl); used = dgl; }
                 else if (fuse && i + 1 < n && can_fuse_add_dense(c, nodes[i], nodes[i + 1], &fa)) { rc = mulmat_dev(c, &nodes[i].src0, &nodes[i].src1, &d, 0, &fa); used = 2; }
@@ -962,6 +1012,10 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                     if (skip_add) used++;
                 }
                 c->rs_hint.on = false; c->rs_hint.done = false;
+                if (!rc && c->qx_hint.on && c->qx_hint.done) {       // the GEMV left the next op's q8_1 activations in (what is now) act_qs / act_ds
+                    c->q_ptr = qx_next->src1.data; c->q_K = qx_next->src0.ne[0]; c->q_N = 1; c->q_stride = qx_next->src1.nb[1]; c->q_kind = 0;
+                }
+                c->qx_hint.on = false; c->qx_hint.done = false;
                 break;
             }
             default: rc = fail(B200_ENOTSUP, "graph node %d: op %d not offloaded", i, d.op);

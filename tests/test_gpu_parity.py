@@ -286,3 +286,64 @@ def test_small_batch_columns(monkeypatch, t, M, K, N):
         assert nmse(got, O.mul_mat(t, raw, x, 1)) <= 1e-9
         assert nmse(got, one) <= 1e-12
         w.free()
+
+
+# ------------------------------------------------------------------ quantise on exit (decode chains without quantise launches)
+def _chain_nodes(ws, x, bufs, K, Ms):
+    """wq / wk / wv over x (group) -> wo(q) + x (ADD fused into the GEMV) -> gate / up over the sum (group) -> down(gate) + sum -> out(sum2)"""
+    def mm(w, src, dst, M):
+        n = B.Node()
+        n.src0, n.src1, n.dst = w.tensor(), B.f32_tensor(src.ptr, [w.K, 1]), B.f32_tensor(dst.ptr, [M, 1], op=B.OP_MUL_MAT)
+        return n
+
+    def add(a, b, d, M):
+        n = B.Node()
+        n.src0, n.src1, n.dst = B.f32_tensor(a.ptr, [M]), B.f32_tensor(b.ptr, [M]), B.f32_tensor(d.ptr, [M], op=B.OP_ADD)
+        return n
+    q, k, v, o, h, g, u, dn, h2, out = bufs
+    return [mm(ws[0], x, q, Ms[0]), mm(ws[1], x, k, Ms[1]), mm(ws[2], x, v, Ms[2]), mm(ws[3], q, o, Ms[3]), add(x, o, h, K),
+            mm(ws[4], h, g, Ms[4]), mm(ws[5], h, u, Ms[5]), mm(ws[6], g, dn, Ms[6]), add(h, dn, h2, K), mm(ws[7], h2, out, Ms[7])]
+
+
+@pytest.mark.parametrize("K,F", [(2048, 5504), (4096, 11008), (1024, 1056)])
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q8_0, O.Q4_K, O.Q6_K])
+def test_quantise_on_exit_chain(monkeypatch, t, K, F):
+    """a decoder-layer-shaped node list: every MUL_MAT but the first finds its q8_1 activations written by the GEMV in front of it
+    (gemv_quant_on_exit): same bits as with the quantise launches (B200_QX=0), fewer launches, and on the oracle; gemv4 and gemv5
+    tiles, groups of 3 and 2, fused ADDs, CUDA graph replay"""
+    if t in (O.Q4_K, O.Q6_K) and (K % 256 or F % 256):
+        pytest.skip("K-quants want multiples of 256")
+    monkeypatch.setenv("B200_GEMV6", "0")
+    rng = np.random.default_rng(77 + t + K)
+    Ms = [K, K // 4, K // 4, K, F, F, K, 1000]
+    Ks = [K, K, K, K, K, K, F, K]
+    raws = [O.random_blocks(t, m, k, rng, 0.05) for m, k in zip(Ms, Ks)]
+    x = rng.uniform(-1, 1, (1, K)).astype(np.float32)
+    with B.Session(0) as s:
+        ws = [s.weights(t, r, k) for r, k in zip(raws, Ks)]
+        xb = s.to_device(x)
+        sizes = [K, K // 4, K // 4, K, K, F, F, K, K, 1000]
+        bufs = [s.malloc(4 * n) for n in sizes]
+        nodes = _chain_nodes(ws, xb, bufs, K, Ms)
+        res = {}
+        for qx in ("0", "1"):
+            monkeypatch.setenv("B200_QX", qx)
+            for b, n in zip(bufs, sizes):
+                s.h2d(b, np.zeros(n, np.float32))
+            l0 = s.launch_count()
+            s.graph_compute(nodes, use_cuda_graph=False)
+            s.sync()
+            res[qx] = ([s.to_host(b, (n,), np.float32) for b, n in zip(bufs, sizes)], s.launch_count() - l0)
+        (plain, l_plain), (fused, l_fused) = res["0"], res["1"]
+        for a, b in zip(plain, fused):
+            assert np.array_equal(a, b)
+        assert l_plain == 5 + 5 and l_fused == 5 + 1, (l_plain, l_fused)      # 5 GEMV launches (q/k/v, wo + ADD, gate/up, down + ADD, out), each behind a quantise launch / only the first
+        for _ in range(3):                                                      # capture + replays
+            s.graph_compute(nodes, use_cuda_graph=2)
+        s.sync()
+        for a, b, n in zip(fused, bufs, sizes):
+            assert np.array_equal(a, s.to_host(b, (n,), np.float32))
+        mm = lambda i, v: O.mul_mat(t, raws[i], v.reshape(1, -1), 1).reshape(-1)
+        q = mm(0, x); o = mm(3, q); h = x.reshape(-1) + o; g = mm(4, h); dn = mm(6, g); h2 = h + dn
+        for got, ref in ((fused[0], q), (fused[3], o), (fused[4], h), (fused[5], g), (fused[7], dn), (fused[8], h2), (fused[9], mm(7, h2))):
+            assert nmse(got, ref) <= 1e-6      # (a chain: every op quantises an input that differs in the last bits from the oracle's own chain)
