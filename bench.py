@@ -700,8 +700,23 @@ def run_b200(args, rank, world):
     for _ in range(max(args.warmup, 3)):
         wl.step()
     barrier()
+    # clocks: nvidia-smi needs ~0.1 s per sample and the timed region is K milliseconds, so the same steps keep running without a gap
+    # before and after it (0.6 s each, untimed) while the sampler runs: the samples are of this workload under load, timed region included
     sampler = ClockSampler(local)
     sampler.start()
+
+    def roll(seconds):
+        if world > 1:                              # row split: every rank must run the same number of steps (they meet in every exchange)
+            for _ in range(150):
+                wl.step()
+            s.sync()
+            return
+        t_end = time.perf_counter() + seconds
+        while time.perf_counter() < t_end:
+            for _ in range(20):
+                wl.step()
+            s.sync()
+    roll(0.6)
     l0 = s.launch_count()
     e0, e1 = s.event(), s.event()
     s.record(e0)
@@ -710,6 +725,7 @@ def run_b200(args, rank, world):
     s.record(e1)
     ms = s.elapsed_ms(e0, e1)
     launches = s.launch_count() - l0
+    roll(0.6)
     barrier()
     if dist is not None:
         import torch

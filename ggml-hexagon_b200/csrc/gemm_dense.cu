@@ -252,6 +252,13 @@ __device__ __forceinline__ uint2 gd_u8x4_f(uint32_t w, float ds, float ms) {
     const float f2 = __fmaf_rn(ds, (float) ((w >> 16) & 0xFFu), -ms), f3 = __fmaf_rn(ds, (float) (w >> 24), -ms);
     return make_uint2(gd_pack_h2f(f0, f1), gd_pack_h2f(f2, f3));
 }
+__device__ __forceinline__ uint32_t gd_h2fma(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+// 4 bytes of w (values 0 .. 255) -> 4 halfs v * ds2 + nms2 (v exact in fp16, one rounding in the FMA; ds2 / nms2 = the f32 scale and negated
+// minimum rounded to fp16 once per sub-block): the K-quants' packed path, ~2.3x fewer instructions than I2F + FFMA + cvt per element
+__device__ __forceinline__ uint2 gd_u8x4_hf(uint32_t w, uint32_t ds2, uint32_t nms2) {
+    const uint32_t lo = gd_prmt(w, 0x64646464u, 0x5140u), hi = gd_prmt(w, 0x64646464u, 0x5342u);
+    return make_uint2(gd_h2fma(gd_h2sub(lo, 0x64006400u), ds2, nms2), gd_h2fma(gd_h2sub(hi, 0x64006400u), ds2, nms2));
+}
 struct GdRaw { uint4 a, b, c, e; uint32_t s0, s1; float fs; };      // fs: K-quant row scale (power of two)      // one slab's native bytes of a thread (unused members cost nothing)
 __device__ __forceinline__ void gd_cpa16(uint32_t dst, const void * src) { asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory"); }
 __device__ __forceinline__ void gd_cpa4(uint32_t dst, const void * src)  { asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory"); }
@@ -318,10 +325,11 @@ template <> struct GdCvt<T_Q4_K> {
         if (g < 4) { sc = byte(g) & 63u; mn = byte(g + 4) & 63u; }
         else       { sc = (byte(g + 4) & 0xFu) | ((byte(g - 4) >> 6) << 4); mn = (byte(g + 4) >> 4) | ((byte(g) >> 6) << 4); }
         const __half2 dd = *(const __half2 *) &r.c.x;
-        const float ds = __fmul_rn(__low2float(dd), (float) sc) * r.fs, ms = __fmul_rn(__high2float(dd), (float) mn) * r.fs;
+        const float dsf = __fmul_rn(__low2float(dd), (float) sc) * r.fs, msf = __fmul_rn(__high2float(dd), (float) mn) * r.fs;
+        const uint32_t ds = gd_pack_h2f(dsf, dsf), ms = gd_pack_h2f(-msf, -msf);
         const uint32_t m = 0x0F0F0F0Fu; const int sh = hk * 4;
-        const uint2 a = gd_u8x4_f((r.a.x >> sh) & m, ds, ms), b = gd_u8x4_f((r.a.y >> sh) & m, ds, ms), c = gd_u8x4_f((r.a.z >> sh) & m, ds, ms), d = gd_u8x4_f((r.a.w >> sh) & m, ds, ms);
-        const uint2 e = gd_u8x4_f((r.b.x >> sh) & m, ds, ms), f = gd_u8x4_f((r.b.y >> sh) & m, ds, ms), gg = gd_u8x4_f((r.b.z >> sh) & m, ds, ms), h = gd_u8x4_f((r.b.w >> sh) & m, ds, ms);
+        const uint2 a = gd_u8x4_hf((r.a.x >> sh) & m, ds, ms), b = gd_u8x4_hf((r.a.y >> sh) & m, ds, ms), c = gd_u8x4_hf((r.a.z >> sh) & m, ds, ms), d = gd_u8x4_hf((r.a.w >> sh) & m, ds, ms);
+        const uint2 e = gd_u8x4_hf((r.b.x >> sh) & m, ds, ms), f = gd_u8x4_hf((r.b.y >> sh) & m, ds, ms), gg = gd_u8x4_hf((r.b.z >> sh) & m, ds, ms), h = gd_u8x4_hf((r.b.w >> sh) & m, ds, ms);
         o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(c.x, c.y, d.x, d.y);
         o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(gg.x, gg.y, h.x, h.y);
     }
@@ -350,10 +358,10 @@ template <> struct GdCvt<T_Q6_K> {
         const uint32_t m = 0x0F0F0F0Fu, m3 = 0x03030303u;
         auto q = [&](uint32_t l, uint32_t hh) { return ((l >> ns) & m) | (((hh >> sh) & m3) << 4); };
         const float d = __half2float(__ushort_as_half((unsigned short) r.s1)) * r.fs;
-        const float d0 = __fmul_rn(d, (float) (int8_t) (r.s0 & 0xFF)), d1 = __fmul_rn(d, (float) (int8_t) ((r.s0 >> 8) & 0xFF));
-        const float m0 = d0 * 32.f, m1 = d1 * 32.f;                      // (exact: power of two)
-        const uint2 a = gd_u8x4_f(q(r.a.x, r.c.x), d0, m0), b = gd_u8x4_f(q(r.a.y, r.c.y), d0, m0), cc = gd_u8x4_f(q(r.a.z, r.c.z), d0, m0), dd = gd_u8x4_f(q(r.a.w, r.c.w), d0, m0);
-        const uint2 e = gd_u8x4_f(q(r.b.x, r.e.x), d1, m1), f = gd_u8x4_f(q(r.b.y, r.e.y), d1, m1), g = gd_u8x4_f(q(r.b.z, r.e.z), d1, m1), h = gd_u8x4_f(q(r.b.w, r.e.w), d1, m1);
+        const float d0f = __fmul_rn(d, (float) (int8_t) (r.s0 & 0xFF)), d1f = __fmul_rn(d, (float) (int8_t) ((r.s0 >> 8) & 0xFF));
+        const uint32_t d0 = gd_pack_h2f(d0f, d0f), d1 = gd_pack_h2f(d1f, d1f), bias = 0x64206420u;      // 1056 = 1024 + 32: (q - 32) exact, then one rounding multiply
+        const uint2 a = gd_u8x4_h(q(r.a.x, r.c.x), bias, d0), b = gd_u8x4_h(q(r.a.y, r.c.y), bias, d0), cc = gd_u8x4_h(q(r.a.z, r.c.z), bias, d0), dd = gd_u8x4_h(q(r.a.w, r.c.w), bias, d0);
+        const uint2 e = gd_u8x4_h(q(r.b.x, r.e.x), bias, d1), f = gd_u8x4_h(q(r.b.y, r.e.y), bias, d1), g = gd_u8x4_h(q(r.b.z, r.e.z), bias, d1), h = gd_u8x4_h(q(r.b.w, r.e.w), bias, d1);
         o[0] = make_uint4(a.x, a.y, b.x, b.y); o[1] = make_uint4(cc.x, cc.y, dd.x, dd.y);
         o[2] = make_uint4(e.x, e.y, f.x, f.y); o[3] = make_uint4(g.x, g.y, h.x, h.y);
     }
