@@ -64,6 +64,7 @@ static int nccl_load() {
 // ------------------------------------------------------------------------------------------------ context
 struct GraphEntry { cudaGraphExec_t exec = nullptr; int64_t n_kernels = 0; int32_t n_nodes = 0; uint64_t check = 0; /* second, independent hash of the node list */ };
 
+constexpr int PIN_SLOTS = 8; constexpr size_t PIN_SLOT_BYTES = 256 * 1024;
 struct Ctx {
     uint64_t magic = 0xB200B200B200B200ull;
     int dev = 0;
@@ -71,6 +72,10 @@ struct Ctx {
     // q8_1 activation scratch (two-plane SoA), capacity in 32-element blocks
     int8_t * act_qs = nullptr; ActDS * act_ds = nullptr; int64_t act_cap = 0;
     // quantise on exit: the GEMV writes the NEXT op's q8_1 activations into the second scratch, which then becomes act_qs / act_ds (pointer swap)
+    // pinned bounce slots for small synchronous copies from / to pageable host memory (b200_memcpy_h2d / _d2h): a pageable cudaMemcpyAsync is
+    // staged by the driver and then waited for; through our own pinned slot an upload returns at once (the slot owns the bytes) and a
+    // download is one DMA + one memcpy
+    uint8_t * pin = nullptr; cudaEvent_t pin_ev[PIN_SLOTS] = {}; int pin_next = 0;
     int8_t * act_qs2 = nullptr; ActDS * act_ds2 = nullptr; uint2 * qx_slots = nullptr;
     struct { bool on = false, done = false; const void * vec = nullptr; } qx_hint;
     // device staging (host tensors, repack)
@@ -204,6 +209,7 @@ extern "C" int b200_close(b200_handle h) {
     cudaFree(c->rs_heap);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->act_qs2); cudaFree(c->act_ds2); cudaFree(c->qx_slots); cudaFree(c->stage); cudaFree(c->flush);
+    if (c->pin) { cudaFreeHost(c->pin); for (int i = 0; i < PIN_SLOTS; i++) if (c->pin_ev[i]) cudaEventDestroy(c->pin_ev[i]); }
     cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp); cudaFree(c->gm_tail);
     cudaStreamDestroy(c->st);
     c->magic = 0;
@@ -236,11 +242,41 @@ extern "C" int b200_free(b200_handle h, void * ptr) {
     CTX(h);
     CU(cudaStreamSynchronize(c->st)); CU(cudaFree(ptr)); return 0;
 }
+static int pin_slot(Ctx * c, uint8_t ** slot, cudaEvent_t * ev) {
+    if (!c->pin) {
+        CU(cudaMallocHost((void **) &c->pin, PIN_SLOTS * PIN_SLOT_BYTES));
+        for (int i = 0; i < PIN_SLOTS; i++) CU(cudaEventCreateWithFlags(&c->pin_ev[i], cudaEventDisableTiming));
+    }
+    const int i = c->pin_next; c->pin_next = (i + 1) % PIN_SLOTS;
+    CU(cudaEventSynchronize(c->pin_ev[i]));          // (the copy that last used the slot; long done unless 8 uploads are in flight)
+    *slot = c->pin + (size_t) i * PIN_SLOT_BYTES; *ev = c->pin_ev[i];
+    return 0;
+}
+static bool capturing(Ctx * c) { cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone; cudaStreamIsCapturing(c->st, &st); return st != cudaStreamCaptureStatusNone; }
 extern "C" int b200_memcpy_h2d(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+    CTX(h); c->q_ptr = nullptr;
+    if (n > 0 && n <= PIN_SLOT_BYTES && !capturing(c)) {          // small: through a pinned slot, no wait (later work on the stream sees it in order)
+        uint8_t * slot; cudaEvent_t ev;
+        int rc = pin_slot(c, &slot, &ev); if (rc) return rc;
+        memcpy(slot, s, n);
+        CU(cudaMemcpyAsync(d, slot, n, cudaMemcpyHostToDevice, c->st));
+        CU(cudaEventRecord(ev, c->st));
+        return 0;
+    }
+    CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_d2h(b200_handle h, void * d, const void * s, size_t n) {
-    CTX(h); CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
+    CTX(h);
+    if (n > 0 && n <= PIN_SLOT_BYTES && !capturing(c)) {
+        uint8_t * slot; cudaEvent_t ev;
+        int rc = pin_slot(c, &slot, &ev); if (rc) return rc;
+        CU(cudaMemcpyAsync(slot, s, n, cudaMemcpyDeviceToHost, c->st));
+        CU(cudaEventRecord(ev, c->st));
+        CU(cudaEventSynchronize(ev));
+        memcpy(d, slot, n);
+        return 0;
+    }
+    CU(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, c->st)); CU(cudaStreamSynchronize(c->st)); return 0;
 }
 extern "C" int b200_memcpy_h2d_async(b200_handle h, void * d, const void * s, size_t n) {
     CTX(h); c->q_ptr = nullptr; CU(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, c->st)); return 0;

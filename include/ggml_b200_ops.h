@@ -147,6 +147,9 @@ B200_API int b200_block_dots(b200_handle h, const b200_tensor * w_row, const int
  *      ggml-backend-impl.h:17-58; ggml-hexagon.cpp:5361-5478) */
 B200_API int b200_malloc(b200_handle h, size_t size, void ** ptr);
 B200_API int b200_free(b200_handle h, void * ptr);
+/* h2d returns when src_host may be reused; the bytes are in place for everything submitted to the session afterwards (up to 256 KB travel
+ * through a pinned slot of the session and are NOT waited for: call b200_synchronize before touching dst_dev from another stream).
+ * d2h returns when dst_host holds the bytes. */
 B200_API int b200_memcpy_h2d(b200_handle h, void * dst_dev, const void * src_host, size_t n);
 B200_API int b200_memcpy_d2h(b200_handle h, void * dst_host, const void * src_dev, size_t n);
 B200_API int b200_memcpy_d2d(b200_handle h, void * dst_dev, const void * src_dev, size_t n);

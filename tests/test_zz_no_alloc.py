@@ -81,6 +81,7 @@ def test_noalloc_refuses_what_does_not_fit():
             s.mulmat_noalloc(w, xb, db, N)
         n_ok = SCRATCH // per_col - 1                         # just inside the limit: runs
         s.h2d(xb, rng.uniform(-1, 1, (N, K)).astype(np.float32))
+        s.sync()                                                  # (the session's stream and the default stream are not ordered)
         s.mulmat_noalloc(w, xb, db, n_ok)
         assert C.CDLL("libcudart.so.12").cudaDeviceSynchronize() == 0
         got = s.to_host(db, (N, M), np.float32)[:n_ok]
