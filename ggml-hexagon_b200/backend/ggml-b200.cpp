@@ -50,6 +50,9 @@ struct b200_graph_entry {
     std::vector<b200_node> nodes;
     uint64_t               key = 0;
     uint64_t               last_use = 0;
+    std::vector<std::pair<int, int>> dyn;   // (index in nodes, index in the cgraph) of the nodes flagged B200_TENSOR_DYNAMIC
+    uint32_t               seen = 0;        // calls with this fingerprint: a CUDA graph is captured from the second one on, so node lists that
+                                            // change every call (a decode step whose KV-cache views move with the position) are launched directly
 };
 struct b200_backend_ctx {
     b200_device_ctx * dev = nullptr;
@@ -108,6 +111,11 @@ static bool b200_supports_mul_mat(const ggml_tensor * op) {
     const ggml_tensor * a = op->src[0]; const ggml_tensor * b = op->src[1];
     if (!a || !b) return false;
     if (b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+    if (a->type == GGML_TYPE_F16) {          // attention: K / V cache views (graph_ops.cu); K contiguous on both sides, other strides free
+        if (a->nb[0] != sizeof(ggml_fp16_t) || b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
+        if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
+        return b->ne[2] * b->ne[3] <= 65535;
+    }
     if (!(a->type == GGML_TYPE_F32 || is_qweight(a->type))) return false;
     if (b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
     if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
@@ -152,6 +160,35 @@ static bool b200_supports_pool_2d(const ggml_tensor * op) {
     if (o[0] != GGML_OP_POOL_MAX && o[0] != GGML_OP_POOL_AVG) return false;
     return a->nb[0] == ggml_type_size(a->type) && a->nb[3] == a->nb[2] * (size_t) a->ne[2];
 }
+// The ops between the MUL_MATs of a Llama layer (graph_ops.cu), admitted in the layouts llama.cpp's graphs use; everything else stays
+// with ggml-cpu.  With B200_GRAPH_OPS=0 the admission is the cDSP table's and nothing more.
+static bool graph_ops_enabled(void) { static const bool on = !(getenv("B200_GRAPH_OPS") && atoi(getenv("B200_GRAPH_OPS")) == 0); return on; }
+static bool f32_or_f16(enum ggml_type t) { return t == GGML_TYPE_F32 || t == GGML_TYPE_F16; }
+static bool b200_supports_graph_op(const ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0]; const ggml_tensor * b = op->src[1];
+    if (!graph_ops_enabled() || !a) return false;
+    switch (op->op) {
+        case GGML_OP_MUL:
+            return b && a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ggml_are_same_shape(a, op) && ggml_can_repeat(b, a);
+        case GGML_OP_UNARY:
+            return ggml_get_unary_op(op) == GGML_UNARY_OP_SILU && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+                   ggml_is_contiguous(a) && ggml_is_contiguous(op) && ggml_are_same_shape(a, op);
+        case GGML_OP_ROPE: {
+            if (!b || op->src[2] || a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || b->type != GGML_TYPE_I32) return false;
+            const int mode = op->op_params[2], n_dims = op->op_params[1];
+            if (mode != 0 && mode != GGML_ROPE_TYPE_NEOX) return false;
+            if (n_dims <= 0 || n_dims % 2 || n_dims > a->ne[0] || a->ne[0] % 2) return false;
+            return a->nb[0] == sizeof(float) && op->nb[0] == sizeof(float) && ggml_are_same_shape(a, op) && b->ne[0] >= a->ne[2] && b->nb[0] == sizeof(int32_t);
+        }
+        case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT:
+            return f32_or_f16(a->type) && f32_or_f16(op->type) && ggml_nelements(a) == ggml_nelements(op);
+        case GGML_OP_GET_ROWS:
+            return b && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && b->type == GGML_TYPE_I32 && a->nb[0] == sizeof(float) &&
+                   op->nb[0] == sizeof(float) && b->nb[0] == sizeof(int32_t) && b->ne[3] == 1 && a->ne[2] == b->ne[1] && a->ne[3] == b->ne[2];
+        default:
+            return false;
+    }
+}
 static bool b200_device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
     switch (op->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
@@ -161,7 +198,7 @@ static bool b200_device_supports_op(ggml_backend_dev_t, const ggml_tensor * op) 
         case GGML_OP_RMS_NORM: return b200_supports_rms_norm(op);
         case GGML_OP_SOFT_MAX: return b200_supports_soft_max(op);
         case GGML_OP_POOL_2D:  return b200_supports_pool_2d(op);
-        default:               return false;
+        default:               return b200_supports_graph_op(op);
     }
 }
 
@@ -297,6 +334,13 @@ static int b200_op_of(const ggml_tensor * node) {
         case GGML_OP_RMS_NORM: return B200_OP_RMS_NORM;
         case GGML_OP_SOFT_MAX: return B200_OP_SOFT_MAX;
         case GGML_OP_POOL_2D:  return B200_OP_POOL_2D;
+        case GGML_OP_MUL:      return B200_OP_MUL;
+        case GGML_OP_UNARY:    return B200_OP_UNARY;
+        case GGML_OP_ROPE:     return B200_OP_ROPE;
+        case GGML_OP_CPY:      return B200_OP_CPY;
+        case GGML_OP_DUP:      return B200_OP_DUP;
+        case GGML_OP_CONT:     return B200_OP_CONT;
+        case GGML_OP_GET_ROWS: return B200_OP_GET_ROWS;
         default:               return -1;
     }
 }
@@ -304,9 +348,17 @@ static int b200_op_of(const ggml_tensor * node) {
 // node is dst = op(src0, src1).  The whole list goes down in ONE call; asynchronous (ggml_backend_graph_compute adds
 // the synchronize, ggml-backend.cpp:327-335).
 static std::atomic<uint64_t> g_graph_key{1};
-static void fp_tensor(std::vector<uint64_t> & fp, const ggml_tensor * t) {
+// A KV-cache store -- ggml_cpy into a view of a larger tensor (llama-graph.cpp:1341-1363) -- lands at an offset that moves with the position
+// while everything else about the graph stays the same from one token to the next.  Such a node is marked B200_TENSOR_DYNAMIC: its data
+// pointer stays out of the fingerprint (the cache tensor's own address goes in instead), and the op layer reads the destination of each call
+// from a device table, so that one captured CUDA graph serves every position.
+static bool is_dynamic_store(const ggml_tensor * node) {
+    return node->op == GGML_OP_CPY && node->view_src && node->src[1] && node->src[1]->view_src == node->view_src &&
+           node->view_src->buffer && ggml_nbytes(node) < ggml_nbytes(node->view_src);
+}
+static void fp_tensor(std::vector<uint64_t> & fp, const ggml_tensor * t, bool masked = false) {
     if (!t) { fp.push_back(0); return; }
-    fp.push_back((uint64_t) (uintptr_t) t); fp.push_back((uint64_t) (uintptr_t) t->data); fp.push_back((uint64_t) (uintptr_t) t->view_src);
+    fp.push_back((uint64_t) (uintptr_t) t); fp.push_back(masked ? 0x64796eull : (uint64_t) (uintptr_t) t->data); fp.push_back((uint64_t) (uintptr_t) t->view_src);
     fp.push_back((uint64_t) t->type | ((uint64_t) t->op << 32));
     for (int i = 0; i < 4; i++) { fp.push_back((uint64_t) t->ne[i]); fp.push_back((uint64_t) t->nb[i]); }
     fp.push_back(t->view_src ? (uint64_t) (uintptr_t) t->view_src->data : 0);
@@ -319,7 +371,8 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     for (int i = 0; i < cgraph->n_nodes; i++) {
         const ggml_tensor * node = cgraph->nodes[i];
         if (is_view_op(node->op) || ggml_is_empty(node)) continue;
-        fp_tensor(fp, node); fp_tensor(fp, node->src[0]); fp_tensor(fp, node->src[1]); fp_tensor(fp, node->src[2]);
+        const bool dyn = is_dynamic_store(node);
+        fp_tensor(fp, node, dyn); fp_tensor(fp, node->src[0]); fp_tensor(fp, node->src[1], dyn); fp_tensor(fp, node->src[2]);
         uint64_t prm[2]; memcpy(prm, node->op_params, sizeof(prm));
         fp.push_back(prm[0]); fp.push_back(prm[1]);
     }
@@ -327,7 +380,7 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     b200_graph_entry & e = c->graphs[cgraph];
     e.last_use = ++c->tick;
     if (e.fp != fp) {
-        e.nodes.clear();
+        e.nodes.clear(); e.dyn.clear();
         for (int i = 0; i < cgraph->n_nodes; i++) {
             ggml_tensor * node = cgraph->nodes[i];
             if (is_view_op(node->op) || ggml_is_empty(node)) continue;
@@ -344,9 +397,18 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
                 c->graphs.erase(cgraph);
                 return GGML_STATUS_FAILED;
             }
+            if (is_dynamic_store(node)) { n.dst.flags |= B200_TENSOR_DYNAMIC; e.dyn.push_back({(int) e.nodes.size(), i}); }
             e.nodes.push_back(n);
         }
-        e.fp = fp;
+        if (getenv("GGML_B200_DUMP") && cgraph->n_nodes > 64) {          // development: the order the scheduler hands the nodes over in
+            static int dumped = 0;
+            if (dumped++ < 2) for (int i = 0; i < cgraph->n_nodes && i < 80; i++) {
+                const ggml_tensor * t = cgraph->nodes[i];
+                fprintf(stderr, "[ggml-b200] node %3d %-10s %-24s [%lld,%lld,%lld,%lld] data=%p src0=%p src1=%p\n", i, ggml_op_desc(t), t->name, (long long) t->ne[0], (long long) t->ne[1],
+                              (long long) t->ne[2], (long long) t->ne[3], t->data, t->src[0] ? t->src[0]->data : nullptr, t->src[1] ? t->src[1]->data : nullptr);
+            }
+        }
+        e.fp = fp; e.seen = 0;
         e.key = g_graph_key.fetch_add(1);          // a new key per distinct list: the op layer's caches never see one key with two lists
         if (c->graphs.size() > 512) {              // (a scheduler keeps a few dozen split graphs alive; drop the oldest half beyond that)
             std::vector<std::pair<uint64_t, const ggml_cgraph *>> age;
@@ -359,7 +421,12 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
     // long node lists (a decode step) are captured once as a CUDA graph and replayed; short ones are launched directly
     static const int graph_min = getenv("GGML_B200_GRAPH_MIN") ? atoi(getenv("GGML_B200_GRAPH_MIN")) : 8;
     DEV_LOCK(c->dev);
-    const int rc = b200_graph_compute_keyed(dev_session(c->dev), g.nodes.data(), (int32_t) g.nodes.size(), (int) g.nodes.size() >= graph_min, g.key);
+    for (auto & d : g.dyn) {                    // same graph, this call's positions
+        g.nodes[d.first].dst.data  = cgraph->nodes[d.second]->data;
+        g.nodes[d.first].src1.data = cgraph->nodes[d.second]->src[1]->data;
+    }
+    g.seen++;
+    const int rc = b200_graph_compute_keyed(dev_session(c->dev), g.nodes.data(), (int32_t) g.nodes.size(), (int) g.nodes.size() >= graph_min && g.seen >= 2, g.key);
     if (rc == B200_ENOMEM) return GGML_STATUS_ALLOC_FAILED;
     if (rc) { B200_ERR("graph_compute: %s", b200_last_error()); return GGML_STATUS_FAILED; }
     return GGML_STATUS_SUCCESS;

@@ -172,8 +172,26 @@ struct AddArgs {
     int64_t ne[4];      // dst / src0 shape
     int64_t neb[4];     // src1 shape
     int64_t nba[4], nbb[4], nbd[4];   // byte strides
+    int mul;            // 0: a + b   1: a * b (GGML_OP_MUL, same broadcast rules)
 };
 cudaError_t launch_add_f32(const AddArgs & a, cudaStream_t st);
+
+// ---- graph_ops.cu: the ops between the MUL_MATs of a Llama layer (all strides in bytes, ggml order)
+struct RopeArgs {
+    const char * x; char * y; const int32_t * pos;
+    int64_t ne[4], nbs[4], nbd[4];
+    int n_dims, neox;
+    float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
+};
+cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st);
+struct CpyArgs { const char * x; char * y; char * const * dyn /* device: where this launch's dst starts, or NULL = y */; int64_t nes[4], nbs[4], ned[4], nbd[4]; };
+cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream_t st);
+struct GetRowsArgs { const char * x; const char * ids; char * y; int64_t ne00, ne01, ne10, ne11, ne12; int64_t nbs[4], nbi[3], nbd[4]; };
+cudaError_t launch_get_rows_f32(const GetRowsArgs & p, cudaStream_t st);
+struct MmF16Args { const char * a; const char * b; char * d; int64_t M, N, K, ne12, ne13, r2, r3; int64_t nba[4], nbb[4], nbd[4]; };
+cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st);
+cudaError_t launch_silu_f32(const float * x, float * y, int64_t n, cudaStream_t st);
+cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, cudaStream_t st);
 
 // ---- norm_ops.cu: RMS_NORM / SOFT_MAX / POOL_2D (ne, nb: ggml order, bytes)
 cudaError_t launch_rms_norm_f32(const void * x, void * y, const int64_t * ne, const int64_t * nb_src, const int64_t * nb_dst, float eps, cudaStream_t st);

@@ -1,0 +1,271 @@
+// graph_ops.cu — the ops that sit BETWEEN the MUL_MATs of a Llama layer in the graphs llama.cpp builds (src/llama-model.cpp:4191-4358,
+// src/llama-graph.cpp:1126-1216, :1306-1420): MUL (norm weight, gate*up), UNARY SILU, ROPE, CPY / CONT (KV-cache store, head merge),
+// GET_ROWS f32 (output rows), and the f16 x f32 MUL_MAT of attention (K and V live in the cache as f16).  The cDSP backend leaves all of
+// them to ggml-cpu; here that would cost a scheduler split with a host round trip after every MUL_MAT (8(f) rank 2-3 of SURVEY.md), so
+// they run on the device as plain HBM-bound kernels and the whole layer stack stays one split.
+// Specifications (ggml-cpu): binary-ops.cpp:50-117 (MUL), unary-ops.cpp / ggml_silu_f32, ggml_compute_forward_rope_f32
+// (ggml-cpu.c:8708-8889; cache init :8634-8648, YaRN :8610-8632), ggml_compute_forward_dup (:3164-4010: element i of src in logical order
+// -> element i of dst in logical order), ggml_compute_forward_get_rows_f32 (:7853-7892), ggml_compute_forward_mul_mat with an f16 src0
+// (src1 rounded to f16 first: vec_dot_type, ggml-cpu.c:256-270 and :6807-6842; f32 accumulation).
+#include "b200_internal.cuh"
+
+#include <mma.h>
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------ UNARY (SILU)
+__global__ void __launch_bounds__(256) silu_f32_kernel(const float * __restrict__ x, float * __restrict__ y, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const float v = x[i];
+        y[i] = __fdiv_rn(v, __fadd_rn(1.0f, expf(-v)));                 // ggml_silu_f32: x / (1 + expf(-x))
+    }
+}
+// SILU(gate) * up in one pass: the pair every SwiGLU FFN issues back to back (llama-graph.cpp build_ffn, LLM_FFN_SILU + LLM_FFN_PAR)
+__global__ void __launch_bounds__(256) silu_mul_f32_kernel(const float * __restrict__ g, const float * __restrict__ u, float * __restrict__ y, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const float v = g[i];
+        y[i] = __fmul_rn(__fdiv_rn(v, __fadd_rn(1.0f, expf(-v))), u[i]);
+    }
+}
+static unsigned ew_blocks(int64_t n) { int64_t b = (n + 255) / 256; if (b > 148 * 16) b = 148 * 16; return (unsigned) (b < 1 ? 1 : b); }
+cudaError_t launch_silu_f32(const float * x, float * y, int64_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    silu_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(x, y, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    silu_mul_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(g, u, y, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ ROPE (f32; normal and NeoX pairing)
+// one thread per rotated pair (or per passed-through pair beyond n_dims).  theta of pair k = pos * theta_scale^k, built by k successive
+// f32 multiplications exactly as the reference's cache loop does (ggml-cpu.c:8638-8647), so the angle is the reference's bit for bit.
+__global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
+    const int64_t half = p.ne[0] / 2;
+    const int64_t total = half * p.ne[1] * p.ne[2] * p.ne[3];
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t t = i;
+        const int64_t k = t % half; t /= half;
+        const int64_t i1 = t % p.ne[1]; t /= p.ne[1];
+        const int64_t i2 = t % p.ne[2]; const int64_t i3 = t / p.ne[2];
+        const char * s = p.x + i1 * p.nbs[1] + i2 * p.nbs[2] + i3 * p.nbs[3];
+        char * d = p.y + i1 * p.nbd[1] + i2 * p.nbd[2] + i3 * p.nbd[3];
+        const int64_t i0 = 2 * k;
+        if (i0 >= p.n_dims) {                                            // channels past n_dims are copied through
+            ((float *) d)[i0] = ((const float *) s)[i0]; ((float *) d)[i0 + 1] = ((const float *) s)[i0 + 1];
+            continue;
+        }
+        float theta = (float) p.pos[i2];
+        for (int64_t j = 0; j < k; j++) theta = __fmul_rn(theta, p.theta_scale);
+        const float theta_extrap = theta;                                // (freq_factors: declined by the admission check)
+        const float theta_interp = __fmul_rn(p.freq_scale, theta_extrap);
+        float th = theta_interp, mscale = p.attn_factor;
+        if (p.ext_factor != 0.0f) {
+            const float y = ((float) (i0 / 2) - p.corr0) / fmaxf(0.001f, p.corr1 - p.corr0);
+            const float ramp = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * p.ext_factor;
+            th = theta_interp * (1.0f - ramp) + theta_extrap * ramp;
+            mscale *= 1.0f + 0.1f * logf(1.0f / p.freq_scale);
+        }
+        const float c = __fmul_rn(cosf(th), mscale), sn = __fmul_rn(sinf(th), mscale);
+        const int64_t a = p.neox ? k : i0, b = p.neox ? k + p.n_dims / 2 : i0 + 1;
+        const float x0 = ((const float *) s)[a], x1 = ((const float *) s)[b];
+        ((float *) d)[a] = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
+        ((float *) d)[b] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+    }
+}
+cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st) {
+    const int64_t total = p.ne[0] / 2 * p.ne[1] * p.ne[2] * p.ne[3];
+    if (total == 0) return cudaSuccess;
+    rope_f32_kernel<<<ew_blocks(total), 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
+// element i (logical order of src) -> element i (logical order of dst); any byte strides on both sides; f32 / f16 either side
+template <typename TS, typename TD> __device__ __forceinline__ TD cvt_el(TS v);
+template <> __device__ __forceinline__ float  cvt_el<float, float>(float v)    { return v; }
+template <> __device__ __forceinline__ __half cvt_el<float, __half>(float v)   { return __float2half_rn(v); }
+template <> __device__ __forceinline__ float  cvt_el<__half, float>(__half v)  { return __half2float(v); }
+template <> __device__ __forceinline__ __half cvt_el<__half, __half>(__half v) { return v; }
+template <typename TS, typename TD>
+__global__ void __launch_bounds__(256) cpy_kernel(const CpyArgs p, const int64_t n) {
+    char * const y = p.dyn ? *p.dyn : p.y;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t t = i;
+        const int64_t s0 = t % p.nes[0]; t /= p.nes[0];
+        const int64_t s1 = t % p.nes[1]; t /= p.nes[1];
+        const int64_t s2 = t % p.nes[2]; const int64_t s3 = t / p.nes[2];
+        t = i;
+        const int64_t d0 = t % p.ned[0]; t /= p.ned[0];
+        const int64_t d1 = t % p.ned[1]; t /= p.ned[1];
+        const int64_t d2 = t % p.ned[2]; const int64_t d3 = t / p.ned[2];
+        const TS v = *(const TS *) (p.x + s0 * p.nbs[0] + s1 * p.nbs[1] + s2 * p.nbs[2] + s3 * p.nbs[3]);
+        *(TD *) (y + d0 * p.nbd[0] + d1 * p.nbd[1] + d2 * p.nbd[2] + d3 * p.nbd[3]) = cvt_el<TS, TD>(v);
+    }
+}
+cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream_t st) {
+    const int64_t n = p.nes[0] * p.nes[1] * p.nes[2] * p.nes[3];
+    if (n == 0) return cudaSuccess;
+    const unsigned b = ew_blocks(n);
+    if (!src_f16 && !dst_f16) cpy_kernel<float, float><<<b, 256, 0, st>>>(p, n);
+    else if (!src_f16 && dst_f16) cpy_kernel<float, __half><<<b, 256, 0, st>>>(p, n);
+    else if (src_f16 && !dst_f16) cpy_kernel<__half, float><<<b, 256, 0, st>>>(p, n);
+    else cpy_kernel<__half, __half><<<b, 256, 0, st>>>(p, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ GET_ROWS (f32 rows, i32 ids)
+__global__ void __launch_bounds__(256) get_rows_f32_kernel(const GetRowsArgs p, const int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t t = i;
+        const int64_t i0 = t % p.ne00; t /= p.ne00;
+        const int64_t i10 = t % p.ne10; t /= p.ne10;
+        const int64_t i11 = t % p.ne11; const int64_t i12 = t / p.ne11;
+        const int64_t r = *(const int32_t *) (p.ids + i10 * p.nbi[0] + i11 * p.nbi[1] + i12 * p.nbi[2]);
+        if (r < 0 || r >= p.ne01) continue;                              // (the reference asserts; never write from outside src0)
+        *(float *) (p.y + i0 * 4 + i10 * p.nbd[1] + i11 * p.nbd[2] + i12 * p.nbd[3]) =
+            *(const float *) (p.x + i0 * 4 + r * p.nbs[1] + i11 * p.nbs[2] + i12 * p.nbs[3]);
+    }
+}
+cudaError_t launch_get_rows_f32(const GetRowsArgs & p, cudaStream_t st) {
+    const int64_t n = p.ne00 * p.ne10 * p.ne11 * p.ne12;
+    if (n == 0) return cudaSuccess;
+    get_rows_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(p, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ MUL_MAT, f16 src0 x f32 src1 -> f32
+// dst[m, n, i12, i13] = sum_k src0[k, m, i12 / r2, i13 / r3] * f16(src1[k, n, i12, i13]); K contiguous on both sides, every other stride free
+// (K / V cache views: rows n_embd_k_gqa apart, heads interleaved; V transposed with rows n_ctx apart).
+__device__ __forceinline__ float rnd_h(float v) { return __half2float(__float2half_rn(v)); }
+
+// few columns (decode): one warp per output row, the row's f16 values read once and used for up to 8 columns
+template <int NC>
+__global__ void __launch_bounds__(128) mm_f16_vec_kernel(const MmF16Args p) {
+    const int lane = threadIdx.x & 31;
+    const int64_t m = (int64_t) blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (m >= p.M) return;
+    const int64_t i12 = blockIdx.y % p.ne12, i13 = blockIdx.y / p.ne12;
+    const __half * w = (const __half *) (p.a + m * p.nba[1] + (i12 / p.r2) * p.nba[2] + (i13 / p.r3) * p.nba[3]);
+    const char * xb = p.b + i12 * p.nbb[2] + i13 * p.nbb[3];
+    char * db = p.d + i12 * p.nbd[2] + i13 * p.nbd[3];
+    for (int64_t n0 = 0; n0 < p.N; n0 += NC) {
+        float acc[NC];
+        #pragma unroll
+        for (int c = 0; c < NC; c++) acc[c] = 0.f;
+        const bool vec = ((uintptr_t) w & 3) == 0 && ((((uintptr_t) xb) | (uintptr_t) p.nbb[1]) & 7) == 0 && p.K % 2 == 0;
+        if (vec) {
+            for (int64_t k2 = lane; k2 < p.K / 2; k2 += 32) {
+                const float2 wf = __half22float2(((const __half2 *) w)[k2]);
+                #pragma unroll
+                for (int c = 0; c < NC; c++) {
+                    if (n0 + c < p.N) {
+                        const float2 xv = *(const float2 *) (xb + (n0 + c) * p.nbb[1] + k2 * 8);
+                        acc[c] = fmaf(wf.x, rnd_h(xv.x), acc[c]); acc[c] = fmaf(wf.y, rnd_h(xv.y), acc[c]);
+                    }
+                }
+            }
+        } else {
+            for (int64_t k = lane; k < p.K; k += 32) {
+                const float wf = __half2float(w[k]);
+                #pragma unroll
+                for (int c = 0; c < NC; c++)
+                    if (n0 + c < p.N) acc[c] = fmaf(wf, rnd_h(*(const float *) (xb + (n0 + c) * p.nbb[1] + k * 4)), acc[c]);
+            }
+        }
+        #pragma unroll
+        for (int c = 0; c < NC; c++) {
+            float s = acc[c];
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0 && n0 + c < p.N) *(float *) (db + (n0 + c) * p.nbd[1] + m * 4) = s;
+        }
+    }
+}
+
+// many columns (prefill): 64 x 64 output tile per CTA of 4 warps, K in steps of 32 staged through shared memory as f16 (src1 rounded to f16
+// on the way in, which is what the reference does before its dot products), warp-level HMMA with f32 accumulators (2 x 2 fragments per warp).
+// This is the attention GEMM beside the hot path (2 x 2.1 GFLOP per layer at pp512 against 26 GFLOP of weight GEMMs), not the weight GEMM.
+#define MMT 64
+#define MMK 32
+#define MMLD (MMK + 8)
+__global__ void __launch_bounds__(128) mm_f16_tile_kernel(const MmF16Args p) {
+    using namespace nvcuda;
+    __shared__ __align__(32) __half As[MMT * MMLD];
+    __shared__ __align__(32) __half Bs[MMT * MMLD];
+    __shared__ __align__(32) float Cs[4][16 * 16];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t m0 = (int64_t) blockIdx.x * MMT, n0 = (int64_t) blockIdx.y * MMT;
+    const int64_t i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
+    const char * ab = p.a + (i12 / p.r2) * p.nba[2] + (i13 / p.r3) * p.nba[3];
+    const char * bb = p.b + i12 * p.nbb[2] + i13 * p.nbb[3];
+    char * db = p.d + i12 * p.nbd[2] + i13 * p.nbd[3];
+    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][2];
+    #pragma unroll
+    for (int i = 0; i < 2; i++)
+        #pragma unroll
+        for (int j = 0; j < 2; j++) wmma::fill_fragment(acc[i][j], 0.0f);
+    const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+    for (int64_t k0 = 0; k0 < p.K; k0 += MMK) {
+        for (int e = threadIdx.x; e < MMT * MMK; e += 128) {               // consecutive threads walk K: coalesced on both operands
+            const int r = e / MMK, kk = e % MMK;
+            const int64_t k = k0 + kk;
+            __half av = __float2half_rn(0.f), bv = av;
+            if (k < p.K) {
+                if (m0 + r < p.M) av = *(const __half *) (ab + (m0 + r) * p.nba[1] + k * 2);
+                if (n0 + r < p.N) bv = __float2half_rn(*(const float *) (bb + (n0 + r) * p.nbb[1] + k * 4));
+            }
+            As[r * MMLD + kk] = av; Bs[r * MMLD + kk] = bv;
+        }
+        __syncthreads();
+        #pragma unroll
+        for (int kk = 0; kk < MMK; kk += 16) {
+            wmma::fragment<wmma::matrix_a, 16, 16, 16, __half, wmma::row_major> fa[2];
+            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[2];
+            #pragma unroll
+            for (int i = 0; i < 2; i++) wmma::load_matrix_sync(fa[i], As + (wm + i * 16) * MMLD + kk, MMLD);
+            #pragma unroll
+            for (int j = 0; j < 2; j++) wmma::load_matrix_sync(fb[j], Bs + (wn + j * 16) * MMLD + kk, MMLD);
+            #pragma unroll
+            for (int i = 0; i < 2; i++)
+                #pragma unroll
+                for (int j = 0; j < 2; j++) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    // C fragment (m, n) -> dst[n][m]: staged per warp so that the store walks m (contiguous in dst) and respects the edges
+    #pragma unroll
+    for (int i = 0; i < 2; i++)
+        #pragma unroll
+        for (int j = 0; j < 2; j++) {
+            wmma::store_matrix_sync(Cs[warp], acc[i][j], 16, wmma::mem_col_major);      // Cs[n * 16 + m]
+            __syncwarp();
+            for (int e = lane; e < 256; e += 32) {
+                const int nn = e >> 4, mm = e & 15;
+                const int64_t m = m0 + wm + i * 16 + mm, n = n0 + wn + j * 16 + nn;
+                if (m < p.M && n < p.N) *(float *) (db + n * p.nbd[1] + m * 4) = Cs[warp][e];
+            }
+            __syncwarp();
+        }
+}
+cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st) {
+    const int64_t batch = p.ne12 * p.ne13;
+    if (p.M == 0 || p.N == 0 || batch == 0) return cudaSuccess;
+    if (batch > 65535) return cudaErrorInvalidValue;
+    if (p.N <= 16) {
+        dim3 grid((unsigned) ((p.M + 3) / 4), (unsigned) batch);
+        if (p.N == 1) mm_f16_vec_kernel<1><<<grid, 128, 0, st>>>(p);
+        else if (p.N <= 4) mm_f16_vec_kernel<4><<<grid, 128, 0, st>>>(p);
+        else mm_f16_vec_kernel<8><<<grid, 128, 0, st>>>(p);
+    } else {
+        const int64_t gy = (p.N + MMT - 1) / MMT;
+        if (gy > 65535) return cudaErrorInvalidValue;
+        dim3 grid((unsigned) ((p.M + MMT - 1) / MMT), (unsigned) gy, (unsigned) batch);
+        mm_f16_tile_kernel<<<grid, 128, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace b200

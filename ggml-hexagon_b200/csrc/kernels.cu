@@ -165,6 +165,7 @@ cudaError_t launch_quantize_q8_1_aos(const float * x, int64_t K, int64_t nrows, 
 
 // ------------------------------------------------------------------------------------------------ ADD
 // Fast path: everything contiguous, src1 either same shape or one row repeated -> float4 grid-stride.
+template <bool MUL>
 __global__ void __launch_bounds__(256)
 add_f32_vec_kernel(const float4 * __restrict__ a, const float4 * __restrict__ b, float4 * __restrict__ d,
                    const int64_t n4, const int64_t nb4 /* period of b in float4, or n4 */) {
@@ -174,10 +175,12 @@ add_f32_vec_kernel(const float4 * __restrict__ a, const float4 * __restrict__ b,
 #endif
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
         const float4 x = a[i], y = b[nb4 == n4 ? i : i % nb4];
-        d[i] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+        d[i] = MUL ? make_float4(__fmul_rn(x.x, y.x), __fmul_rn(x.y, y.y), __fmul_rn(x.z, y.z), __fmul_rn(x.w, y.w))
+                   : make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
     }
 }
 // General path: any byte strides, src1 repeated in every dim (i % ne1x), one thread per element.
+template <bool MUL>
 __global__ void __launch_bounds__(256) add_f32_gen_kernel(const AddArgs p, const int64_t n) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t t = i;
@@ -187,7 +190,7 @@ __global__ void __launch_bounds__(256) add_f32_gen_kernel(const AddArgs p, const
         const float x = *(const float *) (p.a + i0 * p.nba[0] + i1 * p.nba[1] + i2 * p.nba[2] + i3 * p.nba[3]);
         const float y = *(const float *) (p.b + (i0 % p.neb[0]) * p.nbb[0] + (i1 % p.neb[1]) * p.nbb[1] +
                                                  (i2 % p.neb[2]) * p.nbb[2] + (i3 % p.neb[3]) * p.nbb[3]);
-        *(float *) (p.d + i0 * p.nbd[0] + i1 * p.nbd[1] + i2 * p.nbd[2] + i3 * p.nbd[3]) = x + y;
+        *(float *) (p.d + i0 * p.nbd[0] + i1 * p.nbd[1] + i2 * p.nbd[2] + i3 * p.nbd[3]) = MUL ? __fmul_rn(x, y) : x + y;
     }
 }
 
@@ -217,10 +220,12 @@ cudaError_t launch_add_f32(const AddArgs & p, cudaStream_t st) {
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        return cudaLaunchKernelEx(&cfg, add_f32_vec_kernel, (const float4 *) p.a, (const float4 *) p.b, (float4 *) p.d, n4, nb_el / 4);
+        return p.mul ? cudaLaunchKernelEx(&cfg, add_f32_vec_kernel<true>, (const float4 *) p.a, (const float4 *) p.b, (float4 *) p.d, n4, nb_el / 4)
+                     : cudaLaunchKernelEx(&cfg, add_f32_vec_kernel<false>, (const float4 *) p.a, (const float4 *) p.b, (float4 *) p.d, n4, nb_el / 4);
     }
     int64_t blocks = (n + 255) / 256; if (blocks > 148 * 16) blocks = 148 * 16;
-    add_f32_gen_kernel<<<(unsigned) blocks, 256, 0, st>>>(p, n);
+    if (p.mul) add_f32_gen_kernel<true><<<(unsigned) blocks, 256, 0, st>>>(p, n);
+    else       add_f32_gen_kernel<false><<<(unsigned) blocks, 256, 0, st>>>(p, n);
     return cudaGetLastError();
 }
 

@@ -95,6 +95,9 @@ struct Ctx {
     float *  gm_tail = nullptr; size_t gm_tail_cap = 0;  // stream-K tail partial tiles of the dense GEMM (gemm_dense_tail_ws_bytes)
     float *  gm_sp = nullptr; size_t gm_sp_cap = 0;      // split-K partial results      // K-quants: f32 block scales (and negated block minima) of the unpacked weights
     bool capturing = false;       // inside cudaStreamBeginCapture .. EndCapture: no allocation, no synchronisation
+    // B200_TENSOR_DYNAMIC destinations (KV-cache stores): a device table of the current dst pointers, refreshed before every launch of a captured
+    // graph, so that one CUDA graph serves every position of the cache
+    char ** dyn_tab = nullptr; int dyn_i = 0; bool dyn_on = false;
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
@@ -210,7 +213,7 @@ extern "C" int b200_close(b200_handle h) {
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     cudaFree(c->act_qs); cudaFree(c->act_ds); cudaFree(c->act_qs2); cudaFree(c->act_ds2); cudaFree(c->qx_slots); cudaFree(c->stage); cudaFree(c->flush);
     if (c->pin) { cudaFreeHost(c->pin); for (int i = 0; i < PIN_SLOTS; i++) if (c->pin_ev[i]) cudaEventDestroy(c->pin_ev[i]); }
-    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp); cudaFree(c->gm_tail);
+    cudaFree(c->gm_qb); cudaFree(c->gm_db); cudaFree(c->gm_a); cudaFree(c->gm_ws); cudaFree(c->gm_sp); cudaFree(c->gm_tail); cudaFree(c->dyn_tab);
     cudaStreamDestroy(c->st);
     c->magic = 0;
     delete c;
@@ -374,6 +377,7 @@ static int add_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200
 }
 
 // ------------------------------------------------------------------------------------------------ RMS_NORM / SOFT_MAX / POOL_2D
+static void wrote(Ctx * c, const b200_tensor * d);
 static float f32_param(const b200_tensor * t, int i) { float f; memcpy(&f, &t->op_params[i], 4); return f; }
 static int rms_norm_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     if (s->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "rms_norm: f32 only");
@@ -382,7 +386,7 @@ static int rms_norm_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     const float eps = f32_param(d, 0);
     if (!(eps >= 0.0f)) return fail(B200_EINVAL, "rms_norm: eps < 0");
     CU(launch_rms_norm_f32(s->data, d->data, s->ne, s->nb, d->nb, eps, c->st)); c->launches++;
-    c->q_ptr = nullptr;
+    wrote(c, d);
     return 0;
 }
 static bool contiguous_f32_t(const b200_tensor * t) {
@@ -402,7 +406,7 @@ static int soft_max_dev(Ctx * c, const b200_tensor * s, const b200_tensor * m, b
     }
     CU(launch_soft_max_f32((const float *) s->data, has_mask ? m->data : nullptr, has_mask && m->type == T_F16, (float *) d->data, s->ne,
                            f32_param(d, 0), f32_param(d, 1), c->st)); c->launches++;
-    c->q_ptr = nullptr;
+    wrote(c, d);
     return 0;
 }
 static int pool_2d_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
@@ -414,6 +418,112 @@ static int pool_2d_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     if (!contiguous_f32_t(d) || d->ne[2] != s->ne[2] || d->ne[3] != s->ne[3]) return fail(B200_EINVAL, "pool_2d: dst must be contiguous [px, py, ne2, ne3]");
     CU(launch_pool_2d(s->data, s->type == T_F16, (float *) d->data, s->ne, s->nb, d->ne[0], d->ne[1], o, c->st)); c->launches++;
     c->q_ptr = nullptr;
+    return 0;
+}
+// ------------------------------------------------------------------------------------------------ graph_ops.cu: MUL / SILU / ROPE / CPY / GET_ROWS / f16 MUL_MAT
+constexpr int T_I32 = 26;                                   // GGML_TYPE_I32 (ggml.h:349-390)
+constexpr int DYN_MAX = 1024;
+// an op wrote d: a cached conversion of the activations at q_ptr stays valid unless d touches the memory it was taken from (the ops of
+// this section sit BETWEEN MUL_MATs that share their src1 -- q / k / v with the ROPEs in between -- so dropping the cache blindly would
+// quantise the same vector three times)
+static void wrote(Ctx * c, const b200_tensor * d) {
+    if (!c->q_ptr) return;
+    int64_t span = d->type == T_F16 ? 2 : 4;
+    for (int i = 0; i < 4; i++) span += (d->ne[i] - 1) * d->nb[i];
+    const int64_t qspan = (c->q_N > 1 ? (c->q_N - 1) * c->q_stride : 0) + c->q_K * 4;
+    const char * a = (const char *) d->data; const char * b = (const char *) c->q_ptr;
+    if (a < b + qspan && b < a + span) c->q_ptr = nullptr;
+}
+static int mul_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    if (s0->type != T_F32 || s1->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "mul: f32 only");
+    AddArgs a{};
+    a.a = (const char *) s0->data; a.b = (const char *) s1->data; a.d = (char *) d->data; a.mul = 1;
+    for (int i = 0; i < 4; i++) {
+        if (s0->ne[i] != d->ne[i]) return fail(B200_EINVAL, "mul: src0 and dst shapes differ in dim %d", i);
+        if (s1->ne[i] <= 0 || d->ne[i] % s1->ne[i]) return fail(B200_EINVAL, "mul: src1 dim %d does not repeat into dst", i);
+        a.ne[i] = d->ne[i]; a.neb[i] = s1->ne[i];
+        a.nba[i] = s0->nb[i]; a.nbb[i] = s1->nb[i]; a.nbd[i] = d->nb[i];
+    }
+    CU(launch_add_f32(a, c->st)); c->launches++;
+    wrote(c, d);
+    return 0;
+}
+static int64_t nelems(const b200_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+static int unary_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
+    if (d->op_params[0] != B200_UNARY_SILU) return fail(B200_ENOTSUP, "unary: only SILU (%d) is implemented, got %d", B200_UNARY_SILU, d->op_params[0]);
+    if (s->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "silu: f32 only");
+    for (int i = 0; i < 4; i++) if (s->ne[i] != d->ne[i]) return fail(B200_EINVAL, "silu: src and dst shapes differ");
+    if (!contiguous_f32_t(s) || !contiguous_f32_t(d)) return fail(B200_ENOTSUP, "silu: src and dst must be contiguous");
+    CU(launch_silu_f32((const float *) s->data, (float *) d->data, nelems(s), c->st)); c->launches++;
+    wrote(c, d);
+    return 0;
+}
+static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, b200_tensor * d) {
+    if (s->type != T_F32 || d->type != T_F32 || pos->type != T_I32) return fail(B200_ENOTSUP, "rope: f32 data, i32 positions");
+    for (int i = 0; i < 4; i++) if (s->ne[i] != d->ne[i]) return fail(B200_EINVAL, "rope: src and dst shapes differ");
+    if (s->nb[0] != 4 || d->nb[0] != 4) return fail(B200_ENOTSUP, "rope: rows must be contiguous");
+    const int32_t * o = d->op_params;
+    const int n_dims = o[1], mode = o[2], n_ctx_orig = o[4];
+    if (mode != 0 && mode != 2) return fail(B200_ENOTSUP, "rope: mode %d (only normal = 0 and NeoX = 2)", mode);
+    if (n_dims <= 0 || n_dims % 2 || n_dims > s->ne[0] || s->ne[0] % 2) return fail(B200_EINVAL, "rope: n_dims = %d on rows of %lld", n_dims, (long long) s->ne[0]);
+    if (pos->ne[0] < s->ne[2] || pos->nb[0] != 4) return fail(B200_EINVAL, "rope: one position per ne[2] index");
+    RopeArgs a{};
+    a.x = (const char *) s->data; a.y = (char *) d->data; a.pos = (const int32_t *) pos->data;
+    for (int i = 0; i < 4; i++) { a.ne[i] = s->ne[i]; a.nbs[i] = s->nb[i]; a.nbd[i] = d->nb[i]; }
+    a.n_dims = n_dims; a.neox = mode == 2;
+    const float freq_base = f32_param(d, 5), beta_fast = f32_param(d, 9), beta_slow = f32_param(d, 10);
+    a.freq_scale = f32_param(d, 6); a.ext_factor = f32_param(d, 7); a.attn_factor = f32_param(d, 8);
+    a.theta_scale = powf(freq_base, -2.0f / n_dims);
+    // ggml_rope_yarn_corr_dims (ggml.c:3741-3753)
+    auto corr = [&](float n_rot) { return n_dims * logf(n_ctx_orig / (n_rot * 2 * 3.14159265358979323846f)) / (2 * logf(freq_base)); };
+    a.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); a.corr1 = fminf((float) (n_dims - 1), ceilf(corr(beta_slow)));
+    CU(launch_rope_f32(a, c->st)); c->launches++;
+    wrote(c, d);
+    return 0;
+}
+static int cpy_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
+    if ((s->type != T_F32 && s->type != T_F16) || (d->type != T_F32 && d->type != T_F16)) return fail(B200_ENOTSUP, "cpy: f32 / f16 only");
+    if (nelems(s) != nelems(d)) return fail(B200_EINVAL, "cpy: element counts differ");
+    CpyArgs a{};
+    a.x = (const char *) s->data; a.y = (char *) d->data;
+    for (int i = 0; i < 4; i++) { a.nes[i] = s->ne[i]; a.nbs[i] = s->nb[i]; a.ned[i] = d->ne[i]; a.nbd[i] = d->nb[i]; }
+    if (d->flags & B200_TENSOR_DYNAMIC) {
+        if (c->dyn_on) { if (c->dyn_i >= DYN_MAX) return fail(B200_ENOTSUP, "more than %d dynamic destinations in one node list", DYN_MAX); a.dyn = c->dyn_tab + c->dyn_i; }
+        c->dyn_i++;
+        c->q_ptr = nullptr;         // (where it lands differs from launch to launch)
+    }
+    CU(launch_cpy(a, s->type == T_F16, d->type == T_F16, c->st)); c->launches++;
+    wrote(c, d);
+    return 0;
+}
+static int get_rows_dev(Ctx * c, const b200_tensor * s, const b200_tensor * ids, b200_tensor * d) {
+    if (s->type != T_F32 || d->type != T_F32 || ids->type != T_I32) return fail(B200_ENOTSUP, "get_rows: f32 rows, i32 ids");
+    if (s->nb[0] != 4 || d->nb[0] != 4 || ids->nb[0] != 4) return fail(B200_ENOTSUP, "get_rows: dim 0 must be contiguous");
+    if (d->ne[0] != s->ne[0] || d->ne[1] != ids->ne[0] || d->ne[2] != ids->ne[1] || d->ne[3] != ids->ne[2] || ids->ne[3] != 1 ||
+        s->ne[2] != ids->ne[1] || s->ne[3] != ids->ne[2]) return fail(B200_EINVAL, "get_rows: shapes do not match");
+    GetRowsArgs a{};
+    a.x = (const char *) s->data; a.ids = (const char *) ids->data; a.y = (char *) d->data;
+    a.ne00 = s->ne[0]; a.ne01 = s->ne[1]; a.ne10 = ids->ne[0]; a.ne11 = ids->ne[1]; a.ne12 = ids->ne[2];
+    for (int i = 0; i < 4; i++) { a.nbs[i] = s->nb[i]; a.nbd[i] = d->nb[i]; }
+    for (int i = 0; i < 3; i++) a.nbi[i] = ids->nb[i];
+    CU(launch_get_rows_f32(a, c->st)); c->launches++;
+    wrote(c, d);
+    return 0;
+}
+static int mm_f16_dev(Ctx * c, const b200_tensor * s0, const b200_tensor * s1, b200_tensor * d) {
+    if (s0->type != T_F16 || s1->type != T_F32 || d->type != T_F32) return fail(B200_ENOTSUP, "mulmat f16: f16 x f32 -> f32");
+    const int64_t K = s0->ne[0], M = s0->ne[1], N = s1->ne[1];
+    if (s1->ne[0] != K) return fail(B200_EINVAL, "mulmat f16: K mismatch");
+    if (d->ne[0] != M || d->ne[1] != N || d->ne[2] != s1->ne[2] || d->ne[3] != s1->ne[3]) return fail(B200_EINVAL, "mulmat f16: dst shape mismatch");
+    if (s0->ne[2] <= 0 || s0->ne[3] <= 0 || s1->ne[2] % s0->ne[2] || s1->ne[3] % s0->ne[3]) return fail(B200_EINVAL, "mulmat f16: batch dims do not broadcast");
+    if (s0->nb[0] != 2 || s1->nb[0] != 4 || d->nb[0] != 4) return fail(B200_ENOTSUP, "mulmat f16: K (src0, src1) and M (dst) must be contiguous");
+    if (M == 0 || N == 0) return 0;
+    MmF16Args a{};
+    a.a = (const char *) s0->data; a.b = (const char *) s1->data; a.d = (char *) d->data;
+    a.M = M; a.N = N; a.K = K; a.ne12 = s1->ne[2]; a.ne13 = s1->ne[3]; a.r2 = s1->ne[2] / s0->ne[2]; a.r3 = s1->ne[3] / s0->ne[3];
+    for (int i = 0; i < 4; i++) { a.nba[i] = s0->nb[i]; a.nbb[i] = s1->nb[i]; a.nbd[i] = d->nb[i]; }
+    CU(launch_mm_f16(a, c->st)); c->launches++;
+    wrote(c, d);
     return 0;
 }
 static bool any_host(const b200_tensor * a, const b200_tensor * b, const b200_tensor * d) {
@@ -974,7 +1084,7 @@ extern "C" int b200_mulmat(b200_handle h, const b200_tensor * s0, const b200_ten
 // ------------------------------------------------------------------------------------------------ graph compute
 static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
     static const bool fuse = !(getenv("B200_FUSE") && atoi(getenv("B200_FUSE")) == 0);
-    c->in_graph = true; c->q_ptr = nullptr; c->rs_ops = 0;
+    c->in_graph = true; c->q_ptr = nullptr; c->rs_ops = 0; c->dyn_i = 0;
     int rc = 0;
     for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
@@ -985,7 +1095,14 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             case B200_OP_RMS_NORM: rc = rms_norm_dev(c, &nodes[i].src0, &d); break;
             case B200_OP_SOFT_MAX: rc = soft_max_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
             case B200_OP_POOL_2D:  rc = pool_2d_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_MUL:      rc = mul_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_UNARY:    rc = unary_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_ROPE:     rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_DUP: case B200_OP_CONT: case B200_OP_CPY:      // (ggml_cpy(a, b): the node is a view of b, so dst carries b's layout)
+                                   rc = cpy_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_GET_ROWS: rc = get_rows_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
             case B200_OP_MUL_MAT: {
+                if (nodes[i].src0.type == T_F16) { rc = mm_f16_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break; }
                 FusedAdd fa;
                 const int gl = fuse ? group_len(nodes, i, n) : 1;
                 // row split: what consumes this op's gathered vectors next?  [ADD with a plain vector ->] vector MUL_MAT: the gather kernel
@@ -1114,7 +1231,23 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     if (use_cuda_graph && (!c->rs_on || gemm_dense_enabled()))      // (row split: src0 is the rank's slice, so the sizes are the slice's)
         for (int i = 0; i < n; i++)
             if (nodes[i].dst.op == B200_OP_MUL_MAT) { rc = presize_gemm(c, &nodes[i].src0, &nodes[i].src1); if (rc) return rc; }
+    int n_dyn = 0;
+    for (int i = 0; i < n; i++) if (nodes[i].dst.flags & B200_TENSOR_DYNAMIC) {
+        const int op = nodes[i].dst.op;
+        if (op != B200_OP_CPY && op != B200_OP_DUP && op != B200_OP_CONT) return fail(B200_ENOTSUP, "B200_TENSOR_DYNAMIC is for the destination of CPY / DUP / CONT nodes");
+        n_dyn++;
+    }
     if (!use_cuda_graph) return run_nodes(c, nodes, n);
+    if (n_dyn > DYN_MAX) return fail(B200_ENOTSUP, "more than %d dynamic destinations in one node list", DYN_MAX);
+    if (n_dyn) {        // this call's destinations -> device table, stream-ordered in front of the graph launch (and outside the capture)
+        if (!c->dyn_tab) CU(cudaMalloc((void **) &c->dyn_tab, DYN_MAX * sizeof(char *)));
+        uint8_t * slot; cudaEvent_t ev;
+        rc = pin_slot(c, &slot, &ev); if (rc) return rc;
+        char ** hp = (char **) slot; int j = 0;
+        for (int i = 0; i < n; i++) if (nodes[i].dst.flags & B200_TENSOR_DYNAMIC) hp[j++] = (char *) nodes[i].dst.data;
+        CU(cudaMemcpyAsync(c->dyn_tab, hp, (size_t) n_dyn * sizeof(char *), cudaMemcpyHostToDevice, c->st));
+        CU(cudaEventRecord(ev, c->st));
+    }
 
     // cache key: the caller's (b200_graph_compute_keyed) or a hash of the whole list; a hit on a hashed key is confirmed by the node
     // count and a second, independent hash before anything captured for another list could be replayed
@@ -1129,9 +1262,9 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
     if (it == c->graphs.end()) {
         const int64_t before = c->launches;
         CU(cudaStreamBeginCapture(c->st, cudaStreamCaptureModeThreadLocal));
-        c->capturing = true;
+        c->capturing = true; c->dyn_on = n_dyn > 0;
         rc = run_nodes(c, nodes, n);
-        c->capturing = false;
+        c->capturing = false; c->dyn_on = false;
         cudaGraph_t g = nullptr;
         cudaError_t e = cudaStreamEndCapture(c->st, &g);
         const int64_t captured = c->launches - before;

@@ -26,7 +26,7 @@ extern "C" {
 /* tensor element types: numeric values of enum ggml_type (ggml/include/ggml.h:349-390) */
 enum b200_type {
     B200_TYPE_F32  = 0,
-    B200_TYPE_F16  = 1,   /* SOFT_MAX mask, POOL_2D input only */
+    B200_TYPE_F16  = 1,   /* SOFT_MAX mask, POOL_2D input, CPY either side, MUL_MAT src0 (KV cache) */
     B200_TYPE_Q4_0 = 2,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
@@ -43,7 +43,18 @@ enum b200_op {
     B200_OP_MUL_MAT  = 27,
     B200_OP_SOFT_MAX = 43,
     B200_OP_POOL_2D  = 53,
+    /* the ops between the MUL_MATs of a Llama layer, taken only in node lists (b200_graph_compute): with them on the device the
+     * scheduler keeps a whole layer stack in one split instead of a host round trip per MUL_MAT (graph_ops.cu) */
+    B200_OP_DUP      = 1,
+    B200_OP_MUL      = 6,    /* f32, src1 broadcast as in ADD */
+    B200_OP_CPY      = 32,   /* src0 -> src1's layout (dst is a view of src1); f32 / f16 either side */
+    B200_OP_CONT     = 33,
+    B200_OP_GET_ROWS = 38,   /* f32 rows, i32 ids */
+    B200_OP_ROPE     = 45,   /* f32; mode 0 (normal) or 2 (NeoX); src1 = i32 positions; no frequency factors (src2) */
+    B200_OP_UNARY    = 73,   /* op_params[0] = B200_UNARY_SILU */
 };
+#define B200_UNARY_SILU 10   /* GGML_UNARY_OP_SILU */
+#define B200_TYPE_I32   26   /* GGML_TYPE_I32: ROPE positions, GET_ROWS ids */
 
 enum b200_err {
     B200_OK       = 0,
@@ -58,6 +69,8 @@ enum b200_err {
 /* flags of b200_tensor */
 #define B200_TENSOR_HOST      0x1  /* data is a HOST pointer: the call copies it in/out (as FastRPC does with dsptensor.data) */
 #define B200_TENSOR_REPACKED  0x2  /* quantised weight already in the device SoA layout written by b200_weights_upload */
+#define B200_TENSOR_DYNAMIC   0x4  /* dst of a CPY / DUP / CONT node: `data` may differ between calls made under one b200_graph_compute_keyed key
+                                    * (a KV-cache store moves with the position); everything else about the node list is the same */
 
 /*
  * Replaces `struct dsptensor` (ggmlop_ap_skel.h:235-244).  Same fields, but ne/nb are 64-bit
