@@ -12,6 +12,8 @@ LIB_PATH = os.environ.get("B200_LIB") or os.path.join(HERE, "lib", "libb200ops.s
 
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K = 0, 1, 2, 8, 9, 12, 14
 OP_NONE, OP_ADD, OP_RMS_NORM, OP_MUL_MAT, OP_SOFT_MAX, OP_POOL_2D = 0, 2, 23, 27, 43, 53
+OP_DUP, OP_MUL, OP_CPY, OP_CONT, OP_GET_ROWS, OP_ROPE, OP_UNARY = 1, 6, 32, 33, 38, 45, 73      # graph_ops.cu (node lists only)
+UNARY_SILU, TYPE_I32, TENSOR_DYNAMIC = 10, 26, 0x4
 TENSOR_HOST, TENSOR_REPACKED = 1, 2
 BLOCK = {F32: (1, 4), Q4_0: (32, 18), Q8_0: (32, 34), Q8_1: (32, 36), Q4_K: (256, 144), Q6_K: (256, 210)}
 TYPE_NAMES = {F32: "f32", Q4_0: "q4_0", Q8_0: "q8_0", Q4_K: "q4_K", Q6_K: "q6_K"}
@@ -72,6 +74,7 @@ def lib():
         L.b200_pool_2d.argtypes = [H, TP, TP]
         L.b200_mulmat_rowsplit.argtypes = [H, TP, TP, TP]
         L.b200_graph_compute.argtypes = [H, C.POINTER(Node), I32, I32]
+        L.b200_graph_compute_keyed.argtypes = [H, C.POINTER(Node), I32, I32, C.c_uint64]
         L.b200_synchronize.argtypes = [H]
         L.b200_quantize_q8_1.argtypes = [H, VP, VP, I64, I64]
         L.b200_block_dots.argtypes = [H, TP, VP, VP]
@@ -426,6 +429,12 @@ class Session:
     def graph_compute(self, nodes, use_cuda_graph=True):
         arr = (Node * len(nodes))(*nodes) if not isinstance(nodes, C.Array) else nodes
         _ck(lib().b200_graph_compute(self.h, arr, len(arr), int(use_cuda_graph)))
+        return arr
+
+    def graph_compute_keyed(self, nodes, key, use_cuda_graph=True):
+        """the caller vouches that `key` names this node list (up to the data pointers of TENSOR_DYNAMIC destinations)"""
+        arr = (Node * len(nodes))(*nodes) if not isinstance(nodes, C.Array) else nodes
+        _ck(lib().b200_graph_compute_keyed(self.h, arr, len(arr), int(use_cuda_graph), C.c_uint64(key)))
         return arr
 
     # timing

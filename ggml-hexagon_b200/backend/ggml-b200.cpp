@@ -112,6 +112,7 @@ static bool b200_supports_mul_mat(const ggml_tensor * op) {
     if (!a || !b) return false;
     if (b->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
     if (a->type == GGML_TYPE_F16) {          // attention: K / V cache views (graph_ops.cu); K contiguous on both sides, other strides free
+        if (getenv("B200_GRAPH_OPS") && atoi(getenv("B200_GRAPH_OPS")) == 0) return false;
         if (a->nb[0] != sizeof(ggml_fp16_t) || b->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) return false;
         if (a->ne[2] <= 0 || a->ne[3] <= 0 || b->ne[2] % a->ne[2] || b->ne[3] % a->ne[3]) return false;
         return b->ne[2] * b->ne[3] <= 65535;

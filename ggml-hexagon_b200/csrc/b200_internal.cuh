@@ -191,7 +191,10 @@ cudaError_t launch_get_rows_f32(const GetRowsArgs & p, cudaStream_t st);
 struct MmF16Args { const char * a; const char * b; char * d; int64_t M, N, K, ne12, ne13, r2, r3; int64_t nba[4], nbb[4], nbd[4]; };
 cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st);
 cudaError_t launch_silu_f32(const float * x, float * y, int64_t n, cudaStream_t st);
-cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, cudaStream_t st);
+cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st);
+cudaError_t launch_rms_norm_mul(const float * x, const float * w, float * y, int64_t ne00, int64_t rows, int64_t xs, int64_t ys, float eps,
+                                int8_t * qs, ActDS * ds, cudaStream_t st);
+cudaError_t launch_cont_quant(const CpyArgs & p, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st);
 
 // ---- norm_ops.cu: RMS_NORM / SOFT_MAX / POOL_2D (ne, nb: ggml order, bytes)
 cudaError_t launch_rms_norm_f32(const void * x, void * y, const int64_t * ne, const int64_t * nb_src, const int64_t * nb_dst, float eps, cudaStream_t st);

@@ -13,36 +13,133 @@
 
 namespace b200 {
 
+// Every kernel here starts with the programmatic-dependent-launch pair (its grid may be scheduled while the previous kernel drains; nothing is
+// read or written before cudaGridDependencySynchronize returns, which waits for the whole previous grid), and is launched through pdl_launch.
+#define PDL_PROLOGUE() do { cudaTriggerProgrammaticLaunchCompletion(); cudaGridDependencySynchronize(); } while (0)
+template <typename... KArgs, typename... Args>
+static cudaError_t pdl_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+// q8_1 quantisation of one 32-element block held by 8 consecutive lanes (one float4 each), written into the two-plane SoA scratch the GEMV
+// kernels read: the body of quantize_q8_1_kernel (kernels.cu; = quantize_row_q8_1_ref, ggml-quants.c:220-253), for producers that quantise
+// what they have just computed.  All 32 lanes of the warp must call it.
+__device__ __forceinline__ void q8_1_soa_emit(const float4 v, const int sub, const int64_t row, const int64_t b, const int64_t NB,
+                                              int8_t * __restrict__ qs, ActDS * __restrict__ ds) {
+    float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const int q0 = (int) roundf(__fmul_rn(v.x, id)), q1 = (int) roundf(__fmul_rn(v.y, id));
+    const int q2 = (int) roundf(__fmul_rn(v.z, id)), q3 = (int) roundf(__fmul_rn(v.w, id));
+    int sum = q0 + q1 + q2 + q3;
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+    sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+    const int other = __shfl_xor_sync(0xffffffffu, sum, 4);
+    const uint32_t packed = (uint32_t) (q0 & 0xFF) | ((uint32_t) (q1 & 0xFF) << 8) | ((uint32_t) (q2 & 0xFF) << 16) | ((uint32_t) (q3 & 0xFF) << 24);
+    int8_t * col = qs + row * NB * 32;
+    *(uint32_t *) (col + ((int64_t) (sub >> 2) * NB + b) * 16 + (sub & 3) * 4) = packed;
+    if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; ds[row * NB + b] = o; }
+}
+
 // ------------------------------------------------------------------------------------------------ UNARY (SILU)
 __global__ void __launch_bounds__(256) silu_f32_kernel(const float * __restrict__ x, float * __restrict__ y, const int64_t n) {
+    PDL_PROLOGUE();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const float v = x[i];
         y[i] = __fdiv_rn(v, __fadd_rn(1.0f, expf(-v)));                 // ggml_silu_f32: x / (1 + expf(-x))
     }
 }
-// SILU(gate) * up in one pass: the pair every SwiGLU FFN issues back to back (llama-graph.cpp build_ffn, LLM_FFN_SILU + LLM_FFN_PAR)
-__global__ void __launch_bounds__(256) silu_mul_f32_kernel(const float * __restrict__ g, const float * __restrict__ u, float * __restrict__ y, const int64_t n) {
-    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
-        const float v = g[i];
-        y[i] = __fmul_rn(__fdiv_rn(v, __fadd_rn(1.0f, expf(-v))), u[i]);
+// SILU(gate) * up in one pass: the pair every SwiGLU FFN issues around the up projection (llama-graph.cpp build_ffn, LLM_FFN_SILU +
+// LLM_FFN_PAR); same two roundings as the separate kernels.  QUANT: rows of K (K % 128 == 0) are also written as q8_1 for the MUL_MAT that
+// consumes the product next (ffn_down).
+template <bool QUANT>
+__global__ void __launch_bounds__(256) silu_mul_f32_kernel(const float4 * __restrict__ g, const float4 * __restrict__ u, float4 * __restrict__ y, const int64_t n4,
+                                                           const int64_t K, int8_t * __restrict__ qs, ActDS * __restrict__ ds) {
+    PDL_PROLOGUE();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        const float4 a = g[i], b = u[i];
+        float4 r;
+        r.x = __fmul_rn(__fdiv_rn(a.x, __fadd_rn(1.0f, expf(-a.x))), b.x); r.y = __fmul_rn(__fdiv_rn(a.y, __fadd_rn(1.0f, expf(-a.y))), b.y);
+        r.z = __fmul_rn(__fdiv_rn(a.z, __fadd_rn(1.0f, expf(-a.z))), b.z); r.w = __fmul_rn(__fdiv_rn(a.w, __fadd_rn(1.0f, expf(-a.w))), b.w);
+        y[i] = r;
+        if (QUANT) {                                            // n4 % 32 == 0: whole warps leave the loop together
+            const int64_t e = i * 4, row = e / K, b32 = (e - row * K) >> 5;
+            q8_1_soa_emit(r, (int) (i & 7), row, b32, K / 32, qs, ds);
+        }
     }
 }
 static unsigned ew_blocks(int64_t n) { int64_t b = (n + 255) / 256; if (b > 148 * 16) b = 148 * 16; return (unsigned) (b < 1 ? 1 : b); }
 cudaError_t launch_silu_f32(const float * x, float * y, int64_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    silu_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(x, y, n);
-    return cudaGetLastError();
+    return pdl_launch(silu_f32_kernel, dim3(ew_blocks(n)), dim3(256), st, x, y, n);
 }
-cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, cudaStream_t st) {
+// n % 4 == 0, 16-byte aligned pointers; qs != NULL: also quantise rows of K elements (K % 128 == 0)
+cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    silu_mul_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(g, u, y, n);
-    return cudaGetLastError();
+    const int64_t n4 = n / 4;
+    if (qs) return pdl_launch(silu_mul_f32_kernel<true>, dim3(ew_blocks(n4)), dim3(256), st, (const float4 *) g, (const float4 *) u, (float4 *) y, n4, K, qs, ds);
+    return pdl_launch(silu_mul_f32_kernel<false>, dim3(ew_blocks(n4)), dim3(256), st, (const float4 *) g, (const float4 *) u, (float4 *) y, n4, K, qs, ds);
+}
+
+// ------------------------------------------------------------------------------------------------ RMS_NORM * weight (+ q8_1)
+// RMS_NORM followed by the in-place MUL with the norm weight (build_norm, llama-graph.cpp): one CTA per row; y = fl(fl(x * scale) * w), the
+// two roundings of the separate kernels.  QUANT (ne00 % 128 == 0): the row is also written as q8_1 for the MUL_MATs that read it next.
+template <bool QUANT>
+__global__ void __launch_bounds__(256)
+rms_norm_mul_kernel(const float * __restrict__ x, const float * __restrict__ w, float * __restrict__ y, const int64_t ne00, const int64_t xs, const int64_t ys,
+                    const float eps, int8_t * __restrict__ qs, ActDS * __restrict__ ds) {
+    __shared__ double sh[8];
+    PDL_PROLOGUE();
+    const int64_t row = blockIdx.x;
+    const float4 * xr = (const float4 *) (x + row * xs);
+    float4 * yr = (float4 *) (y + row * ys);
+    const int64_t n4 = ne00 / 4;
+    double sum = 0.0;
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+        const float4 v = xr[i];
+        sum += (double) __fmul_rn(v.x, v.x) + (double) __fmul_rn(v.y, v.y) + (double) __fmul_rn(v.z, v.z) + (double) __fmul_rn(v.w, v.w);
+    }
+    {   // block sum, same order in every thread (as block_reduce of norm_ops.cu)
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (lane == 0) sh[warp] = sum;
+        __syncthreads();
+        sum = sh[0];
+        for (int i = 1; i < 8; i++) sum += sh[i];
+    }
+    const float mean = (float) (sum / (double) ne00);
+    const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+        const float4 v = xr[i], g = ((const float4 *) w)[i];
+        const float4 r = make_float4(__fmul_rn(__fmul_rn(v.x, scale), g.x), __fmul_rn(__fmul_rn(v.y, scale), g.y),
+                                     __fmul_rn(__fmul_rn(v.z, scale), g.z), __fmul_rn(__fmul_rn(v.w, scale), g.w));
+        yr[i] = r;
+        if (QUANT) q8_1_soa_emit(r, (int) (i & 7), row, i >> 3, ne00 / 32, qs, ds);
+    }
+}
+cudaError_t launch_rms_norm_mul(const float * x, const float * w, float * y, int64_t ne00, int64_t rows, int64_t xs, int64_t ys, float eps,
+                                int8_t * qs, ActDS * ds, cudaStream_t st) {
+    if (rows == 0 || ne00 == 0) return cudaSuccess;
+    if (rows > 0x7fffffff) return cudaErrorInvalidValue;
+    if (qs) return pdl_launch(rms_norm_mul_kernel<true>, dim3((unsigned) rows), dim3(256), st, x, w, y, ne00, xs, ys, eps, qs, ds);
+    return pdl_launch(rms_norm_mul_kernel<false>, dim3((unsigned) rows), dim3(256), st, x, w, y, ne00, xs, ys, eps, qs, ds);
 }
 
 // ------------------------------------------------------------------------------------------------ ROPE (f32; normal and NeoX pairing)
 // one thread per rotated pair (or per passed-through pair beyond n_dims).  theta of pair k = pos * theta_scale^k, built by k successive
 // f32 multiplications exactly as the reference's cache loop does (ggml-cpu.c:8638-8647), so the angle is the reference's bit for bit.
 __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
+    PDL_PROLOGUE();
     const int64_t half = p.ne[0] / 2;
     const int64_t total = half * p.ne[1] * p.ne[2] * p.ne[3];
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
@@ -78,8 +175,7 @@ __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
 cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st) {
     const int64_t total = p.ne[0] / 2 * p.ne[1] * p.ne[2] * p.ne[3];
     if (total == 0) return cudaSuccess;
-    rope_f32_kernel<<<ew_blocks(total), 256, 0, st>>>(p);
-    return cudaGetLastError();
+    return pdl_launch(rope_f32_kernel, dim3(ew_blocks(total)), dim3(256), st, p);
 }
 
 // ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
@@ -91,6 +187,7 @@ template <> __device__ __forceinline__ float  cvt_el<__half, float>(__half v)  {
 template <> __device__ __forceinline__ __half cvt_el<__half, __half>(__half v) { return v; }
 template <typename TS, typename TD>
 __global__ void __launch_bounds__(256) cpy_kernel(const CpyArgs p, const int64_t n) {
+    PDL_PROLOGUE();
     char * const y = p.dyn ? *p.dyn : p.y;
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t t = i;
@@ -109,15 +206,36 @@ cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream
     const int64_t n = p.nes[0] * p.nes[1] * p.nes[2] * p.nes[3];
     if (n == 0) return cudaSuccess;
     const unsigned b = ew_blocks(n);
-    if (!src_f16 && !dst_f16) cpy_kernel<float, float><<<b, 256, 0, st>>>(p, n);
-    else if (!src_f16 && dst_f16) cpy_kernel<float, __half><<<b, 256, 0, st>>>(p, n);
-    else if (src_f16 && !dst_f16) cpy_kernel<__half, float><<<b, 256, 0, st>>>(p, n);
-    else cpy_kernel<__half, __half><<<b, 256, 0, st>>>(p, n);
-    return cudaGetLastError();
+    if (!src_f16 && !dst_f16) return pdl_launch(cpy_kernel<float, float>, dim3(b), dim3(256), st, p, n);
+    if (!src_f16 && dst_f16)  return pdl_launch(cpy_kernel<float, __half>, dim3(b), dim3(256), st, p, n);
+    if (src_f16 && !dst_f16)  return pdl_launch(cpy_kernel<__half, float>, dim3(b), dim3(256), st, p, n);
+    return pdl_launch(cpy_kernel<__half, __half>, dim3(b), dim3(256), st, p, n);
+}
+
+// CONT of f32 into contiguous rows of K elements that a MUL_MAT reads next (the head merge in front of the attention output projection):
+// float4 along dim 0 of both sides (src ne[0] % 4 == 0), the row also written as q8_1 (K % 128 == 0)
+__global__ void __launch_bounds__(256) cont_quant_kernel(const CpyArgs p, const int64_t n4, const int64_t K, int8_t * __restrict__ qs, ActDS * __restrict__ ds) {
+    PDL_PROLOGUE();
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        int64_t t = i * 4;
+        const int64_t s0 = t % p.nes[0]; t /= p.nes[0];
+        const int64_t s1 = t % p.nes[1]; t /= p.nes[1];
+        const int64_t s2 = t % p.nes[2]; const int64_t s3 = t / p.nes[2];
+        const float4 v = *(const float4 *) (p.x + s0 * 4 + s1 * p.nbs[1] + s2 * p.nbs[2] + s3 * p.nbs[3]);
+        ((float4 *) p.y)[i] = v;
+        const int64_t e = i * 4, row = e / K, b32 = (e - row * K) >> 5;
+        q8_1_soa_emit(v, (int) (i & 7), row, b32, K / 32, qs, ds);
+    }
+}
+cudaError_t launch_cont_quant(const CpyArgs & p, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st) {
+    const int64_t n = p.nes[0] * p.nes[1] * p.nes[2] * p.nes[3];
+    if (n == 0) return cudaSuccess;
+    return pdl_launch(cont_quant_kernel, dim3(ew_blocks(n / 4)), dim3(256), st, p, n / 4, K, qs, ds);
 }
 
 // ------------------------------------------------------------------------------------------------ GET_ROWS (f32 rows, i32 ids)
 __global__ void __launch_bounds__(256) get_rows_f32_kernel(const GetRowsArgs p, const int64_t n) {
+    PDL_PROLOGUE();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t t = i;
         const int64_t i0 = t % p.ne00; t /= p.ne00;
@@ -132,8 +250,7 @@ __global__ void __launch_bounds__(256) get_rows_f32_kernel(const GetRowsArgs p, 
 cudaError_t launch_get_rows_f32(const GetRowsArgs & p, cudaStream_t st) {
     const int64_t n = p.ne00 * p.ne10 * p.ne11 * p.ne12;
     if (n == 0) return cudaSuccess;
-    get_rows_f32_kernel<<<ew_blocks(n), 256, 0, st>>>(p, n);
-    return cudaGetLastError();
+    return pdl_launch(get_rows_f32_kernel, dim3(ew_blocks(n)), dim3(256), st, p, n);
 }
 
 // ------------------------------------------------------------------------------------------------ MUL_MAT, f16 src0 x f32 src1 -> f32
@@ -144,6 +261,7 @@ __device__ __forceinline__ float rnd_h(float v) { return __half2float(__float2ha
 // few columns (decode): one warp per output row, the row's f16 values read once and used for up to 8 columns
 template <int NC>
 __global__ void __launch_bounds__(128) mm_f16_vec_kernel(const MmF16Args p) {
+    PDL_PROLOGUE();
     const int lane = threadIdx.x & 31;
     const int64_t m = (int64_t) blockIdx.x * 4 + (threadIdx.x >> 5);
     if (m >= p.M) return;
@@ -256,9 +374,9 @@ cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st) {
     if (batch > 65535) return cudaErrorInvalidValue;
     if (p.N <= 16) {
         dim3 grid((unsigned) ((p.M + 3) / 4), (unsigned) batch);
-        if (p.N == 1) mm_f16_vec_kernel<1><<<grid, 128, 0, st>>>(p);
-        else if (p.N <= 4) mm_f16_vec_kernel<4><<<grid, 128, 0, st>>>(p);
-        else mm_f16_vec_kernel<8><<<grid, 128, 0, st>>>(p);
+        if (p.N == 1) return pdl_launch(mm_f16_vec_kernel<1>, grid, dim3(128), st, p);
+        if (p.N <= 4) return pdl_launch(mm_f16_vec_kernel<4>, grid, dim3(128), st, p);
+        return pdl_launch(mm_f16_vec_kernel<8>, grid, dim3(128), st, p);
     } else {
         const int64_t gy = (p.N + MMT - 1) / MMT;
         if (gy > 65535) return cudaErrorInvalidValue;

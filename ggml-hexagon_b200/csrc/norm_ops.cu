@@ -77,6 +77,10 @@ soft_max_f32_kernel(const float * __restrict__ x, const void * __restrict__ mask
                     const int64_t ne02, const float scale, const float max_bias, const float m0, const float m1, const uint32_t n_head_log2) {
     __shared__ double shd[8];
     __shared__ float shf[8];
+#if __CUDA_ARCH__ >= 900
+    cudaTriggerProgrammaticLaunchCompletion();
+    cudaGridDependencySynchronize();
+#endif
     const int64_t row = blockIdx.x;
     const uint32_t h = (uint32_t) ((row / ne01) % ne02);
     const float slope = max_bias > 0.0f ? (h < n_head_log2 ? powf(m0, (float) (h + 1)) : powf(m1, (float) (2 * (h - n_head_log2) + 1))) : 1.0f;
@@ -106,9 +110,14 @@ cudaError_t launch_soft_max_f32(const float * x, const void * mask, bool mask_f1
     const uint32_t n_head = (uint32_t) ne[2];
     const uint32_t n_head_log2 = 1u << (uint32_t) floor(log2((double) n_head));
     const float m0 = powf(2.0f, -(max_bias) / n_head_log2), m1 = powf(2.0f, -(max_bias / 2.0f) / n_head_log2);
-    if (mask_f16) soft_max_f32_kernel<true><<<(unsigned) rows, 256, 0, st>>>(x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
-    else          soft_max_f32_kernel<false><<<(unsigned) rows, 256, 0, st>>>(x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) rows); cfg.blockDim = dim3(256); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    if (mask_f16) return cudaLaunchKernelEx(&cfg, soft_max_f32_kernel<true>, x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
+    return cudaLaunchKernelEx(&cfg, soft_max_f32_kernel<false>, x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
 }
 
 // ---- POOL_2D: one thread per output element; taps summed ky-outer / kx-inner as the reference (bit-exact averages)

@@ -1081,25 +1081,131 @@ extern "C" int b200_mulmat(b200_handle h, const b200_tensor * s0, const b200_ten
     return run_with_staging(c, B200_OP_MUL_MAT, s0, s1, d);
 }
 
+// ---- producer fusions of a Llama layer (graph_ops.cu).  Each one replaces launches the node list asks for by ONE kernel with the same
+// roundings, and only where the skipped intermediate is overwritten in place by the pair's second node (so nothing can observe it).
+static bool graph_fuse_enabled() { const char * e = getenv("B200_GRAPH_FUSE"); return !(e && atoi(e) == 0); }      // (read per call: tests flip it)
+static bool same_shape(const b200_tensor & a, const b200_tensor & b) { for (int i = 0; i < 4; i++) if (a.ne[i] != b.ne[i]) return false; return true; }
+static bool al16(const void * p) { return ((uintptr_t) p & 15) == 0; }
+// a quantised MUL_MAT that reads the single f32 column x[K] next: its q8_1 activations can be written by the producer of x
+static bool reads_vec_q(const b200_node & nd, const void * x, int64_t K) {
+    return nd.dst.op == B200_OP_MUL_MAT && is_qweight(nd.src0.type) && nd.src1.type == T_F32 && nd.src1.data == x && nd.src0.ne[0] == K &&
+           nd.src1.ne[0] == K && nd.src1.ne[1] == 1 && nd.src1.ne[2] == 1 && nd.src1.ne[3] == 1 && nd.src1.nb[0] == 4;
+}
+static void set_qcache(Ctx * c, const b200_tensor & d) { c->q_ptr = d.data; c->q_K = d.ne[0]; c->q_N = 1; c->q_stride = d.nb[1]; c->q_kind = 0; }
+// RMS_NORM x -> X ; MUL X, w -> X (in place, w one row): one kernel; [+ q8_1 of X when a vector MUL_MAT reads it next]
+static int try_rms_norm_mul(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
+    if (!graph_fuse_enabled() || c->rs_on || i + 1 >= n) return 0;
+    const b200_node & r = nodes[i]; const b200_node & m = nodes[i + 1];
+    if (m.dst.op != B200_OP_MUL || m.src0.data != r.dst.data || m.dst.data != r.dst.data) return 0;
+    if (r.src0.type != T_F32 || r.dst.type != T_F32 || m.src1.type != T_F32 || m.dst.type != T_F32) return 0;
+    if (!same_shape(r.src0, r.dst) || !same_shape(m.dst, r.dst) || !same_shape(m.src0, r.dst)) return 0;
+    const int64_t ne00 = r.dst.ne[0], rows = r.dst.ne[1];
+    if (r.dst.ne[2] != 1 || r.dst.ne[3] != 1 || ne00 % 4 || r.src0.nb[0] != 4 || r.dst.nb[0] != 4 || m.dst.nb[0] != 4 || m.dst.nb[1] != r.dst.nb[1]) return 0;
+    if (m.src1.ne[0] != ne00 || m.src1.ne[1] != 1 || m.src1.ne[2] != 1 || m.src1.ne[3] != 1 || m.src1.nb[0] != 4) return 0;
+    if (!al16(r.src0.data) || !al16(r.dst.data) || !al16(m.src1.data) || (r.src0.nb[1] & 15) || (r.dst.nb[1] & 15)) return 0;
+    const float eps = f32_param(&r.dst, 0);
+    if (!(eps >= 0.0f)) return 0;
+    const bool quant = rows == 1 && ne00 % 128 == 0 && i + 2 < n && reads_vec_q(nodes[i + 2], r.dst.data, ne00);
+    if (quant) { int rc = ensure_act(c, ne00 / 32); if (rc) return rc; }
+    CU(launch_rms_norm_mul((const float *) r.src0.data, (const float *) m.src1.data, (float *) r.dst.data, ne00, rows, r.src0.nb[1] / 4, r.dst.nb[1] / 4, eps,
+                           quant ? c->act_qs : nullptr, quant ? c->act_ds : nullptr, c->st)); c->launches++;
+    wrote(c, &r.dst);
+    if (quant) set_qcache(c, m.dst);
+    *used = 2;
+    return 0;
+}
+// SILU G -> X ; [MUL_MAT ... -> U] ; MUL X, U -> X (in place): the SILU is folded into the MUL; [+ q8_1 of X for the vector MUL_MAT that follows]
+static int try_silu_mul(Ctx * c, const b200_node * nodes, int i, int n, int * used, int * deferred_mul) {
+    if (!graph_fuse_enabled() || c->rs_on) return 0;
+    const b200_node & sn = nodes[i];
+    if (sn.dst.op_params[0] != B200_UNARY_SILU || sn.src0.type != T_F32 || sn.dst.type != T_F32) return 0;
+    int j = i + 1;
+    if (j < n && nodes[j].dst.op == B200_OP_MUL_MAT) {          // the up projection in between must not touch G or X
+        const b200_node & u = nodes[j];
+        const int64_t xs = nelems(&sn.dst) * 4, us = nelems(&u.dst) * 4;
+        if (u.src1.data == sn.dst.data || overlap(u.dst.data, us, sn.dst.data, xs) || overlap(u.dst.data, us, sn.src0.data, xs)) return 0;
+        j++;
+    }
+    if (j >= n) return 0;
+    const b200_node & m = nodes[j];
+    if (m.dst.op != B200_OP_MUL || m.src0.data != sn.dst.data || m.dst.data != sn.dst.data) return 0;
+    if (m.src1.type != T_F32 || m.dst.type != T_F32 || !same_shape(m.src0, sn.dst) || !same_shape(m.src1, sn.dst) || !same_shape(m.dst, sn.dst) || !same_shape(sn.src0, sn.dst)) return 0;
+    if (!contiguous_f32_t(&sn.src0) || !contiguous_f32_t(&sn.dst) || !contiguous_f32_t(&m.src1)) return 0;
+    const int64_t tot = nelems(&sn.dst);
+    if (tot % 4 || !al16(sn.src0.data) || !al16(sn.dst.data) || !al16(m.src1.data)) return 0;
+    if (overlap(m.src1.data, tot * 4, sn.dst.data, tot * 4)) return 0;
+    if (j == i + 1) {           // adjacent: run the fused kernel now
+        const int64_t K = sn.dst.ne[0];
+        const bool quant = tot == K && K % 128 == 0 && j + 1 < n && reads_vec_q(nodes[j + 1], m.dst.data, K);
+        if (quant) { int rc = ensure_act(c, K / 32); if (rc) return rc; }
+        CU(launch_silu_mul_f32((const float *) sn.src0.data, (const float *) m.src1.data, (float *) m.dst.data, tot, K, quant ? c->act_qs : nullptr, quant ? c->act_ds : nullptr, c->st)); c->launches++;
+        wrote(c, &m.dst);
+        if (quant) set_qcache(c, m.dst);
+        *used = 2;
+    } else {                    // one MUL_MAT in between: skip the SILU now, the MUL node (index j) runs the fused kernel
+        *deferred_mul = j; *used = 1;
+    }
+    return 0;
+}
+// CONT -> contiguous X[K] read next by a vector MUL_MAT: copy + q8_1 in one kernel
+static int try_cont_quant(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
+    if (!graph_fuse_enabled() || c->rs_on || i + 1 >= n) return 0;
+    const b200_node & cn = nodes[i];
+    if (cn.src0.type != T_F32 || cn.dst.type != T_F32 || (cn.dst.flags & B200_TENSOR_DYNAMIC)) return 0;
+    const int64_t K = cn.dst.ne[0];
+    if (nelems(&cn.dst) != K || nelems(&cn.src0) != K || K % 128 || !contiguous_f32_t(&cn.dst) || !reads_vec_q(nodes[i + 1], cn.dst.data, K)) return 0;
+    if (cn.src0.nb[0] != 4 || cn.src0.ne[0] % 4 || !al16(cn.src0.data) || !al16(cn.dst.data) || ((cn.src0.nb[1] | cn.src0.nb[2] | cn.src0.nb[3]) & 15)) return 0;
+    int rc = ensure_act(c, K / 32); if (rc) return rc;
+    CpyArgs a{};
+    a.x = (const char *) cn.src0.data; a.y = (char *) cn.dst.data;
+    for (int k = 0; k < 4; k++) { a.nes[k] = cn.src0.ne[k]; a.nbs[k] = cn.src0.nb[k]; a.ned[k] = cn.dst.ne[k]; a.nbd[k] = cn.dst.nb[k]; }
+    CU(launch_cont_quant(a, K, c->act_qs, c->act_ds, c->st)); c->launches++;
+    wrote(c, &cn.dst);
+    set_qcache(c, cn.dst);
+    *used = 1;
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------------ graph compute
 static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
     static const bool fuse = !(getenv("B200_FUSE") && atoi(getenv("B200_FUSE")) == 0);
     c->in_graph = true; c->q_ptr = nullptr; c->rs_ops = 0; c->dyn_i = 0;
     int rc = 0;
+    int silu_mul_at = -1;            // index of a MUL node that also applies the SILU skipped two nodes earlier (try_silu_mul)
     for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
         int used = 1;
         switch (d.op) {
             case B200_OP_NONE: break;
             case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
-            case B200_OP_RMS_NORM: rc = rms_norm_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_RMS_NORM: {
+                int u = 0; rc = try_rms_norm_mul(c, nodes, i, n, &u);
+                if (!rc && u) used = u; else if (!rc) rc = rms_norm_dev(c, &nodes[i].src0, &d);
+            } break;
             case B200_OP_SOFT_MAX: rc = soft_max_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
             case B200_OP_POOL_2D:  rc = pool_2d_dev(c, &nodes[i].src0, &d); break;
-            case B200_OP_MUL:      rc = mul_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
-            case B200_OP_UNARY:    rc = unary_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_MUL:
+                if (i == silu_mul_at) {         // SILU(G) * U -> X; G is the skipped SILU's input, X its output = this node's src0 = dst
+                    const b200_node & sn = nodes[i - 2];
+                    const int64_t K = d.ne[0], tot = nelems(&d);
+                    const bool quant = tot == K && K % 128 == 0 && i + 1 < n && reads_vec_q(nodes[i + 1], d.data, K);
+                    if (quant) rc = ensure_act(c, K / 32);
+                    if (!rc) { CU(launch_silu_mul_f32((const float *) sn.src0.data, (const float *) nodes[i].src1.data, (float *) d.data, tot, K,
+                                                      quant ? c->act_qs : nullptr, quant ? c->act_ds : nullptr, c->st)); c->launches++; }
+                    wrote(c, &d);
+                    if (!rc && quant) set_qcache(c, d);
+                    silu_mul_at = -1;
+                } else rc = mul_dev(c, &nodes[i].src0, &nodes[i].src1, &d);
+                break;
+            case B200_OP_UNARY: {
+                int u = 0, dm = -1; rc = try_silu_mul(c, nodes, i, n, &u, &dm);
+                if (!rc && u) { used = u; if (dm >= 0) silu_mul_at = dm; } else if (!rc) rc = unary_dev(c, &nodes[i].src0, &d);
+            } break;
             case B200_OP_ROPE:     rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
-            case B200_OP_DUP: case B200_OP_CONT: case B200_OP_CPY:      // (ggml_cpy(a, b): the node is a view of b, so dst carries b's layout)
-                                   rc = cpy_dev(c, &nodes[i].src0, &d); break;
+            case B200_OP_DUP: case B200_OP_CONT: case B200_OP_CPY: {    // (ggml_cpy(a, b): the node is a view of b, so dst carries b's layout)
+                int u = 0; if (d.op == B200_OP_CONT) rc = try_cont_quant(c, nodes, i, n, &u);
+                if (!rc && !u) rc = cpy_dev(c, &nodes[i].src0, &d);
+            } break;
             case B200_OP_GET_ROWS: rc = get_rows_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
             case B200_OP_MUL_MAT: {
                 if (nodes[i].src0.type == T_F16) { rc = mm_f16_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break; }

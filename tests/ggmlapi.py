@@ -58,6 +58,12 @@ def lib(variant=None):
         "ggml_rms_norm": (VP, [VP, VP, C.c_float]), "ggml_soft_max": (VP, [VP, VP]),
         "ggml_soft_max_ext": (VP, [VP, VP, VP, C.c_float, C.c_float]),
         "ggml_view_1d": (VP, [VP, VP, I64, SZ]), "ggml_view_2d": (VP, [VP, VP, I64, I64, SZ, SZ]),
+        "ggml_view_3d": (VP, [VP, VP, I64, I64, I64, SZ, SZ, SZ]),
+        "ggml_mul": (VP, [VP, VP, VP]), "ggml_silu": (VP, [VP, VP]), "ggml_cpy": (VP, [VP, VP, VP]), "ggml_cont": (VP, [VP, VP]),
+        "ggml_cont_2d": (VP, [VP, VP, I64, I64]), "ggml_reshape_2d": (VP, [VP, VP, I64, I64]), "ggml_reshape_3d": (VP, [VP, VP, I64, I64, I64]),
+        "ggml_permute": (VP, [VP, VP, C.c_int, C.c_int, C.c_int, C.c_int]), "ggml_transpose": (VP, [VP, VP]),
+        "ggml_rope_ext": (VP, [VP, VP, VP, VP, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),
+        "ggml_get_rows": (VP, [VP, VP, VP]), "ggml_element_size": (SZ, [VP]),
         "ggml_new_graph": (VP, [VP]), "ggml_build_forward_expand": (None, [VP, VP]),
         "ggml_backend_load": (VP, [C.c_char_p]), "ggml_backend_reg_dev_count": (SZ, [VP]), "ggml_backend_reg_dev_get": (VP, [VP, SZ]),
         "ggml_backend_reg_name": (C.c_char_p, [VP]), "ggml_backend_reg_get_proc_address": (VP, [VP, C.c_char_p]),

@@ -233,7 +233,8 @@ def test_plugin_supports_op_answers(plug):
     assert G.ggml_backend_dev_supports_op(dev, w)                        # GGML_OP_NONE leaf (tests call it on leaves)
     xh = c.tensor(GA.F16, 4096, 3)
     wf = c.tensor(GA.F16, 4096, 64)
-    assert not G.ggml_backend_dev_supports_op(dev, G.ggml_mul_mat(c.ctx, wf, x))      # f16 weights: declined, never emulated
+    assert G.ggml_backend_dev_supports_op(dev, G.ggml_mul_mat(c.ctx, wf, x))          # f16 src0 = the KV cache in attention (graph_ops.cu)
+    assert not G.ggml_backend_dev_supports_op(dev, G.ggml_mul_mat(c.ctx, wf, xh))     # f16 src1: declined, never emulated
     a, b = c.tensor(GA.F32, 4096, 5), c.tensor(GA.F32, 4096, 1)
     assert G.ggml_backend_dev_supports_op(dev, G.ggml_add(c.ctx, a, b))
     assert not G.ggml_backend_dev_supports_op(dev, G.ggml_add(c.ctx, xh, xh))

@@ -1,0 +1,3 @@
+cd /root/repo
+python -m pytest tests/test_gpu_graph_ops.py tests/test_gpu_plugin.py tests/test_gpu_norm_ops.py -x -q -m gpu 2>&1 | tail -15
+SKIP_CPU=1 NKVO=0 bash tools/gpu_llama_bench.sh r02_l
