@@ -890,7 +890,9 @@ static bool can_fuse_add(const b200_node & mm, const b200_node & ad, FusedAdd * 
     if (ad.src0.data == mm.dst.data) other = ad.src1.data; else if (ad.src1.data == mm.dst.data) other = ad.src0.data; else return false;
     const int64_t bytes = M * 4, K4 = mm.src0.ne[0] * 4;
     // the add result must not land on anything other CTAs of the same launch still read or write
-    if (overlap(ad.dst.data, bytes, mm.src1.data, K4) || overlap(ad.dst.data, bytes, mm.dst.data, bytes)) return false;
+    // (the ADD in place on the product -- ad.dst == mm.dst exactly, as ggml-alloc lays out `cur = ggml_add(cur, residual)` -- is fine: the
+    //  thread that stores the product stores the sum to the same address right after it)
+    if (overlap(ad.dst.data, bytes, mm.src1.data, K4) || (ad.dst.data != mm.dst.data && overlap(ad.dst.data, bytes, mm.dst.data, bytes))) return false;
     if (other != ad.dst.data && overlap(ad.dst.data, bytes, other, bytes)) return false;
     if (overlap(mm.dst.data, bytes, other, bytes) || overlap(mm.dst.data, bytes, mm.src1.data, K4)) return false;
     fa->src = (const float *) other; fa->dst = (float *) ad.dst.data;
@@ -1384,7 +1386,16 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         if (c->graphs.size() > 64) { for (auto & kv : c->graphs) cudaGraphExecDestroy(kv.second.exec); c->graphs.clear(); }
         it = c->graphs.emplace(key, ge).first;
     }
+    static const bool time_it = getenv("B200_GRAPH_TIME") != nullptr;          // development: device time of each replay, to stderr
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    if (time_it) { cudaEventCreate(&t0); cudaEventCreate(&t1); cudaEventRecord(t0, c->st); }
     CU(cudaGraphLaunch(it->second.exec, c->st));
+    if (time_it) {
+        cudaEventRecord(t1, c->st); cudaEventSynchronize(t1);
+        float ms = 0; cudaEventElapsedTime(&ms, t0, t1);
+        fprintf(stderr, "[b200] graph replay: %d nodes, %lld kernels, %.3f ms\n", n, (long long) it->second.n_kernels, ms);
+        cudaEventDestroy(t0); cudaEventDestroy(t1);
+    }
     c->launches += it->second.n_kernels;      // a replay runs exactly the kernels captured
     return 0;
 }
