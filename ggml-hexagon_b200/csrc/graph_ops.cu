@@ -202,14 +202,61 @@ __global__ void __launch_bounds__(256) cpy_kernel(const CpyArgs p, const int64_t
         *(TD *) (y + d0 * p.nbd[0] + d1 * p.nbd[1] + d2 * p.nbd[2] + d3 * p.nbd[3]) = cvt_el<TS, TD>(v);
     }
 }
+// fast paths of the shapes a Llama graph stores with (everything else takes the generic kernel above):
+//  flat      both sides contiguous in the same logical order (K rows into the cache): 4 elements per thread
+//  transpose 2-D, src contiguous along dim 1, dst along dim 0 (V^T into the cache at prefill): 32 x 32 tiles through shared memory
+template <typename TS, typename TD>
+__global__ void __launch_bounds__(256) cpy_flat4_kernel(const CpyArgs p, const int64_t n4) {
+    PDL_PROLOGUE();
+    char * const y = p.dyn ? *p.dyn : p.y;
+    const bool al = ((uintptr_t) y & (sizeof(TD) * 4 - 1)) == 0;        // (a dynamic destination's alignment is only known now)
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        TS v[4]; TD o[4];
+        if (sizeof(TS) == 4) *(float4 *) v = ((const float4 *) p.x)[i]; else *(uint2 *) v = ((const uint2 *) p.x)[i];
+        #pragma unroll
+        for (int k = 0; k < 4; k++) o[k] = cvt_el<TS, TD>(v[k]);
+        if (!al) { for (int k = 0; k < 4; k++) ((TD *) y)[i * 4 + k] = o[k]; }
+        else if (sizeof(TD) == 4) ((float4 *) y)[i] = *(float4 *) o; else ((uint2 *) y)[i] = *(uint2 *) o;
+    }
+}
+template <typename TS, typename TD>
+__global__ void __launch_bounds__(256) cpy_transpose_kernel(const CpyArgs p) {
+    __shared__ float tile[32][33];
+    PDL_PROLOGUE();
+    char * const y = p.dyn ? *p.dyn : p.y;
+    const int64_t i0 = (int64_t) blockIdx.x * 32, i1 = (int64_t) blockIdx.y * 32;      // dims 0 and 1 of the (shared) logical shape
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {           // read: tx walks dim 1 (contiguous in src)
+        const int64_t a0 = i0 + r, a1 = i1 + tx;
+        if (a0 < p.nes[0] && a1 < p.nes[1]) tile[r][tx] = cvt_el<TS, float>(*(const TS *) (p.x + a0 * p.nbs[0] + a1 * p.nbs[1]));
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {           // write: tx walks dim 0 (contiguous in dst)
+        const int64_t a0 = i0 + tx, a1 = i1 + r;
+        if (a0 < p.nes[0] && a1 < p.nes[1]) *(TD *) (y + a0 * p.nbd[0] + a1 * p.nbd[1]) = cvt_el<float, TD>(tile[tx][r]);
+    }
+}
+template <typename T> static bool logical_contig(const int64_t * ne, const int64_t * nb) {
+    int64_t s = sizeof(T);
+    for (int i = 0; i < 4; i++) { if (ne[i] != 1 && nb[i] != s) return false; s *= ne[i]; }
+    return true;
+}
+template <typename TS, typename TD>
+static cudaError_t launch_cpy_t(const CpyArgs & p, int64_t n, cudaStream_t st) {
+    if (n % 4 == 0 && logical_contig<TS>(p.nes, p.nbs) && logical_contig<TD>(p.ned, p.nbd) && ((uintptr_t) p.x & 15) == 0)
+        return pdl_launch(cpy_flat4_kernel<TS, TD>, dim3(ew_blocks(n / 4)), dim3(256), st, p, n / 4);
+    if (p.nes[2] == 1 && p.nes[3] == 1 && p.ned[2] == 1 && p.ned[3] == 1 && p.nes[0] == p.ned[0] && p.nes[1] == p.ned[1] &&
+        p.nbs[1] == (int64_t) sizeof(TS) && p.nbd[0] == (int64_t) sizeof(TD) && p.nes[0] >= 32 && p.nes[1] >= 32 && (p.nes[1] + 31) / 32 <= 65535)
+        return pdl_launch(cpy_transpose_kernel<TS, TD>, dim3((unsigned) ((p.nes[0] + 31) / 32), (unsigned) ((p.nes[1] + 31) / 32)), dim3(256), st, p);
+    return pdl_launch(cpy_kernel<TS, TD>, dim3(ew_blocks(n)), dim3(256), st, p, n);
+}
 cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream_t st) {
     const int64_t n = p.nes[0] * p.nes[1] * p.nes[2] * p.nes[3];
     if (n == 0) return cudaSuccess;
-    const unsigned b = ew_blocks(n);
-    if (!src_f16 && !dst_f16) return pdl_launch(cpy_kernel<float, float>, dim3(b), dim3(256), st, p, n);
-    if (!src_f16 && dst_f16)  return pdl_launch(cpy_kernel<float, __half>, dim3(b), dim3(256), st, p, n);
-    if (src_f16 && !dst_f16)  return pdl_launch(cpy_kernel<__half, float>, dim3(b), dim3(256), st, p, n);
-    return pdl_launch(cpy_kernel<__half, __half>, dim3(b), dim3(256), st, p, n);
+    if (!src_f16 && !dst_f16) return launch_cpy_t<float, float>(p, n, st);
+    if (!src_f16 && dst_f16)  return launch_cpy_t<float, __half>(p, n, st);
+    if (src_f16 && !dst_f16)  return launch_cpy_t<__half, float>(p, n, st);
+    return launch_cpy_t<__half, __half>(p, n, st);
 }
 
 // CONT of f32 into contiguous rows of K elements that a MUL_MAT reads next (the head merge in front of the attention output projection):
@@ -303,67 +350,102 @@ __global__ void __launch_bounds__(128) mm_f16_vec_kernel(const MmF16Args p) {
     }
 }
 
-// many columns (prefill): 64 x 64 output tile per CTA of 4 warps, K in steps of 32 staged through shared memory as f16 (src1 rounded to f16
-// on the way in, which is what the reference does before its dot products), warp-level HMMA with f32 accumulators (2 x 2 fragments per warp).
-// This is the attention GEMM beside the hot path (2 x 2.1 GFLOP per layer at pp512 against 26 GFLOP of weight GEMMs), not the weight GEMM.
-#define MMT 64
+// many columns (prefill): 128 x 128 output tile per CTA of 8 warps (4 x 2, each 32 x 64 = 2 x 4 HMMA fragments with f32 accumulators), K in steps
+// of 32 staged through shared memory as f16 -- src1 is rounded to f16 on the way in, which is what the reference does before its dot products
+// -- with the next step's 16-byte global loads in flight while the current one is multiplied.  This is the attention GEMM beside the hot path
+// (2 x 2.1 GFLOP per layer at pp512 against 26 GFLOP of weight GEMMs), not the weight GEMM.
+#define MMT 128
 #define MMK 32
 #define MMLD (MMK + 8)
-__global__ void __launch_bounds__(128) mm_f16_tile_kernel(const MmF16Args p) {
+struct MmStage { uint4 a[2]; uint4 b[2]; };
+__device__ __forceinline__ uint4 mm_load_a(const char * row, const int64_t k, const int64_t K, const bool ok, const bool vec) {
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (!ok || k >= K) return r;
+    if (vec && k + 8 <= K) return *(const uint4 *) (row + k * 2);
+    __half h[8];
+    #pragma unroll
+    for (int i = 0; i < 8; i++) h[i] = k + i < K ? *(const __half *) (row + (k + i) * 2) : __float2half_rn(0.f);
+    return *(uint4 *) h;
+}
+__device__ __forceinline__ uint4 mm_load_b(const char * row, const int64_t k, const int64_t K, const bool ok, const bool vec) {
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (!ok || k >= K) return r;
+    float f[8];
+    if (vec && k + 8 <= K) { *(float4 *) f = *(const float4 *) (row + k * 4); *(float4 *) (f + 4) = *(const float4 *) (row + k * 4 + 16); }
+    else {
+        #pragma unroll
+        for (int i = 0; i < 8; i++) f[i] = k + i < K ? *(const float *) (row + (k + i) * 4) : 0.f;
+    }
+    __half2 h[4];
+    #pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+    return *(uint4 *) h;
+}
+__global__ void __launch_bounds__(256) mm_f16_tile_kernel(const MmF16Args p) {
     using namespace nvcuda;
     __shared__ __align__(32) __half As[MMT * MMLD];
     __shared__ __align__(32) __half Bs[MMT * MMLD];
-    __shared__ __align__(32) float Cs[4][16 * 16];
+    PDL_PROLOGUE();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t m0 = (int64_t) blockIdx.x * MMT, n0 = (int64_t) blockIdx.y * MMT;
     const int64_t i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
     const char * ab = p.a + (i12 / p.r2) * p.nba[2] + (i13 / p.r3) * p.nba[3];
     const char * bb = p.b + i12 * p.nbb[2] + i13 * p.nbb[3];
     char * db = p.d + i12 * p.nbd[2] + i13 * p.nbd[3];
-    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][2];
+    const bool veca = (((uintptr_t) ab | (uintptr_t) p.nba[1]) & 15) == 0, vecb = (((uintptr_t) bb | (uintptr_t) p.nbb[1]) & 15) == 0;
+    // each thread moves two 8-element chunks of each operand per K step: chunk c -> row c / 4, k offset (c % 4) * 8
+    int rr[2], kc[2]; const char * arow[2]; const char * brow[2]; bool aok[2], bok[2];
+    #pragma unroll
+    for (int j = 0; j < 2; j++) {
+        const int c = threadIdx.x + j * 256;
+        rr[j] = c >> 2; kc[j] = (c & 3) * 8;
+        aok[j] = m0 + rr[j] < p.M; bok[j] = n0 + rr[j] < p.N;
+        arow[j] = ab + (m0 + rr[j]) * p.nba[1]; brow[j] = bb + (n0 + rr[j]) * p.nbb[1];
+    }
+    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][4];
     #pragma unroll
     for (int i = 0; i < 2; i++)
         #pragma unroll
-        for (int j = 0; j < 2; j++) wmma::fill_fragment(acc[i][j], 0.0f);
-    const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+        for (int j = 0; j < 4; j++) wmma::fill_fragment(acc[i][j], 0.0f);
+    const int wm = (warp >> 1) * 32, wn = (warp & 1) * 64;
+    MmStage st;
+    #pragma unroll
+    for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], kc[j], p.K, aok[j], veca); st.b[j] = mm_load_b(brow[j], kc[j], p.K, bok[j], vecb); }
     for (int64_t k0 = 0; k0 < p.K; k0 += MMK) {
-        for (int e = threadIdx.x; e < MMT * MMK; e += 128) {               // consecutive threads walk K: coalesced on both operands
-            const int r = e / MMK, kk = e % MMK;
-            const int64_t k = k0 + kk;
-            __half av = __float2half_rn(0.f), bv = av;
-            if (k < p.K) {
-                if (m0 + r < p.M) av = *(const __half *) (ab + (m0 + r) * p.nba[1] + k * 2);
-                if (n0 + r < p.N) bv = __float2half_rn(*(const float *) (bb + (n0 + r) * p.nbb[1] + k * 4));
-            }
-            As[r * MMLD + kk] = av; Bs[r * MMLD + kk] = bv;
-        }
+        #pragma unroll
+        for (int j = 0; j < 2; j++) { *(uint4 *) (As + rr[j] * MMLD + kc[j]) = st.a[j]; *(uint4 *) (Bs + rr[j] * MMLD + kc[j]) = st.b[j]; }
         __syncthreads();
+        if (k0 + MMK < p.K) {
+            #pragma unroll
+            for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], k0 + MMK + kc[j], p.K, aok[j], veca); st.b[j] = mm_load_b(brow[j], k0 + MMK + kc[j], p.K, bok[j], vecb); }
+        }
         #pragma unroll
         for (int kk = 0; kk < MMK; kk += 16) {
             wmma::fragment<wmma::matrix_a, 16, 16, 16, __half, wmma::row_major> fa[2];
-            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[2];
+            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[4];
             #pragma unroll
             for (int i = 0; i < 2; i++) wmma::load_matrix_sync(fa[i], As + (wm + i * 16) * MMLD + kk, MMLD);
             #pragma unroll
-            for (int j = 0; j < 2; j++) wmma::load_matrix_sync(fb[j], Bs + (wn + j * 16) * MMLD + kk, MMLD);
+            for (int j = 0; j < 4; j++) wmma::load_matrix_sync(fb[j], Bs + (wn + j * 16) * MMLD + kk, MMLD);
             #pragma unroll
             for (int i = 0; i < 2; i++)
                 #pragma unroll
-                for (int j = 0; j < 2; j++) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+                for (int j = 0; j < 4; j++) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
         }
         __syncthreads();
     }
-    // C fragment (m, n) -> dst[n][m]: staged per warp so that the store walks m (contiguous in dst) and respects the edges
+    // C fragment (m, n) -> dst[n][m]: staged per warp (in the A tile's memory, free now) so that the store walks m, contiguous in dst, and respects the edges
+    float * Cs = (float *) As + warp * 256;
     #pragma unroll
     for (int i = 0; i < 2; i++)
         #pragma unroll
-        for (int j = 0; j < 2; j++) {
-            wmma::store_matrix_sync(Cs[warp], acc[i][j], 16, wmma::mem_col_major);      // Cs[n * 16 + m]
+        for (int j = 0; j < 4; j++) {
+            wmma::store_matrix_sync(Cs, acc[i][j], 16, wmma::mem_col_major);      // Cs[n * 16 + m]
             __syncwarp();
             for (int e = lane; e < 256; e += 32) {
                 const int nn = e >> 4, mm = e & 15;
                 const int64_t m = m0 + wm + i * 16 + mm, n = n0 + wn + j * 16 + nn;
-                if (m < p.M && n < p.N) *(float *) (db + n * p.nbd[1] + m * 4) = Cs[warp][e];
+                if (m < p.M && n < p.N) *(float *) (db + n * p.nbd[1] + m * 4) = Cs[e];
             }
             __syncwarp();
         }
@@ -381,7 +463,7 @@ cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st) {
         const int64_t gy = (p.N + MMT - 1) / MMT;
         if (gy > 65535) return cudaErrorInvalidValue;
         dim3 grid((unsigned) ((p.M + MMT - 1) / MMT), (unsigned) gy, (unsigned) batch);
-        mm_f16_tile_kernel<<<grid, 128, 0, st>>>(p);
+        return pdl_launch(mm_f16_tile_kernel, grid, dim3(256), st, p);
     }
     return cudaGetLastError();
 }
