@@ -609,6 +609,50 @@ def plugin_e2e(model, steps, x_host):
     return res, logits
 
 
+def llama_bench(use_plugin, n_prompt=512, n_gen=128, reps=3):
+    """BASELINE.json's literal metric on its literal harness: the reference's own llama-bench, built unmodified into
+    oracle/_ref by `make -f oracle/Makefile.ref llama`, on a synthetic Llama-2-7B Q4_0 GGUF (tools/make_gguf.py; there are no model files
+    on the box), the ggml scheduler placing the graph.  use_plugin: libggml-b200.so through GGML_BACKEND_PATH, all layers offloaded;
+    otherwise the reference's CPU backend with every host core."""
+    import subprocess, tempfile
+    import pyref
+    d = pyref.ref_dir()
+    exe = os.path.join(d or "", "llama-bench")
+    if not d or not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/<variant>/llama-bench not built (make -f oracle/Makefile.ref llama)"}
+    tmp = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
+    gguf = os.path.join(tmp, "b200_bench_l7b_%d.gguf" % os.getpid())
+    try:
+        subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), gguf, "--preset", "7b"], check=True, capture_output=True, timeout=300)
+        env = dict(os.environ)
+        cmd = [exe, "-m", gguf, "-p", str(n_prompt), "-n", str(n_gen), "-r", str(reps), "-t", str(os.cpu_count() or 1), "-o", "jsonl"]
+        if use_plugin:
+            env["GGML_BACKEND_PATH"] = os.path.join(ROOT, "ggml-hexagon_b200", "lib", "libggml-b200.so")
+            cmd += ["-ngl", "99"]
+        else:
+            env.pop("GGML_BACKEND_PATH", None)
+            cmd += ["-ngl", "0"]
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
+        out = {"harness": "reference llama-bench, unmodified (oracle/_ref/%s)" % os.path.basename(d), "model": "synthetic llama 7B Q4_0 GGUF (3.56 GiB, random blocks)",
+               "backend": None, "reps": reps}
+        for l in r.stdout.splitlines():
+            try:
+                j = json.loads(l)
+            except ValueError:
+                continue
+            out["backend"] = j.get("backends")
+            key = ("pp%d" % j["n_prompt"]) if j["n_prompt"] else ("tg%d" % j["n_gen"])
+            out[key] = {"tokens_per_s": round(j["avg_ts"], 2), "stddev": round(j["stddev_ts"], 2)}
+        if r.returncode != 0 or not any(k.startswith(("pp", "tg")) for k in out):
+            out["unavailable"] = "llama-bench rc=%d: %s" % (r.returncode, (r.stderr or "")[-300:])
+        return out
+    except (subprocess.SubprocessError, OSError) as e:
+        return {"unavailable": "%s: %s" % (type(e).__name__, e)}
+    finally:
+        if os.path.exists(gguf):
+            os.remove(gguf)
+
+
 def cpu_baseline(model, budget_s):
     """reference ggml-cpu (oracle/_ref) on the host cores; falls back to the single-threaded C port only if _ref is absent"""
     import pyref
@@ -651,6 +695,8 @@ def run_reference(args, rank):
             "vs_baseline": None, "dtype": "q4_0 x q8_0 int8 dot, f32 accumulate", "data": "synthetic",
             "config": {"workload": model + "-q4_0-decode", "batch": 1}, "cpu_baseline": cb,
             "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    if args.gpus == 1:
+        line["llama_bench"] = llama_bench(False, n_gen=32, reps=1)
     print(json.dumps(line))
 
 
@@ -880,6 +926,9 @@ def run_b200(args, rank, world):
         line["add"] = adds
     if not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(model, budget_s=15.0)
+    if world == 1 and rank == 0 and not args.no_plugin:
+        s.sync()
+        line["llama_bench"] = llama_bench(True)          # (its own process and CUDA context; this one is idle meanwhile)
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
