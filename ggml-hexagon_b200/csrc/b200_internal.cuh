@@ -190,6 +190,13 @@ struct GetRowsArgs { const char * x; const char * ids; char * y; int64_t ne00, n
 cudaError_t launch_get_rows_f32(const GetRowsArgs & p, cudaStream_t st);
 struct MmF16Args { const char * a; const char * b; char * d; int64_t M, N, K, ne12, ne13, r2, r3; int64_t nba[4], nbb[4], nbd[4]; };
 cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st);
+// one query column: K^T q, soft_max(scale * . + mask), V p in one launch (n_kv <= AD_MAX_KV; every operand row contiguous and aligned)
+constexpr int AD_MAX_PER_THREAD = 16; constexpr int AD_MAX_KV = 256 * AD_MAX_PER_THREAD;
+struct AttnDecodeArgs {
+    const char * k; const char * v; const char * q; const float * mask; char * prob; char * out;
+    int64_t hd, n_kv, r2, nbk1, nbk2, nbv1, nbv2, nbq2, nbp2, nbo2; float scale;
+};
+cudaError_t launch_attn_decode(const AttnDecodeArgs & p, int n_head, cudaStream_t st);
 cudaError_t launch_silu_f32(const float * x, float * y, int64_t n, cudaStream_t st);
 cudaError_t launch_silu_mul_f32(const float * g, const float * u, float * y, int64_t n, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st);
 cudaError_t launch_rms_norm_mul(const float * x, const float * w, float * y, int64_t ne00, int64_t rows, int64_t xs, int64_t ys, float eps,

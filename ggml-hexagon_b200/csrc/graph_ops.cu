@@ -10,6 +10,7 @@
 #include "b200_internal.cuh"
 
 #include <mma.h>
+#include <math_constants.h>
 
 namespace b200 {
 
@@ -138,20 +139,26 @@ cudaError_t launch_rms_norm_mul(const float * x, const float * w, float * y, int
 // ------------------------------------------------------------------------------------------------ ROPE (f32; normal and NeoX pairing)
 // one thread per rotated pair (or per passed-through pair beyond n_dims).  theta of pair k = pos * theta_scale^k, built by k successive
 // f32 multiplications exactly as the reference's cache loop does (ggml-cpu.c:8638-8647), so the angle is the reference's bit for bit.
+// The angle depends on (position, pair) only: one thread computes it once and rotates that pair in ROPE_HEADS heads (blockIdx.y walks the
+// head chunks), so the sin / cos and the multiplication chain are not repeated per head.
+#define ROPE_HEADS 8
 __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
     PDL_PROLOGUE();
     const int64_t half = p.ne[0] / 2;
-    const int64_t total = half * p.ne[1] * p.ne[2] * p.ne[3];
+    const int64_t total = half * p.ne[2] * p.ne[3];
+    const int64_t h0 = (int64_t) blockIdx.y * ROPE_HEADS, h1 = h0 + ROPE_HEADS < p.ne[1] ? h0 + ROPE_HEADS : p.ne[1];
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t t = i;
         const int64_t k = t % half; t /= half;
-        const int64_t i1 = t % p.ne[1]; t /= p.ne[1];
         const int64_t i2 = t % p.ne[2]; const int64_t i3 = t / p.ne[2];
-        const char * s = p.x + i1 * p.nbs[1] + i2 * p.nbs[2] + i3 * p.nbs[3];
-        char * d = p.y + i1 * p.nbd[1] + i2 * p.nbd[2] + i3 * p.nbd[3];
+        const char * s = p.x + i2 * p.nbs[2] + i3 * p.nbs[3];
+        char * d = p.y + i2 * p.nbd[2] + i3 * p.nbd[3];
         const int64_t i0 = 2 * k;
         if (i0 >= p.n_dims) {                                            // channels past n_dims are copied through
-            ((float *) d)[i0] = ((const float *) s)[i0]; ((float *) d)[i0 + 1] = ((const float *) s)[i0 + 1];
+            for (int64_t i1 = h0; i1 < h1; i1++) {
+                const float * sr = (const float *) (s + i1 * p.nbs[1]); float * dr = (float *) (d + i1 * p.nbd[1]);
+                dr[i0] = sr[i0]; dr[i0 + 1] = sr[i0 + 1];
+            }
             continue;
         }
         float theta = (float) p.pos[i2];
@@ -167,15 +174,22 @@ __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
         }
         const float c = __fmul_rn(cosf(th), mscale), sn = __fmul_rn(sinf(th), mscale);
         const int64_t a = p.neox ? k : i0, b = p.neox ? k + p.n_dims / 2 : i0 + 1;
-        const float x0 = ((const float *) s)[a], x1 = ((const float *) s)[b];
-        ((float *) d)[a] = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
-        ((float *) d)[b] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+        for (int64_t i1 = h0; i1 < h1; i1++) {
+            const float * sr = (const float *) (s + i1 * p.nbs[1]); float * dr = (float *) (d + i1 * p.nbd[1]);
+            const float x0 = sr[a], x1 = sr[b];
+            dr[a] = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
+            dr[b] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+        }
     }
 }
 cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st) {
-    const int64_t total = p.ne[0] / 2 * p.ne[1] * p.ne[2] * p.ne[3];
-    if (total == 0) return cudaSuccess;
-    return pdl_launch(rope_f32_kernel, dim3(ew_blocks(total)), dim3(256), st, p);
+    const int64_t total = p.ne[0] / 2 * p.ne[2] * p.ne[3];
+    if (total == 0 || p.ne[1] == 0) return cudaSuccess;
+    const int64_t chunks = (p.ne[1] + ROPE_HEADS - 1) / ROPE_HEADS;
+    if (chunks > 65535) return cudaErrorInvalidValue;
+    const int block = total < 256 ? 64 : 256;
+    int64_t gx = (total + block - 1) / block; if (gx > 148 * 16) gx = 148 * 16;
+    return pdl_launch(rope_f32_kernel, dim3((unsigned) gx, (unsigned) chunks), dim3(block), st, p);
 }
 
 // ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
@@ -236,6 +250,7 @@ __global__ void __launch_bounds__(256) cpy_transpose_kernel(const CpyArgs p) {
         if (a0 < p.nes[0] && a1 < p.nes[1]) *(TD *) (y + a0 * p.nbd[0] + a1 * p.nbd[1]) = cvt_el<float, TD>(tile[tx][r]);
     }
 }
+cudaError_t launch_cont_quant(const CpyArgs & p, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st);
 template <typename T> static bool logical_contig(const int64_t * ne, const int64_t * nb) {
     int64_t s = sizeof(T);
     for (int i = 0; i < 4; i++) { if (ne[i] != 1 && nb[i] != s) return false; s *= ne[i]; }
@@ -248,6 +263,9 @@ static cudaError_t launch_cpy_t(const CpyArgs & p, int64_t n, cudaStream_t st) {
     if (p.nes[2] == 1 && p.nes[3] == 1 && p.ned[2] == 1 && p.ned[3] == 1 && p.nes[0] == p.ned[0] && p.nes[1] == p.ned[1] &&
         p.nbs[1] == (int64_t) sizeof(TS) && p.nbd[0] == (int64_t) sizeof(TD) && p.nes[0] >= 32 && p.nes[1] >= 32 && (p.nes[1] + 31) / 32 <= 65535)
         return pdl_launch(cpy_transpose_kernel<TS, TD>, dim3((unsigned) ((p.nes[0] + 31) / 32), (unsigned) ((p.nes[1] + 31) / 32)), dim3(256), st, p);
+    if (sizeof(TS) == 4 && sizeof(TD) == 4 && !p.dyn && logical_contig<TD>(p.ned, p.nbd) && p.nbs[0] == 4 && p.nes[0] % 4 == 0 &&
+        (((uintptr_t) p.x | (uintptr_t) p.y | (uintptr_t) p.nbs[1] | (uintptr_t) p.nbs[2] | (uintptr_t) p.nbs[3]) & 15) == 0)
+        return launch_cont_quant(p, 0, nullptr, nullptr, st);        // contiguous destination, rows of src gathered 16 bytes at a time (head merge)
     return pdl_launch(cpy_kernel<TS, TD>, dim3(ew_blocks(n)), dim3(256), st, p, n);
 }
 cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream_t st) {
@@ -261,6 +279,7 @@ cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream
 
 // CONT of f32 into contiguous rows of K elements that a MUL_MAT reads next (the head merge in front of the attention output projection):
 // float4 along dim 0 of both sides (src ne[0] % 4 == 0), the row also written as q8_1 (K % 128 == 0)
+template <bool QUANT>
 __global__ void __launch_bounds__(256) cont_quant_kernel(const CpyArgs p, const int64_t n4, const int64_t K, int8_t * __restrict__ qs, ActDS * __restrict__ ds) {
     PDL_PROLOGUE();
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
@@ -270,14 +289,17 @@ __global__ void __launch_bounds__(256) cont_quant_kernel(const CpyArgs p, const 
         const int64_t s2 = t % p.nes[2]; const int64_t s3 = t / p.nes[2];
         const float4 v = *(const float4 *) (p.x + s0 * 4 + s1 * p.nbs[1] + s2 * p.nbs[2] + s3 * p.nbs[3]);
         ((float4 *) p.y)[i] = v;
-        const int64_t e = i * 4, row = e / K, b32 = (e - row * K) >> 5;
-        q8_1_soa_emit(v, (int) (i & 7), row, b32, K / 32, qs, ds);
+        if (QUANT) {
+            const int64_t e = i * 4, row = e / K, b32 = (e - row * K) >> 5;
+            q8_1_soa_emit(v, (int) (i & 7), row, b32, K / 32, qs, ds);
+        }
     }
 }
 cudaError_t launch_cont_quant(const CpyArgs & p, int64_t K, int8_t * qs, ActDS * ds, cudaStream_t st) {
     const int64_t n = p.nes[0] * p.nes[1] * p.nes[2] * p.nes[3];
     if (n == 0) return cudaSuccess;
-    return pdl_launch(cont_quant_kernel, dim3(ew_blocks(n / 4)), dim3(256), st, p, n / 4, K, qs, ds);
+    if (qs) return pdl_launch(cont_quant_kernel<true>, dim3(ew_blocks(n / 4)), dim3(256), st, p, n / 4, K, qs, ds);
+    return pdl_launch(cont_quant_kernel<false>, dim3(ew_blocks(n / 4)), dim3(256), st, p, n / 4, K, qs, ds);
 }
 
 // ------------------------------------------------------------------------------------------------ GET_ROWS (f32 rows, i32 ids)
@@ -450,6 +472,105 @@ __global__ void __launch_bounds__(256) mm_f16_tile_kernel(const MmF16Args p) {
             __syncwarp();
         }
 }
+// ------------------------------------------------------------------------------------------------ one-column attention (decode)
+// K^T q -> soft_max(scale * . + mask) -> V p for ONE query column, one CTA of 8 warps per head: the three launches a decode step spends per
+// layer on attention become one.  Every loop is the loop of the kernel it replaces (mm_f16_vec_kernel<1> for both products, the block
+// soft_max of norm_ops.cu), same lane / thread assignment and reduction order, so the results are the unfused ones bit for bit; the
+// probabilities are written out too (soft_max ran in place on the scores, so they are what the graph can observe).
+__global__ void __launch_bounds__(1024) attn_decode_kernel(const AttnDecodeArgs p) {
+    extern __shared__ float prob[];                  // n_kv scores -> probabilities
+    __shared__ double shd[8];
+    __shared__ float shf[8];
+    PDL_PROLOGUE();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int64_t h = blockIdx.x, hk = h / p.r2;
+    const char * kb = p.k + hk * p.nbk2;
+    const char * vb = p.v + hk * p.nbv2;
+    const char * qb = p.q + h * p.nbq2;
+    float * pr = (float *) (p.prob + h * p.nbp2);
+    // scores: row j of K (hd f16, contiguous) . q -- 4 rows in flight per warp, each row's sum in the order of mm_f16_vec_kernel<1>
+    for (int64_t j0 = (int64_t) warp * 4; j0 < p.n_kv; j0 += (int64_t) nw * 4) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int64_t k2 = lane; k2 < p.hd / 2; k2 += 32) {
+            const float2 xv = *(const float2 *) (qb + k2 * 8);
+            const float x0 = rnd_h(xv.x), x1 = rnd_h(xv.y);
+            #pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (j0 + r < p.n_kv) {
+                    const float2 wf = __half22float2(((const __half2 *) (kb + (j0 + r) * p.nbk1))[k2]);
+                    acc[r] = fmaf(wf.x, x0, acc[r]); acc[r] = fmaf(wf.y, x1, acc[r]);
+                }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < 4; r++) {
+            float a = acc[r];
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (lane == 0 && j0 + r < p.n_kv) prob[j0 + r] = a;
+        }
+    }
+    __syncthreads();
+    // soft_max over the n_kv scores (max_bias = 0: slope 1): the first 256 threads in the roles of the block kernel's 256
+    const float * mf = p.mask;
+    const bool act = threadIdx.x < 256;
+    auto wp = [&](int64_t i) { float v = __fmul_rn(prob[i], p.scale); if (mf) v = __fadd_rn(v, __fmul_rn(1.0f, mf[i])); return v; };
+    float mx = -CUDART_INF_F;
+    if (act) for (int64_t i = threadIdx.x; i < p.n_kv; i += 256) mx = fmaxf(mx, wp(i));
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const float w = __shfl_xor_sync(0xffffffffu, mx, o); mx = w > mx ? w : mx; }
+    if (lane == 0 && warp < 8) shf[warp] = mx;
+    __syncthreads();
+    mx = shf[0];
+    for (int i = 1; i < 8; i++) mx = shf[i] > mx ? shf[i] : mx;
+    double sum = 0.0;
+    float e[AD_MAX_PER_THREAD];
+    int ne = 0;
+    if (act) for (int64_t i = threadIdx.x; i < p.n_kv; i += 256) { const float v = expf(__fsub_rn(wp(i), mx)); e[ne++] = v; sum += (double) v; }
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0 && warp < 8) shd[warp] = sum;
+    __syncthreads();                                  // (also: every score has been read before the probabilities overwrite them)
+    sum = shd[0];
+    for (int i = 1; i < 8; i++) sum += shd[i];
+    const float inv = (float) (1.0 / sum);
+    ne = 0;
+    if (act) for (int64_t i = threadIdx.x; i < p.n_kv; i += 256) { const float v = __fmul_rn(e[ne++], inv); prob[i] = v; pr[i] = v; }
+    __syncthreads();
+    // V p: row d of V^T (n_kv f16, contiguous) . probabilities, 4 rows in flight per warp
+    float * out = (float *) (p.out + h * p.nbo2);
+    for (int64_t d0 = (int64_t) warp * 4; d0 < p.hd; d0 += (int64_t) nw * 4) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int64_t k2 = lane; k2 < p.n_kv / 2; k2 += 32) {
+            const float x0 = rnd_h(prob[2 * k2]), x1 = rnd_h(prob[2 * k2 + 1]);
+            #pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (d0 + r < p.hd) {
+                    const float2 wf = __half22float2(((const __half2 *) (vb + (d0 + r) * p.nbv1))[k2]);
+                    acc[r] = fmaf(wf.x, x0, acc[r]); acc[r] = fmaf(wf.y, x1, acc[r]);
+                }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < 4; r++) {
+            float a = acc[r];
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (lane == 0 && d0 + r < p.hd) out[d0 + r] = a;
+        }
+    }
+}
+cudaError_t launch_attn_decode(const AttnDecodeArgs & p, int n_head, cudaStream_t st) {
+    if (n_head == 0 || p.n_kv == 0) return cudaSuccess;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) n_head); cfg.blockDim = dim3(1024); cfg.stream = st; cfg.dynamicSmemBytes = (size_t) p.n_kv * sizeof(float);
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, attn_decode_kernel, p);
+}
+
 cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st) {
     const int64_t batch = p.ne12 * p.ne13;
     if (p.M == 0 || p.N == 0 || batch == 0) return cudaSuccess;

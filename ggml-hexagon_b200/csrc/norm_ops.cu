@@ -159,7 +159,7 @@ cudaError_t launch_soft_max_f32(const float * x, const void * mask, bool mask_f1
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
-    if (ne[0] <= 1024 && rows >= 64) {
+    if (ne[0] <= 1024 && rows >= 512) {        // (fewer rows: the block kernel, whose order the one-column attention kernel of graph_ops.cu reproduces)
         cfg.gridDim = dim3((unsigned) ((rows + 7) / 8));
         if (mask_f16) return cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<true>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2);
         return cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<false>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2);

@@ -1149,6 +1149,43 @@ static int try_silu_mul(Ctx * c, const b200_node * nodes, int i, int n, int * us
     }
     return 0;
 }
+// MUL_MAT(K view f16, q) -> SOFT_MAX in place (mask, scale) -> MUL_MAT(V^T view f16, p), one query column: one launch per layer instead of three
+// (graph_ops.cu attn_decode_kernel; bit-equal to the three kernels, whose vectorised paths it requires)
+static int64_t attn_decode_max_kv() { const char * e = getenv("B200_ATTN_FUSE_MAX_KV"); const int64_t v = e ? atoll(e) : 1024; return v < AD_MAX_KV ? v : AD_MAX_KV; }
+static int try_attn_decode(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
+    if (!graph_fuse_enabled() || c->rs_on || i + 2 >= n) return 0;
+    const b200_node & kq = nodes[i]; const b200_node & sm = nodes[i + 1]; const b200_node & pv = nodes[i + 2];
+    if (sm.dst.op != B200_OP_SOFT_MAX || pv.dst.op != B200_OP_MUL_MAT || pv.src0.type != T_F16 || kq.src0.type != T_F16) return 0;
+    if (kq.src1.type != T_F32 || kq.dst.type != T_F32 || pv.src1.type != T_F32 || pv.dst.type != T_F32 || sm.src0.type != T_F32 || sm.dst.type != T_F32) return 0;
+    const int64_t hd = kq.src0.ne[0], n_kv = kq.src0.ne[1], nhk = kq.src0.ne[2], nh = kq.src1.ne[2];
+    if (kq.src0.ne[3] != 1 || kq.src1.ne[3] != 1 || kq.src1.ne[1] != 1 || kq.src1.ne[0] != hd || nhk <= 0 || nh % nhk) return 0;
+    if (hd % 2 || n_kv % 2 || n_kv <= 0 || n_kv > attn_decode_max_kv() || nh >= 512) return 0;       // (longer contexts: the three kernels spread over more CTAs than one per head)
+    if (kq.src0.nb[0] != 2 || kq.src1.nb[0] != 4) return 0;
+    const b200_tensor & s = kq.dst;            // scores / probabilities [n_kv, 1, nh], contiguous
+    if (s.ne[0] != n_kv || s.ne[1] != 1 || s.ne[2] != nh || s.ne[3] != 1 || s.nb[0] != 4 || s.nb[2] != n_kv * 4) return 0;
+    if (sm.src0.data != s.data || sm.dst.data != s.data || !same_shape(sm.src0, s) || !same_shape(sm.dst, s) || !contiguous_f32_t(&sm.src0) || !contiguous_f32_t(&sm.dst)) return 0;
+    const b200_tensor & m = sm.src1;
+    if (!m.data || m.type != T_F32 || m.ne[0] != n_kv || m.ne[1] < 1 || m.nb[0] != 4 || m.nb[1] != n_kv * 4) return 0;
+    if (f32_param(&sm.dst, 1) != 0.0f) return 0;                                         // ALiBi slopes: not in a Llama graph
+    if (pv.src1.data != s.data || !same_shape(pv.src1, s) || pv.src1.nb[0] != 4 || pv.src1.nb[2] != n_kv * 4) return 0;
+    if (pv.src0.ne[0] != n_kv || pv.src0.ne[1] != hd || pv.src0.ne[2] != nhk || pv.src0.ne[3] != 1 || pv.src0.nb[0] != 2) return 0;
+    const b200_tensor & o = pv.dst;
+    if (o.ne[0] != hd || o.ne[1] != 1 || o.ne[2] != nh || o.ne[3] != 1 || o.nb[0] != 4) return 0;
+    // the alignment under which the separate kernels take their 2-element paths
+    auto a4 = [](const void * p, int64_t x, int64_t y) { return (((uintptr_t) p | (uintptr_t) x | (uintptr_t) y) & 3) == 0; };
+    auto a8 = [](const void * p, int64_t x, int64_t y) { return (((uintptr_t) p | (uintptr_t) x | (uintptr_t) y) & 7) == 0; };
+    if (!a4(kq.src0.data, kq.src0.nb[1], kq.src0.nb[2]) || !a4(pv.src0.data, pv.src0.nb[1], pv.src0.nb[2])) return 0;
+    if (!a8(kq.src1.data, kq.src1.nb[1], kq.src1.nb[2]) || !a8(s.data, s.nb[1], s.nb[2])) return 0;
+    AttnDecodeArgs a{};
+    a.k = (const char *) kq.src0.data; a.v = (const char *) pv.src0.data; a.q = (const char *) kq.src1.data; a.mask = (const float *) m.data;
+    a.prob = (char *) s.data; a.out = (char *) o.data;
+    a.hd = hd; a.n_kv = n_kv; a.r2 = nh / nhk; a.nbk1 = kq.src0.nb[1]; a.nbk2 = kq.src0.nb[2]; a.nbv1 = pv.src0.nb[1]; a.nbv2 = pv.src0.nb[2];
+    a.nbq2 = kq.src1.nb[2]; a.nbp2 = s.nb[2]; a.nbo2 = o.nb[2]; a.scale = f32_param(&sm.dst, 0);
+    CU(launch_attn_decode(a, (int) nh, c->st)); c->launches++;
+    wrote(c, &s); wrote(c, &o);
+    *used = 3;
+    return 0;
+}
 // CONT -> contiguous X[K] read next by a vector MUL_MAT: copy + q8_1 in one kernel
 static int try_cont_quant(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
     if (!graph_fuse_enabled() || c->rs_on || i + 1 >= n) return 0;
@@ -1210,7 +1247,11 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             } break;
             case B200_OP_GET_ROWS: rc = get_rows_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
             case B200_OP_MUL_MAT: {
-                if (nodes[i].src0.type == T_F16) { rc = mm_f16_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break; }
+                if (nodes[i].src0.type == T_F16) {
+                    int u = 0; rc = try_attn_decode(c, nodes, i, n, &u);
+                    if (!rc && u) used = u; else if (!rc) rc = mm_f16_dev(c, &nodes[i].src0, &nodes[i].src1, &d);
+                    break;
+                }
                 FusedAdd fa;
                 const int gl = fuse ? group_len(nodes, i, n) : 1;
                 // row split: what consumes this op's gathered vectors next?  [ADD with a plain vector ->] vector MUL_MAT: the gather kernel

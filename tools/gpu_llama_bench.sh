@@ -9,7 +9,7 @@ OUT=$HERE/gpurun_out; mkdir -p $OUT
 V=${REF_VARIANT:-$(cd $HERE/oracle && python -c 'import pyref; print(pyref.best_variant())')}
 BIN=$HERE/oracle/_ref/$V/llama-bench
 M=/dev/shm/l7b.gguf
-python $HERE/tools/make_gguf.py $M --preset 7b --type ${GGUF_TYPE:-q4_0} 2> $OUT/${TAG}_gguf.log || exit 1
+python $HERE/tools/make_gguf.py $M --preset ${GGUF_PRESET:-7b} --type ${GGUF_TYPE:-q4_0} ${GGUF_EXTRA:-} 2> $OUT/${TAG}_gguf.log || exit 1
 NT=$(nproc)
 if [ "${SKIP_CPU:-0}" != 1 ]; then
   timeout 900 $BIN -m $M -p ${CPU_PP:-512} -n ${CPU_TG:-32} -ngl 0 -t $NT -r 1 -o jsonl > $OUT/${TAG}_llama_bench_cpu.jsonl 2> $OUT/${TAG}_llama_bench_cpu.err

@@ -9,7 +9,9 @@ not in the tree): magic "GGUF", u32 version 3, i64 n_tensors, i64 n_kv; each kv 
 string name, u32 n_dims, i64 ne[], i32 ggml_type, u64 offset; then the data section aligned to general.alignment (32).
 Key names: src/llama-arch.cpp:76-180 (LLM_KV_*), tensor names :200-230 (LLM_TENSOR_NAMES for LLM_ARCH_LLAMA).
 
-usage: make_gguf.py OUT.gguf [--preset 7b|tiny] [--type q4_0|q8_0|q4_K|q6_K] [--layers N]
+usage: make_gguf.py OUT.gguf [--preset 7b|8b|tiny] [--type q4_0|q8_0|q4_K|q6_K] [--kmix] [--layers N]
+(8b = the Llama-3-8B shapes of BASELINE.json configs[3]: 8 KV heads, 14336-wide FFN, 128256-entry vocabulary; --kmix = attn_v and ffn_down in
+q6_K, the rest in --type, as a Q4_K_M file is laid out)
 """
 import argparse
 import struct
@@ -75,14 +77,18 @@ def random_blocks(t, rows, K, rng, sigma):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("out")
-    ap.add_argument("--preset", default="7b", choices=["7b", "tiny"])
+    ap.add_argument("--preset", default="7b", choices=["7b", "8b", "tiny"])
+    ap.add_argument("--kmix", action="store_true", help="attn_v and ffn_down in q6_K (Q4_K_M-style mix)")
     ap.add_argument("--type", default="q4_0", choices=sorted(TYPES))
     ap.add_argument("--out-type", default="q6_K", choices=sorted(TYPES), help="type of output.weight (llama-quantize keeps it at q6_K in a Q4_0 file)")
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--seed", type=int, default=1234)
     a = ap.parse_args()
+    freq_base = 10000.0
     if a.preset == "7b":
         n_embd, n_ff, n_head, n_head_kv, n_layer, n_vocab, n_ctx = 4096, 11008, 32, 32, 32, 32000, 4096
+    elif a.preset == "8b":
+        n_embd, n_ff, n_head, n_head_kv, n_layer, n_vocab, n_ctx, freq_base = 4096, 14336, 32, 8, 32, 128256, 8192, 500000.0
     else:
         n_embd, n_ff, n_head, n_head_kv, n_layer, n_vocab, n_ctx = 256, 512, 4, 4, 2, 512, 512
     if a.layers:
@@ -112,6 +118,7 @@ def main():
         kv("llama.attention.head_count", GGUF_U32, n_head),
         kv("llama.attention.head_count_kv", GGUF_U32, n_head_kv),
         kv("llama.attention.layer_norm_rms_epsilon", GGUF_F32, 1e-5),
+        kv("llama.rope.freq_base", GGUF_F32, freq_base),
         kv("tokenizer.ggml.model", GGUF_STR, "llama"),
         kv_arr("tokenizer.ggml.tokens", GGUF_STR, tokens),
         kv_arr("tokenizer.ggml.scores", GGUF_F32, scores),
@@ -129,10 +136,14 @@ def main():
     # identical content does not change what the kernels do, and it keeps the 3.8 GB file to seconds of generation
     cache = {}
 
-    def lw(key, rows, K):
+    t6 = GGML_Q6_K if a.kmix else t
+
+    def lw(key, rows, K, ty=None):
+        ty = t if ty is None else ty
+
         def gen():
             if key not in cache:
-                cache[key] = random_blocks(t, rows, K, rng, sig(K))
+                cache[key] = random_blocks(ty, rows, K, rng, sig(K))
             return cache[key]
         return gen
     ones = lambda: np.ones(n_embd, np.float32)
@@ -142,11 +153,11 @@ def main():
             (p + "attn_norm.weight", (n_embd,), GGML_F32, ones),
             (p + "attn_q.weight", (n_embd, n_embd), t, lw("q", n_embd, n_embd)),
             (p + "attn_k.weight", (n_embd, n_kv_dim), t, lw("k", n_kv_dim, n_embd)),
-            (p + "attn_v.weight", (n_embd, n_kv_dim), t, lw("v", n_kv_dim, n_embd)),
+            (p + "attn_v.weight", (n_embd, n_kv_dim), t6, lw("v", n_kv_dim, n_embd, t6)),
             (p + "attn_output.weight", (n_embd, n_embd), t, lw("o", n_embd, n_embd)),
             (p + "ffn_norm.weight", (n_embd,), GGML_F32, ones),
             (p + "ffn_gate.weight", (n_embd, n_ff), t, lw("gate", n_ff, n_embd)),
-            (p + "ffn_down.weight", (n_ff, n_embd), t, lw("down", n_embd, n_ff)),
+            (p + "ffn_down.weight", (n_ff, n_embd), t6, lw("down", n_embd, n_ff, t6)),
             (p + "ffn_up.weight", (n_embd, n_ff), t, lw("up", n_ff, n_embd)),
         ]
     tensors += [("output_norm.weight", (n_embd,), GGML_F32, ones),
