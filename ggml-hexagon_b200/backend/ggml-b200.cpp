@@ -51,8 +51,9 @@ struct b200_graph_entry {
     uint64_t               key = 0;
     uint64_t               last_use = 0;
     std::vector<std::pair<int, int>> dyn;   // (index in nodes, index in the cgraph) of the nodes flagged B200_TENSOR_DYNAMIC
-    bool                   trust = false;   // the previous fingerprint of this cgraph was replayed several times (a decode loop whose cache view just grew
-                                            // by one block): capture the new list on its first sighting
+    bool                   trust = false;   // capture a new list of this cgraph on its FIRST sighting: large lists (a whole model's layer stack) start out trusted,
+                                            // a list whose predecessor was replayed several times (a decode loop whose cache view just grew by one block) earns it,
+    uint32_t               misses = 0;      // and four lists in a row that were never seen twice lose it (capture + instantiate costs several launches' worth)
     uint32_t               seen = 0;        // calls with this fingerprint: a CUDA graph is captured from the second one on, so node lists that
                                             // change every call (a decode step whose KV-cache views move with the position) are launched directly
 };
@@ -417,7 +418,10 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
                               (long long) t->ne[2], (long long) t->ne[3], t->data, t->src[0] ? t->src[0]->data : nullptr, t->src[1] ? t->src[1]->data : nullptr);
             }
         }
-        e.fp = fp; e.trust = e.seen >= 6; e.seen = 0;
+        static const int eager_min = getenv("GGML_B200_GRAPH_EAGER_MIN") ? atoi(getenv("GGML_B200_GRAPH_EAGER_MIN")) : 256;
+        if (e.seen >= 2) e.misses = 0; else if (e.seen == 1) e.misses++;
+        e.trust = e.misses < 4 && (e.seen >= 6 || (int) e.nodes.size() >= eager_min);
+        e.fp = fp; e.seen = 0;
         e.key = g_graph_key.fetch_add(1);          // a new key per distinct list: the op layer's caches never see one key with two lists
         if (c->graphs.size() > 512) {              // (a scheduler keeps a few dozen split graphs alive; drop the oldest half beyond that)
             std::vector<std::pair<uint64_t, const ggml_cgraph *>> age;
