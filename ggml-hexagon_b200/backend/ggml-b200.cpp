@@ -178,11 +178,11 @@ static bool b200_supports_graph_op(const ggml_tensor * op) {
             return ggml_get_unary_op(op) == GGML_UNARY_OP_SILU && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
                    ggml_is_contiguous(a) && ggml_is_contiguous(op) && ggml_are_same_shape(a, op);
         case GGML_OP_ROPE: {
-            if (!b || op->src[2] || a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || b->type != GGML_TYPE_I32) return false;
+            if (!b || op->src[2] || !f32_or_f16(a->type) || op->type != a->type || b->type != GGML_TYPE_I32) return false;
             const int mode = op->op_params[2], n_dims = op->op_params[1];
             if (mode != 0 && mode != GGML_ROPE_TYPE_NEOX) return false;
             if (n_dims <= 0 || n_dims % 2 || n_dims > a->ne[0] || a->ne[0] % 2) return false;
-            return a->nb[0] == sizeof(float) && op->nb[0] == sizeof(float) && ggml_are_same_shape(a, op) && b->ne[0] >= a->ne[2] && b->nb[0] == sizeof(int32_t);
+            return a->nb[0] == ggml_type_size(a->type) && op->nb[0] == ggml_type_size(a->type) && ggml_are_same_shape(a, op) && b->ne[0] >= a->ne[2] && b->nb[0] == sizeof(int32_t);
         }
         case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT:
             return f32_or_f16(a->type) && f32_or_f16(op->type) && ggml_nelements(a) == ggml_nelements(op);

@@ -183,7 +183,7 @@ struct RopeArgs {
     int n_dims, neox;
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
 };
-cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st);
+cudaError_t launch_rope_f32(const RopeArgs & p, bool f16, cudaStream_t st);       // f16: both sides __half (rotated in f32)
 struct CpyArgs { const char * x; char * y; char * const * dyn /* device: where this launch's dst starts, or NULL = y */; int64_t nes[4], nbs[4], ned[4], nbd[4]; };
 cudaError_t launch_cpy(const CpyArgs & p, bool src_f16, bool dst_f16, cudaStream_t st);
 struct GetRowsArgs { const char * x; const char * ids; char * y; int64_t ne00, ne01, ne10, ne11, ne12; int64_t nbs[4], nbi[3], nbd[4]; };

@@ -51,6 +51,12 @@ __device__ __forceinline__ void q8_1_soa_emit(const float4 v, const int sub, con
     if (sub == 0) { ActDS o; o.d = __half2float(__float2half_rn(d)); o.isum0 = (short) sum; o.isum1 = (short) other; ds[row * NB + b] = o; }
 }
 
+template <typename TS, typename TD> __device__ __forceinline__ TD cvt_el(TS v);
+template <> __device__ __forceinline__ float  cvt_el<float, float>(float v)    { return v; }
+template <> __device__ __forceinline__ __half cvt_el<float, __half>(float v)   { return __float2half_rn(v); }
+template <> __device__ __forceinline__ float  cvt_el<__half, float>(__half v)  { return __half2float(v); }
+template <> __device__ __forceinline__ __half cvt_el<__half, __half>(__half v) { return v; }
+
 // ------------------------------------------------------------------------------------------------ UNARY (SILU)
 __global__ void __launch_bounds__(256) silu_f32_kernel(const float * __restrict__ x, float * __restrict__ y, const int64_t n) {
     PDL_PROLOGUE();
@@ -142,7 +148,10 @@ cudaError_t launch_rms_norm_mul(const float * x, const float * w, float * y, int
 // The angle depends on (position, pair) only: one thread computes it once and rotates that pair in ROPE_HEADS heads (blockIdx.y walks the
 // head chunks), so the sin / cos and the multiplication chain are not repeated per head.
 #define ROPE_HEADS 8
-__global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
+// T = float, or __half (the in-place rotation of f16 K-cache rows when llama.cpp shifts its context: convert, rotate in f32, round back, as
+// ggml_compute_forward_rope_f16 does)
+template <typename T>
+__global__ void __launch_bounds__(256) rope_kernel(const RopeArgs p) {
     PDL_PROLOGUE();
     const int64_t half = p.ne[0] / 2;
     const int64_t total = half * p.ne[2] * p.ne[3];
@@ -156,7 +165,7 @@ __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
         const int64_t i0 = 2 * k;
         if (i0 >= p.n_dims) {                                            // channels past n_dims are copied through
             for (int64_t i1 = h0; i1 < h1; i1++) {
-                const float * sr = (const float *) (s + i1 * p.nbs[1]); float * dr = (float *) (d + i1 * p.nbd[1]);
+                const T * sr = (const T *) (s + i1 * p.nbs[1]); T * dr = (T *) (d + i1 * p.nbd[1]);
                 dr[i0] = sr[i0]; dr[i0 + 1] = sr[i0 + 1];
             }
             continue;
@@ -175,30 +184,26 @@ __global__ void __launch_bounds__(256) rope_f32_kernel(const RopeArgs p) {
         const float c = __fmul_rn(cosf(th), mscale), sn = __fmul_rn(sinf(th), mscale);
         const int64_t a = p.neox ? k : i0, b = p.neox ? k + p.n_dims / 2 : i0 + 1;
         for (int64_t i1 = h0; i1 < h1; i1++) {
-            const float * sr = (const float *) (s + i1 * p.nbs[1]); float * dr = (float *) (d + i1 * p.nbd[1]);
-            const float x0 = sr[a], x1 = sr[b];
-            dr[a] = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
-            dr[b] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+            const T * sr = (const T *) (s + i1 * p.nbs[1]); T * dr = (T *) (d + i1 * p.nbd[1]);
+            const float x0 = cvt_el<T, float>(sr[a]), x1 = cvt_el<T, float>(sr[b]);
+            dr[a] = cvt_el<float, T>(__fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)));
+            dr[b] = cvt_el<float, T>(__fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c)));
         }
     }
 }
-cudaError_t launch_rope_f32(const RopeArgs & p, cudaStream_t st) {
+cudaError_t launch_rope_f32(const RopeArgs & p, bool f16, cudaStream_t st) {
     const int64_t total = p.ne[0] / 2 * p.ne[2] * p.ne[3];
     if (total == 0 || p.ne[1] == 0) return cudaSuccess;
     const int64_t chunks = (p.ne[1] + ROPE_HEADS - 1) / ROPE_HEADS;
     if (chunks > 65535) return cudaErrorInvalidValue;
     const int block = total < 256 ? 64 : 256;
     int64_t gx = (total + block - 1) / block; if (gx > 148 * 16) gx = 148 * 16;
-    return pdl_launch(rope_f32_kernel, dim3((unsigned) gx, (unsigned) chunks), dim3(block), st, p);
+    if (f16) return pdl_launch(rope_kernel<__half>, dim3((unsigned) gx, (unsigned) chunks), dim3(block), st, p);
+    return pdl_launch(rope_kernel<float>, dim3((unsigned) gx, (unsigned) chunks), dim3(block), st, p);
 }
 
 // ------------------------------------------------------------------------------------------------ CPY / CONT / DUP
 // element i (logical order of src) -> element i (logical order of dst); any byte strides on both sides; f32 / f16 either side
-template <typename TS, typename TD> __device__ __forceinline__ TD cvt_el(TS v);
-template <> __device__ __forceinline__ float  cvt_el<float, float>(float v)    { return v; }
-template <> __device__ __forceinline__ __half cvt_el<float, __half>(float v)   { return __float2half_rn(v); }
-template <> __device__ __forceinline__ float  cvt_el<__half, float>(__half v)  { return __half2float(v); }
-template <> __device__ __forceinline__ __half cvt_el<__half, __half>(__half v) { return v; }
 template <typename TS, typename TD>
 __global__ void __launch_bounds__(256) cpy_kernel(const CpyArgs p, const int64_t n) {
     PDL_PROLOGUE();

@@ -459,9 +459,11 @@ static int unary_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     return 0;
 }
 static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, b200_tensor * d) {
-    if (s->type != T_F32 || d->type != T_F32 || pos->type != T_I32) return fail(B200_ENOTSUP, "rope: f32 data, i32 positions");
+    const bool f16 = s->type == T_F16;
+    if ((s->type != T_F32 && s->type != T_F16) || d->type != s->type || pos->type != T_I32) return fail(B200_ENOTSUP, "rope: f32 or f16 data (same on both sides), i32 positions");
+    const int64_t es = f16 ? 2 : 4;
     for (int i = 0; i < 4; i++) if (s->ne[i] != d->ne[i]) return fail(B200_EINVAL, "rope: src and dst shapes differ");
-    if (s->nb[0] != 4 || d->nb[0] != 4) return fail(B200_ENOTSUP, "rope: rows must be contiguous");
+    if (s->nb[0] != es || d->nb[0] != es) return fail(B200_ENOTSUP, "rope: rows must be contiguous");
     const int32_t * o = d->op_params;
     const int n_dims = o[1], mode = o[2], n_ctx_orig = o[4];
     if (mode != 0 && mode != 2) return fail(B200_ENOTSUP, "rope: mode %d (only normal = 0 and NeoX = 2)", mode);
@@ -477,7 +479,7 @@ static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, b20
     // ggml_rope_yarn_corr_dims (ggml.c:3741-3753)
     auto corr = [&](float n_rot) { return n_dims * logf(n_ctx_orig / (n_rot * 2 * 3.14159265358979323846f)) / (2 * logf(freq_base)); };
     a.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); a.corr1 = fminf((float) (n_dims - 1), ceilf(corr(beta_slow)));
-    CU(launch_rope_f32(a, c->st)); c->launches++;
+    CU(launch_rope_f32(a, f16, c->st)); c->launches++;
     wrote(c, d);
     return 0;
 }
