@@ -40,7 +40,7 @@ class Tensor(C.Structure):
 
 
 class Node(C.Structure):
-    _fields_ = [("src0", Tensor), ("src1", Tensor), ("dst", Tensor)]
+    _fields_ = [("src0", Tensor), ("src1", Tensor), ("dst", Tensor), ("src2", Tensor)]
 
 
 class B200Error(RuntimeError):

@@ -178,7 +178,8 @@ static bool b200_supports_graph_op(const ggml_tensor * op) {
             return ggml_get_unary_op(op) == GGML_UNARY_OP_SILU && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
                    ggml_is_contiguous(a) && ggml_is_contiguous(op) && ggml_are_same_shape(a, op);
         case GGML_OP_ROPE: {
-            if (!b || op->src[2] || !f32_or_f16(a->type) || op->type != a->type || b->type != GGML_TYPE_I32) return false;
+            if (!b || !f32_or_f16(a->type) || op->type != a->type || b->type != GGML_TYPE_I32) return false;
+            if (op->src[2] && (op->src[2]->type != GGML_TYPE_F32 || op->src[2]->nb[0] != sizeof(float) || op->src[2]->ne[0] < op->op_params[1] / 2)) return false;   // frequency factors
             const int mode = op->op_params[2], n_dims = op->op_params[1];
             if (mode != 0 && mode != GGML_ROPE_TYPE_NEOX) return false;
             if (n_dims <= 0 || n_dims % 2 || n_dims > a->ne[0] || a->ne[0] % 2) return false;
@@ -402,7 +403,8 @@ static enum ggml_status b200_backend_graph_compute(ggml_backend_t backend, ggml_
             }
             b200_node n;
             memset(&n, 0, sizeof(n));
-            if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || (node->src[1] && !to_b200(node->src[1], &n.src1, B200_OP_NONE)) || !to_b200(node, &n.dst, op)) {
+            if (!to_b200(node->src[0], &n.src0, B200_OP_NONE) || (node->src[1] && !to_b200(node->src[1], &n.src1, B200_OP_NONE)) ||
+                (node->src[2] && !to_b200(node->src[2], &n.src2, B200_OP_NONE)) || !to_b200(node, &n.dst, op)) {
                 B200_ERR("graph_compute: node %s has a layout supports_op declines", node->name);
                 c->graphs.erase(cgraph);
                 return GGML_STATUS_FAILED;

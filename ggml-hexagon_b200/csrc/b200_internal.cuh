@@ -178,7 +178,7 @@ cudaError_t launch_add_f32(const AddArgs & a, cudaStream_t st);
 
 // ---- graph_ops.cu: the ops between the MUL_MATs of a Llama layer (all strides in bytes, ggml order)
 struct RopeArgs {
-    const char * x; char * y; const int32_t * pos;
+    const char * x; char * y; const int32_t * pos; const float * ff /* frequency factors [n_dims / 2] or NULL */;
     int64_t ne[4], nbs[4], nbd[4];
     int n_dims, neox;
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;

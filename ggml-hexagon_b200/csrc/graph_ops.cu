@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs p) {
         }
         float theta = (float) p.pos[i2];
         for (int64_t j = 0; j < k; j++) theta = __fmul_rn(theta, p.theta_scale);
-        const float theta_extrap = theta;                                // (freq_factors: declined by the admission check)
+        const float theta_extrap = p.ff ? __fdiv_rn(theta, p.ff[k]) : theta;     // (theta / freq_factors[i0 / 2], ggml-cpu.c:8640-8642)
         const float theta_interp = __fmul_rn(p.freq_scale, theta_extrap);
         float th = theta_interp, mscale = p.attn_factor;
         if (p.ext_factor != 0.0f) {

@@ -458,7 +458,7 @@ static int unary_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     wrote(c, d);
     return 0;
 }
-static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, b200_tensor * d) {
+static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, const b200_tensor * ff, b200_tensor * d) {
     const bool f16 = s->type == T_F16;
     if ((s->type != T_F32 && s->type != T_F16) || d->type != s->type || pos->type != T_I32) return fail(B200_ENOTSUP, "rope: f32 or f16 data (same on both sides), i32 positions");
     const int64_t es = f16 ? 2 : 4;
@@ -473,6 +473,10 @@ static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, b20
     a.x = (const char *) s->data; a.y = (char *) d->data; a.pos = (const int32_t *) pos->data;
     for (int i = 0; i < 4; i++) { a.ne[i] = s->ne[i]; a.nbs[i] = s->nb[i]; a.nbd[i] = d->nb[i]; }
     a.n_dims = n_dims; a.neox = mode == 2;
+    if (ff && ff->data) {
+        if (ff->type != T_F32 || ff->nb[0] != 4 || ff->ne[0] < n_dims / 2) return fail(B200_EINVAL, "rope: frequency factors must be f32 [>= n_dims / 2]");
+        a.ff = (const float *) ff->data;
+    }
     const float freq_base = f32_param(d, 5), beta_fast = f32_param(d, 9), beta_slow = f32_param(d, 10);
     a.freq_scale = f32_param(d, 6); a.ext_factor = f32_param(d, 7); a.attn_factor = f32_param(d, 8);
     a.theta_scale = powf(freq_base, -2.0f / n_dims);
@@ -1242,7 +1246,7 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                 int u = 0, dm = -1; rc = try_silu_mul(c, nodes, i, n, &u, &dm);
                 if (!rc && u) { used = u; if (dm >= 0) silu_mul_at = dm; } else if (!rc) rc = unary_dev(c, &nodes[i].src0, &d);
             } break;
-            case B200_OP_ROPE:     rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
+            case B200_OP_ROPE:     rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &nodes[i].src2, &d); break;
             case B200_OP_DUP: case B200_OP_CONT: case B200_OP_CPY: {    // (ggml_cpy(a, b): the node is a view of b, so dst carries b's layout)
                 int u = 0; if (d.op == B200_OP_CONT) rc = try_cont_quant(c, nodes, i, n, &u);
                 if (!rc && !u) rc = cpy_dev(c, &nodes[i].src0, &d);

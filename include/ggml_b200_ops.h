@@ -50,7 +50,7 @@ enum b200_op {
     B200_OP_CPY      = 32,   /* src0 -> src1's layout (dst is a view of src1); f32 / f16 either side */
     B200_OP_CONT     = 33,
     B200_OP_GET_ROWS = 38,   /* f32 rows, i32 ids */
-    B200_OP_ROPE     = 45,   /* f32 or f16 (same on both sides); mode 0 (normal) or 2 (NeoX); src1 = i32 positions; no frequency factors (src2) */
+    B200_OP_ROPE     = 45,   /* f32 or f16 (same on both sides); mode 0 (normal) or 2 (NeoX); src1 = i32 positions; src2 = optional f32 frequency factors */
     B200_OP_UNARY    = 73,   /* op_params[0] = B200_UNARY_SILU */
 };
 #define B200_UNARY_SILU 10   /* GGML_UNARY_OP_SILU */
@@ -98,6 +98,7 @@ typedef struct b200_tensor {
 /* one node of a compute graph: dst = op(src0, src1)   (ggml_cgraph node, ggml-hexagon.cpp:5555-5574) */
 typedef struct b200_node {
     b200_tensor src0, src1, dst;
+    b200_tensor src2;      /* third operand where the op has one (ROPE: f32 frequency factors); data = NULL otherwise */
 } b200_node;
 
 typedef uint64_t b200_handle;   /* replaces remote_handle64 */

@@ -47,7 +47,7 @@ def test_block_geometry_matches_ggml_common():
 def test_struct_layout_matches_header():
     # b200_tensor: 4 i32 + 4 i64 + 4 i64 + 16 i32 + ptr + i64 + ptr + 2 i64
     assert C.sizeof(B.Tensor) == 16 + 32 + 32 + 64 + 8 + 8 + 8 + 16
-    assert C.sizeof(B.Node) == 3 * C.sizeof(B.Tensor)
+    assert C.sizeof(B.Node) == 4 * C.sizeof(B.Tensor)        # src0, src1, dst, src2
 
 
 def test_no_cpu_fallback_without_gpu():

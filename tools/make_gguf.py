@@ -81,6 +81,7 @@ def main():
     ap.add_argument("--kmix", action="store_true", help="attn_v and ffn_down in q6_K (Q4_K_M-style mix)")
     ap.add_argument("--type", default="q4_0", choices=sorted(TYPES))
     ap.add_argument("--out-type", default="q6_K", choices=sorted(TYPES), help="type of output.weight (llama-quantize keeps it at q6_K in a Q4_0 file)")
+    ap.add_argument("--rope-freqs", action="store_true", help="add rope_freqs.weight (Llama-3.1-style frequency factors: ROPE gets a third operand)")
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--seed", type=int, default=1234)
     a = ap.parse_args()
@@ -160,6 +161,9 @@ def main():
             (p + "ffn_down.weight", (n_ff, n_embd), t6, lw("down", n_embd, n_ff, t6)),
             (p + "ffn_up.weight", (n_embd, n_ff), t, lw("up", n_ff, n_embd)),
         ]
+    if a.rope_freqs:
+        hd2 = n_embd // n_head // 2
+        tensors.append(("rope_freqs.weight", (hd2,), GGML_F32, lambda: np.linspace(1.0, 8.0, hd2).astype(np.float32)))
     tensors += [("output_norm.weight", (n_embd,), GGML_F32, ones),
                 ("output.weight", (n_embd, n_vocab), t_out, lambda: random_blocks(t_out, n_vocab, n_embd, rng, sig(n_embd)))]
 
