@@ -98,6 +98,7 @@ struct Ctx {
     // B200_TENSOR_DYNAMIC destinations (KV-cache stores): a device table of the current dst pointers, refreshed before every launch of a captured
     // graph, so that one CUDA graph serves every position of the cache
     char ** dyn_tab = nullptr; int dyn_i = 0; bool dyn_on = false;
+    uint64_t last_graph_key = 0;  // the CUDA graph captured last: donor of cudaGraphExecUpdate when the next capture has the same topology
     int sms = 0;
     // row split
     nccl_comm comm = nullptr; int rank = 0, world = 1;
@@ -1427,9 +1428,20 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         if (rc) { if (g) cudaGraphDestroy(g); return rc; }
         if (e != cudaSuccess) return fail(B200_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
         GraphEntry ge; ge.n_kernels = captured; ge.n_nodes = n; ge.check = check;
-        e = cudaGraphInstantiate(&ge.exec, g, 0);
+        // a decode loop re-captures the same topology with other shapes every time its cache view grows by a block: updating the executable
+        // graph captured last in place is several times cheaper than instantiating a new one (the old list is captured again if it comes back)
+        static const bool upd = !(getenv("B200_GRAPH_UPDATE") && atoi(getenv("B200_GRAPH_UPDATE")) == 0);
+        auto donor = upd && c->last_graph_key ? c->graphs.find(c->last_graph_key) : c->graphs.end();
+        if (donor != c->graphs.end() && donor->second.n_nodes == n && donor->second.n_kernels == captured) {
+            cudaGraphExecUpdateResultInfo info;
+            if (cudaGraphExecUpdate(donor->second.exec, g, &info) == cudaSuccess) ge.exec = donor->second.exec;
+            else { cudaGetLastError(); cudaGraphExecDestroy(donor->second.exec); }      // (another kernel somewhere: not the same topology after all;
+            c->graphs.erase(donor);                                                      //  a failed update may leave the donor half-updated: drop it)
+        }
+        e = ge.exec ? cudaSuccess : cudaGraphInstantiate(&ge.exec, g, 0);
         cudaGraphDestroy(g);
         if (e != cudaSuccess) return fail(B200_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+        c->last_graph_key = key;
         if (c->graphs.size() > 64) { for (auto & kv : c->graphs) cudaGraphExecDestroy(kv.second.exec); c->graphs.clear(); }
         it = c->graphs.emplace(key, ge).first;
     }
