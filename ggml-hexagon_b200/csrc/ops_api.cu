@@ -16,6 +16,7 @@
 #include <mutex>
 #include <string>
 #include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 using namespace b200;
@@ -98,6 +99,7 @@ struct Ctx {
     // B200_TENSOR_DYNAMIC destinations (KV-cache stores): a device table of the current dst pointers, refreshed before every launch of a captured
     // graph, so that one CUDA graph serves every position of the cache
     char ** dyn_tab = nullptr; int dyn_i = 0; bool dyn_on = false;
+    std::unordered_set<uint64_t> taken_over;
     uint64_t last_graph_key = 0;  // the CUDA graph captured last: donor of cudaGraphExecUpdate when the next capture has the same topology
     int sms = 0;
     // row split
@@ -1221,6 +1223,7 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
     for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
         int used = 1;
+        if (silu_mul_at >= 0 && i > silu_mul_at) { rc = fail(B200_EINVAL, "internal: node %d that carries a deferred SILU was skipped", silu_mul_at); break; }
         switch (d.op) {
             case B200_OP_NONE: break;
             case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
@@ -1431,10 +1434,13 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         // a decode loop re-captures the same topology with other shapes every time its cache view grows by a block: updating the executable
         // graph captured last in place is several times cheaper than instantiating a new one (the old list is captured again if it comes back)
         static const bool upd = !(getenv("B200_GRAPH_UPDATE") && atoi(getenv("B200_GRAPH_UPDATE")) == 0);
-        auto donor = upd && c->last_graph_key ? c->graphs.find(c->last_graph_key) : c->graphs.end();
+        // (a key whose graph was taken over before and that now comes back -- two lists alternating, or a loop that starts over -- gets an
+        //  executable graph of its own, so that lists which do recur end up replayed without any capture)
+        const bool came_back = c->taken_over.count(key) != 0;
+        auto donor = upd && !came_back && c->last_graph_key ? c->graphs.find(c->last_graph_key) : c->graphs.end();
         if (donor != c->graphs.end() && donor->second.n_nodes == n && donor->second.n_kernels == captured) {
             cudaGraphExecUpdateResultInfo info;
-            if (cudaGraphExecUpdate(donor->second.exec, g, &info) == cudaSuccess) ge.exec = donor->second.exec;
+            if (cudaGraphExecUpdate(donor->second.exec, g, &info) == cudaSuccess) { ge.exec = donor->second.exec; c->taken_over.insert(donor->first); }
             else { cudaGetLastError(); cudaGraphExecDestroy(donor->second.exec); }      // (another kernel somewhere: not the same topology after all;
             c->graphs.erase(donor);                                                      //  a failed update may leave the donor half-updated: drop it)
         }
@@ -1442,7 +1448,8 @@ extern "C" int b200_graph_compute(b200_handle h, const b200_node * nodes, int32_
         cudaGraphDestroy(g);
         if (e != cudaSuccess) return fail(B200_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
         c->last_graph_key = key;
-        if (c->graphs.size() > 64) { for (auto & kv : c->graphs) cudaGraphExecDestroy(kv.second.exec); c->graphs.clear(); }
+        if (c->graphs.size() > 64) { for (auto & kv : c->graphs) cudaGraphExecDestroy(kv.second.exec); c->graphs.clear(); c->taken_over.clear(); }
+        if (c->taken_over.size() > 4096) c->taken_over.clear();
         it = c->graphs.emplace(key, ge).first;
     }
     static const bool time_it = getenv("B200_GRAPH_TIME") != nullptr;          // development: device time of each replay, to stderr

@@ -26,6 +26,8 @@ run ub8 -p 64 -n 8 -b 8 -ub 8
 run pg -p 0 -n 0 -pg 512,64
 run fa1 -p 64 -n 16 -fa 1
 run nkvo_q8 -p 64 -n 16 -nkvo 1 -ctk q8_0
+# the cDSP admission table alone (MUL_MAT / ADD / RMS_NORM / SOFT_MAX offloaded, the rest on ggml-cpu, KV cache on the host)
+B200_GRAPH_OPS=0 run cdsp_table -p 512 -n 128 -nkvo 1
 # Llama-3.1-style frequency factors: ROPE with a third operand stays on the device
 python $HERE/tools/make_gguf.py $M --preset 7b --rope-freqs 2> /dev/null || exit 1
 run ropefreqs -p 512 -n 64
