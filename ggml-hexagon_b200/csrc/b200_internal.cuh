@@ -150,6 +150,15 @@ cudaError_t launch_unpack_f16(int type, const WPtrs & w, long long nblocks, __ha
 // res_dst != null: also res_dst[i] = res_src[i] + out[i] over [N][M] contiguous (the residual ADD node behind the MUL_MAT, fused)
 cudaError_t launch_reduce_splits(const float * ws, int S, long long MN, int M, float * out, long long out_cs, int add_to_out, cudaStream_t st,
                                  const float * res_src = nullptr, float * res_dst = nullptr, void * act_out = nullptr);
+// a producer of a dense GEMM's src1 that also converts it (gemm_dense.cu row_act_kernel): mode 0 RMS_NORM * w, 1 SILU(a) * b, 2 gather (CONT)
+constexpr int ROW_ACT_MAX_K = 14 * 1024;
+struct RowActArgs {
+    const char * a; const char * b; char * y; void * act; float * colscale;
+    long long as, bs, ys;         // byte strides between rows of a, b (mode 1), y
+    int K; float eps;
+    long long nes[4], nbs[4];     // mode 2: logical shape and byte strides of the source
+};
+cudaError_t launch_row_act(int mode, const RowActArgs & p, int N, cudaStream_t st);
 bool reduce_splits_can_fuse_residual(long long M, long long out_cs, const void * out, const void * res_src, const void * res_dst);
 // ---- dense prefill GEMM (gemm_dense.cu): block scales folded into fp16 operands, the whole K accumulated in TMEM
 cudaError_t launch_dequant_act_f16(const float * x, long long row_stride_bytes, int K, int N, __half * out, float * colscale, cudaStream_t st);

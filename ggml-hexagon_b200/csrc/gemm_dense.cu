@@ -908,6 +908,100 @@ cudaError_t launch_reduce_splits_act(const float * ws, int S, int M, int N, floa
     return cudaLaunchKernelEx(&cfg, reduce_splits4_act_kernel, (const float4 *) ws, S, (long long) M * N / 4, M / 4, (float4 *) out, out_cs / 4,
                               (const float4 *) res_src, (float4 *) res_dst, (uint2 *) act_out, colscale_out);
 }
+// ---- producers of a dense GEMM's src1 that also write its converted form (ops_api.cu, the Llama-layer fusions at many columns):
+// one CTA per column n; the column's K floats are produced, written, kept in registers, then converted exactly as dequant_act_f16_kernel
+// would convert them after reading them back (column amax -> power-of-two scale -> fp16(d q 2^g) per 32-element block).
+//   MODE 0  y = fl(fl(x * rsqrt(mean(x^2) + eps)) * w)      RMS_NORM followed by the in-place MUL with the norm weight
+//   MODE 1  y = fl(silu(g) * u)                              SwiGLU gate
+//   MODE 2  y = gather of 16-byte pieces                     CONT (head merge): source strides in `nes / nbs`
+template <int MODE, int NV>
+__global__ void __launch_bounds__(256)
+row_act_kernel(const RowActArgs p) {
+    __shared__ float sh[8];
+    __shared__ double shd[8];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const long long n = blockIdx.x;
+    const int K4 = p.K >> 2;
+    float4 * yr = (float4 *) (p.y + n * p.ys);
+    float scale = 0.f;
+    if (MODE == 0) {
+        const float4 * xr = (const float4 *) (p.a + n * p.as);
+        double sum = 0.0;
+        for (int i = threadIdx.x; i < K4; i += 256) {
+            const float4 v = xr[i];
+            sum += (double) __fmul_rn(v.x, v.x) + (double) __fmul_rn(v.y, v.y) + (double) __fmul_rn(v.z, v.z) + (double) __fmul_rn(v.w, v.w);
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if ((threadIdx.x & 31) == 0) shd[threadIdx.x >> 5] = sum;
+        __syncthreads();
+        sum = shd[0];
+        for (int i = 1; i < 8; i++) sum += shd[i];
+        const float mean = (float) (sum / (double) p.K);
+        scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, p.eps)));
+    }
+    float4 z[NV];
+    float amax = 0.0f;
+    #pragma unroll
+    for (int it = 0; it < NV; it++) {
+        const int i = it * 256 + threadIdx.x;
+        z[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < K4) {
+            float4 r;
+            if (MODE == 0) {
+                const float4 v = ((const float4 *) (p.a + n * p.as))[i], g = ((const float4 *) p.b)[i];
+                r = make_float4(__fmul_rn(__fmul_rn(v.x, scale), g.x), __fmul_rn(__fmul_rn(v.y, scale), g.y), __fmul_rn(__fmul_rn(v.z, scale), g.z), __fmul_rn(__fmul_rn(v.w, scale), g.w));
+            } else if (MODE == 1) {
+                const float4 a = ((const float4 *) (p.a + n * p.as))[i], b = ((const float4 *) (p.b + n * p.bs))[i];
+                r.x = __fmul_rn(__fdiv_rn(a.x, __fadd_rn(1.0f, expf(-a.x))), b.x); r.y = __fmul_rn(__fdiv_rn(a.y, __fadd_rn(1.0f, expf(-a.y))), b.y);
+                r.z = __fmul_rn(__fdiv_rn(a.z, __fadd_rn(1.0f, expf(-a.z))), b.z); r.w = __fmul_rn(__fdiv_rn(a.w, __fadd_rn(1.0f, expf(-a.w))), b.w);
+            } else {
+                long long t = (n * p.K + (long long) i * 4);                      // logical element index of the source
+                const long long s0 = t % p.nes[0]; t /= p.nes[0];
+                const long long s1 = t % p.nes[1]; t /= p.nes[1];
+                const long long s2 = t % p.nes[2]; const long long s3 = t / p.nes[2];
+                r = *(const float4 *) ((const char *) p.a + s0 * 4 + s1 * p.nbs[1] + s2 * p.nbs[2] + s3 * p.nbs[3]);
+            }
+            z[it] = r; yr[i] = r;
+            amax = fmaxf(amax, fmaxf(fmaxf(fabsf(r.x), fabsf(r.y)), fmaxf(fabsf(r.z), fabsf(r.w))));
+        }
+    }
+    float inv;
+    const float sc = gd_col_scale(gd_block_max<8>(amax, sh), &inv);
+    if (threadIdx.x == 0) p.colscale[n] = inv;
+    uint2 * o = (uint2 *) p.act + n * K4;
+    #pragma unroll
+    for (int it = 0; it < NV; it++) {
+        if (it * 256 < K4) {                                // (uniform: the shuffles inside want whole warps)
+            const int i = it * 256 + threadIdx.x;
+            const uint2 h = gd_q8_1_f16x4(z[it], sc);
+            if (i < K4) o[i] = h;
+        }
+    }
+}
+template <int MODE>
+static cudaError_t launch_row_act_m(const RowActArgs & p, int N, cudaStream_t st) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) N); cfg.blockDim = dim3(256); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
+    const int nv = (p.K / 4 + 255) / 256;
+    if (nv <= 4)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 4>, p);
+    if (nv <= 8)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 8>, p);
+    if (nv <= 11) return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 11>, p);
+    return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 14>, p);
+}
+// K % 32 == 0, K <= ROW_ACT_MAX_K, every row 16-byte aligned; act: fp16 [N][K], colscale: [N] (the layout launch_dequant_act_f16 writes)
+cudaError_t launch_row_act(int mode, const RowActArgs & p, int N, cudaStream_t st) {
+    if (N <= 0 || p.K <= 0) return cudaSuccess;
+    if (p.K % 32 != 0 || p.K > ROW_ACT_MAX_K || ((uintptr_t) p.act & 7) != 0) return cudaErrorInvalidValue;
+    if (mode == 0) return launch_row_act_m<0>(p, N, st);
+    if (mode == 1) return launch_row_act_m<1>(p, N, st);
+    return launch_row_act_m<2>(p, N, st);
+}
 // ---- stream-K tail: dst tile = sum of the tail_ws slots of the chunks that cover it, in chunk order
 struct GdFixArgs {
     const float * ws; int tail_T, tail_L, nks, full_tiles, ntiles, bn, N;

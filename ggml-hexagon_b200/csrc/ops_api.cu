@@ -1103,6 +1103,18 @@ static bool reads_vec_q(const b200_node & nd, const void * x, int64_t K) {
            nd.src1.ne[0] == K && nd.src1.ne[1] == 1 && nd.src1.ne[2] == 1 && nd.src1.ne[3] == 1 && nd.src1.nb[0] == 4;
 }
 static void set_qcache(Ctx * c, const b200_tensor & d) { c->q_ptr = d.data; c->q_K = d.ne[0]; c->q_N = 1; c->q_stride = d.nb[1]; c->q_kind = 0; }
+// a dense-GEMM MUL_MAT that reads the N columns x[K] (rows K * 4 bytes apart) next: its fp16 activations + column scales can be written by the
+// producer of x (gemm_dense.cu row_act_kernel).  Returns the scratch to write into (room made), or NULL.
+static bool reads_cols_dense(Ctx * c, const b200_node & nd, const void * x, int64_t K, int64_t N) {
+    return gemm_dense_enabled() && is_dense_mulmat(c, nd) && nd.src1.type == T_F32 && nd.src1.data == x && nd.src0.ne[0] == K && nd.src1.ne[0] == K &&
+           nd.src1.ne[1] == N && nd.src1.nb[1] == K * 4 && K % 32 == 0 && K <= ROW_ACT_MAX_K;
+}
+static int dense_act_room(Ctx * c, int64_t N, int64_t K, void ** act, float ** cs) {
+    int rc = ensure_buf(c, &c->gm_qb, &c->gm_qb_cap, dense_act_bytes(N, K)); if (rc) return rc;
+    *act = c->gm_qb; *cs = (float *) (c->gm_qb + dense_act_cs_off(N, K));
+    return 0;
+}
+static void set_qcache_dense(Ctx * c, const void * x, int64_t K, int64_t N) { c->q_ptr = x; c->q_K = K; c->q_N = N; c->q_stride = K * 4; c->q_kind = 1; }
 // RMS_NORM x -> X ; MUL X, w -> X (in place, w one row): one kernel; [+ q8_1 of X when a vector MUL_MAT reads it next]
 static int try_rms_norm_mul(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
     if (!graph_fuse_enabled() || c->rs_on || i + 1 >= n) return 0;
@@ -1116,6 +1128,17 @@ static int try_rms_norm_mul(Ctx * c, const b200_node * nodes, int i, int n, int 
     if (!al16(r.src0.data) || !al16(r.dst.data) || !al16(m.src1.data) || (r.src0.nb[1] & 15) || (r.dst.nb[1] & 15)) return 0;
     const float eps = f32_param(&r.dst, 0);
     if (!(eps >= 0.0f)) return 0;
+    if (rows > 1 && i + 2 < n && r.dst.nb[1] == ne00 * 4 && reads_cols_dense(c, nodes[i + 2], r.dst.data, ne00, rows)) {
+        void * act; float * cs; int rc = dense_act_room(c, rows, ne00, &act, &cs); if (rc) return rc;
+        RowActArgs a{};
+        a.a = (const char *) r.src0.data; a.as = r.src0.nb[1]; a.b = (const char *) m.src1.data; a.y = (char *) r.dst.data; a.ys = r.dst.nb[1];
+        a.act = act; a.colscale = cs; a.K = (int) ne00; a.eps = eps;
+        CU(launch_row_act(0, a, (int) rows, c->st)); c->launches++;
+        wrote(c, &r.dst);
+        set_qcache_dense(c, r.dst.data, ne00, rows);
+        *used = 2;
+        return 0;
+    }
     const bool quant = rows == 1 && ne00 % 128 == 0 && i + 2 < n && reads_vec_q(nodes[i + 2], r.dst.data, ne00);
     if (quant) { int rc = ensure_act(c, ne00 / 32); if (rc) return rc; }
     CU(launch_rms_norm_mul((const float *) r.src0.data, (const float *) m.src1.data, (float *) r.dst.data, ne00, rows, r.src0.nb[1] / 4, r.dst.nb[1] / 4, eps,
@@ -1123,6 +1146,20 @@ static int try_rms_norm_mul(Ctx * c, const b200_node * nodes, int i, int n, int 
     wrote(c, &r.dst);
     if (quant) set_qcache(c, m.dst);
     *used = 2;
+    return 0;
+}
+// SILU(G) * U -> X for N > 1 columns of K that a dense GEMM reads next: one kernel that also converts X; false = not that case
+static int silu_mul_cols(Ctx * c, const b200_node * nodes, int next, int n, const b200_tensor & x, const void * g, const void * u, bool * done) {
+    *done = false;
+    const int64_t K = x.ne[0], N = x.ne[1];
+    if (N <= 1 || x.ne[2] != 1 || x.ne[3] != 1 || next >= n || !reads_cols_dense(c, nodes[next], x.data, K, N)) return 0;
+    void * act; float * cs; int rc = dense_act_room(c, N, K, &act, &cs); if (rc) return rc;
+    RowActArgs a{};
+    a.a = (const char *) g; a.as = K * 4; a.b = (const char *) u; a.bs = K * 4; a.y = (char *) x.data; a.ys = K * 4; a.act = act; a.colscale = cs; a.K = (int) K;
+    CU(launch_row_act(1, a, (int) N, c->st)); c->launches++;
+    wrote(c, &x);
+    set_qcache_dense(c, x.data, K, N);
+    *done = true;
     return 0;
 }
 // SILU G -> X ; [MUL_MAT ... -> U] ; MUL X, U -> X (in place): the SILU is folded into the MUL; [+ q8_1 of X for the vector MUL_MAT that follows]
@@ -1146,6 +1183,8 @@ static int try_silu_mul(Ctx * c, const b200_node * nodes, int i, int n, int * us
     if (tot % 4 || !al16(sn.src0.data) || !al16(sn.dst.data) || !al16(m.src1.data)) return 0;
     if (overlap(m.src1.data, tot * 4, sn.dst.data, tot * 4)) return 0;
     if (j == i + 1) {           // adjacent: run the fused kernel now
+        bool done = false; int rc0 = silu_mul_cols(c, nodes, j + 1, n, m.dst, sn.src0.data, m.src1.data, &done); if (rc0) return rc0;
+        if (done) { *used = 2; return 0; }
         const int64_t K = sn.dst.ne[0];
         const bool quant = tot == K && K % 128 == 0 && j + 1 < n && reads_vec_q(nodes[j + 1], m.dst.data, K);
         if (quant) { int rc = ensure_act(c, K / 32); if (rc) return rc; }
@@ -1201,6 +1240,20 @@ static int try_cont_quant(Ctx * c, const b200_node * nodes, int i, int n, int * 
     const b200_node & cn = nodes[i];
     if (cn.src0.type != T_F32 || cn.dst.type != T_F32 || (cn.dst.flags & B200_TENSOR_DYNAMIC)) return 0;
     const int64_t K = cn.dst.ne[0];
+    if (cn.dst.ne[1] > 1 && cn.dst.ne[2] == 1 && cn.dst.ne[3] == 1 && contiguous_f32_t(&cn.dst) && nelems(&cn.src0) == nelems(&cn.dst) &&
+        cn.src0.nb[0] == 4 && cn.src0.ne[0] % 4 == 0 && al16(cn.src0.data) && al16(cn.dst.data) && !((cn.src0.nb[1] | cn.src0.nb[2] | cn.src0.nb[3]) & 15) &&
+        reads_cols_dense(c, nodes[i + 1], cn.dst.data, K, cn.dst.ne[1])) {
+        const int64_t N = cn.dst.ne[1];
+        void * act; float * cs; int rc = dense_act_room(c, N, K, &act, &cs); if (rc) return rc;
+        RowActArgs a{};
+        a.a = (const char *) cn.src0.data; a.y = (char *) cn.dst.data; a.ys = K * 4; a.act = act; a.colscale = cs; a.K = (int) K;
+        for (int k = 0; k < 4; k++) { a.nes[k] = cn.src0.ne[k]; a.nbs[k] = cn.src0.nb[k]; }
+        CU(launch_row_act(2, a, (int) N, c->st)); c->launches++;
+        wrote(c, &cn.dst);
+        set_qcache_dense(c, cn.dst.data, K, N);
+        *used = 1;
+        return 0;
+    }
     if (nelems(&cn.dst) != K || nelems(&cn.src0) != K || K % 128 || !contiguous_f32_t(&cn.dst) || !reads_vec_q(nodes[i + 1], cn.dst.data, K)) return 0;
     if (cn.src0.nb[0] != 4 || cn.src0.ne[0] % 4 || !al16(cn.src0.data) || !al16(cn.dst.data) || ((cn.src0.nb[1] | cn.src0.nb[2] | cn.src0.nb[3]) & 15)) return 0;
     int rc = ensure_act(c, K / 32); if (rc) return rc;
@@ -1236,6 +1289,9 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
             case B200_OP_MUL:
                 if (i == silu_mul_at) {         // SILU(G) * U -> X; G is the skipped SILU's input, X its output = this node's src0 = dst
                     const b200_node & sn = nodes[i - 2];
+                    silu_mul_at = -1;
+                    bool done = false; rc = silu_mul_cols(c, nodes, i + 1, n, d, sn.src0.data, nodes[i].src1.data, &done);
+                    if (rc || done) break;
                     const int64_t K = d.ne[0], tot = nelems(&d);
                     const bool quant = tot == K && K % 128 == 0 && i + 1 < n && reads_vec_q(nodes[i + 1], d.data, K);
                     if (quant) rc = ensure_act(c, K / 32);

@@ -184,7 +184,7 @@ def _mask(N, head, n_kv):
 
 
 @pytest.mark.parametrize("t", [GA.Q4_0, GA.Q6_K])
-@pytest.mark.parametrize("N,head,n_kv", [(1, 37, 64), (48, 0, 64), (5, 20, 32)])
+@pytest.mark.parametrize("N,head,n_kv", [(1, 37, 64), (48, 0, 64), (5, 20, 32), (64, 0, 64)])
 def test_llama_stack_vs_ggml_cpu(plug, monkeypatch, t, N, head, n_kv):
     G, be, cpu = plug
     n_embd, n_head, n_ff, n_ctx, L = 1024, 8, 2816, 128, 2
