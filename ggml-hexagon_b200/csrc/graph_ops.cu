@@ -408,13 +408,17 @@ __device__ __forceinline__ uint4 mm_load_b(const char * row, const int64_t k, co
     for (int i = 0; i < 4; i++) h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
     return *(uint4 *) h;
 }
+// TN = columns per tile: 128, or 64 where 128-wide tiles would leave SMs without a CTA (V p at prefill: M = head size)
+template <int TN>
 __global__ void __launch_bounds__(256) mm_f16_tile_kernel(const MmF16Args p) {
     using namespace nvcuda;
     __shared__ __align__(32) __half As[MMT * MMLD];
-    __shared__ __align__(32) __half Bs[MMT * MMLD];
+    __shared__ __align__(32) __half Bs[TN * MMLD];
+    constexpr int NB = TN / 64;            // B chunks per thread per K step (TN rows x 4 chunks / 256 threads)
+    constexpr int NF = TN / 32;            // 16-wide fragments per warp along N
     PDL_PROLOGUE();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t m0 = (int64_t) blockIdx.x * MMT, n0 = (int64_t) blockIdx.y * MMT;
+    const int64_t m0 = (int64_t) blockIdx.x * MMT, n0 = (int64_t) blockIdx.y * TN;
     const int64_t i12 = blockIdx.z % p.ne12, i13 = blockIdx.z / p.ne12;
     const char * ab = p.a + (i12 / p.r2) * p.nba[2] + (i13 / p.r3) * p.nba[3];
     const char * bb = p.b + i12 * p.nbb[2] + i13 * p.nbb[3];
@@ -426,38 +430,38 @@ __global__ void __launch_bounds__(256) mm_f16_tile_kernel(const MmF16Args p) {
     for (int j = 0; j < 2; j++) {
         const int c = threadIdx.x + j * 256;
         rr[j] = c >> 2; kc[j] = (c & 3) * 8;
-        aok[j] = m0 + rr[j] < p.M; bok[j] = n0 + rr[j] < p.N;
+        aok[j] = m0 + rr[j] < p.M; bok[j] = j < NB && n0 + rr[j] < p.N;
         arow[j] = ab + (m0 + rr[j]) * p.nba[1]; brow[j] = bb + (n0 + rr[j]) * p.nbb[1];
     }
-    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][4];
+    wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][NF];
     #pragma unroll
     for (int i = 0; i < 2; i++)
         #pragma unroll
-        for (int j = 0; j < 4; j++) wmma::fill_fragment(acc[i][j], 0.0f);
-    const int wm = (warp >> 1) * 32, wn = (warp & 1) * 64;
+        for (int j = 0; j < NF; j++) wmma::fill_fragment(acc[i][j], 0.0f);
+    const int wm = (warp >> 1) * 32, wn = (warp & 1) * (TN / 2);
     MmStage st;
     #pragma unroll
-    for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], kc[j], p.K, aok[j], veca); st.b[j] = mm_load_b(brow[j], kc[j], p.K, bok[j], vecb); }
+    for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], kc[j], p.K, aok[j], veca); if (j < NB) st.b[j] = mm_load_b(brow[j], kc[j], p.K, bok[j], vecb); }
     for (int64_t k0 = 0; k0 < p.K; k0 += MMK) {
         #pragma unroll
-        for (int j = 0; j < 2; j++) { *(uint4 *) (As + rr[j] * MMLD + kc[j]) = st.a[j]; *(uint4 *) (Bs + rr[j] * MMLD + kc[j]) = st.b[j]; }
+        for (int j = 0; j < 2; j++) { *(uint4 *) (As + rr[j] * MMLD + kc[j]) = st.a[j]; if (j < NB) *(uint4 *) (Bs + rr[j] * MMLD + kc[j]) = st.b[j]; }
         __syncthreads();
         if (k0 + MMK < p.K) {
             #pragma unroll
-            for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], k0 + MMK + kc[j], p.K, aok[j], veca); st.b[j] = mm_load_b(brow[j], k0 + MMK + kc[j], p.K, bok[j], vecb); }
+            for (int j = 0; j < 2; j++) { st.a[j] = mm_load_a(arow[j], k0 + MMK + kc[j], p.K, aok[j], veca); if (j < NB) st.b[j] = mm_load_b(brow[j], k0 + MMK + kc[j], p.K, bok[j], vecb); }
         }
         #pragma unroll
         for (int kk = 0; kk < MMK; kk += 16) {
             wmma::fragment<wmma::matrix_a, 16, 16, 16, __half, wmma::row_major> fa[2];
-            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[4];
+            wmma::fragment<wmma::matrix_b, 16, 16, 16, __half, wmma::col_major> fb[NF];
             #pragma unroll
             for (int i = 0; i < 2; i++) wmma::load_matrix_sync(fa[i], As + (wm + i * 16) * MMLD + kk, MMLD);
             #pragma unroll
-            for (int j = 0; j < 4; j++) wmma::load_matrix_sync(fb[j], Bs + (wn + j * 16) * MMLD + kk, MMLD);
+            for (int j = 0; j < NF; j++) wmma::load_matrix_sync(fb[j], Bs + (wn + j * 16) * MMLD + kk, MMLD);
             #pragma unroll
             for (int i = 0; i < 2; i++)
                 #pragma unroll
-                for (int j = 0; j < 4; j++) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+                for (int j = 0; j < NF; j++) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
         }
         __syncthreads();
     }
@@ -466,7 +470,7 @@ __global__ void __launch_bounds__(256) mm_f16_tile_kernel(const MmF16Args p) {
     #pragma unroll
     for (int i = 0; i < 2; i++)
         #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < NF; j++) {
             wmma::store_matrix_sync(Cs, acc[i][j], 16, wmma::mem_col_major);      // Cs[n * 16 + m]
             __syncwarp();
             for (int e = lane; e < 256; e += 32) {
@@ -586,10 +590,13 @@ cudaError_t launch_mm_f16(const MmF16Args & p, cudaStream_t st) {
         if (p.N <= 4) return pdl_launch(mm_f16_vec_kernel<4>, grid, dim3(128), st, p);
         return pdl_launch(mm_f16_vec_kernel<8>, grid, dim3(128), st, p);
     } else {
-        const int64_t gy = (p.N + MMT - 1) / MMT;
+        const int64_t gx = (p.M + MMT - 1) / MMT;
+        const bool narrow = gx * ((p.N + MMT - 1) / MMT) * batch < 2 * 148;        // fewer than two CTAs per SM with 128-wide tiles
+        const int64_t gy = (p.N + (narrow ? 64 : MMT) - 1) / (narrow ? 64 : MMT);
         if (gy > 65535) return cudaErrorInvalidValue;
-        dim3 grid((unsigned) ((p.M + MMT - 1) / MMT), (unsigned) gy, (unsigned) batch);
-        return pdl_launch(mm_f16_tile_kernel, grid, dim3(256), st, p);
+        dim3 grid((unsigned) gx, (unsigned) gy, (unsigned) batch);
+        if (narrow) return pdl_launch(mm_f16_tile_kernel<64>, grid, dim3(256), st, p);
+        return pdl_launch(mm_f16_tile_kernel<128>, grid, dim3(256), st, p);
     }
     return cudaGetLastError();
 }

@@ -248,3 +248,24 @@ def test_dynamic_destination_one_graph_two_positions():
         for row in range(8):
             assert np.array_equal(got[row], want if row in (0, 1, 3, 5) else np.zeros(K, np.float16)), row
         assert np.array_equal(s.to_host(y, (K,), np.float32), x + x)
+
+
+@pytest.mark.parametrize("M,N,K,nh,nhk", [(512, 512, 128, 32, 8), (128, 512, 512, 32, 32), (100, 70, 50, 3, 1), (64, 17, 96, 2, 2), (40, 5, 128, 4, 2)])
+def test_mul_mat_f16_shapes_vs_numpy(M, N, K, nh, nhk):
+    """the f16 x f32 MUL_MAT kernels on their own (node list through the C-ABI): 128-wide tiles (>= 2 CTAs per SM), 64-wide tiles, edge tiles
+    and unaligned rows (scalar operand loads), the one-warp-per-row kernels at few columns; grouped-query broadcast (nh / nhk query heads per
+    cache head).  Reference: f32 matmul of the f16 weights with src1 rounded to f16, as ggml-cpu computes an f16 src0."""
+    rng = np.random.default_rng(M + N + K)
+    w = (rng.standard_normal((nhk, M, K)) * 0.5).astype(np.float16)
+    x = rng.standard_normal((nh, N, K)).astype(np.float32)
+    want = np.einsum("hmk,hnk->hnm", np.repeat(w, nh // nhk, axis=0).astype(np.float32), x.astype(np.float16).astype(np.float32), dtype=np.float32)
+    with B.Session(0) as s:
+        wb, xb, yb = s.to_device(w), s.to_device(x), s.malloc(4 * nh * N * M)
+        nd = B.Node()
+        a = B.f32_tensor(wb.ptr, [K, M, nhk], nb=[2, 2 * K, 2 * K * M, 2 * K * M * nhk]); a.type = B.F16; a.data_len = w.nbytes
+        nd.src0 = a
+        nd.src1 = B.f32_tensor(xb.ptr, [K, N, nh])
+        nd.dst = B.f32_tensor(yb.ptr, [M, N, nh], op=B.OP_MUL_MAT)
+        s.graph_compute([nd], use_cuda_graph=False)
+        got = s.to_host(yb, (nh, N, M), np.float32)
+    assert nmse(got, want) <= 1e-6, nmse(got, want)
