@@ -914,10 +914,12 @@ cudaError_t launch_reduce_splits_act(const float * ws, int S, int M, int N, floa
 //   MODE 0  y = fl(fl(x * rsqrt(mean(x^2) + eps)) * w)      RMS_NORM followed by the in-place MUL with the norm weight
 //   MODE 1  y = fl(silu(g) * u)                              SwiGLU gate
 //   MODE 2  y = gather of 16-byte pieces                     CONT (head merge): source strides in `nes / nbs`
-template <int MODE, int NV>
-__global__ void __launch_bounds__(256)
+// NTHR threads per column: 256 for MODE 0 (the sum of squares keeps the order of rms_norm_mul_kernel), 512 for the long SwiGLU columns, whose
+// only reduction is a max
+template <int MODE, int NV, int NTHR>
+__global__ void __launch_bounds__(NTHR)
 row_act_kernel(const RowActArgs p) {
-    __shared__ float sh[8];
+    __shared__ float sh[NTHR / 32];
     __shared__ double shd[8];
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -928,7 +930,7 @@ row_act_kernel(const RowActArgs p) {
     if (MODE == 0) {
         const float4 * xr = (const float4 *) (p.a + n * p.as);
         double sum = 0.0;
-        for (int i = threadIdx.x; i < K4; i += 256) {
+        for (int i = threadIdx.x; i < K4; i += NTHR) {
             const float4 v = xr[i];
             sum += (double) __fmul_rn(v.x, v.x) + (double) __fmul_rn(v.y, v.y) + (double) __fmul_rn(v.z, v.z) + (double) __fmul_rn(v.w, v.w);
         }
@@ -945,7 +947,7 @@ row_act_kernel(const RowActArgs p) {
     float amax = 0.0f;
     #pragma unroll
     for (int it = 0; it < NV; it++) {
-        const int i = it * 256 + threadIdx.x;
+        const int i = it * NTHR + threadIdx.x;
         z[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (i < K4) {
             float4 r;
@@ -968,13 +970,13 @@ row_act_kernel(const RowActArgs p) {
         }
     }
     float inv;
-    const float sc = gd_col_scale(gd_block_max<8>(amax, sh), &inv);
+    const float sc = gd_col_scale(gd_block_max<NTHR / 32>(amax, sh), &inv);
     if (threadIdx.x == 0) p.colscale[n] = inv;
     uint2 * o = (uint2 *) p.act + n * K4;
     #pragma unroll
     for (int it = 0; it < NV; it++) {
-        if (it * 256 < K4) {                                // (uniform: the shuffles inside want whole warps)
-            const int i = it * 256 + threadIdx.x;
+        if (it * NTHR < K4) {                                // (uniform: the shuffles inside want whole warps)
+            const int i = it * NTHR + threadIdx.x;
             const uint2 h = gd_q8_1_f16x4(z[it], sc);
             if (i < K4) o[i] = h;
         }
@@ -989,10 +991,16 @@ static cudaError_t launch_row_act_m(const RowActArgs & p, int N, cudaStream_t st
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
     const int nv = (p.K / 4 + 255) / 256;
-    if (nv <= 4)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 4>, p);
-    if (nv <= 8)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 8>, p);
-    if (nv <= 11) return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 11>, p);
-    return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 14>, p);
+    if (nv <= 4)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 4, 256>, p);
+    if (MODE != 0) {                       // long columns: twice the threads, half the serial work per thread
+        cfg.blockDim = dim3(512);
+        if (nv <= 8)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 4, 512>, p);
+        if (nv <= 12) return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 6, 512>, p);
+        return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 7, 512>, p);
+    }
+    if (nv <= 8)  return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 8, 256>, p);
+    if (nv <= 11) return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 11, 256>, p);
+    return cudaLaunchKernelEx(&cfg, row_act_kernel<MODE, 14, 256>, p);
 }
 // K % 32 == 0, K <= ROW_ACT_MAX_K, every row 16-byte aligned; act: fp16 [N][K], colscale: [N] (the layout launch_dequant_act_f16 writes)
 cudaError_t launch_row_act(int mode, const RowActArgs & p, int N, cudaStream_t st) {

@@ -105,7 +105,7 @@ soft_max_f32_kernel(const float * __restrict__ x, const void * __restrict__ mask
 }
 // rows of up to 1024 elements (attention scores at prefill: thousands of short rows): one warp per row, the row held in registers between
 // the three passes; same operations per element as the block kernel, the double sum reduced by shuffles
-template <bool MASK_F16>
+template <bool MASK_F16, int NT>
 __global__ void __launch_bounds__(256)
 soft_max_f32_warp_kernel(const float * __restrict__ x, const void * __restrict__ mask, float * __restrict__ y, const int64_t ne00, const int64_t ne01,
                          const int64_t ne02, const int64_t rows, const float scale, const float max_bias, const float m0, const float m1, const uint32_t n_head_log2) {
@@ -122,10 +122,10 @@ soft_max_f32_warp_kernel(const float * __restrict__ x, const void * __restrict__
     float * dp = y + row * ne00;
     const float * mf = mask && !MASK_F16 ? (const float *) mask + (row % ne01) * ne00 : nullptr;
     const __half * mh = mask && MASK_F16 ? (const __half *) mask + (row % ne01) * ne00 : nullptr;
-    float v[32];
+    float v[NT];                       // NT x 32 >= ne00
     float mx = -CUDART_INF_F;
     #pragma unroll
-    for (int t = 0; t < 32; t++) {
+    for (int t = 0; t < NT; t++) {
         const int64_t i = lane + 32 * t;
         v[t] = -CUDART_INF_F;
         if (i < ne00) {
@@ -139,12 +139,12 @@ soft_max_f32_warp_kernel(const float * __restrict__ x, const void * __restrict__
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     double sum = 0.0;
     #pragma unroll
-    for (int t = 0; t < 32; t++) if (lane + 32 * t < ne00) { v[t] = expf(__fsub_rn(v[t], mx)); sum += (double) v[t]; }
+    for (int t = 0; t < NT; t++) if (lane + 32 * t < ne00) { v[t] = expf(__fsub_rn(v[t], mx)); sum += (double) v[t]; }
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const float inv = (float) (1.0 / sum);
     #pragma unroll
-    for (int t = 0; t < 32; t++) if (lane + 32 * t < ne00) dp[lane + 32 * t] = __fmul_rn(v[t], inv);
+    for (int t = 0; t < NT; t++) if (lane + 32 * t < ne00) dp[lane + 32 * t] = __fmul_rn(v[t], inv);
 }
 cudaError_t launch_soft_max_f32(const float * x, const void * mask, bool mask_f16, float * y, const int64_t * ne, float scale, float max_bias, cudaStream_t st) {
     const int64_t rows = ne[1] * ne[2] * ne[3];
@@ -161,8 +161,12 @@ cudaError_t launch_soft_max_f32(const float * x, const void * mask, bool mask_f1
     cfg.attrs = at; cfg.numAttrs = gemv_pdl_enabled() ? 1 : 0;
     if (ne[0] <= 1024 && rows >= 512) {        // (fewer rows: the block kernel, whose order the one-column attention kernel of graph_ops.cu reproduces)
         cfg.gridDim = dim3((unsigned) ((rows + 7) / 8));
-        if (mask_f16) return cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<true>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2);
-        return cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<false>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2);
+#define B200_SM_WARP(NT) (mask_f16 ? cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<true, NT>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2) \
+                                   : cudaLaunchKernelEx(&cfg, soft_max_f32_warp_kernel<false, NT>, x, mask, y, ne[0], ne[1], ne[2], rows, scale, max_bias, m0, m1, n_head_log2))
+        if (ne[0] <= 256) return B200_SM_WARP(8);
+        if (ne[0] <= 512) return B200_SM_WARP(16);
+        return B200_SM_WARP(32);
+#undef B200_SM_WARP
     }
     if (mask_f16) return cudaLaunchKernelEx(&cfg, soft_max_f32_kernel<true>, x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
     return cudaLaunchKernelEx(&cfg, soft_max_f32_kernel<false>, x, mask, y, ne[0], ne[1], ne[2], scale, max_bias, m0, m1, n_head_log2);
