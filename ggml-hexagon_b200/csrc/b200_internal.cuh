@@ -191,6 +191,8 @@ struct RopeArgs {
     int64_t ne[4], nbs[4], nbd[4];
     int n_dims, neox;
     float theta_scale, freq_scale, ext_factor, attn_factor, corr0, corr1;
+    // optional second copy of the result as f16, flat in logical order (the K-cache store that follows ROPE(K)): at st_y, or where *st_dyn points
+    char * st_y; char * const * st_dyn;
 };
 cudaError_t launch_rope_f32(const RopeArgs & p, bool f16, cudaStream_t st);       // f16: both sides __half (rotated in f32)
 struct CpyArgs { const char * x; char * y; char * const * dyn /* device: where this launch's dst starts, or NULL = y */; int64_t nes[4], nbs[4], ned[4], nbd[4]; };

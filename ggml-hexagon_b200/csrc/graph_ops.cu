@@ -156,6 +156,7 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs p) {
     const int64_t half = p.ne[0] / 2;
     const int64_t total = half * p.ne[2] * p.ne[3];
     const int64_t h0 = (int64_t) blockIdx.y * ROPE_HEADS, h1 = h0 + ROPE_HEADS < p.ne[1] ? h0 + ROPE_HEADS : p.ne[1];
+    __half * const st = (__half *) (p.st_dyn ? *p.st_dyn : p.st_y);
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         int64_t t = i;
         const int64_t k = t % half; t /= half;
@@ -167,6 +168,10 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs p) {
             for (int64_t i1 = h0; i1 < h1; i1++) {
                 const T * sr = (const T *) (s + i1 * p.nbs[1]); T * dr = (T *) (d + i1 * p.nbd[1]);
                 dr[i0] = sr[i0]; dr[i0 + 1] = sr[i0 + 1];
+                if (st) {
+                    const int64_t row = ((i3 * p.ne[2] + i2) * p.ne[1] + i1) * p.ne[0];
+                    st[row + i0] = __float2half_rn(cvt_el<T, float>(sr[i0])); st[row + i0 + 1] = __float2half_rn(cvt_el<T, float>(sr[i0 + 1]));
+                }
             }
             continue;
         }
@@ -186,8 +191,13 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs p) {
         for (int64_t i1 = h0; i1 < h1; i1++) {
             const T * sr = (const T *) (s + i1 * p.nbs[1]); T * dr = (T *) (d + i1 * p.nbd[1]);
             const float x0 = cvt_el<T, float>(sr[a]), x1 = cvt_el<T, float>(sr[b]);
-            dr[a] = cvt_el<float, T>(__fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)));
-            dr[b] = cvt_el<float, T>(__fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c)));
+            const float r0 = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn)), r1 = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+            dr[a] = cvt_el<float, T>(r0);
+            dr[b] = cvt_el<float, T>(r1);
+            if (st) {                                                    // the f16 cache row, element (a | b, i1, i2, i3) at its logical index
+                const int64_t row = ((i3 * p.ne[2] + i2) * p.ne[1] + i1) * p.ne[0];
+                st[row + a] = __float2half_rn(r0); st[row + b] = __float2half_rn(r1);
+            }
         }
     }
 }

@@ -461,7 +461,7 @@ static int unary_dev(Ctx * c, const b200_tensor * s, b200_tensor * d) {
     wrote(c, d);
     return 0;
 }
-static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, const b200_tensor * ff, b200_tensor * d) {
+static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, const b200_tensor * ff, b200_tensor * d, char * st_y = nullptr, char * const * st_dyn = nullptr) {
     const bool f16 = s->type == T_F16;
     if ((s->type != T_F32 && s->type != T_F16) || d->type != s->type || pos->type != T_I32) return fail(B200_ENOTSUP, "rope: f32 or f16 data (same on both sides), i32 positions");
     const int64_t es = f16 ? 2 : 4;
@@ -486,6 +486,7 @@ static int rope_dev(Ctx * c, const b200_tensor * s, const b200_tensor * pos, con
     // ggml_rope_yarn_corr_dims (ggml.c:3741-3753)
     auto corr = [&](float n_rot) { return n_dims * logf(n_ctx_orig / (n_rot * 2 * 3.14159265358979323846f)) / (2 * logf(freq_base)); };
     a.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); a.corr1 = fminf((float) (n_dims - 1), ceilf(corr(beta_slow)));
+    a.st_y = st_y; a.st_dyn = st_dyn;
     CU(launch_rope_f32(a, f16, c->st)); c->launches++;
     wrote(c, d);
     return 0;
@@ -1234,6 +1235,33 @@ static int try_attn_decode(Ctx * c, const b200_node * nodes, int i, int n, int *
     *used = 3;
     return 0;
 }
+// ROPE -> X (f32, contiguous) ... CPY X -> f16 cache rows, flat (llama-graph.cpp:1341-1345, with the V projection ordered in between): the
+// ROPE kernel stores the f16 row as well and the CPY node is skipped when the loop reaches it.  `*cpy_at` = index of that node, `*slot` =
+// its position among the list's dynamic destinations.
+static bool rope_store_target(Ctx * c, const b200_node * nodes, int i, int n, int * cpy_at, int * slot) {
+    if (!graph_fuse_enabled() || c->rs_on) return false;
+    const b200_node & r = nodes[i];
+    if (r.dst.type != T_F32 || !contiguous_f32_t(&r.dst)) return false;
+    const int64_t E = nelems(&r.dst);
+    int ndyn = 0;
+    for (int j = i + 1; j < n && j <= i + 4; j++) {
+        const b200_node & x = nodes[j];
+        if (x.dst.op == B200_OP_CPY && x.src0.data == r.dst.data) {
+            if (x.src0.type != T_F32 || x.dst.type != T_F16 || nelems(&x.src0) != E || nelems(&x.dst) != E || !contiguous_f32_t(&x.src0)) return false;
+            int64_t st = 2;                                   // dst: f16, contiguous in logical order
+            for (int k = 0; k < 4; k++) { if (x.dst.ne[k] != 1 && x.dst.nb[k] != st) return false; st *= x.dst.ne[k]; }
+            if (overlap(x.dst.data, E * 2, r.dst.data, E * 4) || overlap(x.dst.data, E * 2, r.src0.data, E * 4)) return false;
+            *cpy_at = j; *slot = ndyn;
+            return true;
+        }
+        // what may sit in between: a vector / matrix MUL_MAT over quantised weights that touches neither X nor the cache rows
+        if (x.dst.op != B200_OP_MUL_MAT || !is_qweight(x.src0.type) || x.src1.data == r.dst.data) return false;
+        int64_t span = 4; for (int k = 0; k < 4; k++) span += (x.dst.ne[k] - 1) * x.dst.nb[k];
+        if (overlap(x.dst.data, span, r.dst.data, E * 4)) return false;
+        if (x.dst.flags & B200_TENSOR_DYNAMIC) ndyn++;
+    }
+    return false;
+}
 // CONT -> contiguous X[K] read next by a vector MUL_MAT: copy + q8_1 in one kernel
 static int try_cont_quant(Ctx * c, const b200_node * nodes, int i, int n, int * used) {
     if (!graph_fuse_enabled() || c->rs_on || i + 1 >= n) return 0;
@@ -1273,10 +1301,12 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
     c->in_graph = true; c->q_ptr = nullptr; c->rs_ops = 0; c->dyn_i = 0;
     int rc = 0;
     int silu_mul_at = -1;            // index of a MUL node that also applies the SILU skipped two nodes earlier (try_silu_mul)
+    int cpy_done_at = -1;            // index of a CPY node whose store the ROPE before it has already done (rope_store_target)
     for (int i = 0; i < n && !rc; ) {
         b200_tensor d = nodes[i].dst;
         int used = 1;
         if (silu_mul_at >= 0 && i > silu_mul_at) { rc = fail(B200_EINVAL, "internal: node %d that carries a deferred SILU was skipped", silu_mul_at); break; }
+        if (cpy_done_at >= 0 && i > cpy_done_at) { rc = fail(B200_EINVAL, "internal: the CPY node %d whose store was done early was never reached", cpy_done_at); break; }
         switch (d.op) {
             case B200_OP_NONE: break;
             case B200_OP_ADD: rc = add_dev(c, &nodes[i].src0, &nodes[i].src1, &d); break;
@@ -1306,8 +1336,23 @@ static int run_nodes(Ctx * c, const b200_node * nodes, int n) {
                 int u = 0, dm = -1; rc = try_silu_mul(c, nodes, i, n, &u, &dm);
                 if (!rc && u) { used = u; if (dm >= 0) silu_mul_at = dm; } else if (!rc) rc = unary_dev(c, &nodes[i].src0, &d);
             } break;
-            case B200_OP_ROPE:     rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &nodes[i].src2, &d); break;
+            case B200_OP_ROPE: {
+                int at = -1, slot = 0;
+                if (cpy_done_at < 0 && rope_store_target(c, nodes, i, n, &at, &slot)) {
+                    const b200_tensor & cd = nodes[at].dst;
+                    const bool dyn = (cd.flags & B200_TENSOR_DYNAMIC) && c->dyn_on;
+                    if (dyn && c->dyn_i + slot >= DYN_MAX) { rc = fail(B200_ENOTSUP, "more than %d dynamic destinations in one node list", DYN_MAX); break; }
+                    rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &nodes[i].src2, &d, (char *) cd.data, dyn ? c->dyn_tab + c->dyn_i + slot : nullptr);
+                    // (the store lands in the cache tensor whatever the position: the quantised activations q / k / v share stay valid across it)
+                    if (!rc) { cpy_done_at = at; wrote(c, &cd); }
+                } else rc = rope_dev(c, &nodes[i].src0, &nodes[i].src1, &nodes[i].src2, &d);
+            } break;
             case B200_OP_DUP: case B200_OP_CONT: case B200_OP_CPY: {    // (ggml_cpy(a, b): the node is a view of b, so dst carries b's layout)
+                if (i == cpy_done_at) {          // stored by the ROPE that produced its source; only its slot in the dynamic table is consumed
+                    if (d.flags & B200_TENSOR_DYNAMIC) c->dyn_i++;
+                    cpy_done_at = -1;
+                    break;
+                }
                 int u = 0; if (d.op == B200_OP_CONT) rc = try_cont_quant(c, nodes, i, n, &u);
                 if (!rc && !u) rc = cpy_dev(c, &nodes[i].src0, &d);
             } break;
