@@ -2,7 +2,9 @@
 // src/llama-graph.cpp:1126-1216, :1306-1420): MUL (norm weight, gate*up), UNARY SILU, ROPE, CPY / CONT (KV-cache store, head merge),
 // GET_ROWS f32 (output rows), and the f16 x f32 MUL_MAT of attention (K and V live in the cache as f16).  The cDSP backend leaves all of
 // them to ggml-cpu; here that would cost a scheduler split with a host round trip after every MUL_MAT (8(f) rank 2-3 of SURVEY.md), so
-// they run on the device as plain HBM-bound kernels and the whole layer stack stays one split.
+// they run on the device as plain HBM-bound kernels and the whole layer stack stays one split.  Also here: the kernels ops_api.cu's graph-level
+// fusions launch instead of pairs / triples of the above (RMS_NORM * weight, SILU * up, CONT, each with the q8_1 write for the vector MUL_MAT that
+// follows; ROPE with the f16 K-cache store; K^T q -> soft_max -> V p of one query column), every one of them bit-equal to what it replaces.
 // Specifications (ggml-cpu): binary-ops.cpp:50-117 (MUL), unary-ops.cpp / ggml_silu_f32, ggml_compute_forward_rope_f32
 // (ggml-cpu.c:8708-8889; cache init :8634-8648, YaRN :8610-8632), ggml_compute_forward_dup (:3164-4010: element i of src in logical order
 // -> element i of dst in logical order), ggml_compute_forward_get_rows_f32 (:7853-7892), ggml_compute_forward_mul_mat with an f16 src0
