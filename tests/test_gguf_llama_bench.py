@@ -21,7 +21,7 @@ def _bench_exe():
     return exe
 
 
-@pytest.mark.parametrize("typ,extra", [("q4_0", []), ("q8_0", []), ("q4_K", ["--out-type", "q6_K"])])
+@pytest.mark.parametrize("typ,extra", [("q4_0", []), ("q8_0", []), ("q4_K", ["--out-type", "q6_K"]), ("q4_0", ["--rope-freqs"]), ("q4_K", ["--kmix"])])
 def test_tiny_gguf_loads_and_runs_on_the_reference_cpu_backend(tmp_path, typ, extra):
     exe = _bench_exe()
     gguf = str(tmp_path / "tiny.gguf")
